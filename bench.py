@@ -1,0 +1,411 @@
+#!/usr/bin/env python
+"""bench.py -- panorama frames/sec of the warp + composite hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload cfg3]
+
+A "step" is one pass of the hot path over one batch of synthetic input: `--frames-per-step`
+panorama frames (default 64), cycling through a ring of 8 distinct frame sets per camera, so the
+inputs of consecutive launches never sit in L2 (ring of 8 x (sources + canvas) = 1.19 GB at cfg3,
+L2 is 126 MB).
+
+Printed JSON (one line, rank 0):
+  value      frames/sec, whole job (all ranks), inputs and canvases resident in HBM;
+  e2e        the same metric through bs_submit/bs_wait with pinned HOST buffers, H2D and D2H copies
+             inside the timed region;
+  roofline   algorithmic bytes per frame / average kernel-launch duration (CUDA events on the
+             launching stream) against the measured HBM peak of MEASURED_PEAKS.json;
+  cpu_baseline  the reference's OpenCV path (cv2.warpPerspective, same call as
+             /root/reference/tools/stitch/main.cpp:150-151) on this box's host cores;
+  clocks     SM clock and throttle reasons sampled during the timed regions.
+
+--impl reference times that OpenCV CPU path alone (a step = one panorama frame).
+Multi-GPU: one process per GPU under torchrun, frames sharded frame-parallel, no data-path
+collective; torch.distributed is used only for the barrier and the max-over-ranks time.
+"""
+import argparse
+import hashlib
+import importlib
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+RING = 8
+METRIC = "panorama_frames_per_sec"
+UNIT = "frames/s"
+FALLBACK_HBM_GBS = 6650.0   # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=40)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg3", choices=["cfg2", "cfg3", "cfg5", "cfg1"])
+    ap.add_argument("--content", default="noise", choices=["noise", "smooth"])
+    ap.add_argument("--frames-per-step", type=int, default=64)
+    ap.add_argument("--e2e-frames-per-step", type=int, default=8)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0,
+                    help="bound on the cpu_baseline sample (wall seconds)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--flags", type=int, default=0, help="BS_FLAG_* for the handle (debug)")
+    return ap.parse_args()
+
+
+def workload_text(w):
+    return (f"{w.name}: {w.n_cams}x{w.src_wh[0]}x{w.src_wh[1]} BGR u8 -> {w.canvas_wh[0]}x{w.canvas_wh[1]} "
+            f"panorama (BASELINE.json configs, SURVEY.md App. B.2 homographies)")
+
+
+# ------------------------------------------------------------------------------------------
+# CPU reference: the OpenCV call the reference makes, through cv2; the C port only if cv2 is
+# not importable on this box.
+# ------------------------------------------------------------------------------------------
+class CpuReference:
+    def __init__(self, w, content):
+        wl = importlib.import_module("image-stitching_b200.workloads")
+        import numpy as np
+        self.np = np
+        self.w = w
+        self.frames = [[wl.gen_frame_numpy(w.src_wh[0], w.src_wh[1], i, f, content)
+                        for i in range(w.n_cams)] for f in range(2)]
+        self.canvas = np.zeros((w.canvas_wh[1], w.canvas_wh[0], 3), np.uint8)
+        try:
+            import cv2
+            self.cv2 = cv2
+            cv2.setNumThreads(cv2.getNumberOfCPUs())
+            self.cores = int(cv2.getNumThreads())
+            self.kind = "reference"
+            self.what = f"cv2 {cv2.__version__} warpPerspective(INTER_LINEAR, BORDER_TRANSPARENT)"
+        except Exception:   # pragma: no cover - cv2 ships in this image
+            import oracle
+            self.cv2 = None
+            self.oracle = oracle
+            self.cores = oracle.default_threads()
+            self.kind = "port"
+            self.what = "oracle/warp_oracle.c (OpenMP)"
+
+    def one_frame(self, f):
+        w = self.w
+        self.canvas[:] = 0
+        srcs = self.frames[f % len(self.frames)]
+        if self.cv2 is not None:
+            for s, H in zip(srcs, w.H):
+                self.cv2.warpPerspective(s, H, w.canvas_wh, dst=self.canvas, flags=self.cv2.INTER_LINEAR,
+                                         borderMode=self.cv2.BORDER_TRANSPARENT)
+        else:
+            for s, H in zip(srcs, w.H):
+                self.oracle.warp_perspective(s, H, self.canvas, nthreads=self.cores)
+        return self.canvas
+
+    def time_frames(self, n_warm, n, budget_s=None):
+        for i in range(n_warm):
+            self.one_frame(i)
+        t0 = time.perf_counter()
+        done = 0
+        for i in range(n):
+            self.one_frame(i)
+            done += 1
+            if budget_s is not None and time.perf_counter() - t0 > budget_s:
+                break
+        dt = time.perf_counter() - t0
+        return done, dt
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    wl = importlib.import_module("image-stitching_b200.workloads")
+    w = wl.get(args.workload)
+    ref = CpuReference(w, args.content)
+    done, dt = ref.time_frames(args.warmup, args.steps)
+    fps = done / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * dt / done, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_text(w), "content": args.content,
+                   "step": "one panorama frame on the host cores (bounded sample of the workload)"},
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
+                         "sample": f"{done} frames of {w.name}, {ref.what}"},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+        0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+        0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._h = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                for bit, name in self.REASONS.items():
+                    if r & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.005)
+
+    def __enter__(self):
+        if self._h is not None:
+            self._stop.clear()
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        return self
+
+    def __exit__(self, *a):
+        if self._thread is not None:
+            self._stop.set()
+            self._thread.join()
+            self._thread = None
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def physical_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            return local_rank
+    return local_rank
+
+
+# ------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------
+def run_b200(args, rank, local_rank, world):
+    import numpy as np
+    import torch
+    pkg = importlib.import_module("image-stitching_b200")
+    wl = importlib.import_module("image-stitching_b200.workloads")
+    if not torch.cuda.is_available() or pkg.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback "
+                         "(use --impl reference for the host baseline)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    w = wl.get(args.workload)
+    n = w.n_cams
+    sw, sh = w.src_wh
+    W, H = w.canvas_wh
+    B = args.frames_per_step
+
+    # ring of RING frame sets per camera, distinct per rank (frame f -> GPU f mod world)
+    d_frames = [[wl.gen_frame_torch(sw, sh, i, rank + world * f, args.content, dev) for i in range(n)]
+                for f in range(RING)]
+    d_canvas = [torch.empty((H, W, 3), dtype=torch.uint8, device=dev) for _ in range(RING)]
+    st = pkg.Stitcher([w.src_wh] * n, w.canvas_wh, w.H, flags=args.flags, device=local_rank)
+    stream = torch.cuda.current_stream()
+    sp = stream.cuda_stream
+    f_ptrs = [[t.data_ptr() for t in fs] for fs in d_frames]
+    f_pitch = [t.stride(0) for t in d_frames[0]]
+    c_ptrs = [t.data_ptr() for t in d_canvas]
+    c_pitch = d_canvas[0].stride(0)
+
+    def device_step():
+        for j in range(B):
+            k = j % RING
+            st.submit_device(f_ptrs[k], f_pitch, c_ptrs[k], c_pitch, sp)
+
+    # ---- parity spot check (untimed): frame 0 of rank 0 against the recorded OpenCV hash --------
+    parity = None
+    if rank == 0 and args.content == "noise":
+        try:
+            ka = json.load(open(os.path.join(ROOT, "tests", "golden", "known_answers.json")))
+            want = [c for c in ka["cases"] if (c["config"], c["content"], c["frame"]) == (w.name, "noise", 0)]
+            st.submit_device(f_ptrs[0], f_pitch, c_ptrs[0], c_pitch, sp)
+            stream.synchronize()
+            got = hashlib.sha256(d_canvas[0].cpu().numpy().tobytes()).hexdigest()
+            if want:
+                parity = "sha256 == OpenCV golden" if got == want[0]["canvas_sha256"] else "MISMATCH vs OpenCV golden"
+        except Exception as e:   # pragma: no cover
+            parity = f"not checked ({e})"
+
+    # ---- device-resident: `value` and the roofline ------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    launches0 = st.stats()["kernel_launches"]
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    with sampler:
+        ev0.record(stream)
+        for _ in range(args.steps):
+            device_step()
+        ev1.record(stream)
+        torch.cuda.synchronize()
+    barrier()
+    dev_ms = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = st.stats()["kernel_launches"] - launches0
+    frames_dev = args.steps * B
+    value = world * frames_dev / (dev_ms * 1e-3)
+    kernel_us = 1e3 * dev_ms / frames_dev          # one frame = the launches of one submit
+
+    # ---- end to end: pinned host buffers, copies inside the timed region ------------------------
+    e2e = None
+    if not args.no_e2e:
+        Be = args.e2e_frames_per_step
+        depth = pkg.lib().bs_pipeline_depth(st._h)
+        h_frames = []
+        for f in range(RING):
+            fs = []
+            for i in range(n):
+                a = pkg.pinned_empty((sh, sw, 3))
+                a[...] = d_frames[f][i].cpu().numpy()
+                fs.append(a)
+            h_frames.append(fs)
+        h_out = [pkg.pinned_empty((H, W, 3)) for _ in range(depth + 1)]
+
+        last = {"j": 0}
+
+        def e2e_steps(k_steps):
+            tickets = []
+            j = 0
+            for _ in range(k_steps):
+                for _ in range(Be):
+                    if len(tickets) >= depth:
+                        st.wait(tickets[len(tickets) - depth])
+                    tickets.append(st.submit(h_frames[j % RING], h_out[j % len(h_out)]))
+                    j += 1
+            for t in tickets[-depth:]:
+                st.wait(t)
+            last["j"] = j - 1
+
+        e2e_steps(max(2, min(args.warmup, 3)))
+        barrier()
+        with sampler:
+            t0 = time.perf_counter()
+            e2e_steps(args.steps)
+            st.sync()
+            t1 = time.perf_counter()
+        barrier()
+        e2e_s = max_over_ranks(t1 - t0)
+        e2e = {"value": world * args.steps * Be / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": Be * w.src_bytes, "d2h_bytes_per_step": Be * w.canvas_bytes,
+               "frames_per_step": Be, "pipeline_depth": depth, "ms_per_frame": 1e3 * e2e_s / (args.steps * Be),
+               "host_buffers": "pinned (bs_host_alloc)"}
+        if rank == 0:   # the last panorama read back must equal the device-resident result
+            j = last["j"]
+            e2e["matches_device_path"] = bool(np.array_equal(h_out[j % len(h_out)],
+                                                             d_canvas[j % RING].cpu().numpy()))
+
+    stats = st.stats()
+    st.close()
+
+    # ---- CPU baseline: rank 0, N = 1 only ------------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ref = CpuReference(w, args.content)
+        done, dt = ref.time_frames(2, 10 ** 6, budget_s=args.cpu_seconds)
+        cpu = {"value": done / dt, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
+               "sample": f"{done} frames of {w.name} in {dt:.1f} s, {ref.what}, all host threads"}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+    alg = w.algorithmic_bytes
+    roofline = None
+    if alg:
+        achieved = alg / (kernel_us * 1e-6) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg, "kernel_us": kernel_us,
+                    "frac_of_nominal_8TBs": achieved / 8000.0}
+        tpath = os.path.join(ROOT, "profiles", "dram_traffic.json")
+        if os.path.exists(tpath):
+            try:
+                roofline["traffic"] = json.load(open(tpath)).get(w.name)
+            except Exception:
+                pass
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_text(w), "content": args.content, "frames_per_step": B,
+                   "ring_frames": RING,
+                   "l2": f"inputs larger than L2: ring of {RING} frame sets + canvases = "
+                         f"{RING * (w.src_bytes + w.canvas_bytes) / 1e9:.2f} GB cycled per GPU",
+                   "parallelism": f"frame-parallel x{world}, no collective",
+                   "tiles_fast_exact_empty": [stats["n_tiles_fast"], stats["n_tiles_exact"], stats["n_tiles_empty"]]},
+        "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "clocks": sampler.summary(), "parity": parity,
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    run_b200(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

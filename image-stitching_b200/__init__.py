@@ -1,0 +1,225 @@
+"""B200-native compositing engine for the stitch stage of AlexeySachkov/image-stitching.
+
+This module is a thin ctypes view of the C ABI in include/b200_stitch.h (built in-tree as
+libb200stitch.so from csrc/).  It exists for the tests and the benchmark; the product boundary is
+the C ABI, and the C++ host (host/) is the drop-in for the reference's `stitch` tool.
+
+There is no CPU fallback: if the shared library is missing the import fails, and without a CUDA
+device every compute call raises StitchError.
+"""
+import ctypes
+import os
+import weakref
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200stitch.so")
+
+FLAG_LEGACY_BORDER = 0x1
+FLAG_KEEP_CANVAS = 0x2
+FLAG_EXACT_ONLY = 0x4
+
+# names of the cv2 constants the reference passes (tools/stitch/main.cpp:116-117)
+INTER_LINEAR = 1
+BORDER_TRANSPARENT = 5
+
+EXPORTS = [
+    "bs_device_count", "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_submit",
+    "bs_wait", "bs_pipeline_depth", "bs_stitch", "bs_submit_device", "bs_sync",
+    "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats",
+]
+
+
+class StitchError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"b200_stitch error {code}: {msg}")
+        self.code = code
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("n_cams", ctypes.c_int), ("canvas_w", ctypes.c_int), ("canvas_h", ctypes.c_int),
+                ("tile_w", ctypes.c_int), ("tile_h", ctypes.c_int),
+                ("n_tiles", ctypes.c_int64), ("n_tiles_fast", ctypes.c_int64),
+                ("n_tiles_exact", ctypes.c_int64), ("n_tiles_empty", ctypes.c_int64),
+                ("kernel_launches", ctypes.c_int64), ("frames_submitted", ctypes.c_int64),
+                ("device_bytes", ctypes.c_uint64), ("scratch_bytes", ctypes.c_uint64)]
+
+
+_lib = None
+
+
+def build():
+    """Compile the CUDA library in-tree (nvcc, sm_100a)."""
+    import subprocess
+    subprocess.check_call(["make", "-C", os.path.join(_HERE, "csrc"), "-s"])
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `make -C {_HERE}/csrc` "
+                          "(there is no fallback implementation)")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, i, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
+    ip, dp = ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_double)
+    L.bs_device_count.restype = i
+    L.bs_version.restype = ctypes.c_char_p
+    L.bs_last_error.argtypes = [vp]
+    L.bs_last_error.restype = ctypes.c_char_p
+    L.bs_create.argtypes = [i, i, ip, ip, i, i, dp, ctypes.c_uint, ctypes.POINTER(vp)]
+    L.bs_destroy.argtypes = [vp]
+    L.bs_submit.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz,
+                            ctypes.POINTER(ctypes.c_int64)]
+    L.bs_wait.argtypes = [vp, ctypes.c_int64]
+    L.bs_pipeline_depth.argtypes = [vp]
+    L.bs_stitch.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz]
+    L.bs_submit_device.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz, vp]
+    L.bs_sync.argtypes = [vp]
+    L.bs_warp_perspective.argtypes = [vp, i, i, sz, vp, i, i, sz, dp, ctypes.c_uint]
+    L.bs_host_alloc.argtypes = [sz]
+    L.bs_host_alloc.restype = vp
+    L.bs_host_free.argtypes = [vp]
+    L.bs_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
+    _lib = L
+    return L
+
+
+def device_count():
+    return lib().bs_device_count()
+
+
+def version():
+    return lib().bs_version().decode()
+
+
+def _check(rc, handle=None):
+    if rc != 0:
+        raise StitchError(rc, lib().bs_last_error(handle).decode())
+
+
+def _check_img(a, name):
+    if not (isinstance(a, np.ndarray) and a.dtype == np.uint8 and a.ndim == 3 and a.shape[2] == 3
+            and a.strides[2] == 1 and a.strides[1] == 3):
+        raise ValueError(f"{name} must be an HxWx3 uint8 array with packed pixels")
+
+
+def pinned_empty(shape):
+    """uint8 ndarray backed by pinned host memory (bs_host_alloc); freed with the array."""
+    n = int(np.prod(shape))
+    p = lib().bs_host_alloc(n)
+    if not p:
+        raise StitchError(-5, lib().bs_last_error(None).decode())
+    buf = (ctypes.c_uint8 * n).from_address(p)
+    weakref.finalize(buf, lib().bs_host_free, p)   # freed when the last view of buf dies
+    return np.frombuffer(buf, dtype=np.uint8).reshape(shape)
+
+
+class Stitcher:
+    """One calibration on one GPU: bs_create ... bs_destroy.
+
+    src_whs: [(w, h)] per camera; canvas_wh: (W, H); Hs: n x 3 x 3 forward homographies
+    (as in stitch.conf.xml, /root/reference/tools/stitch/main.cpp:60-73).
+    """
+
+    def __init__(self, src_whs, canvas_wh, Hs, flags=0, device=0):
+        L = lib()
+        n = len(src_whs)
+        self.n_cams = n
+        self.src_whs = [(int(w), int(h)) for w, h in src_whs]
+        self.canvas_wh = (int(canvas_wh[0]), int(canvas_wh[1]))
+        Hs = np.ascontiguousarray(np.asarray(Hs, dtype=np.float64).reshape(n, 9))
+        sw = (ctypes.c_int * n)(*[w for w, _ in self.src_whs])
+        sh = (ctypes.c_int * n)(*[h for _, h in self.src_whs])
+        self._h = ctypes.c_void_p()
+        _check(L.bs_create(device, n, sw, sh, self.canvas_wh[0], self.canvas_wh[1],
+                           Hs.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), flags,
+                           ctypes.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().bs_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # --- host buffers -------------------------------------------------------------------
+    def _frame_args(self, frames):
+        if len(frames) != self.n_cams:
+            raise ValueError(f"expected {self.n_cams} frames, got {len(frames)}")
+        ptrs = (ctypes.c_void_p * self.n_cams)()
+        pitches = (ctypes.c_size_t * self.n_cams)()
+        for k, (f, (w, h)) in enumerate(zip(frames, self.src_whs)):
+            _check_img(f, f"frames[{k}]")
+            if f.shape[0] != h or f.shape[1] != w:
+                raise ValueError(f"frames[{k}] is {f.shape[1]}x{f.shape[0]}, expected {w}x{h}")
+            ptrs[k] = f.ctypes.data
+            pitches[k] = f.strides[0]
+        return ptrs, pitches
+
+    def new_canvas(self, pinned=False):
+        shape = (self.canvas_wh[1], self.canvas_wh[0], 3)
+        return pinned_empty(shape) if pinned else np.empty(shape, np.uint8)
+
+    def submit(self, frames, out):
+        ptrs, pitches = self._frame_args(frames)
+        _check_img(out, "out")
+        t = ctypes.c_int64(-1)
+        _check(lib().bs_submit(self._h, ptrs, pitches, out.ctypes.data, out.strides[0],
+                               ctypes.byref(t)), self._h)
+        return t.value
+
+    def wait(self, ticket):
+        _check(lib().bs_wait(self._h, ticket), self._h)
+
+    def stitch(self, frames, out=None):
+        if out is None:
+            out = self.new_canvas()
+        self.wait(self.submit(frames, out))
+        return out
+
+    # --- device buffers -------------------------------------------------------------------
+    def submit_device(self, frame_ptrs, frame_pitches, canvas_ptr, canvas_pitch, stream=0):
+        ptrs = (ctypes.c_void_p * self.n_cams)(*[int(p) for p in frame_ptrs])
+        pitches = (ctypes.c_size_t * self.n_cams)(*[int(p) for p in frame_pitches])
+        _check(lib().bs_submit_device(self._h, ptrs, pitches, int(canvas_ptr), int(canvas_pitch),
+                                      int(stream) if stream else None), self._h)
+
+    def sync(self):
+        _check(lib().bs_sync(self._h), self._h)
+
+    def stats(self):
+        s = Stats()
+        _check(lib().bs_get_stats(self._h, ctypes.byref(s)), self._h)
+        return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+
+def warpPerspective(src, dst, H, dsize, flags=INTER_LINEAR, borderMode=BORDER_TRANSPARENT,
+                    legacy_border=False):
+    """Mirror of the call the reference makes (tools/stitch/main.cpp:116-117):
+    warpPerspective(src, dst, H, dsize, INTER_LINEAR, BORDER_TRANSPARENT), dst updated in place."""
+    if flags != INTER_LINEAR or borderMode != BORDER_TRANSPARENT:
+        raise StitchError(-4, "only INTER_LINEAR + BORDER_TRANSPARENT (the reference's call) is implemented")
+    _check_img(src, "src")
+    _check_img(dst, "dst")
+    if (dst.shape[1], dst.shape[0]) != tuple(dsize):
+        raise ValueError("dst does not have size dsize")
+    H = np.ascontiguousarray(np.asarray(H, dtype=np.float64).reshape(9))
+    _check(lib().bs_warp_perspective(src.ctypes.data, src.shape[1], src.shape[0], src.strides[0],
+                                     dst.ctypes.data, dst.shape[1], dst.shape[0], dst.strides[0],
+                                     H.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+                                     FLAG_LEGACY_BORDER if legacy_border else 0))
+    return dst

@@ -1,0 +1,424 @@
+// stitch_api.cu -- C ABI (include/b200_stitch.h) over the sm_100a kernels.
+//
+// Host-side responsibilities, all replacing set-up the reference does inline in
+// /root/reference/tools/stitch/main.cpp: invert the homographies (what cv::warpPerspective does
+// on entry, :116), own the canvas (:108, :144), and run the per-frame camera loop (:145-152) as
+// kernel launches fed by copy streams.
+#include "../../include/b200_stitch.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "stitch_exact.cuh"
+
+namespace {
+
+thread_local std::string g_last_error = "";
+thread_local int g_last_device = 0;
+
+constexpr int kPipelineDepth = 3;
+
+struct Slot {
+    std::vector<uint8_t *> d_frame;
+    uint8_t *d_canvas = nullptr;
+    cudaEvent_t ev_h2d = nullptr, ev_kernel = nullptr, ev_done = nullptr;
+    int64_t ticket = -1;
+    bool busy = false;
+};
+
+}  // namespace
+
+struct bs_handle {
+    int device = 0;
+    int n_cams = 0;
+    std::vector<int> sw, sh;
+    int W = 0, H = 0;
+    unsigned flags = 0;
+    std::vector<double> M;               // n_cams x 9, inverse homographies
+    std::vector<size_t> d_frame_pitch;   // device pitch of each camera's frame
+    size_t d_canvas_pitch = 0;
+    cudaStream_t s_h2d = nullptr, s_compute = nullptr, s_d2h = nullptr;
+    std::vector<Slot> ring;
+    int64_t next_ticket = 0;
+    int64_t kernel_launches = 0;
+    uint64_t device_bytes = 0, scratch_bytes = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(bs_handle *h, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    if (h) h->err = buf;
+    return code;
+}
+
+#define BS_CUDA(h, call)                                                                      \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess)                                                               \
+            return fail(h, BS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
+                        __FILE__, __LINE__);                                                  \
+    } while (0)
+
+// 3x3 inverse as cv::invert computes it for a 3x3 CV_64F matrix: cofactors times 1/det.
+// (cv::warpPerspective inverts H on entry because the reference passes the forward map,
+// tools/stitch/main.cpp:116.)  Singular input leaves M = 0, as OpenCV does.
+void invert3x3(const double *H, double *M)
+{
+    const double a = H[0], b = H[1], c = H[2], d = H[3], e = H[4], f = H[5], g = H[6], hh = H[7],
+                 i = H[8];
+    double det = a * (e * i - f * hh) - b * (d * i - f * g) + c * (d * hh - e * g);
+    if (det == 0.0) {
+        for (int k = 0; k < 9; ++k) M[k] = 0.0;
+        return;
+    }
+    det = 1.0 / det;
+    M[0] = (e * i - f * hh) * det;
+    M[1] = (c * hh - b * i) * det;
+    M[2] = (b * f - c * e) * det;
+    M[3] = (f * g - d * i) * det;
+    M[4] = (a * i - c * g) * det;
+    M[5] = (c * d - a * f) * det;
+    M[6] = (d * hh - e * g) * det;
+    M[7] = (b * g - a * hh) * det;
+    M[8] = (a * e - b * d) * det;
+}
+
+// Column granularity of OpenCV's coordinate blocks (32*32 pixels, at most 16 rows).
+int opencv_block_width(int W, int H)
+{
+    int bh = H < 16 ? H : 16;
+    if (bh < 1) bh = 1;
+    int bw = 1024 / bh;
+    if (bw > W) bw = W;
+    if (bw < 1) bw = 1;
+    return bw;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int require_device(bs_handle *h)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        return fail(h, BS_ERR_NO_DEVICE, "no CUDA device available (%s); this library has no CPU path",
+                    e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    }
+    return BS_OK;
+}
+
+// Launch the kernels of one frame.  Cameras beyond the per-launch limit go in further
+// launches that keep what is already on the canvas (later cameras win, Appendix A.5).
+int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch, uint8_t *d_canvas,
+                 size_t cpitch, bool keep, cudaStream_t stream)
+{
+    for (int base = 0; base < h->n_cams; base += bs::kMaxCamsPerLaunch) {
+        bs::FrameArgs A;
+        memset(&A, 0, sizeof A);
+        A.n_cams = std::min(bs::kMaxCamsPerLaunch, h->n_cams - base);
+        for (int i = 0; i < A.n_cams; ++i) {
+            memcpy(A.cam[i].M, &h->M[9 * (base + i)], 9 * sizeof(double));
+            A.cam[i].ptr = static_cast<const uint8_t *>(d_frames[base + i]);
+            A.cam[i].pitch = (long long)pitch[base + i];
+            A.cam[i].w = h->sw[base + i];
+            A.cam[i].h = h->sh[base + i];
+        }
+        A.canvas = d_canvas;
+        A.cpitch = (long long)cpitch;
+        A.W = h->W;
+        A.H = h->H;
+        A.block_w = opencv_block_width(h->W, h->H);
+        A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
+        A.keep_canvas = (keep || base > 0) ? 1 : 0;
+        A.cam_base = base;
+        dim3 grid((h->W + bs::kExactTileW - 1) / bs::kExactTileW,
+                  (h->H + bs::kExactTileH - 1) / bs::kExactTileH);
+        bs::stitch_exact_kernel<<<grid, dim3(32, bs::kExactTileH), 0, stream>>>(A);
+        BS_CUDA(h, cudaGetLastError());
+        h->kernel_launches++;
+    }
+    return BS_OK;
+}
+
+int ensure_ring(bs_handle *h)
+{
+    if (!h->ring.empty()) return BS_OK;
+    h->ring.resize(kPipelineDepth);
+    for (Slot &s : h->ring) {
+        s.d_frame.assign(h->n_cams, nullptr);
+        for (int i = 0; i < h->n_cams; ++i) {
+            size_t bytes = h->d_frame_pitch[i] * (size_t)h->sh[i];
+            BS_CUDA(h, cudaMalloc(&s.d_frame[i], bytes));
+            h->device_bytes += bytes;
+        }
+        size_t cbytes = h->d_canvas_pitch * (size_t)h->H;
+        BS_CUDA(h, cudaMalloc(&s.d_canvas, cbytes));
+        h->device_bytes += cbytes;
+        BS_CUDA(h, cudaEventCreateWithFlags(&s.ev_h2d, cudaEventDisableTiming));
+        BS_CUDA(h, cudaEventCreateWithFlags(&s.ev_kernel, cudaEventDisableTiming));
+        BS_CUDA(h, cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
+    }
+    return BS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bs_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+const char *bs_version(void) { return "b200-stitch 0.1 (sm_100a)"; }
+
+const char *bs_last_error(const bs_handle *h) { return h ? h->err.c_str() : g_last_error.c_str(); }
+
+int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int canvas_w,
+              int canvas_h, const double *H, unsigned flags, bs_handle **out)
+{
+    if (!out) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: out is NULL");
+    *out = nullptr;
+    if (n_cams < 1 || n_cams > BS_MAX_CAMERAS)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: n_cams=%d outside [1, %d]", n_cams,
+                    BS_MAX_CAMERAS);
+    if (!src_w || !src_h || !H) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: NULL array");
+    if (canvas_w < 1 || canvas_h < 1 || canvas_w > 65535 || canvas_h > 65535)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: canvas %dx%d outside [1, 65535]",
+                    canvas_w, canvas_h);
+    for (int i = 0; i < n_cams; ++i)
+        if (src_w[i] < 1 || src_h[i] < 1 || src_w[i] > BS_MAX_DIM || src_h[i] > BS_MAX_DIM)
+            return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: camera %d is %dx%d, outside [1, %d]",
+                        i, src_w[i], src_h[i], BS_MAX_DIM);
+    int rc = require_device(nullptr);
+    if (rc != BS_OK) return rc;
+    int ndev = bs_device_count();
+    if (device_id < 0 || device_id >= ndev)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: device %d not in [0, %d)", device_id, ndev);
+
+    bs_handle *h = new (std::nothrow) bs_handle;
+    if (!h) return fail(nullptr, BS_ERR_NOMEM, "bs_create: out of host memory");
+    h->device = device_id;
+    h->n_cams = n_cams;
+    h->sw.assign(src_w, src_w + n_cams);
+    h->sh.assign(src_h, src_h + n_cams);
+    h->W = canvas_w;
+    h->H = canvas_h;
+    h->flags = flags;
+    h->M.resize(9 * (size_t)n_cams);
+    for (int i = 0; i < n_cams; ++i) invert3x3(H + 9 * i, &h->M[9 * i]);
+    h->d_frame_pitch.resize(n_cams);
+    for (int i = 0; i < n_cams; ++i) h->d_frame_pitch[i] = align_up((size_t)src_w[i] * 3, 128);
+    h->d_canvas_pitch = align_up((size_t)canvas_w * 3, 128);
+
+    cudaError_t e = cudaSetDevice(device_id);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_compute, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        fail(nullptr, BS_ERR_CUDA, "bs_create: stream set-up failed: %s", cudaGetErrorString(e));
+        bs_destroy(h);
+        return BS_ERR_CUDA;
+    }
+    g_last_device = device_id;
+    *out = h;
+    return BS_OK;
+}
+
+int bs_destroy(bs_handle *h)
+{
+    if (!h) return BS_OK;
+    cudaSetDevice(h->device);
+    if (h->s_h2d) cudaStreamSynchronize(h->s_h2d);
+    if (h->s_compute) cudaStreamSynchronize(h->s_compute);
+    if (h->s_d2h) cudaStreamSynchronize(h->s_d2h);
+    for (Slot &s : h->ring) {
+        for (uint8_t *p : s.d_frame) cudaFree(p);
+        cudaFree(s.d_canvas);
+        if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
+        if (s.ev_kernel) cudaEventDestroy(s.ev_kernel);
+        if (s.ev_done) cudaEventDestroy(s.ev_done);
+    }
+    if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+    if (h->s_compute) cudaStreamDestroy(h->s_compute);
+    if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    delete h;
+    return BS_OK;
+}
+
+int bs_pipeline_depth(const bs_handle *) { return kPipelineDepth; }
+
+int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, uint8_t *out,
+              size_t out_pitch, int64_t *ticket)
+{
+    if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_submit: NULL handle");
+    if (!frames || !pitch || !out) return fail(h, BS_ERR_INVALID_ARG, "bs_submit: NULL argument");
+    for (int i = 0; i < h->n_cams; ++i) {
+        if (!frames[i]) return fail(h, BS_ERR_INVALID_ARG, "bs_submit: frame %d is NULL", i);
+        if (pitch[i] < (size_t)h->sw[i] * 3)
+            return fail(h, BS_ERR_INVALID_ARG, "bs_submit: pitch[%d]=%zu < %d*3", i, pitch[i], h->sw[i]);
+    }
+    if (out_pitch < (size_t)h->W * 3)
+        return fail(h, BS_ERR_INVALID_ARG, "bs_submit: out_pitch=%zu < %d*3", out_pitch, h->W);
+    BS_CUDA(h, cudaSetDevice(h->device));
+    int rc = ensure_ring(h);
+    if (rc != BS_OK) return rc;
+
+    const int64_t t = h->next_ticket;
+    Slot &s = h->ring[t % kPipelineDepth];
+    if (s.busy) {   // the slot's previous frame must have left the device
+        BS_CUDA(h, cudaEventSynchronize(s.ev_done));
+        s.busy = false;
+    }
+    for (int i = 0; i < h->n_cams; ++i)
+        BS_CUDA(h, cudaMemcpy2DAsync(s.d_frame[i], h->d_frame_pitch[i], frames[i], pitch[i],
+                                     (size_t)h->sw[i] * 3, h->sh[i], cudaMemcpyHostToDevice, h->s_h2d));
+    const bool keep = (h->flags & BS_FLAG_KEEP_CANVAS) != 0;
+    if (keep)
+        BS_CUDA(h, cudaMemcpy2DAsync(s.d_canvas, h->d_canvas_pitch, out, out_pitch, (size_t)h->W * 3,
+                                     h->H, cudaMemcpyHostToDevice, h->s_h2d));
+    BS_CUDA(h, cudaEventRecord(s.ev_h2d, h->s_h2d));
+    BS_CUDA(h, cudaStreamWaitEvent(h->s_compute, s.ev_h2d, 0));
+    std::vector<const void *> d_frames(s.d_frame.begin(), s.d_frame.end());
+    rc = launch_frame(h, d_frames.data(), h->d_frame_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep,
+                      h->s_compute);
+    if (rc != BS_OK) return rc;
+    BS_CUDA(h, cudaEventRecord(s.ev_kernel, h->s_compute));
+    BS_CUDA(h, cudaStreamWaitEvent(h->s_d2h, s.ev_kernel, 0));
+    BS_CUDA(h, cudaMemcpy2DAsync(out, out_pitch, s.d_canvas, h->d_canvas_pitch, (size_t)h->W * 3, h->H,
+                                 cudaMemcpyDeviceToHost, h->s_d2h));
+    BS_CUDA(h, cudaEventRecord(s.ev_done, h->s_d2h));
+    s.ticket = t;
+    s.busy = true;
+    h->next_ticket++;
+    if (ticket) *ticket = t;
+    return BS_OK;
+}
+
+int bs_wait(bs_handle *h, int64_t ticket)
+{
+    if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_wait: NULL handle");
+    if (ticket < 0 || ticket >= h->next_ticket)
+        return fail(h, BS_ERR_BAD_TICKET, "bs_wait: ticket %lld was never issued", (long long)ticket);
+    if (ticket < h->next_ticket - kPipelineDepth) return BS_OK;   // its slot was already recycled => done
+    Slot &s = h->ring[ticket % kPipelineDepth];
+    if (s.ticket != ticket || !s.busy) return BS_OK;
+    BS_CUDA(h, cudaSetDevice(h->device));
+    BS_CUDA(h, cudaEventSynchronize(s.ev_done));
+    s.busy = false;
+    return BS_OK;
+}
+
+int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, uint8_t *out,
+              size_t out_pitch)
+{
+    int64_t t = -1;
+    int rc = bs_submit(h, frames, pitch, out, out_pitch, &t);
+    if (rc != BS_OK) return rc;
+    return bs_wait(h, t);
+}
+
+int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pitch, void *d_canvas,
+                     size_t canvas_pitch, void *stream)
+{
+    if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_submit_device: NULL handle");
+    if (!d_frames || !pitch || !d_canvas)
+        return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: NULL argument");
+    for (int i = 0; i < h->n_cams; ++i) {
+        if (!d_frames[i]) return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: frame %d is NULL", i);
+        if (pitch[i] < (size_t)h->sw[i] * 3)
+            return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: pitch[%d]=%zu < %d*3", i, pitch[i],
+                        h->sw[i]);
+    }
+    if (canvas_pitch < (size_t)h->W * 3)
+        return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: canvas_pitch=%zu < %d*3", canvas_pitch, h->W);
+    BS_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : h->s_compute;
+    return launch_frame(h, d_frames, pitch, static_cast<uint8_t *>(d_canvas), canvas_pitch,
+                        (h->flags & BS_FLAG_KEEP_CANVAS) != 0, st);
+}
+
+int bs_sync(bs_handle *h)
+{
+    if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_sync: NULL handle");
+    BS_CUDA(h, cudaSetDevice(h->device));
+    BS_CUDA(h, cudaStreamSynchronize(h->s_h2d));
+    BS_CUDA(h, cudaStreamSynchronize(h->s_compute));
+    BS_CUDA(h, cudaStreamSynchronize(h->s_d2h));
+    for (Slot &s : h->ring) s.busy = false;
+    return BS_OK;
+}
+
+int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8_t *dst, int dw, int dh,
+                        size_t dpitch, const double H[9], unsigned flags)
+{
+    if (!src || !dst || !H) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_warp_perspective: NULL argument");
+    int rc = require_device(nullptr);
+    if (rc != BS_OK) return rc;
+    bs_handle *h = nullptr;
+    rc = bs_create(g_last_device, 1, &sw, &sh, dw, dh, H, flags | BS_FLAG_KEEP_CANVAS, &h);
+    if (rc != BS_OK) return rc;
+    const uint8_t *frames[1] = {src};
+    size_t pitches[1] = {spitch};
+    rc = bs_stitch(h, frames, pitches, dst, dpitch);
+    if (rc != BS_OK) g_last_error = h->err;
+    bs_destroy(h);
+    return rc;
+}
+
+void *bs_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        fail(nullptr, BS_ERR_NOMEM, "bs_host_alloc: cudaHostAlloc(%zu) failed", bytes);
+        return nullptr;
+    }
+    return p;
+}
+
+void bs_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+int bs_get_stats(const bs_handle *h, bs_stats *out)
+{
+    if (!h || !out) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_get_stats: NULL argument");
+    memset(out, 0, sizeof *out);
+    out->n_cams = h->n_cams;
+    out->canvas_w = h->W;
+    out->canvas_h = h->H;
+    out->tile_w = bs::kExactTileW;
+    out->tile_h = bs::kExactTileH;
+    out->n_tiles = (int64_t)((h->W + bs::kExactTileW - 1) / bs::kExactTileW) *
+                   ((h->H + bs::kExactTileH - 1) / bs::kExactTileH);
+    out->n_tiles_exact = out->n_tiles;
+    out->kernel_launches = h->kernel_launches;
+    out->frames_submitted = h->next_ticket;
+    out->device_bytes = h->device_bytes;
+    out->scratch_bytes = h->scratch_bytes;
+    return BS_OK;
+}
+
+}  // extern "C"

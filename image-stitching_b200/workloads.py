@@ -79,3 +79,41 @@ WORKLOADS = {
 
 def get(name):
     return WORKLOADS[name]
+
+
+# ---- synthetic frame content ---------------------------------------
+def gen_frame_numpy(w, h, cam, frame, kind="noise"):
+    """Camera `cam`, frame `frame`, packed BGR u8.  kind: 'noise' (hash) or 'smooth' (ramp)."""
+    x = np.arange(w, dtype=np.uint32)[None, :, None]
+    y = np.arange(h, dtype=np.uint32)[:, None, None]
+    c = np.arange(3, dtype=np.uint32)[None, None, :]
+    if kind == "smooth":
+        return ((x + 2 * y + 64 * c + np.uint32(7 * frame + 31 * cam)) & 255).astype(np.uint8)
+    with np.errstate(over="ignore"):
+        v = (x * np.uint32(0x9E3779B1)) ^ (y * np.uint32(0x85EBCA77)) ^ (c * np.uint32(0xC2B2AE3D))
+        v = v ^ (np.uint32(cam * 131 + frame) * np.uint32(0x27D4EB2F))
+        v ^= v >> 15
+        v *= np.uint32(0x2C1B3C6D)
+        v ^= v >> 12
+        v *= np.uint32(0x297A2D39)
+        v ^= v >> 15
+    return (v >> 24).astype(np.uint8)
+
+
+def gen_frame_torch(w, h, cam, frame, kind="noise", device="cuda"):
+    """Same content generated on the device (uint32 arithmetic emulated in int64)."""
+    import torch
+    m = 0xFFFFFFFF
+    x = torch.arange(w, dtype=torch.int64, device=device)[None, :, None]
+    y = torch.arange(h, dtype=torch.int64, device=device)[:, None, None]
+    c = torch.arange(3, dtype=torch.int64, device=device)[None, None, :]
+    if kind == "smooth":
+        return ((x + 2 * y + 64 * c + (7 * frame + 31 * cam)) & 255).to(torch.uint8).contiguous()
+    v = ((x * 0x9E3779B1) & m) ^ ((y * 0x85EBCA77) & m) ^ ((c * 0xC2B2AE3D) & m)
+    v = v ^ (((cam * 131 + frame) * 0x27D4EB2F) & m)
+    v = v ^ (v >> 15)
+    v = (v * 0x2C1B3C6D) & m
+    v = v ^ (v >> 12)
+    v = (v * 0x297A2D39) & m
+    v = v ^ (v >> 15)
+    return (v >> 24).to(torch.uint8).contiguous()

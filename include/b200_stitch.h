@@ -1,0 +1,139 @@
+/*
+ * b200_stitch.h -- C ABI of the B200-native compositing engine for the stitch stage of
+ * AlexeySachkov/image-stitching.
+ *
+ * The reference has no FFI or plugin interface for this path: its stitch tool calls
+ * cv::warpPerspective inline from main() (/root/reference/tools/stitch/main.cpp:116-117 in
+ * image mode, :150-151 in video mode, preceded by cv::undistort at :148-149).  The entry points
+ * below are what a C/C++ (or cgo/JNI/ctypes) caller binds instead of those OpenCV calls; each
+ * one cites the reference lines it replaces.  INTEGRATION.md shows the edit to stitch's main().
+ *
+ * Conventions
+ *   - plain C linkage, no exceptions, no C++ or torch types in any signature;
+ *   - images are packed 8-bit BGR (CV_8UC3), row pitch in bytes, as in a continuous cv::Mat;
+ *   - homographies are 3x3 row-major doubles, FORWARD (source pixel -> canvas pixel), exactly
+ *     as stored under "H" in stitch.conf.xml (tools/calibrate/main.cpp:497-522);
+ *   - every function returns BS_OK (0) or a negative BS_ERR_* code; bs_last_error() gives text;
+ *   - a handle is single-threaded: use one handle (and one host thread) per GPU;
+ *   - output pixels no camera covers are 0 (the reference leaves them uninitialised,
+ *     tools/stitch/main.cpp:108,144) unless BS_FLAG_KEEP_CANVAS is given;
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails with
+ *     BS_ERR_NO_DEVICE.
+ */
+#ifndef B200_STITCH_H
+#define B200_STITCH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BS_OK 0
+#define BS_ERR_INVALID_ARG (-1)
+#define BS_ERR_CUDA (-2)
+#define BS_ERR_NO_DEVICE (-3)
+#define BS_ERR_UNSUPPORTED (-4)
+#define BS_ERR_NOMEM (-5)
+#define BS_ERR_BAD_TICKET (-6)
+
+/* Border rule on the last source row/column: default is OpenCV 4.x (pixel written, weights
+ * renormalised); LEGACY is OpenCV 2.4/3.x (pixel left untouched).  SURVEY.md Appendix A.4. */
+#define BS_FLAG_LEGACY_BORDER 0x1u
+/* Read-modify-write canvas, as one cv::warpPerspective(..., BORDER_TRANSPARENT) call into an
+ * existing Mat (tools/stitch/main.cpp:116): uncovered pixels keep their previous contents. */
+#define BS_FLAG_KEEP_CANVAS 0x2u
+/* Testing aid: run every tile through the exact per-pixel kernel (no tile plan fast path). */
+#define BS_FLAG_EXACT_ONLY 0x4u
+
+#define BS_MAX_CAMERAS 64
+#define BS_MAX_DIM 32767 /* OpenCV keeps integer source coordinates in int16 */
+
+typedef struct bs_handle bs_handle;
+
+typedef struct bs_stats {
+    int n_cams, canvas_w, canvas_h;
+    int tile_w, tile_h;
+    int64_t n_tiles;          /* canvas tiles in the plan */
+    int64_t n_tiles_fast;     /* tiles fully covered by their top camera (staged path) */
+    int64_t n_tiles_exact;    /* tiles on the exact per-pixel path (seams, edges, holes) */
+    int64_t n_tiles_empty;    /* tiles no camera touches */
+    int64_t kernel_launches;  /* kernels of this library launched through this handle */
+    int64_t frames_submitted;
+    uint64_t device_bytes;    /* device memory owned by the handle */
+    uint64_t scratch_bytes;   /* of which plan/scratch */
+} bs_stats;
+
+/* Number of CUDA devices visible; 0 if none (never negative). */
+int bs_device_count(void);
+
+/* Library version string, e.g. "b200-stitch 0.1 (sm_100a)". */
+const char *bs_version(void);
+
+/* Last error text of a handle, or of the calling thread when h == NULL. Never NULL. */
+const char *bs_last_error(const bs_handle *h);
+
+/*
+ * Set-up, once per calibration.  Replaces the state the reference builds at
+ * tools/stitch/main.cpp:53-73 (result_size, H[]) and :108 / :144 (canvas allocation):
+ * inverts every H in double the way cv::warpPerspective does, builds the tile plan on the
+ * device, allocates device frame/canvas rings and the copy/compute streams.
+ *   src_w/src_h[n_cams], H[n_cams*9]; flags = BS_FLAG_*.
+ */
+int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int canvas_w,
+              int canvas_h, const double *H, unsigned flags, bs_handle **out);
+
+int bs_destroy(bs_handle *h);
+
+/*
+ * One panorama frame from HOST buffers, asynchronous.  Replaces the body of the camera loop,
+ * tools/stitch/main.cpp:145-152 (video mode) / :113-121 (image mode): N warps into one canvas,
+ * highest camera index wins in overlaps.  frames[i]/pitch[i] are packed BGR rows of camera i;
+ * `out` receives canvas_h rows of canvas_w*3 bytes at out_pitch.  All host pointers must stay
+ * valid until bs_wait(ticket).  Pinned buffers (bs_host_alloc) are copied by DMA directly;
+ * pageable ones work but copy slower.  Up to bs_pipeline_depth() frames may be in flight.
+ */
+int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, uint8_t *out,
+              size_t out_pitch, int64_t *ticket);
+int bs_wait(bs_handle *h, int64_t ticket);
+int bs_pipeline_depth(const bs_handle *h);
+
+/* bs_submit + bs_wait. */
+int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, uint8_t *out,
+              size_t out_pitch);
+
+/*
+ * Same work on DEVICE-resident buffers (kernel only, no copies), asynchronous on `stream`
+ * (a cudaStream_t; NULL = the handle's compute stream).  d_frames[i] and d_canvas are device
+ * pointers; for the staged fast path they must be 16-byte aligned with pitches that are
+ * multiples of 16, otherwise the exact path is used for the whole frame.
+ * Replaces tools/stitch/main.cpp:145-152 for callers that decode straight into GPU memory.
+ */
+int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pitch,
+                     void *d_canvas, size_t canvas_pitch, void *stream);
+
+/* Block until everything submitted through the handle has finished. */
+int bs_sync(bs_handle *h);
+
+/*
+ * Drop-in for ONE call
+ *   cv::warpPerspective(src, dst, H, Size(dw, dh), INTER_LINEAR, BORDER_TRANSPARENT)
+ * (tools/stitch/main.cpp:116-117, :150-151; also tools/calibrate/main.cpp:484-485) on host
+ * buffers: synchronous, dst is read-modify-write.  flags: BS_FLAG_LEGACY_BORDER.  Uses device
+ * 0 (or the device of the last bs_create on this thread).  Convenience only: it uploads dst,
+ * so the per-frame loop should use bs_create + bs_submit instead.
+ */
+int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8_t *dst, int dw,
+                        int dh, size_t dpitch, const double H[9], unsigned flags);
+
+/* Pinned host memory for frames and panoramas (cudaHostAlloc / cudaFreeHost). */
+void *bs_host_alloc(size_t bytes);
+void bs_host_free(void *p);
+
+int bs_get_stats(const bs_handle *h, bs_stats *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_STITCH_H */

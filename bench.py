@@ -244,11 +244,13 @@ def run_b200(args, rank, local_rank, world):
     B = args.frames_per_step
 
     # ring of RING frame sets per camera, distinct per rank (frame f -> GPU f mod world)
+    torch.cuda.synchronize()
     d_frames = [[wl.gen_frame_torch(sw, sh, i, rank + world * f, args.content, dev) for i in range(n)]
                 for f in range(RING)]
     d_canvas = [torch.empty((H, W, 3), dtype=torch.uint8, device=dev) for _ in range(RING)]
     st = pkg.Stitcher([w.src_wh] * n, w.canvas_wh, w.H, flags=args.flags, device=local_rank)
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)       # the kernels and the timing events share this stream
+    torch.cuda.set_stream(stream)
     sp = stream.cuda_stream
     f_ptrs = [[t.data_ptr() for t in fs] for fs in d_frames]
     f_pitch = [t.stride(0) for t in d_frames[0]]

@@ -353,7 +353,7 @@ int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pi
     if (canvas_pitch < (size_t)h->W * 3)
         return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: canvas_pitch=%zu < %d*3", canvas_pitch, h->W);
     BS_CUDA(h, cudaSetDevice(h->device));
-    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : h->s_compute;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);   // NULL = the legacy default stream
     return launch_frame(h, d_frames, pitch, static_cast<uint8_t *>(d_canvas), canvas_pitch,
                         (h->flags & BS_FLAG_KEEP_CANVAS) != 0, st);
 }

@@ -105,7 +105,7 @@ int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
 
 /*
  * Same work on DEVICE-resident buffers (kernel only, no copies), asynchronous on `stream`
- * (a cudaStream_t; NULL = the handle's compute stream).  d_frames[i] and d_canvas are device
+ * (a cudaStream_t; NULL = the legacy default stream, as everywhere in CUDA).  d_frames[i] and d_canvas are device
  * pointers; for the staged fast path they must be 16-byte aligned with pitches that are
  * multiples of 16, otherwise the exact path is used for the whole frame.
  * Replaces tools/stitch/main.cpp:145-152 for callers that decode straight into GPU memory.

@@ -10,12 +10,15 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
 #include <vector>
 
-#include "stitch_exact.cuh"
+#include <algorithm>
+
+#include "stitch_fast.cuh"
 
 namespace {
 
@@ -47,6 +50,13 @@ struct bs_handle {
     std::vector<Slot> ring;
     int64_t next_ticket = 0;
     int64_t kernel_launches = 0;
+    // tile plan (static per calibration)
+    bool fast_ok = false;                // the staged kernel can be used
+    bs::TileRec *d_tiles = nullptr;      // plan, ordered: exact tiles, fast tiles, empty tiles
+    int n_tiles = 0, tiles_x = 0, tiles_y = 0;
+    int64_t n_fast = 0, n_exact = 0, n_empty = 0;
+    int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
+    int stage_bytes = 0, smem_bytes = 0, grid = 0;
     uint64_t device_bytes = 0, scratch_bytes = 0;
     std::string err;
 };
@@ -122,11 +132,217 @@ int require_device(bs_handle *h)
     return BS_OK;
 }
 
+
+// ---- TMA descriptors ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encoder()
+{
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// Source frame as a 2-D tensor of 4-byte elements: [h rows][pitch / 4 elements].
+int encode_frame_map(CUtensorMap *m, const void *ptr, size_t pitch, int h, int box_we, int box_h)
+{
+    EncodeTiledFn enc = get_encoder();
+    if (!enc) return -1;
+    cuuint64_t gdim[2] = {(cuuint64_t)(pitch / 4), (cuuint64_t)h};
+    cuuint64_t gstride[1] = {(cuuint64_t)pitch};
+    cuuint32_t box[2] = {(cuuint32_t)box_we, (cuuint32_t)box_h};
+    cuuint32_t estr[2] = {1, 1};
+    return (int)enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void *>(ptr), gdim, gstride, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+}
+
+constexpr int kStageBytesMax = 32 * 1024;   // per-stage cap on a camera's source box
+
+// Build the tile plan on the device and post-process it on the host (once per calibration).
+int build_plan(bs_handle *h)
+{
+    h->fast_ok = false;
+    h->tiles_x = (h->W + bs::kTileW - 1) / bs::kTileW;
+    h->tiles_y = (h->H + bs::kTileH - 1) / bs::kTileH;
+    h->n_tiles = h->tiles_x * h->tiles_y;
+    if ((h->flags & BS_FLAG_EXACT_ONLY) || h->n_cams > bs::kMaxCamsPerLaunch || !get_encoder()) return BS_OK;
+
+    bs::PlanArgs *P = new bs::PlanArgs;
+    memset(P, 0, sizeof *P);
+    for (int i = 0; i < h->n_cams; ++i) {
+        memcpy(P->M[i], &h->M[9 * i], 9 * sizeof(double));
+        P->w[i] = h->sw[i];
+        P->h[i] = h->sh[i];
+    }
+    P->n_cams = h->n_cams;
+    P->W = h->W;
+    P->H = h->H;
+    P->block_w = opencv_block_width(h->W, h->H);
+    P->legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
+    P->tiles_x = h->tiles_x;
+    P->tiles_y = h->tiles_y;
+    const size_t bytes = sizeof(bs::TileRec) * (size_t)h->n_tiles;
+    cudaError_t e = cudaMalloc(&h->d_tiles, bytes);
+    if (e == cudaSuccess) {
+        P->out = h->d_tiles;
+        bs::plan_kernel<<<dim3(h->tiles_x, h->tiles_y), bs::kThreads, 0, h->s_compute>>>(*P);
+        e = cudaGetLastError();
+    }
+    delete P;
+    std::vector<bs::TileRec> recs(h->n_tiles);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(recs.data(), h->d_tiles, bytes, cudaMemcpyDeviceToHost, h->s_compute);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
+    if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "tile plan failed: %s", cudaGetErrorString(e));
+    h->kernel_launches++;
+    h->device_bytes += bytes;
+    h->scratch_bytes += bytes;
+
+    // per-camera TMA box = largest source box among its tiles; tiles whose box is too big go exact
+    int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
+    for (bs::TileRec &r : recs) {
+        if (r.type != bs::kTileFast) continue;
+        bool ok = true;
+        int twe[bs::kMaxLayers], tbh[bs::kMaxLayers];
+        for (int l = 0; l < r.n_layers; ++l) {
+            const int e0 = bs::box_elem0(r.bx0[l]), e1 = (3 * r.bx1[l] + 2) >> 2;   // box starts 16-byte aligned
+            twe[l] = (e1 - e0 + 1 + 3) & ~3;            // inner extent must be a multiple of 16 bytes
+            tbh[l] = r.by1[l] - r.by0[l] + 1;
+            if (twe[l] > 256 || tbh[l] > 256 || twe[l] * 4 * tbh[l] > kStageBytesMax) ok = false;
+        }
+        if (!ok) {
+            r.type = bs::kTileExact;
+            continue;
+        }
+        for (int l = 0; l < r.n_layers; ++l) {
+            we[r.cam[l]] = std::max(we[r.cam[l]], twe[l]);
+            bh[r.cam[l]] = std::max(bh[r.cam[l]], tbh[l]);
+        }
+    }
+    // the per-camera maxima of width and height come from different tiles; re-check the product
+    int stage = 0;
+    for (int c = 0; c < h->n_cams; ++c) {
+        if (we[c] * 4 * bh[c] > kStageBytesMax) {
+            // shrink by sending this camera's largest-box tiles to the exact path
+            for (bs::TileRec &r : recs) {
+                if (r.type != bs::kTileFast) continue;
+                for (int l = 0; l < r.n_layers; ++l)
+                    if (r.cam[l] == c) r.type = bs::kTileExact;
+            }
+            we[c] = bh[c] = 0;
+        }
+        h->box_we[c] = we[c];
+        h->box_h[c] = bh[c];
+        stage = std::max(stage, we[c] * 4 * bh[c]);
+    }
+    h->stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
+
+    std::vector<bs::TileRec> ordered;
+    ordered.reserve(recs.size());
+    h->n_fast = h->n_exact = h->n_empty = 0;
+    for (const bs::TileRec &r : recs)
+        if (r.type == bs::kTileExact) ordered.push_back(r), h->n_exact++;
+    for (const bs::TileRec &r : recs)
+        if (r.type == bs::kTileFast) ordered.push_back(r), h->n_fast++;
+    for (const bs::TileRec &r : recs)
+        if (r.type == bs::kTileEmpty) ordered.push_back(r), h->n_empty++;
+    BS_CUDA(h, cudaMemcpy(h->d_tiles, ordered.data(), bytes, cudaMemcpyHostToDevice));
+
+    if (getenv("BS_DEBUG_PLAN")) {
+        for (int c = 0; c < h->n_cams; ++c)
+            fprintf(stderr, "[plan] cam %d: %dx%d box %d elems x %d rows\n", c, h->sw[c], h->sh[c], h->box_we[c],
+                    h->box_h[c]);
+        for (const bs::TileRec &r : ordered) {
+            fprintf(stderr, "[plan] tile (%d,%d) type %d layers %d unc %d full %x:", r.tx, r.ty, r.type, r.n_layers,
+                    r.has_uncovered, r.full_mask);
+            for (int l = 0; l < r.n_layers; ++l)
+                fprintf(stderr, " [cam %d x %d..%d y %d..%d exact %x]", r.cam[l], r.bx0[l], r.bx1[l], r.by0[l],
+                        r.by1[l], r.exact_mask[l]);
+            fprintf(stderr, "\n");
+        }
+    }
+    h->smem_bytes = 2 * h->stage_bytes + 2 * bs::kOutTileBytes + bs::kLutBytes + 64;
+    BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    h->smem_bytes));
+    int per_sm = 0, sms = 0;
+    BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kThreads,
+                                                             h->smem_bytes));
+    BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+    if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
+    h->grid = std::min(h->n_tiles, per_sm * sms);
+    if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, std::min(h->n_tiles, atoi(g)));
+    h->fast_ok = true;
+    return BS_OK;
+}
+
+bool aligned16(const void *p, size_t pitch) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (pitch & 15) == 0; }
+
 // Launch the kernels of one frame.  Cameras beyond the per-launch limit go in further
 // launches that keep what is already on the canvas (later cameras win, Appendix A.5).
 int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch, uint8_t *d_canvas,
                  size_t cpitch, bool keep, cudaStream_t stream)
 {
+    static const bool dbg_sync = getenv("BS_DEBUG_SYNC") != nullptr;
+    if (dbg_sync) {
+        cudaError_t e0 = cudaDeviceSynchronize();
+        if (e0 != cudaSuccess) return fail(h, BS_ERR_CUDA, "[debug] error pending BEFORE launch_frame: %s", cudaGetErrorString(e0));
+    }
+    bool fast = h->fast_ok && aligned16(d_canvas, cpitch);
+    for (int i = 0; fast && i < h->n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
+    if (fast) {
+        bs::FastArgs FA;
+        memset(&FA, 0, sizeof FA);
+        bs::FrameArgs &A = FA.F;
+        A.n_cams = h->n_cams;
+        for (int i = 0; i < A.n_cams; ++i) {
+            memcpy(A.cam[i].M, &h->M[9 * i], 9 * sizeof(double));
+            A.cam[i].ptr = static_cast<const uint8_t *>(d_frames[i]);
+            A.cam[i].pitch = (long long)pitch[i];
+            A.cam[i].w = h->sw[i];
+            A.cam[i].h = h->sh[i];
+            FA.box_we[i] = h->box_we[i];
+            FA.box_h[i] = h->box_h[i];
+            if (h->box_we[i] > 0) {
+                const int er = encode_frame_map(&FA.tmap[i], d_frames[i], pitch[i], h->sh[i], h->box_we[i],
+                                                h->box_h[i]);
+                if (er != 0)
+                    return fail(h, BS_ERR_CUDA,
+                                "cuTensorMapEncodeTiled failed (%d) for camera %d: ptr=%p pitch=%zu h=%d box=%dx%d", er,
+                                i, d_frames[i], pitch[i], h->sh[i], h->box_we[i], h->box_h[i]);
+            }
+        }
+        A.canvas = d_canvas;
+        A.cpitch = (long long)cpitch;
+        A.W = h->W;
+        A.H = h->H;
+        A.block_w = opencv_block_width(h->W, h->H);
+        A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
+        A.keep_canvas = keep ? 1 : 0;
+        FA.tiles = h->d_tiles;
+        FA.n_tiles = h->n_tiles;
+        FA.stage_bytes = h->stage_bytes;
+        bs::stitch_fast_kernel<<<h->grid, bs::kThreads, h->smem_bytes, stream>>>(FA);
+        BS_CUDA(h, cudaGetLastError());
+        if (dbg_sync) {
+            cudaError_t e1 = cudaDeviceSynchronize();
+            if (e1 != cudaSuccess)
+                return fail(h, BS_ERR_CUDA, "[debug] stitch_fast_kernel (grid %d, smem %d) faulted: %s", h->grid,
+                            h->smem_bytes, cudaGetErrorString(e1));
+        }
+        h->kernel_launches++;
+        return BS_OK;
+    }
     for (int base = 0; base < h->n_cams; base += bs::kMaxCamsPerLaunch) {
         bs::FrameArgs A;
         memset(&A, 0, sizeof A);
@@ -241,6 +457,12 @@ int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int
         return BS_ERR_CUDA;
     }
     g_last_device = device_id;
+    rc = build_plan(h);
+    if (rc != BS_OK) {
+        g_last_error = h->err;
+        bs_destroy(h);
+        return rc;
+    }
     *out = h;
     return BS_OK;
 }
@@ -259,6 +481,7 @@ int bs_destroy(bs_handle *h)
         if (s.ev_kernel) cudaEventDestroy(s.ev_kernel);
         if (s.ev_done) cudaEventDestroy(s.ev_done);
     }
+    cudaFree(h->d_tiles);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
@@ -409,11 +632,20 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
     out->n_cams = h->n_cams;
     out->canvas_w = h->W;
     out->canvas_h = h->H;
-    out->tile_w = bs::kExactTileW;
-    out->tile_h = bs::kExactTileH;
-    out->n_tiles = (int64_t)((h->W + bs::kExactTileW - 1) / bs::kExactTileW) *
-                   ((h->H + bs::kExactTileH - 1) / bs::kExactTileH);
-    out->n_tiles_exact = out->n_tiles;
+    if (h->fast_ok) {
+        out->tile_w = bs::kTileW;
+        out->tile_h = bs::kTileH;
+        out->n_tiles = h->n_tiles;
+        out->n_tiles_fast = h->n_fast;
+        out->n_tiles_exact = h->n_exact;
+        out->n_tiles_empty = h->n_empty;
+    } else {
+        out->tile_w = bs::kExactTileW;
+        out->tile_h = bs::kExactTileH;
+        out->n_tiles = (int64_t)((h->W + bs::kExactTileW - 1) / bs::kExactTileW) *
+                       ((h->H + bs::kExactTileH - 1) / bs::kExactTileH);
+        out->n_tiles_exact = out->n_tiles;
+    }
     out->kernel_launches = h->kernel_launches;
     out->frames_submitted = h->next_ticket;
     out->device_bytes = h->device_bytes;

@@ -1,0 +1,251 @@
+// stitch_plan.cuh -- the tile plan: static per calibration, built once on the device.
+//
+// The reference recomputes everything per frame (cv::warpPerspective regenerates the coordinate
+// maps on every call, /root/reference/tools/stitch/main.cpp:150-151), but H and result_size are
+// fixed for the whole run (:53-73).  The plan classifies every 128x32 canvas tile once:
+//   EMPTY  no camera writes any pixel                      -> zero fill
+//   FAST   every written pixel is an interior (4-tap) pixel of one of <= 4 cameras whose source
+//          bounding boxes fit a shared-memory stage        -> staged kernel, one pass per camera
+//   EXACT  anything else (last-row/column pixels, too many cameras, huge boxes) -> per-pixel kernel
+// and, for FAST tiles, proves by exhaustive comparison which 8-pixel runs may use the cheap
+// fp32 coordinate recurrence (fast_run_coords) instead of the exact fp64 form.
+#pragma once
+
+#include "stitch_common.cuh"
+
+namespace bs {
+
+constexpr int kTileW = 128;
+constexpr int kTileH = 32;
+constexpr int kThreads = 256;
+constexpr int kRun = 8;            // consecutive pixels per thread and row
+constexpr int kMaxLayers = 4;      // cameras that may share one FAST tile
+constexpr int kMaxPlanCams = 64;
+
+enum TileType : uint8_t { kTileEmpty = 0, kTileFast = 1, kTileExact = 2 };
+
+struct TileRec {                   // 64 bytes
+    uint16_t tx, ty;               // tile coordinates
+    uint8_t type;                  // TileType
+    uint8_t n_layers;
+    uint8_t has_uncovered;         // some in-canvas pixel of the tile is written by no layer
+    uint8_t full_mask;             // bit l: layer l covers every in-canvas pixel of the tile
+    uint8_t cam[kMaxLayers];       // ascending camera index = compositing order
+    int16_t bx0[kMaxLayers], by0[kMaxLayers], bx1[kMaxLayers], by1[kMaxLayers];  // texel bbox incl. taps
+    uint32_t exact_mask[kMaxLayers];   // bit (warp*2 + pass): that half-warp-row must use exact coords
+    uint32_t pad;
+};
+static_assert(sizeof(TileRec) == 64, "TileRec layout");
+
+// ---- cheap coordinates for a run of kRun pixels on one canvas row ----------------------------
+// Anchor at the run's 5th pixel in fp64, then fX(xc + k) = fXc + k (32 M0 - M6 fXc) / W(xc + k)
+// evaluated in fp32.  The result is only used where the plan has checked, pixel by pixel, that
+// it equals coord_exact(); every operation is an explicit intrinsic so plan and frame kernels
+// execute the same instruction sequence.
+struct RunAnchor {
+    int Ix, Iy;        // rint(fXc), rint(fYc) minus the float-magic bias
+    float fx, fy;      // fXc - Ix, fYc - Iy
+    float Cx, Cy;      // numerators of the per-pixel increment
+    float W0, m6;
+};
+
+constexpr int kMagicBias = 0x4B400000;   // bits of 12582912.0f = 1.5 * 2^23
+
+__device__ __forceinline__ RunAnchor run_anchor(const double *__restrict__ M, int xc, int y)
+{
+    const double dx = (double)xc, dy = (double)y;
+    const double Xn = fma(M[0], dx, fma(M[1], dy, M[2]));
+    const double Yn = fma(M[3], dx, fma(M[4], dy, M[5]));
+    const double Wn = fma(M[6], dx, fma(M[7], dy, M[8]));
+    const double r = 32.0 / Wn;
+    double fX = fmin(fmax(Xn * r, -1.0e9), 1.0e9);
+    double fY = fmin(fmax(Yn * r, -1.0e9), 1.0e9);
+    const double rX = rint(fX), rY = rint(fY);
+    RunAnchor a;
+    a.Ix = (int)rX - kMagicBias;
+    a.Iy = (int)rY - kMagicBias;
+    a.fx = (float)(fX - rX);
+    a.fy = (float)(fY - rY);
+    a.Cx = (float)fma(-M[6], fX, 32.0 * M[0]);
+    a.Cy = (float)fma(-M[6], fY, 32.0 * M[3]);
+    a.W0 = (float)Wn;
+    a.m6 = (float)M[6];
+    return a;
+}
+
+// k in [0, kRun): pixel xc - 4 + k
+__device__ __forceinline__ void run_coord(const RunAnchor &a, int k, int &X, int &Y)
+{
+    const float kf = (float)(k - kRun / 2);
+    const float Wk = __fmaf_rn(kf, a.m6, a.W0);
+    float rk;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rk) : "f"(Wk));
+    const float t = __fmul_rn(kf, rk);
+    const float sX = __fmaf_rn(a.Cx, t, a.fx);
+    const float sY = __fmaf_rn(a.Cy, t, a.fy);
+    // round half to even through the fp32 adder: (s + 1.5*2^23) has rint(s) in its low mantissa bits
+    X = __float_as_int(__fadd_rn(sX, 12582912.0f)) + a.Ix;
+    Y = __float_as_int(__fadd_rn(sY, 12582912.0f)) + a.Iy;
+}
+
+// thread -> pixels of a tile, shared by the plan and the staged kernel:
+// column group g = tid & 15 (8 pixels wide), rows (tid >> 4) and (tid >> 4) + 16.
+__device__ __forceinline__ int tile_col(int tid) { return (tid & 15) * kRun; }
+__device__ __forceinline__ int tile_row(int tid, int pass) { return (tid >> 4) + 16 * pass; }
+
+struct PlanArgs {
+    double M[kMaxPlanCams][9];
+    int w[kMaxPlanCams], h[kMaxPlanCams];
+    int n_cams;
+    int W, H;
+    int block_w;
+    int legacy_border;
+    int tiles_x, tiles_y;
+    TileRec *out;
+};
+
+// 0 = not written, 1 = interior (Appendix A.3), 2 = written by the last-row/column rule (A.4)
+__device__ __forceinline__ int cover_class(int X, int Y, int w, int h, int legacy)
+{
+    const int sx = sat_s16(X >> kFracBits), sy = sat_s16(Y >> kFracBits);
+    if (sx < 0 || sy < 0 || sx > w - 1 || sy > h - 1) return 0;
+    if (sx < w - 1 && sy < h - 1) return 1;
+    return legacy ? 0 : 2;
+}
+
+// One CTA per tile.
+__global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ PlanArgs P)
+{
+    __shared__ unsigned long long s_win;       // cameras that win at least one pixel
+    __shared__ int s_edge_win, s_uncovered;
+    __shared__ int s_bx0[kMaxLayers], s_by0[kMaxLayers], s_bx1[kMaxLayers], s_by1[kMaxLayers];
+    __shared__ int s_notfull[kMaxLayers];
+    __shared__ unsigned s_exact[kMaxLayers];
+
+    const int tid = threadIdx.x;
+    const int tx = blockIdx.x, ty = blockIdx.y;
+    if (tid == 0) {
+        s_win = 0ull;
+        s_edge_win = 0;
+        s_uncovered = 0;
+    }
+    if (tid < kMaxLayers) {
+        s_bx0[tid] = s_by0[tid] = INT_MAX;
+        s_bx1[tid] = s_by1[tid] = INT_MIN;
+        s_notfull[tid] = 0;
+        s_exact[tid] = 0u;
+    }
+    __syncthreads();
+
+    const int x0 = tx * kTileW + tile_col(tid);
+    // ---- phase 1: who wins each pixel -----------------------------------------------------
+    unsigned long long my_win = 0ull;
+    int my_edge = 0, my_unc = 0;
+    for (int pass = 0; pass < 2; ++pass) {
+        const int y = ty * kTileH + tile_row(tid, pass);
+        if (y >= P.H) continue;
+        for (int k = 0; k < kRun; ++k) {
+            const int x = x0 + k;
+            if (x >= P.W) break;
+            const int xb = (x / P.block_w) * P.block_w;
+            int cls = 0, i = P.n_cams - 1;
+            for (; i >= 0; --i) {
+                int X, Y;
+                coord_exact(P.M[i], xb, x - xb, y, X, Y);
+                cls = cover_class(X, Y, P.w[i], P.h[i], P.legacy_border);
+                if (cls) break;
+            }
+            if (cls == 0) my_unc = 1;
+            else {
+                my_win |= 1ull << i;
+                if (cls == 2) my_edge = 1;
+            }
+        }
+    }
+    if (my_win) atomicOr(&s_win, my_win);
+    if (my_edge) atomicOr(&s_edge_win, 1);
+    if (my_unc) atomicOr(&s_uncovered, 1);
+    __syncthreads();
+
+    TileRec rec;
+    memset(&rec, 0, sizeof rec);
+    rec.tx = (uint16_t)tx;
+    rec.ty = (uint16_t)ty;
+    const unsigned long long win = s_win;
+    const int n_layers = __popcll(win);
+    rec.has_uncovered = (uint8_t)s_uncovered;
+    TileRec *dst = P.out + (size_t)ty * P.tiles_x + tx;
+    if (n_layers == 0) {
+        rec.type = kTileEmpty;
+        if (tid == 0) *dst = rec;
+        return;
+    }
+    if (n_layers > kMaxLayers || s_edge_win) {
+        rec.type = kTileExact;
+        if (tid == 0) *dst = rec;
+        return;
+    }
+    int cams[kMaxLayers];
+    {
+        unsigned long long m = win;
+        for (int l = 0; l < n_layers; ++l) {
+            cams[l] = __ffsll((long long)m) - 1;
+            m &= m - 1;
+        }
+    }
+    // ---- phase 2: per layer, source bounding box and validity of the cheap coordinates -----
+    const int warp = tid >> 5;
+    for (int l = 0; l < n_layers; ++l) {
+        const int c = cams[l];
+        int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN, notfull = 0;
+        for (int pass = 0; pass < 2; ++pass) {
+            const int y = ty * kTileH + tile_row(tid, pass);
+            if (y >= P.H) continue;
+            const RunAnchor a = run_anchor(P.M[c], x0 + kRun / 2, y);
+            bool mismatch = false;
+            for (int k = 0; k < kRun; ++k) {
+                const int x = x0 + k;
+                if (x >= P.W) break;
+                const int xb = (x / P.block_w) * P.block_w;
+                int X, Y, Xf, Yf;
+                coord_exact(P.M[c], xb, x - xb, y, X, Y);
+                run_coord(a, k, Xf, Yf);
+                mismatch |= (X != Xf) | (Y != Yf);
+                if (cover_class(X, Y, P.w[c], P.h[c], 1) == 1) {   // interior only
+                    const int sx = X >> kFracBits, sy = Y >> kFracBits;
+                    bx0 = min(bx0, sx);
+                    by0 = min(by0, sy);
+                    bx1 = max(bx1, sx + 1);
+                    by1 = max(by1, sy + 1);
+                } else {
+                    notfull = 1;
+                }
+            }
+            if (mismatch) atomicOr(&s_exact[l], 1u << (warp * 2 + pass));
+        }
+        if (bx0 != INT_MAX) {
+            atomicMin(&s_bx0[l], bx0);
+            atomicMin(&s_by0[l], by0);
+            atomicMax(&s_bx1[l], bx1);
+            atomicMax(&s_by1[l], by1);
+        }
+        if (notfull) atomicOr(&s_notfull[l], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        rec.type = kTileFast;
+        rec.n_layers = (uint8_t)n_layers;
+        for (int l = 0; l < n_layers; ++l) {
+            rec.cam[l] = (uint8_t)cams[l];
+            rec.bx0[l] = (int16_t)s_bx0[l];
+            rec.by0[l] = (int16_t)s_by0[l];
+            rec.bx1[l] = (int16_t)s_bx1[l];
+            rec.by1[l] = (int16_t)s_by1[l];
+            rec.exact_mask[l] = s_exact[l];
+            if (!s_notfull[l]) rec.full_mask |= (uint8_t)(1u << l);
+        }
+        *dst = rec;
+    }
+}
+
+}  // namespace bs

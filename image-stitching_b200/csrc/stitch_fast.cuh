@@ -107,15 +107,16 @@ __device__ __forceinline__ uint2 lut_entry(int idx)
     return e;
 }
 
-// One interior pixel from a staged box.  `wa` = shared address of the aligned word holding the
-// first byte of texel (sx, sy), `sh` = 8 * (byte offset of that texel in the word), `pitch` =
-// stage row pitch in bytes.  Returns B | G<<8 | R<<16.
-__device__ __forceinline__ uint32_t sample_staged(uint32_t wa, uint32_t sh, int pitch, uint32_t lut_base, int X,
-                                                  int Y)
+// One interior pixel from a staged box.  `o` = shared byte address of texel (sx, sy) (any
+// alignment), `pitch` = stage row pitch in bytes, `lut_off` = shared address of the weight-table
+// entry.  Returns B | G<<8 | R<<16.
+__device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint32_t lut_off)
 {
+    const uint32_t wa = o & ~3u;
+    const uint32_t sh = o << 3;          // the funnel shift uses the low 5 bits: 8 * (o & 3)
     const uint32_t w0 = lds32(wa), w1 = lds32(wa + 4), w2 = lds32(wa + 8);
     const uint32_t v0 = lds32(wa + pitch), v1 = lds32(wa + pitch + 4), v2 = lds32(wa + pitch + 8);
-    const uint2 wt = lds64(lut_base + (uint32_t)((((Y & 31) << 5) | (X & 31)) << 3));
+    const uint2 wt = lds64(lut_off);
     // six aligned bytes of each row: r?a = [B0 G0 R0 B1], r?b = [G1 R1 . .]
     const uint32_t r0a = __funnelshift_r(w0, w1, sh), r0b = __funnelshift_r(w1, w2, sh);
     const uint32_t r1a = __funnelshift_r(v0, v1, sh), r1b = __funnelshift_r(v1, v2, sh);
@@ -133,6 +134,89 @@ __device__ __forceinline__ uint32_t sample_staged(uint32_t wa, uint32_t sh, int 
     return __byte_perm(bg, vr, 0x7610);
 }
 
+// Store one row's pixel of every lane into the output tile: lanes 4q..4q+3 hold 4 adjacent
+// pixels = 12 bytes = 3 words; lane 4q+i (i < 3) builds word i from its own pixel and its right
+// neighbour's and stores it.  `row_addr` = shared address of the tile row, `keep` = this lane's
+// word must not be stored (used by partially covered layers, which fall back to byte stores).
+__device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, int lane, uint32_t sel)
+{
+    const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
+    const uint32_t word = __byte_perm(px, nxt, sel);
+    if ((lane & 3) != 3)
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(row_addr + 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3))), "r"(word)
+                     : "memory");
+}
+
+// Shared address of the first output-tile row of thread tid's run, at the start of its warp's
+// 96-byte (32-pixel) span.
+__device__ __forceinline__ uint32_t out_span(uint32_t out_tile, int tid)
+{
+    return out_tile + (uint32_t)(tile_row0(tid) * (kTileW * 3) + ((tid & (kTileW - 1)) >> 5) * 96);
+}
+
+// Hot path: the layer covers every pixel of the tile with interior samples, the tile lies inside
+// the canvas and the plan verified the cheap coordinates for this warp's whole 32x16 block.
+// No coverage tests, no fp64 beyond the run's anchor; fully unrolled so k is a constant.
+__device__ __forceinline__ void run_layer_full(const CamDev &cam, int pitch, uint32_t stage_origin, uint32_t lut_base,
+                                               uint32_t out_tile, int x, int y0, int tid)
+{
+    const int lane = tid & 31;
+    const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
+    const uint32_t out_col = out_span(out_tile, tid);
+    const RunAnchor a = run_anchor(cam.M, x, y0 + kRun / 2);
+    const uint32_t run_base = stage_origin + (uint32_t)((a.by >> kFracBits) * pitch + (a.bx >> kFracBits) * 3);
+#pragma unroll
+    for (int k = 0; k < kRun; ++k) {
+        int xbits, ybits;
+        run_coord_bits(a, k, xbits, ybits);
+        const uint32_t o = run_base + (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
+        const uint32_t lut_off = lut_base + (uint32_t)(((ybits & 31) << 8) + ((xbits & 31) << 3));
+        const uint32_t px = sample_staged(o, pitch, lut_off);
+        store_row_pixel(px, out_col + (uint32_t)(k * (kTileW * 3)), lane, sel);
+    }
+}
+
+// General path: partially covered layers, tiles that stick out of the canvas, and warps for which
+// the plan found at least one pixel where the cheap coordinates differ (those 32x4 groups use
+// the exact fp64 form).  Same arithmetic per pixel, with coverage tests and byte stores.
+__device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &cam, int pitch, uint32_t stage_origin,
+                                               uint32_t lut_base, uint32_t out_tile, uint32_t exact_mask, bool full,
+                                               bool first_layer, int x, int y0, int tid)
+{
+    const int lane = tid & 31;
+    const uint32_t out_col = out_span(out_tile, tid);
+    const RunAnchor a = run_anchor(cam.M, x, y0 + kRun / 2);
+    const int xb = (x / A.F.block_w) * A.F.block_w;
+#pragma unroll 1
+    for (int k = 0; k < kRun; ++k) {
+        int X, Y;
+        if ((exact_mask >> exact_bit(tid, k)) & 1) {     // warp-uniform
+            coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
+        } else {
+            // same instruction sequence as run_coord_bits, with k at run time
+            const float kf = (float)(k - kRun / 2);
+            const float sX = __fmaf_rn(kf, __fmaf_rn(kf, a.Ex, a.Dx), a.fx);
+            const float sY = __fmaf_rn(kf, __fmaf_rn(kf, a.Ey, a.Dy), a.fy);
+            X = __float_as_int(__fadd_rn(sX, 12582912.0f)) + a.bx;
+            Y = __float_as_int(__fadd_rn(sY, 12582912.0f)) + a.by;
+        }
+        const int sx = X >> kFracBits, sy = Y >> kFracBits;
+        bool in = (x < A.F.W) && (y0 + k < A.F.H);
+        if (!full) in = in && sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1;
+        const uint32_t o = in ? stage_origin + (uint32_t)(sy * pitch + sx * 3) : out_tile;   // any valid address
+        const uint32_t lut_off = lut_base + (uint32_t)((((Y & 31) << 5) | (X & 31)) << 3);
+        uint32_t px = sample_staged(o, pitch, lut_off);
+        // the first layer also defines the background: pixels it does not cover start at 0
+        if (in || first_layer) {
+            if (!in) px = 0;
+            const uint32_t p8 = out_col + (uint32_t)(k * (kTileW * 3)) + 3u * (uint32_t)lane;
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8), "r"(px) : "memory");
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 1), "r"(px >> 8) : "memory");
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 2), "r"(px >> 16) : "memory");
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kThreads, 3) stitch_fast_kernel(const __grid_constant__ FastArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -141,7 +225,6 @@ __global__ void __launch_bounds__(kThreads, 3) stitch_fast_kernel(const __grid_c
     uint64_t *const bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(lut) + kLutBytes);
 
     const int tid = threadIdx.x;
-    const int warp = tid >> 5;
     for (int i = tid; i < 1024; i += kThreads) lut[i] = lut_entry(i);
     if (tid == 0) {
         mbar_init(&bars[0], 1);
@@ -180,7 +263,6 @@ __global__ void __launch_bounds__(kThreads, 3) stitch_fast_kernel(const __grid_c
 
     uint32_t n_consumed = 0;
     int out_sel = 0;
-    const int gcol = tile_col(tid);
     for (int k = blockIdx.x; k < A.n_tiles; k += gridDim.x) {
         const TileRec *const rec = &A.tiles[k];
         const int tx0 = rec->tx * kTileW, ty0 = rec->ty * kTileH;
@@ -204,16 +286,15 @@ __global__ void __launch_bounds__(kThreads, 3) stitch_fast_kernel(const __grid_c
                     }
                 }
             } else {
-                for (int pass = 0; pass < 2; ++pass) {
-                    const int y = ty0 + tile_row(tid, pass);
-                    exact_quad(A.F, tx0 + gcol, y);
-                    exact_quad(A.F, tx0 + gcol + 4, y);
-                }
+                // exact tile: thread t takes the 4-pixel group (t & 31) of rows (t >> 5) + 8 j
+                for (int j = 0; j < kTileH / 8; ++j) exact_quad(A.F, tx0 + (tid & 31) * 4, ty0 + (tid >> 5) + 8 * j);
             }
             continue;
         }
 
-        uint8_t *const outt = out_base + out_sel * kOutTileBytes;
+        const uint32_t outt = smem_u32(out_base + out_sel * kOutTileBytes);
+        const int x = tx0 + tile_col(tid);
+        const int y0 = ty0 + tile_row0(tid);
         for (int l = 0; l < n_layers; ++l) {
             const int c = rec->cam[l];
             const CamDev &cam = A.F.cam[c];
@@ -221,77 +302,31 @@ __global__ void __launch_bounds__(kThreads, 3) stitch_fast_kernel(const __grid_c
             const int pitch = A.box_we[c] * 4;
             const bool full = ((rec->full_mask >> l) & 1) && !edge_tile;
             const uint32_t exact_mask = rec->exact_mask[l];
-            // byte offset of texel (0, 0) of this camera relative to the stage, were the whole frame staged
-            const int origin = -(int)rec->by0[l] * pitch - 4 * box_elem0((int)rec->bx0[l]);
-            const uint32_t stage = smem_u32(smem + s * A.stage_bytes);
+            // shared address texel (0, 0) of this camera would have, were the whole frame staged
+            const uint32_t stage_origin = smem_u32(smem + s * A.stage_bytes) -
+                                          (uint32_t)((int)rec->by0[l] * pitch + 4 * box_elem0((int)rec->bx0[l]));
             mbar_wait(&bars[s], (n_consumed >> 1) & 1);
-#pragma unroll 1
-            for (int pass = 0; pass < 2; ++pass) {
-                const int row = tile_row(tid, pass);
-                const int y = ty0 + row;
-                const int x0 = tx0 + gcol;
-                int X[kRun], Y[kRun];
-                if ((exact_mask >> (warp * 2 + pass)) & 1) {
-#pragma unroll
-                    for (int j = 0; j < kRun; ++j) {
-                        const int x = x0 + j;
-                        const int xb = (x / A.F.block_w) * A.F.block_w;
-                        coord_exact(cam.M, xb, x - xb, y, X[j], Y[j]);
-                    }
-                } else {
-                    const RunAnchor a = run_anchor(cam.M, x0 + kRun / 2, y);
-#pragma unroll
-                    for (int j = 0; j < kRun; ++j) run_coord(a, j, X[j], Y[j]);
-                }
-                uint32_t px[kRun];
-                uint32_t covered = 0;
-#pragma unroll
-                for (int j = 0; j < kRun; ++j) {
-                    const int sx = X[j] >> kFracBits, sy = Y[j] >> kFracBits;
-                    bool in = full || (sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1);
-                    if (edge_tile) in = in && (x0 + j < A.F.W) && (y < A.F.H);
-                    const int o = in ? origin + sy * pitch + 3 * sx : 0;
-                    px[j] = sample_staged(stage + (uint32_t)(o & ~3), (uint32_t)(o & 3) * 8u, pitch, lut_base, X[j],
-                                          Y[j]);
-                    covered |= (in ? 1u : 0u) << j;
-                }
-                uint8_t *o8 = outt + row * (kTileW * 3) + gcol * 3;
-                if (covered == 0xFFu || l == 0) {
-                    // first layer also defines the background: uncovered pixels start at 0
-#pragma unroll
-                    for (int j = 0; j < kRun; ++j)
-                        if (!((covered >> j) & 1)) px[j] = 0;
-                    uint2 *o64 = reinterpret_cast<uint2 *>(o8);
-                    o64[0] = make_uint2(__byte_perm(px[0], px[1], 0x4210), __byte_perm(px[1], px[2], 0x5421));
-                    o64[1] = make_uint2(__byte_perm(px[2], px[3], 0x6542), __byte_perm(px[4], px[5], 0x4210));
-                    o64[2] = make_uint2(__byte_perm(px[5], px[6], 0x5421), __byte_perm(px[6], px[7], 0x6542));
-                } else {
-#pragma unroll
-                    for (int j = 0; j < kRun; ++j)
-                        if ((covered >> j) & 1) {
-                            o8[3 * j + 0] = (uint8_t)px[j];
-                            o8[3 * j + 1] = (uint8_t)(px[j] >> 8);
-                            o8[3 * j + 2] = (uint8_t)(px[j] >> 16);
-                        }
-                }
-            }
+            const uint32_t warp_mask = (exact_mask >> ((tid >> 5) * 4)) & 15u;    // this warp's 4 row groups
+            if (full && warp_mask == 0u) run_layer_full(cam, pitch, stage_origin, lut_base, outt, x, y0, tid);
+            else run_layer_general(A, cam, pitch, stage_origin, lut_base, outt, exact_mask, full, l == 0, x, y0, tid);
             ++n_consumed;
-            __syncthreads();                 // stage s fully read; this layer's pixels are in outt
+            __syncthreads();                 // stage s fully read; this layer's pixels are in the tile
             if (tid == 0) issue_next();      // refill stage s while the next item computes
         }
         // ---- flush the tile: 32 rows x 384 bytes as 16-byte vector stores -----------------------
         {
+            const uint8_t *const ot = out_base + out_sel * kOutTileBytes;
             const int wbytes = min(kTileW, A.F.W - tx0) * 3;
 #pragma unroll
             for (int q = tid; q < kTileH * 24; q += kThreads) {
                 const int row = q / 24, cb = (q % 24) * 16;
                 if (ty0 + row >= A.F.H || cb >= wbytes) continue;
-                const uint4 v = *reinterpret_cast<const uint4 *>(outt + row * (kTileW * 3) + cb);
+                const uint4 v = *reinterpret_cast<const uint4 *>(ot + row * (kTileW * 3) + cb);
                 uint8_t *p = A.F.canvas + (long long)(ty0 + row) * A.F.cpitch + (long long)tx0 * 3 + cb;
                 if (cb + 16 <= wbytes) {
                     *reinterpret_cast<uint4 *>(p) = v;
                 } else {
-                    const uint8_t *sv = outt + row * (kTileW * 3) + cb;
+                    const uint8_t *sv = ot + row * (kTileW * 3) + cb;
                     for (int j = 0; j < wbytes - cb; ++j) p[j] = sv[j];
                 }
             }

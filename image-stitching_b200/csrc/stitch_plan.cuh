@@ -18,7 +18,7 @@ namespace bs {
 constexpr int kTileW = 128;
 constexpr int kTileH = 32;
 constexpr int kThreads = 256;
-constexpr int kRun = 8;            // consecutive pixels per thread and row
+constexpr int kRun = 16;           // vertical run: consecutive rows per thread
 constexpr int kMaxLayers = 4;      // cameras that may share one FAST tile
 constexpr int kMaxPlanCams = 64;
 
@@ -32,66 +32,69 @@ struct TileRec {                   // 64 bytes
     uint8_t full_mask;             // bit l: layer l covers every in-canvas pixel of the tile
     uint8_t cam[kMaxLayers];       // ascending camera index = compositing order
     int16_t bx0[kMaxLayers], by0[kMaxLayers], bx1[kMaxLayers], by1[kMaxLayers];  // texel bbox incl. taps
-    uint32_t exact_mask[kMaxLayers];   // bit (warp*2 + pass): that half-warp-row must use exact coords
+    uint32_t exact_mask[kMaxLayers];   // bit (warp*4 + row group): those 32x4 pixels must use exact coords
     uint32_t pad;
 };
 static_assert(sizeof(TileRec) == 64, "TileRec layout");
 
-// ---- cheap coordinates for a run of kRun pixels on one canvas row ----------------------------
-// Anchor at the run's 5th pixel in fp64, then fX(xc + k) = fXc + k (32 M0 - M6 fXc) / W(xc + k)
-// evaluated in fp32.  The result is only used where the plan has checked, pixel by pixel, that
-// it equals coord_exact(); every operation is an explicit intrinsic so plan and frame kernels
-// execute the same instruction sequence.
+// ---- cheap coordinates for a vertical run of kRun pixels (one canvas column) -----------------
+// Along a column the source coordinate is fX(yc + k) = fXc + k (32 M1 - M7 fXc) / (Wc + k M7).
+// The run is anchored at its 9th pixel in fp64; the increment is expanded to second order in k
+// and evaluated in fp32:  sX(k) = fx + k (Dx + k Ex).  The result is only used where the plan has
+// checked, pixel by pixel, that it equals coord_exact(); every operation is an explicit
+// intrinsic so the plan kernel and the frame kernel execute the same instruction sequence.
 struct RunAnchor {
-    int Ix, Iy;        // rint(fXc), rint(fYc) minus the float-magic bias
-    float fx, fy;      // fXc - Ix, fYc - Iy
-    float Cx, Cy;      // numerators of the per-pixel increment
-    float W0, m6;
+    int bx, by;        // integer bases (multiples of 32) minus the float-magic bias
+    float fx, fy;      // fXc - base, in [-0.5, 32.5)
+    float Dx, Ex, Dy, Ey;
 };
 
-constexpr int kMagicBias = 0x4B400000;   // bits of 12582912.0f = 1.5 * 2^23
+constexpr int kMagicBias = 0x4B400000;   // bits of 12582912.0f = 1.5 * 2^23 (a multiple of 32)
 
-__device__ __forceinline__ RunAnchor run_anchor(const double *__restrict__ M, int xc, int y)
+__device__ __forceinline__ RunAnchor run_anchor(const double *__restrict__ M, int x, int yc)
 {
-    const double dx = (double)xc, dy = (double)y;
-    const double Xn = fma(M[0], dx, fma(M[1], dy, M[2]));
-    const double Yn = fma(M[3], dx, fma(M[4], dy, M[5]));
-    const double Wn = fma(M[6], dx, fma(M[7], dy, M[8]));
-    const double r = 32.0 / Wn;
-    double fX = fmin(fmax(Xn * r, -1.0e9), 1.0e9);
-    double fY = fmin(fmax(Yn * r, -1.0e9), 1.0e9);
-    const double rX = rint(fX), rY = rint(fY);
+    const double dx = (double)x, dy = (double)yc;
+    const double Xn = fma(M[1], dy, fma(M[0], dx, M[2]));
+    const double Yn = fma(M[4], dy, fma(M[3], dx, M[5]));
+    const double Wn = fma(M[7], dy, fma(M[6], dx, M[8]));
+    const double inv = 1.0 / Wn;
+    const double fX = fmin(fmax(Xn * inv * 32.0, -1.0e9), 1.0e9);
+    const double fY = fmin(fmax(Yn * inv * 32.0, -1.0e9), 1.0e9);
+    const double eps = M[7] * inv;
+    const double dX = fma(-M[7], fX, 32.0 * M[1]) * inv;   // d fX / dk at k = 0
+    const double dY = fma(-M[7], fY, 32.0 * M[4]) * inv;
+    const int ix = (int)rint(fX) & ~31, iy = (int)rint(fY) & ~31;
     RunAnchor a;
-    a.Ix = (int)rX - kMagicBias;
-    a.Iy = (int)rY - kMagicBias;
-    a.fx = (float)(fX - rX);
-    a.fy = (float)(fY - rY);
-    a.Cx = (float)fma(-M[6], fX, 32.0 * M[0]);
-    a.Cy = (float)fma(-M[6], fY, 32.0 * M[3]);
-    a.W0 = (float)Wn;
-    a.m6 = (float)M[6];
+    a.bx = ix - kMagicBias;
+    a.by = iy - kMagicBias;
+    a.fx = (float)(fX - (double)ix);
+    a.fy = (float)(fY - (double)iy);
+    a.Dx = (float)dX;
+    a.Ex = (float)(-dX * eps);
+    a.Dy = (float)dY;
+    a.Ey = (float)(-dY * eps);
     return a;
 }
 
-// k in [0, kRun): pixel xc - 4 + k
-__device__ __forceinline__ void run_coord(const RunAnchor &a, int k, int &X, int &Y)
+// k in [0, kRun): pixel row yc - kRun/2 + k.  Returns the raw bits of (s + 1.5*2^23): their low
+// bits are rint(s) (round half to even, done by the fp32 adder), so with the anchor's bases
+//   X = bits + a.bx,   X & 31 = bits & 31,   X >> 5 = (bits >> 5) + (a.bx >> 5).
+__device__ __forceinline__ void run_coord_bits(const RunAnchor &a, int k, int &xbits, int &ybits)
 {
     const float kf = (float)(k - kRun / 2);
-    const float Wk = __fmaf_rn(kf, a.m6, a.W0);
-    float rk;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rk) : "f"(Wk));
-    const float t = __fmul_rn(kf, rk);
-    const float sX = __fmaf_rn(a.Cx, t, a.fx);
-    const float sY = __fmaf_rn(a.Cy, t, a.fy);
-    // round half to even through the fp32 adder: (s + 1.5*2^23) has rint(s) in its low mantissa bits
-    X = __float_as_int(__fadd_rn(sX, 12582912.0f)) + a.Ix;
-    Y = __float_as_int(__fadd_rn(sY, 12582912.0f)) + a.Iy;
+    const float sX = __fmaf_rn(kf, __fmaf_rn(kf, a.Ex, a.Dx), a.fx);
+    const float sY = __fmaf_rn(kf, __fmaf_rn(kf, a.Ey, a.Dy), a.fy);
+    xbits = __float_as_int(__fadd_rn(sX, 12582912.0f));
+    ybits = __float_as_int(__fadd_rn(sY, 12582912.0f));
 }
 
-// thread -> pixels of a tile, shared by the plan and the staged kernel:
-// column group g = tid & 15 (8 pixels wide), rows (tid >> 4) and (tid >> 4) + 16.
-__device__ __forceinline__ int tile_col(int tid) { return (tid & 15) * kRun; }
-__device__ __forceinline__ int tile_row(int tid, int pass) { return (tid >> 4) + 16 * pass; }
+// thread -> pixels of a tile, shared by the plan and the staged kernel: thread t owns column
+// (t & 127) and the kRun rows starting at kRun * (t >> 7).  A warp is 32 adjacent columns, so its
+// shared-memory gathers touch one contiguous span per source row (no bank conflicts).
+__device__ __forceinline__ int tile_col(int tid) { return tid & (kTileW - 1); }
+__device__ __forceinline__ int tile_row0(int tid) { return (tid >> 7) * kRun; }
+// bit of TileRec::exact_mask covering row k of thread tid's run: (warp, group of 4 rows)
+__device__ __forceinline__ int exact_bit(int tid, int k) { return (tid >> 5) * 4 + (k >> 2); }
 
 struct PlanArgs {
     double M[kMaxPlanCams][9];
@@ -137,17 +140,16 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
     }
     __syncthreads();
 
-    const int x0 = tx * kTileW + tile_col(tid);
+    const int x = tx * kTileW + tile_col(tid);
+    const int y0 = ty * kTileH + tile_row0(tid);
+    const int xb = (x / P.block_w) * P.block_w;
     // ---- phase 1: who wins each pixel -----------------------------------------------------
     unsigned long long my_win = 0ull;
     int my_edge = 0, my_unc = 0;
-    for (int pass = 0; pass < 2; ++pass) {
-        const int y = ty * kTileH + tile_row(tid, pass);
-        if (y >= P.H) continue;
+    if (x < P.W) {
         for (int k = 0; k < kRun; ++k) {
-            const int x = x0 + k;
-            if (x >= P.W) break;
-            const int xb = (x / P.block_w) * P.block_w;
+            const int y = y0 + k;
+            if (y >= P.H) break;
             int cls = 0, i = P.n_cams - 1;
             for (; i >= 0; --i) {
                 int X, Y;
@@ -194,23 +196,19 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
         }
     }
     // ---- phase 2: per layer, source bounding box and validity of the cheap coordinates -----
-    const int warp = tid >> 5;
     for (int l = 0; l < n_layers; ++l) {
         const int c = cams[l];
         int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN, notfull = 0;
-        for (int pass = 0; pass < 2; ++pass) {
-            const int y = ty * kTileH + tile_row(tid, pass);
-            if (y >= P.H) continue;
-            const RunAnchor a = run_anchor(P.M[c], x0 + kRun / 2, y);
-            bool mismatch = false;
+        unsigned mism = 0u;
+        if (x < P.W) {
+            const RunAnchor a = run_anchor(P.M[c], x, y0 + kRun / 2);
             for (int k = 0; k < kRun; ++k) {
-                const int x = x0 + k;
-                if (x >= P.W) break;
-                const int xb = (x / P.block_w) * P.block_w;
-                int X, Y, Xf, Yf;
+                const int y = y0 + k;
+                if (y >= P.H) break;
+                int X, Y, xbits, ybits;
                 coord_exact(P.M[c], xb, x - xb, y, X, Y);
-                run_coord(a, k, Xf, Yf);
-                mismatch |= (X != Xf) | (Y != Yf);
+                run_coord_bits(a, k, xbits, ybits);
+                if (X != xbits + a.bx || Y != ybits + a.by) mism |= 1u << exact_bit(tid, k);
                 if (cover_class(X, Y, P.w[c], P.h[c], 1) == 1) {   // interior only
                     const int sx = X >> kFracBits, sy = Y >> kFracBits;
                     bx0 = min(bx0, sx);
@@ -221,8 +219,8 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
                     notfull = 1;
                 }
             }
-            if (mismatch) atomicOr(&s_exact[l], 1u << (warp * 2 + pass));
         }
+        if (mism) atomicOr(&s_exact[l], mism);
         if (bx0 != INT_MAX) {
             atomicMin(&s_bx0[l], bx0);
             atomicMin(&s_by0[l], by0);

@@ -1,0 +1,241 @@
+// image_io.cpp -- see image_io.hpp.
+#include "image_io.hpp"
+
+#include <algorithm>
+#include <cctype>
+#include <cstring>
+
+#ifdef BS_WITH_NVJPEG
+#include <cuda_runtime.h>
+#include <nvjpeg.h>
+#endif
+
+namespace bsio {
+
+namespace {
+
+void set_err(std::string *err, const std::string &m) {
+  if (err) *err = m;
+}
+
+std::string lower_ext(const std::string &p) {
+  auto d = p.rfind('.');
+  std::string e = d == std::string::npos ? "" : p.substr(d + 1);
+  std::transform(e.begin(), e.end(), e.begin(), [](unsigned char c) { return (char)tolower(c); });
+  return e;
+}
+
+// reads one whitespace/comment-delimited header integer of a PNM file
+bool pnm_int(FILE *f, int &v) {
+  int c = fgetc(f);
+  for (;;) {
+    while (c != EOF && isspace(c)) c = fgetc(f);
+    if (c == '#') {
+      while (c != EOF && c != '\n') c = fgetc(f);
+      continue;
+    }
+    break;
+  }
+  if (c == EOF || !isdigit(c)) return false;
+  long n = 0;
+  while (c != EOF && isdigit(c)) {
+    n = n * 10 + (c - '0');
+    if (n > 1000000) return false;
+    c = fgetc(f);
+  }
+  v = (int)n;   // the single whitespace after the last header field has been consumed
+  return true;
+}
+
+bool read_ppm_frame(FILE *f, Image &out, std::string *err) {
+  int c0 = fgetc(f);
+  while (c0 != EOF && isspace(c0)) c0 = fgetc(f);
+  if (c0 == EOF) {
+    set_err(err, "end of stream");
+    return false;
+  }
+  int c1 = fgetc(f);
+  if (c0 != 'P' || c1 != '6') {
+    set_err(err, "not a binary PPM (P6)");
+    return false;
+  }
+  int w, h, maxv;
+  if (!pnm_int(f, w) || !pnm_int(f, h) || !pnm_int(f, maxv) || maxv != 255 || w < 1 || h < 1) {
+    set_err(err, "bad PPM header");
+    return false;
+  }
+  out.w = w;
+  out.h = h;
+  out.bgr.resize((size_t)w * h * 3);
+  if (fread(out.bgr.data(), 1, out.bgr.size(), f) != out.bgr.size()) {
+    set_err(err, "truncated PPM");
+    return false;
+  }
+  for (size_t i = 0; i + 2 < out.bgr.size(); i += 3) std::swap(out.bgr[i], out.bgr[i + 2]);   // RGB -> BGR
+  return true;
+}
+
+#ifdef BS_WITH_NVJPEG
+bool read_file(const std::string &path, std::vector<unsigned char> &data) {
+  FILE *f = fopen(path.c_str(), "rb");
+  if (!f) return false;
+  fseek(f, 0, SEEK_END);
+  long n = ftell(f);
+  fseek(f, 0, SEEK_SET);
+  data.resize(n > 0 ? (size_t)n : 0);
+  bool ok = n > 0 && fread(data.data(), 1, data.size(), f) == data.size();
+  fclose(f);
+  return ok;
+}
+
+bool read_jpeg(const std::string &path, Image &out, std::string *err) {
+  std::vector<unsigned char> data;
+  if (!read_file(path, data)) {
+    set_err(err, "cannot read " + path);
+    return false;
+  }
+  nvjpegHandle_t h = nullptr;
+  nvjpegJpegState_t st = nullptr;
+  bool ok = false;
+  unsigned char *dbuf = nullptr;
+  do {
+    if (nvjpegCreateSimple(&h) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegCreateSimple failed (no GPU?)"); break; }
+    if (nvjpegJpegStateCreate(h, &st) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegJpegStateCreate failed"); break; }
+    int nc = 0, ws[NVJPEG_MAX_COMPONENT], hs[NVJPEG_MAX_COMPONENT];
+    nvjpegChromaSubsampling_t ss;
+    if (nvjpegGetImageInfo(h, data.data(), data.size(), &nc, &ss, ws, hs) != NVJPEG_STATUS_SUCCESS) { set_err(err, "not a JPEG: " + path); break; }
+    out.w = ws[0];
+    out.h = hs[0];
+    size_t bytes = (size_t)out.w * out.h * 3;
+    if (cudaMalloc(&dbuf, bytes) != cudaSuccess) { set_err(err, "cudaMalloc failed"); break; }
+    nvjpegImage_t img;
+    memset(&img, 0, sizeof img);
+    img.channel[0] = dbuf;
+    img.pitch[0] = (size_t)out.w * 3;
+    if (nvjpegDecode(h, st, data.data(), data.size(), NVJPEG_OUTPUT_BGRI, &img, 0) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegDecode failed: " + path); break; }
+    out.bgr.resize(bytes);
+    if (cudaMemcpy(out.bgr.data(), dbuf, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) { set_err(err, "cudaMemcpy failed"); break; }
+    ok = true;
+  } while (false);
+  if (dbuf) cudaFree(dbuf);
+  if (st) nvjpegJpegStateDestroy(st);
+  if (h) nvjpegDestroy(h);
+  return ok;
+}
+
+bool write_jpeg(const std::string &path, const Image &im, std::string *err) {
+  nvjpegHandle_t h = nullptr;
+  nvjpegEncoderState_t es = nullptr;
+  nvjpegEncoderParams_t ep = nullptr;
+  unsigned char *dbuf = nullptr;
+  bool ok = false;
+  do {
+    if (nvjpegCreateSimple(&h) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegCreateSimple failed (no GPU?)"); break; }
+    if (nvjpegEncoderStateCreate(h, &es, 0) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegEncoderStateCreate failed"); break; }
+    if (nvjpegEncoderParamsCreate(h, &ep, 0) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegEncoderParamsCreate failed"); break; }
+    nvjpegEncoderParamsSetQuality(ep, 95, 0);                       // cv::imwrite's default JPEG quality
+    nvjpegEncoderParamsSetSamplingFactors(ep, NVJPEG_CSS_420, 0);   // and its default 4:2:0 subsampling
+    size_t bytes = im.bgr.size();
+    if (cudaMalloc(&dbuf, bytes) != cudaSuccess) { set_err(err, "cudaMalloc failed"); break; }
+    if (cudaMemcpy(dbuf, im.bgr.data(), bytes, cudaMemcpyHostToDevice) != cudaSuccess) { set_err(err, "cudaMemcpy failed"); break; }
+    nvjpegImage_t img;
+    memset(&img, 0, sizeof img);
+    img.channel[0] = dbuf;
+    img.pitch[0] = im.pitch();
+    if (nvjpegEncodeImage(h, es, ep, &img, NVJPEG_INPUT_BGRI, im.w, im.h, 0) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpegEncodeImage failed"); break; }
+    size_t len = 0;
+    if (nvjpegEncodeRetrieveBitstream(h, es, nullptr, &len, 0) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpeg bitstream size failed"); break; }
+    cudaStreamSynchronize(0);
+    std::vector<unsigned char> bits(len);
+    if (nvjpegEncodeRetrieveBitstream(h, es, bits.data(), &len, 0) != NVJPEG_STATUS_SUCCESS) { set_err(err, "nvjpeg bitstream failed"); break; }
+    cudaStreamSynchronize(0);
+    FILE *f = fopen(path.c_str(), "wb");
+    if (!f) { set_err(err, "cannot write " + path); break; }
+    ok = fwrite(bits.data(), 1, len, f) == len;
+    fclose(f);
+  } while (false);
+  if (dbuf) cudaFree(dbuf);
+  if (ep) nvjpegEncoderParamsDestroy(ep);
+  if (es) nvjpegEncoderStateDestroy(es);
+  if (h) nvjpegDestroy(h);
+  return ok;
+}
+#endif
+
+}  // namespace
+
+bool have_jpeg() {
+#ifdef BS_WITH_NVJPEG
+  return true;
+#else
+  return false;
+#endif
+}
+
+bool read_image(const std::string &path, Image &out, std::string *err) {
+  const std::string e = lower_ext(path);
+  if (e == "jpg" || e == "jpeg") {
+#ifdef BS_WITH_NVJPEG
+    return read_jpeg(path, out, err);
+#else
+    set_err(err, "JPEG support not built in");
+    return false;
+#endif
+  }
+  FILE *f = fopen(path.c_str(), "rb");
+  if (!f) {
+    set_err(err, "cannot open " + path);
+    return false;
+  }
+  bool ok = read_ppm_frame(f, out, err);
+  fclose(f);
+  return ok;
+}
+
+bool write_image(const std::string &path, const Image &img, std::string *err) {
+  const std::string e = lower_ext(path);
+  if (e == "jpg" || e == "jpeg") {
+#ifdef BS_WITH_NVJPEG
+    return write_jpeg(path, img, err);
+#else
+    set_err(err, "JPEG support not built in");
+    return false;
+#endif
+  }
+  FILE *f = fopen(path.c_str(), "wb");
+  if (!f) {
+    set_err(err, "cannot write " + path);
+    return false;
+  }
+  fprintf(f, "P6\n%d %d\n255\n", img.w, img.h);
+  std::vector<uint8_t> row((size_t)img.w * 3);
+  bool ok = true;
+  for (int y = 0; y < img.h && ok; ++y) {
+    const uint8_t *s = img.bgr.data() + (size_t)y * img.pitch();
+    for (int x = 0; x < img.w; ++x) {
+      row[3 * x + 0] = s[3 * x + 2];
+      row[3 * x + 1] = s[3 * x + 1];
+      row[3 * x + 2] = s[3 * x + 0];
+    }
+    ok = fwrite(row.data(), 1, row.size(), f) == row.size();
+  }
+  fclose(f);
+  return ok;
+}
+
+FrameStream::~FrameStream() {
+  if (f_) fclose(f_);
+}
+
+bool FrameStream::open(const std::string &path) {
+  if (f_) fclose(f_);
+  f_ = fopen(path.c_str(), "rb");
+  return f_ != nullptr;
+}
+
+bool FrameStream::read(Image &out) {
+  if (!f_) return false;
+  return read_ppm_frame(f_, out, nullptr);
+}
+
+}  // namespace bsio

@@ -1,0 +1,42 @@
+// image_io.hpp -- frame input/output of the stitch host.
+// The reference reads with cv::imread / cv::VideoCapture and writes with cv::imwrite
+// (/root/reference/tools/stitch/main.cpp:107,114,125,127-147); OpenCV's C++ SDK is not available
+// to this build, so the host reads/writes binary PPM (P6) itself and uses nvJPEG for JPEG.
+// All images are packed BGR, 8 bits per channel, like a continuous CV_8UC3 cv::Mat.
+#ifndef B200_STITCH_HOST_IMAGE_IO_HPP
+#define B200_STITCH_HOST_IMAGE_IO_HPP
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+namespace bsio {
+
+struct Image {
+  int w = 0, h = 0;
+  std::vector<uint8_t> bgr;   // h rows of w*3 bytes
+  bool empty() const { return w == 0 || h == 0; }
+  size_t pitch() const { return (size_t)w * 3; }
+};
+
+// PPM (.ppm/.pnm) and, when built with nvJPEG, JPEG (.jpg/.jpeg).  Returns false on failure.
+bool read_image(const std::string &path, Image &out, std::string *err = nullptr);
+bool write_image(const std::string &path, const Image &img, std::string *err = nullptr);
+
+// A "video": a stream of concatenated binary PPM frames (what
+// `ffmpeg -i in.mp4 -f image2pipe -vcodec ppm out.ppms` produces).  Stands in for cv::VideoCapture.
+class FrameStream {
+ public:
+  ~FrameStream();
+  bool open(const std::string &path);
+  bool isOpened() const { return f_ != nullptr; }
+  bool read(Image &out);   // false at end of stream
+ private:
+  FILE *f_ = nullptr;
+};
+
+bool have_jpeg();
+
+}  // namespace bsio
+#endif

@@ -1,0 +1,245 @@
+// stitch_main.cpp -- drop-in for the reference's `stitch` tool
+// (/root/reference/tools/stitch/main.cpp): same command line, same stitch.conf.xml, same exit
+// codes and messages; the per-frame OpenCV calls (:116-117, :148-151) are replaced by the CUDA
+// engine behind include/b200_stitch.h.
+//
+//   stitch [--s-conf=stitch.conf.xml] [-i] [-v=N]        (reference flags)
+//          [--out=PATH] [--frames=N] [--device=N] [--legacy-border]   (extensions)
+//
+// Differences a user can observe, all forced by what this build can link against:
+//   * images are read as JPEG through nvJPEG or as binary PPM (no libjpeg / OpenCV here);
+//   * a "video" input is a stream of concatenated PPM frames; at end of input the tool exits 0
+//     (the reference loops forever and dies on an OpenCV assertion at EOF, main.cpp:143-155);
+//   * uncovered canvas pixels are 0 (the reference leaves them uninitialised, main.cpp:108,144);
+//   * -i opens no window (no display on a GPU node): displayResult is a headless no-op.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "../../include/b200_stitch.h"
+#include "file_storage.hpp"
+#include "image_io.hpp"
+#include "opts.hpp"
+
+extern command_line_opts opts;
+
+namespace {
+
+// lib/Calibrate/utils.cpp:208-218 shows a window when opts.interactive; there is no display here.
+void displayResult(const std::string &, const bsio::Image &, bool = false) {}
+
+bool read_matrix_seq(const bsfs::Node &n, std::vector<bsfs::Matrix> &out) {
+  for (size_t i = 0; i < n.size() && i < out.size(); ++i)
+    if (!n[i].asMatrix(out[i])) out[i] = bsfs::Matrix();
+  return true;
+}
+
+int fail_bs(const char *what, bs_handle *h) {
+  std::cout << what << ": " << bs_last_error(h) << std::endl;
+  return 6;
+}
+
+}  // namespace
+
+int main(int argc, char *argv[]) {
+  if (!parse_command_line_opts(argc, argv)) {
+    std::cout << "Usage: " << argv[0] << " -c=/path/to/conf.xml";
+    return 1;
+  }
+
+  bsfs::FileStorage fs;
+  fs.open(opts.stitch_config);
+  if (!fs.isOpened()) {
+    std::cout << "Failed to open configuration file " << opts.stitch_config << std::endl;
+    return 2;
+  }
+
+  opts.video = fs["video"].asInt(opts.video ? 1 : 0) != 0;
+  const bsfs::Node &fNames = fs["file_paths"];
+  if (!fNames.isSeq()) {
+    std::cout << "file_paths is not a sequence!" << std::endl;
+    return 4;
+  }
+  opts.file_paths.resize(fNames.size());
+  for (size_t i = 0; i < fNames.size(); ++i) opts.file_paths[i] = fNames[i].asString();
+  if (opts.file_paths.empty()) {
+    std::cout << "Usage: " << argv[0] << " /path/to/img1.jpg /path/to/img2.jpg";
+    return 3;
+  }
+
+  int result_w = 0, result_h = 0;
+  const bsfs::Node &fSize = fs["result_size"];
+  if (fSize.isSeq() && fSize.size() >= 2) {
+    result_w = fSize[0].asInt();
+    result_h = fSize[1].asInt();
+  }
+
+  const size_t n = opts.file_paths.size();
+  std::vector<bsfs::Matrix> H(n), cameraMatrix(n), distCoeffs(n);
+  const bsfs::Node &fH = fs["H"];
+  if (!fH.isSeq()) {
+    std::cout << "H is not a sequence!" << std::endl;
+    return 4;
+  }
+  read_matrix_seq(fH, H);
+  const bsfs::Node &fK = fs["cameraMatrix"];
+  if (!fK.isSeq()) {
+    std::cout << "cameraMatrix is not a sequence!" << std::endl;
+    return 4;
+  }
+  read_matrix_seq(fK, cameraMatrix);
+  const bsfs::Node &fD = fs["distCoeffs"];
+  if (!fD.isSeq()) {
+    std::cout << "distCoeffs is not a sequence!" << std::endl;
+    return 4;
+  }
+  read_matrix_seq(fD, distCoeffs);
+
+  for (size_t i = 0; i < n; ++i)
+    if (H[i].rows != 3 || H[i].cols != 3) {
+      std::cout << "H[" << i << "] is not a 3x3 matrix" << std::endl;
+      return 4;
+    }
+  if (result_w < 1 || result_h < 1) {
+    std::cout << "result_size is missing or empty" << std::endl;
+    return 4;
+  }
+  const unsigned flags = opts.legacy_border ? BS_FLAG_LEGACY_BORDER : 0u;
+
+  if (!opts.video) {
+    bsio::Image result;
+    result.w = result_w;
+    result.h = result_h;
+    result.bgr.assign((size_t)result_w * result_h * 3, 0);
+    for (size_t i = 0; i < n; ++i) {
+      bsio::Image image;
+      std::string err;
+      if (!bsio::read_image(opts.file_paths[i], image, &err)) {
+        std::cout << "Failed to read " << opts.file_paths[i] << ": " << err << std::endl;
+        return 5;
+      }
+      auto start = std::chrono::steady_clock::now();
+      int rc = bs_warp_perspective(image.bgr.data(), image.w, image.h, image.pitch(), result.bgr.data(), result.w,
+                                   result.h, result.pitch(), H[i].data.data(), flags);
+      auto end = std::chrono::steady_clock::now();
+      if (rc != BS_OK) return fail_bs("warpPerspective failed", nullptr);
+      std::cout << std::chrono::duration<double, std::milli>(end - start).count() << std::endl;
+      displayResult("temp", result, true);
+    }
+    displayResult("Final", result, true);
+    std::string out = opts.output.empty() ? (bsio::have_jpeg() ? "final.jpg" : "final.ppm") : opts.output;
+    std::string err;
+    if (!bsio::write_image(out, result, &err)) {
+      std::cout << "Failed to write " << out << ": " << err << std::endl;
+      return 6;
+    }
+    return 0;
+  }
+
+  // ---- video mode ------------------------------------------------------------------------------
+  std::vector<bsio::FrameStream> videos(n);
+  for (size_t i = 0; i < n; ++i) {
+    videos[i].open(opts.file_paths[i]);
+    if (!videos[i].isOpened()) {
+      std::cout << "Failed to open file " << opts.file_paths[i] << "!" << std::endl;
+      return 5;
+    }
+  }
+  // the reference reads and drops the first frame of every stream (main.cpp:136-141)
+  std::vector<bsio::Image> first(n);
+  for (size_t i = 0; i < n; ++i)
+    if (!videos[i].read(first[i])) {
+      std::cout << "Failed to open file " << opts.file_paths[i] << "!" << std::endl;
+      return 5;
+    }
+
+  std::vector<int> sw(n), sh(n);
+  std::vector<double> Hall(9 * n);
+  for (size_t i = 0; i < n; ++i) {
+    sw[i] = first[i].w;
+    sh[i] = first[i].h;
+    memcpy(&Hall[9 * i], H[i].data.data(), 9 * sizeof(double));
+  }
+  bs_handle *h = nullptr;
+  if (bs_create(opts.device, (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags, &h) != BS_OK)
+    return fail_bs("bs_create failed", nullptr);
+  for (size_t i = 0; i < n; ++i) {
+    const bsfs::Matrix &K = cameraMatrix[i], &d = distCoeffs[i];
+    if (K.empty()) continue;   // configs written in image mode carry 0x0 matrices: nothing to undo
+    if (K.rows != 3 || K.cols != 3 ||
+        bs_set_undistort(h, (int)i, K.data.data(), d.empty() ? nullptr : d.data.data(), (int)d.data.size()) != BS_OK) {
+      int rc = fail_bs("bs_set_undistort failed", h);
+      bs_destroy(h);
+      return rc;
+    }
+  }
+
+  const int depth = bs_pipeline_depth(h);
+  std::vector<std::vector<bsio::Image>> frames(depth, std::vector<bsio::Image>(n));
+  std::vector<bsio::Image> results(depth);
+  std::vector<int64_t> tickets(depth, -1);
+  for (auto &r : results) {
+    r.w = result_w;
+    r.h = result_h;
+    r.bgr.assign((size_t)result_w * result_h * 3, 0);
+  }
+  auto emit = [&](int slot, long index) -> bool {
+    if (bs_wait(h, tickets[slot]) != BS_OK) return false;
+    tickets[slot] = -1;
+    displayResult("Final", results[slot]);
+    if (!opts.output.empty()) {
+      char name[4096];
+      snprintf(name, sizeof name, opts.output.c_str(), index);   // e.g. --out=pano_%05ld.ppm
+      std::string err;
+      if (!bsio::write_image(name, results[slot], &err)) std::cout << "Failed to write " << name << ": " << err << std::endl;
+    }
+    return true;
+  };
+
+  long produced = 0, emitted = 0;
+  auto t0 = std::chrono::steady_clock::now();
+  bool ok = true;
+  while (ok && (opts.max_frames < 0 || produced < opts.max_frames)) {
+    const int slot = (int)(produced % depth);
+    if (tickets[slot] >= 0) {
+      if (!emit(slot, emitted)) { ok = false; break; }
+      ++emitted;
+    }
+    bool eof = false;
+    for (size_t i = 0; i < n; ++i) {
+      if (!videos[i].read(frames[slot][i]) || frames[slot][i].w != sw[i] || frames[slot][i].h != sh[i]) {
+        eof = true;
+        break;
+      }
+    }
+    if (eof) break;
+    std::vector<const uint8_t *> ptrs(n);
+    std::vector<size_t> pitches(n);
+    for (size_t i = 0; i < n; ++i) {
+      ptrs[i] = frames[slot][i].bgr.data();
+      pitches[i] = frames[slot][i].pitch();
+    }
+    if (bs_submit(h, ptrs.data(), pitches.data(), results[slot].bgr.data(), results[slot].pitch(), &tickets[slot]) !=
+        BS_OK) {
+      ok = false;
+      break;
+    }
+    ++produced;
+  }
+  while (ok && emitted < produced) {
+    const int slot = (int)(emitted % depth);
+    if (!emit(slot, emitted)) { ok = false; break; }
+    ++emitted;
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  int rc = 0;
+  if (!ok) rc = fail_bs("stitching failed", h);
+  else if (opts.verbosity > 0)
+    std::cout << produced << " frames, " << std::chrono::duration<double, std::milli>(t1 - t0).count() / (produced ? produced : 1)
+              << " ms/frame" << std::endl;
+  bs_destroy(h);
+  return rc;
+}

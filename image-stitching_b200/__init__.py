@@ -14,7 +14,7 @@ import weakref
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200stitch.so")
+LIB_PATH = os.environ.get("B200_STITCH_LIB") or os.path.join(_HERE, "libb200stitch.so")   # env: development override
 
 FLAG_LEGACY_BORDER = 0x1
 FLAG_KEEP_CANVAS = 0x2

@@ -259,24 +259,51 @@ int build_plan(bs_handle *h)
         if (r.type == bs::kTileEmpty) ordered.push_back(r), h->n_empty++;
     BS_CUDA(h, cudaMemcpy(h->d_tiles, ordered.data(), bytes, cudaMemcpyHostToDevice));
 
+    if (getenv("BS_DEBUG_PLAN_SUMMARY")) {
+        long groups = 0, flagged_groups = 0, blocks = 0, flagged_blocks = 0;
+        long per_cam[bs::kMaxCamsPerLaunch] = {0};
+        for (const bs::TileRec &r : ordered) {
+            if (r.type != bs::kTileFast) continue;
+            for (int l = 0; l < r.n_layers; ++l) {
+                for (int w = 0; w < 8; ++w) {
+                    const unsigned g = (r.exact_mask[l] >> (4 * w)) & 15u;
+                    blocks++;
+                    groups += 4;
+                    flagged_groups += __builtin_popcount(g);
+                    if (g) flagged_blocks++, per_cam[r.cam[l]]++;
+                }
+            }
+        }
+        fprintf(stderr, "[plan] blocks %ld flagged %ld (%.2f%%), 32x4 groups %ld flagged %ld (%.2f%%)\n", blocks,
+                flagged_blocks, 100.0 * flagged_blocks / (blocks ? blocks : 1), groups, flagged_groups,
+                100.0 * flagged_groups / (groups ? groups : 1));
+        for (int c = 0; c < h->n_cams; ++c) fprintf(stderr, "[plan]   cam %d flagged blocks %ld\n", c, per_cam[c]);
+        int shown = 0;
+        for (const bs::TileRec &r : ordered)
+            for (int l = 0; l < r.n_layers && shown < 12; ++l)
+                if (r.type == bs::kTileFast && r.exact_mask[l]) {
+                    fprintf(stderr, "[plan]   tile (%d,%d) cam %d mask %08x\n", r.tx, r.ty, r.cam[l], r.exact_mask[l]);
+                    shown++;
+                }
+    }
     if (getenv("BS_DEBUG_PLAN")) {
         for (int c = 0; c < h->n_cams; ++c)
             fprintf(stderr, "[plan] cam %d: %dx%d box %d elems x %d rows\n", c, h->sw[c], h->sh[c], h->box_we[c],
                     h->box_h[c]);
         for (const bs::TileRec &r : ordered) {
-            fprintf(stderr, "[plan] tile (%d,%d) type %d layers %d unc %d full %x:", r.tx, r.ty, r.type, r.n_layers,
-                    r.has_uncovered, r.full_mask);
+            fprintf(stderr, "[plan] tile (%d,%d) type %d layers %d unc %d:", r.tx, r.ty, r.type, r.n_layers,
+                    r.has_uncovered);
             for (int l = 0; l < r.n_layers; ++l)
-                fprintf(stderr, " [cam %d x %d..%d y %d..%d exact %x]", r.cam[l], r.bx0[l], r.bx1[l], r.by0[l],
-                        r.by1[l], r.exact_mask[l]);
+                fprintf(stderr, " [cam %d x %d..%d y %d..%d exact %x all %02x none %02x]", r.cam[l], r.bx0[l], r.bx1[l],
+                        r.by0[l], r.by1[l], r.exact_mask[l], r.all_mask[l], r.none_mask[l]);
             fprintf(stderr, "\n");
         }
     }
-    h->smem_bytes = 2 * h->stage_bytes + 2 * bs::kOutTileBytes + bs::kLutBytes + 64;
+    h->smem_bytes = bs::kStages * h->stage_bytes + bs::kConsumerWarps * bs::kWarpOutBytes + 2 * bs::kLutBytes + bs::kStages * bs::kMetaBytes + 64;   // + 8 KB slack to align the table
     BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     h->smem_bytes));
     int per_sm = 0, sms = 0;
-    BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kThreads,
+    BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kFastThreads,
                                                              h->smem_bytes));
     BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
     if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
@@ -332,7 +359,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         FA.tiles = h->d_tiles;
         FA.n_tiles = h->n_tiles;
         FA.stage_bytes = h->stage_bytes;
-        bs::stitch_fast_kernel<<<h->grid, bs::kThreads, h->smem_bytes, stream>>>(FA);
+        bs::stitch_fast_kernel<<<h->grid, bs::kFastThreads, h->smem_bytes, stream>>>(FA);
         BS_CUDA(h, cudaGetLastError());
         if (dbg_sync) {
             cudaError_t e1 = cudaDeviceSynchronize();

@@ -52,18 +52,22 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
     asm volatile(
         "{\n"
         ".reg .pred P1;\n"
         "LAB_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n"
         "@P1 bra DONE;\n"
         "bra LAB_WAIT;\n"
         "DONE:\n"
         "}" ::"r"(smem_u32(bar)),
-        "r"(parity)
+        "r"(parity), "r"(20000u)   // suspend-time hint (ns): sleep in hardware, woken by the completing arrive
         : "memory");
 }
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tmap, int c0, int c1, uint64_t *bar)
@@ -134,10 +138,9 @@ __device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint32_
     return __byte_perm(bg, vr, 0x7610);
 }
 
-// Store one row's pixel of every lane into the output tile: lanes 4q..4q+3 hold 4 adjacent
+// Store one row's pixel of every lane into the warp's output block: lanes 4q..4q+3 hold 4 adjacent
 // pixels = 12 bytes = 3 words; lane 4q+i (i < 3) builds word i from its own pixel and its right
-// neighbour's and stores it.  `row_addr` = shared address of the tile row, `keep` = this lane's
-// word must not be stored (used by partially covered layers, which fall back to byte stores).
+// neighbour's and stores it.  `row_addr` = shared address of the block row (96 bytes).
 __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, int lane, uint32_t sel)
 {
     const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
@@ -147,69 +150,79 @@ __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, 
                      : "memory");
 }
 
-// Shared address of the first output-tile row of thread tid's run, at the start of its warp's
-// 96-byte (32-pixel) span.
-__device__ __forceinline__ uint32_t out_span(uint32_t out_tile, int tid)
-{
-    return out_tile + (uint32_t)(tile_row0(tid) * (kTileW * 3) + ((tid & (kTileW - 1)) >> 5) * 96);
-}
+// ---- work decomposition ------------------------------------------------------------------------
+// A CTA is 8 consumer warps + 1 producer warp.  A 128x32 tile is 8 blocks of 32 columns x 16 rows;
+// consumer warp w owns block (w & 3, w >> 2) of every tile its CTA processes: lane = column, one
+// vertical run of kRun pixels per lane.  The warps never meet at a CTA barrier: the producer feeds
+// source boxes through a ring of kStages stages guarded by full/empty mbarriers, and every warp
+// composites into, and flushes, its own 16 x 96-byte output block.
+constexpr int kConsumerWarps = kBlocksPerTile;
+constexpr int kFastThreads = 32 * (kConsumerWarps + 1);
+#ifndef BS_MIN_CTAS
+#define BS_MIN_CTAS 3
+#endif
+#ifndef BS_STAGES
+#define BS_STAGES 3
+#endif
+constexpr int kStages = BS_STAGES;
+constexpr int kBlockRowBytes = 96;                     // 32 pixels
+constexpr int kWarpOutBytes = kRun * kBlockRowBytes;   // 1536
 
-// Hot path: the layer covers every pixel of the tile with interior samples, the tile lies inside
-// the canvas and the plan verified the cheap coordinates for this warp's whole 32x16 block.
-// No coverage tests, no fp64 beyond the run's anchor; fully unrolled so k is a constant.
+// Hot path: the layer covers every pixel of the block with interior samples, the tile lies inside
+// the canvas and the plan verified the cheap coordinates for the whole block.  No coverage tests,
+// no fp64 beyond the run's anchor; fully unrolled so k is a constant.
 __device__ __forceinline__ void run_layer_full(const CamDev &cam, int pitch, uint32_t stage_origin, uint32_t lut_base,
-                                               uint32_t out_tile, int x, int y0, int tid)
+                                               uint32_t out_blk, int x, int yc, int lane)
 {
-    const int lane = tid & 31;
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
-    const uint32_t out_col = out_span(out_tile, tid);
-    const RunAnchor a = run_anchor(cam.M, x, y0 + kRun / 2);
+    const RunAnchor a = run_anchor(cam.M, x, yc);
     const uint32_t run_base = stage_origin + (uint32_t)((a.by >> kFracBits) * pitch + (a.bx >> kFracBits) * 3);
+    const int step = a.ny * pitch + a.nx * 3;      // whole texels per canvas row, as a byte offset
 #pragma unroll
     for (int k = 0; k < kRun; ++k) {
+        const int j = k - kRun / 2;
         int xbits, ybits;
-        run_coord_bits(a, k, xbits, ybits);
-        const uint32_t o = run_base + (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
-        const uint32_t lut_off = lut_base + (uint32_t)(((ybits & 31) << 8) + ((xbits & 31) << 3));
+        run_coord_bits(a, (float)j, xbits, ybits);
+        const uint32_t o = run_base + (uint32_t)(j * step) +
+                           (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
+        // the table sits on an 8 KB boundary, so its base can be OR-ed in after masking the index
+        const uint32_t lut_off = lut_base | ((uint32_t)((ybits << 8) + ((xbits << 3) & 0xF8)) & 0x1FF8u);
         const uint32_t px = sample_staged(o, pitch, lut_off);
-        store_row_pixel(px, out_col + (uint32_t)(k * (kTileW * 3)), lane, sel);
+        store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
     }
 }
 
-// General path: partially covered layers, tiles that stick out of the canvas, and warps for which
+// General path: partially covered layers, tiles that stick out of the canvas, and blocks for which
 // the plan found at least one pixel where the cheap coordinates differ (those 32x4 groups use
 // the exact fp64 form).  Same arithmetic per pixel, with coverage tests and byte stores.
 __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &cam, int pitch, uint32_t stage_origin,
-                                               uint32_t lut_base, uint32_t out_tile, uint32_t exact_mask, bool full,
-                                               bool first_layer, int x, int y0, int tid)
+                                               uint32_t lut_base, uint32_t out_blk, uint32_t group_mask, bool full,
+                                               bool first_layer, int x, int y0, int lane)
 {
-    const int lane = tid & 31;
-    const uint32_t out_col = out_span(out_tile, tid);
     const RunAnchor a = run_anchor(cam.M, x, y0 + kRun / 2);
     const int xb = (x / A.F.block_w) * A.F.block_w;
 #pragma unroll 1
     for (int k = 0; k < kRun; ++k) {
         int X, Y;
-        if ((exact_mask >> exact_bit(tid, k)) & 1) {     // warp-uniform
+        if ((group_mask >> (k >> 2)) & 1) {     // warp-uniform
             coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
         } else {
-            // same instruction sequence as run_coord_bits, with k at run time
-            const float kf = (float)(k - kRun / 2);
-            const float sX = __fmaf_rn(kf, __fmaf_rn(kf, a.Ex, a.Dx), a.fx);
-            const float sY = __fmaf_rn(kf, __fmaf_rn(kf, a.Ey, a.Dy), a.fy);
-            X = __float_as_int(__fadd_rn(sX, 12582912.0f)) + a.bx;
-            Y = __float_as_int(__fadd_rn(sY, 12582912.0f)) + a.by;
+            const int j = k - kRun / 2;
+            int xbits, ybits;
+            run_coord_bits(a, (float)j, xbits, ybits);
+            X = xbits + a.bx + 32 * a.nx * j;
+            Y = ybits + a.by + 32 * a.ny * j;
         }
         const int sx = X >> kFracBits, sy = Y >> kFracBits;
         bool in = (x < A.F.W) && (y0 + k < A.F.H);
         if (!full) in = in && sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1;
-        const uint32_t o = in ? stage_origin + (uint32_t)(sy * pitch + sx * 3) : out_tile;   // any valid address
+        const uint32_t o = in ? stage_origin + (uint32_t)(sy * pitch + sx * 3) : out_blk;   // any valid address
         const uint32_t lut_off = lut_base + (uint32_t)((((Y & 31) << 5) | (X & 31)) << 3);
         uint32_t px = sample_staged(o, pitch, lut_off);
         // the first layer also defines the background: pixels it does not cover start at 0
         if (in || first_layer) {
             if (!in) px = 0;
-            const uint32_t p8 = out_col + (uint32_t)(k * (kTileW * 3)) + 3u * (uint32_t)lane;
+            const uint32_t p8 = out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane;
             asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8), "r"(px) : "memory");
             asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 1), "r"(px >> 8) : "memory");
             asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 2), "r"(px >> 16) : "memory");
@@ -217,121 +230,211 @@ __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &
     }
 }
 
-__global__ void __launch_bounds__(kThreads, 3) stitch_fast_kernel(const __grid_constant__ FastArgs A)
+// What the producer publishes with every ring slot: everything a consumer needs to know about the
+// item, so consumers never wait on plan records in global memory.
+//   word 0  tx | ty << 16
+//   word 1  type | last_layer << 8 | all_mask << 16 | skip_mask << 24
+//   word 2  camera
+//   word 3  by0 * pitch + 4 * box_elem0(bx0): stage offset of the box origin texel
+//   word 4  exact_mask
+//   word 5  stage row pitch in bytes
+constexpr int kMetaBytes = 32;
+
+__device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity)
 {
-    extern __shared__ __align__(128) uint8_t smem[];
-    uint8_t *const out_base = smem + 2 * A.stage_bytes;              // two output tiles
-    uint2 *const lut = reinterpret_cast<uint2 *>(out_base + 2 * kOutTileBytes);
-    uint64_t *const bars = reinterpret_cast<uint64_t *>(reinterpret_cast<uint8_t *>(lut) + kLutBytes);
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "LAB_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n"
+        "@P1 bra DONE;\n"
+        "bra LAB_WAIT;\n"
+        "DONE:\n"
+        "}" ::"r"(bar),
+        "r"(parity), "r"(20000u)   // suspend-time hint (ns): sleep in hardware, woken by the completing arrive
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_addr(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr)
+{
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+// Rows x 96 bytes of one block, with bounds checks: zero fill (src == 0) or copy from shared.
+__device__ __noinline__ void store_block_checked(const FrameArgs &F, uint32_t src, int tx0, int ty0, int lane)
+{
+    const int wbytes = min(32, F.W - tx0) * 3;
+    for (int c = lane; c < kRun * 6; c += 32) {
+        const int row = c / 6, cb = (c % 6) * 16;
+        if (ty0 + row >= F.H || cb >= wbytes) continue;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (src) v = lds128(src + (uint32_t)(row * kBlockRowBytes + cb));
+        uint8_t *p = F.canvas + (long long)(ty0 + row) * F.cpitch + (long long)tx0 * 3 + cb;
+        if (cb + 16 <= wbytes) {
+            *reinterpret_cast<uint4 *>(p) = v;
+        } else {
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            for (int j = 0; j < wbytes - cb; ++j) p[j] = (uint8_t)(w[j >> 2] >> (8 * (j & 3)));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(const __grid_constant__ FastArgs A)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    // layout: [pad to an 8 KB boundary][weight table 8 KB][kStages stages][8 output blocks][meta][barriers]
+    const uint32_t raw_base = smem_u32(smem_raw);
+    const uint32_t lut_base = (raw_base + 8191u) & ~8191u;
+    const uint32_t stage0 = lut_base + kLutBytes;                                // 8 KB aligned
+    const uint32_t out0 = stage0 + (uint32_t)(kStages * A.stage_bytes);          // 8 private output blocks
+    const uint32_t meta0 = out0 + kConsumerWarps * kWarpOutBytes;
+    const uint32_t full0 = meta0 + kStages * kMetaBytes;
+    const uint32_t empty0 = full0 + kStages * 8;
+    uint8_t *const gen0 = smem_raw + (lut_base - raw_base);                      // generic pointer to the table
 
     const int tid = threadIdx.x;
-    for (int i = tid; i < 1024; i += kThreads) lut[i] = lut_entry(i);
+    const int warp = tid >> 5, lane = tid & 31;
+    {
+        uint2 *lut = reinterpret_cast<uint2 *>(gen0);
+        for (int i = tid; i < 1024; i += kFastThreads) lut[i] = lut_entry(i);
+    }
     if (tid == 0) {
-        mbar_init(&bars[0], 1);
-        mbar_init(&bars[1], 1);
+        for (int s = 0; s < kStages; ++s) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(1));
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty0 + 8 * s), "r"(kConsumerWarps));
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    const uint32_t lut_base = smem_u32(lut);
 
-    // ---- prefetch cursor (thread 0 only): walks the (tile, layer) items of this CTA ------------
-    int pf_k = blockIdx.x, pf_layer = 0;     // next item to issue
-    uint32_t n_issued = 0;
-    auto issue_next = [&]() {                // thread 0: issue the TMA of the next FAST item, if any
-        while (pf_k < A.n_tiles) {
-            const TileRec *r = &A.tiles[pf_k];
-            const bool fast = (r->type == kTileFast) && !(A.F.keep_canvas && r->has_uncovered);
-            if (fast && pf_layer < r->n_layers) {
-                const int c = r->cam[pf_layer];
-                const int s = n_issued & 1;
-                const uint32_t bytes = (uint32_t)(A.box_we[c] * 4 * A.box_h[c]);
-                mbar_expect_tx(&bars[s], bytes);
-                tma_load_2d(smem + s * A.stage_bytes, &A.tmap[c], box_elem0((int)r->bx0[pf_layer]),
-                            (int)r->by0[pf_layer], &bars[s]);
-                ++n_issued;
-                ++pf_layer;
-                return;
-            }
-            pf_k += gridDim.x;
-            pf_layer = 0;
-        }
-    };
-    if (tid == 0) {
-        issue_next();
-        issue_next();
-    }
-
-    uint32_t n_consumed = 0;
-    int out_sel = 0;
-    for (int k = blockIdx.x; k < A.n_tiles; k += gridDim.x) {
-        const TileRec *const rec = &A.tiles[k];
-        const int tx0 = rec->tx * kTileW, ty0 = rec->ty * kTileH;
-        const int n_layers = rec->n_layers;
-        const int rec_type = rec->type;
-        const bool fast = (rec_type == kTileFast) && !(A.F.keep_canvas && rec->has_uncovered);
-        // tiles that stick out of the canvas: their outside pixels must not be sampled
-        const bool edge_tile = (tx0 + kTileW > A.F.W) || (ty0 + kTileH > A.F.H);
-        if (!fast) {
-            if (rec_type == kTileEmpty) {
-                if (!A.F.keep_canvas) {
-                    // zero fill: rows of the tile, 16-byte chunks where aligned
-                    const int wbytes = min(kTileW, A.F.W - tx0) * 3;
-                    for (int q = tid; q < kTileH * 24; q += kThreads) {
-                        const int row = q / 24, cb = (q % 24) * 16;
-                        if (ty0 + row >= A.F.H || cb >= wbytes) continue;
-                        uint8_t *p = A.F.canvas + (long long)(ty0 + row) * A.F.cpitch + (long long)tx0 * 3 + cb;
-                        if (cb + 16 <= wbytes) *reinterpret_cast<uint4 *>(p) = make_uint4(0, 0, 0, 0);
-                        else
-                            for (int j = 0; j < wbytes - cb; ++j) p[j] = 0;
+    if (warp == kConsumerWarps) {
+        // ===== producer: one lane walks the tiles of this CTA and keeps the ring full ===============
+        // Every tile becomes one ring item per layer (FAST) or a single descriptor-only item.
+        if (lane == 0) {
+            uint32_t slot = 0, phase = 1;    // a fresh mbarrier passes a wait on parity 1
+            for (int k = blockIdx.x; k < A.n_tiles; k += gridDim.x) {
+                const uint4 *rp = reinterpret_cast<const uint4 *>(&A.tiles[k]);
+                TileRec r;
+                {
+                    uint4 *dst = reinterpret_cast<uint4 *>(&r);
+#pragma unroll
+                    for (int q = 0; q < (int)(sizeof(TileRec) / 16); ++q) dst[q] = __ldg(rp + q);
+                }
+                const bool fast = (r.type == kTileFast) && !(A.F.keep_canvas && r.has_uncovered);
+                const int n_items = fast ? r.n_layers : 1;
+                uint32_t higher_all = 0;     // blocks fully written by a later (higher) layer
+                uint32_t skip[kMaxLayers];
+                if (fast)
+                    for (int l = n_items - 1; l >= 0; --l) {
+                        skip[l] = (uint32_t)r.none_mask[l] | higher_all;
+                        higher_all |= r.all_mask[l];
+                    }
+                for (int l = 0; l < n_items; ++l) {
+                    mbar_wait_addr(empty0 + 8 * slot, phase);   // all 8 warps released the slot
+                    uint32_t kind, cam = 0, origin_off = 0, exact_mask = 0, pitch = 0;
+                    if (fast) {
+                        cam = r.cam[l];
+                        pitch = (uint32_t)(A.box_we[cam] * 4);
+                        kind = (uint32_t)kTileFast | ((l == n_items - 1) ? 1u << 8 : 0u) | ((uint32_t)r.all_mask[l] << 16) |
+                               (skip[l] << 24);
+                        origin_off = (uint32_t)((int)r.by0[l] * (int)pitch + 4 * box_elem0((int)r.bx0[l]));
+                        exact_mask = r.exact_mask[l];
+                    } else {
+                        kind = (uint32_t)(r.type == kTileFast ? kTileExact : r.type) | (1u << 8);
+                    }
+                    const uint32_t ma = meta0 + kMetaBytes * slot;
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(ma),
+                                 "r"((uint32_t)r.tx | ((uint32_t)r.ty << 16)), "r"(kind), "r"(cam), "r"(origin_off)
+                                 : "memory");
+                    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(ma + 16), "r"(exact_mask), "r"(pitch) : "memory");
+                    if (fast) {
+                        // arrive has release semantics: the meta words are visible to whoever sees the phase flip
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full0 + 8 * slot),
+                                     "r"((uint32_t)(A.box_we[cam] * 4 * A.box_h[cam]))
+                                     : "memory");
+                        asm volatile(
+                            "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                                stage0 + slot * (uint32_t)A.stage_bytes),
+                            "l"(&A.tmap[cam]), "r"(box_elem0((int)r.bx0[l])), "r"((int)r.by0[l]), "r"(full0 + 8 * slot)
+                            : "memory");
+                    } else {
+                        mbar_arrive_addr(full0 + 8 * slot);
+                    }
+                    if (++slot == kStages) {
+                        slot = 0;
+                        phase ^= 1u;
                     }
                 }
-            } else {
-                // exact tile: thread t takes the 4-pixel group (t & 31) of rows (t >> 5) + 8 j
-                for (int j = 0; j < kTileH / 8; ++j) exact_quad(A.F, tx0 + (tid & 31) * 4, ty0 + (tid >> 5) + 8 * j);
             }
-            continue;
         }
+        return;
+    }
 
-        const uint32_t outt = smem_u32(out_base + out_sel * kOutTileBytes);
-        const int x = tx0 + tile_col(tid);
-        const int y0 = ty0 + tile_row0(tid);
-        for (int l = 0; l < n_layers; ++l) {
-            const int c = rec->cam[l];
-            const CamDev &cam = A.F.cam[c];
-            const int s = n_consumed & 1;
-            const int pitch = A.box_we[c] * 4;
-            const bool full = ((rec->full_mask >> l) & 1) && !edge_tile;
-            const uint32_t exact_mask = rec->exact_mask[l];
-            // shared address texel (0, 0) of this camera would have, were the whole frame staged
-            const uint32_t stage_origin = smem_u32(smem + s * A.stage_bytes) -
-                                          (uint32_t)((int)rec->by0[l] * pitch + 4 * box_elem0((int)rec->bx0[l]));
-            mbar_wait(&bars[s], (n_consumed >> 1) & 1);
-            const uint32_t warp_mask = (exact_mask >> ((tid >> 5) * 4)) & 15u;    // this warp's 4 row groups
-            if (full && warp_mask == 0u) run_layer_full(cam, pitch, stage_origin, lut_base, outt, x, y0, tid);
-            else run_layer_general(A, cam, pitch, stage_origin, lut_base, outt, exact_mask, full, l == 0, x, y0, tid);
-            ++n_consumed;
-            __syncthreads();                 // stage s fully read; this layer's pixels are in the tile
-            if (tid == 0) issue_next();      // refill stage s while the next item computes
-        }
-        // ---- flush the tile: 32 rows x 384 bytes as 16-byte vector stores -----------------------
-        {
-            const uint8_t *const ot = out_base + out_sel * kOutTileBytes;
-            const int wbytes = min(kTileW, A.F.W - tx0) * 3;
+    // ===== consumers ====================================================================================
+    const uint32_t out_blk = out0 + (uint32_t)(warp * kWarpOutBytes);
+    const int bx = (warp & 3) * 32, by = (warp >> 2) * kRun;      // block origin inside a tile
+    uint32_t slot = 0, phase = 0;
+    for (int k = blockIdx.x; k < A.n_tiles; k += gridDim.x) {
+        bool wrote = false, last;
+        do {
+            mbar_wait_addr(full0 + 8 * slot, phase);
+            const uint4 m0 = lds128(meta0 + kMetaBytes * slot);
+            const int tx0 = (int)(m0.x & 0xFFFFu) * kTileW + bx, ty0 = (int)(m0.x >> 16) * kTileH + by;
+            const int type = (int)(m0.y & 0xFFu);
+            last = (m0.y >> 8) & 1u;
+            if (type == kTileFast) {
+                if (!((m0.y >> (24 + warp)) & 1u)) {          // this layer writes into this block
+                    const uint2 m1 = lds64(meta0 + kMetaBytes * slot + 16);
+                    const CamDev &cam = A.F.cam[m0.z];
+                    const int pitch = (int)m1.y;
+                    const bool full = (m0.y >> (16 + warp)) & 1u;
+                    const uint32_t group_mask = (m1.x >> (warp * 4)) & 15u;   // this block's 4 row groups
+                    // shared address texel (0, 0) of this camera would have, were the whole frame staged
+                    const uint32_t stage_origin = stage0 + slot * (uint32_t)A.stage_bytes - m0.w;
+                    if (full && group_mask == 0u)
+                        run_layer_full(cam, pitch, stage_origin, lut_base, out_blk, tx0 + lane, ty0 + kRun / 2, lane);
+                    else
+                        run_layer_general(A, cam, pitch, stage_origin, lut_base, out_blk, group_mask, full, !wrote,
+                                          tx0 + lane, ty0, lane);
+                    wrote = true;
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive_addr(empty0 + 8 * slot);    // this warp is done with the slot
+                if (last) {
+                    if (!wrote) {
+                        if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);   // nobody wrote here
+                    } else if (tx0 + 32 <= A.F.W && ty0 + kRun <= A.F.H) {
+                        // flush: lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
+                        const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
+                        uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch +
+                                            (long long)tx0 * 3 + (lane & 1) * 16;
 #pragma unroll
-            for (int q = tid; q < kTileH * 24; q += kThreads) {
-                const int row = q / 24, cb = (q % 24) * 16;
-                if (ty0 + row >= A.F.H || cb >= wbytes) continue;
-                const uint4 v = *reinterpret_cast<const uint4 *>(ot + row * (kTileW * 3) + cb);
-                uint8_t *p = A.F.canvas + (long long)(ty0 + row) * A.F.cpitch + (long long)tx0 * 3 + cb;
-                if (cb + 16 <= wbytes) {
-                    *reinterpret_cast<uint4 *>(p) = v;
+                        for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4 *>(gp + 32 * j) = lds128(so + 32u * j);
+                    } else {
+                        store_block_checked(A.F, out_blk, tx0, ty0, lane);
+                    }
+                    __syncwarp();   // the block is free again
+                }
+            } else {
+                __syncwarp();
+                if (lane == 0) mbar_arrive_addr(empty0 + 8 * slot);
+                if (type == kTileEmpty) {
+                    if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);
                 } else {
-                    const uint8_t *sv = ot + row * (kTileW * 3) + cb;
-                    for (int j = 0; j < wbytes - cb; ++j) p[j] = sv[j];
+                    // exact block: lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j
+                    for (int j = 0; j < kRun / 4; ++j) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
                 }
             }
-        }
-        out_sel ^= 1;
+            if (++slot == kStages) {
+                slot = 0;
+                phase ^= 1u;
+            }
+        } while (!last);
     }
 }
 

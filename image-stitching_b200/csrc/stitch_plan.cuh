@@ -16,40 +16,59 @@
 namespace bs {
 
 constexpr int kTileW = 128;
-constexpr int kTileH = 32;
-constexpr int kThreads = 256;
+constexpr int kBlocksPerTile = 8;   // 32x16 blocks per tile = consumer warps per CTA (4: one row of blocks)
+constexpr int kThreads = 32 * kBlocksPerTile;
 constexpr int kRun = 16;           // vertical run: consecutive rows per thread
+constexpr int kTileH = kRun * (kBlocksPerTile / 4);
 constexpr int kMaxLayers = 4;      // cameras that may share one FAST tile
 constexpr int kMaxPlanCams = 64;
 
 enum TileType : uint8_t { kTileEmpty = 0, kTileFast = 1, kTileExact = 2 };
 
-struct TileRec {                   // 64 bytes
+struct TileRec {                   // 80 bytes, read by the producer as five 16-byte loads
     uint16_t tx, ty;               // tile coordinates
     uint8_t type;                  // TileType
     uint8_t n_layers;
     uint8_t has_uncovered;         // some in-canvas pixel of the tile is written by no layer
-    uint8_t full_mask;             // bit l: layer l covers every in-canvas pixel of the tile
+    uint8_t reserved;
     uint8_t cam[kMaxLayers];       // ascending camera index = compositing order
+    // per layer, bit w = 32x16 block w of the tile (block w belongs to warp w of the kernels):
+    uint8_t all_mask[kMaxLayers];  //   the block lies inside the canvas and the layer writes every pixel of it
+    uint8_t none_mask[kMaxLayers]; //   the layer writes no pixel of the block
     int16_t bx0[kMaxLayers], by0[kMaxLayers], bx1[kMaxLayers], by1[kMaxLayers];  // texel bbox incl. taps
-    uint32_t exact_mask[kMaxLayers];   // bit (warp*4 + row group): those 32x4 pixels must use exact coords
-    uint32_t pad;
+    uint32_t exact_mask[kMaxLayers];   // bit (w*4 + row group): those 32x4 pixels must use exact coords
+    uint32_t pad[3];
 };
-static_assert(sizeof(TileRec) == 64, "TileRec layout");
+static_assert(sizeof(TileRec) == 80, "TileRec layout");
 
 // ---- cheap coordinates for a vertical run of kRun pixels (one canvas column) -----------------
-// Along a column the source coordinate is fX(yc + k) = fXc + k (32 M1 - M7 fXc) / (Wc + k M7).
-// The run is anchored at its 9th pixel in fp64; the increment is expanded to second order in k
-// and evaluated in fp32:  sX(k) = fx + k (Dx + k Ex).  The result is only used where the plan has
-// checked, pixel by pixel, that it equals coord_exact(); every operation is an explicit
-// intrinsic so the plan kernel and the frame kernel execute the same instruction sequence.
+// Along a column the source coordinate is fX(yc + j) = fXc + j (32 M1 - M7 fXc) / (Wc + j M7),
+// j = k - kRun/2.  The run is anchored at its 9th pixel in fp64; the increment is expanded to
+// second order in j.  Its whole-texel part, 32 n per step with n = round(dX / 32), is exact integer
+// arithmetic and goes straight into the address; only the small remainder is evaluated in fp32:
+//     sX(j) = fx + j (Dx + j Ex),   X(j) = rint(sX(j)) + base_x + 32 n_x j.
+// The result is only used where the plan has checked, pixel by pixel, that it equals
+// coord_exact(); every floating-point operation is an explicit intrinsic (or PTX) so the plan
+// kernel and the frame kernel execute the same instruction sequence.
 struct RunAnchor {
     int bx, by;        // integer bases (multiples of 32) minus the float-magic bias
+    int nx, ny;        // whole source texels advanced per canvas row
     float fx, fy;      // fXc - base, in [-0.5, 32.5)
     float Dx, Ex, Dy, Ey;
 };
 
 constexpr int kMagicBias = 0x4B400000;   // bits of 12582912.0f = 1.5 * 2^23 (a multiple of 32)
+
+// 1/w to a few ulp: hardware seed (about 20 bits) and two Newton steps, no IEEE special cases.
+// A bad value (w = 0, denormal, ...) only makes the plan reject the run.
+__device__ __forceinline__ double fast_rcp(double w)
+{
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(w));
+    r = fma(r, fma(-w, r, 1.0), r);
+    r = fma(r, fma(-w, r, 1.0), r);
+    return r;
+}
 
 __device__ __forceinline__ RunAnchor run_anchor(const double *__restrict__ M, int x, int yc)
 {
@@ -57,33 +76,35 @@ __device__ __forceinline__ RunAnchor run_anchor(const double *__restrict__ M, in
     const double Xn = fma(M[1], dy, fma(M[0], dx, M[2]));
     const double Yn = fma(M[4], dy, fma(M[3], dx, M[5]));
     const double Wn = fma(M[7], dy, fma(M[6], dx, M[8]));
-    const double inv = 1.0 / Wn;
-    const double fX = fmin(fmax(Xn * inv * 32.0, -1.0e9), 1.0e9);
-    const double fY = fmin(fmax(Yn * inv * 32.0, -1.0e9), 1.0e9);
-    const double eps = M[7] * inv;
-    const double dX = fma(-M[7], fX, 32.0 * M[1]) * inv;   // d fX / dk at k = 0
+    const double inv = fast_rcp(Wn);
+    const double inv32 = inv * 32.0;
+    const double fX = Xn * inv32, fY = Yn * inv32;
+    const double dX = fma(-M[7], fX, 32.0 * M[1]) * inv;   // d fX / dj at j = 0
     const double dY = fma(-M[7], fY, 32.0 * M[4]) * inv;
-    const int ix = (int)rint(fX) & ~31, iy = (int)rint(fY) & ~31;
+    const float e = (float)(-M[7] * inv);
+    const float dXf = (float)dX, dYf = (float)dY;
     RunAnchor a;
+    a.nx = __float2int_rn(dXf * 0.03125f);
+    a.ny = __float2int_rn(dYf * 0.03125f);
+    const int ix = __double2int_rn(fX) & ~31, iy = __double2int_rn(fY) & ~31;
     a.bx = ix - kMagicBias;
     a.by = iy - kMagicBias;
     a.fx = (float)(fX - (double)ix);
     a.fy = (float)(fY - (double)iy);
-    a.Dx = (float)dX;
-    a.Ex = (float)(-dX * eps);
-    a.Dy = (float)dY;
-    a.Ey = (float)(-dY * eps);
+    a.Dx = (float)(dX - (double)(32 * a.nx));
+    a.Dy = (float)(dY - (double)(32 * a.ny));
+    a.Ex = __fmul_rn(dXf, e);
+    a.Ey = __fmul_rn(dYf, e);
     return a;
 }
 
 // k in [0, kRun): pixel row yc - kRun/2 + k.  Returns the raw bits of (s + 1.5*2^23): their low
-// bits are rint(s) (round half to even, done by the fp32 adder), so with the anchor's bases
-//   X = bits + a.bx,   X & 31 = bits & 31,   X >> 5 = (bits >> 5) + (a.bx >> 5).
-__device__ __forceinline__ void run_coord_bits(const RunAnchor &a, int k, int &xbits, int &ybits)
+// bits are rint(s) (round half to even, done by the fp32 adder), so with j = k - kRun/2
+//   X = bits + a.bx + 32 a.nx j,   X & 31 = bits & 31,   X >> 5 = (bits >> 5) + (a.bx >> 5) + a.nx j.
+__device__ __forceinline__ void run_coord_bits(const RunAnchor &a, float jf, int &xbits, int &ybits)
 {
-    const float kf = (float)(k - kRun / 2);
-    const float sX = __fmaf_rn(kf, __fmaf_rn(kf, a.Ex, a.Dx), a.fx);
-    const float sY = __fmaf_rn(kf, __fmaf_rn(kf, a.Ey, a.Dy), a.fy);
+    const float sX = __fmaf_rn(jf, __fmaf_rn(jf, a.Ex, a.Dx), a.fx);
+    const float sY = __fmaf_rn(jf, __fmaf_rn(jf, a.Ey, a.Dy), a.fy);
     xbits = __float_as_int(__fadd_rn(sX, 12582912.0f));
     ybits = __float_as_int(__fadd_rn(sY, 12582912.0f));
 }
@@ -95,6 +116,7 @@ __device__ __forceinline__ int tile_col(int tid) { return tid & (kTileW - 1); }
 __device__ __forceinline__ int tile_row0(int tid) { return (tid >> 7) * kRun; }
 // bit of TileRec::exact_mask covering row k of thread tid's run: (warp, group of 4 rows)
 __device__ __forceinline__ int exact_bit(int tid, int k) { return (tid >> 5) * 4 + (k >> 2); }
+// (warp w of the plan kernel covers the same 32x16 block as consumer warp w of the frame kernel)
 
 struct PlanArgs {
     double M[kMaxPlanCams][9];
@@ -122,7 +144,7 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
     __shared__ unsigned long long s_win;       // cameras that win at least one pixel
     __shared__ int s_edge_win, s_uncovered;
     __shared__ int s_bx0[kMaxLayers], s_by0[kMaxLayers], s_bx1[kMaxLayers], s_by1[kMaxLayers];
-    __shared__ int s_notfull[kMaxLayers];
+    __shared__ unsigned s_all[kMaxLayers], s_none[kMaxLayers];
     __shared__ unsigned s_exact[kMaxLayers];
 
     const int tid = threadIdx.x;
@@ -135,7 +157,8 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
     if (tid < kMaxLayers) {
         s_bx0[tid] = s_by0[tid] = INT_MAX;
         s_bx1[tid] = s_by1[tid] = INT_MIN;
-        s_notfull[tid] = 0;
+        s_all[tid] = 0u;
+        s_none[tid] = 0u;
         s_exact[tid] = 0u;
     }
     __syncthreads();
@@ -198,7 +221,8 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
     // ---- phase 2: per layer, source bounding box and validity of the cheap coordinates -----
     for (int l = 0; l < n_layers; ++l) {
         const int c = cams[l];
-        int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN, notfull = 0;
+        int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN;
+        bool all_in = (x < P.W) && (y0 + kRun <= P.H), any_in = false;
         unsigned mism = 0u;
         if (x < P.W) {
             const RunAnchor a = run_anchor(P.M[c], x, y0 + kRun / 2);
@@ -207,16 +231,19 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
                 if (y >= P.H) break;
                 int X, Y, xbits, ybits;
                 coord_exact(P.M[c], xb, x - xb, y, X, Y);
-                run_coord_bits(a, k, xbits, ybits);
-                if (X != xbits + a.bx || Y != ybits + a.by) mism |= 1u << exact_bit(tid, k);
+                const int j = k - kRun / 2;
+                run_coord_bits(a, (float)j, xbits, ybits);
+                if (X != xbits + a.bx + 32 * a.nx * j || Y != ybits + a.by + 32 * a.ny * j)
+                    mism |= 1u << exact_bit(tid, k);
                 if (cover_class(X, Y, P.w[c], P.h[c], 1) == 1) {   // interior only
                     const int sx = X >> kFracBits, sy = Y >> kFracBits;
                     bx0 = min(bx0, sx);
                     by0 = min(by0, sy);
                     bx1 = max(bx1, sx + 1);
                     by1 = max(by1, sy + 1);
+                    any_in = true;
                 } else {
-                    notfull = 1;
+                    all_in = false;
                 }
             }
         }
@@ -227,7 +254,12 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
             atomicMax(&s_bx1[l], bx1);
             atomicMax(&s_by1[l], by1);
         }
-        if (notfull) atomicOr(&s_notfull[l], 1);
+        // block-level coverage (a warp is exactly one 32x16 block)
+        const bool blk_all = __all_sync(0xffffffffu, all_in), blk_any = __any_sync(0xffffffffu, any_in);
+        if ((tid & 31) == 0) {
+            if (blk_all) atomicOr(&s_all[l], 1u << (tid >> 5));
+            if (!blk_any) atomicOr(&s_none[l], 1u << (tid >> 5));
+        }
     }
     __syncthreads();
     if (tid == 0) {
@@ -240,7 +272,8 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
             rec.bx1[l] = (int16_t)s_bx1[l];
             rec.by1[l] = (int16_t)s_by1[l];
             rec.exact_mask[l] = s_exact[l];
-            if (!s_notfull[l]) rec.full_mask |= (uint8_t)(1u << l);
+            rec.all_mask[l] = (uint8_t)s_all[l];
+            rec.none_mask[l] = (uint8_t)s_none[l];
         }
         *dst = rec;
     }

@@ -53,6 +53,7 @@ struct bs_handle {
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
     bs::TileRec *d_tiles = nullptr;      // plan, ordered: exact tiles, fast tiles, empty tiles
+    unsigned *d_sched = nullptr;         // tile scheduler counters of the frame kernel
     int n_tiles = 0, tiles_x = 0, tiles_y = 0;
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
@@ -253,11 +254,16 @@ int build_plan(bs_handle *h)
     h->n_fast = h->n_exact = h->n_empty = 0;
     for (const bs::TileRec &r : recs)
         if (r.type == bs::kTileExact) ordered.push_back(r), h->n_exact++;
-    for (const bs::TileRec &r : recs)
-        if (r.type == bs::kTileFast) ordered.push_back(r), h->n_fast++;
+    for (int layers = bs::kMaxLayers; layers >= 1; --layers)   // heaviest tiles first
+        for (const bs::TileRec &r : recs)
+            if (r.type == bs::kTileFast && r.n_layers == layers) ordered.push_back(r), h->n_fast++;
     for (const bs::TileRec &r : recs)
         if (r.type == bs::kTileEmpty) ordered.push_back(r), h->n_empty++;
     BS_CUDA(h, cudaMemcpy(h->d_tiles, ordered.data(), bytes, cudaMemcpyHostToDevice));
+    BS_CUDA(h, cudaMalloc(&h->d_sched, 2 * sizeof(unsigned)));
+    BS_CUDA(h, cudaMemset(h->d_sched, 0, 2 * sizeof(unsigned)));   // [0] is set to the grid size below
+    h->device_bytes += 8;
+    h->scratch_bytes += 8;
 
     if (getenv("BS_DEBUG_PLAN_SUMMARY")) {
         long groups = 0, flagged_groups = 0, blocks = 0, flagged_blocks = 0;
@@ -309,6 +315,10 @@ int build_plan(bs_handle *h)
     if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
     h->grid = std::min(h->n_tiles, per_sm * sms);
     if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, std::min(h->n_tiles, atoi(g)));
+    {   // the first tile of every CTA is static, so the dynamic counter starts at the grid size
+        const unsigned first_dynamic = (unsigned)h->grid;
+        BS_CUDA(h, cudaMemcpy(h->d_sched, &first_dynamic, sizeof first_dynamic, cudaMemcpyHostToDevice));
+    }
     h->fast_ok = true;
     return BS_OK;
 }
@@ -359,7 +369,23 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         FA.tiles = h->d_tiles;
         FA.n_tiles = h->n_tiles;
         FA.stage_bytes = h->stage_bytes;
-        bs::stitch_fast_kernel<<<h->grid, bs::kFastThreads, h->smem_bytes, stream>>>(FA);
+        FA.sched = h->d_sched;
+        {
+            // programmatic dependent launch: the prologue and first tile of this frame may overlap the
+            // tail of the previous frame's kernel on the same stream (see stitch_fast.cuh)
+            cudaLaunchConfig_t cfg;
+            memset(&cfg, 0, sizeof cfg);
+            cfg.gridDim = dim3(h->grid);
+            cfg.blockDim = dim3(bs::kFastThreads);
+            cfg.dynamicSmemBytes = (size_t)h->smem_bytes;
+            cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast_kernel, FA));
+        }
         BS_CUDA(h, cudaGetLastError());
         if (dbg_sync) {
             cudaError_t e1 = cudaDeviceSynchronize();
@@ -509,6 +535,7 @@ int bs_destroy(bs_handle *h)
         if (s.ev_done) cudaEventDestroy(s.ev_done);
     }
     cudaFree(h->d_tiles);
+    cudaFree(h->d_sched);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);

@@ -31,6 +31,7 @@ struct FastArgs {
     int box_we[kMaxCamsPerLaunch];         // TMA box of camera i: width in 4-byte elements, rows
     int box_h[kMaxCamsPerLaunch];
     int stage_bytes;                       // shared memory per stage (multiple of 128)
+    unsigned *sched;                       // [0] next tile to hand out, [1] CTAs that ran dry (self-resetting)
 };
 
 // First 4-byte element of the staged box for a bounding box whose first texel column is bx0.
@@ -111,31 +112,55 @@ __device__ __forceinline__ uint2 lut_entry(int idx)
     return e;
 }
 
-// One interior pixel from a staged box.  `o` = shared byte address of texel (sx, sy) (any
-// alignment), `pitch` = stage row pitch in bytes, `lut_off` = shared address of the weight-table
-// entry.  Returns B | G<<8 | R<<16.
-__device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint32_t lut_off)
+// The twelve tap bytes of one interior pixel as they come out of shared memory, plus its weights.
+struct Taps {
+    uint32_t w0, w1, w2;   // three aligned words of source row sy starting at the word that holds texel sx
+    uint32_t v0, v1, v2;   // same for row sy + 1
+    uint2 wt;              // weight-table entry
+    uint32_t sh;           // 8 * (byte offset of texel sx in w0); the funnel shifter uses the low 5 bits
+};
+
+// `o` = shared byte address of texel (sx, sy) (any alignment), `pitch` = stage row pitch in bytes,
+// `lut_off` = shared address of the weight-table entry.
+__device__ __forceinline__ Taps fetch_taps(uint32_t o, int pitch, uint32_t lut_off)
 {
+    Taps t;
     const uint32_t wa = o & ~3u;
-    const uint32_t sh = o << 3;          // the funnel shift uses the low 5 bits: 8 * (o & 3)
-    const uint32_t w0 = lds32(wa), w1 = lds32(wa + 4), w2 = lds32(wa + 8);
-    const uint32_t v0 = lds32(wa + pitch), v1 = lds32(wa + pitch + 4), v2 = lds32(wa + pitch + 8);
-    const uint2 wt = lds64(lut_off);
+    t.sh = o << 3;
+    t.w0 = lds32(wa);
+    t.w1 = lds32(wa + 4);
+    t.w2 = lds32(wa + 8);
+    t.v0 = lds32(wa + pitch);
+    t.v1 = lds32(wa + pitch + 4);
+    t.v2 = lds32(wa + pitch + 8);
+    t.wt = lds64(lut_off);
+    return t;
+}
+
+// Fixed-point bilinear blend of one pixel, bit-identical to (sum w*S + 2^14) >> 15 per channel.
+// Returns B | G<<8 | R<<16.
+__device__ __forceinline__ uint32_t blend_taps(const Taps &t)
+{
     // six aligned bytes of each row: r?a = [B0 G0 R0 B1], r?b = [G1 R1 . .]
-    const uint32_t r0a = __funnelshift_r(w0, w1, sh), r0b = __funnelshift_r(w1, w2, sh);
-    const uint32_t r1a = __funnelshift_r(v0, v1, sh), r1b = __funnelshift_r(v1, v2, sh);
+    const uint32_t r0a = __funnelshift_r(t.w0, t.w1, t.sh), r0b = __funnelshift_r(t.w1, t.w2, t.sh);
+    const uint32_t r1a = __funnelshift_r(t.v0, t.v1, t.sh), r1b = __funnelshift_r(t.v1, t.v2, t.sh);
     // transpose to one word per channel, taps in order 00 01 10 11
     const uint32_t qb = __byte_perm(r0a, r1a, 0x7430);
     const uint32_t t0 = __byte_perm(r0a, r0b, 0x5241);   // [G00 G01 R00 R01]
     const uint32_t t1 = __byte_perm(r1a, r1b, 0x5241);   // [G10 G11 R10 R11]
     const uint32_t qg = __byte_perm(t0, t1, 0x5410);
     const uint32_t qr = __byte_perm(t0, t1, 0x7632);
-    const uint32_t vb = __dp4a(qb, wt.x, 128u) * 256u + __dp4a(qb, wt.y, 0u);
-    const uint32_t vg = __dp4a(qg, wt.x, 128u) * 256u + __dp4a(qg, wt.y, 0u);
-    const uint32_t vr = __dp4a(qr, wt.x, 128u) * 256u + __dp4a(qr, wt.y, 0u);
+    const uint32_t vb = __dp4a(qb, t.wt.x, 128u) * 256u + __dp4a(qb, t.wt.y, 0u);
+    const uint32_t vg = __dp4a(qg, t.wt.x, 128u) * 256u + __dp4a(qg, t.wt.y, 0u);
+    const uint32_t vr = __dp4a(qr, t.wt.x, 128u) * 256u + __dp4a(qr, t.wt.y, 0u);
     // results sit in byte 2 of vb, vg, vr; byte 3 is always 0
     const uint32_t bg = __byte_perm(vb, vg, 0x3362);
     return __byte_perm(bg, vr, 0x7610);
+}
+
+__device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint32_t lut_off)
+{
+    return blend_taps(fetch_taps(o, pitch, lut_off));
 }
 
 // Store one row's pixel of every lane into the warp's output block: lanes 4q..4q+3 hold 4 adjacent
@@ -159,7 +184,7 @@ __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, 
 constexpr int kConsumerWarps = kBlocksPerTile;
 constexpr int kFastThreads = 32 * (kConsumerWarps + 1);
 #ifndef BS_MIN_CTAS
-#define BS_MIN_CTAS 3
+#define BS_MIN_CTAS 2
 #endif
 #ifndef BS_STAGES
 #define BS_STAGES 3
@@ -178,8 +203,9 @@ __device__ __forceinline__ void run_layer_full(const CamDev &cam, int pitch, uin
     const RunAnchor a = run_anchor(cam.M, x, yc);
     const uint32_t run_base = stage_origin + (uint32_t)((a.by >> kFracBits) * pitch + (a.bx >> kFracBits) * 3);
     const int step = a.ny * pitch + a.nx * 3;      // whole texels per canvas row, as a byte offset
-#pragma unroll
-    for (int k = 0; k < kRun; ++k) {
+    // software pipeline: the shared-memory loads of pixel k+1 are issued before the arithmetic of
+    // pixel k, so a warp has work to do while its loads are in flight
+    auto fetch = [&](int k) {
         const int j = k - kRun / 2;
         int xbits, ybits;
         run_coord_bits(a, (float)j, xbits, ybits);
@@ -187,8 +213,16 @@ __device__ __forceinline__ void run_layer_full(const CamDev &cam, int pitch, uin
                            (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
         // the table sits on an 8 KB boundary, so its base can be OR-ed in after masking the index
         const uint32_t lut_off = lut_base | ((uint32_t)((ybits << 8) + ((xbits << 3) & 0xF8)) & 0x1FF8u);
-        const uint32_t px = sample_staged(o, pitch, lut_off);
+        return fetch_taps(o, pitch, lut_off);
+    };
+    Taps cur = fetch(0);
+#pragma unroll
+    for (int k = 0; k < kRun; ++k) {
+        Taps nxt = cur;
+        if (k + 1 < kRun) nxt = fetch(k + 1);
+        const uint32_t px = blend_taps(cur);
         store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
+        cur = nxt;
     }
 }
 
@@ -299,6 +333,10 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
+    // Programmatic dependent launch: let the next frame's kernel start filling SMs as this one's CTAs
+    // retire.  It may prefetch and composite its first tile, but touches the canvas and the tile
+    // scheduler only after griddepcontrol.wait, i.e. after this grid has completed.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     {
         uint2 *lut = reinterpret_cast<uint2 *>(gen0);
         for (int i = tid; i < 1024; i += kFastThreads) lut[i] = lut_entry(i);
@@ -317,7 +355,11 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         // Every tile becomes one ring item per layer (FAST) or a single descriptor-only item.
         if (lane == 0) {
             uint32_t slot = 0, phase = 1;    // a fresh mbarrier passes a wait on parity 1
-            for (int k = blockIdx.x; k < A.n_tiles; k += gridDim.x) {
+            // The first tile of a CTA is static (its index is the CTA's), the rest are handed out
+            // dynamically, heaviest first in the plan's order, so there is no tail imbalance.  The
+            // counter may still belong to the previous launch until that grid has completed.
+            bool prior_grid_done = false;
+            for (int k = (int)blockIdx.x; k < A.n_tiles;) {
                 const uint4 *rp = reinterpret_cast<const uint4 *>(&A.tiles[k]);
                 TileRec r;
                 {
@@ -370,7 +412,20 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                         phase ^= 1u;
                     }
                 }
+                if (!prior_grid_done) {
+                    asm volatile("griddepcontrol.wait;" ::: "memory");
+                    prior_grid_done = true;
+                }
+                k = (int)atomicAdd(&A.sched[0], 1u);
             }
+            if (!prior_grid_done) asm volatile("griddepcontrol.wait;" ::: "memory");
+            // out of tiles: tell the consumers to stop, and let the last CTA re-arm the scheduler
+            mbar_wait_addr(empty0 + 8 * slot, phase);
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(meta0 + kMetaBytes * slot), "r"(0u), "r"(0xFFu),
+                         "r"(0u), "r"(0u)
+                         : "memory");
+            mbar_arrive_addr(full0 + 8 * slot);
+            if (atomicInc(&A.sched[1], gridDim.x - 1) == gridDim.x - 1) atomicExch(&A.sched[0], gridDim.x);
         }
         return;
     }
@@ -379,13 +434,15 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     const uint32_t out_blk = out0 + (uint32_t)(warp * kWarpOutBytes);
     const int bx = (warp & 3) * 32, by = (warp >> 2) * kRun;      // block origin inside a tile
     uint32_t slot = 0, phase = 0;
-    for (int k = blockIdx.x; k < A.n_tiles; k += gridDim.x) {
+    bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
+    for (;;) {
         bool wrote = false, last;
         do {
             mbar_wait_addr(full0 + 8 * slot, phase);
             const uint4 m0 = lds128(meta0 + kMetaBytes * slot);
             const int tx0 = (int)(m0.x & 0xFFFFu) * kTileW + bx, ty0 = (int)(m0.x >> 16) * kTileH + by;
             const int type = (int)(m0.y & 0xFFu);
+            if (type == 0xFF) return;          // the producer ran out of tiles
             last = (m0.y >> 8) & 1u;
             if (type == kTileFast) {
                 if (!((m0.y >> (24 + warp)) & 1u)) {          // this layer writes into this block
@@ -406,6 +463,10 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                 __syncwarp();
                 if (lane == 0) mbar_arrive_addr(empty0 + 8 * slot);    // this warp is done with the slot
                 if (last) {
+                    if (!prior_grid_done) {
+                        asm volatile("griddepcontrol.wait;" ::: "memory");
+                        prior_grid_done = true;
+                    }
                     if (!wrote) {
                         if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);   // nobody wrote here
                     } else if (tx0 + 32 <= A.F.W && ty0 + kRun <= A.F.H) {
@@ -423,6 +484,10 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             } else {
                 __syncwarp();
                 if (lane == 0) mbar_arrive_addr(empty0 + 8 * slot);
+                if (!prior_grid_done) {
+                    asm volatile("griddepcontrol.wait;" ::: "memory");
+                    prior_grid_done = true;
+                }
                 if (type == kTileEmpty) {
                     if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);
                 } else {

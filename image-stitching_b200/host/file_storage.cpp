@@ -3,6 +3,7 @@
 
 #include <cctype>
 #include <cstdio>
+#include <cstring>
 #include <cstdlib>
 #include <fstream>
 #include <sstream>

@@ -306,8 +306,14 @@ int build_plan(bs_handle *h)
         }
     }
     h->smem_bytes = bs::kStages * h->stage_bytes + bs::kConsumerWarps * bs::kWarpOutBytes + 2 * bs::kLutBytes + bs::kStages * bs::kMetaBytes + 64;   // + 8 KB slack to align the table
-    BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    h->smem_bytes));
+    {
+        // The limit is a per-device property of the kernel, shared by every handle: always raise it to
+        // the device's opt-in maximum, so a handle with a small plan cannot lower it for another one.
+        int optin = 0;
+        BS_CUDA(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+        if (h->smem_bytes > optin) return BS_OK;   // does not fit: stay on the exact kernel
+        BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+    }
     int per_sm = 0, sms = 0;
     BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kFastThreads,
                                                              h->smem_bytes));

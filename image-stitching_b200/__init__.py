@@ -27,7 +27,7 @@ BORDER_TRANSPARENT = 5
 EXPORTS = [
     "bs_device_count", "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_submit",
     "bs_wait", "bs_pipeline_depth", "bs_stitch", "bs_submit_device", "bs_sync",
-    "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats",
+    "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
 ]
 
 
@@ -84,6 +84,8 @@ def lib():
     L.bs_host_alloc.restype = vp
     L.bs_host_free.argtypes = [vp]
     L.bs_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
+    L.bs_stitch_device_static.argtypes = [i, ip, ip, ctypes.POINTER(vp), ctypes.POINTER(sz), i, i, vp, sz, dp,
+                                          ctypes.c_uint, vp]
     _lib = L
     return L
 
@@ -205,6 +207,22 @@ class Stitcher:
         s = Stats()
         _check(lib().bs_get_stats(self._h, ctypes.byref(s)), self._h)
         return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+
+def stitch_device_static(src_whs, frame_ptrs, frame_pitches, canvas_wh, canvas_ptr, canvas_pitch, Hs, flags=0,
+                         stream=0):
+    """bs_stitch_device_static: one frame on device buffers, no allocation anywhere (the plan lives
+    in the library's fixed static device array).  Pointers are raw device addresses."""
+    n = len(src_whs)
+    Hs = np.ascontiguousarray(np.asarray(Hs, dtype=np.float64).reshape(n, 9))
+    sw = (ctypes.c_int * n)(*[int(w) for w, _ in src_whs])
+    sh = (ctypes.c_int * n)(*[int(h) for _, h in src_whs])
+    ptrs = (ctypes.c_void_p * n)(*[int(p) for p in frame_ptrs])
+    pitches = (ctypes.c_size_t * n)(*[int(p) for p in frame_pitches])
+    _check(lib().bs_stitch_device_static(n, sw, sh, ptrs, pitches, int(canvas_wh[0]), int(canvas_wh[1]),
+                                         int(canvas_ptr), int(canvas_pitch),
+                                         Hs.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), flags,
+                                         int(stream) if stream else None))
 
 
 def warpPerspective(src, dst, H, dsize, flags=INTER_LINEAR, borderMode=BORDER_TRANSPARENT,

@@ -714,3 +714,254 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// bs_stitch_device_static -- one panorama frame without allocating anything.
+//
+// Who this is for: callers that hold every buffer themselves and are not allowed to allocate while
+// they run -- a capture/render loop with a fixed memory budget, code running under an allocator that
+// forbids cudaMalloc after start-up (cudaMalloc also synchronises the whole device, which a frame loop
+// cannot afford), or a process whose memory was handed to it by a host application.  bs_create and
+// bs_submit allocate (plan, rings, streams); this entry point does not call cudaMalloc, cudaFree,
+// cudaHostAlloc, or any host heap routine.
+//
+// The staged kernel needs scratch memory: the tile plan and its scheduler counters.  Here they live
+// in ONE file-scope device array of a fixed size.  Consequences a caller must know:
+//   * every GPU that loads this library holds the array (BS_STATIC_SCRATCH_BYTES) until the process exits;
+//   * canvases that need more than BS_STATIC_MAX_TILES tiles of 128x32 pixels are refused;
+//   * all calls share the array and it keeps the previous call's contents.  The plan is rebuilt in full
+//     and the scheduler counters are re-armed by every call, so nothing stale is ever read, but two
+//     calls whose GPU work overlaps (different streams, or different host threads on different
+//     streams) race on it.  Issue calls on one stream, or order the streams yourself.
+//   * the first call on each device looks up the array's device address (cudaGetSymbolAddress) and
+//     sets the kernel's shared-memory limit; make that first call before any stream capture begins.
+// ================================================================================================
+#include <mutex>
+
+namespace {
+
+struct StaticScratch {
+    bs::TileRec tiles[BS_STATIC_MAX_TILES];
+    unsigned sched[64];          // [0] next dynamic tile, [1] CTAs that ran dry; padded to 256 bytes
+};
+static_assert(sizeof(StaticScratch) == BS_STATIC_SCRATCH_BYTES, "BS_STATIC_SCRATCH_BYTES is out of date");
+
+// The scratch itself.  In host code this name is only a stand-in for the device object: its device
+// address comes from cudaGetSymbolAddress (static_device_state), never from &g_static_scratch.
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+struct StaticDeviceState {
+    bool ready = false;
+    StaticScratch *scratch = nullptr;   // device address of g_static_scratch on this device
+    int sms = 0;
+    int smem_optin = 0;
+};
+constexpr int kStaticMaxDevices = 64;
+StaticDeviceState g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mutex;                            // host side of the sharing; the GPU side is the caller's job
+bs::TileRec g_static_recs[BS_STATIC_MAX_TILES];       // host staging for the plan, fixed size (no heap)
+bs::TileRec g_static_ordered[BS_STATIC_MAX_TILES];
+bs::PlanArgs g_static_plan_args;
+
+__global__ void static_sched_arm(unsigned *sched, unsigned first_dynamic)
+{
+    sched[0] = first_dynamic;   // the first tile of every CTA is static
+    sched[1] = 0u;
+}
+
+// Once per device, with that device current.
+int static_device_state(int dev, StaticDeviceState **out)
+{
+    if (dev < 0 || dev >= kStaticMaxDevices)
+        return fail(nullptr, BS_ERR_UNSUPPORTED, "bs_stitch_device_static: device ordinal %d not supported", dev);
+    StaticDeviceState &st = g_static_dev[dev];
+    if (!st.ready) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(nullptr, BS_ERR_CUDA, "bs_stitch_device_static: cudaGetSymbolAddress failed: %s",
+                        cudaGetErrorString(e));
+        st.scratch = static_cast<StaticScratch *>(p);
+        BS_CUDA(nullptr, cudaDeviceGetAttribute(&st.sms, cudaDevAttrMultiProcessorCount, dev));
+        BS_CUDA(nullptr, cudaDeviceGetAttribute(&st.smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+        BS_CUDA(nullptr, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              st.smem_optin));
+        st.ready = true;
+    }
+    *out = &st;
+    return BS_OK;
+}
+
+}  // namespace
+
+extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *src_h, const void *const *d_frames,
+                                       const size_t *pitch, int canvas_w, int canvas_h, void *d_canvas,
+                                       size_t canvas_pitch, const double *H, unsigned flags, void *stream)
+{
+    const char *me = "bs_stitch_device_static";
+    if (!src_w || !src_h || !d_frames || !pitch || !d_canvas || !H)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "%s: NULL argument", me);
+    if (n_cams < 1 || n_cams > bs::kMaxCamsPerLaunch)
+        return fail(nullptr, BS_ERR_UNSUPPORTED, "%s: n_cams=%d outside [1, %d]", me, n_cams, bs::kMaxCamsPerLaunch);
+    if (canvas_w < 1 || canvas_h < 1 || canvas_w > 65535 || canvas_h > 65535)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "%s: canvas %dx%d outside [1, 65535]", me, canvas_w, canvas_h);
+    for (int i = 0; i < n_cams; ++i) {
+        if (src_w[i] < 1 || src_h[i] < 1 || src_w[i] > BS_MAX_DIM || src_h[i] > BS_MAX_DIM)
+            return fail(nullptr, BS_ERR_INVALID_ARG, "%s: camera %d is %dx%d, outside [1, %d]", me, i, src_w[i], src_h[i],
+                        BS_MAX_DIM);
+        if (!d_frames[i] || pitch[i] < (size_t)src_w[i] * 3)
+            return fail(nullptr, BS_ERR_INVALID_ARG, "%s: frame %d is NULL or its pitch is below %d*3", me, i, src_w[i]);
+    }
+    if (canvas_pitch < (size_t)canvas_w * 3)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "%s: canvas_pitch=%zu < %d*3", me, canvas_pitch, canvas_w);
+    const int tiles_x = (canvas_w + bs::kTileW - 1) / bs::kTileW, tiles_y = (canvas_h + bs::kTileH - 1) / bs::kTileH;
+    const long long n_tiles_ll = (long long)tiles_x * tiles_y;
+    if (n_tiles_ll > BS_STATIC_MAX_TILES)
+        return fail(nullptr, BS_ERR_UNSUPPORTED,
+                    "%s: a %dx%d canvas needs %lld tiles of %dx%d pixels, the static scratch holds %d; use bs_create", me,
+                    canvas_w, canvas_h, n_tiles_ll, bs::kTileW, bs::kTileH, BS_STATIC_MAX_TILES);
+    const int n_tiles = (int)n_tiles_ll;
+    int rc = require_device(nullptr);
+    if (rc != BS_OK) return rc;
+    int dev = 0;
+    BS_CUDA(nullptr, cudaGetDevice(&dev));
+
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    StaticDeviceState *st = nullptr;
+    rc = static_device_state(dev, &st);
+    if (rc != BS_OK) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool keep = (flags & BS_FLAG_KEEP_CANVAS) != 0;
+    const int legacy = (flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
+    const int block_w = opencv_block_width(canvas_w, canvas_h);
+
+    // ---- plan into the static scratch -------------------------------------------------------------
+    bs::PlanArgs &P = g_static_plan_args;
+    memset(&P, 0, sizeof P);
+    for (int i = 0; i < n_cams; ++i) {
+        invert3x3(H + 9 * i, P.M[i]);
+        P.w[i] = src_w[i];
+        P.h[i] = src_h[i];
+    }
+    P.n_cams = n_cams;
+    P.W = canvas_w;
+    P.H = canvas_h;
+    P.block_w = block_w;
+    P.legacy_border = legacy;
+    P.tiles_x = tiles_x;
+    P.tiles_y = tiles_y;
+    P.out = st->scratch->tiles;
+    bs::plan_kernel<<<dim3(tiles_x, tiles_y), bs::kThreads, 0, s>>>(P);
+    BS_CUDA(nullptr, cudaGetLastError());
+    const size_t plan_bytes = sizeof(bs::TileRec) * (size_t)n_tiles;
+    BS_CUDA(nullptr, cudaMemcpyAsync(g_static_recs, st->scratch->tiles, plan_bytes, cudaMemcpyDeviceToHost, s));
+    BS_CUDA(nullptr, cudaStreamSynchronize(s));
+
+    // ---- size one TMA box per camera; tiles whose source box is too big go to the exact path -------
+    int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
+    for (int t = 0; t < n_tiles; ++t) {
+        bs::TileRec &r = g_static_recs[t];
+        if (r.type != bs::kTileFast) continue;
+        bool ok = true;
+        int twe[bs::kMaxLayers], tbh[bs::kMaxLayers];
+        for (int l = 0; l < r.n_layers; ++l) {
+            const int e0 = bs::box_elem0(r.bx0[l]), e1 = (3 * r.bx1[l] + 2) >> 2;
+            twe[l] = (e1 - e0 + 1 + 3) & ~3;
+            tbh[l] = r.by1[l] - r.by0[l] + 1;
+            if (twe[l] > 256 || tbh[l] > 256 || twe[l] * 4 * tbh[l] > kStageBytesMax) ok = false;
+        }
+        if (!ok) {
+            r.type = bs::kTileExact;
+            continue;
+        }
+        for (int l = 0; l < r.n_layers; ++l) {
+            we[r.cam[l]] = std::max(we[r.cam[l]], twe[l]);
+            bh[r.cam[l]] = std::max(bh[r.cam[l]], tbh[l]);
+        }
+    }
+    int stage = 0;
+    for (int c = 0; c < n_cams; ++c) {
+        if (we[c] * 4 * bh[c] > kStageBytesMax) {
+            for (int t = 0; t < n_tiles; ++t) {
+                bs::TileRec &r = g_static_recs[t];
+                if (r.type != bs::kTileFast) continue;
+                for (int l = 0; l < r.n_layers; ++l)
+                    if (r.cam[l] == c) r.type = bs::kTileExact;
+            }
+            we[c] = bh[c] = 0;
+        }
+        stage = std::max(stage, we[c] * 4 * bh[c]);
+    }
+    const int stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
+    int n_ordered = 0, n_fast = 0;
+    for (int t = 0; t < n_tiles; ++t)
+        if (g_static_recs[t].type == bs::kTileExact) g_static_ordered[n_ordered++] = g_static_recs[t];
+    for (int layers = bs::kMaxLayers; layers >= 1; --layers)
+        for (int t = 0; t < n_tiles; ++t)
+            if (g_static_recs[t].type == bs::kTileFast && g_static_recs[t].n_layers == layers)
+                g_static_ordered[n_ordered++] = g_static_recs[t], ++n_fast;
+    for (int t = 0; t < n_tiles; ++t)
+        if (g_static_recs[t].type == bs::kTileEmpty) g_static_ordered[n_ordered++] = g_static_recs[t];
+
+    const int smem_bytes = bs::kStages * stage_bytes + bs::kConsumerWarps * bs::kWarpOutBytes + 2 * bs::kLutBytes +
+                           bs::kStages * bs::kMetaBytes + 64;
+    bool fast = n_fast > 0 && get_encoder() && smem_bytes <= st->smem_optin && aligned16(d_canvas, canvas_pitch);
+    for (int i = 0; fast && i < n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
+    int per_sm = 0;
+    if (fast) {
+        BS_CUDA(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kFastThreads,
+                                                                       smem_bytes));
+        fast = per_sm >= 1;
+    }
+
+    bs::FastArgs FA;
+    memset(&FA, 0, sizeof FA);
+    bs::FrameArgs &A = FA.F;
+    A.n_cams = n_cams;
+    for (int i = 0; i < n_cams; ++i) {
+        memcpy(A.cam[i].M, P.M[i], 9 * sizeof(double));
+        A.cam[i].ptr = static_cast<const uint8_t *>(d_frames[i]);
+        A.cam[i].pitch = (long long)pitch[i];
+        A.cam[i].w = src_w[i];
+        A.cam[i].h = src_h[i];
+    }
+    A.canvas = static_cast<uint8_t *>(d_canvas);
+    A.cpitch = (long long)canvas_pitch;
+    A.W = canvas_w;
+    A.H = canvas_h;
+    A.block_w = block_w;
+    A.legacy_border = legacy;
+    A.keep_canvas = keep ? 1 : 0;
+
+    if (!fast) {
+        // no staged tiles (or unaligned buffers): the per-pixel kernel needs no scratch at all
+        dim3 grid((canvas_w + bs::kExactTileW - 1) / bs::kExactTileW, (canvas_h + bs::kExactTileH - 1) / bs::kExactTileH);
+        bs::stitch_exact_kernel<<<grid, dim3(32, bs::kExactTileH), 0, s>>>(A);
+        BS_CUDA(nullptr, cudaGetLastError());
+        return BS_OK;
+    }
+
+    for (int i = 0; i < n_cams; ++i) {
+        FA.box_we[i] = we[i];
+        FA.box_h[i] = bh[i];
+        if (we[i] > 0) {
+            const int er = encode_frame_map(&FA.tmap[i], d_frames[i], pitch[i], src_h[i], we[i], bh[i]);
+            if (er != 0) return fail(nullptr, BS_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d) for camera %d", me, er, i);
+        }
+    }
+    const int grid = std::min(n_tiles, per_sm * st->sms);
+    // the ordered plan replaces the raw one in the scratch, and the scheduler is re-armed: both are
+    // stream-ordered after the previous call's kernels on this stream
+    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->tiles, g_static_ordered, plan_bytes, cudaMemcpyHostToDevice, s));
+    static_sched_arm<<<1, 1, 0, s>>>(st->scratch->sched, (unsigned)grid);
+    BS_CUDA(nullptr, cudaGetLastError());
+    FA.tiles = st->scratch->tiles;
+    FA.n_tiles = n_tiles;
+    FA.stage_bytes = stage_bytes;
+    FA.sched = st->scratch->sched;
+    bs::stitch_fast_kernel<<<grid, bs::kFastThreads, smem_bytes, s>>>(FA);
+    BS_CUDA(nullptr, cudaGetLastError());
+    // the host staging arrays are reused by the next call: the copy above must have left them
+    BS_CUDA(nullptr, cudaStreamSynchronize(s));
+    return BS_OK;
+}

@@ -133,6 +133,29 @@ void bs_host_free(void *p);
 
 int bs_get_stats(const bs_handle *h, bs_stats *out);
 
+/*
+ * One panorama frame on DEVICE buffers without allocating anything.  No counterpart in the
+ * reference (it has no GPU path and no allocation discipline); added for callers that own all their
+ * memory and must not allocate while running -- frame loops with a fixed device-memory budget,
+ * hosts that forbid cudaMalloc after start-up (it also synchronises the device), plug-ins living
+ * inside someone else's allocator.  Same result as bs_create + bs_submit_device for the same
+ * arguments (flags: BS_FLAG_LEGACY_BORDER, BS_FLAG_KEEP_CANVAS), but the tile plan is rebuilt on every
+ * call, so it is slower per frame; n_cams <= 16.
+ *
+ * The plan and scheduler counters live in one static device array of BS_STATIC_SCRATCH_BYTES that
+ * every GPU loading the library keeps until exit.  Canvases needing more than BS_STATIC_MAX_TILES
+ * tiles of 128x32 pixels (ceil(w/128) * ceil(h/32) > 8192; a 15360x2160 panorama needs 8160) are
+ * refused with BS_ERR_UNSUPPORTED.  All calls share that array: calls whose GPU work overlaps (different
+ * streams) race on it, so keep them on one stream.  The first call on each device performs the
+ * one-time address lookup and must come before any stream capture.  The call returns after its
+ * kernels have finished (it synchronises `stream` once for the plan and once at the end).
+ */
+#define BS_STATIC_MAX_TILES 8192
+#define BS_STATIC_SCRATCH_BYTES (BS_STATIC_MAX_TILES * 80 + 256)
+int bs_stitch_device_static(int n_cams, const int *src_w, const int *src_h, const void *const *d_frames,
+                            const size_t *pitch, int canvas_w, int canvas_h, void *d_canvas,
+                            size_t canvas_pitch, const double *H, unsigned flags, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,93 @@
+"""bs_stitch_device_static: the entry point for callers that may not allocate.
+
+Some users of this library own all of their memory and cannot allocate while frames are flowing:
+a capture or render loop with a fixed device-memory budget, a host application that forbids
+cudaMalloc after start-up (it stalls the whole GPU), a plug-in running inside somebody else's
+allocator.  For them the library keeps the staged kernel's scratch (tile plan + scheduler counters)
+in one fixed static device array and offers one call that allocates nothing.
+
+What is checked here, through the C ABI, on the GPU:
+  * the static entry point produces exactly the bytes the regular entry points produce
+    (bs_create + bs_submit_device), on two calls in a row -- the second call finds the array full of
+    the first call's plan and counters and must not be disturbed by them;
+  * a different calibration right afterwards (other canvas, seams, ragged edges) is also exact, so
+    nothing stale survives in the shared array;
+  * a canvas that needs more tiles than the array holds is refused with a clear message.
+This file sorts last on purpose: with `pytest -x` every other test has already run if it fails.
+"""
+import numpy as np
+import pytest
+
+import oracle
+from conftest import pkg, workloads
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def regular_path(p, src_whs, canvas_wh, Hs, d_src, flags=0, prior=None):
+    """The existing entry points: handle + device-resident submit."""
+    d_out = torch.zeros((canvas_wh[1], canvas_wh[0], 3), dtype=torch.uint8, device="cuda")
+    if prior is not None:
+        d_out.copy_(torch.from_numpy(prior))
+    with p.Stitcher(src_whs, canvas_wh, Hs, flags=flags) as st:
+        st.submit_device([t.data_ptr() for t in d_src], [t.stride(0) for t in d_src], d_out.data_ptr(), d_out.stride(0), 0)
+        torch.cuda.synchronize()
+    return d_out.cpu().numpy()
+
+
+def static_path(p, src_whs, canvas_wh, Hs, d_src, flags=0, prior=None):
+    d_out = torch.full((canvas_wh[1], canvas_wh[0], 3), 201, dtype=torch.uint8, device="cuda")
+    if prior is not None:
+        d_out.copy_(torch.from_numpy(prior))
+    p.stitch_device_static(src_whs, [t.data_ptr() for t in d_src], [t.stride(0) for t in d_src], canvas_wh,
+                           d_out.data_ptr(), d_out.stride(0), Hs, flags=flags, stream=0)
+    torch.cuda.synchronize()
+    return d_out.cpu().numpy()
+
+
+def test_static_entry_matches_regular_entry_twice_in_a_row():
+    p = pkg()
+    w = workloads().get("cfg2")
+    whs = [w.src_wh] * w.n_cams
+    for frame in (0, 1):        # two calls in a row share the static array
+        srcs = [oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, frame, oracle.NOISE) for i in range(w.n_cams)]
+        d_src = [torch.from_numpy(s).cuda() for s in srcs]
+        want = regular_path(p, whs, w.canvas_wh, w.H, d_src)
+        got = static_path(p, whs, w.canvas_wh, w.H, d_src)
+        assert np.array_equal(got, want), f"frame {frame}: {(got != want).any(axis=2).sum()} pixels differ"
+        assert np.array_equal(got, oracle.stitch(srcs, w.H, w.canvas_wh))
+
+
+def test_other_calibration_right_after_is_not_disturbed_by_stale_scratch():
+    p = pkg()
+    rng = np.random.default_rng(77)
+    # first fill the array with a large plan ...
+    w = workloads().get("cfg2")
+    big = [torch.from_numpy(oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, 3, oracle.NOISE)).cuda() for i in range(2)]
+    static_path(p, [w.src_wh] * 2, w.canvas_wh, w.H, big)
+    # ... then run a small, ragged, three-camera canvas with seams, holes and last-row/column pixels
+    whs = [(200, 120), (160, 130), (96, 64)]
+    canvas = (531, 203)
+    Hs = [np.array([[1.1, 0.03, 5.0], [-0.02, 1.2, 8.0], [2e-5, 1e-5, 1.0]]),
+          np.array([[0.9, -0.05, 230.0], [0.04, 1.05, 20.0], [-1e-5, 2e-5, 1.0]]),
+          np.array([[2.5, 0.0, 300.0], [0.0, 2.5, 30.0], [0.0, 0.0, 1.0]])]
+    srcs = [rng.integers(0, 256, (h, wd, 3), dtype=np.uint8) for wd, h in whs]
+    d_src = [torch.from_numpy(s).cuda() for s in srcs]
+    for flags, prior in ((0, None), (p.FLAG_LEGACY_BORDER, None),
+                         (p.FLAG_KEEP_CANVAS, rng.integers(0, 256, (canvas[1], canvas[0], 3), dtype=np.uint8))):
+        want = regular_path(p, whs, canvas, Hs, d_src, flags, prior)
+        got = static_path(p, whs, canvas, Hs, d_src, flags, prior)
+        assert np.array_equal(got, want), f"flags={flags}"
+
+
+def test_canvas_beyond_the_static_array_is_refused():
+    p = pkg()
+    w = workloads().get("cfg1")        # 6085 x 8353 needs 48 x 262 = 12576 tiles, the array holds 8192
+    d_src = [torch.zeros((8, 8, 3), dtype=torch.uint8, device="cuda")]
+    d_out = torch.zeros((16, 16, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(p.StitchError) as e:
+        p.stitch_device_static([(8, 8)], [d_src[0].data_ptr()], [d_src[0].stride(0)], w.canvas_wh, d_out.data_ptr(),
+                               w.canvas_wh[0] * 3, [np.eye(3)])
+    assert e.value.code == -4
+    assert "12576 tiles" in str(e.value) and "8192" in str(e.value)

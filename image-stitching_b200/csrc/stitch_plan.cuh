@@ -16,7 +16,10 @@
 namespace bs {
 
 constexpr int kTileW = 128;
-constexpr int kBlocksPerTile = 8;   // 32x16 blocks per tile = consumer warps per CTA (4: one row of blocks)
+#ifndef BS_BLOCKS_PER_TILE
+#define BS_BLOCKS_PER_TILE 8
+#endif
+constexpr int kBlocksPerTile = BS_BLOCKS_PER_TILE;   // 32x16 blocks per tile = consumer warps per CTA (4: one row of blocks)
 constexpr int kThreads = 32 * kBlocksPerTile;
 constexpr int kRun = 16;           // vertical run: consecutive rows per thread
 constexpr int kTileH = kRun * (kBlocksPerTile / 4);

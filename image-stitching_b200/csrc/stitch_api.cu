@@ -52,9 +52,9 @@ struct bs_handle {
     int64_t kernel_launches = 0;
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
-    bs::TileRec *d_tiles = nullptr;      // plan, ordered: exact tiles, fast tiles, empty tiles
-    unsigned *d_sched = nullptr;         // tile scheduler counters of the frame kernel
-    int n_tiles = 0, tiles_x = 0, tiles_y = 0;
+    bs::WorkItem *d_items = nullptr;     // plan: work items, heaviest blocks first (same allocation held the raw records)
+    int *d_warp_start = nullptr;         // item range of every warp of the grid
+    int n_blocks = 0, blocks_x = 0, blocks_y = 0, n_items = 0;
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
@@ -168,15 +168,125 @@ int encode_frame_map(CUtensorMap *m, const void *ptr, size_t pitch, int h, int b
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
 
-constexpr int kStageBytesMax = 32 * 1024;   // per-stage cap on a camera's source box
+constexpr int kStageBytesMax = 6 * 1024;    // per-warp, per-stage cap on a block's source box
 
-// Build the tile plan on the device and post-process it on the host (once per calibration).
+// Result of turning the raw block records into what the frame kernel consumes.
+struct PlanLayout {
+    int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
+    int stage_bytes = 0, smem_bytes = 0;
+    int n_items = 0;
+    int64_t n_fast = 0, n_exact = 0, n_empty = 0;
+};
+
+// Host post-processing of the plan, on caller-provided storage (no allocation here):
+//   recs[n_blocks]        raw records from plan_kernel (modified: oversized boxes are demoted to EXACT)
+//   items[>= 2*n_blocks]  output, heaviest blocks first, a block's layers adjacent
+// Sizes one TMA box per camera (the largest source box among its blocks).
+void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *items, PlanLayout *L)
+{
+    int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
+    for (int t = 0; t < n_blocks; ++t) {
+        bs::BlockRec &r = recs[t];
+        if (r.type != bs::kBlockFast) continue;
+        int twe[bs::kMaxLayers], tbh[bs::kMaxLayers];
+        bool ok = true;
+        for (int l = 0; l < r.n_layers; ++l) {
+            const int e0 = bs::box_elem0(r.layer[l].x0), e1 = (3 * r.layer[l].x1 + 2) >> 2;   // box starts 16-byte aligned
+            twe[l] = (e1 - e0 + 1 + 3) & ~3;                                                   // inner extent: multiple of 16 bytes
+            tbh[l] = r.layer[l].y1 - r.layer[l].y0 + 1;
+            if (twe[l] > 256 || tbh[l] > 256 || twe[l] * 4 * tbh[l] > kStageBytesMax) ok = false;
+        }
+        if (!ok) {
+            r.type = bs::kBlockExact;
+            continue;
+        }
+        for (int l = 0; l < r.n_layers; ++l) {
+            const int c = r.layer[l].cam;
+            we[c] = std::max(we[c], twe[l]);
+            bh[c] = std::max(bh[c], tbh[l]);
+        }
+    }
+    // the per-camera maxima of width and height come from different blocks; re-check the product
+    int stage = 0;
+    for (int c = 0; c < n_cams; ++c) {
+        if (we[c] * 4 * bh[c] > kStageBytesMax) {
+            for (int t = 0; t < n_blocks; ++t) {
+                bs::BlockRec &r = recs[t];
+                if (r.type != bs::kBlockFast) continue;
+                for (int l = 0; l < r.n_layers; ++l)
+                    if (r.layer[l].cam == c) r.type = bs::kBlockExact;
+            }
+            we[c] = bh[c] = 0;
+        }
+        L->box_we[c] = we[c];
+        L->box_h[c] = bh[c];
+        stage = std::max(stage, we[c] * 4 * bh[c]);
+    }
+    L->stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
+    L->smem_bytes = 2 * bs::kLutBytes + bs::kWarpsPerCta * bs::warp_smem_bytes(L->stage_bytes) + 64;   // table + 8 KB alignment slack
+    L->n_fast = L->n_exact = L->n_empty = 0;
+    int n = 0;
+    auto emit = [&](const bs::BlockRec &r, int l) {
+        bs::WorkItem &it = items[n++];
+        memset(&it, 0, sizeof it);
+        it.bx = r.bx;
+        it.by = r.by;
+        it.type = r.type;
+        const int nl = (r.type == bs::kBlockFast) ? r.n_layers : 1;
+        it.flags = (uint8_t)((l == 0 ? bs::kItemFirst : 0) | (l == nl - 1 ? bs::kItemLast : 0));
+        if (r.type == bs::kBlockFast) {
+            it.flags |= r.layer[l].full ? bs::kItemFull : 0;
+            it.cam = r.layer[l].cam;
+            it.groups = r.layer[l].groups;
+            it.c0 = (int16_t)bs::box_elem0(r.layer[l].x0);
+            it.y0 = r.layer[l].y0;
+            it.origin_off = (uint32_t)((int)it.y0 * (L->box_we[it.cam] * 4) + 4 * (int)it.c0);
+        }
+    };
+    for (int t = 0; t < n_blocks; ++t)
+        if (recs[t].type == bs::kBlockExact) emit(recs[t], 0), L->n_exact++;
+    for (int layers = bs::kMaxLayers; layers >= 1; --layers)
+        for (int t = 0; t < n_blocks; ++t)
+            if (recs[t].type == bs::kBlockFast && recs[t].n_layers == layers) {
+                for (int l = 0; l < layers; ++l) emit(recs[t], l);
+                L->n_fast++;
+            }
+    for (int t = 0; t < n_blocks; ++t)
+        if (recs[t].type == bs::kBlockEmpty) emit(recs[t], 0), L->n_empty++;
+    L->n_items = n;
+}
+
+// Contiguous item ranges for the n_warps warps of the grid, balanced by estimated cost; a block's
+// layers stay with one warp.  warp_start has n_warps + 1 entries.
+void split_items(const bs::WorkItem *items, int n_items, int n_warps, int *warp_start)
+{
+    // relative run times measured on B200: the unrolled hot path = 4, the general path (coverage
+    // tests, byte stores, exact coordinates where flagged) about twice that, per-pixel fp64 blocks far more
+    auto cost = [](const bs::WorkItem &it) -> long long {
+        if (it.type == bs::kBlockExact) return 60;
+        if (it.type != bs::kBlockFast) return 1;
+        return ((it.flags & bs::kItemFull) && it.groups == 0) ? 4 : 9;
+    };
+    long long total = 0;
+    for (int i = 0; i < n_items; ++i) total += cost(items[i]);
+    int i = 0;
+    long long acc = 0;
+    warp_start[0] = 0;
+    for (int w = 1; w <= n_warps; ++w) {
+        const long long target = (total * w + n_warps - 1) / n_warps;
+        while (i < n_items && (acc < target || !(items[i].flags & bs::kItemFirst))) acc += cost(items[i++]);
+        warp_start[w] = i;
+    }
+    warp_start[n_warps] = n_items;
+}
+
+// Build the block plan on the device and post-process it on the host (once per calibration).
 int build_plan(bs_handle *h)
 {
     h->fast_ok = false;
-    h->tiles_x = (h->W + bs::kTileW - 1) / bs::kTileW;
-    h->tiles_y = (h->H + bs::kTileH - 1) / bs::kTileH;
-    h->n_tiles = h->tiles_x * h->tiles_y;
+    h->blocks_x = (h->W + bs::kBlockW - 1) / bs::kBlockW;
+    h->blocks_y = (h->H + bs::kBlockH - 1) / bs::kBlockH;
+    h->n_blocks = h->blocks_x * h->blocks_y;
     if ((h->flags & BS_FLAG_EXACT_ONLY) || h->n_cams > bs::kMaxCamsPerLaunch || !get_encoder()) return BS_OK;
 
     bs::PlanArgs *P = new bs::PlanArgs;
@@ -191,121 +301,57 @@ int build_plan(bs_handle *h)
     P->H = h->H;
     P->block_w = opencv_block_width(h->W, h->H);
     P->legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
-    P->tiles_x = h->tiles_x;
-    P->tiles_y = h->tiles_y;
-    const size_t bytes = sizeof(bs::TileRec) * (size_t)h->n_tiles;
-    cudaError_t e = cudaMalloc(&h->d_tiles, bytes);
+    P->keep_canvas = (h->flags & BS_FLAG_KEEP_CANVAS) ? 1 : 0;
+    P->blocks_x = h->blocks_x;
+    P->blocks_y = h->blocks_y;
+    // device scratch: raw records first, later overwritten by the item list (2 items of 16 bytes per block)
+    const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)h->n_blocks;
+    void *d_plan = nullptr;
+    cudaError_t e = cudaMalloc(&d_plan, raw_bytes);
     if (e == cudaSuccess) {
-        P->out = h->d_tiles;
-        bs::plan_kernel<<<dim3(h->tiles_x, h->tiles_y), bs::kThreads, 0, h->s_compute>>>(*P);
+        h->d_items = static_cast<bs::WorkItem *>(d_plan);
+        P->out = static_cast<bs::BlockRec *>(d_plan);
+        bs::plan_kernel<<<dim3((h->blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, h->blocks_y), 32 * bs::kPlanWarps, 0,
+                          h->s_compute>>>(*P);
         e = cudaGetLastError();
     }
     delete P;
-    std::vector<bs::TileRec> recs(h->n_tiles);
-    if (e == cudaSuccess)
-        e = cudaMemcpyAsync(recs.data(), h->d_tiles, bytes, cudaMemcpyDeviceToHost, h->s_compute);
+    std::vector<bs::BlockRec> recs(h->n_blocks);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(recs.data(), d_plan, raw_bytes, cudaMemcpyDeviceToHost, h->s_compute);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
-    if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "tile plan failed: %s", cudaGetErrorString(e));
+    if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "block plan failed: %s", cudaGetErrorString(e));
     h->kernel_launches++;
-    h->device_bytes += bytes;
-    h->scratch_bytes += bytes;
+    h->device_bytes += raw_bytes;
+    h->scratch_bytes += raw_bytes;
 
-    // per-camera TMA box = largest source box among its tiles; tiles whose box is too big go exact
-    int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
-    for (bs::TileRec &r : recs) {
-        if (r.type != bs::kTileFast) continue;
-        bool ok = true;
-        int twe[bs::kMaxLayers], tbh[bs::kMaxLayers];
-        for (int l = 0; l < r.n_layers; ++l) {
-            const int e0 = bs::box_elem0(r.bx0[l]), e1 = (3 * r.bx1[l] + 2) >> 2;   // box starts 16-byte aligned
-            twe[l] = (e1 - e0 + 1 + 3) & ~3;            // inner extent must be a multiple of 16 bytes
-            tbh[l] = r.by1[l] - r.by0[l] + 1;
-            if (twe[l] > 256 || tbh[l] > 256 || twe[l] * 4 * tbh[l] > kStageBytesMax) ok = false;
-        }
-        if (!ok) {
-            r.type = bs::kTileExact;
-            continue;
-        }
-        for (int l = 0; l < r.n_layers; ++l) {
-            we[r.cam[l]] = std::max(we[r.cam[l]], twe[l]);
-            bh[r.cam[l]] = std::max(bh[r.cam[l]], tbh[l]);
-        }
-    }
-    // the per-camera maxima of width and height come from different tiles; re-check the product
-    int stage = 0;
-    for (int c = 0; c < h->n_cams; ++c) {
-        if (we[c] * 4 * bh[c] > kStageBytesMax) {
-            // shrink by sending this camera's largest-box tiles to the exact path
-            for (bs::TileRec &r : recs) {
-                if (r.type != bs::kTileFast) continue;
-                for (int l = 0; l < r.n_layers; ++l)
-                    if (r.cam[l] == c) r.type = bs::kTileExact;
-            }
-            we[c] = bh[c] = 0;
-        }
-        h->box_we[c] = we[c];
-        h->box_h[c] = bh[c];
-        stage = std::max(stage, we[c] * 4 * bh[c]);
-    }
-    h->stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
-
-    std::vector<bs::TileRec> ordered;
-    ordered.reserve(recs.size());
-    h->n_fast = h->n_exact = h->n_empty = 0;
-    for (const bs::TileRec &r : recs)
-        if (r.type == bs::kTileExact) ordered.push_back(r), h->n_exact++;
-    for (int layers = bs::kMaxLayers; layers >= 1; --layers)   // heaviest tiles first
-        for (const bs::TileRec &r : recs)
-            if (r.type == bs::kTileFast && r.n_layers == layers) ordered.push_back(r), h->n_fast++;
-    for (const bs::TileRec &r : recs)
-        if (r.type == bs::kTileEmpty) ordered.push_back(r), h->n_empty++;
-    BS_CUDA(h, cudaMemcpy(h->d_tiles, ordered.data(), bytes, cudaMemcpyHostToDevice));
-    BS_CUDA(h, cudaMalloc(&h->d_sched, 2 * sizeof(unsigned)));
-    BS_CUDA(h, cudaMemset(h->d_sched, 0, 2 * sizeof(unsigned)));   // [0] is set to the grid size below
-    h->device_bytes += 8;
-    h->scratch_bytes += 8;
+    std::vector<bs::WorkItem> items((size_t)h->n_blocks * bs::kMaxLayers);
+    PlanLayout L;
+    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L);
+    memcpy(h->box_we, L.box_we, sizeof h->box_we);
+    memcpy(h->box_h, L.box_h, sizeof h->box_h);
+    h->stage_bytes = L.stage_bytes;
+    h->smem_bytes = L.smem_bytes;
+    h->n_items = L.n_items;
+    h->n_fast = L.n_fast;
+    h->n_exact = L.n_exact;
+    h->n_empty = L.n_empty;
 
     if (getenv("BS_DEBUG_PLAN_SUMMARY")) {
-        long groups = 0, flagged_groups = 0, blocks = 0, flagged_blocks = 0;
-        long per_cam[bs::kMaxCamsPerLaunch] = {0};
-        for (const bs::TileRec &r : ordered) {
-            if (r.type != bs::kTileFast) continue;
-            for (int l = 0; l < r.n_layers; ++l) {
-                for (int w = 0; w < 8; ++w) {
-                    const unsigned g = (r.exact_mask[l] >> (4 * w)) & 15u;
-                    blocks++;
-                    groups += 4;
-                    flagged_groups += __builtin_popcount(g);
-                    if (g) flagged_blocks++, per_cam[r.cam[l]]++;
-                }
+        long flagged = 0, fast_items = 0, full_items = 0;
+        for (int i = 0; i < L.n_items; ++i)
+            if (items[i].type == bs::kBlockFast) {
+                fast_items++;
+                flagged += items[i].groups != 0;
+                full_items += (items[i].flags & bs::kItemFull) != 0;
             }
-        }
-        fprintf(stderr, "[plan] blocks %ld flagged %ld (%.2f%%), 32x4 groups %ld flagged %ld (%.2f%%)\n", blocks,
-                flagged_blocks, 100.0 * flagged_blocks / (blocks ? blocks : 1), groups, flagged_groups,
-                100.0 * flagged_groups / (groups ? groups : 1));
-        for (int c = 0; c < h->n_cams; ++c) fprintf(stderr, "[plan]   cam %d flagged blocks %ld\n", c, per_cam[c]);
-        int shown = 0;
-        for (const bs::TileRec &r : ordered)
-            for (int l = 0; l < r.n_layers && shown < 12; ++l)
-                if (r.type == bs::kTileFast && r.exact_mask[l]) {
-                    fprintf(stderr, "[plan]   tile (%d,%d) cam %d mask %08x\n", r.tx, r.ty, r.cam[l], r.exact_mask[l]);
-                    shown++;
-                }
-    }
-    if (getenv("BS_DEBUG_PLAN")) {
+        fprintf(stderr, "[plan] blocks %d: fast %lld exact %lld empty %lld; items %d, fast items %ld (full %ld, exact-coordinate groups in %ld)\n",
+                h->n_blocks, (long long)L.n_fast, (long long)L.n_exact, (long long)L.n_empty, L.n_items, fast_items,
+                full_items, flagged);
         for (int c = 0; c < h->n_cams; ++c)
-            fprintf(stderr, "[plan] cam %d: %dx%d box %d elems x %d rows\n", c, h->sw[c], h->sh[c], h->box_we[c],
-                    h->box_h[c]);
-        for (const bs::TileRec &r : ordered) {
-            fprintf(stderr, "[plan] tile (%d,%d) type %d layers %d unc %d:", r.tx, r.ty, r.type, r.n_layers,
-                    r.has_uncovered);
-            for (int l = 0; l < r.n_layers; ++l)
-                fprintf(stderr, " [cam %d x %d..%d y %d..%d exact %x all %02x none %02x]", r.cam[l], r.bx0[l], r.bx1[l],
-                        r.by0[l], r.by1[l], r.exact_mask[l], r.all_mask[l], r.none_mask[l]);
-            fprintf(stderr, "\n");
-        }
+            fprintf(stderr, "[plan]   cam %d: %dx%d box %d elems x %d rows\n", c, h->sw[c], h->sh[c], h->box_we[c], h->box_h[c]);
+        fprintf(stderr, "[plan]   stage %d B, smem/CTA %d B\n", h->stage_bytes, h->smem_bytes);
     }
-    h->smem_bytes = bs::kStages * h->stage_bytes + bs::kConsumerWarps * bs::kWarpOutBytes + 2 * bs::kLutBytes + bs::kStages * bs::kMetaBytes + 64;   // + 8 KB slack to align the table
+
     {
         // The limit is a per-device property of the kernel, shared by every handle: always raise it to
         // the device's opt-in maximum, so a handle with a small plan cannot lower it for another one.
@@ -319,12 +365,19 @@ int build_plan(bs_handle *h)
                                                              h->smem_bytes));
     BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
     if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
-    h->grid = std::min(h->n_tiles, per_sm * sms);
-    if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, std::min(h->n_tiles, atoi(g)));
-    {   // the first tile of every CTA is static, so the dynamic counter starts at the grid size
-        const unsigned first_dynamic = (unsigned)h->grid;
-        BS_CUDA(h, cudaMemcpy(h->d_sched, &first_dynamic, sizeof first_dynamic, cudaMemcpyHostToDevice));
-    }
+    h->grid = std::max(1, std::min((h->n_items + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
+    if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
+    const int n_warps = h->grid * bs::kWarpsPerCta;
+    std::vector<int> warp_start(n_warps + 1);
+    split_items(items.data(), h->n_items, n_warps, warp_start.data());
+
+    const size_t item_bytes = sizeof(bs::WorkItem) * (size_t)h->n_items;   // <= raw_bytes: 2 x 16 B per block
+    BS_CUDA(h, cudaMemcpy(h->d_items, items.data(), item_bytes, cudaMemcpyHostToDevice));
+    const size_t ws_bytes = sizeof(int) * (size_t)(n_warps + 1);
+    BS_CUDA(h, cudaMalloc(&h->d_warp_start, ws_bytes));
+    BS_CUDA(h, cudaMemcpy(h->d_warp_start, warp_start.data(), ws_bytes, cudaMemcpyHostToDevice));
+    h->device_bytes += ws_bytes;
+    h->scratch_bytes += ws_bytes;
     h->fast_ok = true;
     return BS_OK;
 }
@@ -354,8 +407,8 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             A.cam[i].pitch = (long long)pitch[i];
             A.cam[i].w = h->sw[i];
             A.cam[i].h = h->sh[i];
-            FA.box_we[i] = h->box_we[i];
-            FA.box_h[i] = h->box_h[i];
+            FA.pitch[i] = h->box_we[i] * 4;
+            FA.box_bytes[i] = h->box_we[i] * 4 * h->box_h[i];
             if (h->box_we[i] > 0) {
                 const int er = encode_frame_map(&FA.tmap[i], d_frames[i], pitch[i], h->sh[i], h->box_we[i],
                                                 h->box_h[i]);
@@ -372,10 +425,9 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.block_w = opencv_block_width(h->W, h->H);
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = keep ? 1 : 0;
-        FA.tiles = h->d_tiles;
-        FA.n_tiles = h->n_tiles;
+        FA.items = h->d_items;
+        FA.warp_start = h->d_warp_start;
         FA.stage_bytes = h->stage_bytes;
-        FA.sched = h->d_sched;
         {
             // programmatic dependent launch: the prologue and first tile of this frame may overlap the
             // tail of the previous frame's kernel on the same stream (see stitch_fast.cuh)
@@ -540,8 +592,8 @@ int bs_destroy(bs_handle *h)
         if (s.ev_kernel) cudaEventDestroy(s.ev_kernel);
         if (s.ev_done) cudaEventDestroy(s.ev_done);
     }
-    cudaFree(h->d_tiles);
-    cudaFree(h->d_sched);
+    cudaFree(h->d_items);
+    cudaFree(h->d_warp_start);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
@@ -693,9 +745,9 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
     out->canvas_w = h->W;
     out->canvas_h = h->H;
     if (h->fast_ok) {
-        out->tile_w = bs::kTileW;
-        out->tile_h = bs::kTileH;
-        out->n_tiles = h->n_tiles;
+        out->tile_w = bs::kBlockW;
+        out->tile_h = bs::kBlockH;
+        out->n_tiles = h->n_blocks;
         out->n_tiles_fast = h->n_fast;
         out->n_tiles_exact = h->n_exact;
         out->n_tiles_empty = h->n_empty;
@@ -725,12 +777,12 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 // bs_submit allocate (plan, rings, streams); this entry point does not call cudaMalloc, cudaFree,
 // cudaHostAlloc, or any host heap routine.
 //
-// The staged kernel needs scratch memory: the tile plan and its scheduler counters.  Here they live
+// The staged kernel needs scratch memory: the block plan and the per-warp work split.  Here they live
 // in ONE file-scope device array of a fixed size.  Consequences a caller must know:
 //   * every GPU that loads this library holds the array (BS_STATIC_SCRATCH_BYTES) until the process exits;
-//   * canvases that need more than BS_STATIC_MAX_TILES tiles of 128x32 pixels are refused;
+//   * canvases that need more than BS_STATIC_MAX_BLOCKS blocks of 32x16 pixels are refused;
 //   * all calls share the array and it keeps the previous call's contents.  The plan is rebuilt in full
-//     and the scheduler counters are re-armed by every call, so nothing stale is ever read, but two
+//     and the work split rewritten by every call, so nothing stale is ever read, but two
 //     calls whose GPU work overlaps (different streams, or different host threads on different
 //     streams) race on it.  Issue calls on one stream, or order the streams yourself.
 //   * the first call on each device looks up the array's device address (cudaGetSymbolAddress) and
@@ -740,11 +792,14 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 
 namespace {
 
+constexpr int kStaticMaxWarps = 8192;   // grid warps the warp_start table has room for (B200: 148 SMs x 2 CTAs x 8 = 2368)
 struct StaticScratch {
-    bs::TileRec tiles[BS_STATIC_MAX_TILES];
-    unsigned sched[64];          // [0] next dynamic tile, [1] CTAs that ran dry; padded to 256 bytes
+    // raw block records from the plan kernel; then overwritten by the work items (2 x 16 bytes per block)
+    bs::BlockRec plan[BS_STATIC_MAX_BLOCKS];
+    int warp_start[kStaticMaxWarps];
 };
 static_assert(sizeof(StaticScratch) == BS_STATIC_SCRATCH_BYTES, "BS_STATIC_SCRATCH_BYTES is out of date");
+static_assert(sizeof(bs::WorkItem) * bs::kMaxLayers <= sizeof(bs::BlockRec), "items must fit where the raw records were");
 
 // The scratch itself.  In host code this name is only a stand-in for the device object: its device
 // address comes from cudaGetSymbolAddress (static_device_state), never from &g_static_scratch.
@@ -759,15 +814,10 @@ struct StaticDeviceState {
 constexpr int kStaticMaxDevices = 64;
 StaticDeviceState g_static_dev[kStaticMaxDevices];
 std::mutex g_static_mutex;                            // host side of the sharing; the GPU side is the caller's job
-bs::TileRec g_static_recs[BS_STATIC_MAX_TILES];       // host staging for the plan, fixed size (no heap)
-bs::TileRec g_static_ordered[BS_STATIC_MAX_TILES];
+bs::BlockRec g_static_recs[BS_STATIC_MAX_BLOCKS];     // host staging for the plan, fixed size (no heap)
+bs::WorkItem g_static_items[BS_STATIC_MAX_BLOCKS * bs::kMaxLayers];
+int g_static_warp_start[kStaticMaxWarps];
 bs::PlanArgs g_static_plan_args;
-
-__global__ void static_sched_arm(unsigned *sched, unsigned first_dynamic)
-{
-    sched[0] = first_dynamic;   // the first tile of every CTA is static
-    sched[1] = 0u;
-}
 
 // Once per device, with that device current.
 int static_device_state(int dev, StaticDeviceState **out)
@@ -814,13 +864,13 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     }
     if (canvas_pitch < (size_t)canvas_w * 3)
         return fail(nullptr, BS_ERR_INVALID_ARG, "%s: canvas_pitch=%zu < %d*3", me, canvas_pitch, canvas_w);
-    const int tiles_x = (canvas_w + bs::kTileW - 1) / bs::kTileW, tiles_y = (canvas_h + bs::kTileH - 1) / bs::kTileH;
-    const long long n_tiles_ll = (long long)tiles_x * tiles_y;
-    if (n_tiles_ll > BS_STATIC_MAX_TILES)
+    const int blocks_x = (canvas_w + bs::kBlockW - 1) / bs::kBlockW, blocks_y = (canvas_h + bs::kBlockH - 1) / bs::kBlockH;
+    const long long n_blocks_ll = (long long)blocks_x * blocks_y;
+    if (n_blocks_ll > BS_STATIC_MAX_BLOCKS)
         return fail(nullptr, BS_ERR_UNSUPPORTED,
-                    "%s: a %dx%d canvas needs %lld tiles of %dx%d pixels, the static scratch holds %d; use bs_create", me,
-                    canvas_w, canvas_h, n_tiles_ll, bs::kTileW, bs::kTileH, BS_STATIC_MAX_TILES);
-    const int n_tiles = (int)n_tiles_ll;
+                    "%s: a %dx%d canvas needs %lld blocks of %dx%d pixels, the static scratch holds %d; use bs_create", me,
+                    canvas_w, canvas_h, n_blocks_ll, bs::kBlockW, bs::kBlockH, BS_STATIC_MAX_BLOCKS);
+    const int n_blocks = (int)n_blocks_ll;
     int rc = require_device(nullptr);
     if (rc != BS_OK) return rc;
     int dev = 0;
@@ -835,7 +885,7 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     const int legacy = (flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
     const int block_w = opencv_block_width(canvas_w, canvas_h);
 
-    // ---- plan into the static scratch -------------------------------------------------------------
+    // ---- plan into the static scratch (every record is rewritten: nothing stale survives) -----------
     bs::PlanArgs &P = g_static_plan_args;
     memset(&P, 0, sizeof P);
     for (int i = 0; i < n_cams; ++i) {
@@ -848,69 +898,25 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     P.H = canvas_h;
     P.block_w = block_w;
     P.legacy_border = legacy;
-    P.tiles_x = tiles_x;
-    P.tiles_y = tiles_y;
-    P.out = st->scratch->tiles;
-    bs::plan_kernel<<<dim3(tiles_x, tiles_y), bs::kThreads, 0, s>>>(P);
+    P.keep_canvas = keep ? 1 : 0;
+    P.blocks_x = blocks_x;
+    P.blocks_y = blocks_y;
+    P.out = st->scratch->plan;
+    bs::plan_kernel<<<dim3((blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, blocks_y), 32 * bs::kPlanWarps, 0, s>>>(P);
     BS_CUDA(nullptr, cudaGetLastError());
-    const size_t plan_bytes = sizeof(bs::TileRec) * (size_t)n_tiles;
-    BS_CUDA(nullptr, cudaMemcpyAsync(g_static_recs, st->scratch->tiles, plan_bytes, cudaMemcpyDeviceToHost, s));
+    const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)n_blocks;
+    BS_CUDA(nullptr, cudaMemcpyAsync(g_static_recs, st->scratch->plan, raw_bytes, cudaMemcpyDeviceToHost, s));
     BS_CUDA(nullptr, cudaStreamSynchronize(s));
 
-    // ---- size one TMA box per camera; tiles whose source box is too big go to the exact path -------
-    int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
-    for (int t = 0; t < n_tiles; ++t) {
-        bs::TileRec &r = g_static_recs[t];
-        if (r.type != bs::kTileFast) continue;
-        bool ok = true;
-        int twe[bs::kMaxLayers], tbh[bs::kMaxLayers];
-        for (int l = 0; l < r.n_layers; ++l) {
-            const int e0 = bs::box_elem0(r.bx0[l]), e1 = (3 * r.bx1[l] + 2) >> 2;
-            twe[l] = (e1 - e0 + 1 + 3) & ~3;
-            tbh[l] = r.by1[l] - r.by0[l] + 1;
-            if (twe[l] > 256 || tbh[l] > 256 || twe[l] * 4 * tbh[l] > kStageBytesMax) ok = false;
-        }
-        if (!ok) {
-            r.type = bs::kTileExact;
-            continue;
-        }
-        for (int l = 0; l < r.n_layers; ++l) {
-            we[r.cam[l]] = std::max(we[r.cam[l]], twe[l]);
-            bh[r.cam[l]] = std::max(bh[r.cam[l]], tbh[l]);
-        }
-    }
-    int stage = 0;
-    for (int c = 0; c < n_cams; ++c) {
-        if (we[c] * 4 * bh[c] > kStageBytesMax) {
-            for (int t = 0; t < n_tiles; ++t) {
-                bs::TileRec &r = g_static_recs[t];
-                if (r.type != bs::kTileFast) continue;
-                for (int l = 0; l < r.n_layers; ++l)
-                    if (r.cam[l] == c) r.type = bs::kTileExact;
-            }
-            we[c] = bh[c] = 0;
-        }
-        stage = std::max(stage, we[c] * 4 * bh[c]);
-    }
-    const int stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
-    int n_ordered = 0, n_fast = 0;
-    for (int t = 0; t < n_tiles; ++t)
-        if (g_static_recs[t].type == bs::kTileExact) g_static_ordered[n_ordered++] = g_static_recs[t];
-    for (int layers = bs::kMaxLayers; layers >= 1; --layers)
-        for (int t = 0; t < n_tiles; ++t)
-            if (g_static_recs[t].type == bs::kTileFast && g_static_recs[t].n_layers == layers)
-                g_static_ordered[n_ordered++] = g_static_recs[t], ++n_fast;
-    for (int t = 0; t < n_tiles; ++t)
-        if (g_static_recs[t].type == bs::kTileEmpty) g_static_ordered[n_ordered++] = g_static_recs[t];
-
-    const int smem_bytes = bs::kStages * stage_bytes + bs::kConsumerWarps * bs::kWarpOutBytes + 2 * bs::kLutBytes +
-                           bs::kStages * bs::kMetaBytes + 64;
-    bool fast = n_fast > 0 && get_encoder() && smem_bytes <= st->smem_optin && aligned16(d_canvas, canvas_pitch);
+    // ---- size one TMA box per camera, flatten to work items, split them over the grid's warps -------
+    PlanLayout L;
+    layout_plan(g_static_recs, n_blocks, n_cams, g_static_items, &L);
+    bool fast = L.n_fast > 0 && get_encoder() && L.smem_bytes <= st->smem_optin && aligned16(d_canvas, canvas_pitch);
     for (int i = 0; fast && i < n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
     int per_sm = 0;
     if (fast) {
         BS_CUDA(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kFastThreads,
-                                                                       smem_bytes));
+                                                                       L.smem_bytes));
         fast = per_sm >= 1;
     }
 
@@ -934,34 +940,37 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     A.keep_canvas = keep ? 1 : 0;
 
     if (!fast) {
-        // no staged tiles (or unaligned buffers): the per-pixel kernel needs no scratch at all
+        // no staged blocks (or unaligned buffers): the per-pixel kernel needs no scratch at all
         dim3 grid((canvas_w + bs::kExactTileW - 1) / bs::kExactTileW, (canvas_h + bs::kExactTileH - 1) / bs::kExactTileH);
         bs::stitch_exact_kernel<<<grid, dim3(32, bs::kExactTileH), 0, s>>>(A);
         BS_CUDA(nullptr, cudaGetLastError());
+        BS_CUDA(nullptr, cudaStreamSynchronize(s));
         return BS_OK;
     }
 
     for (int i = 0; i < n_cams; ++i) {
-        FA.box_we[i] = we[i];
-        FA.box_h[i] = bh[i];
-        if (we[i] > 0) {
-            const int er = encode_frame_map(&FA.tmap[i], d_frames[i], pitch[i], src_h[i], we[i], bh[i]);
+        FA.pitch[i] = L.box_we[i] * 4;
+        FA.box_bytes[i] = L.box_we[i] * 4 * L.box_h[i];
+        if (L.box_we[i] > 0) {
+            const int er = encode_frame_map(&FA.tmap[i], d_frames[i], pitch[i], src_h[i], L.box_we[i], L.box_h[i]);
             if (er != 0) return fail(nullptr, BS_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d) for camera %d", me, er, i);
         }
     }
-    const int grid = std::min(n_tiles, per_sm * st->sms);
-    // the ordered plan replaces the raw one in the scratch, and the scheduler is re-armed: both are
-    // stream-ordered after the previous call's kernels on this stream
-    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->tiles, g_static_ordered, plan_bytes, cudaMemcpyHostToDevice, s));
-    static_sched_arm<<<1, 1, 0, s>>>(st->scratch->sched, (unsigned)grid);
+    int grid = std::max(1, std::min((L.n_items + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
+    grid = std::min(grid, (kStaticMaxWarps - 1) / bs::kWarpsPerCta);
+    const int n_warps = grid * bs::kWarpsPerCta;
+    split_items(g_static_items, L.n_items, n_warps, g_static_warp_start);
+    // the item list replaces the raw records in the scratch; stream-ordered after the previous call's kernels
+    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_items, sizeof(bs::WorkItem) * (size_t)L.n_items,
+                                     cudaMemcpyHostToDevice, s));
+    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->warp_start, g_static_warp_start, sizeof(int) * (size_t)(n_warps + 1),
+                                     cudaMemcpyHostToDevice, s));
+    FA.items = reinterpret_cast<const bs::WorkItem *>(st->scratch->plan);
+    FA.warp_start = st->scratch->warp_start;
+    FA.stage_bytes = L.stage_bytes;
+    bs::stitch_fast_kernel<<<grid, bs::kFastThreads, L.smem_bytes, s>>>(FA);
     BS_CUDA(nullptr, cudaGetLastError());
-    FA.tiles = st->scratch->tiles;
-    FA.n_tiles = n_tiles;
-    FA.stage_bytes = stage_bytes;
-    FA.sched = st->scratch->sched;
-    bs::stitch_fast_kernel<<<grid, bs::kFastThreads, smem_bytes, s>>>(FA);
-    BS_CUDA(nullptr, cudaGetLastError());
-    // the host staging arrays are reused by the next call: the copy above must have left them
+    // the host staging arrays are reused by the next call: everything queued above must have left them
     BS_CUDA(nullptr, cudaStreamSynchronize(s));
     return BS_OK;
 }

@@ -1,15 +1,19 @@
-// stitch_fast.cuh -- the per-frame kernel: one persistent CTA loop over the planned tiles.
+// stitch_fast.cuh -- the per-frame kernel: every warp is an independent worker on 32x16 blocks.
 //
-// For a FAST tile and each of its cameras (lowest index first, so later cameras overwrite
-// earlier ones exactly as the reference's loop does, /root/reference/tools/stitch/main.cpp:145-152):
-//   1. the camera's source bounding box is prefetched into shared memory by one TMA tensor copy
-//      (cp.async.bulk.tensor.2d, mbarrier-signalled, double buffered across tiles);
-//   2. each thread computes two runs of 8 canvas pixels: coordinates from the plan-verified fp32
-//      recurrence (or exact fp64 where the plan says so), 2x3 aligned words per pixel from the
-//      staged box, OpenCV's fixed-point bilinear weights from a 1024-entry table, three
-//      channel dot products (dp4a) -- bit-identical to (sum w*S + 2^14) >> 15;
-//   3. the finished 128x32 tile goes from shared memory to the canvas as 16-byte vector stores.
-// EXACT tiles run the per-pixel fp64 path of stitch_exact.cuh; EMPTY tiles are zero-filled.
+// Each warp owns a contiguous range of the plan's work items (one item = one canvas block and one
+// camera layer; a block's layers are adjacent, lowest camera first, so later cameras overwrite
+// earlier ones exactly as the reference's loop does, /root/reference/tools/stitch/main.cpp:145-152).
+// For every item the warp
+//   1. prefetches, two items ahead, the camera's source bounding box into its own shared-memory
+//      stage with one TMA tensor copy (cp.async.bulk.tensor.2d) signalled on its own mbarrier --
+//      lane 0 is the producer, nothing is shared with other warps, so no warp ever waits for one;
+//   2. computes one vertical run of 16 canvas pixels per lane: coordinates from the plan-verified
+//      fp32 recurrence (or exact fp64 where the plan says so), 2x3 aligned words per pixel from the
+//      staged box, OpenCV's fixed-point bilinear weights from a 1024-entry table, three channel dot
+//      products (dp4a) -- bit-identical to (sum w*S + 2^14) >> 15;
+//   3. after the block's last layer, writes the finished 16x96-byte block to the canvas as 16-byte
+//      vector stores.
+// EXACT blocks run the per-pixel fp64 path of stitch_exact.cuh; EMPTY blocks are zero-filled.
 #pragma once
 
 #include <cuda.h>   // CUtensorMap (type only; the encoder is fetched at run time)
@@ -19,19 +23,17 @@
 
 namespace bs {
 
-constexpr int kOutTileBytes = kTileW * kTileH * 3;   // 12288
 constexpr int kLutBytes = 1024 * 8;
 constexpr int kStagePad = 128;                       // slack behind a stage for the 3rd word of the last texel
 
 struct FastArgs {
     FrameArgs F;
     CUtensorMap tmap[kMaxCamsPerLaunch];   // source frame of camera i as a [h][pitch/4] u32 tensor
-    const TileRec *tiles;
-    int n_tiles;
-    int box_we[kMaxCamsPerLaunch];         // TMA box of camera i: width in 4-byte elements, rows
-    int box_h[kMaxCamsPerLaunch];
+    const WorkItem *items;                 // the plan, flattened
+    const int *warp_start;                 // n_warps + 1 entries: item range of every warp of the grid
+    int pitch[kMaxCamsPerLaunch];          // TMA box of camera i: row pitch in shared memory (bytes) ...
+    int box_bytes[kMaxCamsPerLaunch];      // ... and total bytes (= what the mbarrier expects)
     int stage_bytes;                       // shared memory per stage (multiple of 128)
-    unsigned *sched;                       // [0] next tile to hand out, [1] CTAs that ran dry (self-resetting)
 };
 
 // First 4-byte element of the staged box for a bounding box whose first texel column is bx0.
@@ -176,22 +178,21 @@ __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, 
 }
 
 // ---- work decomposition ------------------------------------------------------------------------
-// A CTA is 8 consumer warps + 1 producer warp.  A 128x32 tile is 8 blocks of 32 columns x 16 rows;
-// consumer warp w owns block (w & 3, w >> 2) of every tile its CTA processes: lane = column, one
-// vertical run of kRun pixels per lane.  The warps never meet at a CTA barrier: the producer feeds
-// source boxes through a ring of kStages stages guarded by full/empty mbarriers, and every warp
-// composites into, and flushes, its own 16 x 96-byte output block.
-constexpr int kConsumerWarps = kBlocksPerTile;
-constexpr int kFastThreads = 32 * (kConsumerWarps + 1);
+constexpr int kWarpsPerCta = 8;
+constexpr int kFastThreads = 32 * kWarpsPerCta;
 #ifndef BS_MIN_CTAS
 #define BS_MIN_CTAS 2
 #endif
-#ifndef BS_STAGES
-#define BS_STAGES 3
-#endif
-constexpr int kStages = BS_STAGES;
+constexpr int kStages = 3;                             // per warp: source boxes of items i, i+1, i+2
+constexpr int kRecSlots = 4;                           // per warp: records of items i .. i+3
 constexpr int kBlockRowBytes = 96;                     // 32 pixels
 constexpr int kWarpOutBytes = kRun * kBlockRowBytes;   // 1536
+constexpr int kWarpCtlBytes = kRecSlots * 16 + (kStages + kRecSlots) * 8 + 8;   // records + mbarriers (128)
+
+__host__ __device__ constexpr int warp_smem_bytes(int stage_bytes)
+{
+    return kStages * stage_bytes + kWarpOutBytes + kWarpCtlBytes;
+}
 
 // Hot path: the layer covers every pixel of the block with interior samples, the tile lies inside
 // the canvas and the plan verified the cheap coordinates for the whole block.  No coverage tests,
@@ -264,16 +265,6 @@ __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &
     }
 }
 
-// What the producer publishes with every ring slot: everything a consumer needs to know about the
-// item, so consumers never wait on plan records in global memory.
-//   word 0  tx | ty << 16
-//   word 1  type | last_layer << 8 | all_mask << 16 | skip_mask << 24
-//   word 2  camera
-//   word 3  by0 * pitch + 4 * box_elem0(bx0): stage offset of the box origin texel
-//   word 4  exact_mask
-//   word 5  stage row pitch in bytes
-constexpr int kMetaBytes = 32;
-
 __device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity)
 {
     asm volatile(
@@ -321,185 +312,138 @@ __device__ __noinline__ void store_block_checked(const FrameArgs &F, uint32_t sr
 __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(const __grid_constant__ FastArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    // layout: [pad to an 8 KB boundary][weight table 8 KB][kStages stages][8 output blocks][meta][barriers]
+    // layout: [pad to an 8 KB boundary][weight table 8 KB][per warp: kStages stages | output block | records | mbarriers]
     const uint32_t raw_base = smem_u32(smem_raw);
     const uint32_t lut_base = (raw_base + 8191u) & ~8191u;
-    const uint32_t stage0 = lut_base + kLutBytes;                                // 8 KB aligned
-    const uint32_t out0 = stage0 + (uint32_t)(kStages * A.stage_bytes);          // 8 private output blocks
-    const uint32_t meta0 = out0 + kConsumerWarps * kWarpOutBytes;
-    const uint32_t full0 = meta0 + kStages * kMetaBytes;
-    const uint32_t empty0 = full0 + kStages * 8;
-    uint8_t *const gen0 = smem_raw + (lut_base - raw_base);                      // generic pointer to the table
-
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
+    const uint32_t wbase = lut_base + kLutBytes + (uint32_t)(warp * warp_smem_bytes(A.stage_bytes));
+    const uint32_t stage0 = wbase;                                             // 128-byte aligned
+    const uint32_t out_blk = stage0 + (uint32_t)(kStages * A.stage_bytes);
+    const uint32_t rec0 = out_blk + kWarpOutBytes;
+    const uint32_t dbar0 = rec0 + kRecSlots * 16;                              // data barriers, one per stage
+    const uint32_t rbar0 = dbar0 + kStages * 8;                                // record barriers, one per slot
+
     // Programmatic dependent launch: let the next frame's kernel start filling SMs as this one's CTAs
-    // retire.  It may prefetch and composite its first tile, but touches the canvas and the tile
-    // scheduler only after griddepcontrol.wait, i.e. after this grid has completed.
+    // retire.  It may prefetch and composite, but touches the canvas only after griddepcontrol.wait,
+    // i.e. after this grid has completed.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     {
-        uint2 *lut = reinterpret_cast<uint2 *>(gen0);
+        uint2 *lut = reinterpret_cast<uint2 *>(smem_raw + (lut_base - raw_base));
         for (int i = tid; i < 1024; i += kFastThreads) lut[i] = lut_entry(i);
     }
-    if (tid == 0) {
-        for (int s = 0; s < kStages; ++s) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(1));
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty0 + 8 * s), "r"(kConsumerWarps));
-        }
+    if (lane == 0) {
+        for (int s = 0; s < kStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dbar0 + 8 * s), "r"(1));
+        for (int s = 0; s < kRecSlots; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    if (warp == kConsumerWarps) {
-        // ===== producer: one lane walks the tiles of this CTA and keeps the ring full ===============
-        // Every tile becomes one ring item per layer (FAST) or a single descriptor-only item.
-        if (lane == 0) {
-            uint32_t slot = 0, phase = 1;    // a fresh mbarrier passes a wait on parity 1
-            // The first tile of a CTA is static (its index is the CTA's), the rest are handed out
-            // dynamically, heaviest first in the plan's order, so there is no tail imbalance.  The
-            // counter may still belong to the previous launch until that grid has completed.
-            bool prior_grid_done = false;
-            for (int k = (int)blockIdx.x; k < A.n_tiles;) {
-                const uint4 *rp = reinterpret_cast<const uint4 *>(&A.tiles[k]);
-                TileRec r;
-                {
-                    uint4 *dst = reinterpret_cast<uint4 *>(&r);
-#pragma unroll
-                    for (int q = 0; q < (int)(sizeof(TileRec) / 16); ++q) dst[q] = __ldg(rp + q);
-                }
-                const bool fast = (r.type == kTileFast) && !(A.F.keep_canvas && r.has_uncovered);
-                const int n_items = fast ? r.n_layers : 1;
-                uint32_t higher_all = 0;     // blocks fully written by a later (higher) layer
-                uint32_t skip[kMaxLayers];
-                if (fast)
-                    for (int l = n_items - 1; l >= 0; --l) {
-                        skip[l] = (uint32_t)r.none_mask[l] | higher_all;
-                        higher_all |= r.all_mask[l];
-                    }
-                for (int l = 0; l < n_items; ++l) {
-                    mbar_wait_addr(empty0 + 8 * slot, phase);   // all 8 warps released the slot
-                    uint32_t kind, cam = 0, origin_off = 0, exact_mask = 0, pitch = 0;
-                    if (fast) {
-                        cam = r.cam[l];
-                        pitch = (uint32_t)(A.box_we[cam] * 4);
-                        kind = (uint32_t)kTileFast | ((l == n_items - 1) ? 1u << 8 : 0u) | ((uint32_t)r.all_mask[l] << 16) |
-                               (skip[l] << 24);
-                        origin_off = (uint32_t)((int)r.by0[l] * (int)pitch + 4 * box_elem0((int)r.bx0[l]));
-                        exact_mask = r.exact_mask[l];
-                    } else {
-                        kind = (uint32_t)(r.type == kTileFast ? kTileExact : r.type) | (1u << 8);
-                    }
-                    const uint32_t ma = meta0 + kMetaBytes * slot;
-                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(ma),
-                                 "r"((uint32_t)r.tx | ((uint32_t)r.ty << 16)), "r"(kind), "r"(cam), "r"(origin_off)
-                                 : "memory");
-                    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(ma + 16), "r"(exact_mask), "r"(pitch) : "memory");
-                    if (fast) {
-                        // arrive has release semantics: the meta words are visible to whoever sees the phase flip
-                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full0 + 8 * slot),
-                                     "r"((uint32_t)(A.box_we[cam] * 4 * A.box_h[cam]))
-                                     : "memory");
-                        asm volatile(
-                            "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
-                                stage0 + slot * (uint32_t)A.stage_bytes),
-                            "l"(&A.tmap[cam]), "r"(box_elem0((int)r.bx0[l])), "r"((int)r.by0[l]), "r"(full0 + 8 * slot)
-                            : "memory");
-                    } else {
-                        mbar_arrive_addr(full0 + 8 * slot);
-                    }
-                    if (++slot == kStages) {
-                        slot = 0;
-                        phase ^= 1u;
-                    }
-                }
-                if (!prior_grid_done) {
-                    asm volatile("griddepcontrol.wait;" ::: "memory");
-                    prior_grid_done = true;
-                }
-                k = (int)atomicAdd(&A.sched[0], 1u);
-            }
-            if (!prior_grid_done) asm volatile("griddepcontrol.wait;" ::: "memory");
-            // out of tiles: tell the consumers to stop, and let the last CTA re-arm the scheduler
-            mbar_wait_addr(empty0 + 8 * slot, phase);
-            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(meta0 + kMetaBytes * slot), "r"(0u), "r"(0xFFu),
-                         "r"(0u), "r"(0u)
-                         : "memory");
-            mbar_arrive_addr(full0 + 8 * slot);
-            if (atomicInc(&A.sched[1], gridDim.x - 1) == gridDim.x - 1) atomicExch(&A.sched[0], gridDim.x);
-        }
-        return;
-    }
+    const int gw = blockIdx.x * kWarpsPerCta + warp;
+    const int i0 = A.warp_start[gw], i1 = A.warp_start[gw + 1];
+    if (i0 >= i1) return;
 
-    // ===== consumers ====================================================================================
-    const uint32_t out_blk = out0 + (uint32_t)(warp * kWarpOutBytes);
-    const int bx = (warp & 3) * 32, by = (warp >> 2) * kRun;      // block origin inside a tile
-    uint32_t slot = 0, phase = 0;
+    // lane 0 is this warp's producer ------------------------------------------------------------------
+    // record of item i -> record slot, by a 16-byte bulk copy
+    auto request_record = [&](int i, uint32_t slot) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * slot), "r"(16u) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         rec0 + 16 * slot),
+                     "l"(A.items + i), "r"(16u), "r"(rbar0 + 8 * slot)
+                     : "memory");
+    };
+    // source box of the item whose record sits in `slot` -> stage; items without a box just arrive
+    auto issue_box = [&](uint32_t slot, uint32_t rec_parity, uint32_t stage) {
+        mbar_wait_addr(rbar0 + 8 * slot, rec_parity);
+        const uint4 r = lds128(rec0 + 16 * slot);
+        if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
+            const uint32_t cam = (r.y >> 16) & 0xFFu;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
+                         "r"((uint32_t)A.box_bytes[cam])
+                         : "memory");
+            asm volatile(
+                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                    stage0 + stage * (uint32_t)A.stage_bytes),
+                "l"(&A.tmap[cam]), "r"((int)(int16_t)(r.z & 0xFFFFu)), "r"((int)(int16_t)(r.z >> 16)), "r"(dbar0 + 8 * stage)
+                : "memory");
+        } else {
+            mbar_arrive_addr(dbar0 + 8 * stage);
+        }
+    };
+    if (lane == 0) {
+        for (int d = 0; d < 3 && i0 + d < i1; ++d) request_record(i0 + d, (uint32_t)d);
+        issue_box(0u, 0u, 0u);
+        if (i0 + 1 < i1) issue_box(1u, 0u, 1u);
+    }
+    __syncwarp();
+
     bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
-    for (;;) {
-        bool wrote = false, last;
-        do {
-            mbar_wait_addr(full0 + 8 * slot, phase);
-            const uint4 m0 = lds128(meta0 + kMetaBytes * slot);
-            const int tx0 = (int)(m0.x & 0xFFFFu) * kTileW + bx, ty0 = (int)(m0.x >> 16) * kTileH + by;
-            const int type = (int)(m0.y & 0xFFu);
-            if (type == 0xFF) return;          // the producer ran out of tiles
-            last = (m0.y >> 8) & 1u;
-            if (type == kTileFast) {
-                if (!((m0.y >> (24 + warp)) & 1u)) {          // this layer writes into this block
-                    const uint2 m1 = lds64(meta0 + kMetaBytes * slot + 16);
-                    const CamDev &cam = A.F.cam[m0.z];
-                    const int pitch = (int)m1.y;
-                    const bool full = (m0.y >> (16 + warp)) & 1u;
-                    const uint32_t group_mask = (m1.x >> (warp * 4)) & 15u;   // this block's 4 row groups
-                    // shared address texel (0, 0) of this camera would have, were the whole frame staged
-                    const uint32_t stage_origin = stage0 + slot * (uint32_t)A.stage_bytes - m0.w;
-                    if (full && group_mask == 0u)
-                        run_layer_full(cam, pitch, stage_origin, lut_base, out_blk, tx0 + lane, ty0 + kRun / 2, lane);
-                    else
-                        run_layer_general(A, cam, pitch, stage_origin, lut_base, out_blk, group_mask, full, !wrote,
-                                          tx0 + lane, ty0, lane);
-                    wrote = true;
-                }
-                __syncwarp();
-                if (lane == 0) mbar_arrive_addr(empty0 + 8 * slot);    // this warp is done with the slot
-                if (last) {
-                    if (!prior_grid_done) {
-                        asm volatile("griddepcontrol.wait;" ::: "memory");
-                        prior_grid_done = true;
-                    }
-                    if (!wrote) {
-                        if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);   // nobody wrote here
-                    } else if (tx0 + 32 <= A.F.W && ty0 + kRun <= A.F.H) {
-                        // flush: lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
-                        const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
-                        uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch +
-                                            (long long)tx0 * 3 + (lane & 1) * 16;
+    bool wrote = false;               // some layer has written into the current block
+    uint32_t stage = 0, dpar = 0;     // stage and data-barrier parity of the current item
+    uint32_t slot = 0, rpar = 0;      // record slot and record-barrier parity of the current item
+    uint32_t pstage = 2, pslot = 2, ppar = 0;   // producer cursor: item i+2 (its stage, record slot, record parity)
+    for (int i = i0; i < i1; ++i) {
+        mbar_wait_addr(rbar0 + 8 * slot, rpar);
+        const uint4 r = lds128(rec0 + 16 * slot);
+        const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
+        const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
+        mbar_wait_addr(dbar0 + 8 * stage, dpar);
+        if (type == (uint32_t)kBlockFast) {
+            const uint32_t c = (r.y >> 16) & 0xFFu;
+            const CamDev &cam = A.F.cam[c];
+            const int pitch = A.pitch[c];
+            // shared address texel (0, 0) of this camera would have, were the whole frame staged
+            const uint32_t stage_origin = stage0 + stage * (uint32_t)A.stage_bytes - r.w;
+            const uint32_t groups = (r.y >> 24) & 0xFFu;
+            const bool full = (flags & kItemFull) != 0;
+            if (full && groups == 0u)
+                run_layer_full(cam, pitch, stage_origin, lut_base, out_blk, tx0 + lane, ty0 + kRun / 2, lane);
+            else
+                run_layer_general(A, cam, pitch, stage_origin, lut_base, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
+            wrote = true;
+        }
+        __syncwarp();                 // every lane is done with this item's stage and record
+        if (lane == 0) {
+            // refill: the box of item i+2 goes into the stage of item i-1, the record of item i+3 into
+            // the slot of item i-1 (both consumed one iteration ago)
+            if (i + 2 < i1) issue_box(pslot, ppar, pstage);
+            if (i + 3 < i1) request_record(i + 3, (pslot + 1) & (kRecSlots - 1));
+        }
+        if (++pstage == kStages) pstage = 0;
+        if (++pslot == kRecSlots) {
+            pslot = 0;
+            ppar ^= 1u;
+        }
+        if (flags & kItemLast) {
+            if (!prior_grid_done) {
+                asm volatile("griddepcontrol.wait;" ::: "memory");
+                prior_grid_done = true;
+            }
+            if (type == (uint32_t)kBlockExact) {
+                // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j
+                for (int j = 0; j < kRun / 4; ++j) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+            } else if (!wrote) {
+                if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);   // nobody writes here
+            } else if (tx0 + kBlockW <= A.F.W && ty0 + kRun <= A.F.H) {
+                // flush: lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
+                const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
+                uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch + (long long)tx0 * 3 + (lane & 1) * 16;
 #pragma unroll
-                        for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4 *>(gp + 32 * j) = lds128(so + 32u * j);
-                    } else {
-                        store_block_checked(A.F, out_blk, tx0, ty0, lane);
-                    }
-                    __syncwarp();   // the block is free again
-                }
+                for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4 *>(gp + 32 * j) = lds128(so + 32u * j);
             } else {
-                __syncwarp();
-                if (lane == 0) mbar_arrive_addr(empty0 + 8 * slot);
-                if (!prior_grid_done) {
-                    asm volatile("griddepcontrol.wait;" ::: "memory");
-                    prior_grid_done = true;
-                }
-                if (type == kTileEmpty) {
-                    if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);
-                } else {
-                    // exact block: lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j
-                    for (int j = 0; j < kRun / 4; ++j) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
-                }
+                store_block_checked(A.F, out_blk, tx0, ty0, lane);
             }
-            if (++slot == kStages) {
-                slot = 0;
-                phase ^= 1u;
-            }
-        } while (!last);
+            wrote = false;
+            __syncwarp();             // the output block is free again
+        }
+        if (++stage == kStages) {
+            stage = 0;
+            dpar ^= 1u;
+        }
+        if (++slot == kRecSlots) {
+            slot = 0;
+            rpar ^= 1u;
+        }
     }
 }
 

@@ -1,48 +1,60 @@
-// stitch_plan.cuh -- the tile plan: static per calibration, built once on the device.
+// stitch_plan.cuh -- the block plan: static per calibration, built once on the device.
 //
 // The reference recomputes everything per frame (cv::warpPerspective regenerates the coordinate
 // maps on every call, /root/reference/tools/stitch/main.cpp:150-151), but H and result_size are
-// fixed for the whole run (:53-73).  The plan classifies every 128x32 canvas tile once:
+// fixed for the whole run (:53-73).  The plan classifies every 32x16 canvas block once:
 //   EMPTY  no camera writes any pixel                      -> zero fill
-//   FAST   every written pixel is an interior (4-tap) pixel of one of <= 4 cameras whose source
+//   FAST   every written pixel is an interior (4-tap) pixel of one of <= 2 cameras whose source
 //          bounding boxes fit a shared-memory stage        -> staged kernel, one pass per camera
-//   EXACT  anything else (last-row/column pixels, too many cameras, huge boxes) -> per-pixel kernel
-// and, for FAST tiles, proves by exhaustive comparison which 8-pixel runs may use the cheap
-// fp32 coordinate recurrence (fast_run_coords) instead of the exact fp64 form.
+//   EXACT  anything else (last-row/column pixels, three or more cameras, huge boxes)
+//                                                            -> per-pixel fp64 path
+// and, for FAST blocks, proves by exhaustive comparison which 32x4 pixel groups may use the cheap
+// fp32 coordinate recurrence (run_coord_bits) instead of the exact fp64 form.
 #pragma once
 
 #include "stitch_common.cuh"
 
 namespace bs {
 
-constexpr int kTileW = 128;
-#ifndef BS_BLOCKS_PER_TILE
-#define BS_BLOCKS_PER_TILE 8
-#endif
-constexpr int kBlocksPerTile = BS_BLOCKS_PER_TILE;   // 32x16 blocks per tile = consumer warps per CTA (4: one row of blocks)
-constexpr int kThreads = 32 * kBlocksPerTile;
-constexpr int kRun = 16;           // vertical run: consecutive rows per thread
-constexpr int kTileH = kRun * (kBlocksPerTile / 4);
-constexpr int kMaxLayers = 4;      // cameras that may share one FAST tile
+constexpr int kBlockW = 32;        // one warp: lane = canvas column
+constexpr int kRun = 16;           // vertical run: consecutive canvas rows per lane = block height
+constexpr int kBlockH = kRun;
+constexpr int kMaxLayers = 2;      // cameras that may share one FAST block
 constexpr int kMaxPlanCams = 64;
+constexpr int kPlanWarps = 8;      // blocks per CTA of the plan kernel
 
-enum TileType : uint8_t { kTileEmpty = 0, kTileFast = 1, kTileExact = 2 };
+enum BlockType : uint8_t { kBlockEmpty = 0, kBlockFast = 1, kBlockExact = 2 };
 
-struct TileRec {                   // 80 bytes, read by the producer as five 16-byte loads
-    uint16_t tx, ty;               // tile coordinates
-    uint8_t type;                  // TileType
+// Raw output of the plan kernel, one per block (read back by the host).
+struct BlockRec {                  // 32 bytes
+    uint16_t bx, by;               // block coordinates (units of 32 x 16 pixels)
+    uint8_t type;                  // BlockType
     uint8_t n_layers;
-    uint8_t has_uncovered;         // some in-canvas pixel of the tile is written by no layer
+    uint8_t has_uncovered;         // some in-canvas pixel of the block is written by no camera
     uint8_t reserved;
-    uint8_t cam[kMaxLayers];       // ascending camera index = compositing order
-    // per layer, bit w = 32x16 block w of the tile (block w belongs to warp w of the kernels):
-    uint8_t all_mask[kMaxLayers];  //   the block lies inside the canvas and the layer writes every pixel of it
-    uint8_t none_mask[kMaxLayers]; //   the layer writes no pixel of the block
-    int16_t bx0[kMaxLayers], by0[kMaxLayers], bx1[kMaxLayers], by1[kMaxLayers];  // texel bbox incl. taps
-    uint32_t exact_mask[kMaxLayers];   // bit (w*4 + row group): those 32x4 pixels must use exact coords
-    uint32_t pad[3];
+    struct Layer {                 // ascending camera index = compositing order
+        int16_t x0, y0, x1, y1;    // source bounding box (texels, taps included) of the pixels it writes
+        uint8_t cam;
+        uint8_t full;              // writes every pixel of the block and the block lies inside the canvas
+        uint8_t groups;            // bit g: rows 4g..4g+3 of the block must use exact coordinates
+        uint8_t pad;
+    } layer[kMaxLayers];
 };
-static_assert(sizeof(TileRec) == 80, "TileRec layout");
+static_assert(sizeof(BlockRec) == 32, "BlockRec layout");
+
+// What the frame kernel consumes: one item per (block, camera layer), 16 bytes, a block's items
+// adjacent and in compositing order.  EXACT and EMPTY blocks are single items.
+struct WorkItem {
+    uint16_t bx, by;
+    uint8_t type;                  // BlockType
+    uint8_t flags;                 // kItem* bits
+    uint8_t cam;
+    uint8_t groups;                // bit g: rows 4g..4g+3 must use exact coordinates
+    int16_t c0, y0;                // TMA coordinates of the source box: first 4-byte element, first row
+    uint32_t origin_off;           // y0 * stage pitch + 4 * c0: offset of the box origin from texel (0, 0)
+};
+static_assert(sizeof(WorkItem) == 16, "WorkItem layout");
+constexpr uint8_t kItemFirst = 1, kItemLast = 2, kItemFull = 4;
 
 // ---- cheap coordinates for a vertical run of kRun pixels (one canvas column) -----------------
 // Along a column the source coordinate is fX(yc + j) = fXc + j (32 M1 - M7 fXc) / (Wc + j M7),
@@ -112,24 +124,16 @@ __device__ __forceinline__ void run_coord_bits(const RunAnchor &a, float jf, int
     ybits = __float_as_int(__fadd_rn(sY, 12582912.0f));
 }
 
-// thread -> pixels of a tile, shared by the plan and the staged kernel: thread t owns column
-// (t & 127) and the kRun rows starting at kRun * (t >> 7).  A warp is 32 adjacent columns, so its
-// shared-memory gathers touch one contiguous span per source row (no bank conflicts).
-__device__ __forceinline__ int tile_col(int tid) { return tid & (kTileW - 1); }
-__device__ __forceinline__ int tile_row0(int tid) { return (tid >> 7) * kRun; }
-// bit of TileRec::exact_mask covering row k of thread tid's run: (warp, group of 4 rows)
-__device__ __forceinline__ int exact_bit(int tid, int k) { return (tid >> 5) * 4 + (k >> 2); }
-// (warp w of the plan kernel covers the same 32x16 block as consumer warp w of the frame kernel)
-
 struct PlanArgs {
     double M[kMaxPlanCams][9];
     int w[kMaxPlanCams], h[kMaxPlanCams];
     int n_cams;
     int W, H;
-    int block_w;
+    int block_w;                   // OpenCV's coordinate block width (not ours)
     int legacy_border;
-    int tiles_x, tiles_y;
-    TileRec *out;
+    int keep_canvas;               // blocks with uncovered pixels then need the read-modify-write path
+    int blocks_x, blocks_y;
+    BlockRec *out;                 // blocks_y * blocks_x records, row-major
 };
 
 // 0 = not written, 1 = interior (Appendix A.3), 2 = written by the last-row/column rule (A.4)
@@ -141,37 +145,20 @@ __device__ __forceinline__ int cover_class(int X, int Y, int w, int h, int legac
     return legacy ? 0 : 2;
 }
 
-// One CTA per tile.
-__global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ PlanArgs P)
+// One warp per block: lane = column, kRun rows per lane, exactly the frame kernel's mapping.
+__global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_constant__ PlanArgs P)
 {
-    __shared__ unsigned long long s_win;       // cameras that win at least one pixel
-    __shared__ int s_edge_win, s_uncovered;
-    __shared__ int s_bx0[kMaxLayers], s_by0[kMaxLayers], s_bx1[kMaxLayers], s_by1[kMaxLayers];
-    __shared__ unsigned s_all[kMaxLayers], s_none[kMaxLayers];
-    __shared__ unsigned s_exact[kMaxLayers];
-
-    const int tid = threadIdx.x;
-    const int tx = blockIdx.x, ty = blockIdx.y;
-    if (tid == 0) {
-        s_win = 0ull;
-        s_edge_win = 0;
-        s_uncovered = 0;
-    }
-    if (tid < kMaxLayers) {
-        s_bx0[tid] = s_by0[tid] = INT_MAX;
-        s_bx1[tid] = s_by1[tid] = INT_MIN;
-        s_all[tid] = 0u;
-        s_none[tid] = 0u;
-        s_exact[tid] = 0u;
-    }
-    __syncthreads();
-
-    const int x = tx * kTileW + tile_col(tid);
-    const int y0 = ty * kTileH + tile_row0(tid);
+    const int lane = threadIdx.x & 31;
+    const int bx = blockIdx.x * kPlanWarps + (threadIdx.x >> 5), by = blockIdx.y;
+    if (bx >= P.blocks_x) return;
+    const unsigned FULLMASK = 0xffffffffu;
+    const int x = bx * kBlockW + lane;
+    const int y0 = by * kBlockH;
     const int xb = (x / P.block_w) * P.block_w;
-    // ---- phase 1: who wins each pixel -----------------------------------------------------
-    unsigned long long my_win = 0ull;
-    int my_edge = 0, my_unc = 0;
+
+    // ---- phase 1: who wins each pixel (highest camera index that writes it, Appendix A.5) -----
+    unsigned win_lo = 0u, win_hi = 0u;
+    bool edge = false, unc = false;
     if (x < P.W) {
         for (int k = 0; k < kRun; ++k) {
             const int y = y0 + k;
@@ -183,49 +170,45 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
                 cls = cover_class(X, Y, P.w[i], P.h[i], P.legacy_border);
                 if (cls) break;
             }
-            if (cls == 0) my_unc = 1;
+            if (cls == 0) unc = true;
             else {
-                my_win |= 1ull << i;
-                if (cls == 2) my_edge = 1;
+                if (i < 32) win_lo |= 1u << i;
+                else win_hi |= 1u << (i - 32);
+                if (cls == 2) edge = true;
             }
         }
     }
-    if (my_win) atomicOr(&s_win, my_win);
-    if (my_edge) atomicOr(&s_edge_win, 1);
-    if (my_unc) atomicOr(&s_uncovered, 1);
-    __syncthreads();
+    win_lo = __reduce_or_sync(FULLMASK, win_lo);
+    win_hi = __reduce_or_sync(FULLMASK, win_hi);
+    edge = __any_sync(FULLMASK, edge);
+    unc = __any_sync(FULLMASK, unc);
 
-    TileRec rec;
+    BlockRec rec;
     memset(&rec, 0, sizeof rec);
-    rec.tx = (uint16_t)tx;
-    rec.ty = (uint16_t)ty;
-    const unsigned long long win = s_win;
-    const int n_layers = __popcll(win);
-    rec.has_uncovered = (uint8_t)s_uncovered;
-    TileRec *dst = P.out + (size_t)ty * P.tiles_x + tx;
+    rec.bx = (uint16_t)bx;
+    rec.by = (uint16_t)by;
+    rec.has_uncovered = unc ? 1 : 0;
+    BlockRec *dst = P.out + (size_t)by * P.blocks_x + bx;
+    const int n_layers = __popc(win_lo) + __popc(win_hi);
     if (n_layers == 0) {
-        rec.type = kTileEmpty;
-        if (tid == 0) *dst = rec;
+        rec.type = kBlockEmpty;
+        if (lane == 0) *dst = rec;
         return;
     }
-    if (n_layers > kMaxLayers || s_edge_win) {
-        rec.type = kTileExact;
-        if (tid == 0) *dst = rec;
+    if (n_layers > kMaxLayers || edge || (P.keep_canvas && unc)) {
+        rec.type = kBlockExact;
+        if (lane == 0) *dst = rec;
         return;
     }
-    int cams[kMaxLayers];
-    {
-        unsigned long long m = win;
-        for (int l = 0; l < n_layers; ++l) {
-            cams[l] = __ffsll((long long)m) - 1;
-            m &= m - 1;
-        }
-    }
-    // ---- phase 2: per layer, source bounding box and validity of the cheap coordinates -----
+    // ---- phase 2: per layer, source bounding box and validity of the cheap coordinates -----------
+    unsigned long long m = ((unsigned long long)win_hi << 32) | win_lo;
+    rec.type = kBlockFast;
+    rec.n_layers = (uint8_t)n_layers;
     for (int l = 0; l < n_layers; ++l) {
-        const int c = cams[l];
+        const int c = __ffsll((long long)m) - 1;
+        m &= m - 1;
         int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN;
-        bool all_in = (x < P.W) && (y0 + kRun <= P.H), any_in = false;
+        bool all_in = (x < P.W) && (y0 + kRun <= P.H);
         unsigned mism = 0u;
         if (x < P.W) {
             const RunAnchor a = run_anchor(P.M[c], x, y0 + kRun / 2);
@@ -236,50 +219,33 @@ __global__ void __launch_bounds__(kThreads) plan_kernel(const __grid_constant__ 
                 coord_exact(P.M[c], xb, x - xb, y, X, Y);
                 const int j = k - kRun / 2;
                 run_coord_bits(a, (float)j, xbits, ybits);
-                if (X != xbits + a.bx + 32 * a.nx * j || Y != ybits + a.by + 32 * a.ny * j)
-                    mism |= 1u << exact_bit(tid, k);
+                if (X != xbits + a.bx + 32 * a.nx * j || Y != ybits + a.by + 32 * a.ny * j) mism |= 1u << (k >> 2);
                 if (cover_class(X, Y, P.w[c], P.h[c], 1) == 1) {   // interior only
                     const int sx = X >> kFracBits, sy = Y >> kFracBits;
                     bx0 = min(bx0, sx);
                     by0 = min(by0, sy);
                     bx1 = max(bx1, sx + 1);
                     by1 = max(by1, sy + 1);
-                    any_in = true;
                 } else {
                     all_in = false;
                 }
             }
         }
-        if (mism) atomicOr(&s_exact[l], mism);
-        if (bx0 != INT_MAX) {
-            atomicMin(&s_bx0[l], bx0);
-            atomicMin(&s_by0[l], by0);
-            atomicMax(&s_bx1[l], bx1);
-            atomicMax(&s_by1[l], by1);
-        }
-        // block-level coverage (a warp is exactly one 32x16 block)
-        const bool blk_all = __all_sync(0xffffffffu, all_in), blk_any = __any_sync(0xffffffffu, any_in);
-        if ((tid & 31) == 0) {
-            if (blk_all) atomicOr(&s_all[l], 1u << (tid >> 5));
-            if (!blk_any) atomicOr(&s_none[l], 1u << (tid >> 5));
-        }
+        bx0 = __reduce_min_sync(FULLMASK, bx0);
+        by0 = __reduce_min_sync(FULLMASK, by0);
+        bx1 = __reduce_max_sync(FULLMASK, bx1);
+        by1 = __reduce_max_sync(FULLMASK, by1);
+        mism = __reduce_or_sync(FULLMASK, mism);
+        all_in = __all_sync(FULLMASK, all_in);
+        rec.layer[l].x0 = (int16_t)bx0;     // every layer wins, hence interior-covers, at least one pixel
+        rec.layer[l].y0 = (int16_t)by0;
+        rec.layer[l].x1 = (int16_t)bx1;
+        rec.layer[l].y1 = (int16_t)by1;
+        rec.layer[l].cam = (uint8_t)c;
+        rec.layer[l].full = all_in ? 1 : 0;
+        rec.layer[l].groups = (uint8_t)mism;
     }
-    __syncthreads();
-    if (tid == 0) {
-        rec.type = kTileFast;
-        rec.n_layers = (uint8_t)n_layers;
-        for (int l = 0; l < n_layers; ++l) {
-            rec.cam[l] = (uint8_t)cams[l];
-            rec.bx0[l] = (int16_t)s_bx0[l];
-            rec.by0[l] = (int16_t)s_by0[l];
-            rec.bx1[l] = (int16_t)s_bx1[l];
-            rec.by1[l] = (int16_t)s_by1[l];
-            rec.exact_mask[l] = s_exact[l];
-            rec.all_mask[l] = (uint8_t)s_all[l];
-            rec.none_mask[l] = (uint8_t)s_none[l];
-        }
-        *dst = rec;
-    }
+    if (lane == 0) *dst = rec;
 }
 
 }  // namespace bs

@@ -55,10 +55,10 @@ typedef struct bs_handle bs_handle;
 typedef struct bs_stats {
     int n_cams, canvas_w, canvas_h;
     int tile_w, tile_h;
-    int64_t n_tiles;          /* canvas tiles in the plan */
-    int64_t n_tiles_fast;     /* tiles fully covered by their top camera (staged path) */
-    int64_t n_tiles_exact;    /* tiles on the exact per-pixel path (seams, edges, holes) */
-    int64_t n_tiles_empty;    /* tiles no camera touches */
+    int64_t n_tiles;          /* canvas blocks (tile_w x tile_h pixels) in the plan */
+    int64_t n_tiles_fast;     /* blocks on the staged path (interior samples of <= 2 cameras) */
+    int64_t n_tiles_exact;    /* blocks on the exact per-pixel path (last-row/column pixels, 3+ cameras) */
+    int64_t n_tiles_empty;    /* blocks no camera touches */
     int64_t kernel_launches;  /* kernels of this library launched through this handle */
     int64_t frames_submitted;
     uint64_t device_bytes;    /* device memory owned by the handle */
@@ -142,16 +142,17 @@ int bs_get_stats(const bs_handle *h, bs_stats *out);
  * arguments (flags: BS_FLAG_LEGACY_BORDER, BS_FLAG_KEEP_CANVAS), but the tile plan is rebuilt on every
  * call, so it is slower per frame; n_cams <= 16.
  *
- * The plan and scheduler counters live in one static device array of BS_STATIC_SCRATCH_BYTES that
- * every GPU loading the library keeps until exit.  Canvases needing more than BS_STATIC_MAX_TILES
- * tiles of 128x32 pixels (ceil(w/128) * ceil(h/32) > 8192; a 15360x2160 panorama needs 8160) are
- * refused with BS_ERR_UNSUPPORTED.  All calls share that array: calls whose GPU work overlaps (different
- * streams) race on it, so keep them on one stream.  The first call on each device performs the
- * one-time address lookup and must come before any stream capture.  The call returns after its
- * kernels have finished (it synchronises `stream` once for the plan and once at the end).
+ * The staged kernel's scratch (the block plan and the per-warp work split) lives in one static device
+ * array of BS_STATIC_SCRATCH_BYTES that every GPU loading the library keeps until exit.  Canvases
+ * needing more than BS_STATIC_MAX_BLOCKS blocks of 32x16 pixels (ceil(w/32) * ceil(h/16) > 65536; a
+ * 15360x2160 panorama needs 64800) are refused with BS_ERR_UNSUPPORTED.  All calls share that array:
+ * calls whose GPU work overlaps (different streams) race on it, so keep them on one stream.  The
+ * first call on each device performs the one-time address lookup and must come before any stream
+ * capture.  The call returns after its kernels have finished (it synchronises `stream` once for the
+ * plan and once at the end).
  */
-#define BS_STATIC_MAX_TILES 8192
-#define BS_STATIC_SCRATCH_BYTES (BS_STATIC_MAX_TILES * 80 + 256)
+#define BS_STATIC_MAX_BLOCKS 65536
+#define BS_STATIC_SCRATCH_BYTES (BS_STATIC_MAX_BLOCKS * 32 + 32768)
 int bs_stitch_device_static(int n_cams, const int *src_w, const int *src_h, const void *const *d_frames,
                             const size_t *pitch, int canvas_w, int canvas_h, void *d_canvas,
                             size_t canvas_pitch, const double *H, unsigned flags, void *stream);

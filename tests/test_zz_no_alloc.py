@@ -3,7 +3,7 @@
 Some users of this library own all of their memory and cannot allocate while frames are flowing:
 a capture or render loop with a fixed device-memory budget, a host application that forbids
 cudaMalloc after start-up (it stalls the whole GPU), a plug-in running inside somebody else's
-allocator.  For them the library keeps the staged kernel's scratch (tile plan + scheduler counters)
+allocator.  For them the library keeps the staged kernel's scratch (block plan + per-warp work split)
 in one fixed static device array and offers one call that allocates nothing.
 
 What is checked here, through the C ABI, on the GPU:
@@ -12,7 +12,7 @@ What is checked here, through the C ABI, on the GPU:
     the first call's plan and counters and must not be disturbed by them;
   * a different calibration right afterwards (other canvas, seams, ragged edges) is also exact, so
     nothing stale survives in the shared array;
-  * a canvas that needs more tiles than the array holds is refused with a clear message.
+  * a canvas that needs more blocks than the array holds is refused with a clear message.
 This file sorts last on purpose: with `pytest -x` every other test has already run if it fails.
 """
 import numpy as np
@@ -83,11 +83,11 @@ def test_other_calibration_right_after_is_not_disturbed_by_stale_scratch():
 
 def test_canvas_beyond_the_static_array_is_refused():
     p = pkg()
-    w = workloads().get("cfg1")        # 6085 x 8353 needs 48 x 262 = 12576 tiles, the array holds 8192
+    w = workloads().get("cfg1")        # 6085 x 8353 needs 191 x 523 = 99893 blocks of 32x16, the array holds 65536
     d_src = [torch.zeros((8, 8, 3), dtype=torch.uint8, device="cuda")]
     d_out = torch.zeros((16, 16, 3), dtype=torch.uint8, device="cuda")
     with pytest.raises(p.StitchError) as e:
         p.stitch_device_static([(8, 8)], [d_src[0].data_ptr()], [d_src[0].stride(0)], w.canvas_wh, d_out.data_ptr(),
                                w.canvas_wh[0] * 3, [np.eye(3)])
     assert e.value.code == -4
-    assert "12576 tiles" in str(e.value) and "8192" in str(e.value)
+    assert "99893 blocks" in str(e.value) and "65536" in str(e.value)

@@ -53,8 +53,7 @@ struct bs_handle {
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
     bs::WorkItem *d_items = nullptr;     // plan: work items, heaviest blocks first (same allocation held the raw records)
-    int *d_warp_start = nullptr;         // item range of every warp of the grid
-    int n_blocks = 0, blocks_x = 0, blocks_y = 0, n_items = 0;
+    int n_blocks = 0, blocks_x = 0, blocks_y = 0, n_items = 0, n_two = 0;
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
@@ -174,7 +173,7 @@ constexpr int kStageBytesMax = 6 * 1024;    // per-warp, per-stage cap on a bloc
 struct PlanLayout {
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0;
-    int n_items = 0;
+    int n_items = 0, n_two = 0;         // n_two: blocks with two camera layers (they come first)
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
 };
 
@@ -241,43 +240,26 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
             it.c0 = (int16_t)bs::box_elem0(r.layer[l].x0);
             it.y0 = r.layer[l].y0;
             it.origin_off = (uint32_t)((int)it.y0 * (L->box_we[it.cam] * 4) + 4 * (int)it.c0);
+            it.coef = r.coef[l];
         }
     };
+    // order: two-layer blocks (two adjacent items each), then the rest heaviest first; within a class
+    // raster order, so that blocks processed at the same time are neighbours
+    L->n_two = 0;
+    for (int t = 0; t < n_blocks; ++t)
+        if (recs[t].type == bs::kBlockFast && recs[t].n_layers == 2) {
+            emit(recs[t], 0);
+            emit(recs[t], 1);
+            L->n_fast++;
+            L->n_two++;
+        }
     for (int t = 0; t < n_blocks; ++t)
         if (recs[t].type == bs::kBlockExact) emit(recs[t], 0), L->n_exact++;
-    for (int layers = bs::kMaxLayers; layers >= 1; --layers)
-        for (int t = 0; t < n_blocks; ++t)
-            if (recs[t].type == bs::kBlockFast && recs[t].n_layers == layers) {
-                for (int l = 0; l < layers; ++l) emit(recs[t], l);
-                L->n_fast++;
-            }
+    for (int t = 0; t < n_blocks; ++t)
+        if (recs[t].type == bs::kBlockFast && recs[t].n_layers == 1) emit(recs[t], 0), L->n_fast++;
     for (int t = 0; t < n_blocks; ++t)
         if (recs[t].type == bs::kBlockEmpty) emit(recs[t], 0), L->n_empty++;
     L->n_items = n;
-}
-
-// Contiguous item ranges for the n_warps warps of the grid, balanced by estimated cost; a block's
-// layers stay with one warp.  warp_start has n_warps + 1 entries.
-void split_items(const bs::WorkItem *items, int n_items, int n_warps, int *warp_start)
-{
-    // relative run times measured on B200: the unrolled hot path = 4, the general path (coverage
-    // tests, byte stores, exact coordinates where flagged) about twice that, per-pixel fp64 blocks far more
-    auto cost = [](const bs::WorkItem &it) -> long long {
-        if (it.type == bs::kBlockExact) return 60;
-        if (it.type != bs::kBlockFast) return 1;
-        return ((it.flags & bs::kItemFull) && it.groups == 0) ? 4 : 9;
-    };
-    long long total = 0;
-    for (int i = 0; i < n_items; ++i) total += cost(items[i]);
-    int i = 0;
-    long long acc = 0;
-    warp_start[0] = 0;
-    for (int w = 1; w <= n_warps; ++w) {
-        const long long target = (total * w + n_warps - 1) / n_warps;
-        while (i < n_items && (acc < target || !(items[i].flags & bs::kItemFirst))) acc += cost(items[i++]);
-        warp_start[w] = i;
-    }
-    warp_start[n_warps] = n_items;
 }
 
 // Build the block plan on the device and post-process it on the host (once per calibration).
@@ -304,7 +286,7 @@ int build_plan(bs_handle *h)
     P->keep_canvas = (h->flags & BS_FLAG_KEEP_CANVAS) ? 1 : 0;
     P->blocks_x = h->blocks_x;
     P->blocks_y = h->blocks_y;
-    // device scratch: raw records first, later overwritten by the item list (2 items of 16 bytes per block)
+    // device scratch: raw records first, later overwritten by the item list (at most 2 items of 80 bytes per block)
     const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)h->n_blocks;
     void *d_plan = nullptr;
     cudaError_t e = cudaMalloc(&d_plan, raw_bytes);
@@ -365,19 +347,12 @@ int build_plan(bs_handle *h)
                                                              h->smem_bytes));
     BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
     if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
-    h->grid = std::max(1, std::min((h->n_items + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
+    h->grid = std::max(1, std::min((h->n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
     if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
-    const int n_warps = h->grid * bs::kWarpsPerCta;
-    std::vector<int> warp_start(n_warps + 1);
-    split_items(items.data(), h->n_items, n_warps, warp_start.data());
+    h->n_two = L.n_two;
 
-    const size_t item_bytes = sizeof(bs::WorkItem) * (size_t)h->n_items;   // <= raw_bytes: 2 x 16 B per block
+    const size_t item_bytes = sizeof(bs::WorkItem) * (size_t)h->n_items;   // <= raw_bytes: 2 x 80 B per block
     BS_CUDA(h, cudaMemcpy(h->d_items, items.data(), item_bytes, cudaMemcpyHostToDevice));
-    const size_t ws_bytes = sizeof(int) * (size_t)(n_warps + 1);
-    BS_CUDA(h, cudaMalloc(&h->d_warp_start, ws_bytes));
-    BS_CUDA(h, cudaMemcpy(h->d_warp_start, warp_start.data(), ws_bytes, cudaMemcpyHostToDevice));
-    h->device_bytes += ws_bytes;
-    h->scratch_bytes += ws_bytes;
     h->fast_ok = true;
     return BS_OK;
 }
@@ -426,7 +401,8 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = keep ? 1 : 0;
         FA.items = h->d_items;
-        FA.warp_start = h->d_warp_start;
+        FA.n_units = h->n_blocks;
+        FA.n_two = h->n_two;
         FA.stage_bytes = h->stage_bytes;
         {
             // programmatic dependent launch: the prologue and first tile of this frame may overlap the
@@ -593,7 +569,6 @@ int bs_destroy(bs_handle *h)
         if (s.ev_done) cudaEventDestroy(s.ev_done);
     }
     cudaFree(h->d_items);
-    cudaFree(h->d_warp_start);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
@@ -792,11 +767,9 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 
 namespace {
 
-constexpr int kStaticMaxWarps = 8192;   // grid warps the warp_start table has room for (B200: 148 SMs x 2 CTAs x 8 = 2368)
 struct StaticScratch {
-    // raw block records from the plan kernel; then overwritten by the work items (2 x 16 bytes per block)
+    // raw block records from the plan kernel; then overwritten by the work items (at most 2 x 80 bytes per block)
     bs::BlockRec plan[BS_STATIC_MAX_BLOCKS];
-    int warp_start[kStaticMaxWarps];
 };
 static_assert(sizeof(StaticScratch) == BS_STATIC_SCRATCH_BYTES, "BS_STATIC_SCRATCH_BYTES is out of date");
 static_assert(sizeof(bs::WorkItem) * bs::kMaxLayers <= sizeof(bs::BlockRec), "items must fit where the raw records were");
@@ -816,7 +789,6 @@ StaticDeviceState g_static_dev[kStaticMaxDevices];
 std::mutex g_static_mutex;                            // host side of the sharing; the GPU side is the caller's job
 bs::BlockRec g_static_recs[BS_STATIC_MAX_BLOCKS];     // host staging for the plan, fixed size (no heap)
 bs::WorkItem g_static_items[BS_STATIC_MAX_BLOCKS * bs::kMaxLayers];
-int g_static_warp_start[kStaticMaxWarps];
 bs::PlanArgs g_static_plan_args;
 
 // Once per device, with that device current.
@@ -956,17 +928,13 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
             if (er != 0) return fail(nullptr, BS_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d) for camera %d", me, er, i);
         }
     }
-    int grid = std::max(1, std::min((L.n_items + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
-    grid = std::min(grid, (kStaticMaxWarps - 1) / bs::kWarpsPerCta);
-    const int n_warps = grid * bs::kWarpsPerCta;
-    split_items(g_static_items, L.n_items, n_warps, g_static_warp_start);
+    const int grid = std::max(1, std::min((n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
     // the item list replaces the raw records in the scratch; stream-ordered after the previous call's kernels
     BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_items, sizeof(bs::WorkItem) * (size_t)L.n_items,
                                      cudaMemcpyHostToDevice, s));
-    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->warp_start, g_static_warp_start, sizeof(int) * (size_t)(n_warps + 1),
-                                     cudaMemcpyHostToDevice, s));
     FA.items = reinterpret_cast<const bs::WorkItem *>(st->scratch->plan);
-    FA.warp_start = st->scratch->warp_start;
+    FA.n_units = n_blocks;
+    FA.n_two = L.n_two;
     FA.stage_bytes = L.stage_bytes;
     bs::stitch_fast_kernel<<<grid, bs::kFastThreads, L.smem_bytes, s>>>(FA);
     BS_CUDA(nullptr, cudaGetLastError());

@@ -29,8 +29,9 @@ constexpr int kStagePad = 128;                       // slack behind a stage for
 struct FastArgs {
     FrameArgs F;
     CUtensorMap tmap[kMaxCamsPerLaunch];   // source frame of camera i as a [h][pitch/4] u32 tensor
-    const WorkItem *items;                 // the plan, flattened
-    const int *warp_start;                 // n_warps + 1 entries: item range of every warp of the grid
+    const WorkItem *items;                 // the plan, flattened: blocks with two layers first (two adjacent items each)
+    int n_units;                           // blocks in the plan
+    int n_two;                             // of which the first n_two have two items
     int pitch[kMaxCamsPerLaunch];          // TMA box of camera i: row pitch in shared memory (bytes) ...
     int box_bytes[kMaxCamsPerLaunch];      // ... and total bytes (= what the mbarrier expects)
     int stage_bytes;                       // shared memory per stage (multiple of 128)
@@ -183,34 +184,48 @@ constexpr int kFastThreads = 32 * kWarpsPerCta;
 #ifndef BS_MIN_CTAS
 #define BS_MIN_CTAS 2
 #endif
-constexpr int kStages = 3;                             // per warp: source boxes of items i, i+1, i+2
+constexpr int kStages = 2;                             // per warp: source boxes of items i and i+1
 constexpr int kRecSlots = 4;                           // per warp: records of items i .. i+3
 constexpr int kBlockRowBytes = 96;                     // 32 pixels
 constexpr int kWarpOutBytes = kRun * kBlockRowBytes;   // 1536
-constexpr int kWarpCtlBytes = kRecSlots * 16 + (kStages + kRecSlots) * 8 + 8;   // records + mbarriers (128)
+constexpr int kRecBytes = 80;                          // sizeof(WorkItem)
+constexpr int kWarpCtlBytes = (kRecSlots * kRecBytes + (kStages + kRecSlots) * 8 + 127) / 128 * 128;   // records + mbarriers, keeps every warp's region 128-byte aligned
 
 __host__ __device__ constexpr int warp_smem_bytes(int stage_bytes)
 {
     return kStages * stage_bytes + kWarpOutBytes + kWarpCtlBytes;
 }
 
-// Hot path: the layer covers every pixel of the block with interior samples, the tile lies inside
+// The block's coordinate expansion as it sits in a record slot (words 4..19 of the work item).
+__device__ __forceinline__ BlockCoef load_block_coef(uint32_t rec_addr)
+{
+    uint4 q[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(q[i].x), "=r"(q[i].y), "=r"(q[i].z), "=r"(q[i].w)
+                     : "r"(rec_addr + 16u + 16u * i));
+    BlockCoef c;
+    memcpy(&c, q, sizeof c);
+    return c;
+}
+
+// Hot path: the layer covers every pixel of the block with interior samples, the block lies inside
 // the canvas and the plan verified the cheap coordinates for the whole block.  No coverage tests,
-// no fp64 beyond the run's anchor; fully unrolled so k is a constant.
-__device__ __forceinline__ void run_layer_full(const CamDev &cam, int pitch, uint32_t stage_origin, uint32_t lut_base,
-                                               uint32_t out_blk, int x, int yc, int lane)
+// no fp64; fully unrolled so the row offset v is a constant.
+__device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, uint32_t stage_origin, uint32_t lut_base,
+                                               uint32_t out_blk, int lane)
 {
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
-    const RunAnchor a = run_anchor(cam.M, x, yc);
-    const uint32_t run_base = stage_origin + (uint32_t)((a.by >> kFracBits) * pitch + (a.bx >> kFracBits) * 3);
-    const int step = a.ny * pitch + a.nx * 3;      // whole texels per canvas row, as a byte offset
+    const uint32_t run_base = stage_origin + (uint32_t)((lc.by >> kFracBits) * pitch + (lc.bx >> kFracBits) * 3);
+    const int step = lc.nyv * pitch + lc.nxv * 3;      // whole texels per canvas row, as a byte offset
     // software pipeline: the shared-memory loads of pixel k+1 are issued before the arithmetic of
     // pixel k, so a warp has work to do while its loads are in flight
     auto fetch = [&](int k) {
-        const int j = k - kRun / 2;
+        const int v = k - kRun / 2;
         int xbits, ybits;
-        run_coord_bits(a, (float)j, xbits, ybits);
-        const uint32_t o = run_base + (uint32_t)(j * step) +
+        lane_coord_bits(lc, (float)v, xbits, ybits);
+        const uint32_t o = run_base + (uint32_t)(v * step) +
                            (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
         // the table sits on an 8 KB boundary, so its base can be OR-ed in after masking the index
         const uint32_t lut_off = lut_base | ((uint32_t)((ybits << 8) + ((xbits << 3) & 0xF8)) & 0x1FF8u);
@@ -227,14 +242,13 @@ __device__ __forceinline__ void run_layer_full(const CamDev &cam, int pitch, uin
     }
 }
 
-// General path: partially covered layers, tiles that stick out of the canvas, and blocks for which
+// General path: partially covered layers, blocks that stick out of the canvas, and blocks for which
 // the plan found at least one pixel where the cheap coordinates differ (those 32x4 groups use
 // the exact fp64 form).  Same arithmetic per pixel, with coverage tests and byte stores.
-__device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &cam, int pitch, uint32_t stage_origin,
-                                               uint32_t lut_base, uint32_t out_blk, uint32_t group_mask, bool full,
-                                               bool first_layer, int x, int y0, int lane)
+__device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &cam, const LaneCoef &lc, int pitch,
+                                               uint32_t stage_origin, uint32_t lut_base, uint32_t out_blk,
+                                               uint32_t group_mask, bool full, bool first_layer, int x, int y0, int lane)
 {
-    const RunAnchor a = run_anchor(cam.M, x, y0 + kRun / 2);
     const int xb = (x / A.F.block_w) * A.F.block_w;
 #pragma unroll 1
     for (int k = 0; k < kRun; ++k) {
@@ -242,11 +256,11 @@ __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &
         if ((group_mask >> (k >> 2)) & 1) {     // warp-uniform
             coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
         } else {
-            const int j = k - kRun / 2;
+            const int v = k - kRun / 2;
             int xbits, ybits;
-            run_coord_bits(a, (float)j, xbits, ybits);
-            X = xbits + a.bx + 32 * a.nx * j;
-            Y = ybits + a.by + 32 * a.ny * j;
+            lane_coord_bits(lc, (float)v, xbits, ybits);
+            X = xbits + lc.bx + 32 * lc.nxv * v;
+            Y = ybits + lc.by + 32 * lc.nyv * v;
         }
         const int sx = X >> kFracBits, sy = Y >> kFracBits;
         bool in = (x < A.F.W) && (y0 + k < A.F.H);
@@ -321,7 +335,7 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     const uint32_t stage0 = wbase;                                             // 128-byte aligned
     const uint32_t out_blk = stage0 + (uint32_t)(kStages * A.stage_bytes);
     const uint32_t rec0 = out_blk + kWarpOutBytes;
-    const uint32_t dbar0 = rec0 + kRecSlots * 16;                              // data barriers, one per stage
+    const uint32_t dbar0 = rec0 + kRecSlots * kRecBytes;                       // data barriers, one per stage
     const uint32_t rbar0 = dbar0 + kStages * 8;                                // record barriers, one per slot
 
     // Programmatic dependent launch: let the next frame's kernel start filling SMs as this one's CTAs
@@ -339,23 +353,42 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     }
     __syncthreads();
 
-    const int gw = blockIdx.x * kWarpsPerCta + warp;
-    const int i0 = A.warp_start[gw], i1 = A.warp_start[gw + 1];
-    if (i0 >= i1) return;
+    // Work split: block u of the plan goes to warp u mod W (W = warps in the grid).  The plan lists the
+    // heaviest blocks first, so they spread evenly and no cost model is needed; at any moment the grid
+    // works on W consecutive blocks, i.e. on neighbouring pixels, which keeps box overlaps in L2.
+    const int W = (int)gridDim.x * kWarpsPerCta;
+    const int gw = (int)blockIdx.x * kWarpsPerCta + warp;
+    if (gw >= A.n_units) return;
+    const int my_units = (A.n_units - 1 - gw) / W + 1;
+    const int my_two = gw < A.n_two ? (A.n_two - 1 - gw) / W + 1 : 0;
+    const int i0 = 0, i1 = my_units + my_two;       // this warp's items, numbered locally
+    // cursor over this warp's items in order, used by lane 0 to fetch records ahead
+    int cur_unit = gw, cur_layer = 0;
+    auto next_item_index = [&]() {                  // global index of the cursor's item; then advance
+        const int idx = cur_unit + min(cur_unit, A.n_two) + cur_layer;
+        if (cur_layer == 0 && cur_unit < A.n_two) cur_layer = 1;
+        else {
+            cur_layer = 0;
+            cur_unit += W;
+        }
+        return idx;
+    };
 
     // lane 0 is this warp's producer ------------------------------------------------------------------
-    // record of item i -> record slot, by a 16-byte bulk copy
-    auto request_record = [&](int i, uint32_t slot) {
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * slot), "r"(16u) : "memory");
+    // record of item i -> record slot, by an 80-byte bulk copy
+    auto request_record = [&](uint32_t slot) {
+        const int i = next_item_index();
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * slot), "r"((uint32_t)kRecBytes)
+                     : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         rec0 + 16 * slot),
-                     "l"(A.items + i), "r"(16u), "r"(rbar0 + 8 * slot)
+                         rec0 + kRecBytes * slot),
+                     "l"(A.items + i), "r"((uint32_t)kRecBytes), "r"(rbar0 + 8 * slot)
                      : "memory");
     };
     // source box of the item whose record sits in `slot` -> stage; items without a box just arrive
     auto issue_box = [&](uint32_t slot, uint32_t rec_parity, uint32_t stage) {
         mbar_wait_addr(rbar0 + 8 * slot, rec_parity);
-        const uint4 r = lds128(rec0 + 16 * slot);
+        const uint4 r = lds128(rec0 + kRecBytes * slot);
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
             const uint32_t cam = (r.y >> 16) & 0xFFu;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
@@ -371,9 +404,8 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         }
     };
     if (lane == 0) {
-        for (int d = 0; d < 3 && i0 + d < i1; ++d) request_record(i0 + d, (uint32_t)d);
+        for (int d = 0; d < 3 && i0 + d < i1; ++d) request_record((uint32_t)d);
         issue_box(0u, 0u, 0u);
-        if (i0 + 1 < i1) issue_box(1u, 0u, 1u);
     }
     __syncwarp();
 
@@ -381,10 +413,22 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     bool wrote = false;               // some layer has written into the current block
     uint32_t stage = 0, dpar = 0;     // stage and data-barrier parity of the current item
     uint32_t slot = 0, rpar = 0;      // record slot and record-barrier parity of the current item
-    uint32_t pstage = 2, pslot = 2, ppar = 0;   // producer cursor: item i+2 (its stage, record slot, record parity)
+    uint32_t pstage = 1, pslot = 1, ppar = 0;   // producer cursor: item i+1 (its stage, record slot, record parity)
     for (int i = i0; i < i1; ++i) {
+        if (lane == 0) {
+            // prefetch: the box of item i+1 goes into the other stage (item i-1 is done with it), the
+            // record of item i+3 into the slot item i-1 used
+            if (i + 1 < i1) issue_box(pslot, ppar, pstage);
+            if (i + 3 < i1) request_record((pslot + 2) & (kRecSlots - 1));
+        }
+        if (++pstage == kStages) pstage = 0;
+        if (++pslot == kRecSlots) {
+            pslot = 0;
+            ppar ^= 1u;
+        }
+        __syncwarp();
         mbar_wait_addr(rbar0 + 8 * slot, rpar);
-        const uint4 r = lds128(rec0 + 16 * slot);
+        const uint4 r = lds128(rec0 + kRecBytes * slot);
         const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
         mbar_wait_addr(dbar0 + 8 * stage, dpar);
@@ -396,24 +440,14 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             const uint32_t stage_origin = stage0 + stage * (uint32_t)A.stage_bytes - r.w;
             const uint32_t groups = (r.y >> 24) & 0xFFu;
             const bool full = (flags & kItemFull) != 0;
+            const LaneCoef lc = lane_coef(load_block_coef(rec0 + kRecBytes * slot), lane - kBlockW / 2);
             if (full && groups == 0u)
-                run_layer_full(cam, pitch, stage_origin, lut_base, out_blk, tx0 + lane, ty0 + kRun / 2, lane);
+                run_layer_full(lc, pitch, stage_origin, lut_base, out_blk, lane);
             else
-                run_layer_general(A, cam, pitch, stage_origin, lut_base, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
+                run_layer_general(A, cam, lc, pitch, stage_origin, lut_base, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
             wrote = true;
         }
         __syncwarp();                 // every lane is done with this item's stage and record
-        if (lane == 0) {
-            // refill: the box of item i+2 goes into the stage of item i-1, the record of item i+3 into
-            // the slot of item i-1 (both consumed one iteration ago)
-            if (i + 2 < i1) issue_box(pslot, ppar, pstage);
-            if (i + 3 < i1) request_record(i + 3, (pslot + 1) & (kRecSlots - 1));
-        }
-        if (++pstage == kStages) pstage = 0;
-        if (++pslot == kRecSlots) {
-            pslot = 0;
-            ppar ^= 1u;
-        }
         if (flags & kItemLast) {
             if (!prior_grid_done) {
                 asm volatile("griddepcontrol.wait;" ::: "memory");

@@ -25,8 +25,21 @@ constexpr int kPlanWarps = 8;      // blocks per CTA of the plan kernel
 
 enum BlockType : uint8_t { kBlockEmpty = 0, kBlockFast = 1, kBlockExact = 2 };
 
+// Second-order expansion of one camera's source coordinate field around a block's centre, in the
+// form the frame kernel evaluates it (see block_coef / lane_coef / lane_coord_bits below).
+struct BlockCoef {                 // 64 bytes
+    int ix, iy;                    // integer bases of the centre coordinate (multiples of 32)
+    int8_t nxu, nxv, nyu, nyv;     // whole source texels advanced per canvas column (u) and row (v)
+    uint32_t pad;
+    float fx, fy;                  // centre coordinate minus its base, in [-0.5, 32.5)
+    float xu, xv, yu, yv;          // first derivatives minus their whole-texel parts (1/32 px per pixel)
+    float hxuu, xuv, hxvv;         // second derivatives (the pure ones halved)
+    float hyuu, yuv, hyvv;
+};
+static_assert(sizeof(BlockCoef) == 64, "BlockCoef layout");
+
 // Raw output of the plan kernel, one per block (read back by the host).
-struct BlockRec {                  // 32 bytes
+struct BlockRec {                  // 160 bytes
     uint16_t bx, by;               // block coordinates (units of 32 x 16 pixels)
     uint8_t type;                  // BlockType
     uint8_t n_layers;
@@ -39,11 +52,12 @@ struct BlockRec {                  // 32 bytes
         uint8_t groups;            // bit g: rows 4g..4g+3 of the block must use exact coordinates
         uint8_t pad;
     } layer[kMaxLayers];
+    BlockCoef coef[kMaxLayers];
 };
-static_assert(sizeof(BlockRec) == 32, "BlockRec layout");
+static_assert(sizeof(BlockRec) == 160, "BlockRec layout");
 
-// What the frame kernel consumes: one item per (block, camera layer), 16 bytes, a block's items
-// adjacent and in compositing order.  EXACT and EMPTY blocks are single items.
+// What the frame kernel consumes: one item per (block, camera layer), 80 bytes (five 16-byte
+// words), a block's items adjacent and in compositing order.  EXACT and EMPTY blocks are single items.
 struct WorkItem {
     uint16_t bx, by;
     uint8_t type;                  // BlockType
@@ -52,74 +66,92 @@ struct WorkItem {
     uint8_t groups;                // bit g: rows 4g..4g+3 must use exact coordinates
     int16_t c0, y0;                // TMA coordinates of the source box: first 4-byte element, first row
     uint32_t origin_off;           // y0 * stage pitch + 4 * c0: offset of the box origin from texel (0, 0)
+    BlockCoef coef;
 };
-static_assert(sizeof(WorkItem) == 16, "WorkItem layout");
+static_assert(sizeof(WorkItem) == 80, "WorkItem layout");
 constexpr uint8_t kItemFirst = 1, kItemLast = 2, kItemFull = 4;
 
-// ---- cheap coordinates for a vertical run of kRun pixels (one canvas column) -----------------
-// Along a column the source coordinate is fX(yc + j) = fXc + j (32 M1 - M7 fXc) / (Wc + j M7),
-// j = k - kRun/2.  The run is anchored at its 9th pixel in fp64; the increment is expanded to
-// second order in j.  Its whole-texel part, 32 n per step with n = round(dX / 32), is exact integer
-// arithmetic and goes straight into the address; only the small remainder is evaluated in fp32:
-//     sX(j) = fx + j (Dx + j Ex),   X(j) = rint(sX(j)) + base_x + 32 n_x j.
-// The result is only used where the plan has checked, pixel by pixel, that it equals
-// coord_exact(); every floating-point operation is an explicit intrinsic (or PTX) so the plan
-// kernel and the frame kernel execute the same instruction sequence.
-struct RunAnchor {
-    int bx, by;        // integer bases (multiples of 32) minus the float-magic bias
-    int nx, ny;        // whole source texels advanced per canvas row
-    float fx, fy;      // fXc - base, in [-0.5, 32.5)
-    float Dx, Ex, Dy, Ey;
-};
-
+// ---- cheap coordinates ---------------------------------------------------------------------------
+// For camera map M the 1/32-pixel source coordinate of canvas pixel (x, y) is g(x, y) = 32 N / W
+// with N, W affine in (x, y).  Around a block's centre (xc, yc), with u = x - xc in [-16, 15] and
+// v = y - yc in [-8, 7],
+//     g(u, v) ~ g + g_u u + g_v v + g_uu u^2 / 2 + g_uv u v + g_vv v^2 / 2.
+// The derivatives follow from g W = 32 N:  g_u = (32 M0 - M6 g) / W,  g_v = (32 M1 - M7 g) / W,
+// g_uu = -2 M6 g_u / W,  g_vv = -2 M7 g_v / W,  g_uv = -(M6 g_v + M7 g_u) / W.
+// The plan computes them once per block and camera in fp64 (block_coef) and stores them in the work
+// item; the whole-texel parts of g and of its first derivatives are split off as integers, so the
+// frame kernel evaluates only a small remainder in fp32 -- per lane (lane_coef), then two FFMA per
+// coordinate and pixel (lane_coord_bits).  The expansion is only used where the plan has checked,
+// pixel by pixel, that it reproduces coord_exact(); every floating-point operation on the way is an
+// explicit intrinsic so plan kernel and frame kernel execute the same instruction sequence.
 constexpr int kMagicBias = 0x4B400000;   // bits of 12582912.0f = 1.5 * 2^23 (a multiple of 32)
 
-// 1/w to a few ulp: hardware seed (about 20 bits) and two Newton steps, no IEEE special cases.
-// A bad value (w = 0, denormal, ...) only makes the plan reject the run.
-__device__ __forceinline__ double fast_rcp(double w)
+__device__ __forceinline__ BlockCoef block_coef(const double *__restrict__ M, int xc, int yc)
 {
-    double r;
-    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(w));
-    r = fma(r, fma(-w, r, 1.0), r);
-    r = fma(r, fma(-w, r, 1.0), r);
-    return r;
-}
-
-__device__ __forceinline__ RunAnchor run_anchor(const double *__restrict__ M, int x, int yc)
-{
-    const double dx = (double)x, dy = (double)yc;
+    const double dx = (double)xc, dy = (double)yc;
     const double Xn = fma(M[1], dy, fma(M[0], dx, M[2]));
     const double Yn = fma(M[4], dy, fma(M[3], dx, M[5]));
     const double Wn = fma(M[7], dy, fma(M[6], dx, M[8]));
-    const double inv = fast_rcp(Wn);
-    const double inv32 = inv * 32.0;
-    const double fX = Xn * inv32, fY = Yn * inv32;
-    const double dX = fma(-M[7], fX, 32.0 * M[1]) * inv;   // d fX / dj at j = 0
-    const double dY = fma(-M[7], fY, 32.0 * M[4]) * inv;
-    const float e = (float)(-M[7] * inv);
-    const float dXf = (float)dX, dYf = (float)dY;
-    RunAnchor a;
-    a.nx = __float2int_rn(dXf * 0.03125f);
-    a.ny = __float2int_rn(dYf * 0.03125f);
-    const int ix = __double2int_rn(fX) & ~31, iy = __double2int_rn(fY) & ~31;
-    a.bx = ix - kMagicBias;
-    a.by = iy - kMagicBias;
-    a.fx = (float)(fX - (double)ix);
-    a.fy = (float)(fY - (double)iy);
-    a.Dx = (float)(dX - (double)(32 * a.nx));
-    a.Dy = (float)(dY - (double)(32 * a.ny));
-    a.Ex = __fmul_rn(dXf, e);
-    a.Ey = __fmul_rn(dYf, e);
-    return a;
+    const double inv = 1.0 / Wn;
+    const double gx = fmin(fmax(32.0 * Xn * inv, -1.0e9), 1.0e9), gy = fmin(fmax(32.0 * Yn * inv, -1.0e9), 1.0e9);
+    const double gxu = (32.0 * M[0] - M[6] * gx) * inv, gxv = (32.0 * M[1] - M[7] * gx) * inv;
+    const double gyu = (32.0 * M[3] - M[6] * gy) * inv, gyv = (32.0 * M[4] - M[7] * gy) * inv;
+    BlockCoef c;
+    c.ix = (int)rint(gx) & ~31;
+    c.iy = (int)rint(gy) & ~31;
+    c.fx = (float)(gx - (double)c.ix);
+    c.fy = (float)(gy - (double)c.iy);
+    auto whole = [](double d) { return (int)fmin(fmax(rint(d * 0.03125), -127.0), 127.0); };
+    c.nxu = (int8_t)whole(gxu);
+    c.nxv = (int8_t)whole(gxv);
+    c.nyu = (int8_t)whole(gyu);
+    c.nyv = (int8_t)whole(gyv);
+    c.pad = 0;
+    c.xu = (float)(gxu - 32.0 * c.nxu);
+    c.xv = (float)(gxv - 32.0 * c.nxv);
+    c.yu = (float)(gyu - 32.0 * c.nyu);
+    c.yv = (float)(gyv - 32.0 * c.nyv);
+    c.hxuu = (float)(-M[6] * gxu * inv);
+    c.hxvv = (float)(-M[7] * gxv * inv);
+    c.xuv = (float)(-(M[6] * gxv + M[7] * gxu) * inv);
+    c.hyuu = (float)(-M[6] * gyu * inv);
+    c.hyvv = (float)(-M[7] * gyv * inv);
+    c.yuv = (float)(-(M[6] * gyv + M[7] * gyu) * inv);
+    return c;
 }
 
-// k in [0, kRun): pixel row yc - kRun/2 + k.  Returns the raw bits of (s + 1.5*2^23): their low
-// bits are rint(s) (round half to even, done by the fp32 adder), so with j = k - kRun/2
-//   X = bits + a.bx + 32 a.nx j,   X & 31 = bits & 31,   X >> 5 = (bits >> 5) + (a.bx >> 5) + a.nx j.
-__device__ __forceinline__ void run_coord_bits(const RunAnchor &a, float jf, int &xbits, int &ybits)
+// Per-lane form: everything that depends on the column u = lane - 16 only.
+struct LaneCoef {
+    float a0x, a1x, a2x;   // s_x(v) = a0x + v (a1x + v a2x)
+    float a0y, a1y, a2y;
+    int bx, by;            // X = bits_x + bx + 32 nxv v   (float-magic bias folded in)
+    int nxv, nyv;
+};
+
+__device__ __forceinline__ LaneCoef lane_coef(const BlockCoef &c, int u)
 {
-    const float sX = __fmaf_rn(jf, __fmaf_rn(jf, a.Ex, a.Dx), a.fx);
-    const float sY = __fmaf_rn(jf, __fmaf_rn(jf, a.Ey, a.Dy), a.fy);
+    const float uf = (float)u;
+    LaneCoef l;
+    l.a0x = __fmaf_rn(uf, __fmaf_rn(uf, c.hxuu, c.xu), c.fx);
+    l.a1x = __fmaf_rn(uf, c.xuv, c.xv);
+    l.a2x = c.hxvv;
+    l.a0y = __fmaf_rn(uf, __fmaf_rn(uf, c.hyuu, c.yu), c.fy);
+    l.a1y = __fmaf_rn(uf, c.yuv, c.yv);
+    l.a2y = c.hyvv;
+    l.bx = c.ix - kMagicBias + 32 * (int)c.nxu * u;
+    l.by = c.iy - kMagicBias + 32 * (int)c.nyu * u;
+    l.nxv = c.nxv;
+    l.nyv = c.nyv;
+    return l;
+}
+
+// Row v = k - kRun/2 of the lane's run.  Returns the raw bits of (s + 1.5*2^23): their low bits are
+// rint(s) (round half to even, done by the fp32 adder), so
+//   X = bits + l.bx + 32 l.nxv v,   X & 31 = bits & 31,   X >> 5 = (bits >> 5) + (l.bx >> 5) + l.nxv v.
+__device__ __forceinline__ void lane_coord_bits(const LaneCoef &l, float vf, int &xbits, int &ybits)
+{
+    const float sX = __fmaf_rn(vf, __fmaf_rn(vf, l.a2x, l.a1x), l.a0x);
+    const float sY = __fmaf_rn(vf, __fmaf_rn(vf, l.a2y, l.a1y), l.a0y);
     xbits = __float_as_int(__fadd_rn(sX, 12582912.0f));
     ybits = __float_as_int(__fadd_rn(sY, 12582912.0f));
 }
@@ -210,16 +242,18 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
         int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN;
         bool all_in = (x < P.W) && (y0 + kRun <= P.H);
         unsigned mism = 0u;
+        const BlockCoef bc = block_coef(P.M[c], bx * kBlockW + kBlockW / 2, y0 + kRun / 2);
+        rec.coef[l] = bc;
         if (x < P.W) {
-            const RunAnchor a = run_anchor(P.M[c], x, y0 + kRun / 2);
+            const LaneCoef lc = lane_coef(bc, lane - kBlockW / 2);
             for (int k = 0; k < kRun; ++k) {
                 const int y = y0 + k;
                 if (y >= P.H) break;
                 int X, Y, xbits, ybits;
                 coord_exact(P.M[c], xb, x - xb, y, X, Y);
-                const int j = k - kRun / 2;
-                run_coord_bits(a, (float)j, xbits, ybits);
-                if (X != xbits + a.bx + 32 * a.nx * j || Y != ybits + a.by + 32 * a.ny * j) mism |= 1u << (k >> 2);
+                const int v = k - kRun / 2;
+                lane_coord_bits(lc, (float)v, xbits, ybits);
+                if (X != xbits + lc.bx + 32 * lc.nxv * v || Y != ybits + lc.by + 32 * lc.nyv * v) mism |= 1u << (k >> 2);
                 if (cover_class(X, Y, P.w[c], P.h[c], 1) == 1) {   // interior only
                     const int sx = X >> kFracBits, sy = Y >> kFracBits;
                     bx0 = min(bx0, sx);

@@ -83,11 +83,11 @@ def test_other_calibration_right_after_is_not_disturbed_by_stale_scratch():
 
 def test_canvas_beyond_the_static_array_is_refused():
     p = pkg()
-    w = workloads().get("cfg1")        # 6085 x 8353 needs 191 x 523 = 99893 blocks of 32x16, the array holds 65536
+    w = workloads().get("cfg1")        # 6085 x 8353 needs 191 x 523 = 99893 blocks of 32x16, the array holds 32768
     d_src = [torch.zeros((8, 8, 3), dtype=torch.uint8, device="cuda")]
     d_out = torch.zeros((16, 16, 3), dtype=torch.uint8, device="cuda")
     with pytest.raises(p.StitchError) as e:
         p.stitch_device_static([(8, 8)], [d_src[0].data_ptr()], [d_src[0].stride(0)], w.canvas_wh, d_out.data_ptr(),
                                w.canvas_wh[0] * 3, [np.eye(3)])
     assert e.value.code == -4
-    assert "99893 blocks" in str(e.value) and "65536" in str(e.value)
+    assert "99893 blocks" in str(e.value) and "32768" in str(e.value)

@@ -28,6 +28,7 @@ EXPORTS = [
     "bs_device_count", "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_submit",
     "bs_wait", "bs_pipeline_depth", "bs_stitch", "bs_submit_device", "bs_sync",
     "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
+    "bs_set_undistort", "bs_undistort",
 ]
 
 
@@ -84,6 +85,8 @@ def lib():
     L.bs_host_alloc.restype = vp
     L.bs_host_free.argtypes = [vp]
     L.bs_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
+    L.bs_set_undistort.argtypes = [vp, i, dp, dp, i]
+    L.bs_undistort.argtypes = [vp, i, i, sz, vp, sz, dp, dp, i]
     L.bs_stitch_device_static.argtypes = [i, ip, ip, ctypes.POINTER(vp), ctypes.POINTER(sz), i, i, vp, sz, dp,
                                           ctypes.c_uint, vp]
     _lib = L
@@ -203,6 +206,14 @@ class Stitcher:
     def sync(self):
         _check(lib().bs_sync(self._h), self._h)
 
+    def set_undistort(self, cam, K, dist):
+        """Lens model of camera `cam` (cv::undistort before the warp, tools/stitch/main.cpp:148-149)."""
+        K = np.ascontiguousarray(np.asarray(K, dtype=np.float64).reshape(9))
+        dist = np.ascontiguousarray(np.asarray(dist, dtype=np.float64).reshape(-1))
+        dptr = dist.ctypes.data_as(ctypes.POINTER(ctypes.c_double)) if dist.size else None
+        _check(lib().bs_set_undistort(self._h, cam, K.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), dptr,
+                                      int(dist.size)), self._h)
+
     def stats(self):
         s = Stats()
         _check(lib().bs_get_stats(self._h, ctypes.byref(s)), self._h)
@@ -223,6 +234,18 @@ def stitch_device_static(src_whs, frame_ptrs, frame_pitches, canvas_wh, canvas_p
                                          int(canvas_ptr), int(canvas_pitch),
                                          Hs.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), flags,
                                          int(stream) if stream else None))
+
+
+def undistort(src, K, dist):
+    """Mirror of cv::undistort(src, dst, cameraMatrix, distCoeffs) (tools/stitch/main.cpp:148-149)."""
+    _check_img(src, "src")
+    K = np.ascontiguousarray(np.asarray(K, dtype=np.float64).reshape(9))
+    dist = np.ascontiguousarray(np.asarray(dist, dtype=np.float64).reshape(-1))
+    dst = np.empty((src.shape[0], src.shape[1], 3), np.uint8)
+    dptr = dist.ctypes.data_as(ctypes.POINTER(ctypes.c_double)) if dist.size else None
+    _check(lib().bs_undistort(src.ctypes.data, src.shape[1], src.shape[0], src.strides[0], dst.ctypes.data,
+                              dst.strides[0], K.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), dptr, int(dist.size)))
+    return dst
 
 
 def warpPerspective(src, dst, H, dsize, flags=INTER_LINEAR, borderMode=BORDER_TRANSPARENT,

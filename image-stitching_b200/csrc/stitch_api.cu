@@ -19,6 +19,7 @@
 #include <algorithm>
 
 #include "stitch_fast.cuh"
+#include "stitch_undistort.cuh"
 
 namespace {
 
@@ -29,10 +30,19 @@ constexpr int kPipelineDepth = 3;
 
 struct Slot {
     std::vector<uint8_t *> d_frame;
+    std::vector<uint8_t *> d_undist;     // per camera with a lens model: the undistorted frame the warp reads
     uint8_t *d_canvas = nullptr;
     cudaEvent_t ev_h2d = nullptr, ev_kernel = nullptr, ev_done = nullptr;
     int64_t ticket = -1;
     bool busy = false;
+};
+
+// Lens model of one camera (cv::undistort, tools/stitch/main.cpp:148-149).
+struct LensModel {
+    bool enabled = false;                // false: no model, or all coefficients zero (undistort is then a copy)
+    double fx = 0, fy = 0, u0 = 0, v0 = 0, winv = 1;
+    double k[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // k1 k2 p1 p2 k3 k4 k5 k6
+    double *d_xs = nullptr, *d_ys = nullptr;  // device tables, see stitch_undistort.cuh
 };
 
 }  // namespace
@@ -50,6 +60,8 @@ struct bs_handle {
     std::vector<Slot> ring;
     int64_t next_ticket = 0;
     int64_t kernel_launches = 0;
+    std::vector<LensModel> lens;         // per camera
+    std::vector<uint8_t *> d_undist;     // undistorted frames for bs_submit_device (one set, stream-ordered)
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
     bs::WorkItem *d_items = nullptr;     // plan: work items, heaviest blocks first (same allocation held the raw records)
@@ -359,6 +371,77 @@ int build_plan(bs_handle *h)
 
 bool aligned16(const void *p, size_t pitch) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (pitch & 15) == 0; }
 
+// cv::undistort for the cameras that have a lens model: src frame -> tmp[i]; the pointers the warp
+// should read are returned in out_frames / out_pitch.  Stream-ordered before the frame kernel.
+int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pitch, std::vector<uint8_t *> &tmp,
+                     const void **out_frames, size_t *out_pitch, cudaStream_t stream)
+{
+    for (int i = 0; i < h->n_cams; ++i) {
+        out_frames[i] = d_frames[i];
+        out_pitch[i] = pitch[i];
+        if (h->lens.empty() || !h->lens[i].enabled) continue;
+        const LensModel &m = h->lens[i];
+        if ((int)tmp.size() < h->n_cams) tmp.resize(h->n_cams, nullptr);
+        if (!tmp[i]) {
+            const size_t bytes = h->d_frame_pitch[i] * (size_t)h->sh[i];
+            BS_CUDA(h, cudaMalloc(&tmp[i], bytes));
+            h->device_bytes += bytes;
+        }
+        bs::UndistortArgs U;
+        U.src = static_cast<const uint8_t *>(d_frames[i]);
+        U.dst = tmp[i];
+        U.spitch = (long long)pitch[i];
+        U.dpitch = (long long)h->d_frame_pitch[i];
+        U.w = h->sw[i];
+        U.h = h->sh[i];
+        U.xs = m.d_xs;
+        U.ys = m.d_ys;
+        U.winv = m.winv;
+        U.fx = m.fx;
+        U.fy = m.fy;
+        U.u0 = m.u0;
+        U.v0 = m.v0;
+        U.k1 = m.k[0]; U.k2 = m.k[1]; U.p1 = m.k[2]; U.p2 = m.k[3];
+        U.k3 = m.k[4]; U.k4 = m.k[5]; U.k5 = m.k[6]; U.k6 = m.k[7];
+        bs::undistort_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, stream>>>(U);
+        BS_CUDA(h, cudaGetLastError());
+        h->kernel_launches++;
+        out_frames[i] = tmp[i];
+        out_pitch[i] = h->d_frame_pitch[i];
+    }
+    return BS_OK;
+}
+
+// Host-side tables of the lens model: OpenCV's stripe-wise inverse camera matrix and the running
+// sum it forms along a row (see stitch_undistort.cuh).  Only the usual camera-matrix form is accepted.
+int build_lens_tables(int w, int h, const double K[9], LensModel &m, std::vector<double> &xs, std::vector<double> &ys)
+{
+    if (K[1] != 0.0 || K[3] != 0.0 || K[6] != 0.0 || K[7] != 0.0 || K[8] != 1.0 || K[0] == 0.0 || K[4] == 0.0) return BS_ERR_UNSUPPORTED;
+    m.fx = K[0];
+    m.fy = K[4];
+    m.u0 = K[2];
+    m.v0 = K[5];
+    int stripe0 = 4096 / (w > 1 ? w : 1);
+    if (stripe0 < 1) stripe0 = 1;
+    if (stripe0 > h) stripe0 = h;
+    xs.resize(w);
+    ys.resize(h);
+    for (int ys0 = 0; ys0 < h; ys0 += stripe0) {
+        double Ar[9], ir[9];
+        memcpy(Ar, K, sizeof Ar);
+        Ar[5] = K[5] - ys0;
+        invert3x3(Ar, ir);
+        const int rows = std::min(stripe0, h - ys0);
+        for (int i = 0; i < rows; ++i) ys[ys0 + i] = i * ir[4] + ir[5];
+        if (ys0 == 0) {
+            double _x = 0 * ir[1] + ir[2];
+            for (int j = 0; j < w; ++j, _x += ir[0]) xs[j] = _x;
+            m.winv = 1.0 / (0 * ir[7] + ir[8]);
+        }
+    }
+    return BS_OK;
+}
+
 // Launch the kernels of one frame.  Cameras beyond the per-launch limit go in further
 // launches that keep what is already on the canvas (later cameras win, Appendix A.5).
 int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch, uint8_t *d_canvas,
@@ -561,7 +644,13 @@ int bs_destroy(bs_handle *h)
     if (h->s_h2d) cudaStreamSynchronize(h->s_h2d);
     if (h->s_compute) cudaStreamSynchronize(h->s_compute);
     if (h->s_d2h) cudaStreamSynchronize(h->s_d2h);
+    for (LensModel &m : h->lens) {
+        cudaFree(m.d_xs);
+        cudaFree(m.d_ys);
+    }
+    for (uint8_t *p : h->d_undist) cudaFree(p);
     for (Slot &s : h->ring) {
+        for (uint8_t *p : s.d_undist) cudaFree(p);
         for (uint8_t *p : s.d_frame) cudaFree(p);
         cudaFree(s.d_canvas);
         if (s.ev_h2d) cudaEventDestroy(s.ev_h2d);
@@ -609,9 +698,12 @@ int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
                                      h->H, cudaMemcpyHostToDevice, h->s_h2d));
     BS_CUDA(h, cudaEventRecord(s.ev_h2d, h->s_h2d));
     BS_CUDA(h, cudaStreamWaitEvent(h->s_compute, s.ev_h2d, 0));
-    std::vector<const void *> d_frames(s.d_frame.begin(), s.d_frame.end());
-    rc = launch_frame(h, d_frames.data(), h->d_frame_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep,
-                      h->s_compute);
+    std::vector<const void *> d_frames(s.d_frame.begin(), s.d_frame.end()), warp_frames(h->n_cams);
+    std::vector<size_t> warp_pitch(h->n_cams);
+    rc = undistort_frames(h, d_frames.data(), h->d_frame_pitch.data(), s.d_undist, warp_frames.data(), warp_pitch.data(),
+                          h->s_compute);
+    if (rc != BS_OK) return rc;
+    rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep, h->s_compute);
     if (rc != BS_OK) return rc;
     BS_CUDA(h, cudaEventRecord(s.ev_kernel, h->s_compute));
     BS_CUDA(h, cudaStreamWaitEvent(h->s_d2h, s.ev_kernel, 0));
@@ -664,7 +756,11 @@ int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pi
         return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: canvas_pitch=%zu < %d*3", canvas_pitch, h->W);
     BS_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);   // NULL = the legacy default stream
-    return launch_frame(h, d_frames, pitch, static_cast<uint8_t *>(d_canvas), canvas_pitch,
+    std::vector<const void *> warp_frames(h->n_cams);
+    std::vector<size_t> warp_pitch(h->n_cams);
+    int rc = undistort_frames(h, d_frames, pitch, h->d_undist, warp_frames.data(), warp_pitch.data(), st);
+    if (rc != BS_OK) return rc;
+    return launch_frame(h, warp_frames.data(), warp_pitch.data(), static_cast<uint8_t *>(d_canvas), canvas_pitch,
                         (h->flags & BS_FLAG_KEEP_CANVAS) != 0, st);
 }
 
@@ -677,6 +773,72 @@ int bs_sync(bs_handle *h)
     BS_CUDA(h, cudaStreamSynchronize(h->s_d2h));
     for (Slot &s : h->ring) s.busy = false;
     return BS_OK;
+}
+
+int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dist, int n_dist)
+{
+    if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_set_undistort: NULL handle");
+    if (cam < 0 || cam >= h->n_cams) return fail(h, BS_ERR_INVALID_ARG, "bs_set_undistort: camera %d not in [0, %d)", cam, h->n_cams);
+    if (n_dist < 0 || n_dist > 8 || (n_dist > 0 && !dist))
+        return fail(h, BS_ERR_UNSUPPORTED, "bs_set_undistort: %d distortion coefficients (0..8 supported: k1 k2 p1 p2 k3 k4 k5 k6)", n_dist);
+    BS_CUDA(h, cudaSetDevice(h->device));
+    if (h->lens.empty()) h->lens.resize(h->n_cams);
+    LensModel &m = h->lens[cam];
+    cudaFree(m.d_xs);
+    cudaFree(m.d_ys);
+    m = LensModel();
+    bool nonzero = false;
+    for (int i = 0; i < n_dist; ++i) {
+        m.k[i] = dist[i];
+        nonzero = nonzero || dist[i] != 0.0;
+    }
+    if (!K || !nonzero) return BS_OK;     // cv::undistort with a zero model is an exact copy: nothing to run
+    std::vector<double> xs, ys;
+    if (build_lens_tables(h->sw[cam], h->sh[cam], K, m, xs, ys) != BS_OK)
+        return fail(h, BS_ERR_UNSUPPORTED, "bs_set_undistort: camera matrix must be [[fx 0 cx] [0 fy cy] [0 0 1]]");
+    BS_CUDA(h, cudaMalloc(&m.d_xs, xs.size() * sizeof(double)));
+    BS_CUDA(h, cudaMalloc(&m.d_ys, ys.size() * sizeof(double)));
+    BS_CUDA(h, cudaMemcpy(m.d_xs, xs.data(), xs.size() * sizeof(double), cudaMemcpyHostToDevice));
+    BS_CUDA(h, cudaMemcpy(m.d_ys, ys.data(), ys.size() * sizeof(double), cudaMemcpyHostToDevice));
+    h->device_bytes += (xs.size() + ys.size()) * sizeof(double);
+    m.enabled = true;
+    return BS_OK;
+}
+
+int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, size_t dpitch, const double K[9],
+                 const double *dist, int n_dist)
+{
+    if (!src || !dst || !K) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_undistort: NULL argument");
+    if (w < 1 || h < 1 || w > BS_MAX_DIM || h > BS_MAX_DIM || spitch < (size_t)w * 3 || dpitch < (size_t)w * 3)
+        return fail(nullptr, BS_ERR_INVALID_ARG, "bs_undistort: bad size %dx%d or pitch", w, h);
+    int rc = require_device(nullptr);
+    if (rc != BS_OK) return rc;
+    // a one-camera handle whose canvas is never used: it owns the tables and the buffers
+    const double I[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    bs_handle *hd = nullptr;
+    rc = bs_create(g_last_device, 1, &w, &h, 32, 16, I, BS_FLAG_EXACT_ONLY, &hd);
+    if (rc != BS_OK) return rc;
+    rc = bs_set_undistort(hd, 0, K, dist, n_dist);
+    uint8_t *d_src = nullptr;
+    const size_t pitch = hd->d_frame_pitch[0];
+    cudaError_t e = cudaSuccess;
+    if (rc == BS_OK) {
+        e = cudaMalloc(&d_src, pitch * (size_t)h);
+        if (e == cudaSuccess) e = cudaMemcpy2D(d_src, pitch, src, spitch, (size_t)w * 3, h, cudaMemcpyHostToDevice);
+        const void *in[1] = {d_src};
+        const void *out[1] = {nullptr};
+        size_t out_pitch[1] = {0};
+        if (e == cudaSuccess) rc = undistort_frames(hd, in, &pitch, hd->d_undist, out, out_pitch, hd->s_compute);
+        if (e == cudaSuccess && rc == BS_OK) e = cudaStreamSynchronize(hd->s_compute);
+        if (e == cudaSuccess && rc == BS_OK)
+            e = cudaMemcpy2D(dst, dpitch, out[0], out_pitch[0], (size_t)w * 3, h, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(nullptr, BS_ERR_CUDA, "bs_undistort: %s", cudaGetErrorString(e));
+    } else {
+        g_last_error = hd->err;
+    }
+    cudaFree(d_src);
+    bs_destroy(hd);
+    return rc;
 }
 
 int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8_t *dst, int dw, int dh,

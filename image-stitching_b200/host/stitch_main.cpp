@@ -167,16 +167,15 @@ int main(int argc, char *argv[]) {
   if (bs_create(opts.device, (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags, &h) != BS_OK)
     return fail_bs("bs_create failed", nullptr);
   for (size_t i = 0; i < n; ++i) {
-    // cv::undistort (main.cpp:148-149) is the identity when every distortion coefficient is 0 and
-    // for configs written in image mode (0x0 matrices).  The fused undistort kernel is not in this
-    // build yet: refuse real lens models instead of silently skipping them.
-    const bsfs::Matrix &d = distCoeffs[i];
-    bool nonzero = false;
-    for (double v : d.data) nonzero = nonzero || v != 0.0;
-    if (!cameraMatrix[i].empty() && nonzero) {
-      std::cout << "camera " << i << " has a non-zero lens distortion model; undistort is not supported yet" << std::endl;
+    // cv::undistort(frame, undistorted, cameraMatrix[i], distCoeffs[i]) of main.cpp:148-149 runs on the
+    // GPU in front of the warp.  Configs written in image mode carry 0x0 matrices: nothing to undo.
+    const bsfs::Matrix &K = cameraMatrix[i], &d = distCoeffs[i];
+    if (K.empty()) continue;
+    if (K.rows != 3 || K.cols != 3 ||
+        bs_set_undistort(h, (int)i, K.data.data(), d.empty() ? nullptr : d.data.data(), (int)d.data.size()) != BS_OK) {
+      int rc = fail_bs("bs_set_undistort failed", h);
       bs_destroy(h);
-      return 6;
+      return rc;
     }
   }
 

@@ -127,6 +127,20 @@ int bs_sync(bs_handle *h);
 int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8_t *dst, int dw,
                         int dh, size_t dpitch, const double H[9], unsigned flags);
 
+/*
+ * Lens model of one camera: from then on every frame of that camera is undistorted on the GPU
+ * before it is warped, replacing cv::undistort(frame, undistorted, cameraMatrix[i], distCoeffs[i])
+ * at tools/stitch/main.cpp:148-149 (same fixed-point map and bilinear resampling, BORDER_CONSTANT 0,
+ * SURVEY.md Appendix A.6).  K = fx 0 cx 0 fy cy 0 0 1 (row-major); dist = k1 k2 p1 p2 [k3 [k4 k5 k6]],
+ * n_dist in 0..8 (calibrate writes 8, tools/calibrate/main.cpp:173-178).  A model whose
+ * coefficients are all zero (or K == NULL) disables the step: cv::undistort is then an exact copy.
+ */
+int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dist, int n_dist);
+
+/* Drop-in for ONE cv::undistort(src, dst, K, dist) call on host buffers (main.cpp:148-149). */
+int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, size_t dpitch,
+                 const double K[9], const double *dist, int n_dist);
+
 /* Pinned host memory for frames and panoramas (cudaHostAlloc / cudaFreeHost). */
 void *bs_host_alloc(size_t bytes);
 void bs_host_free(void *p);

@@ -158,14 +158,20 @@ def test_ppm_round_trip(tmp_path):
     assert np.array_equal(read_ppm(tmp_path / "b.ppm"), img)
 
 
-def make_config(path, video, paths, result_wh, Hs):
+def make_config(path, video, paths, result_wh, Hs, Ks=None, dists=None):
+    def mat(m):
+        m = np.atleast_2d(np.asarray(m, float))
+        return ('  <_ type_id="opencv-matrix">\n    <rows>%d</rows>\n    <cols>%d</cols>\n    <dt>d</dt>\n    <data>\n      ' % m.shape
+                + " ".join(repr(float(v)) for v in m.reshape(-1)) + "</data></_>\n")
     mats = "".join(
         '  <_ type_id="opencv-matrix">\n    <rows>3</rows>\n    <cols>3</cols>\n    <dt>d</dt>\n    <data>\n      '
         + " ".join(repr(float(v)) for v in np.asarray(H).reshape(-1)) + "</data></_>\n" for H in Hs)
     empty = "".join('  <_ type_id="opencv-matrix"><rows>0</rows><cols>0</cols><dt>d</dt><data></data></_>\n' for _ in Hs)
+    kmats = "".join(mat(K) for K in Ks) if Ks is not None else empty
+    dmats = "".join(mat(d) for d in dists) if dists is not None else empty
     path.write_text('<?xml version="1.0"?>\n<opencv_storage>\n<video>%d</video>\n<file_paths>\n  %s</file_paths>\n'
                     '<result_size>\n  %d %d</result_size>\n<H>\n%s</H>\n<cameraMatrix>\n%s</cameraMatrix>\n<distCoeffs>\n%s</distCoeffs>\n'
-                    '</opencv_storage>\n' % (video, " ".join(str(p) for p in paths), result_wh[0], result_wh[1], mats, empty, empty))
+                    '</opencv_storage>\n' % (video, " ".join(str(p) for p in paths), result_wh[0], result_wh[1], mats, kmats, dmats))
 
 
 def run_stitch(cwd, *args):
@@ -225,3 +231,24 @@ def test_stitch_tool_video_mode_matches_oracle(tmp_path):
         want = oracle.stitch([frames[0][k + 1], frames[1][k + 1]], Hs, (200, 70))
         assert np.array_equal(read_ppm(tmp_path / f"pano_{k:03d}.ppm"), want), f"frame {k}"
     assert not os.path.exists(tmp_path / f"pano_{n_frames:03d}.ppm")
+
+
+@pytest.mark.gpu
+def test_stitch_tool_video_mode_with_lens_models(tmp_path):
+    # cameraMatrix / distCoeffs as calibrate writes them (8 coefficients, column vector): undistort then warp
+    rng = np.random.default_rng(6)
+    Hs = [np.array([[1.02, 0.0, 2.0], [0.0, 1.02, 1.0], [0, 0, 1.0]]), np.array([[1.0, 0.01, 90.0], [0.0, 1.0, 2.0], [0, 1e-5, 1.0]])]
+    Ks = [np.array([[90.0, 0, 48.5], [0, 91.0, 31.2], [0, 0, 1]]), np.array([[85.0, 0, 47.0], [0, 85.0, 33.0], [0, 0, 1]])]
+    dists = [np.array([-0.2, 0.05, 0.001, -0.002, 0.01, 0, 0, 0]), np.zeros(8)]
+    frames = [[rng.integers(0, 256, (64, 96, 3), dtype=np.uint8) for _ in range(4)] for _ in range(2)]
+    for c in range(2):
+        with open(tmp_path / f"cam{c}.ppms", "wb") as f:
+            for im in frames[c]:
+                f.write(b"P6\n96 64\n255\n" + np.ascontiguousarray(im[:, :, ::-1]).tobytes())
+    cfg = tmp_path / "v.xml"
+    make_config(cfg, 1, [tmp_path / "cam0.ppms", tmp_path / "cam1.ppms"], (200, 70), Hs, Ks, [d.reshape(-1, 1) for d in dists])
+    r = run_stitch(tmp_path, f"--s-conf={cfg}", "--out=u_%03ld.ppm")
+    assert r.returncode == 0, r.stdout + r.stderr
+    for k in range(3):
+        und = [oracle.undistort(frames[c][k + 1], Ks[c], dists[c]) for c in range(2)]
+        assert np.array_equal(read_ppm(tmp_path / f"u_{k:03d}.ppm"), oracle.stitch(und, Hs, (200, 70))), f"frame {k}"

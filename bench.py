@@ -335,8 +335,10 @@ def run_b200(args, rank, local_rank, world):
             t1 = time.perf_counter()
         barrier()
         e2e_s = max_over_ranks(t1 - t0)
+        h2d_per_frame = int(st.stats()["h2d_bytes_last_submit"])     # the plan uploads only what it can read
         e2e = {"value": world * args.steps * Be / e2e_s, "unit": UNIT,
-               "h2d_bytes_per_step": Be * w.src_bytes, "d2h_bytes_per_step": Be * w.canvas_bytes,
+               "h2d_bytes_per_step": Be * h2d_per_frame, "d2h_bytes_per_step": Be * w.canvas_bytes,
+               "h2d_bytes_per_step_full_frames": Be * w.src_bytes,
                "frames_per_step": Be, "pipeline_depth": depth, "ms_per_frame": 1e3 * e2e_s / (args.steps * Be),
                "host_buffers": "pinned (bs_host_alloc)"}
         if rank == 0:   # the last panorama read back must equal the device-resident result

@@ -44,7 +44,8 @@ class Stats(ctypes.Structure):
                 ("n_tiles", ctypes.c_int64), ("n_tiles_fast", ctypes.c_int64),
                 ("n_tiles_exact", ctypes.c_int64), ("n_tiles_empty", ctypes.c_int64),
                 ("kernel_launches", ctypes.c_int64), ("frames_submitted", ctypes.c_int64),
-                ("device_bytes", ctypes.c_uint64), ("scratch_bytes", ctypes.c_uint64)]
+                ("device_bytes", ctypes.c_uint64), ("scratch_bytes", ctypes.c_uint64),
+                ("h2d_bytes_last_submit", ctypes.c_uint64)]
 
 
 _lib = None

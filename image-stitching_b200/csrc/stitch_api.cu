@@ -61,6 +61,7 @@ struct bs_handle {
     int64_t next_ticket = 0;
     int64_t kernel_launches = 0;
     std::vector<LensModel> lens;         // per camera
+    std::vector<int> up_x0, up_y0, up_x1, up_y1;   // per camera: source texels the plan can touch (inclusive); empty = whole frame
     std::vector<uint8_t *> d_undist;     // undistorted frames for bs_submit_device (one set, stream-ordered)
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
@@ -70,6 +71,7 @@ struct bs_handle {
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
     uint64_t device_bytes = 0, scratch_bytes = 0;
+    uint64_t h2d_bytes_last = 0;         // bytes the last bs_submit uploaded
     std::string err;
 };
 
@@ -323,6 +325,25 @@ int build_plan(bs_handle *h)
     layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L);
     memcpy(h->box_we, L.box_we, sizeof h->box_we);
     memcpy(h->box_h, L.box_h, sizeof h->box_h);
+    // Source region each camera can contribute: with no EXACT block (they gather anywhere) it is the
+    // union of the staged boxes' bounding boxes, and bs_submit uploads only that part of every frame.
+    h->up_x0.clear();
+    if (L.n_exact == 0) {
+        h->up_x0.assign(h->n_cams, INT_MAX);
+        h->up_y0.assign(h->n_cams, INT_MAX);
+        h->up_x1.assign(h->n_cams, -1);
+        h->up_y1.assign(h->n_cams, -1);
+        for (const bs::BlockRec &r : recs) {
+            if (r.type != bs::kBlockFast) continue;
+            for (int l = 0; l < r.n_layers; ++l) {
+                const int c = r.layer[l].cam;
+                h->up_x0[c] = std::min(h->up_x0[c], (int)r.layer[l].x0);
+                h->up_y0[c] = std::min(h->up_y0[c], (int)r.layer[l].y0);
+                h->up_x1[c] = std::max(h->up_x1[c], (int)r.layer[l].x1);
+                h->up_y1[c] = std::max(h->up_y1[c], (int)r.layer[l].y1);
+            }
+        }
+    }
     h->stage_bytes = L.stage_bytes;
     h->smem_bytes = L.smem_bytes;
     h->n_items = L.n_items;
@@ -685,13 +706,26 @@ int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
 
     const int64_t t = h->next_ticket;
     Slot &s = h->ring[t % kPipelineDepth];
+    h->h2d_bytes_last = 0;
     if (s.busy) {   // the slot's previous frame must have left the device
         BS_CUDA(h, cudaEventSynchronize(s.ev_done));
         s.busy = false;
     }
-    for (int i = 0; i < h->n_cams; ++i)
-        BS_CUDA(h, cudaMemcpy2DAsync(s.d_frame[i], h->d_frame_pitch[i], frames[i], pitch[i],
-                                     (size_t)h->sw[i] * 3, h->sh[i], cudaMemcpyHostToDevice, h->s_h2d));
+    for (int i = 0; i < h->n_cams; ++i) {
+        int x0 = 0, y0 = 0, x1 = h->sw[i] - 1, y1 = h->sh[i] - 1;
+        const bool whole = !h->fast_ok || h->up_x0.empty() || (!h->lens.empty() && h->lens[i].enabled);
+        if (!whole) {
+            if (h->up_x1[i] < 0) continue;           // this camera contributes nothing to the canvas
+            x0 = (h->up_x0[i] / 64) * 64;            // rows start on a 64-byte boundary of the frame (3 * 64 texel bytes)
+            y0 = h->up_y0[i];
+            x1 = std::min(x1, h->up_x1[i]);
+            y1 = std::min(y1, h->up_y1[i]);
+        }
+        BS_CUDA(h, cudaMemcpy2DAsync(s.d_frame[i] + (size_t)y0 * h->d_frame_pitch[i] + (size_t)x0 * 3, h->d_frame_pitch[i],
+                                     frames[i] + (size_t)y0 * pitch[i] + (size_t)x0 * 3, pitch[i], (size_t)(x1 - x0 + 1) * 3,
+                                     (size_t)(y1 - y0 + 1), cudaMemcpyHostToDevice, h->s_h2d));
+        h->h2d_bytes_last += (uint64_t)(x1 - x0 + 1) * 3 * (uint64_t)(y1 - y0 + 1);
+    }
     const bool keep = (h->flags & BS_FLAG_KEEP_CANVAS) != 0;
     if (keep)
         BS_CUDA(h, cudaMemcpy2DAsync(s.d_canvas, h->d_canvas_pitch, out, out_pitch, (size_t)h->W * 3,
@@ -899,6 +933,7 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
     out->frames_submitted = h->next_ticket;
     out->device_bytes = h->device_bytes;
     out->scratch_bytes = h->scratch_bytes;
+    out->h2d_bytes_last_submit = h->h2d_bytes_last;
     return BS_OK;
 }
 

@@ -63,6 +63,8 @@ typedef struct bs_stats {
     int64_t frames_submitted;
     uint64_t device_bytes;    /* device memory owned by the handle */
     uint64_t scratch_bytes;   /* of which plan/scratch */
+    uint64_t h2d_bytes_last_submit; /* bytes the last bs_submit copied to the device: only the part
+                                       of every frame the plan can read is uploaded */
 } bs_stats;
 
 /* Number of CUDA devices visible; 0 if none (never negative). */
@@ -91,7 +93,8 @@ int bs_destroy(bs_handle *h);
  * tools/stitch/main.cpp:145-152 (video mode) / :113-121 (image mode): N warps into one canvas,
  * highest camera index wins in overlaps.  frames[i]/pitch[i] are packed BGR rows of camera i;
  * `out` receives canvas_h rows of canvas_w*3 bytes at out_pitch.  All host pointers must stay
- * valid until bs_wait(ticket).  Pinned buffers (bs_host_alloc) are copied by DMA directly;
+ * valid until bs_wait(ticket).  Only the region of each frame that the calibration can map into the
+ * canvas is copied to the device.  Pinned buffers (bs_host_alloc) are copied by DMA directly;
  * pageable ones work but copy slower.  Up to bs_pipeline_depth() frames may be in flight.
  */
 int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, uint8_t *out,

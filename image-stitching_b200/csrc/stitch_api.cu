@@ -65,8 +65,9 @@ struct bs_handle {
     std::vector<uint8_t *> d_undist;     // undistorted frames for bs_submit_device (one set, stream-ordered)
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
-    bs::WorkItem *d_items = nullptr;     // plan: work items, heaviest blocks first (same allocation held the raw records)
-    int n_blocks = 0, blocks_x = 0, blocks_y = 0, n_items = 0, n_two = 0;
+    bs::WorkItem *d_items = nullptr;     // plan: work items grouped by warp (same allocation held the raw records)
+    int *d_warp_start = nullptr;         // item range of every warp of the grid
+    int n_blocks = 0, blocks_x = 0, blocks_y = 0, n_items = 0;
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
@@ -96,6 +97,15 @@ int fail(bs_handle *h, int code, const char *fmt, ...)
             return fail(h, BS_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), \
                         __FILE__, __LINE__);                                                  \
     } while (0)
+
+// Host -> device copy that is complete when it returns.  (A plain cudaMemcpy from pageable memory
+// may return while the DMA out of the driver's staging buffer is still running, and the handle's
+// streams are non-blocking, so a kernel on them would not wait for it.)
+cudaError_t upload_now(bs_handle *h, void *dst, const void *src, size_t bytes)
+{
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, h->s_compute);
+    return e == cudaSuccess ? cudaStreamSynchronize(h->s_compute) : e;
+}
 
 // 3x3 inverse as cv::invert computes it for a 3x3 CV_64F matrix: cofactors times 1/det.
 // (cv::warpPerspective inverts H on entry because the reference passes the forward map,
@@ -236,7 +246,7 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
         stage = std::max(stage, we[c] * 4 * bh[c]);
     }
     L->stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
-    L->smem_bytes = 2 * bs::kLutBytes + bs::kWarpsPerCta * bs::warp_smem_bytes(L->stage_bytes) + 64;   // table + 8 KB alignment slack
+    L->smem_bytes = bs::kWarpsPerCta * bs::warp_smem_bytes(L->stage_bytes) + 128;   // + alignment slack
     L->n_fast = L->n_exact = L->n_empty = 0;
     int n = 0;
     auto emit = [&](const bs::BlockRec &r, int l) {
@@ -274,6 +284,24 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
     for (int t = 0; t < n_blocks; ++t)
         if (recs[t].type == bs::kBlockEmpty) emit(recs[t], 0), L->n_empty++;
     L->n_items = n;
+}
+
+// Deal the plan's blocks round-robin to the n_warps warps of the grid (block u to warp u mod n_warps;
+// `in` lists the heaviest blocks first, so they spread evenly) and store every warp's items
+// contiguously in `out`.  warp_start has n_warps + 1 entries.  `in` holds the n_two two-layer blocks
+// first (two adjacent items each), then one item per block.
+void group_items_by_warp(const bs::WorkItem *in, int n_units, int n_two, int n_warps, bs::WorkItem *out, int *warp_start)
+{
+    int n = 0;
+    for (int w = 0; w < n_warps; ++w) {
+        warp_start[w] = n;
+        for (int u = w; u < n_units; u += n_warps) {
+            const int first = u + std::min(u, n_two);
+            out[n++] = in[first];
+            if (u < n_two) out[n++] = in[first + 1];
+        }
+    }
+    warp_start[n_warps] = n;
 }
 
 // Build the block plan on the device and post-process it on the host (once per calibration).
@@ -382,10 +410,18 @@ int build_plan(bs_handle *h)
     if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
     h->grid = std::max(1, std::min((h->n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
     if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
-    h->n_two = L.n_two;
+    const int n_warps = h->grid * bs::kWarpsPerCta;
+    std::vector<bs::WorkItem> grouped(items.size());
+    std::vector<int> warp_start(n_warps + 1);
+    group_items_by_warp(items.data(), h->n_blocks, L.n_two, n_warps, grouped.data(), warp_start.data());
 
     const size_t item_bytes = sizeof(bs::WorkItem) * (size_t)h->n_items;   // <= raw_bytes: 2 x 80 B per block
-    BS_CUDA(h, cudaMemcpy(h->d_items, items.data(), item_bytes, cudaMemcpyHostToDevice));
+    BS_CUDA(h, upload_now(h, h->d_items, grouped.data(), item_bytes));
+    const size_t ws_bytes = sizeof(int) * (size_t)(n_warps + 1);
+    BS_CUDA(h, cudaMalloc(&h->d_warp_start, ws_bytes));
+    BS_CUDA(h, upload_now(h, h->d_warp_start, warp_start.data(), ws_bytes));
+    h->device_bytes += ws_bytes;
+    h->scratch_bytes += ws_bytes;
     h->fast_ok = true;
     return BS_OK;
 }
@@ -505,8 +541,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = keep ? 1 : 0;
         FA.items = h->d_items;
-        FA.n_units = h->n_blocks;
-        FA.n_two = h->n_two;
+        FA.warp_start = h->d_warp_start;
         FA.stage_bytes = h->stage_bytes;
         {
             // programmatic dependent launch: the prologue and first tile of this frame may overlap the
@@ -679,6 +714,7 @@ int bs_destroy(bs_handle *h)
         if (s.ev_done) cudaEventDestroy(s.ev_done);
     }
     cudaFree(h->d_items);
+    cudaFree(h->d_warp_start);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
@@ -832,8 +868,8 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
         return fail(h, BS_ERR_UNSUPPORTED, "bs_set_undistort: camera matrix must be [[fx 0 cx] [0 fy cy] [0 0 1]]");
     BS_CUDA(h, cudaMalloc(&m.d_xs, xs.size() * sizeof(double)));
     BS_CUDA(h, cudaMalloc(&m.d_ys, ys.size() * sizeof(double)));
-    BS_CUDA(h, cudaMemcpy(m.d_xs, xs.data(), xs.size() * sizeof(double), cudaMemcpyHostToDevice));
-    BS_CUDA(h, cudaMemcpy(m.d_ys, ys.data(), ys.size() * sizeof(double), cudaMemcpyHostToDevice));
+    BS_CUDA(h, upload_now(h, m.d_xs, xs.data(), xs.size() * sizeof(double)));
+    BS_CUDA(h, upload_now(h, m.d_ys, ys.data(), ys.size() * sizeof(double)));
     h->device_bytes += (xs.size() + ys.size()) * sizeof(double);
     m.enabled = true;
     return BS_OK;
@@ -858,7 +894,7 @@ int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, 
     cudaError_t e = cudaSuccess;
     if (rc == BS_OK) {
         e = cudaMalloc(&d_src, pitch * (size_t)h);
-        if (e == cudaSuccess) e = cudaMemcpy2D(d_src, pitch, src, spitch, (size_t)w * 3, h, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy2DAsync(d_src, pitch, src, spitch, (size_t)w * 3, h, cudaMemcpyHostToDevice, hd->s_compute);
         const void *in[1] = {d_src};
         const void *out[1] = {nullptr};
         size_t out_pitch[1] = {0};
@@ -964,9 +1000,11 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 
 namespace {
 
+constexpr int kStaticMaxWarps = 8191;   // warps of the grid the table below has room for (B200: 148 x 2 x 8 = 2368)
 struct StaticScratch {
     // raw block records from the plan kernel; then overwritten by the work items (at most 2 x 80 bytes per block)
     bs::BlockRec plan[BS_STATIC_MAX_BLOCKS];
+    int warp_start[kStaticMaxWarps + 1];
 };
 static_assert(sizeof(StaticScratch) == BS_STATIC_SCRATCH_BYTES, "BS_STATIC_SCRATCH_BYTES is out of date");
 static_assert(sizeof(bs::WorkItem) * bs::kMaxLayers <= sizeof(bs::BlockRec), "items must fit where the raw records were");
@@ -986,6 +1024,8 @@ StaticDeviceState g_static_dev[kStaticMaxDevices];
 std::mutex g_static_mutex;                            // host side of the sharing; the GPU side is the caller's job
 bs::BlockRec g_static_recs[BS_STATIC_MAX_BLOCKS];     // host staging for the plan, fixed size (no heap)
 bs::WorkItem g_static_items[BS_STATIC_MAX_BLOCKS * bs::kMaxLayers];
+bs::WorkItem g_static_grouped[BS_STATIC_MAX_BLOCKS * bs::kMaxLayers];
+int g_static_warp_start[kStaticMaxWarps + 1];
 bs::PlanArgs g_static_plan_args;
 
 // Once per device, with that device current.
@@ -1125,13 +1165,17 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
             if (er != 0) return fail(nullptr, BS_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d) for camera %d", me, er, i);
         }
     }
-    const int grid = std::max(1, std::min((n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
+    int grid = std::max(1, std::min((n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
+    grid = std::min(grid, kStaticMaxWarps / bs::kWarpsPerCta);
+    const int n_warps = grid * bs::kWarpsPerCta;
+    group_items_by_warp(g_static_items, n_blocks, L.n_two, n_warps, g_static_grouped, g_static_warp_start);
     // the item list replaces the raw records in the scratch; stream-ordered after the previous call's kernels
-    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_items, sizeof(bs::WorkItem) * (size_t)L.n_items,
+    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_grouped, sizeof(bs::WorkItem) * (size_t)L.n_items,
+                                     cudaMemcpyHostToDevice, s));
+    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->warp_start, g_static_warp_start, sizeof(int) * (size_t)(n_warps + 1),
                                      cudaMemcpyHostToDevice, s));
     FA.items = reinterpret_cast<const bs::WorkItem *>(st->scratch->plan);
-    FA.n_units = n_blocks;
-    FA.n_two = L.n_two;
+    FA.warp_start = st->scratch->warp_start;
     FA.stage_bytes = L.stage_bytes;
     bs::stitch_fast_kernel<<<grid, bs::kFastThreads, L.smem_bytes, s>>>(FA);
     BS_CUDA(nullptr, cudaGetLastError());

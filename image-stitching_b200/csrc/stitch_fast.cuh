@@ -8,9 +8,9 @@
 //      stage with one TMA tensor copy (cp.async.bulk.tensor.2d) signalled on its own mbarrier --
 //      lane 0 is the producer, nothing is shared with other warps, so no warp ever waits for one;
 //   2. computes one vertical run of 16 canvas pixels per lane: coordinates from the plan-verified
-//      fp32 recurrence (or exact fp64 where the plan says so), 2x3 aligned words per pixel from the
-//      staged box, OpenCV's fixed-point bilinear weights from a 1024-entry table, three channel dot
-//      products (dp4a) -- bit-identical to (sum w*S + 2^14) >> 15;
+//      fp32 expansion (or exact fp64 where the plan says so), 2x3 aligned words per pixel from the
+//      staged box, OpenCV's fixed-point bilinear weights computed from the fractions, three channel dot
+//      products (dp2a) -- bit-identical to (sum w*S + 2^14) >> 15;
 //   3. after the block's last layer, writes the finished 16x96-byte block to the canvas as 16-byte
 //      vector stores.
 // EXACT blocks run the per-pixel fp64 path of stitch_exact.cuh; EMPTY blocks are zero-filled.
@@ -23,15 +23,13 @@
 
 namespace bs {
 
-constexpr int kLutBytes = 1024 * 8;
 constexpr int kStagePad = 128;                       // slack behind a stage for the 3rd word of the last texel
 
 struct FastArgs {
     FrameArgs F;
     CUtensorMap tmap[kMaxCamsPerLaunch];   // source frame of camera i as a [h][pitch/4] u32 tensor
-    const WorkItem *items;                 // the plan, flattened: blocks with two layers first (two adjacent items each)
-    int n_units;                           // blocks in the plan
-    int n_two;                             // of which the first n_two have two items
+    const WorkItem *items;                 // the plan, flattened and grouped by warp: warp w owns items
+    const int *warp_start;                 //   [warp_start[w], warp_start[w+1]); a block's layers are adjacent
     int pitch[kMaxCamsPerLaunch];          // TMA box of camera i: row pitch in shared memory (bytes) ...
     int box_bytes[kMaxCamsPerLaunch];      // ... and total bytes (= what the mbarrier expects)
     int stage_bytes;                       // shared memory per stage (multiple of 128)
@@ -95,48 +93,49 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr)
     return v;
 }
 
-// Weight table entry for fractional position (a, b), a = X & 31, b = Y & 31.
+// Bilinear weights for fractional position (a, b), a = X & 31, b = Y & 31, as dp2a wants them.
 // w' = w / 32 are OpenCV's 15-bit weights without their common factor 32; they sum to 1024.
-// Entry = { bytes of w' >> 2, bytes of (w' & 3) << 6 } in tap order 00, 01, 10, 11, so that
-//   256 * dp4a(S, hi) + dp4a(S, lo) = 64 * sum(w' S),  and byte 2 of (that + 2^15) is the pixel.
-// (a, b) = (0, 0) would need w'00 = 1024 (9 bits after >> 2); 1023 gives the same pixel for
-// every S in 0..255: (1023 S + 512) >> 10 == S.
-__device__ __forceinline__ uint2 lut_entry(int idx)
+// Result = { 64 w'00 | 64 w'01 << 16, 64 w'10 | 64 w'11 << 16 }, so that
+//   sum(64 w' S) + 2^15 = 2 (sum(w S) + 2^14)  has the pixel in byte 2.
+// Computed, not looked up: a 1024-entry table in shared memory cost 4-5 wavefronts per warp and
+// pixel row (bank conflicts) on a shared-memory pipe that was 80 % busy.  (tests/test_fixed_point_identity.py
+// mirrors this function, wrap-around included.)
+// (a, b) = (0, 0) would need 64 w'00 = 65536; 65535 gives the same pixel for every S in 0..255:
+// (65535 S + 2^15) >> 16 == S  because  0 < 2^15 - S < 2^16.
+__device__ __forceinline__ uint2 tap_weights(uint32_t a, uint32_t b)
 {
-    const int a = idx & 31, b = idx >> 5;
-    int w[4] = {(32 - a) * (32 - b), a * (32 - b), (32 - a) * b, a * b};
-    if (w[0] == 1024) w[0] = 1023;
-    uint2 e = make_uint2(0u, 0u);
-#pragma unroll
-    for (int t = 0; t < 4; ++t) {
-        e.x |= (uint32_t)(w[t] >> 2) << (8 * t);
-        e.y |= (uint32_t)((w[t] & 3) << 6) << (8 * t);
-    }
-    return e;
+    const uint32_t a2 = a * (0xFFFFu * 64u) + 2048u;   // 64 (32 - a) | 64 a << 16; no product below carries between halves ...
+    const uint32_t w23 = b * a2;
+    uint32_t w01 = a2 * 32u - w23;
+    if (w01 == 0x10000u) w01 = 0xFFFFu;                // ... except 64 * 32 * 32 at (0, 0)
+    return make_uint2(w01, w23);
 }
 
 // The twelve tap bytes of one interior pixel as they come out of shared memory, plus its weights.
 struct Taps {
     uint32_t w0, w1, w2;   // three aligned words of source row sy starting at the word that holds texel sx
     uint32_t v0, v1, v2;   // same for row sy + 1
-    uint2 wt;              // weight-table entry
+    uint2 wt;              // tap_weights()
     uint32_t sh;           // 8 * (byte offset of texel sx in w0); the funnel shifter uses the low 5 bits
 };
 
-// `o` = shared byte address of texel (sx, sy) (any alignment), `pitch` = stage row pitch in bytes,
-// `lut_off` = shared address of the weight-table entry.
-__device__ __forceinline__ Taps fetch_taps(uint32_t o, int pitch, uint32_t lut_off)
+// `o` = shared byte address of texel (sx, sy) (any alignment), `pitch` = stage row pitch in bytes.
+__device__ __forceinline__ Taps fetch_taps(uint32_t o, int pitch, uint2 wt)
 {
     Taps t;
     const uint32_t wa = o & ~3u;
     t.sh = o << 3;
+#ifdef BS_ABLATE_LDS
+    t.w0 = wa; t.w1 = wa + 1; t.w2 = wa + 2; t.v0 = wa + 3; t.v1 = wa + 4; t.v2 = wa + 5; t.wt = wt;
+    return t;
+#endif
     t.w0 = lds32(wa);
     t.w1 = lds32(wa + 4);
     t.w2 = lds32(wa + 8);
     t.v0 = lds32(wa + pitch);
     t.v1 = lds32(wa + pitch + 4);
     t.v2 = lds32(wa + pitch + 8);
-    t.wt = lds64(lut_off);
+    t.wt = wt;
     return t;
 }
 
@@ -144,26 +143,26 @@ __device__ __forceinline__ Taps fetch_taps(uint32_t o, int pitch, uint32_t lut_o
 // Returns B | G<<8 | R<<16.
 __device__ __forceinline__ uint32_t blend_taps(const Taps &t)
 {
+#ifdef BS_ABLATE_BLEND
+    return (t.w0 ^ t.w1 ^ t.w2 ^ t.v0 ^ t.v1 ^ t.v2 ^ t.wt.x ^ t.wt.y) + t.sh;
+#endif
     // six aligned bytes of each row: r?a = [B0 G0 R0 B1], r?b = [G1 R1 . .]
     const uint32_t r0a = __funnelshift_r(t.w0, t.w1, t.sh), r0b = __funnelshift_r(t.w1, t.w2, t.sh);
     const uint32_t r1a = __funnelshift_r(t.v0, t.v1, t.sh), r1b = __funnelshift_r(t.v1, t.v2, t.sh);
-    // transpose to one word per channel, taps in order 00 01 10 11
-    const uint32_t qb = __byte_perm(r0a, r1a, 0x7430);
-    const uint32_t t0 = __byte_perm(r0a, r0b, 0x5241);   // [G00 G01 R00 R01]
-    const uint32_t t1 = __byte_perm(r1a, r1b, 0x5241);   // [G10 G11 R10 R11]
-    const uint32_t qg = __byte_perm(t0, t1, 0x5410);
-    const uint32_t qr = __byte_perm(t0, t1, 0x7632);
-    const uint32_t vb = __dp4a(qb, t.wt.x, 128u) * 256u + __dp4a(qb, t.wt.y, 0u);
-    const uint32_t vg = __dp4a(qg, t.wt.x, 128u) * 256u + __dp4a(qg, t.wt.y, 0u);
-    const uint32_t vr = __dp4a(qr, t.wt.x, 128u) * 256u + __dp4a(qr, t.wt.y, 0u);
+    // pair the two taps of a row per channel, as dp2a wants them
+    const uint32_t p0 = __byte_perm(r0a, r0b, 0x4130), q0 = __byte_perm(r0a, r0b, 0x5252);   // [B00 B01 G00 G01], [R00 R01 ..]
+    const uint32_t p1 = __byte_perm(r1a, r1b, 0x4130), q1 = __byte_perm(r1a, r1b, 0x5252);   // same for row 1
+    const uint32_t vb = __dp2a_lo(t.wt.y, p1, __dp2a_lo(t.wt.x, p0, 32768u));
+    const uint32_t vg = __dp2a_hi(t.wt.y, p1, __dp2a_hi(t.wt.x, p0, 32768u));
+    const uint32_t vr = __dp2a_lo(t.wt.y, q1, __dp2a_lo(t.wt.x, q0, 32768u));
     // results sit in byte 2 of vb, vg, vr; byte 3 is always 0
     const uint32_t bg = __byte_perm(vb, vg, 0x3362);
     return __byte_perm(bg, vr, 0x7610);
 }
 
-__device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint32_t lut_off)
+__device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint2 wt)
 {
-    return blend_taps(fetch_taps(o, pitch, lut_off));
+    return blend_taps(fetch_taps(o, pitch, wt));
 }
 
 // Store one row's pixel of every lane into the warp's output block: lanes 4q..4q+3 hold 4 adjacent
@@ -171,6 +170,10 @@ __device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint32_
 // neighbour's and stores it.  `row_addr` = shared address of the block row (96 bytes).
 __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, int lane, uint32_t sel)
 {
+#ifdef BS_ABLATE_STORE
+    if (px == 0x12345678u) asm volatile("st.shared.u32 [%0], %1;" ::"r"(row_addr), "r"(px) : "memory");
+    return;
+#endif
     const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
     const uint32_t word = __byte_perm(px, nxt, sel);
     if ((lane & 3) != 3)
@@ -184,12 +187,17 @@ constexpr int kFastThreads = 32 * kWarpsPerCta;
 #ifndef BS_MIN_CTAS
 #define BS_MIN_CTAS 2
 #endif
-constexpr int kStages = 2;                             // per warp: source boxes of items i and i+1
-constexpr int kRecSlots = 4;                           // per warp: records of items i .. i+3
+#ifndef BS_STAGES
+#define BS_STAGES 2
+#endif
+constexpr int kStages = BS_STAGES;                     // per warp: source boxes of items i .. i + kStages - 1
+constexpr int kPrefetch = kStages - 1;                 // boxes in flight ahead of the one being computed
+constexpr int kRecSlots = 16;                          // per warp: record ring, refilled in halves of 8 by one bulk copy each
+constexpr int kRecHalf = kRecSlots / 2;
 constexpr int kBlockRowBytes = 96;                     // 32 pixels
 constexpr int kWarpOutBytes = kRun * kBlockRowBytes;   // 1536
 constexpr int kRecBytes = 80;                          // sizeof(WorkItem)
-constexpr int kWarpCtlBytes = (kRecSlots * kRecBytes + (kStages + kRecSlots) * 8 + 127) / 128 * 128;   // records + mbarriers, keeps every warp's region 128-byte aligned
+constexpr int kWarpCtlBytes = (kRecSlots * kRecBytes + (kStages + 2) * 8 + 127) / 128 * 128;   // records + mbarriers, keeps every warp's region 128-byte aligned
 
 __host__ __device__ constexpr int warp_smem_bytes(int stage_bytes)
 {
@@ -213,23 +221,19 @@ __device__ __forceinline__ BlockCoef load_block_coef(uint32_t rec_addr)
 // Hot path: the layer covers every pixel of the block with interior samples, the block lies inside
 // the canvas and the plan verified the cheap coordinates for the whole block.  No coverage tests,
 // no fp64; fully unrolled so the row offset v is a constant.
-__device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, uint32_t stage_origin, uint32_t lut_base,
+__device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, uint32_t stage_origin,
                                                uint32_t out_blk, int lane)
 {
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
     const uint32_t run_base = stage_origin + (uint32_t)((lc.by >> kFracBits) * pitch + (lc.bx >> kFracBits) * 3);
     const int step = lc.nyv * pitch + lc.nxv * 3;      // whole texels per canvas row, as a byte offset
-    // software pipeline: the shared-memory loads of pixel k+1 are issued before the arithmetic of
-    // pixel k, so a warp has work to do while its loads are in flight
     auto fetch = [&](int k) {
         const int v = k - kRun / 2;
         int xbits, ybits;
         lane_coord_bits(lc, (float)v, xbits, ybits);
         const uint32_t o = run_base + (uint32_t)(v * step) +
                            (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
-        // the table sits on an 8 KB boundary, so its base can be OR-ed in after masking the index
-        const uint32_t lut_off = lut_base | ((uint32_t)((ybits << 8) + ((xbits << 3) & 0xF8)) & 0x1FF8u);
-        return fetch_taps(o, pitch, lut_off);
+        return fetch_taps(o, pitch, tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     Taps cur = fetch(0);
 #pragma unroll
@@ -246,7 +250,7 @@ __device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, ui
 // the plan found at least one pixel where the cheap coordinates differ (those 32x4 groups use
 // the exact fp64 form).  Same arithmetic per pixel, with coverage tests and byte stores.
 __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &cam, const LaneCoef &lc, int pitch,
-                                               uint32_t stage_origin, uint32_t lut_base, uint32_t out_blk,
+                                               uint32_t stage_origin, uint32_t out_blk,
                                                uint32_t group_mask, bool full, bool first_layer, int x, int y0, int lane)
 {
     const int xb = (x / A.F.block_w) * A.F.block_w;
@@ -266,8 +270,7 @@ __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &
         bool in = (x < A.F.W) && (y0 + k < A.F.H);
         if (!full) in = in && sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1;
         const uint32_t o = in ? stage_origin + (uint32_t)(sy * pitch + sx * 3) : out_blk;   // any valid address
-        const uint32_t lut_off = lut_base + (uint32_t)((((Y & 31) << 5) | (X & 31)) << 3);
-        uint32_t px = sample_staged(o, pitch, lut_off);
+        uint32_t px = sample_staged(o, pitch, tap_weights((uint32_t)X & 31u, (uint32_t)Y & 31u));
         // the first layer also defines the background: pixels it does not cover start at 0
         if (in || first_layer) {
             if (!in) px = 0;
@@ -292,6 +295,21 @@ __device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity)
         "}" ::"r"(bar),
         "r"(parity), "r"(20000u)   // suspend-time hint (ns): sleep in hardware, woken by the completing arrive
         : "memory");
+}
+// One probe of the barrier; lets independent work be issued before the result is needed.
+__device__ __forceinline__ bool mbar_try_wait_addr(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, P1;\n"
+        "}"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
 }
 __device__ __forceinline__ void mbar_arrive_addr(uint32_t bar)
 {
@@ -326,70 +344,57 @@ __device__ __noinline__ void store_block_checked(const FrameArgs &F, uint32_t sr
 __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(const __grid_constant__ FastArgs A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    // layout: [pad to an 8 KB boundary][weight table 8 KB][per warp: kStages stages | output block | records | mbarriers]
-    const uint32_t raw_base = smem_u32(smem_raw);
-    const uint32_t lut_base = (raw_base + 8191u) & ~8191u;
+    // layout: [pad to a 128-byte boundary][per warp: kStages stages | output block | records | mbarriers]
+    const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const uint32_t wbase = lut_base + kLutBytes + (uint32_t)(warp * warp_smem_bytes(A.stage_bytes));
+    const uint32_t wbase = raw_base + (uint32_t)(warp * warp_smem_bytes(A.stage_bytes));
     const uint32_t stage0 = wbase;                                             // 128-byte aligned
     const uint32_t out_blk = stage0 + (uint32_t)(kStages * A.stage_bytes);
     const uint32_t rec0 = out_blk + kWarpOutBytes;
     const uint32_t dbar0 = rec0 + kRecSlots * kRecBytes;                       // data barriers, one per stage
-    const uint32_t rbar0 = dbar0 + kStages * 8;                                // record barriers, one per slot
+    const uint32_t rbar0 = dbar0 + kStages * 8;                                // record barriers, one per half of the ring
 
     // Programmatic dependent launch: let the next frame's kernel start filling SMs as this one's CTAs
     // retire.  It may prefetch and composite, but touches the canvas only after griddepcontrol.wait,
     // i.e. after this grid has completed.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    {
-        uint2 *lut = reinterpret_cast<uint2 *>(smem_raw + (lut_base - raw_base));
-        for (int i = tid; i < 1024; i += kFastThreads) lut[i] = lut_entry(i);
-    }
+#ifdef BS_ABLATE_KERNEL
+    if (A.stage_bytes >= 0) return;
+#endif
     if (lane == 0) {
         for (int s = 0; s < kStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dbar0 + 8 * s), "r"(1));
-        for (int s = 0; s < kRecSlots; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
+        for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    // Work split: block u of the plan goes to warp u mod W (W = warps in the grid).  The plan lists the
-    // heaviest blocks first, so they spread evenly and no cost model is needed; at any moment the grid
-    // works on W consecutive blocks, i.e. on neighbouring pixels, which keeps box overlaps in L2.
-    const int W = (int)gridDim.x * kWarpsPerCta;
+    // Work split: the host deals the plan's blocks round-robin to the warps of the grid (block u to
+    // warp u mod W, heaviest blocks first, so they spread evenly and at any moment the grid works on W
+    // neighbouring blocks) and stores every warp's items contiguously.
     const int gw = (int)blockIdx.x * kWarpsPerCta + warp;
-    if (gw >= A.n_units) return;
-    const int my_units = (A.n_units - 1 - gw) / W + 1;
-    const int my_two = gw < A.n_two ? (A.n_two - 1 - gw) / W + 1 : 0;
-    const int i0 = 0, i1 = my_units + my_two;       // this warp's items, numbered locally
-    // cursor over this warp's items in order, used by lane 0 to fetch records ahead
-    int cur_unit = gw, cur_layer = 0;
-    auto next_item_index = [&]() {                  // global index of the cursor's item; then advance
-        const int idx = cur_unit + min(cur_unit, A.n_two) + cur_layer;
-        if (cur_layer == 0 && cur_unit < A.n_two) cur_layer = 1;
-        else {
-            cur_layer = 0;
-            cur_unit += W;
-        }
-        return idx;
-    };
+    const int i0 = A.warp_start[gw];
+    const int cnt = A.warp_start[gw + 1] - i0;      // this warp's items, numbered n = 0 .. cnt-1
+    if (cnt <= 0) return;
 
     // lane 0 is this warp's producer ------------------------------------------------------------------
-    // record of item i -> record slot, by an 80-byte bulk copy
-    auto request_record = [&](uint32_t slot) {
-        const int i = next_item_index();
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * slot), "r"((uint32_t)kRecBytes)
-                     : "memory");
+    // records of items [first, first + 8) -> their half of the record ring, one bulk copy
+    auto request_records = [&](int first) {
+        const uint32_t bytes = (uint32_t)(min(kRecHalf, cnt - first) * kRecBytes);
+        const uint32_t half = ((uint32_t)first / kRecHalf) & 1u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * half), "r"(bytes) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         rec0 + kRecBytes * slot),
-                     "l"(A.items + i), "r"((uint32_t)kRecBytes), "r"(rbar0 + 8 * slot)
+                         rec0 + kRecBytes * kRecHalf * half),
+                     "l"(A.items + i0 + first), "r"(bytes), "r"(rbar0 + 8 * half)
                      : "memory");
     };
-    // source box of the item whose record sits in `slot` -> stage; items without a box just arrive
-    auto issue_box = [&](uint32_t slot, uint32_t rec_parity, uint32_t stage) {
-        mbar_wait_addr(rbar0 + 8 * slot, rec_parity);
-        const uint4 r = lds128(rec0 + kRecBytes * slot);
+    // source box of the item whose record words are `r` -> stage; items without a box just arrive
+    auto issue_box = [&](const uint4 &r, uint32_t stage) {
+#ifdef BS_ABLATE_TMA
+        if (false) {
+#else
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
+#endif
             const uint32_t cam = (r.y >> 16) & 0xFFu;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
                          "r"((uint32_t)A.box_bytes[cam])
@@ -403,35 +408,52 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             mbar_arrive_addr(dbar0 + 8 * stage);
         }
     };
+    // record words / lane coefficients of item m from the record ring (all lanes)
+    auto rec_addr = [&](int m) { return rec0 + kRecBytes * ((uint32_t)m & (kRecSlots - 1)); };
+    auto wait_half_of = [&](int m) {      // first item of a half: every lane observes the copy's completion itself
+        if ((m & (kRecHalf - 1)) == 0) mbar_wait_addr(rbar0 + 8 * (((uint32_t)m / kRecHalf) & 1u), ((uint32_t)m / kRecSlots) & 1u);
+    };
+
     if (lane == 0) {
-        for (int d = 0; d < 3 && i0 + d < i1; ++d) request_record((uint32_t)d);
-        issue_box(0u, 0u, 0u);
+        request_records(0);
+        if (cnt > kRecHalf) request_records(kRecHalf);
     }
+    __syncwarp();
+    wait_half_of(0);
+    // The per-item set-up is software-pipelined across items: while item n is computed, the record of
+    // item n+2 and the lane coefficients of item n+1 are already being read, and the box of item n+1
+    // is in flight.
+    uint4 rec = lds128(rec_addr(0));
+    uint4 recn = cnt > 1 ? lds128(rec_addr(1)) : rec;
+    LaneCoef lc = lane_coef(load_block_coef(rec_addr(0)), lane - kBlockW / 2);
+    if (lane == 0) issue_box(rec, 0u);
     __syncwarp();
 
     bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
     bool wrote = false;               // some layer has written into the current block
-    uint32_t stage = 0, dpar = 0;     // stage and data-barrier parity of the current item
-    uint32_t slot = 0, rpar = 0;      // record slot and record-barrier parity of the current item
-    uint32_t pstage = 1, pslot = 1, ppar = 0;   // producer cursor: item i+1 (its stage, record slot, record parity)
-    for (int i = i0; i < i1; ++i) {
+    uint32_t stage = 0, dpar = 0;     // stage and data-barrier parity of the current item (kStages == 2)
+    static_assert(kStages == 2, "the item pipeline below is written for two stages");
+    for (int n = 0; n < cnt; ++n) {
         if (lane == 0) {
-            // prefetch: the box of item i+1 goes into the other stage (item i-1 is done with it), the
-            // record of item i+3 into the slot item i-1 used
-            if (i + 1 < i1) issue_box(pslot, ppar, pstage);
-            if (i + 3 < i1) request_record((pslot + 2) & (kRecSlots - 1));
-        }
-        if (++pstage == kStages) pstage = 0;
-        if (++pslot == kRecSlots) {
-            pslot = 0;
-            ppar ^= 1u;
+            // the half of the record ring that items n-8 .. n-1 used is free: refill it with n+8 .. n+15
+            if ((n & (kRecHalf - 1)) == 0 && n >= kRecHalf && n + kRecHalf < cnt) request_records(n + kRecHalf);
+            // prefetch: the box of item n+1 goes into the stage item n-1 is done with
+            if (n + 1 < cnt) issue_box(recn, stage ^ 1u);
         }
         __syncwarp();
-        mbar_wait_addr(rbar0 + 8 * slot, rpar);
-        const uint4 r = lds128(rec0 + kRecBytes * slot);
+        const bool landed = mbar_try_wait_addr(dbar0 + 8 * stage, dpar);    // probe now, look at the answer later
+        // look-ahead reads for the next two items
+        uint4 recn2 = recn;
+        if (n + 2 < cnt) {
+            wait_half_of(n + 2);
+            recn2 = lds128(rec_addr(n + 2));
+        }
+        LaneCoef lcn = lc;
+        if (n + 1 < cnt) lcn = lane_coef(load_block_coef(rec_addr(n + 1)), lane - kBlockW / 2);
+
+        const uint4 r = rec;
         const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
-        mbar_wait_addr(dbar0 + 8 * stage, dpar);
         if (type == (uint32_t)kBlockFast) {
             const uint32_t c = (r.y >> 16) & 0xFFu;
             const CamDev &cam = A.F.cam[c];
@@ -440,14 +462,20 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             const uint32_t stage_origin = stage0 + stage * (uint32_t)A.stage_bytes - r.w;
             const uint32_t groups = (r.y >> 24) & 0xFFu;
             const bool full = (flags & kItemFull) != 0;
-            const LaneCoef lc = lane_coef(load_block_coef(rec0 + kRecBytes * slot), lane - kBlockW / 2);
+            if (!landed) mbar_wait_addr(dbar0 + 8 * stage, dpar);     // the box has landed
+#ifdef BS_ABLATE_HOT
+            if (full && groups == 0u) {
+                if (lc.a0x == 1234.5f) run_layer_full(lc, pitch, stage_origin, out_blk, lane);
+            }
+#else
             if (full && groups == 0u)
-                run_layer_full(lc, pitch, stage_origin, lut_base, out_blk, lane);
+                run_layer_full(lc, pitch, stage_origin, out_blk, lane);
+#endif
             else
-                run_layer_general(A, cam, lc, pitch, stage_origin, lut_base, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
+                run_layer_general(A, cam, lc, pitch, stage_origin, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
             wrote = true;
         }
-        __syncwarp();                 // every lane is done with this item's stage and record
+        __syncwarp();                 // every lane is done with this item's stage
         if (flags & kItemLast) {
             if (!prior_grid_done) {
                 asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -462,22 +490,23 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                 // flush: lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
                 const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
                 uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch + (long long)tx0 * 3 + (lane & 1) * 16;
+#ifndef BS_ABLATE_FLUSH
 #pragma unroll
                 for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4 *>(gp + 32 * j) = lds128(so + 32u * j);
+#else
+                if (so == 0x7fffffffu) *gp = 0;
+#endif
             } else {
                 store_block_checked(A.F, out_blk, tx0, ty0, lane);
             }
             wrote = false;
             __syncwarp();             // the output block is free again
         }
-        if (++stage == kStages) {
-            stage = 0;
-            dpar ^= 1u;
-        }
-        if (++slot == kRecSlots) {
-            slot = 0;
-            rpar ^= 1u;
-        }
+        rec = recn;
+        recn = recn2;
+        lc = lcn;
+        dpar ^= stage;                // the parity flips every second item
+        stage ^= 1u;
     }
 }
 

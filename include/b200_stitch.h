@@ -159,7 +159,7 @@ int bs_get_stats(const bs_handle *h, bs_stats *out);
  * arguments (flags: BS_FLAG_LEGACY_BORDER, BS_FLAG_KEEP_CANVAS), but the tile plan is rebuilt on every
  * call, so it is slower per frame; n_cams <= 16.
  *
- * The staged kernel's scratch (the block plan) lives in one static device
+ * The staged kernel's scratch (the block plan and the per-warp work split) lives in one static device
  * array of BS_STATIC_SCRATCH_BYTES that every GPU loading the library keeps until exit.  Canvases
  * needing more than BS_STATIC_MAX_BLOCKS blocks of 32x16 pixels (ceil(w/32) * ceil(h/16) > 32768; a
  * 7680x2160 panorama needs 32400) are refused with BS_ERR_UNSUPPORTED.  All calls share that array:
@@ -169,7 +169,7 @@ int bs_get_stats(const bs_handle *h, bs_stats *out);
  * plan and once at the end).
  */
 #define BS_STATIC_MAX_BLOCKS 32768
-#define BS_STATIC_SCRATCH_BYTES (BS_STATIC_MAX_BLOCKS * 160)
+#define BS_STATIC_SCRATCH_BYTES (BS_STATIC_MAX_BLOCKS * 160 + 32768)
 int bs_stitch_device_static(int n_cams, const int *src_w, const int *src_h, const void *const *d_frames,
                             const size_t *pitch, int canvas_w, int canvas_h, void *d_canvas,
                             size_t canvas_pitch, const double *H, unsigned flags, void *stream);

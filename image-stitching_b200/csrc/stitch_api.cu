@@ -426,6 +426,14 @@ int build_plan(bs_handle *h)
     return BS_OK;
 }
 
+// True when every byte of the canvas has the same upper 32 address bits.
+int canvas_in_4g(const void *canvas, size_t pitch, int H)
+{
+    static const bool never = getenv("BS_DEBUG_NO_DIRECT") != nullptr;   // test hook: always take the staged store path
+    const uintptr_t a = reinterpret_cast<uintptr_t>(canvas), b = a + pitch * (size_t)H - 1;
+    return (!never && (a >> 32) == (b >> 32)) ? 1 : 0;
+}
+
 bool aligned16(const void *p, size_t pitch) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (pitch & 15) == 0; }
 
 // cv::undistort for the cameras that have a lens model: src frame -> tmp[i]; the pointers the warp
@@ -540,6 +548,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.block_w = opencv_block_width(h->W, h->H);
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = keep ? 1 : 0;
+        A.canvas_in_4g = canvas_in_4g(d_canvas, cpitch, h->H);
         FA.items = h->d_items;
         FA.warp_start = h->d_warp_start;
         FA.stage_bytes = h->stage_bytes;
@@ -1147,6 +1156,7 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     A.block_w = block_w;
     A.legacy_border = legacy;
     A.keep_canvas = keep ? 1 : 0;
+    A.canvas_in_4g = canvas_in_4g(d_canvas, canvas_pitch, canvas_h);
 
     if (!fast) {
         // no staged blocks (or unaligned buffers): the per-pixel kernel needs no scratch at all

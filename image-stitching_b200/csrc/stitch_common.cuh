@@ -32,6 +32,7 @@ struct FrameArgs {
     int legacy_border;    // Appendix A.4 rule
     int keep_canvas;      // 1: uncovered pixels untouched, 0: uncovered pixels = 0
     int cam_base;         // index of cam[0] among all cameras (multi-launch for > 16 cameras)
+    int canvas_in_4g;     // 1: all canvas addresses share their upper 32 bits (staged kernel: rows may be stored with 32-bit address steps)
 };
 
 // ---- Appendix A.1, exact form -------------------------------------------------------------

@@ -180,9 +180,30 @@ __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, 
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(row_addr + 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3))), "r"(word)
                      : "memory");
 }
+// Same, straight to the canvas: (`hi`:`lo`) = address of this lane's word of the row, `storing` != 0
+// for the 24 lanes that own a word (lanes 4q+3 do not).  They cover the row's 96 bytes = three full
+// 32-byte sectors.
+__device__ __forceinline__ void store_row_pixel_global(uint32_t px, uint32_t lo, uint32_t hi, uint32_t storing, uint32_t sel)
+{
+    const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
+    const uint32_t word = __byte_perm(px, nxt, sel);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        ".reg .b64 a;\n"
+        "setp.ne.u32 p, %3, 0;\n"
+        "mov.b64 a, {%0, %1};\n"
+        "@p st.global.u32 [a], %2;\n"
+        "}" ::"r"(lo),
+        "r"(hi), "r"(word), "r"(storing)
+        : "memory");
+}
 
 // ---- work decomposition ------------------------------------------------------------------------
-constexpr int kWarpsPerCta = 8;
+#ifndef BS_WARPS_PER_CTA
+#define BS_WARPS_PER_CTA 8
+#endif
+constexpr int kWarpsPerCta = BS_WARPS_PER_CTA;
 constexpr int kFastThreads = 32 * kWarpsPerCta;
 #ifndef BS_MIN_CTAS
 #define BS_MIN_CTAS 2
@@ -221,10 +242,16 @@ __device__ __forceinline__ BlockCoef load_block_coef(uint32_t rec_addr)
 // Hot path: the layer covers every pixel of the block with interior samples, the block lies inside
 // the canvas and the plan verified the cheap coordinates for the whole block.  No coverage tests,
 // no fp64; fully unrolled so the row offset v is a constant.
+// kDirect: the block has no other layer and the previous frame's kernel is known to have finished,
+// so every row goes straight to the canvas (`grow` = this lane's word of the block's first row);
+// otherwise rows are collected in the warp's output block in shared memory.
+template <bool kDirect>
 __device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, uint32_t stage_origin,
-                                               uint32_t out_blk, int lane)
+                                               uint32_t out_blk, int lane, uint8_t *grow, long long cpitch)
 {
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
+    const uint32_t storing = (uint32_t)((lane & 3) != 3);
+    const uint32_t glo = (uint32_t)reinterpret_cast<uintptr_t>(grow), ghi = (uint32_t)(reinterpret_cast<uintptr_t>(grow) >> 32);
     const uint32_t run_base = stage_origin + (uint32_t)((lc.by >> kFracBits) * pitch + (lc.bx >> kFracBits) * 3);
     const int step = lc.nyv * pitch + lc.nxv * 3;      // whole texels per canvas row, as a byte offset
     auto fetch = [&](int k) {
@@ -235,13 +262,20 @@ __device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, ui
                            (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
         return fetch_taps(o, pitch, tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
+    // software pipeline: the shared-memory loads of pixel k+1 are issued before the arithmetic of
+    // pixel k, so a warp has work to do while its loads are in flight
     Taps cur = fetch(0);
 #pragma unroll
     for (int k = 0; k < kRun; ++k) {
         Taps nxt = cur;
         if (k + 1 < kRun) nxt = fetch(k + 1);
         const uint32_t px = blend_taps(cur);
-        store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
+        if (kDirect) {
+            // the canvas does not straddle a 4 GB boundary (the host checks), so only the low half
+            // of the row address advances -- one add per row instead of a 64-bit one
+            store_row_pixel_global(px, glo + (uint32_t)k * (uint32_t)cpitch, ghi, storing, sel);
+        } else
+            store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
         cur = nxt;
     }
 }
@@ -452,6 +486,7 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         if (n + 1 < cnt) lcn = lane_coef(load_block_coef(rec_addr(n + 1)), lane - kBlockW / 2);
 
         const uint4 r = rec;
+        bool direct = false;
         const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
         if (type == (uint32_t)kBlockFast) {
@@ -463,20 +498,21 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             const uint32_t groups = (r.y >> 24) & 0xFFu;
             const bool full = (flags & kItemFull) != 0;
             if (!landed) mbar_wait_addr(dbar0 + 8 * stage, dpar);     // the box has landed
-#ifdef BS_ABLATE_HOT
             if (full && groups == 0u) {
-                if (lc.a0x == 1234.5f) run_layer_full(lc, pitch, stage_origin, out_blk, lane);
-            }
-#else
-            if (full && groups == 0u)
-                run_layer_full(lc, pitch, stage_origin, out_blk, lane);
-#endif
-            else
+                // single-layer block after the first flush: no staging in shared memory, no flush
+                direct = prior_grid_done && A.F.canvas_in_4g && (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
+                uint8_t *const grow = A.F.canvas + (long long)ty0 * A.F.cpitch + (long long)tx0 * 3 + 4 * (3 * (lane >> 2) + (lane & 3));
+                if (direct)
+                    run_layer_full<true>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch);
+                else
+                    run_layer_full<false>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch);
+            } else {
                 run_layer_general(A, cam, lc, pitch, stage_origin, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
-            wrote = true;
+            }
+            wrote = !direct;
         }
         __syncwarp();                 // every lane is done with this item's stage
-        if (flags & kItemLast) {
+        if ((flags & kItemLast) && !direct) {
             if (!prior_grid_done) {
                 asm volatile("griddepcontrol.wait;" ::: "memory");
                 prior_grid_done = true;

@@ -2,12 +2,14 @@
 the reference's OpenCV path and against the CPU oracle on seeded inputs.  Bar: bit-exact
 (north_star asks >= 99.9 % identical and no pixel more than 1 LSB off; equality implies both)."""
 import hashlib
+import os
+import sys
 
 import numpy as np
 import pytest
 
 import oracle
-from conftest import pkg, workloads
+from conftest import ROOT, pkg, workloads
 
 pytestmark = pytest.mark.gpu
 
@@ -197,3 +199,25 @@ def test_size_independent_properties_at_full_size():
         got = st.stitch([b, a])
     assert np.array_equal(got[:, :sw], a)                             # now the identity camera is last
     assert np.array_equal(got[:, sw:1000 + sw], b[:, sw - 1000:])
+
+
+def test_staged_store_path_known_answer(known_answers):
+    """The frame kernel stores single-layer blocks straight to the canvas when the canvas does not
+    straddle a 4 GB boundary; BS_DEBUG_NO_DIRECT=1 (read once per process) forces the other path,
+    rows collected in shared memory and flushed.  Same OpenCV hash either way."""
+    import subprocess
+    want = [c for c in known_answers["cases"] if (c["config"], c["content"], c["frame"]) == ("cfg2", "noise", 0)][0]
+    code = (
+        "import sys, hashlib, importlib, numpy as np\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "import oracle\n"
+        "p = importlib.import_module('image-stitching_b200')\n"
+        "w = importlib.import_module('image-stitching_b200.workloads').get('cfg2')\n"
+        "srcs = [oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, 0, oracle.NOISE) for i in range(w.n_cams)]\n"
+        "with p.Stitcher([w.src_wh] * w.n_cams, w.canvas_wh, w.H) as st:\n"
+        "    got = st.stitch(srcs)\n"
+        "print(hashlib.sha256(np.ascontiguousarray(got).tobytes()).hexdigest())\n")
+    env = dict(os.environ, BS_DEBUG_NO_DIRECT="1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout.strip().splitlines()[-1] == want["canvas_sha256"]

@@ -43,6 +43,7 @@ struct LensModel {
     double fx = 0, fy = 0, u0 = 0, v0 = 0, winv = 1;
     double k[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // k1 k2 p1 p2 k3 k4 k5 k6
     double *d_xs = nullptr, *d_ys = nullptr;  // device tables, see stitch_undistort.cuh
+    uint32_t *d_map = nullptr;                // cached fixed-point map (w * h words), nullptr: evaluate per frame
 };
 
 }  // namespace
@@ -71,6 +72,7 @@ struct bs_handle {
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
+    int remap_grid = 0;                  // persistent CTAs of undistort_remap_kernel (set with the first lens map)
     uint64_t device_bytes = 0, scratch_bytes = 0;
     uint64_t h2d_bytes_last = 0;         // bytes the last bs_submit uploaded
     std::string err;
@@ -436,6 +438,27 @@ int canvas_in_4g(const void *canvas, size_t pitch, int H)
 
 bool aligned16(const void *p, size_t pitch) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && (pitch & 15) == 0; }
 
+// The lens model of camera i as the undistort kernels take it (frame pointers left unset).
+bs::UndistortArgs lens_args(const bs_handle *h, const LensModel &m, int i)
+{
+    bs::UndistortArgs U;
+    U.src = nullptr;
+    U.dst = nullptr;
+    U.spitch = U.dpitch = 0;
+    U.w = h->sw[i];
+    U.h = h->sh[i];
+    U.xs = m.d_xs;
+    U.ys = m.d_ys;
+    U.winv = m.winv;
+    U.fx = m.fx;
+    U.fy = m.fy;
+    U.u0 = m.u0;
+    U.v0 = m.v0;
+    U.k1 = m.k[0]; U.k2 = m.k[1]; U.p1 = m.k[2]; U.p2 = m.k[3];
+    U.k3 = m.k[4]; U.k4 = m.k[5]; U.k5 = m.k[6]; U.k6 = m.k[7];
+    return U;
+}
+
 // cv::undistort for the cameras that have a lens model: src frame -> tmp[i]; the pointers the warp
 // should read are returned in out_frames / out_pitch.  Stream-ordered before the frame kernel.
 int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pitch, std::vector<uint8_t *> &tmp,
@@ -452,23 +475,26 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
             BS_CUDA(h, cudaMalloc(&tmp[i], bytes));
             h->device_bytes += bytes;
         }
-        bs::UndistortArgs U;
-        U.src = static_cast<const uint8_t *>(d_frames[i]);
-        U.dst = tmp[i];
-        U.spitch = (long long)pitch[i];
-        U.dpitch = (long long)h->d_frame_pitch[i];
-        U.w = h->sw[i];
-        U.h = h->sh[i];
-        U.xs = m.d_xs;
-        U.ys = m.d_ys;
-        U.winv = m.winv;
-        U.fx = m.fx;
-        U.fy = m.fy;
-        U.u0 = m.u0;
-        U.v0 = m.v0;
-        U.k1 = m.k[0]; U.k2 = m.k[1]; U.p1 = m.k[2]; U.p2 = m.k[3];
-        U.k3 = m.k[4]; U.k4 = m.k[5]; U.k5 = m.k[6]; U.k6 = m.k[7];
-        bs::undistort_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, stream>>>(U);
+        const bool aligned4 = (reinterpret_cast<uintptr_t>(d_frames[i]) & 3) == 0 && (pitch[i] & 3) == 0;
+        if (m.d_map && aligned4) {
+            // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
+            bs::RemapArgs R;
+            R.src = static_cast<const uint8_t *>(d_frames[i]);
+            R.dst = tmp[i];
+            R.spitch = (long long)pitch[i];
+            R.dpitch = (long long)h->d_frame_pitch[i];
+            R.w = h->sw[i];
+            R.h = h->sh[i];
+            R.map = m.d_map;
+            bs::undistort_remap_kernel<<<h->remap_grid, 256, 0, stream>>>(R);
+        } else {
+            bs::UndistortArgs U = lens_args(h, m, i);
+            U.src = static_cast<const uint8_t *>(d_frames[i]);
+            U.dst = tmp[i];
+            U.spitch = (long long)pitch[i];
+            U.dpitch = (long long)h->d_frame_pitch[i];
+            bs::undistort_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, stream>>>(U);
+        }
         BS_CUDA(h, cudaGetLastError());
         h->kernel_launches++;
         out_frames[i] = tmp[i];
@@ -712,6 +738,7 @@ int bs_destroy(bs_handle *h)
     for (LensModel &m : h->lens) {
         cudaFree(m.d_xs);
         cudaFree(m.d_ys);
+        cudaFree(m.d_map);
     }
     for (uint8_t *p : h->d_undist) cudaFree(p);
     for (Slot &s : h->ring) {
@@ -865,6 +892,7 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     LensModel &m = h->lens[cam];
     cudaFree(m.d_xs);
     cudaFree(m.d_ys);
+    cudaFree(m.d_map);
     m = LensModel();
     bool nonzero = false;
     for (int i = 0; i < n_dist; ++i) {
@@ -881,6 +909,32 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     BS_CUDA(h, upload_now(h, m.d_ys, ys.data(), ys.size() * sizeof(double)));
     h->device_bytes += (xs.size() + ys.size()) * sizeof(double);
     m.enabled = true;
+    if (h->flags & BS_FLAG_EXACT_ONLY) return BS_OK;     // one-shot handles (bs_undistort): one pass, no map
+    // The map depends on the calibration only: evaluate it once, resample every frame from it.
+    const size_t map_bytes = sizeof(uint32_t) * (size_t)h->sw[cam] * (size_t)h->sh[cam];
+    int *d_overflow = nullptr, overflow = 0;
+    BS_CUDA(h, cudaMalloc(&m.d_map, map_bytes));
+    BS_CUDA(h, cudaMalloc(&d_overflow, sizeof(int)));
+    BS_CUDA(h, cudaMemsetAsync(d_overflow, 0, sizeof(int), h->s_compute));
+    if (h->remap_grid == 0) {
+        int per_sm = 0, sms = 0;
+        BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::undistort_remap_kernel, 256, 0));
+        BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+        h->remap_grid = std::max(1, per_sm * sms);
+    }
+    const bs::UndistortArgs U = lens_args(h, m, cam);
+    bs::undistort_map_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, h->s_compute>>>(U, m.d_map, d_overflow);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&overflow, d_overflow, sizeof(int), cudaMemcpyDeviceToHost, h->s_compute);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
+    cudaFree(d_overflow);
+    if (e != cudaSuccess || overflow) {                  // displacement beyond the packed range: keep the one-pass kernel
+        cudaFree(m.d_map);
+        m.d_map = nullptr;
+        if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "bs_set_undistort: map kernel: %s", cudaGetErrorString(e));
+    } else {
+        h->device_bytes += map_bytes;
+    }
     return BS_OK;
 }
 

@@ -7,11 +7,18 @@
 // advanced along a row by repeated addition of 1/fx, so its value at column j carries j rounding
 // steps; that sequence is identical for every row when the camera matrix has the usual form
 // [[fx 0 cx] [0 fy cy] [0 0 1]], so the host tabulates it once (xs[j]) together with the per-row
-// normalised y (ys[i]); the kernel then evaluates the distortion model per pixel in fp64 with
-// individually rounded operations, in the order of the scalar reference (oracle/warp_oracle.c).
+// normalised y (ys[i]); the distortion model is then evaluated per pixel in fp64 with individually
+// rounded operations, in the order of the scalar reference (oracle/warp_oracle.c).
+//
+// The reference rebuilds that map for every frame, but it depends on the calibration only.  A handle
+// therefore evaluates it once (undistort_map_kernel) into one packed word per pixel and resamples
+// every frame with undistort_remap_kernel: one coalesced map word, six aligned tap words, the frame
+// kernel's dp2a blend.  undistort_kernel (map and resampling in one pass, fp64 per pixel) remains for
+// the one-shot entry point, for unaligned buffers and for lenses whose displacement does not fit
+// the packed word.
 #pragma once
 
-#include "stitch_common.cuh"
+#include "stitch_fast.cuh"
 
 namespace bs {
 
@@ -27,11 +34,10 @@ struct UndistortArgs {
     double k1, k2, p1, p2, k3, k4, k5, k6;
 };
 
-__global__ void __launch_bounds__(256) undistort_kernel(const __grid_constant__ UndistortArgs A)
+// Fixed-point source position of destination pixel (j, i): texel (sx, sy) as OpenCV's int16 map holds
+// it, fractions a, b in 1/32.
+__device__ __forceinline__ void undistort_coord(const UndistortArgs &A, int j, int i, int &sx, int &sy, int &a, int &b)
 {
-    const int j = blockIdx.x * 64 + (threadIdx.x & 63);
-    const int i = blockIdx.y * 4 + (threadIdx.x >> 6);
-    if (j >= A.w || i >= A.h) return;
     const double x = __dmul_rn(A.xs[j], A.winv), y = __dmul_rn(A.ys[i], A.winv);
     const double x2 = __dmul_rn(x, x), y2 = __dmul_rn(y, y);
     const double r2 = __dadd_rn(x2, y2), _2xy = __dmul_rn(__dmul_rn(2.0, x), y);
@@ -45,20 +51,185 @@ __global__ void __launch_bounds__(256) undistort_kernel(const __grid_constant__ 
     const double u = __dadd_rn(__dmul_rn(A.fx, xd), A.u0), v = __dadd_rn(__dmul_rn(A.fy, yd), A.v0);
     const double fu = __dmul_rn(u, (double)kFracOne), fv = __dmul_rn(v, (double)kFracOne);
     const int iu = (fu == fu) ? __double2int_rn(fu) : INT_MIN, iv = (fv == fv) ? __double2int_rn(fv) : INT_MIN;
-    const int sx = (int)(short)(iu >> kFracBits), sy = (int)(short)(iv >> kFracBits);   // OpenCV stores int16
-    const int a = iu & (kFracOne - 1), b = iv & (kFracOne - 1);
+    sx = (int)(short)(iu >> kFracBits);   // OpenCV stores int16
+    sy = (int)(short)(iv >> kFracBits);
+    a = iu & (kFracOne - 1);
+    b = iv & (kFracOne - 1);
+}
+
+// Bilinear sample with BORDER_CONSTANT 0, tap by tap (any position, any alignment).
+__device__ __forceinline__ void undistort_sample_checked(const uint8_t *__restrict__ src, long long spitch, int w, int h,
+                                                         int sx, int sy, int a, int b, uint8_t *o)
+{
     const int wgt[4] = {(kFracOne - a) * (kFracOne - b), a * (kFracOne - b), (kFracOne - a) * b, a * b};
-    uint8_t *o = A.dst + (long long)i * A.dpitch + (long long)j * 3;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         int acc = 0;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int tx = sx + (t & 1), ty = sy + (t >> 1);
-            if (tx >= 0 && tx < A.w && ty >= 0 && ty < A.h)
-                acc += wgt[t] * __ldg(A.src + (long long)ty * A.spitch + (long long)tx * 3 + c);   // outside taps are 0
+            if (tx >= 0 && tx < w && ty >= 0 && ty < h)
+                acc += wgt[t] * __ldg(src + (long long)ty * spitch + (long long)tx * 3 + c);   // outside taps are 0
         }
         o[c] = (uint8_t)((acc + 512) >> 10);   // == (32 acc + 2^14) >> 15
+    }
+}
+
+__global__ void __launch_bounds__(256) undistort_kernel(const __grid_constant__ UndistortArgs A)
+{
+    const int j = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int i = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (j >= A.w || i >= A.h) return;
+    int sx, sy, a, b;
+    undistort_coord(A, j, i, sx, sy, a, b);
+    undistort_sample_checked(A.src, A.spitch, A.w, A.h, sx, sy, a, b, A.dst + (long long)i * A.dpitch + (long long)j * 3);
+}
+
+// ---- cached map -------------------------------------------------------------------------------
+// One word per pixel: a | b << 5 | (sx - j) << 10 | (sy - i) << 21, displacements as 11-bit two's
+// complement; the row displacement -1024 is reserved for "every tap lies outside the frame" (the pixel
+// is 0 whatever the frame holds).  A lens that moves a visible pixel by more than 1023 pixels sets
+// *overflow and the handle keeps the one-pass kernel.
+constexpr int kMapDispBits = 11;
+constexpr int kMapOutside = -(1 << (kMapDispBits - 1));
+
+__global__ void __launch_bounds__(256) undistort_map_kernel(const __grid_constant__ UndistortArgs A, uint32_t *__restrict__ map,
+                                                            int *__restrict__ overflow)
+{
+    const int j = blockIdx.x * 64 + (threadIdx.x & 63);
+    const int i = blockIdx.y * 4 + (threadIdx.x >> 6);
+    if (j >= A.w || i >= A.h) return;
+    int sx, sy, a, b;
+    undistort_coord(A, j, i, sx, sy, a, b);
+    int dx = sx - j, dy = sy - i;
+    const int lim = 1 << (kMapDispBits - 1);
+    if (sx < -1 || sx >= A.w || sy < -1 || sy >= A.h) {
+        dx = 0;
+        dy = kMapOutside;
+    } else if (dx < -lim || dx >= lim || dy <= -lim || dy >= lim) {
+        atomicExch(overflow, 1);
+    }
+    map[(size_t)i * A.w + j] = (uint32_t)a | ((uint32_t)b << 5) | (((uint32_t)dx & 0x7FFu) << 10) | ((uint32_t)dy << 21);
+}
+
+struct RemapArgs {
+    const uint8_t *src;    // 4-byte aligned, pitch a multiple of 4
+    uint8_t *dst;          // 4-byte aligned, pitch a multiple of 4
+    long long spitch, dpitch;
+    int w, h;
+    const uint32_t *map;   // w * h words, row-major without padding
+};
+
+// Lane = destination column within a 32-pixel segment; a warp owns kRemapRows consecutive rows of it
+// (one strip); warps are persistent and walk the strips of the frame with a grid stride; the map words
+// of the next strip are requested before the current strip is resampled, and all 24 tap words of a
+// strip before any arithmetic (one pixel per thread was bound by the latency of the map -> tap load
+// chain).  Interior pixels (all four taps inside, with a margin
+// so that the three aligned tap words stay inside the row) take the frame kernel's path -- 2 x 3
+// aligned words through L1, funnel-shift alignment, dp2a blend; a strip with any other pixel goes
+// tap by tap.  Full segments are stored as 24 words per row (three 32-byte sectors).
+constexpr int kRemapRows = 4;
+
+__device__ __forceinline__ void remap_store_row(uint8_t *row, uint32_t px, int lane, bool full, bool live)
+{
+    if (full) {
+        const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
+        const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
+        const uint32_t word = __byte_perm(px, nxt, sel);
+        if ((lane & 3) != 3) *reinterpret_cast<uint32_t *>(row + 4 * (3 * (lane >> 2) + (lane & 3))) = word;
+    } else if (live) {
+        row[3 * lane] = (uint8_t)px;
+        row[3 * lane + 1] = (uint8_t)(px >> 8);
+        row[3 * lane + 2] = (uint8_t)(px >> 16);
+    }
+}
+
+__global__ void __launch_bounds__(256) undistort_remap_kernel(const __grid_constant__ RemapArgs A)
+{
+    const int lane = threadIdx.x & 31;
+    const int segs = (A.w + 31) >> 5;                      // 32-pixel segments per row
+    const int strips_y = (A.h + kRemapRows - 1) / kRemapRows;
+    const int stride = (int)gridDim.x * 8;                 // persistent warps: strip s, s + stride, ...
+    const int dq = stride / segs, dr = stride - dq * segs; // the same step in (segment, strip row) form
+    const int s0 = (int)blockIdx.x * 8 + (threadIdx.x >> 5);
+    int by = s0 / segs, bx = s0 - by * segs;
+    if (by >= strips_y) return;
+    const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
+    const uint32_t word_off = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
+
+    // map words of a strip; rows past the frame and dead lanes shadow the last row / column
+    auto load_map = [&](int sx_, int sy_, uint32_t (&m)[kRemapRows]) {
+        const int jc = min(sx_ * 32 + lane, A.w - 1);
+#pragma unroll
+        for (int r = 0; r < kRemapRows; ++r) m[r] = __ldg(A.map + (size_t)min(sy_ * kRemapRows + r, A.h - 1) * A.w + jc);
+    };
+    // (Deeper pipelines -- tap words one strip ahead in a second register set -- need 128 registers and
+    // lose more to occupancy than they hide: 37 us against 33 us per 4K frame.)
+    uint32_t m[kRemapRows], mn[kRemapRows];
+    load_map(bx, by, m);
+    while (true) {
+        int nbx = bx + dr, nby = by + dq;
+        if (nbx >= segs) {
+            nbx -= segs;
+            ++nby;
+        }
+        const bool more = nby < strips_y;                  // warp-uniform
+        if (more) load_map(nbx, nby, mn);                  // in flight while this strip is resampled
+        const int i0 = by * kRemapRows;
+        const int j = bx * 32 + lane;
+        const bool whole = bx * 32 + 32 <= A.w && i0 + kRemapRows <= A.h;   // no dead lane, no row past the frame
+        uint8_t *const out = A.dst + (long long)i0 * A.dpitch + (long long)(bx * 32) * 3;
+        uint32_t off[kRemapRows];                          // byte offset of texel (sx, sy) in the frame (< 4 GB)
+        bool interior = whole;
+#pragma unroll
+        for (int r = 0; r < kRemapRows; ++r) {
+            const int sx = j + (((int)(m[r] << 11)) >> 21), sy = i0 + r + ((int)m[r] >> 21);
+            // all four taps inside, with a margin for the third aligned word; "outside" words fail on dy
+            interior = interior && (m[r] >> 21) != (uint32_t)(kMapOutside & 0x7FF) && (uint32_t)sx < (uint32_t)(A.w - 3) &&
+                       (uint32_t)sy < (uint32_t)(A.h - 1);
+            off[r] = (uint32_t)sy * (uint32_t)A.spitch + (uint32_t)sx * 3u;
+        }
+        if (__all_sync(0xffffffffu, interior)) {
+            Taps t[kRemapRows];
+#pragma unroll
+            for (int r = 0; r < kRemapRows; ++r) {
+                const uint32_t *r0 = reinterpret_cast<const uint32_t *>(A.src + (off[r] & ~3u));
+                const uint32_t *r1 = reinterpret_cast<const uint32_t *>(A.src + (off[r] & ~3u) + (uint32_t)A.spitch);
+                t[r].w0 = __ldg(r0); t[r].w1 = __ldg(r0 + 1); t[r].w2 = __ldg(r0 + 2);
+                t[r].v0 = __ldg(r1); t[r].v1 = __ldg(r1 + 1); t[r].v2 = __ldg(r1 + 2);
+                t[r].sh = off[r] << 3;                     // the frame base is 4-byte aligned
+                t[r].wt = tap_weights(m[r] & 31u, (m[r] >> 5) & 31u);
+            }
+            uint8_t *wp = out + word_off;
+#pragma unroll
+            for (int r = 0; r < kRemapRows; ++r) {
+                const uint32_t px = blend_taps(t[r]);
+                const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
+                const uint32_t word = __byte_perm(px, nxt, sel);
+                if ((lane & 3) != 3) *reinterpret_cast<uint32_t *>(wp) = word;
+                wp += A.dpitch;
+            }
+        } else {
+            const bool live = j < A.w;
+            const bool full = bx * 32 + 32 <= A.w;
+            const int jc = live ? j : A.w - 1;
+            for (int r = 0; r < kRemapRows && i0 + r < A.h; ++r) {
+                const int dy = (int)m[r] >> 21;
+                const int sx = jc + (((int)(m[r] << 11)) >> 21), sy = i0 + r + dy;
+                uint32_t px = 0;
+                if (dy != kMapOutside) {
+                    uint8_t o[3];
+                    undistort_sample_checked(A.src, A.spitch, A.w, A.h, sx, sy, (int)(m[r] & 31u), (int)((m[r] >> 5) & 31u), o);
+                    px = (uint32_t)o[0] | ((uint32_t)o[1] << 8) | ((uint32_t)o[2] << 16);
+                }
+                remap_store_row(out + (long long)r * A.dpitch, px, lane, full, live);
+            }
+        }
+        if (!more) break;
+        bx = nbx;
+        by = nby;
+#pragma unroll
+        for (int r = 0; r < kRemapRows; ++r) m[r] = mn[r];
     }
 }
 

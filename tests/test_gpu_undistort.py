@@ -67,3 +67,23 @@ def test_undistort_then_warp_matches_reference_order():
         got = st.stitch(srcs)
         want = oracle.stitch([oracle.undistort(srcs[0], Ks[0], dists[0]), srcs[1]], w.H, w.canvas_wh)
         assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("wh", [(333, 77), (1920, 1080), (4097, 31), (3840, 2160)])
+def test_cached_map_path_matches_oracle(wh):
+    """A handle evaluates the lens map once (bs_set_undistort) and resamples every frame from the
+    packed map; identity homography, canvas = frame size, so the panorama is the undistorted frame.
+    Mild and strong models (the strong ones push border pixels far outside the frame), odd widths
+    (partial 32-pixel segments), two frames through the same map."""
+    p = pkg()
+    w, h = wh
+    K = np.array([[0.9 * w, 0, w / 2 + 3.3], [0, 0.92 * w, h / 2 - 1.7], [0, 0, 1]])
+    eye = [np.eye(3)]
+    for dist in ([-0.25, 0.08, 0.001, 0.0005, 0.01, 0.02, -0.01, 0.003], [0.9, 2.5, 0.02, -0.03, 4.0], [-0.7, 0.3, 0, 0]):
+        with p.Stitcher([wh], wh, eye) as st:
+            st.set_undistort(0, K, dist)
+            for frame in range(2):
+                src = oracle.gen_frame(w, h, 1, frame, oracle.NOISE)
+                got = st.stitch([src])
+                want = oracle.stitch([oracle.undistort(src, K, np.array(dist, dtype=np.float64))], eye, wh)
+                assert np.array_equal(got, want), f"{wh} dist={dist} frame {frame}: {(got != want).any(axis=2).sum()} pixels differ"

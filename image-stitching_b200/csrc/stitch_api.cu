@@ -38,6 +38,14 @@ struct Slot {
 };
 
 // Lens model of one camera (cv::undistort, tools/stitch/main.cpp:148-149).
+// One encoded TMA descriptor of a camera's frame buffer (the box shape is fixed per handle).
+struct TmapEntry {
+    const void *ptr = nullptr;
+    size_t pitch = 0;
+    CUtensorMap map;
+};
+constexpr int kTmapCacheWays = 8;
+
 struct LensModel {
     bool enabled = false;                // false: no model, or all coefficients zero (undistort is then a copy)
     double fx = 0, fy = 0, u0 = 0, v0 = 0, winv = 1;
@@ -73,6 +81,8 @@ struct bs_handle {
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
     int remap_grid = 0;                  // persistent CTAs of undistort_remap_kernel (set with the first lens map)
+    std::vector<TmapEntry> tmap_cache;   // n_cams x kTmapCacheWays, filled round-robin per camera
+    unsigned tmap_next[bs::kMaxCamsPerLaunch] = {0};
     uint64_t device_bytes = 0, scratch_bytes = 0;
     uint64_t h2d_bytes_last = 0;         // bytes the last bs_submit uploaded
     std::string err;
@@ -559,12 +569,23 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             FA.pitch[i] = h->box_we[i] * 4;
             FA.box_bytes[i] = h->box_we[i] * 4 * h->box_h[i];
             if (h->box_we[i] > 0) {
-                const int er = encode_frame_map(&FA.tmap[i], d_frames[i], pitch[i], h->sh[i], h->box_we[i],
-                                                h->box_h[i]);
-                if (er != 0)
-                    return fail(h, BS_ERR_CUDA,
-                                "cuTensorMapEncodeTiled failed (%d) for camera %d: ptr=%p pitch=%zu h=%d box=%dx%d", er,
-                                i, d_frames[i], pitch[i], h->sh[i], h->box_we[i], h->box_h[i]);
+                // frame buffers come from small rings (ours or the caller's): keep the last few encoded maps
+                if (h->tmap_cache.empty()) h->tmap_cache.resize((size_t)h->n_cams * kTmapCacheWays);
+                TmapEntry *ways = &h->tmap_cache[(size_t)i * kTmapCacheWays], *hit = nullptr;
+                for (int k = 0; k < kTmapCacheWays && !hit; ++k)
+                    if (ways[k].ptr == d_frames[i] && ways[k].pitch == pitch[i]) hit = &ways[k];
+                if (!hit) {
+                    hit = &ways[h->tmap_next[i]++ % kTmapCacheWays];
+                    hit->ptr = nullptr;
+                    const int er = encode_frame_map(&hit->map, d_frames[i], pitch[i], h->sh[i], h->box_we[i], h->box_h[i]);
+                    if (er != 0)
+                        return fail(h, BS_ERR_CUDA,
+                                    "cuTensorMapEncodeTiled failed (%d) for camera %d: ptr=%p pitch=%zu h=%d box=%dx%d", er,
+                                    i, d_frames[i], pitch[i], h->sh[i], h->box_we[i], h->box_h[i]);
+                    hit->ptr = d_frames[i];
+                    hit->pitch = pitch[i];
+                }
+                FA.tmap[i] = hit->map;
             }
         }
         A.canvas = d_canvas;

@@ -125,10 +125,6 @@ __device__ __forceinline__ Taps fetch_taps(uint32_t o, int pitch, uint2 wt)
     Taps t;
     const uint32_t wa = o & ~3u;
     t.sh = o << 3;
-#ifdef BS_ABLATE_LDS
-    t.w0 = wa; t.w1 = wa + 1; t.w2 = wa + 2; t.v0 = wa + 3; t.v1 = wa + 4; t.v2 = wa + 5; t.wt = wt;
-    return t;
-#endif
     t.w0 = lds32(wa);
     t.w1 = lds32(wa + 4);
     t.w2 = lds32(wa + 8);
@@ -143,9 +139,6 @@ __device__ __forceinline__ Taps fetch_taps(uint32_t o, int pitch, uint2 wt)
 // Returns B | G<<8 | R<<16.
 __device__ __forceinline__ uint32_t blend_taps(const Taps &t)
 {
-#ifdef BS_ABLATE_BLEND
-    return (t.w0 ^ t.w1 ^ t.w2 ^ t.v0 ^ t.v1 ^ t.v2 ^ t.wt.x ^ t.wt.y) + t.sh;
-#endif
     // six aligned bytes of each row: r?a = [B0 G0 R0 B1], r?b = [G1 R1 . .]
     const uint32_t r0a = __funnelshift_r(t.w0, t.w1, t.sh), r0b = __funnelshift_r(t.w1, t.w2, t.sh);
     const uint32_t r1a = __funnelshift_r(t.v0, t.v1, t.sh), r1b = __funnelshift_r(t.v1, t.v2, t.sh);
@@ -170,10 +163,6 @@ __device__ __forceinline__ uint32_t sample_staged(uint32_t o, int pitch, uint2 w
 // neighbour's and stores it.  `row_addr` = shared address of the block row (96 bytes).
 __device__ __forceinline__ void store_row_pixel(uint32_t px, uint32_t row_addr, int lane, uint32_t sel)
 {
-#ifdef BS_ABLATE_STORE
-    if (px == 0x12345678u) asm volatile("st.shared.u32 [%0], %1;" ::"r"(row_addr), "r"(px) : "memory");
-    return;
-#endif
     const uint32_t nxt = __shfl_down_sync(0xffffffffu, px, 1);
     const uint32_t word = __byte_perm(px, nxt, sel);
     if ((lane & 3) != 3)
@@ -393,9 +382,6 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     // retire.  It may prefetch and composite, but touches the canvas only after griddepcontrol.wait,
     // i.e. after this grid has completed.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-#ifdef BS_ABLATE_KERNEL
-    if (A.stage_bytes >= 0) return;
-#endif
     if (lane == 0) {
         for (int s = 0; s < kStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dbar0 + 8 * s), "r"(1));
         for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
@@ -424,11 +410,7 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     };
     // source box of the item whose record words are `r` -> stage; items without a box just arrive
     auto issue_box = [&](const uint4 &r, uint32_t stage) {
-#ifdef BS_ABLATE_TMA
-        if (false) {
-#else
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
-#endif
             const uint32_t cam = (r.y >> 16) & 0xFFu;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
                          "r"((uint32_t)A.box_bytes[cam])
@@ -526,12 +508,8 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                 // flush: lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
                 const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
                 uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch + (long long)tx0 * 3 + (lane & 1) * 16;
-#ifndef BS_ABLATE_FLUSH
 #pragma unroll
                 for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4 *>(gp + 32 * j) = lds128(so + 32u * j);
-#else
-                if (so == 0x7fffffffu) *gp = 0;
-#endif
             } else {
                 store_block_checked(A.F, out_blk, tx0, ty0, lane);
             }

@@ -305,6 +305,26 @@ __device__ __noinline__ void run_layer_general(const FastArgs &A, const CamDev &
     }
 }
 
+// Fully covered layer with flagged groups: the hot path has filled the output block with the cheap
+// coordinates; redo the flagged 32x4 groups with the exact fp64 coordinates (same taps, same blend).
+__device__ __noinline__ void patch_exact_groups(const FastArgs &A, const CamDev &cam, int pitch, uint32_t stage_origin,
+                                                uint32_t out_blk, uint32_t group_mask, int x, int y0, int lane)
+{
+    const int xb = (x / A.F.block_w) * A.F.block_w;
+#pragma unroll 1
+    for (int k = 0; k < kRun; ++k) {
+        if (!((group_mask >> (k >> 2)) & 1)) continue;     // warp-uniform
+        int X, Y;
+        coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
+        const uint32_t o = stage_origin + (uint32_t)((Y >> kFracBits) * pitch + (X >> kFracBits) * 3);
+        const uint32_t px = sample_staged(o, pitch, tap_weights((uint32_t)X & 31u, (uint32_t)Y & 31u));
+        const uint32_t p8 = out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane;
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8), "r"(px) : "memory");
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 1), "r"(px >> 8) : "memory");
+        asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 2), "r"(px >> 16) : "memory");
+    }
+}
+
 __device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity)
 {
     asm volatile(
@@ -480,14 +500,19 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             const uint32_t groups = (r.y >> 24) & 0xFFu;
             const bool full = (flags & kItemFull) != 0;
             if (!landed) mbar_wait_addr(dbar0 + 8 * stage, dpar);     // the box has landed
-            if (full && groups == 0u) {
+            if (full) {
                 // single-layer block after the first flush: no staging in shared memory, no flush
-                direct = prior_grid_done && A.F.canvas_in_4g && (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
+                direct = groups == 0u && prior_grid_done && A.F.canvas_in_4g &&
+                         (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
                 uint8_t *const grow = A.F.canvas + (long long)ty0 * A.F.cpitch + (long long)tx0 * 3 + 4 * (3 * (lane >> 2) + (lane & 3));
                 if (direct)
                     run_layer_full<true>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch);
                 else
                     run_layer_full<false>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch);
+                if (groups != 0u) {
+                    __syncwarp();
+                    patch_exact_groups(A, cam, pitch, stage_origin, out_blk, groups, tx0 + lane, ty0, lane);
+                }
             } else {
                 run_layer_general(A, cam, lc, pitch, stage_origin, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
             }

@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    __syncthreads();
+    __syncwarp();     // the barriers are private to the warp: no CTA-wide synchronisation anywhere in this kernel
 
     // Work split: the host deals the plan's blocks round-robin to the warps of the grid (block u to
     // warp u mod W, heaviest blocks first, so they spread evenly and at any moment the grid works on W

@@ -128,7 +128,10 @@ struct RemapArgs {
 // so that the three aligned tap words stay inside the row) take the frame kernel's path -- 2 x 3
 // aligned words through L1, funnel-shift alignment, dp2a blend; a strip with any other pixel goes
 // tap by tap.  Full segments are stored as 24 words per row (three 32-byte sectors).
-constexpr int kRemapRows = 4;
+#ifndef BS_REMAP_ROWS
+#define BS_REMAP_ROWS 4
+#endif
+constexpr int kRemapRows = BS_REMAP_ROWS;
 
 __device__ __forceinline__ void remap_store_row(uint8_t *row, uint32_t px, int lane, bool full, bool live)
 {

@@ -112,6 +112,14 @@ int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
  * pointers; for the staged fast path they must be 16-byte aligned with pitches that are
  * multiples of 16, otherwise the exact path is used for the whole frame.
  * Replaces tools/stitch/main.cpp:145-152 for callers that decode straight into GPU memory.
+ *
+ * Ordering: the frame kernel is launched with programmatic stream serialisation, so that back-to-back
+ * frames overlap; it reads the source frames as soon as it starts and writes the canvas only after
+ * the preceding kernel in the stream has completed.  Source frames must therefore be complete before
+ * the preceding kernel in `stream` triggers its dependents -- always the case for copies, for ordinary
+ * kernels and for this library's own kernels; a producer kernel that itself calls
+ * cudaTriggerProgrammaticLaunchCompletion() early must be separated from this call by an event or a
+ * different stream.
  */
 int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pitch,
                      void *d_canvas, size_t canvas_pitch, void *stream);

@@ -210,6 +210,25 @@ def physical_gpu_index(local_rank):
 # ------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------
+def pin_near_gpu(index):
+    """One process per GPU: run this rank on the host cores next to its GPU (NVML's ideal CPU set,
+    intersected with what the container allows), so that its pinned frame buffers are allocated
+    on that NUMA node and the copies do not cross sockets.  Returns the CPU list, or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        ideal = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        cpus = sorted(ideal & os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return cpus
+    except Exception:
+        pass
+    return None
+
+
 def run_b200(args, rank, local_rank, world):
     import numpy as np
     import torch
@@ -220,6 +239,7 @@ def run_b200(args, rank, local_rank, world):
                          "(use --impl reference for the host baseline)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = pin_near_gpu(local_rank) if world > 1 else None
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -391,6 +411,7 @@ def run_b200(args, rank, local_rank, world):
                    "l2": f"inputs larger than L2: ring of {RING} frame sets + canvases = "
                          f"{RING * (w.src_bytes + w.canvas_bytes) / 1e9:.2f} GB cycled per GPU",
                    "parallelism": f"frame-parallel x{world}, no collective",
+                   "host_cpus_per_rank": (len(numa) if numa else None),
                    "tiles_fast_exact_empty": [stats["n_tiles_fast"], stats["n_tiles_exact"], stats["n_tiles_empty"]]},
         "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "clocks": sampler.summary(), "parity": parity,

@@ -119,6 +119,21 @@ class CpuReference:
         return done, dt
 
 
+def _one_thread(self, n):
+    """frames/sec of the same path on ONE host thread (a short sample: n frames)."""
+    if self.cv2 is None:
+        return None
+    self.cv2.setNumThreads(1)
+    try:
+        done, dt = self.time_frames(1, n)
+    finally:
+        self.cv2.setNumThreads(self.cores)
+    return done / dt
+
+
+CpuReference.time_one_thread = _one_thread
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
@@ -376,6 +391,9 @@ def run_b200(args, rank, local_rank, world):
         done, dt = ref.time_frames(2, 10 ** 6, budget_s=args.cpu_seconds)
         cpu = {"value": done / dt, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
                "sample": f"{done} frames of {w.name} in {dt:.1f} s, {ref.what}, all host threads"}
+        one = ref.time_one_thread(3)
+        if one is not None:
+            cpu["one_thread"] = one           # also report the 1-thread figure
 
     if rank != 0:
         if dist is not None:

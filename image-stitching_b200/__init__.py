@@ -19,10 +19,12 @@ LIB_PATH = os.environ.get("B200_STITCH_LIB") or os.path.join(_HERE, "libb200stit
 FLAG_LEGACY_BORDER = 0x1
 FLAG_KEEP_CANVAS = 0x2
 FLAG_EXACT_ONLY = 0x4
+FLAG_BORDER_CONSTANT = 0x8
 
 # names of the cv2 constants the reference passes (tools/stitch/main.cpp:116-117)
 INTER_LINEAR = 1
 BORDER_TRANSPARENT = 5
+BORDER_CONSTANT = 0
 
 EXPORTS = [
     "bs_device_count", "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_submit",
@@ -252,9 +254,10 @@ def undistort(src, K, dist):
 def warpPerspective(src, dst, H, dsize, flags=INTER_LINEAR, borderMode=BORDER_TRANSPARENT,
                     legacy_border=False):
     """Mirror of the call the reference makes (tools/stitch/main.cpp:116-117):
-    warpPerspective(src, dst, H, dsize, INTER_LINEAR, BORDER_TRANSPARENT), dst updated in place."""
-    if flags != INTER_LINEAR or borderMode != BORDER_TRANSPARENT:
-        raise StitchError(-4, "only INTER_LINEAR + BORDER_TRANSPARENT (the reference's call) is implemented")
+    warpPerspective(src, dst, H, dsize, INTER_LINEAR, BORDER_TRANSPARENT), dst updated in place.
+    borderMode=BORDER_CONSTANT (value 0; lib/Calibrate/utils.cpp:390) overwrites all of dst."""
+    if flags != INTER_LINEAR or borderMode not in (BORDER_TRANSPARENT, BORDER_CONSTANT):
+        raise StitchError(-4, "only INTER_LINEAR with BORDER_TRANSPARENT or BORDER_CONSTANT 0 (the reference's calls) is implemented")
     _check_img(src, "src")
     _check_img(dst, "dst")
     if (dst.shape[1], dst.shape[0]) != tuple(dsize):
@@ -263,5 +266,6 @@ def warpPerspective(src, dst, H, dsize, flags=INTER_LINEAR, borderMode=BORDER_TR
     _check(lib().bs_warp_perspective(src.ctypes.data, src.shape[1], src.shape[0], src.strides[0],
                                      dst.ctypes.data, dst.shape[1], dst.shape[0], dst.strides[0],
                                      H.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
-                                     FLAG_LEGACY_BORDER if legacy_border else 0))
+                                     (FLAG_LEGACY_BORDER if legacy_border else 0) |
+                                     (FLAG_BORDER_CONSTANT if borderMode == BORDER_CONSTANT else 0)))
     return dst

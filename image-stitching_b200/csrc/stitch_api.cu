@@ -644,6 +644,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = (keep || base > 0) ? 1 : 0;
         A.cam_base = base;
+        A.border_constant = (h->flags & BS_FLAG_BORDER_CONSTANT) ? 1 : 0;
         dim3 grid((h->W + bs::kExactTileW - 1) / bs::kExactTileW,
                   (h->H + bs::kExactTileH - 1) / bs::kExactTileH);
         bs::stitch_exact_kernel<<<grid, dim3(32, bs::kExactTileH), 0, stream>>>(A);
@@ -722,7 +723,7 @@ int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int
     h->sh.assign(src_h, src_h + n_cams);
     h->W = canvas_w;
     h->H = canvas_h;
-    h->flags = flags;
+    h->flags = (flags & BS_FLAG_BORDER_CONSTANT) ? (flags | BS_FLAG_EXACT_ONLY) : flags;   // no staged path for that mode
     h->M.resize(9 * (size_t)n_cams);
     for (int i = 0; i < n_cams; ++i) invert3x3(H + 9 * i, &h->M[9 * i]);
     h->d_frame_pitch.resize(n_cams);
@@ -1002,7 +1003,8 @@ int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8
     int rc = require_device(nullptr);
     if (rc != BS_OK) return rc;
     bs_handle *h = nullptr;
-    rc = bs_create(g_last_device, 1, &sw, &sh, dw, dh, H, flags | BS_FLAG_KEEP_CANVAS, &h);
+    // BORDER_TRANSPARENT is read-modify-write on dst; BORDER_CONSTANT overwrites all of it
+    rc = bs_create(g_last_device, 1, &sw, &sh, dw, dh, H, (flags & BS_FLAG_BORDER_CONSTANT) ? flags : (flags | BS_FLAG_KEEP_CANVAS), &h);
     if (rc != BS_OK) return rc;
     const uint8_t *frames[1] = {src};
     size_t pitches[1] = {spitch};

@@ -33,6 +33,7 @@ struct FrameArgs {
     int keep_canvas;      // 1: uncovered pixels untouched, 0: uncovered pixels = 0
     int cam_base;         // index of cam[0] among all cameras (multi-launch for > 16 cameras)
     int canvas_in_4g;     // 1: all canvas addresses share their upper 32 bits (staged kernel: rows may be stored with 32-bit address steps)
+    int border_constant;  // 1: cv::BORDER_CONSTANT 0 instead of BORDER_TRANSPARENT (exact kernel only)
 };
 
 // ---- Appendix A.1, exact form -------------------------------------------------------------
@@ -102,10 +103,37 @@ __device__ __forceinline__ bool sample_exact(const CamDev &c, int X, int Y, int 
 }
 
 // Winner search for one canvas pixel: highest camera index that covers it (Appendix A.5).
+// cv::BORDER_CONSTANT with value 0 (lib/Calibrate/utils.cpp:390): every pixel is
+// written, taps outside the source count as 0.
+__device__ __forceinline__ uint32_t sample_constant(const CamDev &c, int X, int Y)
+{
+    const int sx = sat_s16(X >> kFracBits), sy = sat_s16(Y >> kFracBits);
+    const int a = X & (kFracOne - 1), b = Y & (kFracOne - 1);
+    const int wgt[4] = {(kFracOne - a) * (kFracOne - b), a * (kFracOne - b), (kFracOne - a) * b, a * b};
+    uint32_t out = 0;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        int acc = 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int tx = sx + (t & 1), ty = sy + (t >> 1);
+            if (tx >= 0 && tx < c.w && ty >= 0 && ty < c.h) acc += wgt[t] * __ldg(c.ptr + (long long)ty * c.pitch + (long long)tx * 3 + ch);
+        }
+        out |= (uint32_t)((acc + 512) >> 10) << (8 * ch);   // == (32 acc + 2^14) >> 15
+    }
+    return out;
+}
+
 __device__ __forceinline__ bool composite_exact(const FrameArgs &A, int x, int y, uint32_t &bgr)
 {
     const int xb = (x / A.block_w) * A.block_w;
     const int x1 = x - xb;
+    if (A.border_constant) {            // the last camera writes every pixel
+        int X, Y;
+        coord_exact(A.cam[A.n_cams - 1].M, xb, x1, y, X, Y);
+        bgr = sample_constant(A.cam[A.n_cams - 1], X, Y);
+        return true;
+    }
     for (int i = A.n_cams - 1; i >= 0; --i) {
         int X, Y;
         coord_exact(A.cam[i].M, xb, x1, y, X, Y);

@@ -46,6 +46,11 @@ extern "C" {
 #define BS_FLAG_KEEP_CANVAS 0x2u
 /* Testing aid: run every tile through the exact per-pixel kernel (no tile plan fast path). */
 #define BS_FLAG_EXACT_ONLY 0x4u
+/* cv::BORDER_CONSTANT with value 0 instead of BORDER_TRANSPARENT: every canvas pixel is written and
+ * source taps outside the frame count as 0 -- the variant lib/Calibrate/utils.cpp:390
+ * (projectToTheFloor) uses; SURVEY.md row f3.  Meant for bs_warp_perspective; in a handle the last
+ * camera then overwrites the whole canvas, as N such OpenCV calls would.  Implies BS_FLAG_EXACT_ONLY. */
+#define BS_FLAG_BORDER_CONSTANT 0x8u
 
 #define BS_MAX_CAMERAS 64
 #define BS_MAX_DIM 32767 /* OpenCV keeps integer source coordinates in int16 */

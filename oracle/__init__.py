@@ -14,6 +14,7 @@ _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
 BORDER_CV4 = 0
 BORDER_LEGACY = 1
+BORDER_CONSTANT = 2     # warp_perspective only: cv2.BORDER_CONSTANT, value 0, every pixel written
 NOISE = 0
 SMOOTH = 1
 

@@ -150,6 +150,23 @@ static inline int sample_transparent(const uint8_t *src, int sw, int sh, size_t 
     return 1;
 }
 
+/* cv::warpPerspective(..., BORDER_CONSTANT, borderValue = 0) for one canvas pixel: every pixel is
+ * written, taps outside the source count as 0 (lib/Calibrate/utils.cpp:390). */
+static inline void sample_constant(const uint8_t *src, int sw, int sh, size_t spitch, int X, int Y, uint8_t out[3])
+{
+    const int sx = sat_s16(X >> FRAC_BITS), sy = sat_s16(Y >> FRAC_BITS);
+    const int a = X & (FRAC_ONE - 1), b = Y & (FRAC_ONE - 1);
+    const int w[4] = {(FRAC_ONE - a) * (FRAC_ONE - b) * 32, a * (FRAC_ONE - b) * 32, (FRAC_ONE - a) * b * 32, a * b * 32};
+    for (int c = 0; c < 3; ++c) {
+        int v = 0;
+        for (int t = 0; t < 4; ++t) {
+            const int tx = sx + (t & 1), ty = sy + (t >> 1);
+            if (tx >= 0 && tx < sw && ty >= 0 && ty < sh) v += w[t] * src[(size_t)ty * spitch + (size_t)tx * 3 + c];
+        }
+        out[c] = (uint8_t)((v + (1 << (COEF_BITS - 1))) >> COEF_BITS);
+    }
+}
+
 void oracle_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8_t *dst,
                              int dw, int dh, size_t dpitch, const double H[9], int border_rule,
                              int nthreads)
@@ -168,7 +185,12 @@ void oracle_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, 
             int xb = (x / bw) * bw;
             coord_rel(M, xb, x - xb, y, &X, &Y);
             uint8_t px[3];
-            if (sample_transparent(src, sw, sh, spitch, X, Y, border_rule, px)) {
+            if (border_rule == ORACLE_BORDER_CONSTANT) {
+                sample_constant(src, sw, sh, spitch, X, Y, px);
+                drow[3 * x + 0] = px[0];
+                drow[3 * x + 1] = px[1];
+                drow[3 * x + 2] = px[2];
+            } else if (sample_transparent(src, sw, sh, spitch, X, Y, border_rule, px)) {
                 drow[3 * x + 0] = px[0];
                 drow[3 * x + 1] = px[1];
                 drow[3 * x + 2] = px[2];

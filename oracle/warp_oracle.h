@@ -35,6 +35,8 @@ extern "C" {
  * (SURVEY.md Appendix A.4). */
 #define ORACLE_BORDER_CV4 0    /* OpenCV 4.13: written, weights renormalised in fp32 */
 #define ORACLE_BORDER_LEGACY 1 /* OpenCV 2.4/3.x: left untouched */
+#define ORACLE_BORDER_CONSTANT 2 /* not BORDER_TRANSPARENT at all: BORDER_CONSTANT 0, every pixel written
+                                  (oracle_warp_perspective only; lib/Calibrate/utils.cpp:390) */
 
 /* 3x3 double inverse the way cv::warpPerspective obtains M = H^-1
  * (call sites tools/stitch/main.cpp:116,150).  Returns 1 on success, 0 if singular

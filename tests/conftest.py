@@ -43,6 +43,11 @@ def undistort_cases():
 
 
 @pytest.fixture(scope="session")
+def border_constant_cases():
+    return _load_cases("border_constant_cases.npz", "b")
+
+
+@pytest.fixture(scope="session")
 def known_answers():
     with open(os.path.join(GOLDEN, "known_answers.json")) as f:
         return json.load(f)

@@ -169,8 +169,29 @@ def undistort_cases():
     print("undistort cases:", len(meta))
 
 
+def border_constant_cases():
+    """cv::warpPerspective with BORDER_CONSTANT (value 0), the variant projectToTheFloor uses
+    (lib/Calibrate/utils.cpp:390)."""
+    rng = np.random.default_rng(11)
+    arrays = {}
+    meta = []
+    for k, ((sw, sh), (dw, dh)) in enumerate([((90, 60), (200, 120)), ((333, 77), (300, 260)), ((2, 2), (70, 40)),
+                                               ((320, 240), (500, 350)), ((50, 50), (33, 9))]):
+        src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+        H = rand_h(rng, dw, dh, strong=bool(k & 1))
+        arrays[f"b{k}_src"] = src
+        arrays[f"b{k}_H"] = H
+        arrays[f"b{k}_exp"] = cv2.warpPerspective(src, H, (dw, dh), flags=cv2.INTER_LINEAR, borderMode=cv2.BORDER_CONSTANT,
+                                                  borderValue=0)
+        meta.append({"case": k, "src_wh": [sw, sh], "canvas_wh": [dw, dh]})
+    arrays["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+    np.savez_compressed(os.path.join(HERE, "border_constant_cases.npz"), **arrays)
+    print("border-constant cases:", len(meta))
+
+
 if __name__ == "__main__":
     cv2.setNumThreads(cv2.getNumberOfCPUs())
     small_cases()
     undistort_cases()
+    border_constant_cases()
     known_answers()

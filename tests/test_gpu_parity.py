@@ -221,3 +221,27 @@ def test_staged_store_path_known_answer(known_answers):
     out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr[-2000:]
     assert out.stdout.strip().splitlines()[-1] == want["canvas_sha256"]
+
+
+def test_border_constant_warp(border_constant_cases):
+    """the BORDER_CONSTANT variant of the same call (lib/Calibrate/utils.cpp:390),
+    through bs_warp_perspective; dst is overwritten completely."""
+    p = pkg()
+    z, meta = border_constant_cases
+    for m in meta:
+        k = m["case"]
+        dw, dh = m["canvas_wh"]
+        dst = np.full((dh, dw, 3), 201, np.uint8)
+        p.warpPerspective(np.ascontiguousarray(z[f"b{k}_src"]), dst, z[f"b{k}_H"], (dw, dh), borderMode=p.BORDER_CONSTANT)
+        assert_same(dst, z[f"b{k}_exp"], f"border-constant case {k}")
+    rng = np.random.default_rng(77)
+    for trial in range(12):                      # and against the oracle on random maps
+        sw, sh = int(rng.integers(1, 700)), int(rng.integers(1, 500))
+        dw, dh = int(rng.integers(1, 1200)), int(rng.integers(1, 800))
+        src = rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8)
+        H = random_h(rng, dw, dh, strong=bool(trial & 1))
+        want = np.zeros((dh, dw, 3), np.uint8)
+        oracle.warp_perspective(src, H, want, oracle.BORDER_CONSTANT)
+        dst = np.full((dh, dw, 3), 9, np.uint8)
+        p.warpPerspective(src, dst, H, (dw, dh), borderMode=p.BORDER_CONSTANT)
+        assert_same(dst, want, f"border-constant trial {trial}")

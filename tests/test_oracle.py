@@ -134,3 +134,15 @@ def test_invert_matches_cv2_when_available():
                                                             [1e-4, 1e-4, 0.01]])
         M, ok = oracle.invert3x3(H)
         assert np.array_equal(M, cv2.invert(H)[1])
+
+
+def test_border_constant_golden_cases(border_constant_cases):
+    """warpPerspective with BORDER_CONSTANT 0 (lib/Calibrate/utils.cpp:390), against
+    cv2 outputs; the destination's previous contents must not matter."""
+    z, meta = border_constant_cases
+    for m in meta:
+        k = m["case"]
+        dw, dh = m["canvas_wh"]
+        out = np.full((dh, dw, 3), 77, np.uint8)
+        oracle.warp_perspective(np.ascontiguousarray(z[f"b{k}_src"]), z[f"b{k}_H"], out, oracle.BORDER_CONSTANT)
+        assert np.array_equal(out, z[f"b{k}_exp"]), f"case {k}"

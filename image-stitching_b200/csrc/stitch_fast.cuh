@@ -202,7 +202,10 @@ constexpr int kFastThreads = 32 * kWarpsPerCta;
 #endif
 constexpr int kStages = BS_STAGES;                     // per warp: source boxes of items i .. i + kStages - 1
 constexpr int kPrefetch = kStages - 1;                 // boxes in flight ahead of the one being computed
-constexpr int kRecSlots = 16;                          // per warp: record ring, refilled in halves of 8 by one bulk copy each
+#ifndef BS_REC_SLOTS
+#define BS_REC_SLOTS 16
+#endif
+constexpr int kRecSlots = BS_REC_SLOTS;                          // per warp: record ring, refilled in halves of 8 by one bulk copy each
 constexpr int kRecHalf = kRecSlots / 2;
 constexpr int kBlockRowBytes = 96;                     // 32 pixels
 constexpr int kWarpOutBytes = kRun * kBlockRowBytes;   // 1536
@@ -527,14 +530,18 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
             if (type == (uint32_t)kBlockExact) {
                 // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j
                 for (int j = 0; j < kRun / 4; ++j) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
-            } else if (!wrote) {
-                if (!A.F.keep_canvas) store_block_checked(A.F, 0u, tx0, ty0, lane);   // nobody writes here
+            } else if (!wrote && A.F.keep_canvas) {
+                // nobody writes here and the canvas keeps its contents
             } else if (tx0 + kBlockW <= A.F.W && ty0 + kRun <= A.F.H) {
-                // flush: lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
+                // flush (or zero fill of an empty block): lane pair (2r, 2r+1) writes one full 32-byte
+                // sector of row r per instruction
                 const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
                 uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch + (long long)tx0 * 3 + (lane & 1) * 16;
 #pragma unroll
-                for (int j = 0; j < 3; ++j) *reinterpret_cast<uint4 *>(gp + 32 * j) = lds128(so + 32u * j);
+                for (int j = 0; j < 3; ++j)
+                    *reinterpret_cast<uint4 *>(gp + 32 * j) = wrote ? lds128(so + 32u * j) : make_uint4(0u, 0u, 0u, 0u);
+            } else if (!wrote) {
+                store_block_checked(A.F, 0u, tx0, ty0, lane);
             } else {
                 store_block_checked(A.F, out_blk, tx0, ty0, lane);
             }

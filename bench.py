@@ -280,9 +280,22 @@ def run_b200(args, rank, local_rank, world):
 
     # ring of RING frame sets per camera, distinct per rank (frame f -> GPU f mod world)
     torch.cuda.synchronize()
-    d_frames = [[wl.gen_frame_torch(sw, sh, i, rank + world * f, args.content, dev) for i in range(n)]
-                for f in range(RING)]
-    d_canvas = [torch.empty((H, W, 3), dtype=torch.uint8, device=dev) for _ in range(RING)]
+    def padded(h_, w_):
+        """(h_, w_, 3) view of a buffer whose rows start on 128-byte boundaries (any width then takes
+        the staged kernel; a tight pitch that is not a multiple of 16 falls back to the exact kernel)."""
+        pitch = (3 * w_ + 127) // 128 * 128
+        buf = torch.empty((h_, pitch), dtype=torch.uint8, device=dev)
+        return buf[:, :3 * w_].unflatten(1, (w_, 3))
+
+    d_frames = []
+    for f in range(RING):
+        fs = []
+        for i in range(n):
+            t = padded(sh, sw)
+            t.copy_(wl.gen_frame_torch(sw, sh, i, rank + world * f, args.content, dev))
+            fs.append(t)
+        d_frames.append(fs)
+    d_canvas = [padded(H, W) for _ in range(RING)]
     st = pkg.Stitcher([w.src_wh] * n, w.canvas_wh, w.H, flags=args.flags, device=local_rank)
     stream = torch.cuda.Stream(device=dev)       # the kernels and the timing events share this stream
     torch.cuda.set_stream(stream)

@@ -81,6 +81,7 @@ struct bs_handle {
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
     int stage_bytes = 0, smem_bytes = 0, grid = 0;
     int remap_grid = 0;                  // persistent CTAs of undistort_remap_kernel (set with the first lens map)
+    int rec_slots = bs::kRecSlotsMax;    // record ring slots per warp of the frame kernel
     std::vector<TmapEntry> tmap_cache;   // n_cams x kTmapCacheWays, filled round-robin per camera
     unsigned tmap_next[bs::kMaxCamsPerLaunch] = {0};
     uint64_t device_bytes = 0, scratch_bytes = 0;
@@ -205,6 +206,9 @@ int encode_frame_map(CUtensorMap *m, const void *ptr, size_t pitch, int h, int b
 
 constexpr int kStageBytesMax = 6 * 1024;    // per-warp, per-stage cap on a block's source box
 
+// Dynamic shared memory of one CTA of the frame kernel (+ alignment slack).
+int cta_smem_bytes(int stage_bytes, int rec_slots) { return bs::kWarpsPerCta * bs::warp_smem_bytes(stage_bytes, rec_slots) + 128; }
+
 // Result of turning the raw block records into what the frame kernel consumes.
 struct PlanLayout {
     int box_we[bs::kMaxCamsPerLaunch] = {0}, box_h[bs::kMaxCamsPerLaunch] = {0};
@@ -258,7 +262,7 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
         stage = std::max(stage, we[c] * 4 * bh[c]);
     }
     L->stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
-    L->smem_bytes = bs::kWarpsPerCta * bs::warp_smem_bytes(L->stage_bytes) + 128;   // + alignment slack
+    L->smem_bytes = cta_smem_bytes(L->stage_bytes, bs::kRecSlotsMax);
     L->n_fast = L->n_exact = L->n_empty = 0;
     int n = 0;
     auto emit = [&](const bs::BlockRec &r, int l) {
@@ -296,6 +300,21 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
     for (int t = 0; t < n_blocks; ++t)
         if (recs[t].type == bs::kBlockEmpty) emit(recs[t], 0), L->n_empty++;
     L->n_items = n;
+}
+
+// Record ring size and CTAs per SM for a plan: 16 slots per warp unless 8 let one more CTA fit an SM
+// (large source boxes, e.g. strong perspective).  Returns CTAs per SM (0: the kernel does not fit).
+int choose_rec_slots(int stage_bytes, int *rec_slots, int *smem_bytes)
+{
+    int per16 = 0, per8 = 0;
+    const int s16 = cta_smem_bytes(stage_bytes, bs::kRecSlotsMax), s8 = cta_smem_bytes(stage_bytes, bs::kRecSlotsMax / 2);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per16, bs::stitch_fast_kernel, bs::kFastThreads, s16) != cudaSuccess) per16 = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per8, bs::stitch_fast_kernel, bs::kFastThreads, s8) != cudaSuccess) per8 = 0;
+    cudaGetLastError();
+    const bool small = per8 > per16;
+    *rec_slots = small ? bs::kRecSlotsMax / 2 : bs::kRecSlotsMax;
+    *smem_bytes = small ? s8 : s16;
+    return small ? per8 : per16;
 }
 
 // Deal the plan's blocks round-robin to the n_warps warps of the grid (block u to warp u mod n_warps;
@@ -412,12 +431,11 @@ int build_plan(bs_handle *h)
         // the device's opt-in maximum, so a handle with a small plan cannot lower it for another one.
         int optin = 0;
         BS_CUDA(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
-        if (h->smem_bytes > optin) return BS_OK;   // does not fit: stay on the exact kernel
+        if (cta_smem_bytes(h->stage_bytes, bs::kRecSlotsMax / 2) > optin) return BS_OK;   // does not fit: stay on the exact kernel
         BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
     }
-    int per_sm = 0, sms = 0;
-    BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kFastThreads,
-                                                             h->smem_bytes));
+    int sms = 0;
+    const int per_sm = choose_rec_slots(h->stage_bytes, &h->rec_slots, &h->smem_bytes);
     BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
     if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
     h->grid = std::max(1, std::min((h->n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
@@ -599,6 +617,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         FA.items = h->d_items;
         FA.warp_start = h->d_warp_start;
         FA.stage_bytes = h->stage_bytes;
+        FA.rec_slots = h->rec_slots;
         {
             // programmatic dependent launch: the prologue and first tile of this frame may overlap the
             // tail of the previous frame's kernel on the same stream (see stitch_fast.cuh)
@@ -1206,12 +1225,12 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     // ---- size one TMA box per camera, flatten to work items, split them over the grid's warps -------
     PlanLayout L;
     layout_plan(g_static_recs, n_blocks, n_cams, g_static_items, &L);
-    bool fast = L.n_fast > 0 && get_encoder() && L.smem_bytes <= st->smem_optin && aligned16(d_canvas, canvas_pitch);
+    bool fast = L.n_fast > 0 && get_encoder() && cta_smem_bytes(L.stage_bytes, bs::kRecSlotsMax / 2) <= st->smem_optin &&
+                aligned16(d_canvas, canvas_pitch);
     for (int i = 0; fast && i < n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
-    int per_sm = 0;
+    int per_sm = 0, rec_slots = bs::kRecSlotsMax;
     if (fast) {
-        BS_CUDA(nullptr, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast_kernel, bs::kFastThreads,
-                                                                       L.smem_bytes));
+        per_sm = choose_rec_slots(L.stage_bytes, &rec_slots, &L.smem_bytes);
         fast = per_sm >= 1;
     }
 
@@ -1264,6 +1283,7 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     FA.items = reinterpret_cast<const bs::WorkItem *>(st->scratch->plan);
     FA.warp_start = st->scratch->warp_start;
     FA.stage_bytes = L.stage_bytes;
+    FA.rec_slots = rec_slots;
     bs::stitch_fast_kernel<<<grid, bs::kFastThreads, L.smem_bytes, s>>>(FA);
     BS_CUDA(nullptr, cudaGetLastError());
     // the host staging arrays are reused by the next call: everything queued above must have left them

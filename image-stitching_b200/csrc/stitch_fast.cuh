@@ -33,6 +33,7 @@ struct FastArgs {
     int pitch[kMaxCamsPerLaunch];          // TMA box of camera i: row pitch in shared memory (bytes) ...
     int box_bytes[kMaxCamsPerLaunch];      // ... and total bytes (= what the mbarrier expects)
     int stage_bytes;                       // shared memory per stage (multiple of 128)
+    int rec_slots;                         // record ring slots per warp: 16, or 8 when that lets one more CTA fit an SM
 };
 
 // First 4-byte element of the staged box for a bounding box whose first texel column is bx0.
@@ -202,19 +203,21 @@ constexpr int kFastThreads = 32 * kWarpsPerCta;
 #endif
 constexpr int kStages = BS_STAGES;                     // per warp: source boxes of items i .. i + kStages - 1
 constexpr int kPrefetch = kStages - 1;                 // boxes in flight ahead of the one being computed
-#ifndef BS_REC_SLOTS
-#define BS_REC_SLOTS 16
-#endif
-constexpr int kRecSlots = BS_REC_SLOTS;                          // per warp: record ring, refilled in halves of 8 by one bulk copy each
-constexpr int kRecHalf = kRecSlots / 2;
+constexpr int kRecSlotsMax = 16;                       // per warp: record ring of 16 or 8 slots (FastArgs::rec_slots),
+                                                       // refilled in halves by one bulk copy each
 constexpr int kBlockRowBytes = 96;                     // 32 pixels
 constexpr int kWarpOutBytes = kRun * kBlockRowBytes;   // 1536
 constexpr int kRecBytes = 80;                          // sizeof(WorkItem)
-constexpr int kWarpCtlBytes = (kRecSlots * kRecBytes + (kStages + 2) * 8 + 127) / 128 * 128;   // records + mbarriers, keeps every warp's region 128-byte aligned
 
-__host__ __device__ constexpr int warp_smem_bytes(int stage_bytes)
+// records + mbarriers, rounded so that every warp's region stays 128-byte aligned
+__host__ __device__ constexpr int warp_ctl_bytes(int rec_slots)
 {
-    return kStages * stage_bytes + kWarpOutBytes + kWarpCtlBytes;
+    return (rec_slots * kRecBytes + (kStages + 2) * 8 + 127) / 128 * 128;
+}
+
+__host__ __device__ constexpr int warp_smem_bytes(int stage_bytes, int rec_slots)
+{
+    return kStages * stage_bytes + kWarpOutBytes + warp_ctl_bytes(rec_slots);
 }
 
 // The block's coordinate expansion as it sits in a record slot (words 4..19 of the work item).
@@ -394,11 +397,12 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const uint32_t wbase = raw_base + (uint32_t)(warp * warp_smem_bytes(A.stage_bytes));
+    const uint32_t wbase = raw_base + (uint32_t)(warp * warp_smem_bytes(A.stage_bytes, A.rec_slots));
     const uint32_t stage0 = wbase;                                             // 128-byte aligned
     const uint32_t out_blk = stage0 + (uint32_t)(kStages * A.stage_bytes);
     const uint32_t rec0 = out_blk + kWarpOutBytes;
-    const uint32_t dbar0 = rec0 + kRecSlots * kRecBytes;                       // data barriers, one per stage
+    const uint32_t rec_slots = (uint32_t)A.rec_slots, rec_half = rec_slots >> 1;   // powers of two
+    const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per stage
     const uint32_t rbar0 = dbar0 + kStages * 8;                                // record barriers, one per half of the ring
 
     // Programmatic dependent launch: let the next frame's kernel start filling SMs as this one's CTAs
@@ -423,11 +427,11 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     // lane 0 is this warp's producer ------------------------------------------------------------------
     // records of items [first, first + 8) -> their half of the record ring, one bulk copy
     auto request_records = [&](int first) {
-        const uint32_t bytes = (uint32_t)(min(kRecHalf, cnt - first) * kRecBytes);
-        const uint32_t half = ((uint32_t)first / kRecHalf) & 1u;
+        const uint32_t bytes = (uint32_t)(min((int)rec_half, cnt - first) * kRecBytes);
+        const uint32_t half = ((uint32_t)first / rec_half) & 1u;
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * half), "r"(bytes) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         rec0 + kRecBytes * kRecHalf * half),
+                         rec0 + kRecBytes * rec_half * half),
                      "l"(A.items + i0 + first), "r"(bytes), "r"(rbar0 + 8 * half)
                      : "memory");
     };
@@ -448,14 +452,14 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         }
     };
     // record words / lane coefficients of item m from the record ring (all lanes)
-    auto rec_addr = [&](int m) { return rec0 + kRecBytes * ((uint32_t)m & (kRecSlots - 1)); };
+    auto rec_addr = [&](int m) { return rec0 + kRecBytes * ((uint32_t)m & (rec_slots - 1)); };
     auto wait_half_of = [&](int m) {      // first item of a half: every lane observes the copy's completion itself
-        if ((m & (kRecHalf - 1)) == 0) mbar_wait_addr(rbar0 + 8 * (((uint32_t)m / kRecHalf) & 1u), ((uint32_t)m / kRecSlots) & 1u);
+        if (((uint32_t)m & (rec_half - 1)) == 0) mbar_wait_addr(rbar0 + 8 * (((uint32_t)m / rec_half) & 1u), ((uint32_t)m / rec_slots) & 1u);
     };
 
     if (lane == 0) {
         request_records(0);
-        if (cnt > kRecHalf) request_records(kRecHalf);
+        if (cnt > (int)rec_half) request_records((int)rec_half);
     }
     __syncwarp();
     wait_half_of(0);
@@ -475,7 +479,7 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     for (int n = 0; n < cnt; ++n) {
         if (lane == 0) {
             // the half of the record ring that items n-8 .. n-1 used is free: refill it with n+8 .. n+15
-            if ((n & (kRecHalf - 1)) == 0 && n >= kRecHalf && n + kRecHalf < cnt) request_records(n + kRecHalf);
+            if (((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt) request_records(n + (int)rec_half);
             // prefetch: the box of item n+1 goes into the stage item n-1 is done with
             if (n + 1 < cnt) issue_box(recn, stage ^ 1u);
         }

@@ -464,8 +464,9 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     __syncwarp();
     wait_half_of(0);
     // The per-item set-up is software-pipelined across items: while item n is computed, the record of
-    // item n+2 and the lane coefficients of item n+1 are already being read, and the box of item n+1
-    // is in flight.
+    // item n+2 has been read and the box of item n+1 is in flight.  (The lane coefficients of item n+1
+    // are formed after item n: carrying a second set through the hot loop cost ten registers and ten
+    // moves per item for nothing.)
     uint4 rec = lds128(rec_addr(0));
     uint4 recn = cnt > 1 ? lds128(rec_addr(1)) : rec;
     LaneCoef lc = lane_coef(load_block_coef(rec_addr(0)), lane - kBlockW / 2);
@@ -485,15 +486,12 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         }
         __syncwarp();
         const bool landed = mbar_try_wait_addr(dbar0 + 8 * stage, dpar);    // probe now, look at the answer later
-        // look-ahead reads for the next two items
+        // look-ahead read: the record of the item after next
         uint4 recn2 = recn;
         if (n + 2 < cnt) {
             wait_half_of(n + 2);
             recn2 = lds128(rec_addr(n + 2));
         }
-        LaneCoef lcn = lc;
-        if (n + 1 < cnt) lcn = lane_coef(load_block_coef(rec_addr(n + 1)), lane - kBlockW / 2);
-
         const uint4 r = rec;
         bool direct = false;
         const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
@@ -554,7 +552,7 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
         }
         rec = recn;
         recn = recn2;
-        lc = lcn;
+        if (n + 1 < cnt) lc = lane_coef(load_block_coef(rec_addr(n + 1)), lane - kBlockW / 2);
         dpar ^= stage;                // the parity flips every second item
         stage ^= 1u;
     }

@@ -242,10 +242,9 @@ __device__ __forceinline__ BlockCoef load_block_coef(uint32_t rec_addr)
 // otherwise rows are collected in the warp's output block in shared memory.
 template <bool kDirect>
 __device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, uint32_t stage_origin,
-                                               uint32_t out_blk, int lane, uint8_t *grow, long long cpitch)
+                                               uint32_t out_blk, int lane, uint8_t *grow, long long cpitch,
+                                               uint32_t sel, uint32_t storing)
 {
-    const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
-    const uint32_t storing = (uint32_t)((lane & 3) != 3);
     const uint32_t glo = (uint32_t)reinterpret_cast<uintptr_t>(grow), ghi = (uint32_t)(reinterpret_cast<uintptr_t>(grow) >> 32);
     const uint32_t run_base = stage_origin + (uint32_t)((lc.by >> kFracBits) * pitch + (lc.bx >> kFracBits) * 3);
     const int step = lc.nyv * pitch + lc.nxv * 3;      // whole texels per canvas row, as a byte offset
@@ -473,6 +472,9 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     if (lane == 0) issue_box(rec, 0u);
     __syncwarp();
 
+    // lane constants of the output word merge (store_row_pixel): byte selector, and whether this lane owns a word
+    const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
+    const uint32_t storing = (uint32_t)((lane & 3) != 3);
     bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
     bool wrote = false;               // some layer has written into the current block
     uint32_t stage = 0, dpar = 0;     // stage and data-barrier parity of the current item (kStages == 2)
@@ -511,9 +513,9 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                          (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
                 uint8_t *const grow = A.F.canvas + (long long)ty0 * A.F.cpitch + (long long)tx0 * 3 + 4 * (3 * (lane >> 2) + (lane & 3));
                 if (direct)
-                    run_layer_full<true>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch);
+                    run_layer_full<true>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch, sel, storing);
                 else
-                    run_layer_full<false>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch);
+                    run_layer_full<false>(lc, pitch, stage_origin, out_blk, lane, grow, A.F.cpitch, sel, storing);
                 if (groups != 0u) {
                     __syncwarp();
                     patch_exact_groups(A, cam, pitch, stage_origin, out_blk, groups, tx0 + lane, ty0, lane);

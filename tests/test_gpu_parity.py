@@ -245,3 +245,27 @@ def test_border_constant_warp(border_constant_cases):
         dst = np.full((dh, dw, 3), 9, np.uint8)
         p.warpPerspective(src, dst, H, (dw, dh), borderMode=p.BORDER_CONSTANT)
         assert_same(dst, want, f"border-constant trial {trial}")
+
+
+def test_handle_lifecycle_does_not_leak():
+    """bs_create / bs_set_undistort / bs_stitch / bs_destroy in a loop: device memory returns to where it was."""
+    import torch
+    p = pkg()
+    w = workloads().get("cfg2")
+    sw, sh = w.src_wh
+    srcs = [oracle.gen_frame(sw, sh, i, 0, oracle.NOISE) for i in range(w.n_cams)]
+    K = np.array([[0.9 * sw, 0, sw / 2 + 3.3], [0, 0.92 * sw, sh / 2 - 1.7], [0, 0, 1]])
+
+    def cycle():
+        with p.Stitcher([w.src_wh] * w.n_cams, w.canvas_wh, w.H) as st:
+            st.set_undistort(0, K, [-0.2, 0.05, 0.001, -0.002, 0.01])
+            st.stitch(srcs)
+
+    cycle()                                   # first use: context, module and pool warm-up
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(10):
+        cycle()
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free0 - free1 < 8 << 20, f"{(free0 - free1) >> 20} MiB lost over 10 create/destroy cycles"

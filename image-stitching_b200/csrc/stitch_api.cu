@@ -293,8 +293,28 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
             L->n_fast++;
             L->n_two++;
         }
+    // An EXACT block costs a warp about eight plain ones (fp64 coordinates for every camera and pixel):
+    // deal it as four items of four rows each (WorkItem::groups = which rows), as long as the item
+    // array, sized for two items per block, has room.
+    int n_exact_blocks = 0, n_single = 0;
+    for (int t = 0; t < n_blocks; ++t) {
+        n_exact_blocks += recs[t].type == bs::kBlockExact;
+        n_single += recs[t].type != bs::kBlockExact && !(recs[t].type == bs::kBlockFast && recs[t].n_layers == 2);
+    }
+    const bool split_exact = 2 * L->n_two + n_single + (long long)(bs::kRun / 4) * n_exact_blocks <= 2LL * n_blocks;
     for (int t = 0; t < n_blocks; ++t)
-        if (recs[t].type == bs::kBlockExact) emit(recs[t], 0), L->n_exact++;
+        if (recs[t].type == bs::kBlockExact) {
+            if (split_exact) {
+                for (int g = 0; g < bs::kRun / 4; ++g) {
+                    emit(recs[t], 0);
+                    items[n - 1].groups = (uint8_t)(1u << g);
+                }
+            } else {
+                emit(recs[t], 0);
+                items[n - 1].groups = (uint8_t)((1u << (bs::kRun / 4)) - 1);
+            }
+            L->n_exact++;
+        }
     for (int t = 0; t < n_blocks; ++t)
         if (recs[t].type == bs::kBlockFast && recs[t].n_layers == 1) emit(recs[t], 0), L->n_fast++;
     for (int t = 0; t < n_blocks; ++t)
@@ -443,7 +463,7 @@ int build_plan(bs_handle *h)
     const int n_warps = h->grid * bs::kWarpsPerCta;
     std::vector<bs::WorkItem> grouped(items.size());
     std::vector<int> warp_start(n_warps + 1);
-    group_items_by_warp(items.data(), h->n_blocks, L.n_two, n_warps, grouped.data(), warp_start.data());
+    group_items_by_warp(items.data(), L.n_items - L.n_two, L.n_two, n_warps, grouped.data(), warp_start.data());
 
     const size_t item_bytes = sizeof(bs::WorkItem) * (size_t)h->n_items;   // <= raw_bytes: 2 x 80 B per block
     BS_CUDA(h, upload_now(h, h->d_items, grouped.data(), item_bytes));
@@ -1274,7 +1294,7 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     int grid = std::max(1, std::min((n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
     grid = std::min(grid, kStaticMaxWarps / bs::kWarpsPerCta);
     const int n_warps = grid * bs::kWarpsPerCta;
-    group_items_by_warp(g_static_items, n_blocks, L.n_two, n_warps, g_static_grouped, g_static_warp_start);
+    group_items_by_warp(g_static_items, L.n_items - L.n_two, L.n_two, n_warps, g_static_grouped, g_static_warp_start);
     // the item list replaces the raw records in the scratch; stream-ordered after the previous call's kernels
     BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_grouped, sizeof(bs::WorkItem) * (size_t)L.n_items,
                                      cudaMemcpyHostToDevice, s));

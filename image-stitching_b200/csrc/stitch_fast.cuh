@@ -532,8 +532,10 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                 prior_grid_done = true;
             }
             if (type == (uint32_t)kBlockExact) {
-                // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j
-                for (int j = 0; j < kRun / 4; ++j) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+                // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j; the item names its row groups j
+                const uint32_t rows = (r.y >> 24) & 0xFFu;
+                for (int j = 0; j < kRun / 4; ++j)
+                    if ((rows >> j) & 1u) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
             } else if (!wrote && A.F.keep_canvas) {
                 // nobody writes here and the canvas keeps its contents
             } else if (tx0 + kBlockW <= A.F.W && ty0 + kRun <= A.F.H) {

@@ -4,16 +4,18 @@
 // camera layer; a block's layers are adjacent, lowest camera first, so later cameras overwrite
 // earlier ones exactly as the reference's loop does, /root/reference/tools/stitch/main.cpp:145-152).
 // For every item the warp
-//   1. prefetches, two items ahead, the camera's source bounding box into its own shared-memory
-//      stage with one TMA tensor copy (cp.async.bulk.tensor.2d) signalled on its own mbarrier --
+//   1. prefetches, one item ahead, the camera's source bounding box into one of its two shared-memory
+//      stages with one TMA tensor copy (cp.async.bulk.tensor.2d) signalled on its own mbarrier --
 //      lane 0 is the producer, nothing is shared with other warps, so no warp ever waits for one;
 //   2. computes one vertical run of 16 canvas pixels per lane: coordinates from the plan-verified
-//      fp32 expansion (or exact fp64 where the plan says so), 2x3 aligned words per pixel from the
-//      staged box, OpenCV's fixed-point bilinear weights computed from the fractions, three channel dot
-//      products (dp2a) -- bit-identical to (sum w*S + 2^14) >> 15;
-//   3. after the block's last layer, writes the finished 16x96-byte block to the canvas as 16-byte
-//      vector stores.
-// EXACT blocks run the per-pixel fp64 path of stitch_exact.cuh; EMPTY blocks are zero-filled.
+//      fp32 expansion (flagged rows are redone with exact fp64 coordinates), 2x3 aligned words per
+//      pixel from the staged box, OpenCV's fixed-point bilinear weights computed from the fractions,
+//      three channel dot products (dp2a) -- bit-identical to (sum w*S + 2^14) >> 15;
+//   3. stores each finished row straight to the canvas when the block has a single layer; blocks
+//      with two layers, partially covered layers and a warp's first block are composited in a
+//      16x96-byte block in shared memory and written out as 16-byte vector stores.
+// EXACT blocks run the per-pixel fp64 path of stitch_exact.cuh (four rows per item); EMPTY blocks are
+// zero-filled.
 #pragma once
 
 #include <cuda.h>   // CUtensorMap (type only; the encoder is fetched at run time)

@@ -276,6 +276,44 @@ __device__ __forceinline__ void run_layer_full(const LaneCoef &lc, int pitch, ui
     }
 }
 
+// Partially covered layer (a seam, the canvas border) whose cheap coordinates hold everywhere: the
+// hot path's arithmetic and software pipeline, but every pixel tests whether the camera covers it and
+// stores its three bytes on its own.  `first_layer`: pixels this layer does not cover start at 0.
+__device__ __noinline__ void run_layer_masked(const LaneCoef &lc, int pitch, uint32_t stage_origin, uint32_t out_blk, int lane,
+                                              int src_w, int src_h, bool col_in_canvas, int rows_in_canvas, bool first_layer)
+{
+    const uint32_t run_base = stage_origin + (uint32_t)((lc.by >> kFracBits) * pitch + (lc.bx >> kFracBits) * 3);
+    const int step = lc.nyv * pitch + lc.nxv * 3;
+    const uint32_t safe = out_blk;                      // any valid shared address for pixels that are not covered
+    auto fetch = [&](int k, bool &in) {
+        const int v = k - kRun / 2;
+        int xbits, ybits;
+        lane_coord_bits(lc, (float)v, xbits, ybits);
+        const int sx = (xbits + lc.bx + 32 * lc.nxv * v) >> kFracBits, sy = (ybits + lc.by + 32 * lc.nyv * v) >> kFracBits;
+        in = col_in_canvas && k < rows_in_canvas && (uint32_t)sx < (uint32_t)(src_w - 1) && (uint32_t)sy < (uint32_t)(src_h - 1);
+        const uint32_t o = run_base + (uint32_t)(v * step) +
+                           (uint32_t)((ybits >> kFracBits) * pitch + (xbits >> kFracBits) * 3);
+        return fetch_taps(in ? o : safe, pitch, tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+    };
+    bool in_cur, in_nxt = false;
+    Taps cur = fetch(0, in_cur);
+#pragma unroll 4
+    for (int k = 0; k < kRun; ++k) {
+        Taps nxt = cur;
+        if (k + 1 < kRun) nxt = fetch(k + 1, in_nxt);
+        uint32_t px = blend_taps(cur);
+        if (in_cur || first_layer) {
+            if (!in_cur) px = 0;
+            const uint32_t p8 = out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane;
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8), "r"(px) : "memory");
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 1), "r"(px >> 8) : "memory");
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 2), "r"(px >> 16) : "memory");
+        }
+        cur = nxt;
+        in_cur = in_nxt;
+    }
+}
+
 // General path: partially covered layers, blocks that stick out of the canvas, and blocks for which
 // the plan found at least one pixel where the cheap coordinates differ (those 32x4 groups use
 // the exact fp64 form).  Same arithmetic per pixel, with coverage tests and byte stores.
@@ -523,7 +561,10 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                     patch_exact_groups(A, cam, pitch, stage_origin, out_blk, groups, tx0 + lane, ty0, lane);
                 }
             } else {
-                run_layer_general(A, cam, lc, pitch, stage_origin, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
+                if (groups == 0u)
+                    run_layer_masked(lc, pitch, stage_origin, out_blk, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
+                else
+                    run_layer_general(A, cam, lc, pitch, stage_origin, out_blk, groups, full, !wrote, tx0 + lane, ty0, lane);
             }
             wrote = !direct;
         }

@@ -20,6 +20,7 @@ FLAG_LEGACY_BORDER = 0x1
 FLAG_KEEP_CANVAS = 0x2
 FLAG_EXACT_ONLY = 0x4
 FLAG_BORDER_CONSTANT = 0x8
+SUBMIT_SOURCES_SETTLED = 0x1   # bs_submit_device_ex: no kernel directly before the call writes the source frames
 
 # names of the cv2 constants the reference passes (tools/stitch/main.cpp:116-117)
 INTER_LINEAR = 1
@@ -30,7 +31,7 @@ EXPORTS = [
     "bs_device_count", "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_submit",
     "bs_wait", "bs_pipeline_depth", "bs_stitch", "bs_submit_device", "bs_sync",
     "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
-    "bs_set_undistort", "bs_undistort",
+    "bs_set_undistort", "bs_undistort", "bs_submit_device_ex",
 ]
 
 
@@ -82,6 +83,7 @@ def lib():
     L.bs_pipeline_depth.argtypes = [vp]
     L.bs_stitch.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz]
     L.bs_submit_device.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz, vp]
+    L.bs_submit_device_ex.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz, vp, ctypes.c_uint]
     L.bs_sync.argtypes = [vp]
     L.bs_warp_perspective.argtypes = [vp, i, i, sz, vp, i, i, sz, dp, ctypes.c_uint]
     L.bs_host_alloc.argtypes = [sz]
@@ -200,11 +202,16 @@ class Stitcher:
         return out
 
     # --- device buffers -------------------------------------------------------------------
-    def submit_device(self, frame_ptrs, frame_pitches, canvas_ptr, canvas_pitch, stream=0):
+    def submit_device(self, frame_ptrs, frame_pitches, canvas_ptr, canvas_pitch, stream=0, submit_flags=None):
+        """bs_submit_device (submit_flags None) or bs_submit_device_ex."""
         ptrs = (ctypes.c_void_p * self.n_cams)(*[int(p) for p in frame_ptrs])
         pitches = (ctypes.c_size_t * self.n_cams)(*[int(p) for p in frame_pitches])
-        _check(lib().bs_submit_device(self._h, ptrs, pitches, int(canvas_ptr), int(canvas_pitch),
-                                      int(stream) if stream else None), self._h)
+        st = int(stream) if stream else None
+        if submit_flags is None:
+            _check(lib().bs_submit_device(self._h, ptrs, pitches, int(canvas_ptr), int(canvas_pitch), st), self._h)
+        else:
+            _check(lib().bs_submit_device_ex(self._h, ptrs, pitches, int(canvas_ptr), int(canvas_pitch), st,
+                                             int(submit_flags)), self._h)
 
     def sync(self):
         _check(lib().bs_sync(self._h), self._h)

@@ -18,12 +18,14 @@
 
 #include <algorithm>
 
-#include "stitch_fast.cuh"
+#include "stitch_fast2.cuh"
 #include "stitch_undistort.cuh"
 
 namespace {
 
-thread_local std::string g_last_error = "";
+// Error text lives in fixed buffers (per thread, and per handle): reporting an error allocates nothing.
+constexpr size_t kErrLen = 512;
+thread_local char g_last_error[kErrLen] = "";
 thread_local int g_last_device = 0;
 
 constexpr int kPipelineDepth = 3;
@@ -52,6 +54,7 @@ struct LensModel {
     double k[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // k1 k2 p1 p2 k3 k4 k5 k6
     double *d_xs = nullptr, *d_ys = nullptr;  // device tables, see stitch_undistort.cuh
     uint32_t *d_map = nullptr;                // cached fixed-point map (w * h words), nullptr: evaluate per frame
+    uint64_t bytes = 0;                       // device memory behind the three pointers (counted in bs_handle::device_bytes)
 };
 
 }  // namespace
@@ -74,6 +77,7 @@ struct bs_handle {
     std::vector<uint8_t *> d_undist;     // undistorted frames for bs_submit_device (one set, stream-ordered)
     // tile plan (static per calibration)
     bool fast_ok = false;                // the staged kernel can be used
+    bool compact = false;                // ... and it is the compact-box kernel (stitch_fast2.cuh)
     bs::WorkItem *d_items = nullptr;     // plan: work items grouped by warp (same allocation held the raw records)
     int *d_warp_start = nullptr;         // item range of every warp of the grid
     int n_blocks = 0, blocks_x = 0, blocks_y = 0, n_items = 0;
@@ -86,20 +90,18 @@ struct bs_handle {
     unsigned tmap_next[bs::kMaxCamsPerLaunch] = {0};
     uint64_t device_bytes = 0, scratch_bytes = 0;
     uint64_t h2d_bytes_last = 0;         // bytes the last bs_submit uploaded
-    std::string err;
+    char err[512] = "";
 };
 
 namespace {
 
 int fail(bs_handle *h, int code, const char *fmt, ...)
 {
-    char buf[512];
     va_list ap;
     va_start(ap, fmt);
-    vsnprintf(buf, sizeof buf, fmt, ap);
+    vsnprintf(g_last_error, kErrLen, fmt, ap);
     va_end(ap);
-    g_last_error = buf;
-    if (h) h->err = buf;
+    if (h) memcpy(h->err, g_last_error, kErrLen);
     return code;
 }
 
@@ -215,15 +217,34 @@ struct PlanLayout {
     int stage_bytes = 0, smem_bytes = 0;
     int n_items = 0, n_two = 0;         // n_two: blocks with two camera layers (they come first)
     int64_t n_fast = 0, n_exact = 0, n_empty = 0;
+    bool compact = false;               // every staged box fits the compact kernel (stitch_fast2.cuh): 128 bytes x 18 rows
 };
 
 // Host post-processing of the plan, on caller-provided storage (no allocation here):
 //   recs[n_blocks]        raw records from plan_kernel (modified: oversized boxes are demoted to EXACT)
 //   items[>= 2*n_blocks]  output, heaviest blocks first, a block's layers adjacent
 // Sizes one TMA box per camera (the largest source box among its blocks).
-void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *items, PlanLayout *L)
+// First converted texel column of a box whose leftmost texel is x0 (compact kernel: groups of four texels
+// start on word boundaries of the packed rows), and the 16-byte aligned element the TMA box starts at.
+inline int compact_t0(int x0) { return x0 & ~3; }
+inline int compact_c0(int x0) { return bs::box_elem0(compact_t0(x0)); }
+
+void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *items, PlanLayout *L, bool allow_compact)
 {
     int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
+    // compact: every staged layer's texels fit 40 converted columns, 128 staged bytes per row and 18 rows
+    bool compact = allow_compact;
+    for (int t = 0; compact && t < n_blocks; ++t) {
+        const bs::BlockRec &r = recs[t];
+        if (r.type != bs::kBlockFast) continue;
+        for (int l = 0; l < r.n_layers; ++l) {
+            const int x0 = r.layer[l].x0, x1 = r.layer[l].x1;
+            if (x0 < 0 || x1 - compact_t0(x0) >= bs::kConvTexels || 3 * (x1 + 1) - 4 * compact_c0(x0) > bs::kRawPitch ||
+                r.layer[l].y1 - r.layer[l].y0 + 1 > bs::kRawRows)
+                compact = false;
+        }
+    }
+    L->compact = compact;
     for (int t = 0; t < n_blocks; ++t) {
         bs::BlockRec &r = recs[t];
         if (r.type != bs::kBlockFast) continue;
@@ -231,7 +252,7 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
         bool ok = true;
         for (int l = 0; l < r.n_layers; ++l) {
             const int e0 = bs::box_elem0(r.layer[l].x0), e1 = (3 * r.layer[l].x1 + 2) >> 2;   // box starts 16-byte aligned
-            twe[l] = (e1 - e0 + 1 + 3) & ~3;                                                   // inner extent: multiple of 16 bytes
+            twe[l] = compact ? bs::kRawPitch / 4 : (e1 - e0 + 1 + 3) & ~3;                     // inner extent: multiple of 16 bytes
             tbh[l] = r.layer[l].y1 - r.layer[l].y0 + 1;
             if (twe[l] > 256 || tbh[l] > 256 || twe[l] * 4 * tbh[l] > kStageBytesMax) ok = false;
         }
@@ -277,10 +298,14 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
             it.flags |= r.layer[l].full ? bs::kItemFull : 0;
             it.cam = r.layer[l].cam;
             it.groups = r.layer[l].groups;
-            it.c0 = (int16_t)bs::box_elem0(r.layer[l].x0);
+            it.c0 = (int16_t)(L->compact ? compact_c0(r.layer[l].x0) : bs::box_elem0(r.layer[l].x0));
             it.y0 = r.layer[l].y0;
             it.origin_off = (uint32_t)((int)it.y0 * (L->box_we[it.cam] * 4) + 4 * (int)it.c0);
             it.coef = r.coef[l];
+            if (L->compact) {
+                const int t0 = compact_t0(r.layer[l].x0);
+                it.coef.aux = (uint32_t)t0 | ((uint32_t)(3 * t0 - 4 * (int)it.c0) << 16);
+            }
         }
     };
     // order: two-layer blocks (two adjacent items each), then the rest heaviest first; within a class
@@ -401,7 +426,9 @@ int build_plan(bs_handle *h)
 
     std::vector<bs::WorkItem> items((size_t)h->n_blocks * bs::kMaxLayers);
     PlanLayout L;
-    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L);
+    static const bool no_compact = getenv("BS_DEBUG_NO_COMPACT") != nullptr;   // test hook: always the general staged kernel
+    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L, !no_compact);
+    h->compact = L.compact;
     memcpy(h->box_we, L.box_we, sizeof h->box_we);
     memcpy(h->box_h, L.box_h, sizeof h->box_h);
     // Source region each camera can contribute: with no EXACT block (they gather anywhere) it is the
@@ -446,21 +473,30 @@ int build_plan(bs_handle *h)
         fprintf(stderr, "[plan]   stage %d B, smem/CTA %d B\n", h->stage_bytes, h->smem_bytes);
     }
 
-    {
-        // The limit is a per-device property of the kernel, shared by every handle: always raise it to
-        // the device's opt-in maximum, so a handle with a small plan cannot lower it for another one.
-        int optin = 0;
-        BS_CUDA(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    int sms = 0, optin = 0, n_warps = 0;
+    BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+    // The shared-memory limit is a per-device property of a kernel, shared by every handle: always raise it to
+    // the device's opt-in maximum, so a handle with a small plan cannot lower it for another one.
+    BS_CUDA(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
+    if (h->compact) {
+        h->smem_bytes = bs::kWarps2 * bs::kWarp2Smem + 128;
+        int per_sm = 0;
+        if (h->smem_bytes > optin) return BS_OK;
+        BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel, bs::kFast2Threads, h->smem_bytes));
+        if (per_sm < 1) return BS_OK;
+        h->grid = std::max(1, std::min((h->n_blocks + bs::kWarps2 - 1) / bs::kWarps2, per_sm * sms));
+        if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
+        n_warps = h->grid * bs::kWarps2;
+    } else {
         if (cta_smem_bytes(h->stage_bytes, bs::kRecSlotsMax / 2) > optin) return BS_OK;   // does not fit: stay on the exact kernel
         BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        const int per_sm = choose_rec_slots(h->stage_bytes, &h->rec_slots, &h->smem_bytes);
+        if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
+        h->grid = std::max(1, std::min((h->n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
+        if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
+        n_warps = h->grid * bs::kWarpsPerCta;
     }
-    int sms = 0;
-    const int per_sm = choose_rec_slots(h->stage_bytes, &h->rec_slots, &h->smem_bytes);
-    BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
-    if (per_sm < 1) return BS_OK;   // does not fit: stay on the exact kernel
-    h->grid = std::max(1, std::min((h->n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * sms));
-    if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
-    const int n_warps = h->grid * bs::kWarpsPerCta;
     std::vector<bs::WorkItem> grouped(items.size());
     std::vector<int> warp_start(n_warps + 1);
     group_items_by_warp(items.data(), L.n_items - L.n_two, L.n_two, n_warps, grouped.data(), warp_start.data());
@@ -507,22 +543,30 @@ bs::UndistortArgs lens_args(const bs_handle *h, const LensModel &m, int i)
     return U;
 }
 
+// The buffer an undistorted frame of camera `cam` is written to (one per user of the lens model).
+int alloc_undist(bs_handle *h, std::vector<uint8_t *> &tmp, int cam)
+{
+    if ((int)tmp.size() < h->n_cams) tmp.resize(h->n_cams, nullptr);
+    if (tmp[cam]) return BS_OK;
+    const size_t bytes = h->d_frame_pitch[cam] * (size_t)h->sh[cam];
+    BS_CUDA(h, cudaMalloc(&tmp[cam], bytes));
+    h->device_bytes += bytes;
+    return BS_OK;
+}
+
 // cv::undistort for the cameras that have a lens model: src frame -> tmp[i]; the pointers the warp
 // should read are returned in out_frames / out_pitch.  Stream-ordered before the frame kernel.
 int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pitch, std::vector<uint8_t *> &tmp,
-                     const void **out_frames, size_t *out_pitch, cudaStream_t stream)
+                     const void **out_frames, size_t *out_pitch, cudaStream_t stream, bool *launched = nullptr)
 {
+    if (launched) *launched = false;
     for (int i = 0; i < h->n_cams; ++i) {
         out_frames[i] = d_frames[i];
         out_pitch[i] = pitch[i];
         if (h->lens.empty() || !h->lens[i].enabled) continue;
         const LensModel &m = h->lens[i];
-        if ((int)tmp.size() < h->n_cams) tmp.resize(h->n_cams, nullptr);
-        if (!tmp[i]) {
-            const size_t bytes = h->d_frame_pitch[i] * (size_t)h->sh[i];
-            BS_CUDA(h, cudaMalloc(&tmp[i], bytes));
-            h->device_bytes += bytes;
-        }
+        if ((int)tmp.size() < h->n_cams || !tmp[i])     // allocated by bs_set_undistort / ensure_ring, never here
+            return fail(h, BS_ERR_INVALID_ARG, "internal: no undistort buffer for camera %d", i);
         const bool aligned4 = (reinterpret_cast<uintptr_t>(d_frames[i]) & 3) == 0 && (pitch[i] & 3) == 0;
         if (m.d_map && aligned4) {
             // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
@@ -545,6 +589,7 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
         }
         BS_CUDA(h, cudaGetLastError());
         h->kernel_launches++;
+        if (launched) *launched = true;
         out_frames[i] = tmp[i];
         out_pitch[i] = h->d_frame_pitch[i];
     }
@@ -583,8 +628,10 @@ int build_lens_tables(int w, int h, const double K[9], LensModel &m, std::vector
 
 // Launch the kernels of one frame.  Cameras beyond the per-launch limit go in further
 // launches that keep what is already on the canvas (later cameras win, Appendix A.5).
+// `sources_from_kernel`: the frames may have been written by the kernel directly before this launch in
+// `stream` (an undistort kernel of ours, a caller's decoder): every source read is then ordered behind it.
 int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch, uint8_t *d_canvas,
-                 size_t cpitch, bool keep, cudaStream_t stream)
+                 size_t cpitch, bool keep, cudaStream_t stream, bool sources_from_kernel)
 {
     static const bool dbg_sync = getenv("BS_DEBUG_SYNC") != nullptr;
     if (dbg_sync) {
@@ -594,9 +641,12 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
     bool fast = h->fast_ok && aligned16(d_canvas, cpitch);
     for (int i = 0; fast && i < h->n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
     if (fast) {
-        bs::FastArgs FA;
-        memset(&FA, 0, sizeof FA);
-        bs::FrameArgs &A = FA.F;
+        // both staged kernels take the same leading members; the general one adds its box geometry
+        bs::FastArgs FA1;
+        bs::Fast2Args FA2;
+        bs::FrameArgs &A = h->compact ? FA2.F : FA1.F;
+        memset(&A, 0, sizeof A);
+        CUtensorMap *tmaps = h->compact ? FA2.tmap : FA1.tmap;
         A.n_cams = h->n_cams;
         for (int i = 0; i < A.n_cams; ++i) {
             memcpy(A.cam[i].M, &h->M[9 * i], 9 * sizeof(double));
@@ -604,8 +654,12 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             A.cam[i].pitch = (long long)pitch[i];
             A.cam[i].w = h->sw[i];
             A.cam[i].h = h->sh[i];
-            FA.pitch[i] = h->box_we[i] * 4;
-            FA.box_bytes[i] = h->box_we[i] * 4 * h->box_h[i];
+            if (h->compact) {
+                FA2.box_bytes[i] = bs::kRawPitch * h->box_h[i];
+            } else {
+                FA1.pitch[i] = h->box_we[i] * 4;
+                FA1.box_bytes[i] = h->box_we[i] * 4 * h->box_h[i];
+            }
             if (h->box_we[i] > 0) {
                 // frame buffers come from small rings (ours or the caller's): keep the last few encoded maps
                 if (h->tmap_cache.empty()) h->tmap_cache.resize((size_t)h->n_cams * kTmapCacheWays);
@@ -623,7 +677,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
                     hit->ptr = d_frames[i];
                     hit->pitch = pitch[i];
                 }
-                FA.tmap[i] = hit->map;
+                tmaps[i] = hit->map;
             }
         }
         A.canvas = d_canvas;
@@ -634,32 +688,40 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = keep ? 1 : 0;
         A.canvas_in_4g = canvas_in_4g(d_canvas, cpitch, h->H);
-        FA.items = h->d_items;
-        FA.warp_start = h->d_warp_start;
-        FA.stage_bytes = h->stage_bytes;
-        FA.rec_slots = h->rec_slots;
-        {
-            // programmatic dependent launch: the prologue and first tile of this frame may overlap the
-            // tail of the previous frame's kernel on the same stream (see stitch_fast.cuh)
-            cudaLaunchConfig_t cfg;
-            memset(&cfg, 0, sizeof cfg);
-            cfg.gridDim = dim3(h->grid);
+        // Programmatic dependent launch: the prologue and first block of this frame may overlap the
+        // tail of the previous kernel on the same stream (see stitch_fast.cuh).  When that kernel may
+        // have produced the source frames, the kernel waits for it before its first source read.
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3(h->grid);
+        cfg.dynamicSmemBytes = (size_t)h->smem_bytes;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        if (h->compact) {
+            FA2.items = h->d_items;
+            FA2.warp_start = h->d_warp_start;
+            FA2.wait_sources = sources_from_kernel ? 1 : 0;
+            cfg.blockDim = dim3(bs::kFast2Threads);
+            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel, FA2));
+        } else {
+            FA1.items = h->d_items;
+            FA1.warp_start = h->d_warp_start;
+            FA1.stage_bytes = h->stage_bytes;
+            FA1.rec_slots = h->rec_slots;
+            FA1.wait_sources = sources_from_kernel ? 1 : 0;
             cfg.blockDim = dim3(bs::kFastThreads);
-            cfg.dynamicSmemBytes = (size_t)h->smem_bytes;
-            cfg.stream = stream;
-            cudaLaunchAttribute attr[1];
-            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-            attr[0].val.programmaticStreamSerializationAllowed = 1;
-            cfg.attrs = attr;
-            cfg.numAttrs = 1;
-            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast_kernel, FA));
+            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast_kernel, FA1));
         }
         BS_CUDA(h, cudaGetLastError());
         if (dbg_sync) {
             cudaError_t e1 = cudaDeviceSynchronize();
             if (e1 != cudaSuccess)
-                return fail(h, BS_ERR_CUDA, "[debug] stitch_fast_kernel (grid %d, smem %d) faulted: %s", h->grid,
-                            h->smem_bytes, cudaGetErrorString(e1));
+                return fail(h, BS_ERR_CUDA, "[debug] staged kernel (compact %d, grid %d, smem %d) faulted: %s", (int)h->compact,
+                            h->grid, h->smem_bytes, cudaGetErrorString(e1));
         }
         h->kernel_launches++;
         return BS_OK;
@@ -710,6 +772,11 @@ int ensure_ring(bs_handle *h)
         BS_CUDA(h, cudaEventCreateWithFlags(&s.ev_h2d, cudaEventDisableTiming));
         BS_CUDA(h, cudaEventCreateWithFlags(&s.ev_kernel, cudaEventDisableTiming));
         BS_CUDA(h, cudaEventCreateWithFlags(&s.ev_done, cudaEventDisableTiming));
+        for (int i = 0; i < h->n_cams && !h->lens.empty(); ++i)
+            if (h->lens[i].enabled) {
+                const int rc = alloc_undist(h, s.d_undist, i);
+                if (rc != BS_OK) return rc;
+            }
     }
     return BS_OK;
 }
@@ -730,7 +797,7 @@ int bs_device_count(void)
 
 const char *bs_version(void) { return "b200-stitch 0.1 (sm_100a)"; }
 
-const char *bs_last_error(const bs_handle *h) { return h ? h->err.c_str() : g_last_error.c_str(); }
+const char *bs_last_error(const bs_handle *h) { return h ? h->err : g_last_error; }
 
 int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int canvas_w,
               int canvas_h, const double *H, unsigned flags, bs_handle **out)
@@ -781,7 +848,7 @@ int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int
     g_last_device = device_id;
     rc = build_plan(h);
     if (rc != BS_OK) {
-        g_last_error = h->err;
+        memcpy(g_last_error, h->err, kErrLen);
         bs_destroy(h);
         return rc;
     }
@@ -867,10 +934,12 @@ int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
     BS_CUDA(h, cudaStreamWaitEvent(h->s_compute, s.ev_h2d, 0));
     std::vector<const void *> d_frames(s.d_frame.begin(), s.d_frame.end()), warp_frames(h->n_cams);
     std::vector<size_t> warp_pitch(h->n_cams);
+    bool lens_ran = false;
     rc = undistort_frames(h, d_frames.data(), h->d_frame_pitch.data(), s.d_undist, warp_frames.data(), warp_pitch.data(),
-                          h->s_compute);
+                          h->s_compute, &lens_ran);
     if (rc != BS_OK) return rc;
-    rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep, h->s_compute);
+    // without a lens kernel the frames reach the device by copies on another stream, ordered by an event
+    rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep, h->s_compute, lens_ran);
     if (rc != BS_OK) return rc;
     BS_CUDA(h, cudaEventRecord(s.ev_kernel, h->s_compute));
     BS_CUDA(h, cudaStreamWaitEvent(h->s_d2h, s.ev_kernel, 0));
@@ -907,12 +976,14 @@ int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
     return bs_wait(h, t);
 }
 
-int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pitch, void *d_canvas,
-                     size_t canvas_pitch, void *stream)
+int bs_submit_device_ex(bs_handle *h, const void *const *d_frames, const size_t *pitch, void *d_canvas,
+                        size_t canvas_pitch, void *stream, unsigned submit_flags)
 {
     if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_submit_device: NULL handle");
     if (!d_frames || !pitch || !d_canvas)
         return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: NULL argument");
+    if (submit_flags & ~BS_SUBMIT_SOURCES_SETTLED)
+        return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: unknown submit flags 0x%x", submit_flags);
     for (int i = 0; i < h->n_cams; ++i) {
         if (!d_frames[i]) return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: frame %d is NULL", i);
         if (pitch[i] < (size_t)h->sw[i] * 3)
@@ -921,14 +992,26 @@ int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pi
     }
     if (canvas_pitch < (size_t)h->W * 3)
         return fail(h, BS_ERR_INVALID_ARG, "bs_submit_device: canvas_pitch=%zu < %d*3", canvas_pitch, h->W);
-    BS_CUDA(h, cudaSetDevice(h->device));
+    // the caller's current device is left as it was
+    int prev_dev = -1;
+    BS_CUDA(h, cudaGetDevice(&prev_dev));
+    if (prev_dev != h->device) BS_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);   // NULL = the legacy default stream
     std::vector<const void *> warp_frames(h->n_cams);
     std::vector<size_t> warp_pitch(h->n_cams);
-    int rc = undistort_frames(h, d_frames, pitch, h->d_undist, warp_frames.data(), warp_pitch.data(), st);
-    if (rc != BS_OK) return rc;
-    return launch_frame(h, warp_frames.data(), warp_pitch.data(), static_cast<uint8_t *>(d_canvas), canvas_pitch,
-                        (h->flags & BS_FLAG_KEEP_CANVAS) != 0, st);
+    bool lens_ran = false;
+    int rc = undistort_frames(h, d_frames, pitch, h->d_undist, warp_frames.data(), warp_pitch.data(), st, &lens_ran);
+    if (rc == BS_OK)
+        rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), static_cast<uint8_t *>(d_canvas), canvas_pitch,
+                          (h->flags & BS_FLAG_KEEP_CANVAS) != 0, st, lens_ran || !(submit_flags & BS_SUBMIT_SOURCES_SETTLED));
+    if (prev_dev != h->device) cudaSetDevice(prev_dev);
+    return rc;
+}
+
+int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pitch, void *d_canvas,
+                     size_t canvas_pitch, void *stream)
+{
+    return bs_submit_device_ex(h, d_frames, pitch, d_canvas, canvas_pitch, stream, 0u);
 }
 
 int bs_sync(bs_handle *h)
@@ -942,6 +1025,22 @@ int bs_sync(bs_handle *h)
     return BS_OK;
 }
 
+}  // extern "C"
+
+namespace {
+// Drop a lens model and give its device memory back (the bytes leave the handle's account).
+void clear_lens(bs_handle *h, LensModel &m)
+{
+    cudaFree(m.d_xs);
+    cudaFree(m.d_ys);
+    cudaFree(m.d_map);
+    h->device_bytes -= m.bytes;
+    m = LensModel();
+}
+}  // namespace
+
+extern "C" {
+
 int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dist, int n_dist)
 {
     if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_set_undistort: NULL handle");
@@ -951,10 +1050,8 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     BS_CUDA(h, cudaSetDevice(h->device));
     if (h->lens.empty()) h->lens.resize(h->n_cams);
     LensModel &m = h->lens[cam];
-    cudaFree(m.d_xs);
-    cudaFree(m.d_ys);
-    cudaFree(m.d_map);
-    m = LensModel();
+    BS_CUDA(h, cudaStreamSynchronize(h->s_compute));     // frames in flight may still be reading the old tables
+    clear_lens(h, m);
     bool nonzero = false;
     for (int i = 0; i < n_dist; ++i) {
         m.k[i] = dist[i];
@@ -964,38 +1061,55 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     std::vector<double> xs, ys;
     if (build_lens_tables(h->sw[cam], h->sh[cam], K, m, xs, ys) != BS_OK)
         return fail(h, BS_ERR_UNSUPPORTED, "bs_set_undistort: camera matrix must be [[fx 0 cx] [0 fy cy] [0 0 1]]");
-    BS_CUDA(h, cudaMalloc(&m.d_xs, xs.size() * sizeof(double)));
-    BS_CUDA(h, cudaMalloc(&m.d_ys, ys.size() * sizeof(double)));
-    BS_CUDA(h, upload_now(h, m.d_xs, xs.data(), xs.size() * sizeof(double)));
-    BS_CUDA(h, upload_now(h, m.d_ys, ys.data(), ys.size() * sizeof(double)));
-    h->device_bytes += (xs.size() + ys.size()) * sizeof(double);
-    m.enabled = true;
-    if (h->flags & BS_FLAG_EXACT_ONLY) return BS_OK;     // one-shot handles (bs_undistort): one pass, no map
-    // The map depends on the calibration only: evaluate it once, resample every frame from it.
-    const size_t map_bytes = sizeof(uint32_t) * (size_t)h->sw[cam] * (size_t)h->sh[cam];
     int *d_overflow = nullptr, overflow = 0;
-    BS_CUDA(h, cudaMalloc(&m.d_map, map_bytes));
-    BS_CUDA(h, cudaMalloc(&d_overflow, sizeof(int)));
-    BS_CUDA(h, cudaMemsetAsync(d_overflow, 0, sizeof(int), h->s_compute));
-    if (h->remap_grid == 0) {
-        int per_sm = 0, sms = 0;
-        BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::undistort_remap_kernel, 256, 0));
-        BS_CUDA(h, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
-        h->remap_grid = std::max(1, per_sm * sms);
+    const size_t tab_bytes = (xs.size() + ys.size()) * sizeof(double);
+    const size_t map_bytes = sizeof(uint32_t) * (size_t)h->sw[cam] * (size_t)h->sh[cam];
+    const bool want_map = !(h->flags & BS_FLAG_EXACT_ONLY);      // one-shot handles (bs_undistort): one pass, no map
+    cudaError_t e = cudaMalloc(&m.d_xs, xs.size() * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&m.d_ys, ys.size() * sizeof(double));
+    if (e == cudaSuccess) e = upload_now(h, m.d_xs, xs.data(), xs.size() * sizeof(double));
+    if (e == cudaSuccess) e = upload_now(h, m.d_ys, ys.data(), ys.size() * sizeof(double));
+    if (e == cudaSuccess) {
+        m.bytes = tab_bytes;
+        h->device_bytes += tab_bytes;
     }
-    const bs::UndistortArgs U = lens_args(h, m, cam);
-    bs::undistort_map_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, h->s_compute>>>(U, m.d_map, d_overflow);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpyAsync(&overflow, d_overflow, sizeof(int), cudaMemcpyDeviceToHost, h->s_compute);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
-    cudaFree(d_overflow);
-    if (e != cudaSuccess || overflow) {                  // displacement beyond the packed range: keep the one-pass kernel
-        cudaFree(m.d_map);
-        m.d_map = nullptr;
-        if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "bs_set_undistort: map kernel: %s", cudaGetErrorString(e));
-    } else {
-        h->device_bytes += map_bytes;
+    // where this camera's undistorted frames go: the device-submit buffer now, the ring's slots if they exist
+    int rc = BS_OK;
+    if (e == cudaSuccess) rc = alloc_undist(h, h->d_undist, cam);
+    for (size_t k = 0; rc == BS_OK && e == cudaSuccess && k < h->ring.size(); ++k) rc = alloc_undist(h, h->ring[k].d_undist, cam);
+    if (e == cudaSuccess && rc == BS_OK && want_map) {
+        // The map depends on the calibration only: evaluate it once, resample every frame from it.
+        e = cudaMalloc(&m.d_map, map_bytes);
+        if (e == cudaSuccess) e = cudaMalloc(&d_overflow, sizeof(int));
+        if (e == cudaSuccess) e = cudaMemsetAsync(d_overflow, 0, sizeof(int), h->s_compute);
+        if (e == cudaSuccess && h->remap_grid == 0) {
+            int per_sm = 0, sms = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::undistort_remap_kernel, 256, 0);
+            if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+            h->remap_grid = std::max(1, per_sm * sms);
+        }
+        if (e == cudaSuccess) {
+            const bs::UndistortArgs U = lens_args(h, m, cam);
+            bs::undistort_map_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, h->s_compute>>>(U, m.d_map, d_overflow);
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(&overflow, d_overflow, sizeof(int), cudaMemcpyDeviceToHost, h->s_compute);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
+        cudaFree(d_overflow);
+        if (e == cudaSuccess && !overflow) {
+            m.bytes += map_bytes;
+            h->device_bytes += map_bytes;
+        } else {                                             // displacement beyond the packed range: keep the one-pass kernel
+            cudaFree(m.d_map);
+            m.d_map = nullptr;
+        }
     }
+    if (e != cudaSuccess || rc != BS_OK) {
+        clear_lens(h, m);                                    // never leave a half-built model behind
+        if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "bs_set_undistort: %s", cudaGetErrorString(e));
+        return rc;
+    }
+    m.enabled = true;
     return BS_OK;
 }
 
@@ -1028,7 +1142,7 @@ int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, 
             e = cudaMemcpy2D(dst, dpitch, out[0], out_pitch[0], (size_t)w * 3, h, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) rc = fail(nullptr, BS_ERR_CUDA, "bs_undistort: %s", cudaGetErrorString(e));
     } else {
-        g_last_error = hd->err;
+        memcpy(g_last_error, hd->err, kErrLen);
     }
     cudaFree(d_src);
     bs_destroy(hd);
@@ -1048,7 +1162,7 @@ int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8
     const uint8_t *frames[1] = {src};
     size_t pitches[1] = {spitch};
     rc = bs_stitch(h, frames, pitches, dst, dpitch);
-    if (rc != BS_OK) g_last_error = h->err;
+    if (rc != BS_OK) memcpy(g_last_error, h->err, kErrLen);
     bs_destroy(h);
     return rc;
 }
@@ -1108,7 +1222,7 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 // forbids cudaMalloc after start-up (cudaMalloc also synchronises the whole device, which a frame loop
 // cannot afford), or a process whose memory was handed to it by a host application.  bs_create and
 // bs_submit allocate (plan, rings, streams); this entry point does not call cudaMalloc, cudaFree,
-// cudaHostAlloc, or any host heap routine.
+// cudaHostAlloc, or any host heap routine (error texts go to fixed per-thread buffers).
 //
 // The staged kernel needs scratch memory: the block plan and the per-warp work split.  Here they live
 // in ONE file-scope device array of a fixed size.  Consequences a caller must know:
@@ -1198,6 +1312,9 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     }
     if (canvas_pitch < (size_t)canvas_w * 3)
         return fail(nullptr, BS_ERR_INVALID_ARG, "%s: canvas_pitch=%zu < %d*3", me, canvas_pitch, canvas_w);
+    if (flags & ~(BS_FLAG_LEGACY_BORDER | BS_FLAG_KEEP_CANVAS))
+        return fail(nullptr, BS_ERR_UNSUPPORTED, "%s: flags 0x%x: only BS_FLAG_LEGACY_BORDER and BS_FLAG_KEEP_CANVAS are accepted here",
+                    me, flags);
     const int blocks_x = (canvas_w + bs::kBlockW - 1) / bs::kBlockW, blocks_y = (canvas_h + bs::kBlockH - 1) / bs::kBlockH;
     const long long n_blocks_ll = (long long)blocks_x * blocks_y;
     if (n_blocks_ll > BS_STATIC_MAX_BLOCKS)
@@ -1244,7 +1361,7 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
 
     // ---- size one TMA box per camera, flatten to work items, split them over the grid's warps -------
     PlanLayout L;
-    layout_plan(g_static_recs, n_blocks, n_cams, g_static_items, &L);
+    layout_plan(g_static_recs, n_blocks, n_cams, g_static_items, &L, false);
     bool fast = L.n_fast > 0 && get_encoder() && cta_smem_bytes(L.stage_bytes, bs::kRecSlotsMax / 2) <= st->smem_optin &&
                 aligned16(d_canvas, canvas_pitch);
     for (int i = 0; fast && i < n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);

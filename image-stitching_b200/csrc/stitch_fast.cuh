@@ -36,6 +36,8 @@ struct FastArgs {
     int box_bytes[kMaxCamsPerLaunch];      // ... and total bytes (= what the mbarrier expects)
     int stage_bytes;                       // shared memory per stage (multiple of 128)
     int rec_slots;                         // record ring slots per warp: 16, or 8 when that lets one more CTA fit an SM
+    int wait_sources;                      // 1: the source frames may come from the kernel just before this one in the
+                                           // stream: order every source read behind it (griddepcontrol.wait first)
 };
 
 // First 4-byte element of the staged box for a bounding box whose first texel column is bx0.
@@ -509,13 +511,17 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
     uint4 rec = lds128(rec_addr(0));
     uint4 recn = cnt > 1 ? lds128(rec_addr(1)) : rec;
     LaneCoef lc = lane_coef(load_block_coef(rec_addr(0)), lane - kBlockW / 2);
+    bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
+    if (A.wait_sources) {             // only the plan (written long ago) has been read so far
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        prior_grid_done = true;
+    }
     if (lane == 0) issue_box(rec, 0u);
     __syncwarp();
 
     // lane constants of the output word merge (store_row_pixel): byte selector, and whether this lane owns a word
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
     const uint32_t storing = (uint32_t)((lane & 3) != 3);
-    bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
     bool wrote = false;               // some layer has written into the current block
     uint32_t stage = 0, dpar = 0;     // stage and data-barrier parity of the current item (kStages == 2)
     static_assert(kStages == 2, "the item pipeline below is written for two stages");

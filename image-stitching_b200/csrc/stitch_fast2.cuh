@@ -1,0 +1,453 @@
+// stitch_fast2.cuh -- the per-frame kernel for calibrations whose source boxes are compact
+// (a 32x16 canvas block reads at most 18 source rows of 128 bytes: every near-unit-scale video
+// panorama, BASELINE.json configs 2-5).  Same work split, same plan and the same arithmetic as
+// stitch_fast.cuh (which remains the kernel for large boxes); what differs is how a pixel gets its taps:
+//
+//   * after the TMA box of an item has landed, the warp rewrites it once from packed 3-byte texels
+//     into one aligned word per texel (B G R x): 3 LDS + 3 PRMT + 1 STS.128 per four texels;
+//   * a pixel then loads its four taps as four aligned words at immediate offsets from ONE address
+//     (no alignment shifts, no third word), pairs them with four PRMT and blends with six dp2a;
+//   * the x and y coordinate polynomials are evaluated together with the packed fp32 instructions
+//     of sm_100 (fma.rn.f32x2 / add.rn.f32x2): 3 instructions per pixel instead of 6;
+//   * two raw stages + one converted buffer: boxes of items n+1 and n+2 are in flight while item n
+//     is computed.
+// Replaces the camera loop body /root/reference/tools/stitch/main.cpp:145-152.
+#pragma once
+
+#include "stitch_fast.cuh"
+
+namespace bs {
+
+constexpr int kRawPitch = 128;                           // bytes per staged source row: TMA box of 32 four-byte elements
+constexpr int kRawRows = 18;                             // rows a box may have
+constexpr int kRawStage = kRawPitch * kRawRows;          // 2304
+constexpr int kConvGroups = 10;                          // groups of four texels converted per row
+constexpr int kConvTexels = 4 * kConvGroups;             // 40
+constexpr int kConvPitch = 4 * kConvTexels;              // 160 bytes
+constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
+constexpr int kRec2Slots = 16;
+constexpr int kWarp2Smem = 2 * kRawStage + kConvRegion + kWarpOutBytes + warp_ctl_bytes(kRec2Slots);
+static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
+
+#ifndef BS2_WARPS_PER_CTA
+#define BS2_WARPS_PER_CTA 8
+#endif
+#ifndef BS2_MIN_CTAS
+#define BS2_MIN_CTAS 2
+#endif
+constexpr int kWarps2 = BS2_WARPS_PER_CTA;
+constexpr int kFast2Threads = 32 * kWarps2;
+
+struct Fast2Args {
+    FrameArgs F;
+    CUtensorMap tmap[kMaxCamsPerLaunch];   // source frame of camera i as a [h][pitch/4] u32 tensor, box 32 x box_h[i]
+    const WorkItem *items;
+    const int *warp_start;
+    int box_bytes[kMaxCamsPerLaunch];      // 128 * box rows of camera i (what the mbarrier expects)
+    int wait_sources;                      // 1: the source frames may come from the kernel just before this one in
+                                           // the stream: order every source read behind it (griddepcontrol.wait first)
+};
+
+// ---- packed fp32 pairs (x in the low half, y in the high half) -------------------------------------
+__device__ __forceinline__ uint64_t pack2(float lo, float hi)
+{
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, int &lo, int &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c)
+{
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b)
+{
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+
+// lane_coef() of stitch_plan.cuh with x and y held as pairs.  Each half executes exactly the fma
+// sequence the plan kernel verified (fma.rn.f32x2 is two independent IEEE fma.rn.f32).
+struct LaneCoef2 {
+    uint64_t a0, a1, a2;   // s(v) = a0 + v (a1 + v a2), (x, y)
+    int bx, by;            // X = bits_x + bx + 32 nxv v
+    int nxv, nyv;
+};
+__device__ __forceinline__ LaneCoef2 lane_coef2(const BlockCoef &c, int u)
+{
+    const float uf = (float)u;
+    const uint64_t u2 = pack2(uf, uf);
+    LaneCoef2 l;
+    l.a0 = fma2(u2, fma2(u2, pack2(c.hxuu, c.hyuu), pack2(c.xu, c.yu)), pack2(c.fx, c.fy));
+    l.a1 = fma2(u2, pack2(c.xuv, c.yuv), pack2(c.xv, c.yv));
+    l.a2 = pack2(c.hxvv, c.hyvv);
+    l.bx = c.ix - kMagicBias + 32 * (int)c.nxu * u;
+    l.by = c.iy - kMagicBias + 32 * (int)c.nyu * u;
+    l.nxv = c.nxv;
+    l.nyv = c.nyv;
+    return l;
+}
+__device__ __forceinline__ void lane_coord_bits2(const LaneCoef2 &l, float vf, int &xbits, int &ybits)
+{
+    const uint64_t v2 = pack2(vf, vf);
+    const uint64_t s = fma2(v2, fma2(v2, l.a2, l.a1), l.a0);
+    unpack2(add2(s, pack2(12582912.0f, 12582912.0f)), xbits, ybits);
+}
+
+// ---- converted box: one word per texel ---------------------------------------------------------
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+// `src`: this lane's first raw word (row lane/10 of the stage, texel group lane%10), `dst`: its first
+// converted word.  Six steps of three rows; lanes 30 and 31 have nothing to do.
+__device__ __forceinline__ void convert_box(uint32_t src, uint32_t dst, int lane)
+{
+    if (lane < 30) {
+#pragma unroll
+        for (int it = 0; it < kRawRows / 3; ++it) {
+            const uint32_t s = src + (uint32_t)(it * 3 * kRawPitch);
+            const uint32_t w0 = lds32(s), w1 = lds32(s + 4), w2 = lds32(s + 8);   // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+            sts128(dst + (uint32_t)(it * 3 * kConvPitch), w0, __byte_perm(w0, w1, 0x6543), __byte_perm(w1, w2, 0x5432), w2 >> 8);
+        }
+    }
+}
+
+struct Taps2 {
+    uint32_t t00, t01, t10, t11;   // texels (sx, sy), (sx+1, sy), (sx, sy+1), (sx+1, sy+1) as B G R x
+    uint2 wt;
+};
+__device__ __forceinline__ Taps2 fetch_taps2(uint32_t o, uint2 wt)
+{
+    Taps2 t;
+    t.t00 = lds32(o);
+    t.t01 = lds32(o + 4);
+    t.t10 = lds32(o + kConvPitch);
+    t.t11 = lds32(o + kConvPitch + 4);
+    t.wt = wt;
+    return t;
+}
+// Same blend as blend_taps(): bit-identical to (sum w*S + 2^14) >> 15 per channel.
+__device__ __forceinline__ uint32_t blend_taps2(const Taps2 &t)
+{
+    const uint32_t p0 = __byte_perm(t.t00, t.t01, 0x5140), q0 = __byte_perm(t.t00, t.t01, 0x6262);   // [B00 B01 G00 G01], [R00 R01 ..]
+    const uint32_t p1 = __byte_perm(t.t10, t.t11, 0x5140), q1 = __byte_perm(t.t10, t.t11, 0x6262);
+    const uint32_t vb = __dp2a_lo(t.wt.y, p1, __dp2a_lo(t.wt.x, p0, 32768u));
+    const uint32_t vg = __dp2a_hi(t.wt.y, p1, __dp2a_hi(t.wt.x, p0, 32768u));
+    const uint32_t vr = __dp2a_lo(t.wt.y, q1, __dp2a_lo(t.wt.x, q0, 32768u));
+    const uint32_t bg = __byte_perm(vb, vg, 0x3362);
+    return __byte_perm(bg, vr, 0x7610);
+}
+__device__ __forceinline__ uint32_t sample_conv(uint32_t o, uint2 wt) { return blend_taps2(fetch_taps2(o, wt)); }
+
+__device__ __forceinline__ void store_px_bytes(uint32_t p8, uint32_t px)
+{
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8), "r"(px) : "memory");
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 1), "r"(px >> 8) : "memory");
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(p8 + 2), "r"(px >> 16) : "memory");
+}
+
+// Address of a pixel's first tap in the converted buffer: `base` + whole texels of (xbits, ybits).
+// Written so that each coordinate costs a mask and one multiply-add / shift-add.
+__device__ __forceinline__ uint32_t tap_addr(uint32_t base, int xbits, int ybits)
+{
+    const uint32_t ym = (uint32_t)ybits & ~31u, xm = (uint32_t)xbits & ~31u;
+    return base + ym * (uint32_t)(kConvPitch / 32) + (xm >> 3);
+}
+
+// Hot path: the layer covers every pixel of the block with interior samples and the plan verified the
+// cheap coordinates for the whole block.  `run0` = converted-buffer address of this lane's texel base
+// for row v = -kRun/2 (whole-texel parts only), `vstep` = whole texels per canvas row as a byte offset.
+// kDirect: every row goes straight to the canvas, `gp` = address of this lane's word of the block's
+// first row; otherwise rows are collected in the warp's output block in shared memory.
+template <bool kDirect>
+__device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, int vstep, uint32_t out_blk, int lane,
+                                          uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing)
+{
+    auto fetch = [&](int k) {
+        int xbits, ybits;
+        lane_coord_bits2(lc, (float)(k - kRun / 2), xbits, ybits);
+        return fetch_taps2(tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits),
+                           tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+    };
+    Taps2 cur = fetch(0);
+#pragma unroll
+    for (int k = 0; k < kRun; ++k) {
+        Taps2 nxt = cur;
+        if (k + 1 < kRun) nxt = fetch(k + 1);
+        const uint32_t px = blend_taps2(cur);
+        if (kDirect) {
+            // this lane's word of the row, then on to the next row: the canvas does not straddle a 4 GB
+            // boundary (the host checks), so only the low half of the address advances, in place
+            const uint32_t nb = __shfl_down_sync(0xffffffffu, px, 1);
+            const uint32_t word = __byte_perm(px, nb, sel);
+            asm volatile(
+                "{\n"
+                ".reg .pred p;\n"
+                ".reg .b32 lo, hi;\n"
+                "setp.ne.u32 p, %2, 0;\n"
+                "@p st.global.u32 [%0], %1;\n"
+                "mov.b64 {lo, hi}, %0;\n"
+                "add.u32 lo, lo, %3;\n"
+                "mov.b64 %0, {lo, hi};\n"
+                "}"
+                : "+l"(gp)
+                : "r"(word), "r"(storing), "r"(cpitch)
+                : "memory");
+        } else {
+            store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
+        }
+        cur = nxt;
+    }
+}
+
+// Partially covered layer whose cheap coordinates hold everywhere: coverage test and byte stores per pixel.
+__device__ __noinline__ void run_masked2(const LaneCoef2 &lc, uint32_t run0, int vstep, uint32_t out_blk, int lane, int src_w,
+                                         int src_h, bool col_in_canvas, int rows_in_canvas, bool first_layer)
+{
+    const uint32_t safe = out_blk - 2 * kConvPitch;     // inside the converted buffer: valid for every tap offset
+    auto fetch = [&](int k, bool &in) {
+        const int v = k - kRun / 2;
+        int xbits, ybits;
+        lane_coord_bits2(lc, (float)v, xbits, ybits);
+        const int sx = (xbits + lc.bx + 32 * lc.nxv * v) >> kFracBits, sy = (ybits + lc.by + 32 * lc.nyv * v) >> kFracBits;
+        in = col_in_canvas && k < rows_in_canvas && (uint32_t)sx < (uint32_t)(src_w - 1) && (uint32_t)sy < (uint32_t)(src_h - 1);
+        const uint32_t o = tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits);
+        return fetch_taps2(in ? o : safe, tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+    };
+    bool in_cur, in_nxt = false;
+    Taps2 cur = fetch(0, in_cur);
+#pragma unroll 4
+    for (int k = 0; k < kRun; ++k) {
+        Taps2 nxt = cur;
+        if (k + 1 < kRun) nxt = fetch(k + 1, in_nxt);
+        uint32_t px = blend_taps2(cur);
+        if (in_cur || first_layer) {
+            if (!in_cur) px = 0;
+            store_px_bytes(out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane, px);
+        }
+        cur = nxt;
+        in_cur = in_nxt;
+    }
+}
+
+// General path: partially covered layers with flagged 32x4 groups (those use the exact fp64 coordinates).
+// `conv_origin` = address texel (0, 0) of the camera would have in the converted buffer.
+__device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam, const LaneCoef2 &lc, uint32_t conv_origin,
+                                          uint32_t out_blk, uint32_t group_mask, bool first_layer, int x, int y0, int lane)
+{
+    const int xb = (x / F.block_w) * F.block_w;
+    const uint32_t safe = out_blk - 2 * kConvPitch;
+#pragma unroll 1
+    for (int k = 0; k < kRun; ++k) {
+        int X, Y;
+        if ((group_mask >> (k >> 2)) & 1) {     // warp-uniform
+            coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
+        } else {
+            const int v = k - kRun / 2;
+            int xbits, ybits;
+            lane_coord_bits2(lc, (float)v, xbits, ybits);
+            X = xbits + lc.bx + 32 * lc.nxv * v;
+            Y = ybits + lc.by + 32 * lc.nyv * v;
+        }
+        const int sx = X >> kFracBits, sy = Y >> kFracBits;
+        const bool in = (x < F.W) && (y0 + k < F.H) && sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1;
+        const uint32_t o = in ? conv_origin + (uint32_t)(sy * kConvPitch + sx * 4) : safe;
+        uint32_t px = sample_conv(o, tap_weights((uint32_t)X & 31u, (uint32_t)Y & 31u));
+        if (in || first_layer) {
+            if (!in) px = 0;
+            store_px_bytes(out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane, px);
+        }
+    }
+}
+
+// Fully covered layer with flagged groups: redo the flagged rows of the output block with exact coordinates.
+__device__ __noinline__ void patch_exact2(const FrameArgs &F, const CamDev &cam, uint32_t conv_origin, uint32_t out_blk,
+                                          uint32_t group_mask, int x, int y0, int lane)
+{
+    const int xb = (x / F.block_w) * F.block_w;
+#pragma unroll 1
+    for (int k = 0; k < kRun; ++k) {
+        if (!((group_mask >> (k >> 2)) & 1)) continue;     // warp-uniform
+        int X, Y;
+        coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
+        const uint32_t o = conv_origin + (uint32_t)((Y >> kFracBits) * kConvPitch + (X >> kFracBits) * 4);
+        const uint32_t px = sample_conv(o, tap_weights((uint32_t)X & 31u, (uint32_t)Y & 31u));
+        store_px_bytes(out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane, px);
+    }
+}
+
+__global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kernel(const __grid_constant__ Fast2Args A)
+{
+    extern __shared__ __align__(128) uint8_t smem_raw[];
+    // layout: [pad to a 128-byte boundary][per warp: raw stage 0 | raw stage 1 | converted box | output block | records | mbarriers]
+    const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const uint32_t raw0 = raw_base + (uint32_t)(warp * kWarp2Smem);           // 128-byte aligned
+    const uint32_t conv = raw0 + 2 * kRawStage;
+    const uint32_t out_blk = conv + kConvRegion;
+    const uint32_t rec0 = out_blk + kWarpOutBytes;
+    constexpr uint32_t rec_slots = kRec2Slots, rec_half = kRec2Slots / 2;
+    const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per raw stage
+    const uint32_t rbar0 = dbar0 + 16;                                         // record barriers, one per half of the ring
+
+    // Programmatic dependent launch, as in stitch_fast_kernel: the next frame's kernel may start at once;
+    // it touches the canvas only after griddepcontrol.wait.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (lane == 0) {
+        for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dbar0 + 8 * s), "r"(1));
+        for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    const int gw = (int)blockIdx.x * kWarps2 + warp;
+    const int i0 = A.warp_start[gw];
+    const int cnt = A.warp_start[gw + 1] - i0;
+    if (cnt <= 0) return;
+
+    // lane 0 is this warp's producer ------------------------------------------------------------------
+    auto request_records = [&](int first) {
+        const uint32_t bytes = (uint32_t)(min((int)rec_half, cnt - first) * kRecBytes);
+        const uint32_t half = ((uint32_t)first / rec_half) & 1u;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * half), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         rec0 + kRecBytes * rec_half * half),
+                     "l"(A.items + i0 + first), "r"(bytes), "r"(rbar0 + 8 * half)
+                     : "memory");
+    };
+    auto issue_box = [&](const uint4 &r, uint32_t stage) {
+        if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
+            const uint32_t cam = (r.y >> 16) & 0xFFu;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
+                         "r"((uint32_t)A.box_bytes[cam])
+                         : "memory");
+            asm volatile(
+                "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                    raw0 + stage * (uint32_t)kRawStage),
+                "l"(&A.tmap[cam]), "r"((int)(int16_t)(r.z & 0xFFFFu)), "r"((int)(int16_t)(r.z >> 16)), "r"(dbar0 + 8 * stage)
+                : "memory");
+        } else {
+            mbar_arrive_addr(dbar0 + 8 * stage);
+        }
+    };
+    auto rec_addr = [&](int m) { return rec0 + kRecBytes * ((uint32_t)m & (rec_slots - 1)); };
+    auto wait_half_of = [&](int m) {      // first item of a half: every lane observes the copy's completion itself
+        if (((uint32_t)m & (rec_half - 1)) == 0) mbar_wait_addr(rbar0 + 8 * (((uint32_t)m / rec_half) & 1u), ((uint32_t)m / rec_slots) & 1u);
+    };
+
+    if (lane == 0) {
+        request_records(0);
+        if (cnt > (int)rec_half) request_records((int)rec_half);
+    }
+    __syncwarp();
+    wait_half_of(0);
+    bool prior_grid_done = false;     // griddepcontrol.wait executed (needed before any canvas access)
+    if (A.wait_sources) {             // only the plan (written long ago) has been read so far
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        prior_grid_done = true;
+    }
+    if (lane == 0) {
+        issue_box(lds128(rec_addr(0)), 0u);
+        if (cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
+    }
+    __syncwarp();
+
+    // lane constants: output word merge (store_row_pixel), conversion slot, column offset
+    const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
+    const uint32_t storing = (uint32_t)((lane & 3) != 3);
+    const uint32_t cv_src = (uint32_t)((lane / kConvGroups) * kRawPitch + 12 * (lane % kConvGroups));
+    const uint32_t cv_dst = conv + (uint32_t)((lane / kConvGroups) * kConvPitch + 16 * (lane % kConvGroups));
+    const int u = lane - kBlockW / 2;
+    const uint32_t lane_goff = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
+    bool wrote = false;               // some layer has written into the current block
+    for (int n = 0; n < cnt; ++n) {
+        const uint32_t stage = (uint32_t)n & 1u, dpar = ((uint32_t)n >> 1) & 1u;
+        if (lane == 0 && ((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt)
+            request_records(n + (int)rec_half);      // the half items n-8 .. n-1 used is free: refill it with n+8 .. n+15
+        const uint32_t ra = rec_addr(n);
+        const uint4 r = lds128(ra);
+        bool direct = false;
+        const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
+        const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
+        const bool fast = type == (uint32_t)kBlockFast;
+        BlockCoef bc;
+        if (fast) {
+            bc = load_block_coef(ra);
+            mbar_wait_addr(dbar0 + 8 * stage, dpar);                       // the box has landed
+            convert_box(raw0 + stage * (uint32_t)kRawStage + cv_src + (bc.aux >> 16), cv_dst, lane);
+        }
+        __syncwarp();                 // converted box complete; the raw stage is free
+        if (n + 2 < cnt) {
+            wait_half_of(n + 2);
+            if (lane == 0) issue_box(lds128(rec_addr(n + 2)), stage);
+        }
+        if (fast) {
+            const uint32_t c = (r.y >> 16) & 0xFFu;
+            const CamDev &cam = A.F.cam[c];
+            const LaneCoef2 lc = lane_coef2(bc, u);
+            // address texel (0, 0) of this camera would have in the converted buffer
+            const int y0 = (int)(int16_t)(r.z >> 16), t0 = (int)(bc.aux & 0xFFFFu);
+            const uint32_t conv_origin = conv - (uint32_t)(y0 * kConvPitch + t0 * 4);
+            const int vstep = lc.nyv * kConvPitch + lc.nxv * 4;
+            const uint32_t run0 = conv_origin + (uint32_t)((lc.by >> kFracBits) * kConvPitch + (lc.bx >> kFracBits) * 4) -
+                                  (uint32_t)((kRun / 2) * vstep);
+            const uint32_t groups = (r.y >> 24) & 0xFFu;
+            if (flags & kItemFull) {
+                direct = groups == 0u && prior_grid_done && A.F.canvas_in_4g &&
+                         (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
+                const uint64_t grow = reinterpret_cast<uint64_t>(A.F.canvas + (long long)ty0 * A.F.cpitch + (long long)tx0 * 3 + lane_goff);
+                if (direct)
+                    run_full2<true>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing);
+                else
+                    run_full2<false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing);
+                if (groups != 0u) {
+                    __syncwarp();
+                    patch_exact2(A.F, cam, conv_origin, out_blk, groups, tx0 + lane, ty0, lane);
+                }
+            } else if (groups == 0u) {
+                run_masked2(lc, run0, vstep, out_blk, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
+            } else {
+                run_general2(A.F, cam, lc, conv_origin, out_blk, groups, !wrote, tx0 + lane, ty0, lane);
+            }
+            wrote = !direct;
+        }
+        __syncwarp();                 // every lane is done with the converted box
+        if ((flags & kItemLast) && !direct) {
+            if (!prior_grid_done) {
+                asm volatile("griddepcontrol.wait;" ::: "memory");
+                prior_grid_done = true;
+            }
+            if (type == (uint32_t)kBlockExact) {
+                // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j; the item names its row groups j
+                const uint32_t rows = (r.y >> 24) & 0xFFu;
+                for (int j = 0; j < kRun / 4; ++j)
+                    if ((rows >> j) & 1u) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+            } else if (!wrote && A.F.keep_canvas) {
+                // nobody writes here and the canvas keeps its contents
+            } else if (tx0 + kBlockW <= A.F.W && ty0 + kRun <= A.F.H) {
+                // flush (or zero fill of an empty block): lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
+                const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
+                uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch + (long long)tx0 * 3 + (lane & 1) * 16;
+#pragma unroll
+                for (int j = 0; j < 3; ++j)
+                    *reinterpret_cast<uint4 *>(gp + 32 * j) = wrote ? lds128(so + 32u * j) : make_uint4(0u, 0u, 0u, 0u);
+            } else if (!wrote) {
+                store_block_checked(A.F, 0u, tx0, ty0, lane);
+            } else {
+                store_block_checked(A.F, out_blk, tx0, ty0, lane);
+            }
+            wrote = false;
+            __syncwarp();             // the output block is free again
+        }
+    }
+}
+
+}  // namespace bs

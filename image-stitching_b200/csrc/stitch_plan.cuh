@@ -27,14 +27,16 @@ enum BlockType : uint8_t { kBlockEmpty = 0, kBlockFast = 1, kBlockExact = 2 };
 
 // Second-order expansion of one camera's source coordinate field around a block's centre, in the
 // form the frame kernel evaluates it (see block_coef / lane_coef / lane_coord_bits below).
-struct BlockCoef {                 // 64 bytes
+struct BlockCoef {                 // 64 bytes; x and y members adjacent, so a kernel can hold them as packed pairs
     int ix, iy;                    // integer bases of the centre coordinate (multiples of 32)
     int8_t nxu, nxv, nyu, nyv;     // whole source texels advanced per canvas column (u) and row (v)
-    uint32_t pad;
+    uint32_t aux;                  // set by the host: first converted texel column | (its byte offset in the staged box) << 16
     float fx, fy;                  // centre coordinate minus its base, in [-0.5, 32.5)
-    float xu, xv, yu, yv;          // first derivatives minus their whole-texel parts (1/32 px per pixel)
-    float hxuu, xuv, hxvv;         // second derivatives (the pure ones halved)
-    float hyuu, yuv, hyvv;
+    float xu, yu;                  // first derivatives minus their whole-texel parts (1/32 px per pixel)
+    float xv, yv;
+    float hxuu, hyuu;              // second derivatives (the pure ones halved)
+    float xuv, yuv;
+    float hxvv, hyvv;
 };
 static_assert(sizeof(BlockCoef) == 64, "BlockCoef layout");
 
@@ -106,7 +108,7 @@ __device__ __forceinline__ BlockCoef block_coef(const double *__restrict__ M, in
     c.nxv = (int8_t)whole(gxv);
     c.nyu = (int8_t)whole(gyu);
     c.nyv = (int8_t)whole(gyv);
-    c.pad = 0;
+    c.aux = 0;
     c.xu = (float)(gxu - 32.0 * c.nxu);
     c.xv = (float)(gxv - 32.0 * c.nxv);
     c.yu = (float)(gyu - 32.0 * c.nyu);

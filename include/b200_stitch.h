@@ -118,16 +118,25 @@ int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
  * multiples of 16, otherwise the exact path is used for the whole frame.
  * Replaces tools/stitch/main.cpp:145-152 for callers that decode straight into GPU memory.
  *
- * Ordering: the frame kernel is launched with programmatic stream serialisation, so that back-to-back
- * frames overlap; it reads the source frames as soon as it starts and writes the canvas only after
- * the preceding kernel in the stream has completed.  Source frames must therefore be complete before
- * the preceding kernel in `stream` triggers its dependents -- always the case for copies, for ordinary
- * kernels and for this library's own kernels; a producer kernel that itself calls
- * cudaTriggerProgrammaticLaunchCompletion() early must be separated from this call by an event or a
- * different stream.
+ * Ordering: bs_submit_device is an ordinary stream-ordered call -- whatever precedes it in `stream`
+ * (copies, the caller's decode kernels, this library's own kernels) has completed, and is visible,
+ * before the first source texel is read.
+ *
+ * bs_submit_device_ex adds submit flags.  BS_SUBMIT_SOURCES_SETTLED: the caller states that no
+ * kernel directly before this call in `stream` writes the source frames (they were produced earlier,
+ * on another stream ordered by an event, or by copies).  The frame kernel is launched with programmatic
+ * stream serialisation in both forms; with this flag it may also prefetch and blend its first blocks while
+ * the previous kernel in the stream drains, so back-to-back frames overlap; it still touches the canvas
+ * only after that kernel has completed.  Without the flag every source read waits for the previous
+ * kernel (griddepcontrol.wait).  A handle with lens models undistorts with kernels of its own in
+ * `stream` first and ignores the flag; its intermediate frames are one set per handle, so keep such a
+ * handle's device submits on ONE stream.  The caller's current device is not changed.
  */
+#define BS_SUBMIT_SOURCES_SETTLED 0x1u
 int bs_submit_device(bs_handle *h, const void *const *d_frames, const size_t *pitch,
                      void *d_canvas, size_t canvas_pitch, void *stream);
+int bs_submit_device_ex(bs_handle *h, const void *const *d_frames, const size_t *pitch,
+                        void *d_canvas, size_t canvas_pitch, void *stream, unsigned submit_flags);
 
 /* Block until everything submitted through the handle has finished. */
 int bs_sync(bs_handle *h);

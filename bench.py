@@ -12,8 +12,12 @@ Printed JSON (one line, rank 0):
   value      frames/sec, whole job (all ranks), inputs and canvases resident in HBM;
   e2e        the same metric through bs_submit/bs_wait with pinned HOST buffers, H2D and D2H copies
              inside the timed region;
-  roofline   algorithmic bytes per frame / average kernel-launch duration (CUDA events on the
-             launching stream) against the measured HBM peak of MEASURED_PEAKS.json;
+  roofline   algorithmic bytes per frame / kernel time against the measured HBM peak of
+             MEASURED_PEAKS.json.  Two kernel times are printed: `kernel_us_pipelined` = timed region /
+             frames with the launches back to back (programmatic dependent launch lets the head of frame
+             n+1 overlap the tail of frame n; this is the rate a video stream sees, and what `frac` and
+             `achieved` use), and `kernel_us_isolated` = one launch between two events after a device
+             synchronise (best and median of 10);
   cpu_baseline  the reference's OpenCV path (cv2.warpPerspective, same call as
              /root/reference/tools/stitch/main.cpp:150-151) on this box's host cores;
   clocks     SM clock and throttle reasons sampled during the timed regions.
@@ -56,7 +60,16 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--flags", type=int, default=0, help="BS_FLAG_* for the handle (debug)")
+    ap.add_argument("--lens", action="store_true",
+                    help="every camera gets a lens model (cv::undistort before the warp, the video-mode loop "
+                         "of tools/stitch/main.cpp:148-151); adds the `undistort` record")
+    ap.add_argument("--no-host-ceiling", action="store_true")
     return ap.parse_args()
+
+
+def common_config(w, content, lens=False):
+    """`config` is the same dict in both arms (the driver compares them); arm-specific facts go under `run`."""
+    return {"workload": workload_text(w), "content": content, "lens_models": bool(lens)}
 
 
 def workload_text(w):
@@ -68,12 +81,21 @@ def workload_text(w):
 # CPU reference: the OpenCV call the reference makes, through cv2; the C port only if cv2 is
 # not importable on this box.
 # ------------------------------------------------------------------------------------------
+def lens_model(w):
+    """The lens model of tests/test_gpu_undistort.py (8 coefficients, as calibrate writes them)."""
+    import numpy as np
+    sw, sh = w.src_wh
+    K = np.array([[0.9 * sw, 0, sw / 2 + 3.3], [0, 0.92 * sw, sh / 2 - 1.7], [0, 0, 1]])
+    return K, np.array([-0.2, 0.05, 0.001, -0.002, 0.01, 0.0, 0.0, 0.0])
+
+
 class CpuReference:
-    def __init__(self, w, content):
+    def __init__(self, w, content, lens=False):
         wl = importlib.import_module("image-stitching_b200.workloads")
         import numpy as np
         self.np = np
         self.w = w
+        self.lens = lens_model(w) if lens else None
         self.frames = [[wl.gen_frame_numpy(w.src_wh[0], w.src_wh[1], i, f, content)
                         for i in range(w.n_cams)] for f in range(2)]
         self.canvas = np.zeros((w.canvas_wh[1], w.canvas_wh[0], 3), np.uint8)
@@ -98,10 +120,14 @@ class CpuReference:
         srcs = self.frames[f % len(self.frames)]
         if self.cv2 is not None:
             for s, H in zip(srcs, w.H):
+                if self.lens is not None:      # tools/stitch/main.cpp:148-149
+                    s = self.cv2.undistort(s, self.lens[0], self.lens[1])
                 self.cv2.warpPerspective(s, H, w.canvas_wh, dst=self.canvas, flags=self.cv2.INTER_LINEAR,
                                          borderMode=self.cv2.BORDER_TRANSPARENT)
         else:
             for s, H in zip(srcs, w.H):
+                if self.lens is not None:
+                    s = self.oracle.undistort(s, self.lens[0], self.lens[1])
                 self.oracle.warp_perspective(s, H, self.canvas, nthreads=self.cores)
         return self.canvas
 
@@ -139,15 +165,15 @@ def run_reference(args, rank):
         return
     wl = importlib.import_module("image-stitching_b200.workloads")
     w = wl.get(args.workload)
-    ref = CpuReference(w, args.content)
+    ref = CpuReference(w, args.content, args.lens)
     done, dt = ref.time_frames(args.warmup, args.steps)
     fps = done / dt
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
         "steps": done, "warmup": args.warmup, "ms_per_step": 1e3 * dt / done, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_text(w), "content": args.content,
-                   "step": "one panorama frame on the host cores (bounded sample of the workload)"},
+        "config": common_config(w, args.content, args.lens),
+        "run": {"step": "one panorama frame on the host cores (bounded sample of the workload)"},
         "cpu_baseline": {"value": fps, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
                          "sample": f"{done} frames of {w.name}, {ref.what}"},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -297,6 +323,10 @@ def run_b200(args, rank, local_rank, world):
         d_frames.append(fs)
     d_canvas = [padded(H, W) for _ in range(RING)]
     st = pkg.Stitcher([w.src_wh] * n, w.canvas_wh, w.H, flags=args.flags, device=local_rank)
+    if args.lens:
+        K, dist = lens_model(w)
+        for i in range(n):
+            st.set_undistort(i, K, dist)
     stream = torch.cuda.Stream(device=dev)       # the kernels and the timing events share this stream
     torch.cuda.set_stream(stream)
     sp = stream.cuda_stream
@@ -305,10 +335,13 @@ def run_b200(args, rank, local_rank, world):
     c_ptrs = [t.data_ptr() for t in d_canvas]
     c_pitch = d_canvas[0].stride(0)
 
+    # the ring's frames were written long before the timed region: no kernel in the stream produces them
+    settled = pkg.SUBMIT_SOURCES_SETTLED
+
     def device_step():
         for j in range(B):
             k = j % RING
-            st.submit_device(f_ptrs[k], f_pitch, c_ptrs[k], c_pitch, sp)
+            st.submit_device(f_ptrs[k], f_pitch, c_ptrs[k], c_pitch, sp, settled)
 
     # ---- parity spot check (untimed): frame 0 of rank 0 against the recorded OpenCV hash --------
     parity = None
@@ -316,7 +349,7 @@ def run_b200(args, rank, local_rank, world):
         try:
             ka = json.load(open(os.path.join(ROOT, "tests", "golden", "known_answers.json")))
             want = [c for c in ka["cases"] if (c["config"], c["content"], c["frame"]) == (w.name, "noise", 0)]
-            st.submit_device(f_ptrs[0], f_pitch, c_ptrs[0], c_pitch, sp)
+            st.submit_device(f_ptrs[0], f_pitch, c_ptrs[0], c_pitch, sp, settled)
             stream.synchronize()
             got = hashlib.sha256(d_canvas[0].cpu().numpy().tobytes()).hexdigest()
             if want:
@@ -343,6 +376,63 @@ def run_b200(args, rank, local_rank, world):
     frames_dev = args.steps * B
     value = world * frames_dev / (dev_ms * 1e-3)
     kernel_us = 1e3 * dev_ms / frames_dev          # one frame = the launches of one submit
+
+    # one frame alone: device idle before, two events around the launch(es) of a single submit
+    iso = []
+    for j in range(10):
+        torch.cuda.synchronize()
+        ev0.record(stream)
+        st.submit_device(f_ptrs[j % RING], f_pitch, c_ptrs[j % RING], c_pitch, sp, settled)
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        iso.append(1e3 * ev0.elapsed_time(ev1))
+    iso.sort()
+    launches_per_frame = launches / frames_dev
+
+    # row f1 alone: cv::undistort of one camera frame on device buffers (bs_undistort_device)
+    undist = None
+    if args.lens:
+        d_tmp = padded(sh, sw)
+        for _ in range(3):
+            st.undistort_device(0, f_ptrs[0][0], f_pitch[0], d_tmp.data_ptr(), d_tmp.stride(0), sp)
+        torch.cuda.synchronize()
+        reps = 8 * RING
+        ev0.record(stream)
+        for j in range(reps):
+            st.undistort_device(j % n, f_ptrs[j % RING][j % n], f_pitch[j % n], d_tmp.data_ptr(), d_tmp.stride(0), sp)
+        ev1.record(stream)
+        torch.cuda.synchronize()
+        und_us = 1e3 * ev0.elapsed_time(ev1) / reps
+        und_bytes = 2 * sw * sh * 3            # every output pixel written once, every source texel read about once
+        undist = {"us_per_camera_frame": und_us, "algorithmic_bytes": und_bytes,
+                  "achieved_gbs": und_bytes / (und_us * 1e-6) / 1e9, "cameras_per_panorama": n,
+                  "what": "cv::undistort of one 8UC3 frame on device buffers, back to back over the frame ring"}
+
+    # ---- what the host side can carry: the e2e copies alone, all ranks at once ----------------------
+    def host_ceiling(h2d_bytes, d2h_bytes, reps=12):
+        """Frames/s if a frame cost nothing but its copies: the same byte counts as one e2e frame, H2D and
+        D2H concurrently on two side streams from/to pinned memory, every rank at the same time."""
+        up_h = torch.empty(h2d_bytes, dtype=torch.uint8).pin_memory()
+        up_d = torch.empty(h2d_bytes, dtype=torch.uint8, device=dev)
+        dn_h = torch.empty(d2h_bytes, dtype=torch.uint8).pin_memory()
+        dn_d = torch.empty(d2h_bytes, dtype=torch.uint8, device=dev)
+        s_up, s_dn = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+
+        def go(k):
+            for _ in range(k):
+                with torch.cuda.stream(s_up):
+                    up_d.copy_(up_h, non_blocking=True)
+                with torch.cuda.stream(s_dn):
+                    dn_h.copy_(dn_d, non_blocking=True)
+            s_up.synchronize()
+            s_dn.synchronize()
+        go(2)
+        barrier()
+        t0 = time.perf_counter()
+        go(reps)
+        t1 = time.perf_counter()
+        barrier()
+        return world * reps / max_over_ranks(t1 - t0)
 
     # ---- end to end: pinned host buffers, copies inside the timed region ------------------------
     e2e = None
@@ -389,18 +479,22 @@ def run_b200(args, rank, local_rank, world):
                "h2d_bytes_per_step_full_frames": Be * w.src_bytes,
                "frames_per_step": Be, "pipeline_depth": depth, "ms_per_frame": 1e3 * e2e_s / (args.steps * Be),
                "host_buffers": "pinned (bs_host_alloc)"}
+        if not args.no_host_ceiling:
+            e2e["host_ceiling_fps"] = host_ceiling(h2d_per_frame, w.canvas_bytes)
+            e2e["of_host_ceiling"] = e2e["value"] / e2e["host_ceiling_fps"]
         if rank == 0:   # the last panorama read back must equal the device-resident result
             j = last["j"]
             e2e["matches_device_path"] = bool(np.array_equal(h_out[j % len(h_out)],
                                                              d_canvas[j % RING].cpu().numpy()))
 
     stats = st.stats()
+    stats_kernel = ["stitch_exact_kernel", "stitch_fast_kernel (general staged)", "stitch_fast2_kernel (compact boxes)"][stats["frame_kernel"]]
     st.close()
 
     # ---- CPU baseline: rank 0, N = 1 only ------------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        ref = CpuReference(w, args.content)
+        ref = CpuReference(w, args.content, args.lens)
         done, dt = ref.time_frames(2, 10 ** 6, budget_s=args.cpu_seconds)
         cpu = {"value": done / dt, "unit": UNIT, "cores": ref.cores, "kind": ref.kind,
                "sample": f"{done} frames of {w.name} in {dt:.1f} s, {ref.what}, all host threads"}
@@ -425,11 +519,21 @@ def run_b200(args, rank, local_rank, world):
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": alg, "kernel_us": kernel_us,
+                    "kernel_us_pipelined": kernel_us, "kernel_us_isolated": iso[0],
+                    "kernel_us_isolated_median": iso[len(iso) // 2],
+                    "frac_uses": "kernel_us_pipelined (back-to-back launches, the rate a video stream sees)",
+                    "frac_isolated": alg / (iso[0] * 1e-6) / 1e9 / peak,
+                    "launches_per_frame": launches_per_frame,
                     "frac_of_nominal_8TBs": achieved / 8000.0}
+        if args.lens:
+            roofline["note"] = ("lens models on: a frame is n_cams undistort launches + the frame kernel; "
+                                "algorithmic bytes are the frame kernel's only")
         tpath = os.path.join(ROOT, "profiles", "dram_traffic.json")
         if os.path.exists(tpath):
             try:
-                roofline["traffic"] = json.load(open(tpath)).get(w.name)
+                tj = json.load(open(tpath))
+                roofline["traffic"] = tj.get(w.name)
+                roofline["traffic_how"] = tj.get("how")
             except Exception:
                 pass
 
@@ -437,13 +541,15 @@ def run_b200(args, rank, local_rank, world):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_text(w), "content": args.content, "frames_per_step": B,
-                   "ring_frames": RING,
-                   "l2": f"inputs larger than L2: ring of {RING} frame sets + canvases = "
-                         f"{RING * (w.src_bytes + w.canvas_bytes) / 1e9:.2f} GB cycled per GPU",
-                   "parallelism": f"frame-parallel x{world}, no collective",
-                   "host_cpus_per_rank": (len(numa) if numa else None),
-                   "tiles_fast_exact_empty": [stats["n_tiles_fast"], stats["n_tiles_exact"], stats["n_tiles_empty"]]},
+        "config": common_config(w, args.content, args.lens),
+        "run": {"frames_per_step": B, "ring_frames": RING,
+                "l2": f"inputs larger than L2: ring of {RING} frame sets + canvases = "
+                      f"{RING * (w.src_bytes + w.canvas_bytes) / 1e9:.2f} GB cycled per GPU",
+                "parallelism": f"frame-parallel x{world}, no collective",
+                "host_cpus_per_rank": (len(numa) if numa else None),
+                "tiles_fast_exact_empty": [stats["n_tiles_fast"], stats["n_tiles_exact"], stats["n_tiles_empty"]],
+                "kernel": stats_kernel},
+        "undistort": undist,
         "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "clocks": sampler.summary(), "parity": parity,
     }

@@ -31,7 +31,7 @@ EXPORTS = [
     "bs_device_count", "bs_version", "bs_last_error", "bs_create", "bs_destroy", "bs_submit",
     "bs_wait", "bs_pipeline_depth", "bs_stitch", "bs_submit_device", "bs_sync",
     "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
-    "bs_set_undistort", "bs_undistort", "bs_submit_device_ex",
+    "bs_set_undistort", "bs_undistort", "bs_submit_device_ex", "bs_undistort_device",
 ]
 
 
@@ -48,7 +48,7 @@ class Stats(ctypes.Structure):
                 ("n_tiles_exact", ctypes.c_int64), ("n_tiles_empty", ctypes.c_int64),
                 ("kernel_launches", ctypes.c_int64), ("frames_submitted", ctypes.c_int64),
                 ("device_bytes", ctypes.c_uint64), ("scratch_bytes", ctypes.c_uint64),
-                ("h2d_bytes_last_submit", ctypes.c_uint64)]
+                ("h2d_bytes_last_submit", ctypes.c_uint64), ("frame_kernel", ctypes.c_int)]
 
 
 _lib = None
@@ -91,6 +91,7 @@ def lib():
     L.bs_host_free.argtypes = [vp]
     L.bs_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
     L.bs_set_undistort.argtypes = [vp, i, dp, dp, i]
+    L.bs_undistort_device.argtypes = [vp, i, vp, sz, vp, sz, vp]
     L.bs_undistort.argtypes = [vp, i, i, sz, vp, sz, dp, dp, i]
     L.bs_stitch_device_static.argtypes = [i, ip, ip, ctypes.POINTER(vp), ctypes.POINTER(sz), i, i, vp, sz, dp,
                                           ctypes.c_uint, vp]
@@ -223,6 +224,11 @@ class Stitcher:
         dptr = dist.ctypes.data_as(ctypes.POINTER(ctypes.c_double)) if dist.size else None
         _check(lib().bs_set_undistort(self._h, cam, K.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), dptr,
                                       int(dist.size)), self._h)
+
+    def undistort_device(self, cam, src_ptr, src_pitch, dst_ptr, dst_pitch, stream=0):
+        """bs_undistort_device: cv::undistort of one device-resident frame of camera `cam`."""
+        _check(lib().bs_undistort_device(self._h, int(cam), int(src_ptr), int(src_pitch), int(dst_ptr), int(dst_pitch),
+                                         int(stream) if stream else None), self._h)
 
     def stats(self):
         s = Stats()

@@ -543,6 +543,36 @@ bs::UndistortArgs lens_args(const bs_handle *h, const LensModel &m, int i)
     return U;
 }
 
+// cv::undistort of one frame of camera `cam` (which has a lens model) between device buffers.
+int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8_t *d_dst, size_t dpitch, cudaStream_t stream)
+{
+    const LensModel &m = h->lens[cam];
+    const bool aligned4 = (reinterpret_cast<uintptr_t>(d_src) & 3) == 0 && (spitch & 3) == 0 &&
+                          (reinterpret_cast<uintptr_t>(d_dst) & 3) == 0 && (dpitch & 3) == 0;
+    if (m.d_map && aligned4) {
+        // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
+        bs::RemapArgs R;
+        R.src = static_cast<const uint8_t *>(d_src);
+        R.dst = d_dst;
+        R.spitch = (long long)spitch;
+        R.dpitch = (long long)dpitch;
+        R.w = h->sw[cam];
+        R.h = h->sh[cam];
+        R.map = m.d_map;
+        bs::undistort_remap_kernel<<<h->remap_grid, 256, 0, stream>>>(R);
+    } else {
+        bs::UndistortArgs U = lens_args(h, m, cam);
+        U.src = static_cast<const uint8_t *>(d_src);
+        U.dst = d_dst;
+        U.spitch = (long long)spitch;
+        U.dpitch = (long long)dpitch;
+        bs::undistort_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, stream>>>(U);
+    }
+    BS_CUDA(h, cudaGetLastError());
+    h->kernel_launches++;
+    return BS_OK;
+}
+
 // The buffer an undistorted frame of camera `cam` is written to (one per user of the lens model).
 int alloc_undist(bs_handle *h, std::vector<uint8_t *> &tmp, int cam)
 {
@@ -567,28 +597,8 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
         const LensModel &m = h->lens[i];
         if ((int)tmp.size() < h->n_cams || !tmp[i])     // allocated by bs_set_undistort / ensure_ring, never here
             return fail(h, BS_ERR_INVALID_ARG, "internal: no undistort buffer for camera %d", i);
-        const bool aligned4 = (reinterpret_cast<uintptr_t>(d_frames[i]) & 3) == 0 && (pitch[i] & 3) == 0;
-        if (m.d_map && aligned4) {
-            // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
-            bs::RemapArgs R;
-            R.src = static_cast<const uint8_t *>(d_frames[i]);
-            R.dst = tmp[i];
-            R.spitch = (long long)pitch[i];
-            R.dpitch = (long long)h->d_frame_pitch[i];
-            R.w = h->sw[i];
-            R.h = h->sh[i];
-            R.map = m.d_map;
-            bs::undistort_remap_kernel<<<h->remap_grid, 256, 0, stream>>>(R);
-        } else {
-            bs::UndistortArgs U = lens_args(h, m, i);
-            U.src = static_cast<const uint8_t *>(d_frames[i]);
-            U.dst = tmp[i];
-            U.spitch = (long long)pitch[i];
-            U.dpitch = (long long)h->d_frame_pitch[i];
-            bs::undistort_kernel<<<dim3((U.w + 63) / 64, (U.h + 3) / 4), 256, 0, stream>>>(U);
-        }
-        BS_CUDA(h, cudaGetLastError());
-        h->kernel_launches++;
+        const int rc = undistort_one(h, i, d_frames[i], pitch[i], tmp[i], h->d_frame_pitch[i], stream);
+        if (rc != BS_OK) return rc;
         if (launched) *launched = true;
         out_frames[i] = tmp[i];
         out_pitch[i] = h->d_frame_pitch[i];
@@ -1113,6 +1123,28 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     return BS_OK;
 }
 
+int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch, void *d_dst, size_t dpitch, void *stream)
+{
+    if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_undistort_device: NULL handle");
+    if (cam < 0 || cam >= h->n_cams || !d_src || !d_dst || d_src == d_dst)
+        return fail(h, BS_ERR_INVALID_ARG, "bs_undistort_device: bad camera index or buffers");
+    if (spitch < (size_t)h->sw[cam] * 3 || dpitch < (size_t)h->sw[cam] * 3)
+        return fail(h, BS_ERR_INVALID_ARG, "bs_undistort_device: pitch below %d*3", h->sw[cam]);
+    int prev_dev = -1;
+    BS_CUDA(h, cudaGetDevice(&prev_dev));
+    if (prev_dev != h->device) BS_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = BS_OK;
+    if (h->lens.empty() || !h->lens[cam].enabled) {          // zero model: cv::undistort is an exact copy
+        if (cudaMemcpy2DAsync(d_dst, dpitch, d_src, spitch, (size_t)h->sw[cam] * 3, h->sh[cam], cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+            rc = fail(h, BS_ERR_CUDA, "bs_undistort_device: copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+    } else {
+        rc = undistort_one(h, cam, d_src, spitch, static_cast<uint8_t *>(d_dst), dpitch, st);
+    }
+    if (prev_dev != h->device) cudaSetDevice(prev_dev);
+    return rc;
+}
+
 int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, size_t dpitch, const double K[9],
                  const double *dist, int n_dist)
 {
@@ -1209,6 +1241,7 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
     out->device_bytes = h->device_bytes;
     out->scratch_bytes = h->scratch_bytes;
     out->h2d_bytes_last_submit = h->h2d_bytes_last;
+    out->frame_kernel = !h->fast_ok ? 0 : (h->compact ? 2 : 1);
     return BS_OK;
 }
 

@@ -70,6 +70,7 @@ typedef struct bs_stats {
     uint64_t scratch_bytes;   /* of which plan/scratch */
     uint64_t h2d_bytes_last_submit; /* bytes the last bs_submit copied to the device: only the part
                                        of every frame the plan can read is uploaded */
+    int frame_kernel;         /* 0: exact per-pixel kernel only, 1: general staged kernel, 2: compact-box staged kernel */
 } bs_stats;
 
 /* Number of CUDA devices visible; 0 if none (never negative). */
@@ -161,6 +162,12 @@ int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8
  * coefficients are all zero (or K == NULL) disables the step: cv::undistort is then an exact copy.
  */
 int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dist, int n_dist);
+
+/* cv::undistort of one frame of camera `cam` with the model set by bs_set_undistort, between DEVICE
+ * buffers (packed BGR, d_src != d_dst), asynchronous on `stream`: tools/stitch/main.cpp:148-149 for callers
+ * whose frames are already on the GPU.  A camera without a model is copied. */
+int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch, void *d_dst, size_t dpitch,
+                        void *stream);
 
 /* Drop-in for ONE cv::undistort(src, dst, K, dist) call on host buffers (main.cpp:148-149). */
 int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, size_t dpitch,

@@ -25,9 +25,17 @@ constexpr int kConvGroups = 10;                          // groups of four texel
 constexpr int kConvTexels = 4 * kConvGroups;             // 40
 constexpr int kConvPitch = 4 * kConvTexels;              // 160 bytes
 constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
-constexpr int kRec2Slots = 16;
-constexpr int kWarp2Smem = 2 * kRawStage + kConvRegion + kWarpOutBytes + warp_ctl_bytes(kRec2Slots);
+#ifndef BS2_RAW_STAGES
+#define BS2_RAW_STAGES 2
+#endif
+#ifndef BS2_REC_SLOTS
+#define BS2_REC_SLOTS 16
+#endif
+constexpr int kRawStages = BS2_RAW_STAGES;               // boxes in flight ahead of the one being converted
+constexpr int kRec2Slots = BS2_REC_SLOTS;                // record ring slots per warp (two halves)
+constexpr int kWarp2Smem = kRawStages * kRawStage + kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
 static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
+static_assert(kRawStages == 1 || kRawStages == 2, "stage index is n & (kRawStages - 1)");
 
 #ifndef BS2_WARPS_PER_CTA
 #define BS2_WARPS_PER_CTA 8
@@ -110,12 +118,18 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 __device__ __forceinline__ void convert_box(uint32_t src, uint32_t dst, int lane)
 {
     if (lane < 30) {
+        uint32_t w[kRawRows / 3][3];       // every load is issued before the first store: one round trip, not six
 #pragma unroll
         for (int it = 0; it < kRawRows / 3; ++it) {
             const uint32_t s = src + (uint32_t)(it * 3 * kRawPitch);
-            const uint32_t w0 = lds32(s), w1 = lds32(s + 4), w2 = lds32(s + 8);   // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
-            sts128(dst + (uint32_t)(it * 3 * kConvPitch), w0, __byte_perm(w0, w1, 0x6543), __byte_perm(w1, w2, 0x5432), w2 >> 8);
+            w[it][0] = lds32(s);            // B0 G0 R0 B1
+            w[it][1] = lds32(s + 4);        // G1 R1 B2 G2
+            w[it][2] = lds32(s + 8);        // R2 B3 G3 R3
         }
+#pragma unroll
+        for (int it = 0; it < kRawRows / 3; ++it)
+            sts128(dst + (uint32_t)(it * 3 * kConvPitch), w[it][0], __byte_perm(w[it][0], w[it][1], 0x6543),
+                   __byte_perm(w[it][1], w[it][2], 0x5432), w[it][2] >> 8);
     }
 }
 
@@ -158,7 +172,17 @@ __device__ __forceinline__ void store_px_bytes(uint32_t p8, uint32_t px)
 __device__ __forceinline__ uint32_t tap_addr(uint32_t base, int xbits, int ybits)
 {
     const uint32_t ym = (uint32_t)ybits & ~31u, xm = (uint32_t)xbits & ~31u;
-    return base + ym * (uint32_t)(kConvPitch / 32) + (xm >> 3);
+    return __umulhi(xm, 1u << 29) + (ym * (uint32_t)(kConvPitch / 32) + base);      // LEA.HI + IMAD
+}
+// tap_weights() of stitch_fast.cuh with the subtraction kept as one shift-and-subtract (LEA).
+__device__ __forceinline__ uint2 tap_weights2(uint32_t a, uint32_t b)
+{
+    const uint32_t a2 = a * (0xFFFFu * 64u) + 2048u;
+    const uint32_t w23 = b * a2;
+    uint32_t w01;
+    asm("mad.lo.u32 %0, %1, 32, %2;" : "=r"(w01) : "r"(a2), "r"(0u - w23));
+    if (w01 == 0x10000u) w01 = 0xFFFFu;
+    return make_uint2(w01, w23);
 }
 
 // Hot path: the layer covers every pixel of the block with interior samples and the plan verified the
@@ -174,7 +198,7 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
         int xbits, ybits;
         lane_coord_bits2(lc, (float)(k - kRun / 2), xbits, ybits);
         return fetch_taps2(tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits),
-                           tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+                           tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     Taps2 cur = fetch(0);
 #pragma unroll
@@ -208,7 +232,7 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
 }
 
 // Partially covered layer whose cheap coordinates hold everywhere: coverage test and byte stores per pixel.
-__device__ __noinline__ void run_masked2(const LaneCoef2 &lc, uint32_t run0, int vstep, uint32_t out_blk, int lane, int src_w,
+__device__ __noinline__ void run_masked2(const LaneCoef2 lc, uint32_t run0, int vstep, uint32_t out_blk, int lane, int src_w,
                                          int src_h, bool col_in_canvas, int rows_in_canvas, bool first_layer)
 {
     const uint32_t safe = out_blk - 2 * kConvPitch;     // inside the converted buffer: valid for every tap offset
@@ -219,7 +243,7 @@ __device__ __noinline__ void run_masked2(const LaneCoef2 &lc, uint32_t run0, int
         const int sx = (xbits + lc.bx + 32 * lc.nxv * v) >> kFracBits, sy = (ybits + lc.by + 32 * lc.nyv * v) >> kFracBits;
         in = col_in_canvas && k < rows_in_canvas && (uint32_t)sx < (uint32_t)(src_w - 1) && (uint32_t)sy < (uint32_t)(src_h - 1);
         const uint32_t o = tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits);
-        return fetch_taps2(in ? o : safe, tap_weights((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+        return fetch_taps2(in ? o : safe, tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     bool in_cur, in_nxt = false;
     Taps2 cur = fetch(0, in_cur);
@@ -239,7 +263,7 @@ __device__ __noinline__ void run_masked2(const LaneCoef2 &lc, uint32_t run0, int
 
 // General path: partially covered layers with flagged 32x4 groups (those use the exact fp64 coordinates).
 // `conv_origin` = address texel (0, 0) of the camera would have in the converted buffer.
-__device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam, const LaneCoef2 &lc, uint32_t conv_origin,
+__device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam, const LaneCoef2 lc, uint32_t conv_origin,
                                           uint32_t out_blk, uint32_t group_mask, bool first_layer, int x, int y0, int lane)
 {
     const int xb = (x / F.block_w) * F.block_w;
@@ -259,7 +283,7 @@ __device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam,
         const int sx = X >> kFracBits, sy = Y >> kFracBits;
         const bool in = (x < F.W) && (y0 + k < F.H) && sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1;
         const uint32_t o = in ? conv_origin + (uint32_t)(sy * kConvPitch + sx * 4) : safe;
-        uint32_t px = sample_conv(o, tap_weights((uint32_t)X & 31u, (uint32_t)Y & 31u));
+        uint32_t px = sample_conv(o, tap_weights2((uint32_t)X & 31u, (uint32_t)Y & 31u));
         if (in || first_layer) {
             if (!in) px = 0;
             store_px_bytes(out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane, px);
@@ -278,7 +302,7 @@ __device__ __noinline__ void patch_exact2(const FrameArgs &F, const CamDev &cam,
         int X, Y;
         coord_exact(cam.M, xb, x - xb, y0 + k, X, Y);
         const uint32_t o = conv_origin + (uint32_t)((Y >> kFracBits) * kConvPitch + (X >> kFracBits) * 4);
-        const uint32_t px = sample_conv(o, tap_weights((uint32_t)X & 31u, (uint32_t)Y & 31u));
+        const uint32_t px = sample_conv(o, tap_weights2((uint32_t)X & 31u, (uint32_t)Y & 31u));
         store_px_bytes(out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane, px);
     }
 }
@@ -291,7 +315,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const uint32_t raw0 = raw_base + (uint32_t)(warp * kWarp2Smem);           // 128-byte aligned
-    const uint32_t conv = raw0 + 2 * kRawStage;
+    const uint32_t conv = raw0 + kRawStages * kRawStage;
     const uint32_t out_blk = conv + kConvRegion;
     const uint32_t rec0 = out_blk + kWarpOutBytes;
     constexpr uint32_t rec_slots = kRec2Slots, rec_half = kRec2Slots / 2;
@@ -302,7 +326,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     // it touches the canvas only after griddepcontrol.wait.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (lane == 0) {
-        for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dbar0 + 8 * s), "r"(1));
+        for (int s = 0; s < kRawStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(dbar0 + 8 * s), "r"(1));
         for (int s = 0; s < 2; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(rbar0 + 8 * s), "r"(1));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -356,7 +380,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     }
     if (lane == 0) {
         issue_box(lds128(rec_addr(0)), 0u);
-        if (cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
+        if (kRawStages > 1 && cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
     }
     __syncwarp();
 
@@ -369,7 +393,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t lane_goff = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
     bool wrote = false;               // some layer has written into the current block
     for (int n = 0; n < cnt; ++n) {
-        const uint32_t stage = (uint32_t)n & 1u, dpar = ((uint32_t)n >> 1) & 1u;
+        const uint32_t stage = (uint32_t)n & (kRawStages - 1), dpar = ((uint32_t)n / kRawStages) & 1u;
         if (lane == 0 && ((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt)
             request_records(n + (int)rec_half);      // the half items n-8 .. n-1 used is free: refill it with n+8 .. n+15
         const uint32_t ra = rec_addr(n);
@@ -385,9 +409,9 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             convert_box(raw0 + stage * (uint32_t)kRawStage + cv_src + (bc.aux >> 16), cv_dst, lane);
         }
         __syncwarp();                 // converted box complete; the raw stage is free
-        if (n + 2 < cnt) {
-            wait_half_of(n + 2);
-            if (lane == 0) issue_box(lds128(rec_addr(n + 2)), stage);
+        if (n + kRawStages < cnt) {
+            wait_half_of(n + kRawStages);
+            if (lane == 0) issue_box(lds128(rec_addr(n + kRawStages)), stage);
         }
         if (fast) {
             const uint32_t c = (r.y >> 16) & 0xFFu;

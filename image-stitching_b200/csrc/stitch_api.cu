@@ -282,6 +282,11 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
         L->box_h[c] = bh[c];
         stage = std::max(stage, we[c] * 4 * bh[c]);
     }
+    if (compact) {      // one box shape for every camera: the frame kernel then expects one byte count
+        int rows = 0;
+        for (int c = 0; c < n_cams; ++c) rows = std::max(rows, L->box_h[c]);
+        for (int c = 0; c < n_cams; ++c) L->box_h[c] = rows;
+    }
     L->stage_bytes = (int)align_up((size_t)stage + bs::kStagePad, 128);
     L->smem_bytes = cta_smem_bytes(L->stage_bytes, bs::kRecSlotsMax);
     L->n_fast = L->n_exact = L->n_empty = 0;
@@ -303,8 +308,18 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
             it.origin_off = (uint32_t)((int)it.y0 * (L->box_we[it.cam] * 4) + 4 * (int)it.c0);
             it.coef = r.coef[l];
             if (L->compact) {
+                // compact kernel (stitch_fast2.cuh): c0 holds the first converted texel column, origin_off the
+                // converted-buffer offset of lane u = 0 / row v = -8 (whole-texel parts), aux the byte steps
+                // per canvas column and row
                 const int t0 = compact_t0(r.layer[l].x0);
-                it.coef.aux = (uint32_t)t0 | ((uint32_t)(3 * t0 - 4 * (int)it.c0) << 16);
+                const bs::BlockCoef &c = r.coef[l];
+                const int ustep = c.nyu * bs::kConvPitch + c.nxu * 4, vstep = c.nyv * bs::kConvPitch + c.nxv * 4;
+                const long long run_rel = -((long long)it.y0 * bs::kConvPitch + 4LL * t0) +
+                                          (((long long)c.iy - bs::kMagicBias) >> 5) * bs::kConvPitch +
+                                          (((long long)c.ix - bs::kMagicBias) >> 5) * 4 - (long long)(bs::kRun / 2) * vstep;
+                it.c0 = (int16_t)t0;
+                it.origin_off = (uint32_t)run_rel;
+                it.coef.aux = ((uint32_t)ustep & 0xFFFFu) | ((uint32_t)vstep << 16);
             }
         }
     };
@@ -427,7 +442,10 @@ int build_plan(bs_handle *h)
     std::vector<bs::WorkItem> items((size_t)h->n_blocks * bs::kMaxLayers);
     PlanLayout L;
     static const bool no_compact = getenv("BS_DEBUG_NO_COMPACT") != nullptr;   // test hook: always the general staged kernel
-    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L, !no_compact);
+    // the compact kernel's fixed TMA box (32 elements x up to 18 rows) must fit inside every frame
+    bool frames_fit = true;
+    for (int i = 0; i < h->n_cams; ++i) frames_fit = frames_fit && h->sw[i] * 3 >= bs::kRawPitch && h->sh[i] >= bs::kRawRows;
+    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L, !no_compact && frames_fit);
     h->compact = L.compact;
     memcpy(h->box_we, L.box_we, sizeof h->box_we);
     memcpy(h->box_h, L.box_h, sizeof h->box_h);
@@ -664,9 +682,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             A.cam[i].pitch = (long long)pitch[i];
             A.cam[i].w = h->sw[i];
             A.cam[i].h = h->sh[i];
-            if (h->compact) {
-                FA2.box_bytes[i] = bs::kRawPitch * h->box_h[i];
-            } else {
+            if (!h->compact) {
                 FA1.pitch[i] = h->box_we[i] * 4;
                 FA1.box_bytes[i] = h->box_we[i] * 4 * h->box_h[i];
             }
@@ -715,6 +731,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             FA2.items = h->d_items;
             FA2.warp_start = h->d_warp_start;
             FA2.wait_sources = sources_from_kernel ? 1 : 0;
+            FA2.box_bytes = bs::kRawPitch * h->box_h[0];
             cfg.blockDim = dim3(bs::kFast2Threads);
             BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel, FA2));
         } else {

@@ -51,7 +51,7 @@ struct Fast2Args {
     CUtensorMap tmap[kMaxCamsPerLaunch];   // source frame of camera i as a [h][pitch/4] u32 tensor, box 32 x box_h[i]
     const WorkItem *items;
     const int *warp_start;
-    int box_bytes[kMaxCamsPerLaunch];      // 128 * box rows of camera i (what the mbarrier expects)
+    int box_bytes;                         // 128 * box rows (all cameras use the same box; what the mbarrier expects)
     int wait_sources;                      // 1: the source frames may come from the kernel just before this one in
                                            // the stream: order every source read behind it (griddepcontrol.wait first)
 };
@@ -84,17 +84,24 @@ __device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b)
 // sequence the plan kernel verified (fma.rn.f32x2 is two independent IEEE fma.rn.f32).
 struct LaneCoef2 {
     uint64_t a0, a1, a2;   // s(v) = a0 + v (a1 + v a2), (x, y)
-    int bx, by;            // X = bits_x + bx + 32 nxv v
-    int nxv, nyv;
 };
-__device__ __forceinline__ LaneCoef2 lane_coef2(const BlockCoef &c, int u)
+__device__ __forceinline__ LaneCoef2 lane_coef2(const BlockCoef &c, float uf)
 {
-    const float uf = (float)u;
     const uint64_t u2 = pack2(uf, uf);
     LaneCoef2 l;
     l.a0 = fma2(u2, fma2(u2, pack2(c.hxuu, c.hyuu), pack2(c.xu, c.yu)), pack2(c.fx, c.fy));
     l.a1 = fma2(u2, pack2(c.xuv, c.yuv), pack2(c.xv, c.yv));
     l.a2 = pack2(c.hxvv, c.hyvv);
+    return l;
+}
+// What only the partially covered layers need: the whole-texel parts, to test a pixel's source texel
+// against the frame (X = bits_x + bx + 32 nxv v, as in lane_coef()).
+struct LaneBase2 {
+    int bx, by, nxv, nyv;
+};
+__device__ __forceinline__ LaneBase2 lane_base2(const BlockCoef &c, int u)
+{
+    LaneBase2 l;
     l.bx = c.ix - kMagicBias + 32 * (int)c.nxu * u;
     l.by = c.iy - kMagicBias + 32 * (int)c.nyu * u;
     l.nxv = c.nxv;
@@ -232,15 +239,15 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
 }
 
 // Partially covered layer whose cheap coordinates hold everywhere: coverage test and byte stores per pixel.
-__device__ __noinline__ void run_masked2(const LaneCoef2 lc, uint32_t run0, int vstep, uint32_t out_blk, int lane, int src_w,
-                                         int src_h, bool col_in_canvas, int rows_in_canvas, bool first_layer)
+__device__ __noinline__ void run_masked2(const LaneCoef2 lc, const LaneBase2 lb, uint32_t run0, int vstep, uint32_t out_blk, int lane,
+                                         int src_w, int src_h, bool col_in_canvas, int rows_in_canvas, bool first_layer)
 {
     const uint32_t safe = out_blk - 2 * kConvPitch;     // inside the converted buffer: valid for every tap offset
     auto fetch = [&](int k, bool &in) {
         const int v = k - kRun / 2;
         int xbits, ybits;
         lane_coord_bits2(lc, (float)v, xbits, ybits);
-        const int sx = (xbits + lc.bx + 32 * lc.nxv * v) >> kFracBits, sy = (ybits + lc.by + 32 * lc.nyv * v) >> kFracBits;
+        const int sx = (xbits + lb.bx + 32 * lb.nxv * v) >> kFracBits, sy = (ybits + lb.by + 32 * lb.nyv * v) >> kFracBits;
         in = col_in_canvas && k < rows_in_canvas && (uint32_t)sx < (uint32_t)(src_w - 1) && (uint32_t)sy < (uint32_t)(src_h - 1);
         const uint32_t o = tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits);
         return fetch_taps2(in ? o : safe, tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
@@ -263,8 +270,8 @@ __device__ __noinline__ void run_masked2(const LaneCoef2 lc, uint32_t run0, int 
 
 // General path: partially covered layers with flagged 32x4 groups (those use the exact fp64 coordinates).
 // `conv_origin` = address texel (0, 0) of the camera would have in the converted buffer.
-__device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam, const LaneCoef2 lc, uint32_t conv_origin,
-                                          uint32_t out_blk, uint32_t group_mask, bool first_layer, int x, int y0, int lane)
+__device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam, const LaneCoef2 lc, const LaneBase2 lb,
+                                          uint32_t conv_origin, uint32_t out_blk, uint32_t group_mask, bool first_layer, int x, int y0, int lane)
 {
     const int xb = (x / F.block_w) * F.block_w;
     const uint32_t safe = out_blk - 2 * kConvPitch;
@@ -277,8 +284,8 @@ __device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam,
             const int v = k - kRun / 2;
             int xbits, ybits;
             lane_coord_bits2(lc, (float)v, xbits, ybits);
-            X = xbits + lc.bx + 32 * lc.nxv * v;
-            Y = ybits + lc.by + 32 * lc.nyv * v;
+            X = xbits + lb.bx + 32 * lb.nxv * v;
+            Y = ybits + lb.by + 32 * lb.nyv * v;
         }
         const int sx = X >> kFracBits, sy = Y >> kFracBits;
         const bool in = (x < F.W) && (y0 + k < F.H) && sx >= 0 && sy >= 0 && sx < cam.w - 1 && sy < cam.h - 1;
@@ -351,12 +358,14 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
             const uint32_t cam = (r.y >> 16) & 0xFFu;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
-                         "r"((uint32_t)A.box_bytes[cam])
+                         "r"((uint32_t)A.box_bytes)
                          : "memory");
+            // the box starts at the 16-byte aligned element at or before the first converted texel column
+            const int c0 = (int)(((3u * (r.z & 0xFFFFu)) >> 4) << 2);
             asm volatile(
                 "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                     raw0 + stage * (uint32_t)kRawStage),
-                "l"(&A.tmap[cam]), "r"((int)(int16_t)(r.z & 0xFFFFu)), "r"((int)(int16_t)(r.z >> 16)), "r"(dbar0 + 8 * stage)
+                "l"(&A.tmap[cam]), "r"(c0), "r"((int)(int16_t)(r.z >> 16)), "r"(dbar0 + 8 * stage)
                 : "memory");
         } else {
             mbar_arrive_addr(dbar0 + 8 * stage);
@@ -390,6 +399,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t cv_src = (uint32_t)((lane / kConvGroups) * kRawPitch + 12 * (lane % kConvGroups));
     const uint32_t cv_dst = conv + (uint32_t)((lane / kConvGroups) * kConvPitch + 16 * (lane % kConvGroups));
     const int u = lane - kBlockW / 2;
+    const float uf = (float)u;
     const uint32_t lane_goff = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
     bool wrote = false;               // some layer has written into the current block
     for (int n = 0; n < cnt; ++n) {
@@ -397,6 +407,8 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if (lane == 0 && ((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt)
             request_records(n + (int)rec_half);      // the half items n-8 .. n-1 used is free: refill it with n+8 .. n+15
         const uint32_t ra = rec_addr(n);
+        // item header (layout_plan, compact form): bx | by << 16, type | flags << 8 | cam << 16 | groups << 24,
+        // t0 | y0 << 16 (first converted texel column, first box row), run base of lane u = 0 in the converted buffer
         const uint4 r = lds128(ra);
         bool direct = false;
         const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
@@ -406,7 +418,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if (fast) {
             bc = load_block_coef(ra);
             mbar_wait_addr(dbar0 + 8 * stage, dpar);                       // the box has landed
-            convert_box(raw0 + stage * (uint32_t)kRawStage + cv_src + (bc.aux >> 16), cv_dst, lane);
+            convert_box(raw0 + stage * (uint32_t)kRawStage + cv_src + ((3u * (r.z & 0xFFFFu)) & 15u), cv_dst, lane);
         }
         __syncwarp();                 // converted box complete; the raw stage is free
         if (n + kRawStages < cnt) {
@@ -414,16 +426,10 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             if (lane == 0) issue_box(lds128(rec_addr(n + kRawStages)), stage);
         }
         if (fast) {
-            const uint32_t c = (r.y >> 16) & 0xFFu;
-            const CamDev &cam = A.F.cam[c];
-            const LaneCoef2 lc = lane_coef2(bc, u);
-            // address texel (0, 0) of this camera would have in the converted buffer
-            const int y0 = (int)(int16_t)(r.z >> 16), t0 = (int)(bc.aux & 0xFFFFu);
-            const uint32_t conv_origin = conv - (uint32_t)(y0 * kConvPitch + t0 * 4);
-            const int vstep = lc.nyv * kConvPitch + lc.nxv * 4;
-            const uint32_t run0 = conv_origin + (uint32_t)((lc.by >> kFracBits) * kConvPitch + (lc.bx >> kFracBits) * 4) -
-                                  (uint32_t)((kRun / 2) * vstep);
-            const uint32_t groups = (r.y >> 24) & 0xFFu;
+            const LaneCoef2 lc = lane_coef2(bc, uf);
+            const int ustep = (int)(int16_t)(bc.aux & 0xFFFFu), vstep = (int)(int16_t)(bc.aux >> 16);
+            const uint32_t run0 = conv + r.w + (uint32_t)(u * ustep);
+            const uint32_t groups = r.y >> 24;
             if (flags & kItemFull) {
                 direct = groups == 0u && prior_grid_done && A.F.canvas_in_4g &&
                          (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
@@ -434,12 +440,19 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                     run_full2<false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing);
                 if (groups != 0u) {
                     __syncwarp();
-                    patch_exact2(A.F, cam, conv_origin, out_blk, groups, tx0 + lane, ty0, lane);
+                    const uint32_t conv_origin = conv - (uint32_t)((int)(int16_t)(r.z >> 16) * kConvPitch + (int)(r.z & 0xFFFFu) * 4);
+                    patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin, out_blk, groups, tx0 + lane, ty0, lane);
                 }
-            } else if (groups == 0u) {
-                run_masked2(lc, run0, vstep, out_blk, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
             } else {
-                run_general2(A.F, cam, lc, conv_origin, out_blk, groups, !wrote, tx0 + lane, ty0, lane);
+                const CamDev &cam = A.F.cam[(r.y >> 16) & 0xFFu];
+                const LaneBase2 lb = lane_base2(bc, u);
+                if (groups == 0u) {
+                    run_masked2(lc, lb, run0, vstep, out_blk, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
+                } else {
+                    // address texel (0, 0) of this camera would have in the converted buffer
+                    const uint32_t conv_origin = conv - (uint32_t)((int)(int16_t)(r.z >> 16) * kConvPitch + (int)(r.z & 0xFFFFu) * 4);
+                    run_general2(A.F, cam, lc, lb, conv_origin, out_blk, groups, !wrote, tx0 + lane, ty0, lane);
+                }
             }
             wrote = !direct;
         }

@@ -9,8 +9,9 @@
 //     (no alignment shifts, no third word), pairs them with four PRMT and blends with six dp2a;
 //   * the x and y coordinate polynomials are evaluated together with the packed fp32 instructions
 //     of sm_100 (fma.rn.f32x2 / add.rn.f32x2): 3 instructions per pixel instead of 6;
-//   * two raw stages + one converted buffer: boxes of items n+1 and n+2 are in flight while item n
-//     is computed.
+//   * two raw stages + two converted buffers: while item n is blended from one converted buffer the
+//     box of item n+1 is rewritten into the other, its loads and stores spread between the pixel
+//     instructions of the hot loop, and the boxes of items n+2 and n+3 are in flight.
 // Replaces the camera loop body /root/reference/tools/stitch/main.cpp:145-152.
 #pragma once
 
@@ -33,9 +34,9 @@ constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
 #endif
 constexpr int kRawStages = BS2_RAW_STAGES;               // boxes in flight ahead of the one being converted
 constexpr int kRec2Slots = BS2_REC_SLOTS;                // record ring slots per warp (two halves)
-constexpr int kWarp2Smem = kRawStages * kRawStage + kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
+constexpr int kWarp2Smem = kRawStages * kRawStage + 2 * kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
 static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
-static_assert(kRawStages == 1 || kRawStages == 2, "stage index is n & (kRawStages - 1)");
+static_assert(kRawStages == 2, "the item pipeline is written for two raw stages");
 
 #ifndef BS2_WARPS_PER_CTA
 #define BS2_WARPS_PER_CTA 8
@@ -120,24 +121,32 @@ __device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, ui
 {
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
-// `src`: this lane's first raw word (row lane/10 of the stage, texel group lane%10), `dst`: its first
-// converted word.  Six steps of three rows; lanes 30 and 31 have nothing to do.
-__device__ __forceinline__ void convert_box(uint32_t src, uint32_t dst, int lane)
+// One conversion step: three raw words (four packed texels) -> four texel words.
+struct ConvWords {
+    uint32_t w0, w1, w2;      // B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+};
+__device__ __forceinline__ ConvWords conv_load(uint32_t s)
 {
-    if (lane < 30) {
-        uint32_t w[kRawRows / 3][3];       // every load is issued before the first store: one round trip, not six
+    ConvWords c;
+    c.w0 = lds32(s);
+    c.w1 = lds32(s + 4);
+    c.w2 = lds32(s + 8);
+    return c;
+}
+__device__ __forceinline__ void conv_store(uint32_t d, const ConvWords &c)
+{
+    sts128(d, c.w0, __byte_perm(c.w0, c.w1, 0x6543), __byte_perm(c.w1, c.w2, 0x5432), c.w2 >> 8);
+}
+constexpr int kConvSteps = kRawRows / 3;
+// `src`: this lane's first raw word (row slot/10 of the stage, texel group slot%10, slot = min(lane, 29):
+// lanes 30 and 31 repeat the work of 28 and 29), `dst`: its first converted word.  Six steps of three rows.
+__device__ __forceinline__ void convert_box(uint32_t src, uint32_t dst)
+{
+    ConvWords c[kConvSteps];       // every load is issued before the first store: one round trip, not six
 #pragma unroll
-        for (int it = 0; it < kRawRows / 3; ++it) {
-            const uint32_t s = src + (uint32_t)(it * 3 * kRawPitch);
-            w[it][0] = lds32(s);            // B0 G0 R0 B1
-            w[it][1] = lds32(s + 4);        // G1 R1 B2 G2
-            w[it][2] = lds32(s + 8);        // R2 B3 G3 R3
-        }
+    for (int it = 0; it < kConvSteps; ++it) c[it] = conv_load(src + (uint32_t)(it * 3 * kRawPitch));
 #pragma unroll
-        for (int it = 0; it < kRawRows / 3; ++it)
-            sts128(dst + (uint32_t)(it * 3 * kConvPitch), w[it][0], __byte_perm(w[it][0], w[it][1], 0x6543),
-                   __byte_perm(w[it][1], w[it][2], 0x5432), w[it][2] >> 8);
-    }
+    for (int it = 0; it < kConvSteps; ++it) conv_store(dst + (uint32_t)(it * 3 * kConvPitch), c[it]);
 }
 
 struct Taps2 {
@@ -197,9 +206,10 @@ __device__ __forceinline__ uint2 tap_weights2(uint32_t a, uint32_t b)
 // for row v = -kRun/2 (whole-texel parts only), `vstep` = whole texels per canvas row as a byte offset.
 // kDirect: every row goes straight to the canvas, `gp` = address of this lane's word of the block's
 // first row; otherwise rows are collected in the warp's output block in shared memory.
-template <bool kDirect>
+template <bool kDirect, bool kConvert>
 __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, int vstep, uint32_t out_blk, int lane,
-                                          uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing)
+                                          uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing, uint32_t cv_src,
+                                          uint32_t cv_dst)
 {
     auto fetch = [&](int k) {
         int xbits, ybits;
@@ -208,10 +218,14 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
                            tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     Taps2 cur = fetch(0);
+    ConvWords cw;
 #pragma unroll
     for (int k = 0; k < kRun; ++k) {
         Taps2 nxt = cur;
         if (k + 1 < kRun) nxt = fetch(k + 1);
+        // kConvert: the next item's box is rewritten on the side, one step per two pixel rows, so that
+        // its shared-memory round trips hide behind the pixel arithmetic
+        if (kConvert && k < 2 * kConvSteps && (k & 1) == 0) cw = conv_load(cv_src + (uint32_t)((k / 2) * 3 * kRawPitch));
         const uint32_t px = blend_taps2(cur);
         if (kDirect) {
             // this lane's word of the row, then on to the next row: the canvas does not straddle a 4 GB
@@ -234,6 +248,7 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
         } else {
             store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
         }
+        if (kConvert && k < 2 * kConvSteps && (k & 1) == 1) conv_store(cv_dst + (uint32_t)((k / 2) * 3 * kConvPitch), cw);
         cur = nxt;
     }
 }
@@ -317,13 +332,14 @@ __device__ __noinline__ void patch_exact2(const FrameArgs &F, const CamDev &cam,
 __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kernel(const __grid_constant__ Fast2Args A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    // layout: [pad to a 128-byte boundary][per warp: raw stage 0 | raw stage 1 | converted box | output block | records | mbarriers]
+    // layout: [pad to a 128-byte boundary][per warp: raw stage 0 | raw stage 1 | converted box 0 | converted box 1 |
+    //          output block | records | mbarriers]
     const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const uint32_t raw0 = raw_base + (uint32_t)(warp * kWarp2Smem);           // 128-byte aligned
-    const uint32_t conv = raw0 + kRawStages * kRawStage;
-    const uint32_t out_blk = conv + kConvRegion;
+    const uint32_t conv0 = raw0 + kRawStages * kRawStage;
+    const uint32_t out_blk = conv0 + 2 * kConvRegion;
     const uint32_t rec0 = out_blk + kWarpOutBytes;
     constexpr uint32_t rec_slots = kRec2Slots, rec_half = kRec2Slots / 2;
     const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per raw stage
@@ -354,6 +370,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                      "l"(A.items + i0 + first), "r"(bytes), "r"(rbar0 + 8 * half)
                      : "memory");
     };
+    // source box of the item whose header words are `r` -> raw stage; items without a box just arrive
     auto issue_box = [&](const uint4 &r, uint32_t stage) {
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
             const uint32_t cam = (r.y >> 16) & 0xFFu;
@@ -375,6 +392,16 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     auto wait_half_of = [&](int m) {      // first item of a half: every lane observes the copy's completion itself
         if (((uint32_t)m & (rec_half - 1)) == 0) mbar_wait_addr(rbar0 + 8 * (((uint32_t)m / rec_half) & 1u), ((uint32_t)m / rec_slots) & 1u);
     };
+    // item m: its data barrier and parity, its raw stage, and where this lane's conversion slot reads and writes
+    const uint32_t slot = (uint32_t)min(lane, 3 * kConvGroups - 1);
+    const uint32_t cv_src_lane = (slot / kConvGroups) * kRawPitch + 12 * (slot % kConvGroups);
+    const uint32_t cv_dst_lane = (slot / kConvGroups) * kConvPitch + 16 * (slot % kConvGroups);
+    auto box_landed_wait = [&](int m) { mbar_wait_addr(dbar0 + 8 * ((uint32_t)m & 1u), ((uint32_t)m >> 1) & 1u); };
+    auto box_landed_try = [&](int m) { return mbar_try_wait_addr(dbar0 + 8 * ((uint32_t)m & 1u), ((uint32_t)m >> 1) & 1u); };
+    auto cv_src_of = [&](int m, uint32_t hdr_z) {      // first converted texel column t0: its byte offset in the staged row is 3 t0 mod 16
+        return raw0 + ((uint32_t)m & 1u) * (uint32_t)kRawStage + cv_src_lane + ((3u * (hdr_z & 0xFFFFu)) & 15u);
+    };
+    auto cv_dst_of = [&](int m) { return conv0 + ((uint32_t)m & 1u) * (uint32_t)kConvRegion + cv_dst_lane; };
 
     if (lane == 0) {
         request_records(0);
@@ -389,43 +416,50 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     }
     if (lane == 0) {
         issue_box(lds128(rec_addr(0)), 0u);
-        if (kRawStages > 1 && cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
+        if (cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
     }
     __syncwarp();
+    uint4 r = lds128(rec_addr(0));    // header of the current item
+    // Item pipeline: at the top of iteration n the box of item n is already rewritten in converted buffer n & 1,
+    // the box of item n+1 is landing in (or has reached) raw stage (n+1) & 1, the box of item n+2 is in flight.
+    if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
+        box_landed_wait(0);
+        convert_box(cv_src_of(0, r.z), cv_dst_of(0));
+    }
+    __syncwarp();
+    if (cnt > 2) {
+        if (lane == 0) issue_box(lds128(rec_addr(2)), 0u);      // records 0 .. 7 are all there
+        __syncwarp();
+    }
 
-    // lane constants: output word merge (store_row_pixel), conversion slot, column offset
+    // lane constants: output word merge (store_row_pixel), column offsets
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
     const uint32_t storing = (uint32_t)((lane & 3) != 3);
-    const uint32_t cv_src = (uint32_t)((lane / kConvGroups) * kRawPitch + 12 * (lane % kConvGroups));
-    const uint32_t cv_dst = conv + (uint32_t)((lane / kConvGroups) * kConvPitch + 16 * (lane % kConvGroups));
     const int u = lane - kBlockW / 2;
     const float uf = (float)u;
     const uint32_t lane_goff = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
     bool wrote = false;               // some layer has written into the current block
     for (int n = 0; n < cnt; ++n) {
-        const uint32_t stage = (uint32_t)n & (kRawStages - 1), dpar = ((uint32_t)n / kRawStages) & 1u;
         if (lane == 0 && ((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt)
             request_records(n + (int)rec_half);      // the half items n-8 .. n-1 used is free: refill it with n+8 .. n+15
-        const uint32_t ra = rec_addr(n);
         // item header (layout_plan, compact form): bx | by << 16, type | flags << 8 | cam << 16 | groups << 24,
         // t0 | y0 << 16 (first converted texel column, first box row), run base of lane u = 0 in the converted buffer
-        const uint4 r = lds128(ra);
+        const uint32_t ra = rec_addr(n);
+        const uint32_t conv = conv0 + ((uint32_t)n & 1u) * (uint32_t)kConvRegion;
         bool direct = false;
         const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
-        const bool fast = type == (uint32_t)kBlockFast;
-        BlockCoef bc;
-        if (fast) {
-            bc = load_block_coef(ra);
-            mbar_wait_addr(dbar0 + 8 * stage, dpar);                       // the box has landed
-            convert_box(raw0 + stage * (uint32_t)kRawStage + cv_src + ((3u * (r.z & 0xFFFFu)) & 15u), cv_dst, lane);
+        // the next item: does it have a box to rewrite, and has that box landed already?
+        uint4 rn = r;
+        bool next_box = false, next_done = true;
+        if (n + 1 < cnt) {
+            wait_half_of(n + 1);
+            rn = lds128(rec_addr(n + 1));
+            next_box = (rn.y & 0xFFu) == (uint32_t)kBlockFast;
+            next_done = !next_box;
         }
-        __syncwarp();                 // converted box complete; the raw stage is free
-        if (n + kRawStages < cnt) {
-            wait_half_of(n + kRawStages);
-            if (lane == 0) issue_box(lds128(rec_addr(n + kRawStages)), stage);
-        }
-        if (fast) {
+        if (type == (uint32_t)kBlockFast) {
+            const BlockCoef bc = load_block_coef(ra);
             const LaneCoef2 lc = lane_coef2(bc, uf);
             const int ustep = (int)(int16_t)(bc.aux & 0xFFFFu), vstep = (int)(int16_t)(bc.aux >> 16);
             const uint32_t run0 = conv + r.w + (uint32_t)(u * ustep);
@@ -434,10 +468,15 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                 direct = groups == 0u && prior_grid_done && A.F.canvas_in_4g &&
                          (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
                 const uint64_t grow = reinterpret_cast<uint64_t>(A.F.canvas + (long long)ty0 * A.F.cpitch + (long long)tx0 * 3 + lane_goff);
-                if (direct)
-                    run_full2<true>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing);
-                else
-                    run_full2<false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing);
+                if (direct && next_box && __all_sync(0xffffffffu, box_landed_try(n + 1))) {
+                    run_full2<true, true>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing,
+                                          cv_src_of(n + 1, rn.z), cv_dst_of(n + 1));
+                    next_done = true;
+                } else if (direct) {
+                    run_full2<true, false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing, 0u, 0u);
+                } else {
+                    run_full2<false, false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing, 0u, 0u);
+                }
                 if (groups != 0u) {
                     __syncwarp();
                     const uint32_t conv_origin = conv - (uint32_t)((int)(int16_t)(r.z >> 16) * kConvPitch + (int)(r.z & 0xFFFFu) * 4);
@@ -456,7 +495,15 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             }
             wrote = !direct;
         }
-        __syncwarp();                 // every lane is done with the converted box
+        if (!next_done) {             // not rewritten on the side: do it now
+            box_landed_wait(n + 1);
+            convert_box(cv_src_of(n + 1, rn.z), cv_dst_of(n + 1));
+        }
+        __syncwarp();                 // every lane is done with converted buffer n & 1 and with raw stage (n+1) & 1
+        if (n + 3 < cnt) {            // that raw stage takes the box of item n+3
+            wait_half_of(n + 3);
+            if (lane == 0) issue_box(lds128(rec_addr(n + 3)), ((uint32_t)n + 1u) & 1u);
+        }
         if ((flags & kItemLast) && !direct) {
             if (!prior_grid_done) {
                 asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -464,7 +511,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             }
             if (type == (uint32_t)kBlockExact) {
                 // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j; the item names its row groups j
-                const uint32_t rows = (r.y >> 24) & 0xFFu;
+                const uint32_t rows = r.y >> 24;
                 for (int j = 0; j < kRun / 4; ++j)
                     if ((rows >> j) & 1u) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
             } else if (!wrote && A.F.keep_canvas) {
@@ -484,6 +531,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             wrote = false;
             __syncwarp();             // the output block is free again
         }
+        r = rn;
     }
 }
 

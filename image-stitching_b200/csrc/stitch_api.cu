@@ -308,18 +308,22 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
             it.origin_off = (uint32_t)((int)it.y0 * (L->box_we[it.cam] * 4) + 4 * (int)it.c0);
             it.coef = r.coef[l];
             if (L->compact) {
-                // compact kernel (stitch_fast2.cuh): c0 holds the first converted texel column, origin_off the
-                // converted-buffer offset of lane u = 0 / row v = -8 (whole-texel parts), aux the byte steps
-                // per canvas column and row
+                // compact kernel (stitch_fast2.cuh): origin_off holds the converted-buffer offset of lane u = 0 /
+                // row v = -8 (whole-texel parts), aux the byte steps per canvas column and row, flags bits 4-5
+                // where the first converted texel sits in the staged row
                 const int t0 = compact_t0(r.layer[l].x0);
                 const bs::BlockCoef &c = r.coef[l];
                 const int ustep = c.nyu * bs::kConvPitch + c.nxu * 4, vstep = c.nyv * bs::kConvPitch + c.nxv * 4;
                 const long long run_rel = -((long long)it.y0 * bs::kConvPitch + 4LL * t0) +
                                           (((long long)c.iy - bs::kMagicBias) >> 5) * bs::kConvPitch +
                                           (((long long)c.ix - bs::kMagicBias) >> 5) * 4 - (long long)(bs::kRun / 2) * vstep;
-                it.c0 = (int16_t)t0;
                 it.origin_off = (uint32_t)run_rel;
                 it.coef.aux = ((uint32_t)ustep & 0xFFFFu) | ((uint32_t)vstep << 16);
+                it.flags |= (uint8_t)(((3 * t0 - 4 * (int)it.c0) >> 2) << bs::kItemRawOffShift);
+                if (r.layer[l].full && r.layer[l].groups == 0 && nl == 1) {
+                    it.flags |= bs::kItemDirect;
+                    if (!r.layer[l].zero_frac && vstep == bs::kConvPitch) it.flags |= bs::kItemPlain;
+                }
             }
         }
     };

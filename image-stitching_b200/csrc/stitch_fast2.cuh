@@ -15,13 +15,20 @@
 // Replaces the camera loop body /root/reference/tools/stitch/main.cpp:145-152.
 #pragma once
 
+#include <type_traits>
+
 #include "stitch_fast.cuh"
 
 namespace bs {
 
-constexpr int kRawPitch = 128;                           // bytes per staged source row: TMA box of 32 four-byte elements
+#ifndef BS2_RAW_PITCH
+#define BS2_RAW_PITCH 144
+#endif
+constexpr int kRawPitch = BS2_RAW_PITCH;                 // bytes per staged source row: TMA box of 36 four-byte elements.  120 would do;
+                                                         // 144 puts consecutive rows 4 banks apart, so the three rows one conversion
+                                                         // step reads collide in two banks instead of in all of them
 constexpr int kRawRows = 18;                             // rows a box may have
-constexpr int kRawStage = kRawPitch * kRawRows;          // 2304
+constexpr int kRawStage = (kRawPitch * kRawRows + 127) / 128 * 128;   // 2688
 constexpr int kConvGroups = 10;                          // groups of four texels converted per row
 constexpr int kConvTexels = 4 * kConvGroups;             // 40
 constexpr int kConvPitch = 4 * kConvTexels;              // 160 bytes
@@ -153,13 +160,21 @@ struct Taps2 {
     uint32_t t00, t01, t10, t11;   // texels (sx, sy), (sx+1, sy), (sx, sy+1), (sx+1, sy+1) as B G R x
     uint2 wt;
 };
+template <int kImm>
+__device__ __forceinline__ uint32_t lds32_at(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(kImm));
+    return v;
+}
+template <int kOff = 0>
 __device__ __forceinline__ Taps2 fetch_taps2(uint32_t o, uint2 wt)
 {
     Taps2 t;
-    t.t00 = lds32(o);
-    t.t01 = lds32(o + 4);
-    t.t10 = lds32(o + kConvPitch);
-    t.t11 = lds32(o + kConvPitch + 4);
+    t.t00 = lds32_at<kOff>(o);
+    t.t01 = lds32_at<kOff + 4>(o);
+    t.t10 = lds32_at<kOff + kConvPitch>(o);
+    t.t11 = lds32_at<kOff + kConvPitch + 4>(o);
     t.wt = wt;
     return t;
 }
@@ -174,7 +189,7 @@ __device__ __forceinline__ uint32_t blend_taps2(const Taps2 &t)
     const uint32_t bg = __byte_perm(vb, vg, 0x3362);
     return __byte_perm(bg, vr, 0x7610);
 }
-__device__ __forceinline__ uint32_t sample_conv(uint32_t o, uint2 wt) { return blend_taps2(fetch_taps2(o, wt)); }
+__device__ __forceinline__ uint32_t sample_conv(uint32_t o, uint2 wt) { return blend_taps2(fetch_taps2<0>(o, wt)); }
 
 __device__ __forceinline__ void store_px_bytes(uint32_t p8, uint32_t px)
 {
@@ -200,34 +215,58 @@ __device__ __forceinline__ uint2 tap_weights2(uint32_t a, uint32_t b)
     if (w01 == 0x10000u) w01 = 0xFFFFu;
     return make_uint2(w01, w23);
 }
+// For blocks in which the plan found no pixel with a = b = 0: the 2^16 case cannot occur.
+__device__ __forceinline__ uint2 tap_weights2_nz(uint32_t a, uint32_t b)
+{
+    const uint32_t a2 = a * (0xFFFFu * 64u) + 2048u;
+    const uint32_t w23 = b * a2;
+    uint32_t w01;
+    asm("mad.lo.u32 %0, %1, 32, %2;" : "=r"(w01) : "r"(a2), "r"(0u - w23));
+    return make_uint2(w01, w23);
+}
+
+template <int K, int N, typename F>
+__device__ __forceinline__ void static_for(F &&f)
+{
+    if constexpr (K < N) {
+        f(std::integral_constant<int, K>{});
+        static_for<K + 1, N>(f);
+    }
+}
 
 // Hot path: the layer covers every pixel of the block with interior samples and the plan verified the
 // cheap coordinates for the whole block.  `run0` = converted-buffer address of this lane's texel base
 // for row v = -kRun/2 (whole-texel parts only), `vstep` = whole texels per canvas row as a byte offset.
 // kDirect: every row goes straight to the canvas, `gp` = address of this lane's word of the block's
 // first row; otherwise rows are collected in the warp's output block in shared memory.
-template <bool kDirect, bool kConvert>
+// kPlain (with kDirect): no pixel of the block has both fractions 0 and a canvas row advances the source by
+// exactly one converted row, so the weight fix-up is dropped and the row offsets become immediates.
+template <bool kDirect, bool kConvert, bool kPlain>
 __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, int vstep, uint32_t out_blk, int lane,
                                           uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing, uint32_t cv_src,
                                           uint32_t cv_dst)
 {
-    auto fetch = [&](int k) {
+    auto fetch = [&](auto kc) {
+        constexpr int k = decltype(kc)::value;
         int xbits, ybits;
         lane_coord_bits2(lc, (float)(k - kRun / 2), xbits, ybits);
-        return fetch_taps2(tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits),
-                           tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+        if constexpr (kPlain)
+            return fetch_taps2<k * kConvPitch>(tap_addr(run0, xbits, ybits), tap_weights2_nz((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+        else
+            return fetch_taps2<0>(tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits),
+                                  tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
-    Taps2 cur = fetch(0);
+    Taps2 cur = fetch(std::integral_constant<int, 0>{});
     ConvWords cw;
-#pragma unroll
-    for (int k = 0; k < kRun; ++k) {
+    static_for<0, kRun>([&](auto kc) {
+        constexpr int k = decltype(kc)::value;
         Taps2 nxt = cur;
-        if (k + 1 < kRun) nxt = fetch(k + 1);
+        if constexpr (k + 1 < kRun) nxt = fetch(std::integral_constant<int, k + 1>{});
         // kConvert: the next item's box is rewritten on the side, one step per two pixel rows, so that
         // its shared-memory round trips hide behind the pixel arithmetic
-        if (kConvert && k < 2 * kConvSteps && (k & 1) == 0) cw = conv_load(cv_src + (uint32_t)((k / 2) * 3 * kRawPitch));
+        if constexpr (kConvert && k < 2 * kConvSteps && (k & 1) == 0) cw = conv_load(cv_src + (uint32_t)((k / 2) * 3 * kRawPitch));
         const uint32_t px = blend_taps2(cur);
-        if (kDirect) {
+        if constexpr (kDirect) {
             // this lane's word of the row, then on to the next row: the canvas does not straddle a 4 GB
             // boundary (the host checks), so only the low half of the address advances, in place
             const uint32_t nb = __shfl_down_sync(0xffffffffu, px, 1);
@@ -248,9 +287,9 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
         } else {
             store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
         }
-        if (kConvert && k < 2 * kConvSteps && (k & 1) == 1) conv_store(cv_dst + (uint32_t)((k / 2) * 3 * kConvPitch), cw);
+        if constexpr (kConvert && k < 2 * kConvSteps && (k & 1) == 1) conv_store(cv_dst + (uint32_t)((k / 2) * 3 * kConvPitch), cw);
         cur = nxt;
-    }
+    });
 }
 
 // Partially covered layer whose cheap coordinates hold everywhere: coverage test and byte stores per pixel.
@@ -371,18 +410,18 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                      : "memory");
     };
     // source box of the item whose header words are `r` -> raw stage; items without a box just arrive
+    const uint64_t tmap0 = reinterpret_cast<uint64_t>(&A.tmap[0]);
+    static_assert(sizeof(CUtensorMap) == 128, "tensor map stride");
     auto issue_box = [&](const uint4 &r, uint32_t stage) {
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
             const uint32_t cam = (r.y >> 16) & 0xFFu;
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(dbar0 + 8 * stage),
                          "r"((uint32_t)A.box_bytes)
                          : "memory");
-            // the box starts at the 16-byte aligned element at or before the first converted texel column
-            const int c0 = (int)(((3u * (r.z & 0xFFFFu)) >> 4) << 2);
             asm volatile(
                 "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
                     raw0 + stage * (uint32_t)kRawStage),
-                "l"(&A.tmap[cam]), "r"(c0), "r"((int)(int16_t)(r.z >> 16)), "r"(dbar0 + 8 * stage)
+                "l"(tmap0 + 128ull * cam), "r"((int)(int16_t)(r.z & 0xFFFFu)), "r"((int)(int16_t)(r.z >> 16)), "r"(dbar0 + 8 * stage)
                 : "memory");
         } else {
             mbar_arrive_addr(dbar0 + 8 * stage);
@@ -398,10 +437,16 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t cv_dst_lane = (slot / kConvGroups) * kConvPitch + 16 * (slot % kConvGroups);
     auto box_landed_wait = [&](int m) { mbar_wait_addr(dbar0 + 8 * ((uint32_t)m & 1u), ((uint32_t)m >> 1) & 1u); };
     auto box_landed_try = [&](int m) { return mbar_try_wait_addr(dbar0 + 8 * ((uint32_t)m & 1u), ((uint32_t)m >> 1) & 1u); };
-    auto cv_src_of = [&](int m, uint32_t hdr_z) {      // first converted texel column t0: its byte offset in the staged row is 3 t0 mod 16
-        return raw0 + ((uint32_t)m & 1u) * (uint32_t)kRawStage + cv_src_lane + ((3u * (hdr_z & 0xFFFFu)) & 15u);
+    auto cv_src_of = [&](int m, uint32_t hdr_y) {      // flags bits 4-5: where the first converted texel sits in the staged row
+        return raw0 + ((uint32_t)m & 1u) * (uint32_t)kRawStage + cv_src_lane + ((hdr_y >> (8 + kItemRawOffShift - 2)) & 12u);
     };
     auto cv_dst_of = [&](int m) { return conv0 + ((uint32_t)m & 1u) * (uint32_t)kConvRegion + cv_dst_lane; };
+    // address texel (0, 0) of an item's camera would have in its converted buffer (rare paths only)
+    auto conv_origin_of = [&](uint32_t conv, const uint4 &h) {
+        const int c0 = (int)(int16_t)(h.z & 0xFFFFu), y0 = (int)(int16_t)(h.z >> 16);
+        const int t0 = (4 * c0 + (int)((h.y >> (8 + kItemRawOffShift - 2)) & 12u)) / 3;
+        return conv - (uint32_t)(y0 * kConvPitch + t0 * 4);
+    };
 
     if (lane == 0) {
         request_records(0);
@@ -419,12 +464,14 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if (cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
     }
     __syncwarp();
-    uint4 r = lds128(rec_addr(0));    // header of the current item
     // Item pipeline: at the top of iteration n the box of item n is already rewritten in converted buffer n & 1,
     // the box of item n+1 is landing in (or has reached) raw stage (n+1) & 1, the box of item n+2 is in flight.
-    if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
-        box_landed_wait(0);
-        convert_box(cv_src_of(0, r.z), cv_dst_of(0));
+    {
+        const uint4 r = lds128(rec_addr(0));
+        if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
+            box_landed_wait(0);
+            convert_box(cv_src_of(0, r.y), cv_dst_of(0));
+        }
     }
     __syncwarp();
     if (cnt > 2) {
@@ -437,27 +484,33 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t storing = (uint32_t)((lane & 3) != 3);
     const int u = lane - kBlockW / 2;
     const float uf = (float)u;
-    const uint32_t lane_goff = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
+    // this lane's word of canvas row 0, block column 0; a block adds by * 16 * pitch + bx * 96 (32-bit: direct
+    // stores need the canvas inside one 4 GB window anyway)
+    const uint64_t gbase = reinterpret_cast<uint64_t>(A.F.canvas) + 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
+    const uint32_t cpitch = (uint32_t)A.F.cpitch, brow = cpitch * kBlockH;
     bool wrote = false;               // some layer has written into the current block
+    bool can_direct = prior_grid_done && A.F.canvas_in_4g;
     for (int n = 0; n < cnt; ++n) {
         if (lane == 0 && ((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt)
             request_records(n + (int)rec_half);      // the half items n-8 .. n-1 used is free: refill it with n+8 .. n+15
+        // the record ring is read up to three items ahead: make the next half visible when item n+3 is its first
+        if (n + 3 < cnt) wait_half_of(n + 3);
         // item header (layout_plan, compact form): bx | by << 16, type | flags << 8 | cam << 16 | groups << 24,
-        // t0 | y0 << 16 (first converted texel column, first box row), run base of lane u = 0 in the converted buffer
+        // c0 | y0 << 16 (TMA coordinates of the box), run base of lane u = 0 in the converted buffer
         const uint32_t ra = rec_addr(n);
+        const uint4 r = lds128(ra);
         const uint32_t conv = conv0 + ((uint32_t)n & 1u) * (uint32_t)kConvRegion;
         bool direct = false;
-        const int tx0 = (int)(r.x & 0xFFFFu) * kBlockW, ty0 = (int)(r.x >> 16) * kBlockH;
+        const uint32_t bx = r.x & 0xFFFFu, by = r.x >> 16;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
-        // the next item: does it have a box to rewrite, and has that box landed already?
-        uint4 rn = r;
-        bool next_box = false, next_done = true;
+        // the next item: does it have a box to rewrite?
+        uint32_t rn_y = 0;
+        bool next_box = false;
         if (n + 1 < cnt) {
-            wait_half_of(n + 1);
-            rn = lds128(rec_addr(n + 1));
-            next_box = (rn.y & 0xFFu) == (uint32_t)kBlockFast;
-            next_done = !next_box;
+            rn_y = lds32(rec_addr(n + 1) + 4);
+            next_box = (rn_y & 0xFFu) == (uint32_t)kBlockFast;
         }
+        bool next_done = !next_box;
         if (type == (uint32_t)kBlockFast) {
             const BlockCoef bc = load_block_coef(ra);
             const LaneCoef2 lc = lane_coef2(bc, uf);
@@ -465,49 +518,49 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             const uint32_t run0 = conv + r.w + (uint32_t)(u * ustep);
             const uint32_t groups = r.y >> 24;
             if (flags & kItemFull) {
-                direct = groups == 0u && prior_grid_done && A.F.canvas_in_4g &&
-                         (flags & (kItemFirst | kItemLast)) == (kItemFirst | kItemLast);
-                const uint64_t grow = reinterpret_cast<uint64_t>(A.F.canvas + (long long)ty0 * A.F.cpitch + (long long)tx0 * 3 + lane_goff);
+                direct = can_direct && (flags & kItemDirect);
+                const uint64_t grow = gbase + (by * brow + bx * (uint32_t)kBlockRowBytes);
                 if (direct && next_box && __all_sync(0xffffffffu, box_landed_try(n + 1))) {
-                    run_full2<true, true>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing,
-                                          cv_src_of(n + 1, rn.z), cv_dst_of(n + 1));
+                    if (flags & kItemPlain)
+                        run_full2<true, true, true>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, cv_src_of(n + 1, rn_y),
+                                                    cv_dst_of(n + 1));
+                    else
+                        run_full2<true, true, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, cv_src_of(n + 1, rn_y),
+                                                     cv_dst_of(n + 1));
                     next_done = true;
                 } else if (direct) {
-                    run_full2<true, false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing, 0u, 0u);
+                    run_full2<true, false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
                 } else {
-                    run_full2<false, false>(lc, run0, vstep, out_blk, lane, grow, (uint32_t)A.F.cpitch, sel, storing, 0u, 0u);
+                    run_full2<false, false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
                 }
                 if (groups != 0u) {
                     __syncwarp();
-                    const uint32_t conv_origin = conv - (uint32_t)((int)(int16_t)(r.z >> 16) * kConvPitch + (int)(r.z & 0xFFFFu) * 4);
-                    patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin, out_blk, groups, tx0 + lane, ty0, lane);
+                    patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane,
+                                 (int)by * kBlockH, lane);
                 }
             } else {
                 const CamDev &cam = A.F.cam[(r.y >> 16) & 0xFFu];
                 const LaneBase2 lb = lane_base2(bc, u);
-                if (groups == 0u) {
+                const int tx0 = (int)bx * kBlockW, ty0 = (int)by * kBlockH;
+                if (groups == 0u)
                     run_masked2(lc, lb, run0, vstep, out_blk, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
-                } else {
-                    // address texel (0, 0) of this camera would have in the converted buffer
-                    const uint32_t conv_origin = conv - (uint32_t)((int)(int16_t)(r.z >> 16) * kConvPitch + (int)(r.z & 0xFFFFu) * 4);
-                    run_general2(A.F, cam, lc, lb, conv_origin, out_blk, groups, !wrote, tx0 + lane, ty0, lane);
-                }
+                else
+                    run_general2(A.F, cam, lc, lb, conv_origin_of(conv, r), out_blk, groups, !wrote, tx0 + lane, ty0, lane);
             }
             wrote = !direct;
         }
         if (!next_done) {             // not rewritten on the side: do it now
             box_landed_wait(n + 1);
-            convert_box(cv_src_of(n + 1, rn.z), cv_dst_of(n + 1));
+            convert_box(cv_src_of(n + 1, rn_y), cv_dst_of(n + 1));
         }
         __syncwarp();                 // every lane is done with converted buffer n & 1 and with raw stage (n+1) & 1
-        if (n + 3 < cnt) {            // that raw stage takes the box of item n+3
-            wait_half_of(n + 3);
-            if (lane == 0) issue_box(lds128(rec_addr(n + 3)), ((uint32_t)n + 1u) & 1u);
-        }
+        if (n + 3 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 3)), ((uint32_t)n + 1u) & 1u);   // that raw stage takes the box of item n+3
         if ((flags & kItemLast) && !direct) {
+            const int tx0 = (int)bx * kBlockW, ty0 = (int)by * kBlockH;
             if (!prior_grid_done) {
                 asm volatile("griddepcontrol.wait;" ::: "memory");
                 prior_grid_done = true;
+                can_direct = A.F.canvas_in_4g != 0;
             }
             if (type == (uint32_t)kBlockExact) {
                 // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j; the item names its row groups j
@@ -531,7 +584,6 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             wrote = false;
             __syncwarp();             // the output block is free again
         }
-        r = rn;
     }
 }
 

@@ -52,7 +52,7 @@ struct BlockRec {                  // 160 bytes
         uint8_t cam;
         uint8_t full;              // writes every pixel of the block and the block lies inside the canvas
         uint8_t groups;            // bit g: rows 4g..4g+3 of the block must use exact coordinates
-        uint8_t pad;
+        uint8_t zero_frac;         // some pixel it writes has both fractions 0 (its top-left weight is 2^15: see tap_weights)
     } layer[kMaxLayers];
     BlockCoef coef[kMaxLayers];
 };
@@ -72,6 +72,12 @@ struct WorkItem {
 };
 static_assert(sizeof(WorkItem) == 80, "WorkItem layout");
 constexpr uint8_t kItemFirst = 1, kItemLast = 2, kItemFull = 4;
+// compact kernel only (stitch_fast2.cuh): kItemDirect = single full layer without flagged groups (its rows may go
+// straight to the canvas); kItemPlain = kItemDirect, no pixel with both fractions 0, and one source row per
+// canvas row (the hot loop's leanest variant); bits 4-5 = (byte offset of the first converted texel in the
+// staged row) / 4
+constexpr uint8_t kItemDirect = 8, kItemPlain = 0x40;
+constexpr int kItemRawOffShift = 4;
 
 // ---- cheap coordinates ---------------------------------------------------------------------------
 // For camera map M the 1/32-pixel source coordinate of canvas pixel (x, y) is g(x, y) = 32 N / W
@@ -243,6 +249,7 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
         m &= m - 1;
         int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN;
         bool all_in = (x < P.W) && (y0 + kRun <= P.H);
+        bool zf = false;
         unsigned mism = 0u;
         const BlockCoef bc = block_coef(P.M[c], bx * kBlockW + kBlockW / 2, y0 + kRun / 2);
         rec.coef[l] = bc;
@@ -258,6 +265,7 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
                 if (X != xbits + lc.bx + 32 * lc.nxv * v || Y != ybits + lc.by + 32 * lc.nyv * v) mism |= 1u << (k >> 2);
                 if (cover_class(X, Y, P.w[c], P.h[c], 1) == 1) {   // interior only
                     const int sx = X >> kFracBits, sy = Y >> kFracBits;
+                    zf = zf || ((X | Y) & (kFracOne - 1)) == 0;
                     bx0 = min(bx0, sx);
                     by0 = min(by0, sy);
                     bx1 = max(bx1, sx + 1);
@@ -280,6 +288,7 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
         rec.layer[l].cam = (uint8_t)c;
         rec.layer[l].full = all_in ? 1 : 0;
         rec.layer[l].groups = (uint8_t)mism;
+        rec.layer[l].zero_frac = __any_sync(FULLMASK, zf) ? 1 : 0;
     }
     if (lane == 0) *dst = rec;
 }

@@ -145,6 +145,12 @@ __device__ __forceinline__ void conv_store(uint32_t d, const ConvWords &c)
     sts128(d, c.w0, __byte_perm(c.w0, c.w1, 0x6543), __byte_perm(c.w1, c.w2, 0x5432), c.w2 >> 8);
 }
 constexpr int kConvSteps = kRawRows / 3;
+#ifndef BS2_ROWS_PER_PASS
+#define BS2_ROWS_PER_PASS 8
+#endif
+constexpr int kRowsPerPass = BS2_ROWS_PER_PASS;                          // rows of the hot loop's unrolled body
+constexpr int kConvStepsPerPass = kConvSteps * kRowsPerPass / kRun;      // conversion steps done on the side per pass
+static_assert(kRun % kRowsPerPass == 0 && kConvSteps * kRowsPerPass % kRun == 0 && 2 * kConvStepsPerPass <= kRowsPerPass, "pass shape");
 // `src`: this lane's first raw word (row slot/10 of the stage, texel group slot%10, slot = min(lane, 29):
 // lanes 30 and 31 repeat the work of 28 and 29), `dst`: its first converted word.  Six steps of three rows.
 __device__ __forceinline__ void convert_box(uint32_t src, uint32_t dst)
@@ -246,50 +252,73 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
                                           uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing, uint32_t cv_src,
                                           uint32_t cv_dst)
 {
-    auto fetch = [&](auto kc) {
-        constexpr int k = decltype(kc)::value;
+    // The 16 rows run as kRun / kRowsPerPass passes of an unrolled body: the whole unrolled loop (10 KB of code
+    // per variant) did not stay in the instruction cache with four warps per scheduler at different places in it.
+    float vf = (float)(-kRun / 2);          // row offset v of the pixel being fetched: -8, -7, ... (exact in fp32)
+    uint32_t rbase = run0;                  // converted-buffer base of the current pass
+    auto fetch = [&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        const uint64_t v2 = pack2(vf, vf);
+        const uint64_t sxy = fma2(v2, fma2(v2, lc.a2, lc.a1), lc.a0);
         int xbits, ybits;
-        lane_coord_bits2(lc, (float)(k - kRun / 2), xbits, ybits);
+        unpack2(add2(sxy, pack2(12582912.0f, 12582912.0f)), xbits, ybits);
+        vf += 1.0f;
         if constexpr (kPlain)
-            return fetch_taps2<k * kConvPitch>(tap_addr(run0, xbits, ybits), tap_weights2_nz((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+            return fetch_taps2<j * kConvPitch>(tap_addr(rbase, xbits, ybits), tap_weights2_nz((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
         else
-            return fetch_taps2<0>(tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits),
+            return fetch_taps2<0>(tap_addr(rbase + (uint32_t)(j * vstep), xbits, ybits),
                                   tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     Taps2 cur = fetch(std::integral_constant<int, 0>{});
     ConvWords cw;
-    static_for<0, kRun>([&](auto kc) {
-        constexpr int k = decltype(kc)::value;
-        Taps2 nxt = cur;
-        if constexpr (k + 1 < kRun) nxt = fetch(std::integral_constant<int, k + 1>{});
-        // kConvert: the next item's box is rewritten on the side, one step per two pixel rows, so that
-        // its shared-memory round trips hide behind the pixel arithmetic
-        if constexpr (kConvert && k < 2 * kConvSteps && (k & 1) == 0) cw = conv_load(cv_src + (uint32_t)((k / 2) * 3 * kRawPitch));
-        const uint32_t px = blend_taps2(cur);
-        if constexpr (kDirect) {
-            // this lane's word of the row, then on to the next row: the canvas does not straddle a 4 GB
-            // boundary (the host checks), so only the low half of the address advances, in place
-            const uint32_t nb = __shfl_down_sync(0xffffffffu, px, 1);
-            const uint32_t word = __byte_perm(px, nb, sel);
-            asm volatile(
-                "{\n"
-                ".reg .pred p;\n"
-                ".reg .b32 lo, hi;\n"
-                "setp.ne.u32 p, %2, 0;\n"
-                "@p st.global.u32 [%0], %1;\n"
-                "mov.b64 {lo, hi}, %0;\n"
-                "add.u32 lo, lo, %3;\n"
-                "mov.b64 %0, {lo, hi};\n"
-                "}"
-                : "+l"(gp)
-                : "r"(word), "r"(storing), "r"(cpitch)
-                : "memory");
-        } else {
-            store_row_pixel(px, out_blk + (uint32_t)(k * kBlockRowBytes), lane, sel);
+#pragma unroll 1
+    for (int pass = 0; pass < kRun / kRowsPerPass; ++pass) {
+        const bool last_pass = pass == kRun / kRowsPerPass - 1;
+        static_for<0, kRowsPerPass>([&](auto jc) {
+            constexpr int j = decltype(jc)::value;
+            Taps2 nxt = cur;
+            if constexpr (j + 1 < kRowsPerPass) {
+                nxt = fetch(std::integral_constant<int, j + 1>{});
+            } else {
+                // first pixel of the next pass (not needed after the last one; fetched anyway from a valid
+                // address to keep the body branch-free is not possible here: rows beyond the box may not exist)
+                rbase += (uint32_t)(kRowsPerPass * (kPlain ? kConvPitch : vstep));
+                if (!last_pass) nxt = fetch(std::integral_constant<int, 0>{});
+            }
+            // kConvert: the next item's box is rewritten on the side, one step per two pixel rows, so that
+            // its shared-memory round trips hide behind the pixel arithmetic
+            if constexpr (kConvert && j < 2 * kConvStepsPerPass && (j & 1) == 0) cw = conv_load(cv_src + (uint32_t)((j / 2) * 3 * kRawPitch));
+            const uint32_t px = blend_taps2(cur);
+            if constexpr (kDirect) {
+                // this lane's word of the row, then on to the next row: the canvas does not straddle a 4 GB
+                // boundary (the host checks), so only the low half of the address advances, in place
+                const uint32_t nb = __shfl_down_sync(0xffffffffu, px, 1);
+                const uint32_t word = __byte_perm(px, nb, sel);
+                asm volatile(
+                    "{\n"
+                    ".reg .pred p;\n"
+                    ".reg .b32 lo, hi;\n"
+                    "setp.ne.u32 p, %2, 0;\n"
+                    "@p st.global.u32 [%0], %1;\n"
+                    "mov.b64 {lo, hi}, %0;\n"
+                    "add.u32 lo, lo, %3;\n"
+                    "mov.b64 %0, {lo, hi};\n"
+                    "}"
+                    : "+l"(gp)
+                    : "r"(word), "r"(storing), "r"(cpitch)
+                    : "memory");
+            } else {
+                store_row_pixel(px, out_blk + (uint32_t)(j * kBlockRowBytes), lane, sel);
+            }
+            if constexpr (kConvert && j < 2 * kConvStepsPerPass && (j & 1) == 1) conv_store(cv_dst + (uint32_t)((j / 2) * 3 * kConvPitch), cw);
+            cur = nxt;
+        });
+        if constexpr (!kDirect) out_blk += kRowsPerPass * kBlockRowBytes;
+        if constexpr (kConvert) {
+            cv_src += kConvStepsPerPass * 3 * kRawPitch;
+            cv_dst += kConvStepsPerPass * 3 * kConvPitch;
         }
-        if constexpr (kConvert && k < 2 * kConvSteps && (k & 1) == 1) conv_store(cv_dst + (uint32_t)((k / 2) * 3 * kConvPitch), cw);
-        cur = nxt;
-    });
+    }
 }
 
 // Partially covered layer whose cheap coordinates hold everywhere: coverage test and byte stores per pixel.

@@ -29,9 +29,18 @@ constexpr int kRawPitch = BS2_RAW_PITCH;                 // bytes per staged sou
                                                          // step reads collide in two banks instead of in all of them
 constexpr int kRawRows = 18;                             // rows a box may have
 constexpr int kRawStage = (kRawPitch * kRawRows + 127) / 128 * 128;   // 2688
+#ifndef BS2_CONV_PITCH
+#define BS2_CONV_PITCH 160
+#endif
+#ifndef BS2_CONV_BUFFERS
+#define BS2_CONV_BUFFERS 2
+#endif
 constexpr int kConvGroups = 10;                          // groups of four texels converted per row
 constexpr int kConvTexels = 4 * kConvGroups;             // 40
-constexpr int kConvPitch = 4 * kConvTexels;              // 160 bytes
+constexpr int kConvPitch = BS2_CONV_PITCH;               // bytes per converted row: 160 = the 40 texels; 256 keeps every row on the same
+                                                         // banks, so lanes whose taps straddle two rows do not collide
+constexpr bool kTwoConv = BS2_CONV_BUFFERS == 2;         // two converted buffers: the next box is rewritten inside the hot loop
+static_assert(kConvPitch >= 4 * kConvTexels && kConvPitch % 32 == 0, "converted row pitch");
 constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
 #ifndef BS2_RAW_STAGES
 #define BS2_RAW_STAGES 2
@@ -41,7 +50,7 @@ constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
 #endif
 constexpr int kRawStages = BS2_RAW_STAGES;               // boxes in flight ahead of the one being converted
 constexpr int kRec2Slots = BS2_REC_SLOTS;                // record ring slots per warp (two halves)
-constexpr int kWarp2Smem = kRawStages * kRawStage + 2 * kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
+constexpr int kWarp2Smem = kRawStages * kRawStage + BS2_CONV_BUFFERS * kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
 static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
 static_assert(kRawStages == 2, "the item pipeline is written for two raw stages");
 
@@ -146,7 +155,7 @@ __device__ __forceinline__ void conv_store(uint32_t d, const ConvWords &c)
 }
 constexpr int kConvSteps = kRawRows / 3;
 #ifndef BS2_ROWS_PER_PASS
-#define BS2_ROWS_PER_PASS 8
+#define BS2_ROWS_PER_PASS 16
 #endif
 constexpr int kRowsPerPass = BS2_ROWS_PER_PASS;                          // rows of the hot loop's unrolled body
 constexpr int kConvStepsPerPass = kConvSteps * kRowsPerPass / kRun;      // conversion steps done on the side per pass
@@ -407,7 +416,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const int warp = tid >> 5, lane = tid & 31;
     const uint32_t raw0 = raw_base + (uint32_t)(warp * kWarp2Smem);           // 128-byte aligned
     const uint32_t conv0 = raw0 + kRawStages * kRawStage;
-    const uint32_t out_blk = conv0 + 2 * kConvRegion;
+    const uint32_t out_blk = conv0 + BS2_CONV_BUFFERS * kConvRegion;
     const uint32_t rec0 = out_blk + kWarpOutBytes;
     constexpr uint32_t rec_slots = kRec2Slots, rec_half = kRec2Slots / 2;
     const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per raw stage
@@ -469,7 +478,8 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     auto cv_src_of = [&](int m, uint32_t hdr_y) {      // flags bits 4-5: where the first converted texel sits in the staged row
         return raw0 + ((uint32_t)m & 1u) * (uint32_t)kRawStage + cv_src_lane + ((hdr_y >> (8 + kItemRawOffShift - 2)) & 12u);
     };
-    auto cv_dst_of = [&](int m) { return conv0 + ((uint32_t)m & 1u) * (uint32_t)kConvRegion + cv_dst_lane; };
+    auto conv_of = [&](int m) { return conv0 + (kTwoConv ? ((uint32_t)m & 1u) * (uint32_t)kConvRegion : 0u); };
+    auto cv_dst_of = [&](int m) { return conv_of(m) + cv_dst_lane; };
     // address texel (0, 0) of an item's camera would have in its converted buffer (rare paths only)
     auto conv_origin_of = [&](uint32_t conv, const uint4 &h) {
         const int c0 = (int)(int16_t)(h.z & 0xFFFFu), y0 = (int)(int16_t)(h.z >> 16);
@@ -495,17 +505,18 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     __syncwarp();
     // Item pipeline: at the top of iteration n the box of item n is already rewritten in converted buffer n & 1,
     // the box of item n+1 is landing in (or has reached) raw stage (n+1) & 1, the box of item n+2 is in flight.
-    {
+    // (With a single converted buffer every item rewrites its own box at the top of its iteration instead.)
+    if (kTwoConv) {
         const uint4 r = lds128(rec_addr(0));
         if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
             box_landed_wait(0);
             convert_box(cv_src_of(0, r.y), cv_dst_of(0));
         }
-    }
-    __syncwarp();
-    if (cnt > 2) {
-        if (lane == 0) issue_box(lds128(rec_addr(2)), 0u);      // records 0 .. 7 are all there
         __syncwarp();
+        if (cnt > 2) {
+            if (lane == 0) issue_box(lds128(rec_addr(2)), 0u);      // records 0 .. 7 are all there
+            __syncwarp();
+        }
     }
 
     // lane constants: output word merge (store_row_pixel), column offsets
@@ -528,18 +539,26 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         // c0 | y0 << 16 (TMA coordinates of the box), run base of lane u = 0 in the converted buffer
         const uint32_t ra = rec_addr(n);
         const uint4 r = lds128(ra);
-        const uint32_t conv = conv0 + ((uint32_t)n & 1u) * (uint32_t)kConvRegion;
+        const uint32_t conv = conv_of(n);
         bool direct = false;
         const uint32_t bx = r.x & 0xFFFFu, by = r.x >> 16;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
         // the next item: does it have a box to rewrite?
         uint32_t rn_y = 0;
         bool next_box = false;
-        if (n + 1 < cnt) {
+        if (kTwoConv && n + 1 < cnt) {
             rn_y = lds32(rec_addr(n + 1) + 4);
             next_box = (rn_y & 0xFFu) == (uint32_t)kBlockFast;
         }
         bool next_done = !next_box;
+        if (!kTwoConv) {
+            if (type == (uint32_t)kBlockFast) {
+                box_landed_wait(n);
+                convert_box(cv_src_of(n, r.y), cv_dst_of(n));
+            }
+            __syncwarp();             // converted box complete; its raw stage takes the box of item n+2
+            if (n + 2 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 2)), (uint32_t)n & 1u);
+        }
         if (type == (uint32_t)kBlockFast) {
             const BlockCoef bc = load_block_coef(ra);
             const LaneCoef2 lc = lane_coef2(bc, uf);
@@ -583,7 +602,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             convert_box(cv_src_of(n + 1, rn_y), cv_dst_of(n + 1));
         }
         __syncwarp();                 // every lane is done with converted buffer n & 1 and with raw stage (n+1) & 1
-        if (n + 3 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 3)), ((uint32_t)n + 1u) & 1u);   // that raw stage takes the box of item n+3
+        if (kTwoConv && n + 3 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 3)), ((uint32_t)n + 1u) & 1u);   // that raw stage takes the box of item n+3
         if ((flags & kItemLast) && !direct) {
             const int tx0 = (int)bx * kBlockW, ty0 = (int)by * kBlockH;
             if (!prior_grid_done) {

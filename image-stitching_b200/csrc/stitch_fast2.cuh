@@ -33,7 +33,7 @@ constexpr int kRawStage = (kRawPitch * kRawRows + 127) / 128 * 128;   // 2688
 #define BS2_CONV_PITCH 160
 #endif
 #ifndef BS2_CONV_BUFFERS
-#define BS2_CONV_BUFFERS 2
+#define BS2_CONV_BUFFERS 1
 #endif
 constexpr int kConvGroups = 10;                          // groups of four texels converted per row
 constexpr int kConvTexels = 4 * kConvGroups;             // 40

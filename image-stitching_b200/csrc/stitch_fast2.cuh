@@ -576,6 +576,8 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                         run_full2<true, true, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, cv_src_of(n + 1, rn_y),
                                                      cv_dst_of(n + 1));
                     next_done = true;
+                } else if (direct && (flags & kItemPlain)) {
+                    run_full2<true, false, true>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
                 } else if (direct) {
                     run_full2<true, false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
                 } else {

@@ -9,9 +9,11 @@
 //     (no alignment shifts, no third word), pairs them with four PRMT and blends with six dp2a;
 //   * the x and y coordinate polynomials are evaluated together with the packed fp32 instructions
 //     of sm_100 (fma.rn.f32x2 / add.rn.f32x2): 3 instructions per pixel instead of 6;
-//   * two raw stages + two converted buffers: while item n is blended from one converted buffer the
-//     box of item n+1 is rewritten into the other, its loads and stores spread between the pixel
-//     instructions of the hot loop, and the boxes of items n+2 and n+3 are in flight.
+//   * two raw stages + one converted buffer: the boxes of items n+1 and n+2 are in flight while item n
+//     is rewritten and blended;
+//   * blocks in which no pixel has both fractions 0 and whose source advances one row per canvas row
+//     (the plan marks them) run a variant of the hot loop without the 2^16 weight fix-up and with the
+//     row offsets as immediates.
 // Replaces the camera loop body /root/reference/tools/stitch/main.cpp:145-152.
 #pragma once
 
@@ -32,14 +34,10 @@ constexpr int kRawStage = (kRawPitch * kRawRows + 127) / 128 * 128;   // 2688
 #ifndef BS2_CONV_PITCH
 #define BS2_CONV_PITCH 160
 #endif
-#ifndef BS2_CONV_BUFFERS
-#define BS2_CONV_BUFFERS 1
-#endif
 constexpr int kConvGroups = 10;                          // groups of four texels converted per row
 constexpr int kConvTexels = 4 * kConvGroups;             // 40
 constexpr int kConvPitch = BS2_CONV_PITCH;               // bytes per converted row: 160 = the 40 texels; 256 keeps every row on the same
                                                          // banks, so lanes whose taps straddle two rows do not collide
-constexpr bool kTwoConv = BS2_CONV_BUFFERS == 2;         // two converted buffers: the next box is rewritten inside the hot loop
 static_assert(kConvPitch >= 4 * kConvTexels && kConvPitch % 32 == 0, "converted row pitch");
 constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
 #ifndef BS2_RAW_STAGES
@@ -50,7 +48,7 @@ constexpr int kConvRegion = (kConvPitch * kRawRows + 127) / 128 * 128;   // 2944
 #endif
 constexpr int kRawStages = BS2_RAW_STAGES;               // boxes in flight ahead of the one being converted
 constexpr int kRec2Slots = BS2_REC_SLOTS;                // record ring slots per warp (two halves)
-constexpr int kWarp2Smem = kRawStages * kRawStage + BS2_CONV_BUFFERS * kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
+constexpr int kWarp2Smem = kRawStages * kRawStage + kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
 static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
 static_assert(kRawStages == 2, "the item pipeline is written for two raw stages");
 
@@ -158,8 +156,7 @@ constexpr int kConvSteps = kRawRows / 3;
 #define BS2_ROWS_PER_PASS 16
 #endif
 constexpr int kRowsPerPass = BS2_ROWS_PER_PASS;                          // rows of the hot loop's unrolled body
-constexpr int kConvStepsPerPass = kConvSteps * kRowsPerPass / kRun;      // conversion steps done on the side per pass
-static_assert(kRun % kRowsPerPass == 0 && kConvSteps * kRowsPerPass % kRun == 0 && 2 * kConvStepsPerPass <= kRowsPerPass, "pass shape");
+static_assert(kRun % kRowsPerPass == 0, "pass shape");
 // `src`: this lane's first raw word (row slot/10 of the stage, texel group slot%10, slot = min(lane, 29):
 // lanes 30 and 31 repeat the work of 28 and 29), `dst`: its first converted word.  Six steps of three rows.
 __device__ __forceinline__ void convert_box(uint32_t src, uint32_t dst)
@@ -256,13 +253,12 @@ __device__ __forceinline__ void static_for(F &&f)
 // first row; otherwise rows are collected in the warp's output block in shared memory.
 // kPlain (with kDirect): no pixel of the block has both fractions 0 and a canvas row advances the source by
 // exactly one converted row, so the weight fix-up is dropped and the row offsets become immediates.
-template <bool kDirect, bool kConvert, bool kPlain>
+template <bool kDirect, bool kPlain>
 __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, int vstep, uint32_t out_blk, int lane,
-                                          uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing, uint32_t cv_src,
-                                          uint32_t cv_dst)
+                                          uint64_t gp, uint32_t cpitch, uint32_t sel, uint32_t storing)
 {
-    // The 16 rows run as kRun / kRowsPerPass passes of an unrolled body: the whole unrolled loop (10 KB of code
-    // per variant) did not stay in the instruction cache with four warps per scheduler at different places in it.
+    // The 16 rows run as kRun / kRowsPerPass passes of an unrolled body (one pass by default: two passes of
+    // eight rows halve the code, but cost four more instructions per row and were 7 % slower).
     float vf = (float)(-kRun / 2);          // row offset v of the pixel being fetched: -8, -7, ... (exact in fp32)
     uint32_t rbase = run0;                  // converted-buffer base of the current pass
     auto fetch = [&](auto jc) {
@@ -279,7 +275,6 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
                                   tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     Taps2 cur = fetch(std::integral_constant<int, 0>{});
-    ConvWords cw;
 #pragma unroll 1
     for (int pass = 0; pass < kRun / kRowsPerPass; ++pass) {
         const bool last_pass = pass == kRun / kRowsPerPass - 1;
@@ -294,9 +289,6 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
                 rbase += (uint32_t)(kRowsPerPass * (kPlain ? kConvPitch : vstep));
                 if (!last_pass) nxt = fetch(std::integral_constant<int, 0>{});
             }
-            // kConvert: the next item's box is rewritten on the side, one step per two pixel rows, so that
-            // its shared-memory round trips hide behind the pixel arithmetic
-            if constexpr (kConvert && j < 2 * kConvStepsPerPass && (j & 1) == 0) cw = conv_load(cv_src + (uint32_t)((j / 2) * 3 * kRawPitch));
             const uint32_t px = blend_taps2(cur);
             if constexpr (kDirect) {
                 // this lane's word of the row, then on to the next row: the canvas does not straddle a 4 GB
@@ -319,14 +311,9 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
             } else {
                 store_row_pixel(px, out_blk + (uint32_t)(j * kBlockRowBytes), lane, sel);
             }
-            if constexpr (kConvert && j < 2 * kConvStepsPerPass && (j & 1) == 1) conv_store(cv_dst + (uint32_t)((j / 2) * 3 * kConvPitch), cw);
             cur = nxt;
         });
         if constexpr (!kDirect) out_blk += kRowsPerPass * kBlockRowBytes;
-        if constexpr (kConvert) {
-            cv_src += kConvStepsPerPass * 3 * kRawPitch;
-            cv_dst += kConvStepsPerPass * 3 * kConvPitch;
-        }
     }
 }
 
@@ -409,14 +396,13 @@ __device__ __noinline__ void patch_exact2(const FrameArgs &F, const CamDev &cam,
 __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kernel(const __grid_constant__ Fast2Args A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
-    // layout: [pad to a 128-byte boundary][per warp: raw stage 0 | raw stage 1 | converted box 0 | converted box 1 |
-    //          output block | records | mbarriers]
+    // layout: [pad to a 128-byte boundary][per warp: raw stage 0 | raw stage 1 | converted box | output block | records | mbarriers]
     const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     const uint32_t raw0 = raw_base + (uint32_t)(warp * kWarp2Smem);           // 128-byte aligned
     const uint32_t conv0 = raw0 + kRawStages * kRawStage;
-    const uint32_t out_blk = conv0 + BS2_CONV_BUFFERS * kConvRegion;
+    const uint32_t out_blk = conv0 + kConvRegion;
     const uint32_t rec0 = out_blk + kWarpOutBytes;
     constexpr uint32_t rec_slots = kRec2Slots, rec_half = kRec2Slots / 2;
     const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per raw stage
@@ -474,12 +460,10 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t cv_src_lane = (slot / kConvGroups) * kRawPitch + 12 * (slot % kConvGroups);
     const uint32_t cv_dst_lane = (slot / kConvGroups) * kConvPitch + 16 * (slot % kConvGroups);
     auto box_landed_wait = [&](int m) { mbar_wait_addr(dbar0 + 8 * ((uint32_t)m & 1u), ((uint32_t)m >> 1) & 1u); };
-    auto box_landed_try = [&](int m) { return mbar_try_wait_addr(dbar0 + 8 * ((uint32_t)m & 1u), ((uint32_t)m >> 1) & 1u); };
     auto cv_src_of = [&](int m, uint32_t hdr_y) {      // flags bits 4-5: where the first converted texel sits in the staged row
         return raw0 + ((uint32_t)m & 1u) * (uint32_t)kRawStage + cv_src_lane + ((hdr_y >> (8 + kItemRawOffShift - 2)) & 12u);
     };
-    auto conv_of = [&](int m) { return conv0 + (kTwoConv ? ((uint32_t)m & 1u) * (uint32_t)kConvRegion : 0u); };
-    auto cv_dst_of = [&](int m) { return conv_of(m) + cv_dst_lane; };
+    const uint32_t conv = conv0, cv_dst = conv0 + cv_dst_lane;
     // address texel (0, 0) of an item's camera would have in its converted buffer (rare paths only)
     auto conv_origin_of = [&](uint32_t conv, const uint4 &h) {
         const int c0 = (int)(int16_t)(h.z & 0xFFFFu), y0 = (int)(int16_t)(h.z >> 16);
@@ -503,22 +487,6 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if (cnt > 1) issue_box(lds128(rec_addr(1)), 1u);
     }
     __syncwarp();
-    // Item pipeline: at the top of iteration n the box of item n is already rewritten in converted buffer n & 1,
-    // the box of item n+1 is landing in (or has reached) raw stage (n+1) & 1, the box of item n+2 is in flight.
-    // (With a single converted buffer every item rewrites its own box at the top of its iteration instead.)
-    if (kTwoConv) {
-        const uint4 r = lds128(rec_addr(0));
-        if ((r.y & 0xFFu) == (uint32_t)kBlockFast) {
-            box_landed_wait(0);
-            convert_box(cv_src_of(0, r.y), cv_dst_of(0));
-        }
-        __syncwarp();
-        if (cnt > 2) {
-            if (lane == 0) issue_box(lds128(rec_addr(2)), 0u);      // records 0 .. 7 are all there
-            __syncwarp();
-        }
-    }
-
     // lane constants: output word merge (store_row_pixel), column offsets
     const uint32_t sel = (lane & 3) == 0 ? 0x4210u : ((lane & 3) == 1 ? 0x5421u : 0x6542u);
     const uint32_t storing = (uint32_t)((lane & 3) != 3);
@@ -533,32 +501,21 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     for (int n = 0; n < cnt; ++n) {
         if (lane == 0 && ((uint32_t)n & (rec_half - 1)) == 0 && n >= (int)rec_half && n + (int)rec_half < cnt)
             request_records(n + (int)rec_half);      // the half items n-8 .. n-1 used is free: refill it with n+8 .. n+15
-        // the record ring is read up to three items ahead: make the next half visible when item n+3 is its first
-        if (n + 3 < cnt) wait_half_of(n + 3);
+        // the record ring is read two items ahead: make the next half visible when item n+2 is its first
+        if (n + 2 < cnt) wait_half_of(n + 2);
         // item header (layout_plan, compact form): bx | by << 16, type | flags << 8 | cam << 16 | groups << 24,
         // c0 | y0 << 16 (TMA coordinates of the box), run base of lane u = 0 in the converted buffer
         const uint32_t ra = rec_addr(n);
         const uint4 r = lds128(ra);
-        const uint32_t conv = conv_of(n);
         bool direct = false;
         const uint32_t bx = r.x & 0xFFFFu, by = r.x >> 16;
         const uint32_t type = r.y & 0xFFu, flags = (r.y >> 8) & 0xFFu;
-        // the next item: does it have a box to rewrite?
-        uint32_t rn_y = 0;
-        bool next_box = false;
-        if (kTwoConv && n + 1 < cnt) {
-            rn_y = lds32(rec_addr(n + 1) + 4);
-            next_box = (rn_y & 0xFFu) == (uint32_t)kBlockFast;
+        if (type == (uint32_t)kBlockFast) {
+            box_landed_wait(n);
+            convert_box(cv_src_of(n, r.y), cv_dst);
         }
-        bool next_done = !next_box;
-        if (!kTwoConv) {
-            if (type == (uint32_t)kBlockFast) {
-                box_landed_wait(n);
-                convert_box(cv_src_of(n, r.y), cv_dst_of(n));
-            }
-            __syncwarp();             // converted box complete; its raw stage takes the box of item n+2
-            if (n + 2 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 2)), (uint32_t)n & 1u);
-        }
+        __syncwarp();                 // converted box complete; its raw stage takes the box of item n+2
+        if (n + 2 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 2)), (uint32_t)n & 1u);
         if (type == (uint32_t)kBlockFast) {
             const BlockCoef bc = load_block_coef(ra);
             const LaneCoef2 lc = lane_coef2(bc, uf);
@@ -568,21 +525,12 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             if (flags & kItemFull) {
                 direct = can_direct && (flags & kItemDirect);
                 const uint64_t grow = gbase + (by * brow + bx * (uint32_t)kBlockRowBytes);
-                if (direct && next_box && __all_sync(0xffffffffu, box_landed_try(n + 1))) {
-                    if (flags & kItemPlain)
-                        run_full2<true, true, true>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, cv_src_of(n + 1, rn_y),
-                                                    cv_dst_of(n + 1));
-                    else
-                        run_full2<true, true, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, cv_src_of(n + 1, rn_y),
-                                                     cv_dst_of(n + 1));
-                    next_done = true;
-                } else if (direct && (flags & kItemPlain)) {
-                    run_full2<true, false, true>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
-                } else if (direct) {
-                    run_full2<true, false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
-                } else {
-                    run_full2<false, false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing, 0u, 0u);
-                }
+                if (direct && (flags & kItemPlain))
+                    run_full2<true, true>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
+                else if (direct)
+                    run_full2<true, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
+                else
+                    run_full2<false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
                 if (groups != 0u) {
                     __syncwarp();
                     patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane,
@@ -599,12 +547,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             }
             wrote = !direct;
         }
-        if (!next_done) {             // not rewritten on the side: do it now
-            box_landed_wait(n + 1);
-            convert_box(cv_src_of(n + 1, rn_y), cv_dst_of(n + 1));
-        }
-        __syncwarp();                 // every lane is done with converted buffer n & 1 and with raw stage (n+1) & 1
-        if (kTwoConv && n + 3 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 3)), ((uint32_t)n + 1u) & 1u);   // that raw stage takes the box of item n+3
+        __syncwarp();                 // every lane is done with the converted buffer
         if ((flags & kItemLast) && !direct) {
             const int tx0 = (int)bx * kBlockW, ty0 = (int)by * kBlockH;
             if (!prior_grid_done) {

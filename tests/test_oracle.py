@@ -107,12 +107,13 @@ def test_full_size_known_answers(known_answers, cfg, content, frame):
     assert sha(oracle.stitch(srcs, w.H, w.canvas_wh)) == want["canvas_sha256"]
 
 
-@pytest.mark.parametrize("cfg", ["cfg2", "cfg3"])
+@pytest.mark.parametrize("cfg", ["cfg2", "cfg3", "cfg1"])
 def test_algorithmic_bytes(cfg):
     # W*H*3 + 3*sum_i U_i
     w = workloads().get(cfg)
     total, tex, wins = oracle.count_texels([w.src_wh] * w.n_cams, w.canvas_wh, w.H)
-    assert sum(wins) == w.canvas_wh[0] * w.canvas_wh[1]
+    if cfg != "cfg1":       # the synthetic panoramas are fully covered; the two photos cover 56 % of their canvas
+        assert sum(wins) == w.canvas_wh[0] * w.canvas_wh[1]
     assert w.canvas_bytes + 3 * total == w.algorithmic_bytes
 
 

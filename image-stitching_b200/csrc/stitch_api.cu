@@ -812,6 +812,48 @@ int ensure_ring(bs_handle *h)
     return BS_OK;
 }
 
+// Queue one frame from host buffers on slot `s`: uploads on s_h2d, kernels on s_compute, download on s_d2h.
+int issue_frame(bs_handle *h, Slot &s, const uint8_t *const *frames, const size_t *pitch, uint8_t *out, size_t out_pitch)
+{
+    h->h2d_bytes_last = 0;
+    for (int i = 0; i < h->n_cams; ++i) {
+        int x0 = 0, y0 = 0, x1 = h->sw[i] - 1, y1 = h->sh[i] - 1;
+        const bool whole = !h->fast_ok || h->up_x0.empty() || (!h->lens.empty() && h->lens[i].enabled);
+        if (!whole) {
+            if (h->up_x1[i] < 0) continue;           // this camera contributes nothing to the canvas
+            x0 = (h->up_x0[i] / 64) * 64;            // rows start on a 64-byte boundary of the frame (3 * 64 texel bytes)
+            y0 = h->up_y0[i];
+            x1 = std::min(x1, h->up_x1[i]);
+            y1 = std::min(y1, h->up_y1[i]);
+        }
+        BS_CUDA(h, cudaMemcpy2DAsync(s.d_frame[i] + (size_t)y0 * h->d_frame_pitch[i] + (size_t)x0 * 3, h->d_frame_pitch[i],
+                                     frames[i] + (size_t)y0 * pitch[i] + (size_t)x0 * 3, pitch[i], (size_t)(x1 - x0 + 1) * 3,
+                                     (size_t)(y1 - y0 + 1), cudaMemcpyHostToDevice, h->s_h2d));
+        h->h2d_bytes_last += (uint64_t)(x1 - x0 + 1) * 3 * (uint64_t)(y1 - y0 + 1);
+    }
+    const bool keep = (h->flags & BS_FLAG_KEEP_CANVAS) != 0;
+    if (keep)
+        BS_CUDA(h, cudaMemcpy2DAsync(s.d_canvas, h->d_canvas_pitch, out, out_pitch, (size_t)h->W * 3,
+                                     h->H, cudaMemcpyHostToDevice, h->s_h2d));
+    BS_CUDA(h, cudaEventRecord(s.ev_h2d, h->s_h2d));
+    BS_CUDA(h, cudaStreamWaitEvent(h->s_compute, s.ev_h2d, 0));
+    std::vector<const void *> d_frames(s.d_frame.begin(), s.d_frame.end()), warp_frames(h->n_cams);
+    std::vector<size_t> warp_pitch(h->n_cams);
+    bool lens_ran = false;
+    int rc = undistort_frames(h, d_frames.data(), h->d_frame_pitch.data(), s.d_undist, warp_frames.data(), warp_pitch.data(),
+                              h->s_compute, &lens_ran);
+    if (rc != BS_OK) return rc;
+    // without a lens kernel the frames reach the device by copies on another stream, ordered by an event
+    rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep, h->s_compute, lens_ran);
+    if (rc != BS_OK) return rc;
+    BS_CUDA(h, cudaEventRecord(s.ev_kernel, h->s_compute));
+    BS_CUDA(h, cudaStreamWaitEvent(h->s_d2h, s.ev_kernel, 0));
+    BS_CUDA(h, cudaMemcpy2DAsync(out, out_pitch, s.d_canvas, h->d_canvas_pitch, (size_t)h->W * 3, h->H,
+                                 cudaMemcpyDeviceToHost, h->s_d2h));
+    BS_CUDA(h, cudaEventRecord(s.ev_done, h->s_d2h));
+    return BS_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -937,46 +979,22 @@ int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
 
     const int64_t t = h->next_ticket;
     Slot &s = h->ring[t % kPipelineDepth];
-    h->h2d_bytes_last = 0;
     if (s.busy) {   // the slot's previous frame must have left the device
         BS_CUDA(h, cudaEventSynchronize(s.ev_done));
         s.busy = false;
     }
-    for (int i = 0; i < h->n_cams; ++i) {
-        int x0 = 0, y0 = 0, x1 = h->sw[i] - 1, y1 = h->sh[i] - 1;
-        const bool whole = !h->fast_ok || h->up_x0.empty() || (!h->lens.empty() && h->lens[i].enabled);
-        if (!whole) {
-            if (h->up_x1[i] < 0) continue;           // this camera contributes nothing to the canvas
-            x0 = (h->up_x0[i] / 64) * 64;            // rows start on a 64-byte boundary of the frame (3 * 64 texel bytes)
-            y0 = h->up_y0[i];
-            x1 = std::min(x1, h->up_x1[i]);
-            y1 = std::min(y1, h->up_y1[i]);
-        }
-        BS_CUDA(h, cudaMemcpy2DAsync(s.d_frame[i] + (size_t)y0 * h->d_frame_pitch[i] + (size_t)x0 * 3, h->d_frame_pitch[i],
-                                     frames[i] + (size_t)y0 * pitch[i] + (size_t)x0 * 3, pitch[i], (size_t)(x1 - x0 + 1) * 3,
-                                     (size_t)(y1 - y0 + 1), cudaMemcpyHostToDevice, h->s_h2d));
-        h->h2d_bytes_last += (uint64_t)(x1 - x0 + 1) * 3 * (uint64_t)(y1 - y0 + 1);
+    rc = issue_frame(h, s, frames, pitch, out, out_pitch);
+    if (rc != BS_OK) {
+        // Part of the frame may have been queued: let the three streams run dry so that nothing still
+        // refers to the slot or to the caller's buffers, and leave the slot free.  The handle stays usable.
+        cudaStreamSynchronize(h->s_h2d);
+        cudaStreamSynchronize(h->s_compute);
+        cudaStreamSynchronize(h->s_d2h);
+        cudaGetLastError();
+        s.busy = false;
+        s.ticket = -1;
+        return rc;
     }
-    const bool keep = (h->flags & BS_FLAG_KEEP_CANVAS) != 0;
-    if (keep)
-        BS_CUDA(h, cudaMemcpy2DAsync(s.d_canvas, h->d_canvas_pitch, out, out_pitch, (size_t)h->W * 3,
-                                     h->H, cudaMemcpyHostToDevice, h->s_h2d));
-    BS_CUDA(h, cudaEventRecord(s.ev_h2d, h->s_h2d));
-    BS_CUDA(h, cudaStreamWaitEvent(h->s_compute, s.ev_h2d, 0));
-    std::vector<const void *> d_frames(s.d_frame.begin(), s.d_frame.end()), warp_frames(h->n_cams);
-    std::vector<size_t> warp_pitch(h->n_cams);
-    bool lens_ran = false;
-    rc = undistort_frames(h, d_frames.data(), h->d_frame_pitch.data(), s.d_undist, warp_frames.data(), warp_pitch.data(),
-                          h->s_compute, &lens_ran);
-    if (rc != BS_OK) return rc;
-    // without a lens kernel the frames reach the device by copies on another stream, ordered by an event
-    rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep, h->s_compute, lens_ran);
-    if (rc != BS_OK) return rc;
-    BS_CUDA(h, cudaEventRecord(s.ev_kernel, h->s_compute));
-    BS_CUDA(h, cudaStreamWaitEvent(h->s_d2h, s.ev_kernel, 0));
-    BS_CUDA(h, cudaMemcpy2DAsync(out, out_pitch, s.d_canvas, h->d_canvas_pitch, (size_t)h->W * 3, h->H,
-                                 cudaMemcpyDeviceToHost, h->s_d2h));
-    BS_CUDA(h, cudaEventRecord(s.ev_done, h->s_d2h));
     s.ticket = t;
     s.busy = true;
     h->next_ticket++;

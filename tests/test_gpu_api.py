@@ -1,0 +1,159 @@
+"""GPU tests of the C-ABI entry points around the frame kernel that the round-1 review found unexercised:
+device submits of a handle with lens models (caller's stream, two frames in flight), the ordering flag of
+bs_submit_device_ex, bs_undistort_device, a rejected submit between two good ones, real image content, and both
+staged kernels on the same input."""
+import hashlib
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+from conftest import GOLDEN, ROOT, pkg, workloads
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def lens(sw, sh, k):
+    Ks = [np.array([[0.9 * sw, 0, sw / 2 + 3.3], [0, 0.92 * sw, sh / 2 - 1.7], [0, 0, 1]]),
+          np.array([[1.1 * sw, 0, sw / 2 - 7.0], [0, 1.1 * sw, sh / 2 + 2.5], [0, 0, 1]])]
+    ds = [np.array([-0.2, 0.05, 0.001, -0.002, 0.01, 0, 0, 0]), np.array([0.12, -0.03, -0.001, 0.0007, 0.0])]
+    return Ks[k % 2], ds[k % 2]
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def test_device_submit_with_lens_models_two_frames_in_flight():
+    """tools/stitch/main.cpp:145-152 on device buffers: undistort + warp of frame A and of frame B queued back
+    to back on the caller's stream, no synchronisation in between; both panoramas must be exact."""
+    p = pkg()
+    w = workloads().get("cfg2")
+    sw, sh = w.src_wh
+    frames = [[oracle.gen_frame(sw, sh, i, f, oracle.NOISE) for i in range(2)] for f in range(2)]
+    d_frames = [[dev(x) for x in fs] for fs in frames]
+    d_out = [torch.full((w.canvas_wh[1], w.canvas_wh[0], 3), 7, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    stream = torch.cuda.Stream()
+    with p.Stitcher([w.src_wh] * 2, w.canvas_wh, w.H) as st:
+        for i in range(2):
+            st.set_undistort(i, *lens(sw, sh, i))
+        free0 = torch.cuda.mem_get_info()[0]
+        for f in range(2):
+            st.submit_device([t.data_ptr() for t in d_frames[f]], [t.stride(0) for t in d_frames[f]], d_out[f].data_ptr(),
+                             d_out[f].stride(0), stream.cuda_stream)
+        stream.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free0, "a device submit allocated memory (buffers belong to bs_set_undistort)"
+    for f in range(2):
+        und = [oracle.undistort(frames[f][i], *lens(sw, sh, i)) for i in range(2)]
+        want = oracle.stitch(und, w.H, w.canvas_wh)
+        got = d_out[f].cpu().numpy()
+        assert np.array_equal(got, want), f"frame {f}: {(got != want).any(axis=2).sum()} pixels differ"
+
+
+def test_submit_device_ex_flag_and_current_device():
+    p = pkg()
+    w = workloads().get("cfg2")
+    srcs = [oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, 4, oracle.NOISE) for i in range(2)]
+    d_src = [dev(s) for s in srcs]
+    want = oracle.stitch(srcs, w.H, w.canvas_wh)
+    with p.Stitcher([w.src_wh] * 2, w.canvas_wh, w.H) as st:
+        for flags in (None, 0, p.SUBMIT_SOURCES_SETTLED):
+            d_out = torch.zeros((w.canvas_wh[1], w.canvas_wh[0], 3), dtype=torch.uint8, device="cuda")
+            for _ in range(3):       # back to back: with the flag, consecutive frames overlap
+                st.submit_device([t.data_ptr() for t in d_src], [t.stride(0) for t in d_src], d_out.data_ptr(), d_out.stride(0),
+                                 0, flags)
+            torch.cuda.synchronize()
+            assert np.array_equal(d_out.cpu().numpy(), want), f"submit flags {flags}"
+        with pytest.raises(p.StitchError) as e:
+            st.submit_device([t.data_ptr() for t in d_src], [t.stride(0) for t in d_src], d_out.data_ptr(), d_out.stride(0), 0, 0x80)
+        assert e.value.code == -1 and "submit flags" in str(e.value)
+        assert st.stats()["frame_kernel"] == 2          # cfg2's boxes are compact: the compact-box kernel ran
+    assert torch.cuda.current_device() == 0
+
+
+def test_undistort_device_matches_host_entry():
+    p = pkg()
+    sw, sh = 1280, 720
+    src = oracle.gen_frame(sw, sh, 1, 2, oracle.NOISE)
+    K, d = lens(sw, sh, 0)
+    want = oracle.undistort(src, K, d)
+    d_src = dev(src)
+    d_dst = torch.zeros_like(d_src)
+    with p.Stitcher([(sw, sh)], (64, 32), [np.eye(3)]) as st:
+        st.undistort_device(0, d_src.data_ptr(), d_src.stride(0), d_dst.data_ptr(), d_dst.stride(0))     # no model yet: a copy
+        torch.cuda.synchronize()
+        assert np.array_equal(d_dst.cpu().numpy(), src)
+        st.set_undistort(0, K, d)
+        st.undistort_device(0, d_src.data_ptr(), d_src.stride(0), d_dst.data_ptr(), d_dst.stride(0))
+        torch.cuda.synchronize()
+    assert np.array_equal(d_dst.cpu().numpy(), want)
+    assert np.array_equal(p.undistort(src, K, d), want)
+
+
+def test_rejected_submit_between_two_good_frames():
+    """A submit that fails leaves no half-issued slot behind: the frames before and after it are exact and the
+    tickets keep counting."""
+    p = pkg()
+    w = workloads().get("cfg2")
+    frames = [[oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, f, oracle.NOISE) for i in range(2)] for f in range(3)]
+    outs = [np.empty((w.canvas_wh[1], w.canvas_wh[0], 3), np.uint8) for _ in range(3)]
+    with p.Stitcher([w.src_wh] * 2, w.canvas_wh, w.H) as st:
+        t0 = st.submit(frames[0], outs[0])
+        narrow = [f[:, : w.src_wh[0] // 2] for f in frames[1]]       # wrong width: rejected
+        with pytest.raises(ValueError):
+            st.submit(narrow, outs[1])
+        import ctypes
+        L = p.lib()
+        ptrs = (ctypes.c_void_p * 2)(*[f.ctypes.data for f in frames[1]])
+        bad = (ctypes.c_size_t * 2)(w.src_wh[0] * 3, w.src_wh[0] * 3 - 1)   # pitch below width * 3, straight at the C ABI
+        t = ctypes.c_int64(-1)
+        rc = L.bs_submit(st._h, ptrs, bad, outs[1].ctypes.data, outs[1].strides[0], ctypes.byref(t))
+        assert rc == -1 and b"pitch[1]" in L.bs_last_error(st._h)
+        t1 = st.submit(frames[1], outs[1])
+        t2 = st.submit(frames[2], outs[2])
+        assert (t0, t1, t2) == (0, 1, 2)
+        for t in (t0, t1, t2):
+            st.wait(t)
+    for f in range(3):
+        assert np.array_equal(outs[f], oracle.stitch(frames[f], w.H, w.canvas_wh)), f"frame {f}"
+
+
+def test_real_image_content():
+    """Crops of the reference's own photos (test/Inputs/1a.jpg, 1b.jpg) under cfg1-like homographies: the GPU
+    result against the OpenCV hash recorded by tests/golden/make_real_crop.py and against the oracle."""
+    p = pkg()
+    z = np.load(os.path.join(GOLDEN, "real_crop.npz"))
+    meta = json.loads(bytes(z["meta"]).decode())
+    srcs = [np.ascontiguousarray(z["src0"]), np.ascontiguousarray(z["src1"])]
+    whs = [(s.shape[1], s.shape[0]) for s in srcs]
+    for flags in (0, p.FLAG_EXACT_ONLY):
+        with p.Stitcher(whs, tuple(meta["canvas_wh"]), z["H"], flags=flags) as st:
+            got = st.stitch(srcs)
+        assert hashlib.sha256(got.tobytes()).hexdigest() == meta["canvas_sha256"], f"flags={flags}"
+    assert np.array_equal(got, oracle.stitch(srcs, z["H"], tuple(meta["canvas_wh"])))
+    want_legacy = oracle.stitch(srcs, z["H"], tuple(meta["canvas_wh"]), oracle.BORDER_LEGACY)
+    with p.Stitcher(whs, tuple(meta["canvas_wh"]), z["H"], flags=p.FLAG_LEGACY_BORDER) as st:
+        assert np.array_equal(st.stitch(srcs), want_legacy)
+
+
+def test_general_staged_kernel_still_exact_on_compact_plans():
+    """BS_DEBUG_NO_COMPACT routes a compact plan through the general staged kernel (the one strong perspective
+    takes): both kernels must give the recorded OpenCV canvas.  Runs in a child process (the switch is read once)."""
+    code = ("import sys, hashlib, json, importlib; sys.path.insert(0, %r); sys.path.insert(0, %r + '/tests')\n"
+            "import oracle\n"
+            "p = importlib.import_module('image-stitching_b200'); wl = importlib.import_module('image-stitching_b200.workloads')\n"
+            "w = wl.get('cfg2'); srcs = [oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, 0, oracle.NOISE) for i in range(2)]\n"
+            "st = p.Stitcher([w.src_wh] * 2, w.canvas_wh, w.H); got = st.stitch(srcs); k = st.stats()['frame_kernel']; st.close()\n"
+            "print(json.dumps({'kernel': k, 'sha': hashlib.sha256(got.tobytes()).hexdigest()}))\n") % (ROOT, ROOT)
+    ka = json.load(open(os.path.join(GOLDEN, "known_answers.json")))
+    want = [c for c in ka["cases"] if (c["config"], c["content"], c["frame"]) == ("cfg2", "noise", 0)][0]["canvas_sha256"]
+    for env_extra, kernel in (({}, 2), ({"BS_DEBUG_NO_COMPACT": "1"}, 1)):
+        out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=dict(os.environ, **env_extra))
+        assert out.returncode == 0, out.stderr[-1500:]
+        res = json.loads(out.stdout.strip().splitlines()[-1])
+        assert res["kernel"] == kernel and res["sha"] == want, res

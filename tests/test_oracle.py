@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import oracle
-from conftest import workloads
+from conftest import ROOT, workloads
 
 # SURVEY.md Appendix B.3 (recorded when the reference was surveyed) -- must agree with the
 # regenerated tests/golden/known_answers.json
@@ -147,3 +147,12 @@ def test_border_constant_golden_cases(border_constant_cases):
         out = np.full((dh, dw, 3), 77, np.uint8)
         oracle.warp_perspective(np.ascontiguousarray(z[f"b{k}_src"]), z[f"b{k}_H"], out, oracle.BORDER_CONSTANT)
         assert np.array_equal(out, z[f"b{k}_exp"]), f"case {k}"
+
+
+def test_real_crop_fixture_matches_oracle():
+    """tests/golden/real_crop.npz: crops of the reference's photos warped by cv2 (make_real_crop.py)."""
+    import json
+    z = np.load(os.path.join(ROOT, "tests", "golden", "real_crop.npz"))
+    meta = json.loads(bytes(z["meta"]).decode())
+    got = oracle.stitch([np.ascontiguousarray(z["src0"]), np.ascontiguousarray(z["src1"])], z["H"], tuple(meta["canvas_wh"]))
+    assert sha(got) == meta["canvas_sha256"]

@@ -12,7 +12,10 @@ What is checked here, through the C ABI, on the GPU:
     the first call's plan and counters and must not be disturbed by them;
   * a different calibration right afterwards (other canvas, seams, ragged edges) is also exact, so
     nothing stale survives in the shared array;
-  * a canvas that needs more blocks than the array holds is refused with a clear message.
+  * a canvas that needs more blocks than the array holds is refused with a clear message, one block over the
+    limit included, and a panorama that nearly fills the array (7680x2160: 32400 of 32768 blocks) is exact;
+  * repeated calls leave the amount of free device memory unchanged (the property in the name), and flags the
+    entry point does not implement are refused instead of being ignored.
 This file sorts last on purpose: with `pytest -x` every other test has already run if it fails.
 """
 import numpy as np
@@ -91,3 +94,50 @@ def test_canvas_beyond_the_static_array_is_refused():
                                w.canvas_wh[0] * 3, [np.eye(3)])
     assert e.value.code == -4
     assert "99893 blocks" in str(e.value) and "32768" in str(e.value)
+
+
+def test_near_limit_canvas_is_exact_and_nothing_is_allocated():
+    """cfg3 needs 32400 of the array's 32768 blocks.  Ten calls in a row: same bytes as the regular entry points,
+    and cudaMemGetInfo reports the same free memory before and after (calls 2..10; the first call on a device
+    may make the driver load the kernels)."""
+    p = pkg()
+    w = workloads().get("cfg3")
+    whs = [w.src_wh] * w.n_cams
+    srcs = [oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, 0, oracle.NOISE) for i in range(w.n_cams)]
+    d_src = [torch.from_numpy(s).cuda() for s in srcs]
+    want = regular_path(p, whs, w.canvas_wh, w.H, d_src)
+    d_out = torch.zeros((w.canvas_wh[1], w.canvas_wh[0], 3), dtype=torch.uint8, device="cuda")
+    args = (whs, [t.data_ptr() for t in d_src], [t.stride(0) for t in d_src], w.canvas_wh, d_out.data_ptr(), d_out.stride(0), w.H)
+    p.stitch_device_static(*args)
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    import time
+    t0 = time.perf_counter()
+    for _ in range(9):
+        p.stitch_device_static(*args)
+    torch.cuda.synchronize()
+    ms = 1e3 * (time.perf_counter() - t0) / 9
+    assert torch.cuda.mem_get_info()[0] == free0, "bs_stitch_device_static changed the amount of free device memory"
+    assert np.array_equal(d_out.cpu().numpy(), want)
+    print(f"bs_stitch_device_static at cfg3: {ms:.2f} ms per call (plan rebuilt every call)")
+
+
+def test_one_block_over_the_limit_and_unknown_flags_are_refused():
+    p = pkg()
+    d_src = [torch.zeros((8, 8, 3), dtype=torch.uint8, device="cuda")]
+    d_out = torch.zeros((16, 16, 3), dtype=torch.uint8, device="cuda")
+    # 99 x 331 = 32769 blocks of 32x16: one more than the array holds
+    with pytest.raises(p.StitchError) as e:
+        p.stitch_device_static([(8, 8)], [d_src[0].data_ptr()], [24], (99 * 32, 331 * 16), d_out.data_ptr(), 99 * 32 * 3, [np.eye(3)])
+    assert e.value.code == -4 and "32769 blocks" in str(e.value)
+    # 128 x 256 = 32768 blocks: accepted (a tiny source in a huge canvas: everything but one corner is empty)
+    big = torch.full((256 * 16, 128 * 32, 3), 9, dtype=torch.uint8, device="cuda")
+    src = torch.full((8, 8, 3), 200, dtype=torch.uint8, device="cuda")
+    p.stitch_device_static([(8, 8)], [src.data_ptr()], [24], (128 * 32, 256 * 16), big.data_ptr(), big.stride(0), [np.eye(3)])
+    torch.cuda.synchronize()
+    got = big.cpu().numpy()
+    assert (got[:7, :7] == 200).all() and got[8:, :].max() == 0 and got[:, 8:].max() == 0
+    for bad in (p.FLAG_BORDER_CONSTANT, p.FLAG_EXACT_ONLY, 0x100):
+        with pytest.raises(p.StitchError) as e:
+            p.stitch_device_static([(8, 8)], [src.data_ptr()], [24], (64, 32), d_out.data_ptr(), 64 * 3, [np.eye(3)], flags=bad)
+        assert e.value.code == -4 and "flags" in str(e.value)

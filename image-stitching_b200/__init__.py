@@ -32,6 +32,8 @@ EXPORTS = [
     "bs_wait", "bs_pipeline_depth", "bs_stitch", "bs_submit_device", "bs_sync",
     "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
     "bs_set_undistort", "bs_undistort", "bs_submit_device_ex", "bs_undistort_device",
+    "bs_pool_create", "bs_pool_destroy", "bs_pool_size", "bs_pool_depth", "bs_pool_handle", "bs_pool_last_error",
+    "bs_pool_set_undistort", "bs_pool_submit", "bs_pool_wait", "bs_pool_sync",
 ]
 
 
@@ -95,6 +97,18 @@ def lib():
     L.bs_undistort.argtypes = [vp, i, i, sz, vp, sz, dp, dp, i]
     L.bs_stitch_device_static.argtypes = [i, ip, ip, ctypes.POINTER(vp), ctypes.POINTER(sz), i, i, vp, sz, dp,
                                           ctypes.c_uint, vp]
+    L.bs_pool_create.argtypes = [i, ip, i, ip, ip, i, i, dp, ctypes.c_uint, ctypes.POINTER(vp)]
+    L.bs_pool_destroy.argtypes = [vp]
+    L.bs_pool_size.argtypes = [vp]
+    L.bs_pool_depth.argtypes = [vp]
+    L.bs_pool_handle.argtypes = [vp, i]
+    L.bs_pool_handle.restype = vp
+    L.bs_pool_last_error.argtypes = [vp]
+    L.bs_pool_last_error.restype = ctypes.c_char_p
+    L.bs_pool_set_undistort.argtypes = [vp, i, dp, dp, i]
+    L.bs_pool_submit.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz, ctypes.POINTER(ctypes.c_int64)]
+    L.bs_pool_wait.argtypes = [vp, ctypes.c_int64]
+    L.bs_pool_sync.argtypes = [vp]
     _lib = L
     return L
 
@@ -234,6 +248,79 @@ class Stitcher:
         s = Stats()
         _check(lib().bs_get_stats(self._h, ctypes.byref(s)), self._h)
         return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+
+class Pool:
+    """bs_pool_*: one replica of the calibration per GPU, frame f -> device f mod G, results in frame order
+    (the multi-GPU form of the video loop, /root/reference/tools/stitch/main.cpp:143-155)."""
+
+    def __init__(self, devices, src_whs, canvas_wh, Hs, flags=0):
+        L = lib()
+        n = len(src_whs)
+        self.n_cams = n
+        self.src_whs = [(int(w), int(h)) for w, h in src_whs]
+        self.canvas_wh = (int(canvas_wh[0]), int(canvas_wh[1]))
+        Hs = np.ascontiguousarray(np.asarray(Hs, dtype=np.float64).reshape(n, 9))
+        sw = (ctypes.c_int * n)(*[w for w, _ in self.src_whs])
+        sh = (ctypes.c_int * n)(*[h for _, h in self.src_whs])
+        devs = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+        self._p = ctypes.c_void_p()
+        rc = L.bs_pool_create(len(devices), devs, n, sw, sh, self.canvas_wh[0], self.canvas_wh[1],
+                              Hs.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), flags, ctypes.byref(self._p))
+        if rc != 0:
+            raise StitchError(rc, L.bs_last_error(None).decode())
+        self.depth = L.bs_pool_depth(self._p)
+        self.size = L.bs_pool_size(self._p)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise StitchError(rc, lib().bs_pool_last_error(self._p).decode())
+
+    def set_undistort(self, cam, K, dist):
+        K = np.ascontiguousarray(np.asarray(K, dtype=np.float64).reshape(9))
+        dist = np.ascontiguousarray(np.asarray(dist, dtype=np.float64).reshape(-1))
+        dptr = dist.ctypes.data_as(ctypes.POINTER(ctypes.c_double)) if dist.size else None
+        self._check(lib().bs_pool_set_undistort(self._p, cam, K.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), dptr, int(dist.size)))
+
+    def submit(self, frames, out):
+        ptrs = (ctypes.c_void_p * self.n_cams)()
+        pitches = (ctypes.c_size_t * self.n_cams)()
+        for k, f in enumerate(frames):
+            _check_img(f, f"frames[{k}]")
+            ptrs[k] = f.ctypes.data
+            pitches[k] = f.strides[0]
+        _check_img(out, "out")
+        idx = ctypes.c_int64(-1)
+        self._check(lib().bs_pool_submit(self._p, ptrs, pitches, out.ctypes.data, out.strides[0], ctypes.byref(idx)))
+        return idx.value
+
+    def wait(self, frame):
+        self._check(lib().bs_pool_wait(self._p, frame))
+
+    def sync(self):
+        self._check(lib().bs_pool_sync(self._p))
+
+    def replica_stats(self, i):
+        s = Stats()
+        _check(lib().bs_get_stats(lib().bs_pool_handle(self._p, i), ctypes.byref(s)))
+        return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def close(self):
+        if getattr(self, "_p", None):
+            lib().bs_pool_destroy(self._p)
+            self._p = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def stitch_device_static(src_whs, frame_ptrs, frame_pitches, canvas_wh, canvas_ptr, canvas_pitch, Hs, flags=0,

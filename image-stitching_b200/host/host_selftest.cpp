@@ -33,7 +33,9 @@ int main(int argc, char **argv) {
               << ", \"board_width\": " << opts.board_width << ", \"board_height\": " << opts.board_height
               << ", \"angle\": " << opts.angle << ", \"mode\": " << (opts.mode == StitchingMode::ChainOfTargets ? "\"chain\"" : "\"extend\"")
               << ", \"calibrate_config\": " << js(opts.calibrate_config) << ", \"stitch_config\": " << js(opts.stitch_config)
-              << ", \"output\": " << js(opts.output) << ", \"file_paths\": [";
+              << ", \"output\": " << js(opts.output) << ", \"device\": " << opts.device << ", \"devices\": [";
+    for (size_t i = 0; i < opts.devices.size(); ++i) std::cout << (i ? ", " : "") << opts.devices[i];
+    std::cout << "], \"file_paths\": [";
     for (size_t i = 0; i < opts.file_paths.size(); ++i) std::cout << (i ? ", " : "") << js(opts.file_paths[i]);
     std::cout << "]}" << std::endl;
     return 0;

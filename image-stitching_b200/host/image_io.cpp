@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cctype>
+#include <cstdlib>
 #include <cstring>
 
 #ifdef BS_WITH_NVJPEG
@@ -11,6 +12,21 @@
 #endif
 
 namespace bsio {
+
+namespace {
+void *(*g_alloc)(size_t) = nullptr;
+void (*g_release)(void *) = nullptr;
+}  // namespace
+
+void set_pixel_allocator(void *(*alloc)(size_t), void (*release)(void *)) {
+  g_alloc = alloc;
+  g_release = release;
+}
+void *pixel_alloc(size_t bytes) { return g_alloc ? g_alloc(bytes) : malloc(bytes); }
+void pixel_free(void *p) {
+  if (g_release) g_release(p);
+  else free(p);
+}
 
 namespace {
 

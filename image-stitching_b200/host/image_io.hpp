@@ -8,14 +8,37 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <new>
 #include <string>
 #include <vector>
 
 namespace bsio {
 
+// Pixel storage goes through a pair of hooks so that the stitch tool can keep its frames and panoramas in
+// pinned host memory (bs_host_alloc: the engine then copies by DMA straight from / to them); the default is malloc.
+void set_pixel_allocator(void *(*alloc)(size_t), void (*release)(void *));
+void *pixel_alloc(size_t bytes);
+void pixel_free(void *p);
+
+template <class T>
+struct PixelAllocator {
+  using value_type = T;
+  PixelAllocator() = default;
+  template <class U> PixelAllocator(const PixelAllocator<U> &) {}
+  T *allocate(size_t n) {
+    void *p = pixel_alloc(n * sizeof(T));
+    if (!p) throw std::bad_alloc();
+    return static_cast<T *>(p);
+  }
+  void deallocate(T *p, size_t) { pixel_free(p); }
+  template <class U> bool operator==(const PixelAllocator<U> &) const { return true; }
+  template <class U> bool operator!=(const PixelAllocator<U> &) const { return false; }
+};
+using Pixels = std::vector<uint8_t, PixelAllocator<uint8_t>>;
+
 struct Image {
   int w = 0, h = 0;
-  std::vector<uint8_t> bgr;   // h rows of w*3 bytes
+  Pixels bgr;                 // h rows of w*3 bytes
   bool empty() const { return w == 0 || h == 0; }
   size_t pitch() const { return (size_t)w * 3; }
 };

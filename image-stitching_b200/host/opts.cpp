@@ -6,6 +6,7 @@
 // Written table-driven rather than as the reference's if-chain.
 #include "opts.hpp"
 
+#include <algorithm>
 #include <cstdlib>
 #include <functional>
 
@@ -47,6 +48,22 @@ bool parse_command_line_opts(int argc, char *argv[]) {
        }},
       // extensions
       {{"--out"}, [](const std::string &v) { opts.output = v; return true; }},
+      {{"--devices"},      // before "--device": flags match by prefix
+       [](const std::string &v) {
+         opts.devices.clear();
+         size_t pos = 0;
+         while (pos <= v.size()) {
+           const size_t comma = std::min(v.find(',', pos), v.size());
+           const std::string tok = v.substr(pos, comma - pos);
+           const size_t dash = tok.find('-');
+           if (tok.empty()) return false;
+           const int a = atoi(tok.substr(0, dash).c_str()), b = dash == std::string::npos ? a : atoi(tok.substr(dash + 1).c_str());
+           if (a < 0 || b < a || b > 1023) return false;
+           for (int d = a; d <= b; ++d) opts.devices.push_back(d);
+           pos = comma + 1;
+         }
+         return !opts.devices.empty();
+       }},
       {{"--device"}, [](const std::string &v) { opts.device = atoi(v.c_str()); return true; }},
       {{"--frames"}, [](const std::string &v) { opts.max_frames = atoi(v.c_str()); return true; }},
   };

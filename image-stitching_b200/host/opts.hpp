@@ -26,6 +26,7 @@ struct command_line_opts {
   // --- extensions of this build (not in the reference) ---
   std::string output;      // --out=PATH : where the panorama(s) go ("" = final.jpg / final.ppm like the reference)
   int device = 0;          // --device=N
+  std::vector<int> devices;    // --devices=0-3 or --devices=0,2,5 : video mode runs frame-parallel on these GPUs (frame f -> f mod G)
   int max_frames = -1;     // --frames=N : stop video mode after N panoramas (-1 = until end of input)
   bool legacy_border = false;  // --legacy-border : OpenCV 2.4/3.x rule on the last source row/column
 };

@@ -4,14 +4,19 @@
 // engine behind include/b200_stitch.h.
 //
 //   stitch [--s-conf=stitch.conf.xml] [-i] [-v=N]        (reference flags)
-//          [--out=PATH] [--frames=N] [--device=N] [--legacy-border]   (extensions)
+//          [--out=PATH] [--frames=N] [--device=N] [--devices=0-7] [--legacy-border]   (extensions)
 //
 // Differences a user can observe, all forced by what this build can link against:
 //   * images are read as JPEG through nvJPEG or as binary PPM (no libjpeg / OpenCV here);
 //   * a "video" input is a stream of concatenated PPM frames; at end of input the tool exits 0
 //     (the reference loops forever and dies on an OpenCV assertion at EOF, main.cpp:143-155);
 //   * uncovered canvas pixels are 0 (the reference leaves them uninitialised, main.cpp:108,144);
-//   * -i opens no window (no display on a GPU node): displayResult is a headless no-op.
+//   * -i opens no window (no display on a GPU node): displayResult is a headless no-op;
+//   * image mode uploads every photo once and downloads the canvas once (one fused launch for all of
+//     them); the reference's one line of milliseconds per image is kept, each line being that image's
+//     share of the fused time;
+//   * --devices=... runs video mode frame-parallel over several GPUs (frame f on GPU f mod G, panoramas
+//     in frame order); frames and panoramas live in pinned host memory.
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -109,24 +114,50 @@ int main(int argc, char *argv[]) {
   }
   const unsigned flags = opts.legacy_border ? BS_FLAG_LEGACY_BORDER : 0u;
 
+  // frames and panoramas in pinned memory: the engine's copies then go by DMA straight from / to them
+  if (bs_device_count() > 0) bsio::set_pixel_allocator(bs_host_alloc, bs_host_free);
+
   if (!opts.video) {
+    // One handle for all images: every photo is uploaded once, one launch warps and composites them in
+    // the reference's order (later images overwrite earlier ones, main.cpp:113-117), the canvas comes
+    // back once.
+    std::vector<bsio::Image> images(n);
+    std::vector<int> sw(n), sh(n);
+    std::vector<double> Hall(9 * n);
+    for (size_t i = 0; i < n; ++i) {
+      std::string err;
+      if (!bsio::read_image(opts.file_paths[i], images[i], &err)) {
+        std::cout << "Failed to read " << opts.file_paths[i] << ": " << err << std::endl;
+        return 5;
+      }
+      sw[i] = images[i].w;
+      sh[i] = images[i].h;
+      memcpy(&Hall[9 * i], H[i].data.data(), 9 * sizeof(double));
+    }
     bsio::Image result;
     result.w = result_w;
     result.h = result_h;
     result.bgr.assign((size_t)result_w * result_h * 3, 0);
+    bs_handle *h = nullptr;
+    if (bs_create(opts.device, (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags, &h) != BS_OK)
+      return fail_bs("bs_create failed", nullptr);
+    std::vector<const uint8_t *> ptrs(n);
+    std::vector<size_t> pitches(n);
     for (size_t i = 0; i < n; ++i) {
-      bsio::Image image;
-      std::string err;
-      if (!bsio::read_image(opts.file_paths[i], image, &err)) {
-        std::cout << "Failed to read " << opts.file_paths[i] << ": " << err << std::endl;
-        return 5;
-      }
-      auto start = std::chrono::steady_clock::now();
-      int rc = bs_warp_perspective(image.bgr.data(), image.w, image.h, image.pitch(), result.bgr.data(), result.w,
-                                   result.h, result.pitch(), H[i].data.data(), flags);
-      auto end = std::chrono::steady_clock::now();
-      if (rc != BS_OK) return fail_bs("warpPerspective failed", nullptr);
-      std::cout << std::chrono::duration<double, std::milli>(end - start).count() << std::endl;
+      ptrs[i] = images[i].bgr.data();
+      pitches[i] = images[i].pitch();
+    }
+    auto start = std::chrono::steady_clock::now();
+    int rc = bs_stitch(h, ptrs.data(), pitches.data(), result.bgr.data(), result.pitch());
+    auto end = std::chrono::steady_clock::now();
+    if (rc != BS_OK) {
+      rc = fail_bs("warpPerspective failed", h);
+      bs_destroy(h);
+      return rc;
+    }
+    bs_destroy(h);
+    for (size_t i = 0; i < n; ++i) {
+      std::cout << std::chrono::duration<double, std::milli>(end - start).count() / (double)n << std::endl;
       displayResult("temp", result, true);
     }
     displayResult("Final", result, true);
@@ -163,8 +194,11 @@ int main(int argc, char *argv[]) {
     sh[i] = first[i].h;
     memcpy(&Hall[9 * i], H[i].data.data(), 9 * sizeof(double));
   }
-  bs_handle *h = nullptr;
-  if (bs_create(opts.device, (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags, &h) != BS_OK)
+  // one replica of the calibration per GPU; frame f runs on replica f mod G (a single GPU is a pool of one)
+  std::vector<int> devices = opts.devices.empty() ? std::vector<int>{opts.device} : opts.devices;
+  bs_pool *pool = nullptr;
+  if (bs_pool_create((int)devices.size(), devices.data(), (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags,
+                     &pool) != BS_OK)
     return fail_bs("bs_create failed", nullptr);
   for (size_t i = 0; i < n; ++i) {
     // cv::undistort(frame, undistorted, cameraMatrix[i], distCoeffs[i]) of main.cpp:148-149 runs on the
@@ -172,14 +206,14 @@ int main(int argc, char *argv[]) {
     const bsfs::Matrix &K = cameraMatrix[i], &d = distCoeffs[i];
     if (K.empty()) continue;
     if (K.rows != 3 || K.cols != 3 ||
-        bs_set_undistort(h, (int)i, K.data.data(), d.empty() ? nullptr : d.data.data(), (int)d.data.size()) != BS_OK) {
-      int rc = fail_bs("bs_set_undistort failed", h);
-      bs_destroy(h);
-      return rc;
+        bs_pool_set_undistort(pool, (int)i, K.data.data(), d.empty() ? nullptr : d.data.data(), (int)d.data.size()) != BS_OK) {
+      std::cout << "bs_set_undistort failed: " << bs_pool_last_error(pool) << std::endl;
+      bs_pool_destroy(pool);
+      return 6;
     }
   }
 
-  const int depth = bs_pipeline_depth(h);
+  const int depth = bs_pool_depth(pool);
   std::vector<std::vector<bsio::Image>> frames(depth, std::vector<bsio::Image>(n));
   std::vector<bsio::Image> results(depth);
   std::vector<int64_t> tickets(depth, -1);
@@ -189,7 +223,7 @@ int main(int argc, char *argv[]) {
     r.bgr.assign((size_t)result_w * result_h * 3, 0);
   }
   auto emit = [&](int slot, long index) -> bool {
-    if (bs_wait(h, tickets[slot]) != BS_OK) return false;
+    if (bs_pool_wait(pool, tickets[slot]) != BS_OK) return false;
     tickets[slot] = -1;
     displayResult("Final", results[slot]);
     if (!opts.output.empty()) {
@@ -224,7 +258,7 @@ int main(int argc, char *argv[]) {
       ptrs[i] = frames[slot][i].bgr.data();
       pitches[i] = frames[slot][i].pitch();
     }
-    if (bs_submit(h, ptrs.data(), pitches.data(), results[slot].bgr.data(), results[slot].pitch(), &tickets[slot]) !=
+    if (bs_pool_submit(pool, ptrs.data(), pitches.data(), results[slot].bgr.data(), results[slot].pitch(), &tickets[slot]) !=
         BS_OK) {
       ok = false;
       break;
@@ -238,10 +272,13 @@ int main(int argc, char *argv[]) {
   }
   auto t1 = std::chrono::steady_clock::now();
   int rc = 0;
-  if (!ok) rc = fail_bs("stitching failed", h);
-  else if (opts.verbosity > 0)
-    std::cout << produced << " frames, " << std::chrono::duration<double, std::milli>(t1 - t0).count() / (produced ? produced : 1)
-              << " ms/frame" << std::endl;
-  bs_destroy(h);
+  if (!ok) {
+    std::cout << "stitching failed: " << bs_pool_last_error(pool) << std::endl;
+    rc = 6;
+  } else if (opts.verbosity > 0) {
+    std::cout << produced << " frames on " << devices.size() << " GPU(s), "
+              << std::chrono::duration<double, std::milli>(t1 - t0).count() / (produced ? produced : 1) << " ms/frame" << std::endl;
+  }
+  bs_pool_destroy(pool);
   return rc;
 }

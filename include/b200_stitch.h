@@ -180,6 +180,31 @@ void bs_host_free(void *p);
 int bs_get_stats(const bs_handle *h, bs_stats *out);
 
 /*
+ * Frame-parallel dispatch over several GPUs of one box.  Replaces the single loop of
+ * tools/stitch/main.cpp:143-155 for video: every output frame is independent (the canvas is re-created at
+ * :144), so frame f runs on GPU f mod G with a full replica of the calibration; no data is exchanged between
+ * GPUs.  A pool owns one handle and one host thread per device (device_ids[n_devices], NULL = 0..n-1; an id may
+ * repeat).  Submit frames in order from ONE thread; host buffers must stay valid until bs_pool_wait(frame).
+ * bs_pool_submit blocks while bs_pool_depth() frames are outstanding, so wait for old frames as you go:
+ * waiting for frames 0, 1, 2, ... in order yields the panoramas in frame order.  bs_pool_wait(f) returns once
+ * frame f is in `out`; after an error every later call returns that error (bs_pool_last_error has the text).
+ * Lens models (bs_pool_set_undistort) go to every replica and must be set before the first frame.
+ */
+typedef struct bs_pool bs_pool;
+int bs_pool_create(int n_devices, const int *device_ids, int n_cams, const int *src_w, const int *src_h,
+                   int canvas_w, int canvas_h, const double *H, unsigned flags, bs_pool **out);
+int bs_pool_destroy(bs_pool *p);
+int bs_pool_size(const bs_pool *p);                 /* number of replicas */
+int bs_pool_depth(const bs_pool *p);                /* frames that may be outstanding: replicas x bs_pipeline_depth */
+bs_handle *bs_pool_handle(bs_pool *p, int i);       /* replica i (for bs_get_stats) */
+const char *bs_pool_last_error(const bs_pool *p);
+int bs_pool_set_undistort(bs_pool *p, int cam, const double K[9], const double *dist, int n_dist);
+int bs_pool_submit(bs_pool *p, const uint8_t *const *frames, const size_t *pitch, uint8_t *out, size_t out_pitch,
+                   int64_t *frame_index);
+int bs_pool_wait(bs_pool *p, int64_t frame_index);
+int bs_pool_sync(bs_pool *p);                       /* every submitted frame is done */
+
+/*
  * One panorama frame on DEVICE buffers without allocating anything.  No counterpart in the
  * reference (it has no GPU path and no allocation discipline); added for callers that own all their
  * memory and must not allocate while running -- frame loops with a fixed device-memory budget,

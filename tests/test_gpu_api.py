@@ -157,3 +157,56 @@ def test_general_staged_kernel_still_exact_on_compact_plans():
         assert out.returncode == 0, out.stderr[-1500:]
         res = json.loads(out.stdout.strip().splitlines()[-1])
         assert res["kernel"] == kernel and res["sha"] == want, res
+
+
+@pytest.mark.parametrize("devices", [[0, 0, 0], "all"])
+def test_pool_returns_frames_in_order(devices):
+    """bs_pool_*: frame f -> replica f mod G, panoramas in frame order.  [0, 0, 0] runs three replicas on one GPU
+    (the dispatch logic without needing a multi-GPU box); "all" uses every visible GPU and needs at least two."""
+    p = pkg()
+    if devices == "all":
+        n = p.device_count()
+        if n < 2:
+            pytest.skip("needs at least 2 GPUs")
+        devices = list(range(n))
+    w = workloads().get("cfg2")
+    n_frames = 4 * len(devices) + 3
+    frames = [[oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, f, oracle.NOISE) for i in range(2)] for f in range(n_frames)]
+    with p.Pool(devices, [w.src_wh] * 2, w.canvas_wh, w.H) as pool:
+        assert pool.size == len(devices) and pool.depth == 3 * len(devices)
+        outs = [np.empty((w.canvas_wh[1], w.canvas_wh[0], 3), np.uint8) for _ in range(pool.depth)]
+        got_sha, waited = [], 0
+        for f in range(n_frames):
+            if f - waited >= pool.depth:          # the buffer of frame f - depth is about to be reused
+                pool.wait(waited)
+                got_sha.append(hashlib.sha256(outs[waited % pool.depth].tobytes()).hexdigest())
+                waited += 1
+            assert pool.submit(frames[f], outs[f % pool.depth]) == f
+        while waited < n_frames:
+            pool.wait(waited)
+            got_sha.append(hashlib.sha256(outs[waited % pool.depth].tobytes()).hexdigest())
+            waited += 1
+        pool.sync()
+        per_replica = [pool.replica_stats(i)["frames_submitted"] for i in range(pool.size)]
+    assert sum(per_replica) == n_frames and max(per_replica) - min(per_replica) <= 1
+    want = [hashlib.sha256(oracle.stitch(fr, w.H, w.canvas_wh).tobytes()).hexdigest() for fr in frames]
+    assert got_sha == want
+
+
+def test_pool_reports_a_failed_frame():
+    p = pkg()
+    w = workloads().get("cfg2")
+    fr = [oracle.gen_frame(w.src_wh[0], w.src_wh[1], i, 0, oracle.NOISE) for i in range(2)]
+    out = np.empty((w.canvas_wh[1], w.canvas_wh[0], 3), np.uint8)
+    with p.Pool([0, 0], [w.src_wh] * 2, w.canvas_wh, w.H) as pool:
+        f0 = pool.submit(fr, out)
+        pool.wait(f0)
+        import ctypes
+        L = p.lib()
+        ptrs = (ctypes.c_void_p * 2)(*[f.ctypes.data for f in fr])
+        bad = (ctypes.c_size_t * 2)(10, 10)              # pitch below the frame width: the replica's bs_submit fails
+        idx = ctypes.c_int64(-1)
+        assert L.bs_pool_submit(pool._p, ptrs, bad, out.ctypes.data, out.strides[0], ctypes.byref(idx)) == 0
+        with pytest.raises(p.StitchError) as e:
+            pool.wait(idx.value)
+        assert "frame 1 on device 0" in str(e.value) and "pitch" in str(e.value)

@@ -28,7 +28,8 @@ def test_defaults_match_reference_struct():
     o = parse()
     assert o == {"valid": True, "verbosity": 0, "interactive": False, "video": False, "delay": 300,
                  "number_of_frames": 30, "board_width": 5, "board_height": 3, "angle": 1, "mode": "chain",
-                 "calibrate_config": "", "stitch_config": "stitch.conf.xml", "output": "", "file_paths": []}
+                 "calibrate_config": "", "stitch_config": "stitch.conf.xml", "output": "", "device": 0, "devices": [],
+                 "file_paths": []}
 
 
 def test_flags_and_prefix_quirks():
@@ -252,3 +253,32 @@ def test_stitch_tool_video_mode_with_lens_models(tmp_path):
     for k in range(3):
         und = [oracle.undistort(frames[c][k + 1], Ks[c], dists[c]) for c in range(2)]
         assert np.array_equal(read_ppm(tmp_path / f"u_{k:03d}.ppm"), oracle.stitch(und, Hs, (200, 70))), f"frame {k}"
+
+
+def test_devices_flag_forms():
+    out = parse("--devices=0-2,5", "--device=3")
+    assert out["devices"] == [0, 1, 2, 5] and out["device"] == 3
+    assert parse("--devices=1")["devices"] == [1]
+    assert parse("--devices=3-1")["valid"] is False and parse("--devices=")["valid"] is False
+
+
+@pytest.mark.gpu
+def test_stitch_tool_video_mode_over_a_pool_of_replicas(tmp_path):
+    """--devices=0,0: two replicas (on one GPU here; any list of GPUs works), frame f on replica f mod 2,
+    panoramas written in frame order."""
+    rng = np.random.default_rng(9)
+    n_frames = 9
+    Hs = [np.array([[1.02, 0.0, 2.0], [0.0, 1.02, 1.0], [0, 0, 1.0]]), np.array([[1.0, 0.01, 90.0], [0.0, 1.0, 2.0], [0, 1e-5, 1.0]])]
+    frames = [[rng.integers(0, 256, (64, 96, 3), dtype=np.uint8) for _ in range(n_frames + 1)] for _ in range(2)]
+    for c in range(2):
+        with open(tmp_path / f"cam{c}.ppms", "wb") as f:
+            for im in frames[c]:
+                f.write(b"P6\n96 64\n255\n" + np.ascontiguousarray(im[:, :, ::-1]).tobytes())
+    cfg = tmp_path / "v.xml"
+    make_config(cfg, 1, [tmp_path / "cam0.ppms", tmp_path / "cam1.ppms"], (200, 70), Hs)
+    r = run_stitch(tmp_path, f"--s-conf={cfg}", "--out=p_%03ld.ppm", "--devices=0,0", "-v=1")
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert f"{n_frames} frames on 2 GPU(s)" in r.stdout
+    for k in range(n_frames):
+        want = oracle.stitch([frames[0][k + 1], frames[1][k + 1]], Hs, (200, 70))
+        assert np.array_equal(read_ppm(tmp_path / f"p_{k:03d}.ppm"), want), f"frame {k}"

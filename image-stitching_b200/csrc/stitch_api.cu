@@ -54,7 +54,14 @@ struct LensModel {
     double k[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // k1 k2 p1 p2 k3 k4 k5 k6
     double *d_xs = nullptr, *d_ys = nullptr;  // device tables, see stitch_undistort.cuh
     uint32_t *d_map = nullptr;                // cached fixed-point map (w * h words), nullptr: evaluate per frame
-    uint64_t bytes = 0;                       // device memory behind the three pointers (counted in bs_handle::device_bytes)
+    uint64_t bytes = 0;                       // device memory behind the pointers (counted in bs_handle::device_bytes)
+    // block plan of the lens field for the compact frame kernel (stitch_undistort.cuh: lens_plan_kernel)
+    bool plan_ok = false;
+    bs::WorkItem *d_items = nullptr;
+    int *d_warp_start = nullptr;
+    int grid = 0, smem_bytes = 0, box_h = 0;
+    TmapEntry tmaps[kTmapCacheWays];          // source frames come from small rings
+    unsigned tmap_next = 0;
 };
 
 }  // namespace
@@ -566,12 +573,63 @@ bs::UndistortArgs lens_args(const bs_handle *h, const LensModel &m, int i)
 }
 
 // cv::undistort of one frame of camera `cam` (which has a lens model) between device buffers.
-int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8_t *d_dst, size_t dpitch, cudaStream_t stream)
+// `sources_from_kernel`: see launch_frame.
+int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8_t *d_dst, size_t dpitch, cudaStream_t stream,
+                  bool sources_from_kernel)
 {
-    const LensModel &m = h->lens[cam];
+    LensModel &m = h->lens[cam];
     const bool aligned4 = (reinterpret_cast<uintptr_t>(d_src) & 3) == 0 && (spitch & 3) == 0 &&
                           (reinterpret_cast<uintptr_t>(d_dst) & 3) == 0 && (dpitch & 3) == 0;
-    if (m.d_map && aligned4) {
+    if (m.plan_ok && aligned16(d_src, spitch) && aligned16(d_dst, dpitch)) {
+        // the lens field as a block plan: the compact frame kernel resamples the frame (stitch_undistort.cuh)
+        bs::Fast2Args FA;
+        memset(&FA.F, 0, sizeof FA.F);
+        FA.F.n_cams = 1;
+        FA.F.cam[0].ptr = static_cast<const uint8_t *>(d_src);
+        FA.F.cam[0].pitch = (long long)spitch;
+        FA.F.cam[0].w = h->sw[cam];
+        FA.F.cam[0].h = h->sh[cam];
+        FA.F.canvas = d_dst;
+        FA.F.cpitch = (long long)dpitch;
+        FA.F.W = h->sw[cam];
+        FA.F.H = h->sh[cam];
+        FA.F.block_w = 1;
+        FA.F.canvas_in_4g = canvas_in_4g(d_dst, dpitch, h->sh[cam]);
+        TmapEntry *hit = nullptr;
+        for (int k = 0; k < kTmapCacheWays && !hit; ++k)
+            if (m.tmaps[k].ptr == d_src && m.tmaps[k].pitch == spitch) hit = &m.tmaps[k];
+        if (!hit) {
+            hit = &m.tmaps[m.tmap_next++ % kTmapCacheWays];
+            hit->ptr = nullptr;
+            const int er = encode_frame_map(&hit->map, d_src, spitch, h->sh[cam], bs::kRawPitch / 4, m.box_h);
+            if (er != 0) return fail(h, BS_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for the lens plan of camera %d", er, cam);
+            hit->ptr = d_src;
+            hit->pitch = spitch;
+        }
+        FA.tmap[0] = hit->map;
+        FA.items = m.d_items;
+        FA.warp_start = m.d_warp_start;
+        FA.box_bytes = bs::kRawPitch * m.box_h;
+        FA.wait_sources = sources_from_kernel ? 1 : 0;
+        FA.lens_mode = 1;
+        FA.lens = lens_args(h, m, cam);
+        FA.lens.src = static_cast<const uint8_t *>(d_src);
+        FA.lens.dst = d_dst;
+        FA.lens.spitch = (long long)spitch;
+        FA.lens.dpitch = (long long)dpitch;
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof cfg);
+        cfg.gridDim = dim3(m.grid);
+        cfg.blockDim = dim3(bs::kFast2Threads);
+        cfg.dynamicSmemBytes = (size_t)m.smem_bytes;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel, FA));
+    } else if (m.d_map && aligned4) {
         // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
         bs::RemapArgs R;
         R.src = static_cast<const uint8_t *>(d_src);
@@ -609,7 +667,7 @@ int alloc_undist(bs_handle *h, std::vector<uint8_t *> &tmp, int cam)
 // cv::undistort for the cameras that have a lens model: src frame -> tmp[i]; the pointers the warp
 // should read are returned in out_frames / out_pitch.  Stream-ordered before the frame kernel.
 int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pitch, std::vector<uint8_t *> &tmp,
-                     const void **out_frames, size_t *out_pitch, cudaStream_t stream, bool *launched = nullptr)
+                     const void **out_frames, size_t *out_pitch, cudaStream_t stream, bool sources_from_kernel, bool *launched = nullptr)
 {
     if (launched) *launched = false;
     for (int i = 0; i < h->n_cams; ++i) {
@@ -619,7 +677,7 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
         const LensModel &m = h->lens[i];
         if ((int)tmp.size() < h->n_cams || !tmp[i])     // allocated by bs_set_undistort / ensure_ring, never here
             return fail(h, BS_ERR_INVALID_ARG, "internal: no undistort buffer for camera %d", i);
-        const int rc = undistort_one(h, i, d_frames[i], pitch[i], tmp[i], h->d_frame_pitch[i], stream);
+        const int rc = undistort_one(h, i, d_frames[i], pitch[i], tmp[i], h->d_frame_pitch[i], stream, sources_from_kernel);
         if (rc != BS_OK) return rc;
         if (launched) *launched = true;
         out_frames[i] = tmp[i];
@@ -841,7 +899,7 @@ int issue_frame(bs_handle *h, Slot &s, const uint8_t *const *frames, const size_
     std::vector<size_t> warp_pitch(h->n_cams);
     bool lens_ran = false;
     int rc = undistort_frames(h, d_frames.data(), h->d_frame_pitch.data(), s.d_undist, warp_frames.data(), warp_pitch.data(),
-                              h->s_compute, &lens_ran);
+                              h->s_compute, false, &lens_ran);
     if (rc != BS_OK) return rc;
     // without a lens kernel the frames reach the device by copies on another stream, ordered by an event
     rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), s.d_canvas, h->d_canvas_pitch, keep, h->s_compute, lens_ran);
@@ -940,6 +998,8 @@ int bs_destroy(bs_handle *h)
         cudaFree(m.d_xs);
         cudaFree(m.d_ys);
         cudaFree(m.d_map);
+        cudaFree(m.d_items);
+        cudaFree(m.d_warp_start);
     }
     for (uint8_t *p : h->d_undist) cudaFree(p);
     for (Slot &s : h->ring) {
@@ -1049,7 +1109,8 @@ int bs_submit_device_ex(bs_handle *h, const void *const *d_frames, const size_t 
     std::vector<const void *> warp_frames(h->n_cams);
     std::vector<size_t> warp_pitch(h->n_cams);
     bool lens_ran = false;
-    int rc = undistort_frames(h, d_frames, pitch, h->d_undist, warp_frames.data(), warp_pitch.data(), st, &lens_ran);
+    const bool from_kernel = !(submit_flags & BS_SUBMIT_SOURCES_SETTLED);
+    int rc = undistort_frames(h, d_frames, pitch, h->d_undist, warp_frames.data(), warp_pitch.data(), st, from_kernel, &lens_ran);
     if (rc == BS_OK)
         rc = launch_frame(h, warp_frames.data(), warp_pitch.data(), static_cast<uint8_t *>(d_canvas), canvas_pitch,
                           (h->flags & BS_FLAG_KEEP_CANVAS) != 0, st, lens_ran || !(submit_flags & BS_SUBMIT_SOURCES_SETTLED));
@@ -1083,8 +1144,74 @@ void clear_lens(bs_handle *h, LensModel &m)
     cudaFree(m.d_xs);
     cudaFree(m.d_ys);
     cudaFree(m.d_map);
+    cudaFree(m.d_items);
+    cudaFree(m.d_warp_start);
     h->device_bytes -= m.bytes;
     m = LensModel();
+}
+// Block plan of camera `cam`'s lens field (lens_plan_kernel) for the compact frame kernel.  Leaves m.plan_ok
+// false when the field does not fit it (source boxes too large, frame too small): the caller then falls back
+// to the cached per-pixel map.
+int build_lens_plan(bs_handle *h, LensModel &m, int cam)
+{
+    const int w = h->sw[cam], hh = h->sh[cam];
+    if (!get_encoder() || w * 3 < bs::kRawPitch || hh < bs::kRawRows) return BS_OK;
+    const int blocks_x = (w + bs::kBlockW - 1) / bs::kBlockW, blocks_y = (hh + bs::kBlockH - 1) / bs::kBlockH;
+    const int n_blocks = blocks_x * blocks_y;
+    const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)n_blocks;
+    void *d_plan = nullptr;
+    BS_CUDA(h, cudaMalloc(&d_plan, raw_bytes));
+    bs::LensPlanArgs P;
+    P.U = lens_args(h, m, cam);
+    P.blocks_x = blocks_x;
+    P.blocks_y = blocks_y;
+    P.out = static_cast<bs::BlockRec *>(d_plan);
+    bs::lens_plan_kernel<<<dim3((blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, blocks_y), 32 * bs::kPlanWarps, 0, h->s_compute>>>(P);
+    std::vector<bs::BlockRec> recs(n_blocks);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(recs.data(), d_plan, raw_bytes, cudaMemcpyDeviceToHost, h->s_compute);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
+    if (e != cudaSuccess) {
+        cudaFree(d_plan);
+        return fail(h, BS_ERR_CUDA, "lens plan failed: %s", cudaGetErrorString(e));
+    }
+    h->kernel_launches++;
+    std::vector<bs::WorkItem> items((size_t)n_blocks * bs::kMaxLayers);
+    PlanLayout L;
+    layout_plan(recs.data(), n_blocks, 1, items.data(), &L, true);
+    int optin = 0, sms = 0, per_sm = 0;
+    const int smem = bs::kWarps2 * bs::kWarp2Smem + 128;
+    cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    if (!L.compact || L.n_fast == 0 || smem > optin ||
+        cudaFuncSetAttribute(bs::stitch_fast2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel, bs::kFast2Threads, smem) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        cudaFree(d_plan);
+        return BS_OK;
+    }
+    m.grid = std::max(1, std::min((n_blocks + bs::kWarps2 - 1) / bs::kWarps2, per_sm * sms));
+    m.smem_bytes = smem;
+    m.box_h = L.box_h[0];
+    const int n_warps = m.grid * bs::kWarps2;
+    std::vector<bs::WorkItem> grouped(items.size());
+    std::vector<int> warp_start(n_warps + 1);
+    group_items_by_warp(items.data(), L.n_items - L.n_two, L.n_two, n_warps, grouped.data(), warp_start.data());
+    const size_t ws_bytes = sizeof(int) * (size_t)(n_warps + 1);
+    e = upload_now(h, d_plan, grouped.data(), sizeof(bs::WorkItem) * (size_t)L.n_items);     // <= raw_bytes: one item per block here
+    if (e == cudaSuccess) e = cudaMalloc(&m.d_warp_start, ws_bytes);
+    if (e == cudaSuccess) e = upload_now(h, m.d_warp_start, warp_start.data(), ws_bytes);
+    if (e != cudaSuccess) {
+        cudaFree(d_plan);
+        cudaFree(m.d_warp_start);
+        m.d_warp_start = nullptr;
+        return fail(h, BS_ERR_CUDA, "lens plan upload failed: %s", cudaGetErrorString(e));
+    }
+    m.d_items = static_cast<bs::WorkItem *>(d_plan);
+    m.bytes += raw_bytes + ws_bytes;
+    h->device_bytes += raw_bytes + ws_bytes;
+    m.plan_ok = true;
+    return BS_OK;
 }
 }  // namespace
 
@@ -1126,8 +1253,10 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     int rc = BS_OK;
     if (e == cudaSuccess) rc = alloc_undist(h, h->d_undist, cam);
     for (size_t k = 0; rc == BS_OK && e == cudaSuccess && k < h->ring.size(); ++k) rc = alloc_undist(h, h->ring[k].d_undist, cam);
-    if (e == cudaSuccess && rc == BS_OK && want_map) {
-        // The map depends on the calibration only: evaluate it once, resample every frame from it.
+    // The lens field depends on the calibration only.  Preferred form: a block plan for the compact frame kernel.
+    if (e == cudaSuccess && rc == BS_OK && want_map && !getenv("BS_DEBUG_NO_LENS_PLAN")) rc = build_lens_plan(h, m, cam);
+    if (e == cudaSuccess && rc == BS_OK && want_map && !m.plan_ok) {
+        // Otherwise: one packed map word per pixel, evaluated once, every frame resampled from it.
         e = cudaMalloc(&m.d_map, map_bytes);
         if (e == cudaSuccess) e = cudaMalloc(&d_overflow, sizeof(int));
         if (e == cudaSuccess) e = cudaMemsetAsync(d_overflow, 0, sizeof(int), h->s_compute);
@@ -1178,7 +1307,7 @@ int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch,
         if (cudaMemcpy2DAsync(d_dst, dpitch, d_src, spitch, (size_t)h->sw[cam] * 3, h->sh[cam], cudaMemcpyDeviceToDevice, st) != cudaSuccess)
             rc = fail(h, BS_ERR_CUDA, "bs_undistort_device: copy failed: %s", cudaGetErrorString(cudaGetLastError()));
     } else {
-        rc = undistort_one(h, cam, d_src, spitch, static_cast<uint8_t *>(d_dst), dpitch, st);
+        rc = undistort_one(h, cam, d_src, spitch, static_cast<uint8_t *>(d_dst), dpitch, st, true);
     }
     if (prev_dev != h->device) cudaSetDevice(prev_dev);
     return rc;
@@ -1207,7 +1336,7 @@ int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, 
         const void *in[1] = {d_src};
         const void *out[1] = {nullptr};
         size_t out_pitch[1] = {0};
-        if (e == cudaSuccess) rc = undistort_frames(hd, in, &pitch, hd->d_undist, out, out_pitch, hd->s_compute);
+        if (e == cudaSuccess) rc = undistort_frames(hd, in, &pitch, hd->d_undist, out, out_pitch, hd->s_compute, true);
         if (e == cudaSuccess && rc == BS_OK) e = cudaStreamSynchronize(hd->s_compute);
         if (e == cudaSuccess && rc == BS_OK)
             e = cudaMemcpy2D(dst, dpitch, out[0], out_pitch[0], (size_t)w * 3, h, cudaMemcpyDeviceToHost);

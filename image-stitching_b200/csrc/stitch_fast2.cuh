@@ -19,7 +19,7 @@
 
 #include <type_traits>
 
-#include "stitch_fast.cuh"
+#include "stitch_undistort.cuh"
 
 namespace bs {
 
@@ -69,6 +69,8 @@ struct Fast2Args {
     int box_bytes;                         // 128 * box rows (all cameras use the same box; what the mbarrier expects)
     int wait_sources;                      // 1: the source frames may come from the kernel just before this one in
                                            // the stream: order every source read behind it (griddepcontrol.wait first)
+    int lens_mode;                         // 1: the plan is a lens plan (cv::undistort of one frame, stitch_undistort.cuh):
+    UndistortArgs lens;                    //    its EXACT blocks evaluate this model with BORDER_CONSTANT 0
 };
 
 // ---- packed fp32 pairs (x in the low half, y in the high half) -------------------------------------
@@ -393,6 +395,20 @@ __device__ __noinline__ void patch_exact2(const FrameArgs &F, const CamDev &cam,
     }
 }
 
+// The same for a lens plan: the flagged rows are redone with the lens model's exact coordinates.
+__device__ __noinline__ void patch_lens2(const UndistortArgs &U, uint32_t conv_origin, uint32_t out_blk, uint32_t group_mask, int x,
+                                         int y0, int lane)
+{
+#pragma unroll 1
+    for (int k = 0; k < kRun; ++k) {
+        if (!((group_mask >> (k >> 2)) & 1)) continue;     // warp-uniform
+        int sx, sy, a, b;
+        undistort_coord(U, x, y0 + k, sx, sy, a, b);
+        const uint32_t px = sample_conv(conv_origin + (uint32_t)(sy * kConvPitch + sx * 4), tap_weights2((uint32_t)a, (uint32_t)b));
+        store_px_bytes(out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane, px);
+    }
+}
+
 __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kernel(const __grid_constant__ Fast2Args A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -533,8 +549,11 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                     run_full2<false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
                 if (groups != 0u) {
                     __syncwarp();
-                    patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane,
-                                 (int)by * kBlockH, lane);
+                    if (A.lens_mode)
+                        patch_lens2(A.lens, conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane, (int)by * kBlockH, lane);
+                    else
+                        patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane,
+                                     (int)by * kBlockH, lane);
                 }
             } else {
                 const CamDev &cam = A.F.cam[(r.y >> 16) & 0xFFu];
@@ -559,7 +578,10 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                 // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j; the item names its row groups j
                 const uint32_t rows = r.y >> 24;
                 for (int j = 0; j < kRun / 4; ++j)
-                    if ((rows >> j) & 1u) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+                    if ((rows >> j) & 1u) {
+                        if (A.lens_mode) lens_quad(A.lens, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+                        else exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+                    }
             } else if (!wrote && A.F.keep_canvas) {
                 // nobody writes here and the canvas keeps its contents
             } else if (tx0 + kBlockW <= A.F.W && ty0 + kRun <= A.F.H) {

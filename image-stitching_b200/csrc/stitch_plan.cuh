@@ -94,16 +94,11 @@ constexpr int kItemRawOffShift = 4;
 // explicit intrinsic so plan kernel and frame kernel execute the same instruction sequence.
 constexpr int kMagicBias = 0x4B400000;   // bits of 12582912.0f = 1.5 * 2^23 (a multiple of 32)
 
-__device__ __forceinline__ BlockCoef block_coef(const double *__restrict__ M, int xc, int yc)
+// The expansion in the form the frame kernel evaluates it, from the centre value g = (gx, gy) and its first and
+// second derivatives with respect to the canvas column u and row v (h*uu, h*vv: the pure ones already halved).
+__device__ __forceinline__ BlockCoef make_block_coef(double gx, double gy, double gxu, double gxv, double gyu, double gyv, double hxuu,
+                                                     double xuv, double hxvv, double hyuu, double yuv, double hyvv)
 {
-    const double dx = (double)xc, dy = (double)yc;
-    const double Xn = fma(M[1], dy, fma(M[0], dx, M[2]));
-    const double Yn = fma(M[4], dy, fma(M[3], dx, M[5]));
-    const double Wn = fma(M[7], dy, fma(M[6], dx, M[8]));
-    const double inv = 1.0 / Wn;
-    const double gx = fmin(fmax(32.0 * Xn * inv, -1.0e9), 1.0e9), gy = fmin(fmax(32.0 * Yn * inv, -1.0e9), 1.0e9);
-    const double gxu = (32.0 * M[0] - M[6] * gx) * inv, gxv = (32.0 * M[1] - M[7] * gx) * inv;
-    const double gyu = (32.0 * M[3] - M[6] * gy) * inv, gyv = (32.0 * M[4] - M[7] * gy) * inv;
     BlockCoef c;
     c.ix = (int)rint(gx) & ~31;
     c.iy = (int)rint(gy) & ~31;
@@ -119,13 +114,27 @@ __device__ __forceinline__ BlockCoef block_coef(const double *__restrict__ M, in
     c.xv = (float)(gxv - 32.0 * c.nxv);
     c.yu = (float)(gyu - 32.0 * c.nyu);
     c.yv = (float)(gyv - 32.0 * c.nyv);
-    c.hxuu = (float)(-M[6] * gxu * inv);
-    c.hxvv = (float)(-M[7] * gxv * inv);
-    c.xuv = (float)(-(M[6] * gxv + M[7] * gxu) * inv);
-    c.hyuu = (float)(-M[6] * gyu * inv);
-    c.hyvv = (float)(-M[7] * gyv * inv);
-    c.yuv = (float)(-(M[6] * gyv + M[7] * gyu) * inv);
+    c.hxuu = (float)hxuu;
+    c.hxvv = (float)hxvv;
+    c.xuv = (float)xuv;
+    c.hyuu = (float)hyuu;
+    c.hyvv = (float)hyvv;
+    c.yuv = (float)yuv;
     return c;
+}
+
+__device__ __forceinline__ BlockCoef block_coef(const double *__restrict__ M, int xc, int yc)
+{
+    const double dx = (double)xc, dy = (double)yc;
+    const double Xn = fma(M[1], dy, fma(M[0], dx, M[2]));
+    const double Yn = fma(M[4], dy, fma(M[3], dx, M[5]));
+    const double Wn = fma(M[7], dy, fma(M[6], dx, M[8]));
+    const double inv = 1.0 / Wn;
+    const double gx = fmin(fmax(32.0 * Xn * inv, -1.0e9), 1.0e9), gy = fmin(fmax(32.0 * Yn * inv, -1.0e9), 1.0e9);
+    const double gxu = (32.0 * M[0] - M[6] * gx) * inv, gxv = (32.0 * M[1] - M[7] * gx) * inv;
+    const double gyu = (32.0 * M[3] - M[6] * gy) * inv, gyv = (32.0 * M[4] - M[7] * gy) * inv;
+    return make_block_coef(gx, gy, gxu, gxv, gyu, gyv, -M[6] * gxu * inv, -(M[6] * gxv + M[7] * gxu) * inv, -M[7] * gxv * inv,
+                           -M[6] * gyu * inv, -(M[6] * gyv + M[7] * gyu) * inv, -M[7] * gyv * inv);
 }
 
 // Per-lane form: everything that depends on the column u = lane - 16 only.

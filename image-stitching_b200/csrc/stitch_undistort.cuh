@@ -34,9 +34,8 @@ struct UndistortArgs {
     double k1, k2, p1, p2, k3, k4, k5, k6;
 };
 
-// Fixed-point source position of destination pixel (j, i): texel (sx, sy) as OpenCV's int16 map holds
-// it, fractions a, b in 1/32.
-__device__ __forceinline__ void undistort_coord(const UndistortArgs &A, int j, int i, int &sx, int &sy, int &a, int &b)
+// Source position of destination pixel (j, i) in 1/32 pixel, before rounding (OpenCV's operation order).
+__device__ __forceinline__ void undistort_real(const UndistortArgs &A, int j, int i, double &fu, double &fv)
 {
     const double x = __dmul_rn(A.xs[j], A.winv), y = __dmul_rn(A.ys[i], A.winv);
     const double x2 = __dmul_rn(x, x), y2 = __dmul_rn(y, y);
@@ -49,12 +48,27 @@ __device__ __forceinline__ void undistort_coord(const UndistortArgs &A, int j, i
     const double yd = __dadd_rn(__dadd_rn(__dmul_rn(y, kr), __dmul_rn(A.p1, __dadd_rn(r2, __dmul_rn(2.0, y2)))),
                                 __dmul_rn(A.p2, _2xy));
     const double u = __dadd_rn(__dmul_rn(A.fx, xd), A.u0), v = __dadd_rn(__dmul_rn(A.fy, yd), A.v0);
-    const double fu = __dmul_rn(u, (double)kFracOne), fv = __dmul_rn(v, (double)kFracOne);
-    const int iu = (fu == fu) ? __double2int_rn(fu) : INT_MIN, iv = (fv == fv) ? __double2int_rn(fv) : INT_MIN;
+    fu = __dmul_rn(u, (double)kFracOne);
+    fv = __dmul_rn(v, (double)kFracOne);
+}
+
+// Fixed-point source position of destination pixel (j, i): texel (sx, sy) as OpenCV's int16 map holds
+// it, fractions a, b in 1/32; (iu, iv) = the rounded 1/32-pixel coordinates before the int16 cut.
+__device__ __forceinline__ void undistort_coord(const UndistortArgs &A, int j, int i, int &sx, int &sy, int &a, int &b, int &iu, int &iv)
+{
+    double fu, fv;
+    undistort_real(A, j, i, fu, fv);
+    iu = (fu == fu) ? __double2int_rn(fu) : INT_MIN;
+    iv = (fv == fv) ? __double2int_rn(fv) : INT_MIN;
     sx = (int)(short)(iu >> kFracBits);   // OpenCV stores int16
     sy = (int)(short)(iv >> kFracBits);
     a = iu & (kFracOne - 1);
     b = iv & (kFracOne - 1);
+}
+__device__ __forceinline__ void undistort_coord(const UndistortArgs &A, int j, int i, int &sx, int &sy, int &a, int &b)
+{
+    int iu, iv;
+    undistort_coord(A, j, i, sx, sy, a, b, iu, iv);
 }
 
 // Bilinear sample with BORDER_CONSTANT 0, tap by tap (any position, any alignment).
@@ -83,6 +97,120 @@ __global__ void __launch_bounds__(256) undistort_kernel(const __grid_constant__ 
     int sx, sy, a, b;
     undistort_coord(A, j, i, sx, sy, a, b);
     undistort_sample_checked(A.src, A.spitch, A.w, A.h, sx, sy, a, b, A.dst + (long long)i * A.dpitch + (long long)j * 3);
+}
+
+// ---- block plan of a lens model -------------------------------------------------------------------
+// The lens field is as smooth as a homography's, so cv::undistort gets the warp's treatment: the frame is
+// cut into the same 32x16 blocks, and a block all of whose pixels are interior samples (four taps inside the
+// frame) becomes a FAST item of the compact frame kernel (stitch_fast2.cuh) -- source box by TMA, coordinates
+// from a second-order fp32 expansion that this kernel checks pixel by pixel against undistort_coord().
+// Blocks with a pixel that has a tap outside the frame (BORDER_CONSTANT 0 applies there), or that stick out
+// of the frame, are EXACT (lens_quad below); blocks whose pixels all fall outside are EMPTY (zeros).
+// One warp per block, lane = column, as in plan_kernel.
+struct LensPlanArgs {
+    UndistortArgs U;
+    int blocks_x, blocks_y;
+    BlockRec *out;
+};
+
+__global__ void __launch_bounds__(32 * kPlanWarps) lens_plan_kernel(const __grid_constant__ LensPlanArgs P)
+{
+    const UndistortArgs &A = P.U;
+    const int lane = threadIdx.x & 31;
+    const int bx = blockIdx.x * kPlanWarps + (threadIdx.x >> 5), by = blockIdx.y;
+    if (bx >= P.blocks_x) return;
+    const unsigned FULLMASK = 0xffffffffu;
+    const int x = bx * kBlockW + lane, y0 = by * kBlockH;
+    const bool whole = bx * kBlockW + kBlockW <= A.w && y0 + kBlockH <= A.h;
+
+    BlockRec rec;
+    memset(&rec, 0, sizeof rec);
+    rec.bx = (uint16_t)bx;
+    rec.by = (uint16_t)by;
+    BlockRec *dst = P.out + (size_t)by * P.blocks_x + bx;
+
+    // the expansion around the block centre: derivatives by central differences of the exact (unrounded) field
+    BlockCoef bc;
+    memset(&bc, 0, sizeof bc);
+    if (whole) {
+        const int xc = bx * kBlockW + kBlockW / 2, yc = y0 + kBlockH / 2;      // xc +- 1, yc +- 1 lie inside the frame
+        double g[3][3][2];
+        for (int dy = -1; dy <= 1; ++dy)
+            for (int dx = -1; dx <= 1; ++dx) undistort_real(A, xc + dx, yc + dy, g[dy + 1][dx + 1][0], g[dy + 1][dx + 1][1]);
+        double d[2][6];     // per coordinate: value, d/du, d/dv, half d2/du2, d2/dudv, half d2/dv2
+        for (int c = 0; c < 2; ++c) {
+            d[c][0] = fmin(fmax(g[1][1][c], -1.0e9), 1.0e9);
+            d[c][1] = 0.5 * (g[1][2][c] - g[1][0][c]);
+            d[c][2] = 0.5 * (g[2][1][c] - g[0][1][c]);
+            d[c][3] = 0.5 * (g[1][2][c] - 2.0 * g[1][1][c] + g[1][0][c]);
+            d[c][4] = 0.25 * (g[2][2][c] - g[2][0][c] - g[0][2][c] + g[0][0][c]);
+            d[c][5] = 0.5 * (g[2][1][c] - 2.0 * g[1][1][c] + g[0][1][c]);
+        }
+        bc = make_block_coef(d[0][0], d[1][0], d[0][1], d[0][2], d[1][1], d[1][2], d[0][3], d[0][4], d[0][5], d[1][3], d[1][4], d[1][5]);
+    }
+    const LaneCoef lc = lane_coef(bc, lane - kBlockW / 2);
+
+    bool all_interior = whole, all_outside = true, zf = false;
+    unsigned mism = 0u;
+    int bx0 = INT_MAX, by0 = INT_MAX, bx1 = INT_MIN, by1 = INT_MIN;
+    if (x < A.w) {
+        for (int k = 0; k < kRun; ++k) {
+            const int y = y0 + k;
+            if (y >= A.h) break;
+            int sx, sy, a, b, X, Y;
+            undistort_coord(A, x, y, sx, sy, a, b, X, Y);
+            const bool interior = sx >= 0 && sy >= 0 && sx < A.w - 1 && sy < A.h - 1 && (X >> kFracBits) == sx && (Y >> kFracBits) == sy;
+            all_interior = all_interior && interior;
+            all_outside = all_outside && (sx < -1 || sx >= A.w || sy < -1 || sy >= A.h);
+            if (interior) {
+                bx0 = min(bx0, sx);
+                by0 = min(by0, sy);
+                bx1 = max(bx1, sx + 1);
+                by1 = max(by1, sy + 1);
+                zf = zf || ((a | b) == 0);
+            }
+            if (whole) {
+                const int v = k - kRun / 2;
+                int xbits, ybits;
+                lane_coord_bits(lc, (float)v, xbits, ybits);
+                if (X != xbits + lc.bx + 32 * lc.nxv * v || Y != ybits + lc.by + 32 * lc.nyv * v) mism |= 1u << (k >> 2);
+            }
+        }
+    }
+    all_interior = __all_sync(FULLMASK, all_interior);
+    all_outside = __all_sync(FULLMASK, all_outside);
+    if (all_outside) {
+        rec.type = kBlockEmpty;
+    } else if (!all_interior) {
+        rec.type = kBlockExact;
+    } else {
+        rec.type = kBlockFast;
+        rec.n_layers = 1;
+        rec.layer[0].x0 = (int16_t)__reduce_min_sync(FULLMASK, bx0);
+        rec.layer[0].y0 = (int16_t)__reduce_min_sync(FULLMASK, by0);
+        rec.layer[0].x1 = (int16_t)__reduce_max_sync(FULLMASK, bx1);
+        rec.layer[0].y1 = (int16_t)__reduce_max_sync(FULLMASK, by1);
+        rec.layer[0].cam = 0;
+        rec.layer[0].full = 1;
+        rec.layer[0].groups = (uint8_t)__reduce_or_sync(FULLMASK, mism);
+        rec.layer[0].zero_frac = __any_sync(FULLMASK, zf) ? 1 : 0;
+        rec.coef[0] = bc;
+    }
+    if (lane == 0) *dst = rec;
+}
+
+// Four horizontally consecutive destination pixels starting at (x0, y), the exact way: fp64 lens model,
+// tap by tap with BORDER_CONSTANT 0 (the EXACT blocks of a lens plan).
+__device__ __forceinline__ void lens_quad(const UndistortArgs &A, int x0, int y)
+{
+    if (y >= A.h) return;
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        if (x >= A.w) break;
+        int sx, sy, a, b;
+        undistort_coord(A, x, y, sx, sy, a, b);
+        undistort_sample_checked(A.src, A.spitch, A.w, A.h, sx, sy, a, b, A.dst + (long long)y * A.dpitch + (long long)x * 3);
+    }
 }
 
 // ---- cached map -------------------------------------------------------------------------------

@@ -93,7 +93,7 @@ def lib():
     L.bs_host_free.argtypes = [vp]
     L.bs_get_stats.argtypes = [vp, ctypes.POINTER(Stats)]
     L.bs_set_undistort.argtypes = [vp, i, dp, dp, i]
-    L.bs_undistort_device.argtypes = [vp, i, vp, sz, vp, sz, vp]
+    L.bs_undistort_device.argtypes = [vp, i, vp, sz, vp, sz, vp, ctypes.c_uint]
     L.bs_undistort.argtypes = [vp, i, i, sz, vp, sz, dp, dp, i]
     L.bs_stitch_device_static.argtypes = [i, ip, ip, ctypes.POINTER(vp), ctypes.POINTER(sz), i, i, vp, sz, dp,
                                           ctypes.c_uint, vp]
@@ -239,10 +239,10 @@ class Stitcher:
         _check(lib().bs_set_undistort(self._h, cam, K.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), dptr,
                                       int(dist.size)), self._h)
 
-    def undistort_device(self, cam, src_ptr, src_pitch, dst_ptr, dst_pitch, stream=0):
+    def undistort_device(self, cam, src_ptr, src_pitch, dst_ptr, dst_pitch, stream=0, submit_flags=0):
         """bs_undistort_device: cv::undistort of one device-resident frame of camera `cam`."""
         _check(lib().bs_undistort_device(self._h, int(cam), int(src_ptr), int(src_pitch), int(dst_ptr), int(dst_pitch),
-                                         int(stream) if stream else None), self._h)
+                                         int(stream) if stream else None, int(submit_flags)), self._h)
 
     def stats(self):
         s = Stats()

@@ -58,6 +58,7 @@ struct LensModel {
     // block plan of the lens field for the compact frame kernel (stitch_undistort.cuh: lens_plan_kernel)
     bool plan_ok = false;
     bs::WorkItem *d_items = nullptr;
+    bs::CubicCoef *d_cubic = nullptr;         // third-order terms, one per work item
     int *d_warp_start = nullptr;
     int grid = 0, smem_bytes = 0, box_h = 0;
     TmapEntry tmaps[kTmapCacheWays];          // source frames come from small rings
@@ -583,7 +584,7 @@ int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8
     if (m.plan_ok && aligned16(d_src, spitch) && aligned16(d_dst, dpitch)) {
         // the lens field as a block plan: the compact frame kernel resamples the frame (stitch_undistort.cuh)
         bs::Fast2Args FA;
-        memset(&FA.F, 0, sizeof FA.F);
+        memset(&FA, 0, sizeof FA);
         FA.F.n_cams = 1;
         FA.F.cam[0].ptr = static_cast<const uint8_t *>(d_src);
         FA.F.cam[0].pitch = (long long)spitch;
@@ -612,6 +613,7 @@ int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8
         FA.box_bytes = bs::kRawPitch * m.box_h;
         FA.wait_sources = sources_from_kernel ? 1 : 0;
         FA.lens_mode = 1;
+        FA.lens_cubic = m.d_cubic;
         FA.lens = lens_args(h, m, cam);
         FA.lens.src = static_cast<const uint8_t *>(d_src);
         FA.lens.dst = d_dst;
@@ -629,6 +631,12 @@ int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel, FA));
+        if (getenv("BS_DEBUG_SYNC")) {
+            cudaError_t e1 = cudaDeviceSynchronize();
+            if (e1 != cudaSuccess)
+                return fail(h, BS_ERR_CUDA, "[debug] lens kernel of camera %d (grid %d, smem %d, box rows %d) faulted: %s", cam, m.grid,
+                            m.smem_bytes, m.box_h, cudaGetErrorString(e1));
+        }
     } else if (m.d_map && aligned4) {
         // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
         bs::RemapArgs R;
@@ -734,8 +742,9 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         // both staged kernels take the same leading members; the general one adds its box geometry
         bs::FastArgs FA1;
         bs::Fast2Args FA2;
+        memset(&FA1, 0, sizeof FA1);
+        memset(&FA2, 0, sizeof FA2);
         bs::FrameArgs &A = h->compact ? FA2.F : FA1.F;
-        memset(&A, 0, sizeof A);
         CUtensorMap *tmaps = h->compact ? FA2.tmap : FA1.tmap;
         A.n_cams = h->n_cams;
         for (int i = 0; i < A.n_cams; ++i) {
@@ -999,6 +1008,7 @@ int bs_destroy(bs_handle *h)
         cudaFree(m.d_ys);
         cudaFree(m.d_map);
         cudaFree(m.d_items);
+        cudaFree(m.d_cubic);
         cudaFree(m.d_warp_start);
     }
     for (uint8_t *p : h->d_undist) cudaFree(p);
@@ -1145,6 +1155,7 @@ void clear_lens(bs_handle *h, LensModel &m)
     cudaFree(m.d_ys);
     cudaFree(m.d_map);
     cudaFree(m.d_items);
+    cudaFree(m.d_cubic);
     cudaFree(m.d_warp_start);
     h->device_bytes -= m.bytes;
     m = LensModel();
@@ -1160,17 +1171,27 @@ int build_lens_plan(bs_handle *h, LensModel &m, int cam)
     const int n_blocks = blocks_x * blocks_y;
     const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)n_blocks;
     void *d_plan = nullptr;
+    bs::CubicCoef *d_cubic_blocks = nullptr;
     BS_CUDA(h, cudaMalloc(&d_plan, raw_bytes));
+    if (cudaMalloc(&d_cubic_blocks, sizeof(bs::CubicCoef) * (size_t)n_blocks) != cudaSuccess) {
+        cudaFree(d_plan);
+        return fail(h, BS_ERR_CUDA, "lens plan: out of device memory");
+    }
     bs::LensPlanArgs P;
     P.U = lens_args(h, m, cam);
     P.blocks_x = blocks_x;
     P.blocks_y = blocks_y;
     P.out = static_cast<bs::BlockRec *>(d_plan);
+    P.cubic = d_cubic_blocks;
     bs::lens_plan_kernel<<<dim3((blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, blocks_y), 32 * bs::kPlanWarps, 0, h->s_compute>>>(P);
     std::vector<bs::BlockRec> recs(n_blocks);
+    std::vector<bs::CubicCoef> cubic_blocks(n_blocks);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaMemcpyAsync(recs.data(), d_plan, raw_bytes, cudaMemcpyDeviceToHost, h->s_compute);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(cubic_blocks.data(), d_cubic_blocks, sizeof(bs::CubicCoef) * (size_t)n_blocks, cudaMemcpyDeviceToHost, h->s_compute);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
+    cudaFree(d_cubic_blocks);
     if (e != cudaSuccess) {
         cudaFree(d_plan);
         return fail(h, BS_ERR_CUDA, "lens plan failed: %s", cudaGetErrorString(e));
@@ -1179,6 +1200,18 @@ int build_lens_plan(bs_handle *h, LensModel &m, int cam)
     std::vector<bs::WorkItem> items((size_t)n_blocks * bs::kMaxLayers);
     PlanLayout L;
     layout_plan(recs.data(), n_blocks, 1, items.data(), &L, true);
+    if (getenv("BS_DEBUG_PLAN_SUMMARY")) {
+        long flagged = 0, direct = 0, plain = 0;
+        for (int i = 0; i < L.n_items; ++i)
+            if (items[i].type == bs::kBlockFast) {
+                flagged += items[i].groups != 0;
+                direct += (items[i].flags & bs::kItemDirect) != 0;
+                plain += (items[i].flags & bs::kItemPlain) != 0;
+            }
+        fprintf(stderr, "[lens plan] cam %d: blocks %d: fast %lld exact %lld empty %lld; compact %d; flagged %ld direct %ld plain %ld; box rows %d\n",
+                cam, n_blocks, (long long)L.n_fast, (long long)L.n_exact, (long long)L.n_empty, (int)L.compact, flagged, direct, plain,
+                L.box_h[0]);
+    }
     int optin = 0, sms = 0, per_sm = 0;
     const int smem = bs::kWarps2 * bs::kWarp2Smem + 128;
     cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
@@ -1197,19 +1230,25 @@ int build_lens_plan(bs_handle *h, LensModel &m, int cam)
     std::vector<bs::WorkItem> grouped(items.size());
     std::vector<int> warp_start(n_warps + 1);
     group_items_by_warp(items.data(), L.n_items - L.n_two, L.n_two, n_warps, grouped.data(), warp_start.data());
-    const size_t ws_bytes = sizeof(int) * (size_t)(n_warps + 1);
-    e = upload_now(h, d_plan, grouped.data(), sizeof(bs::WorkItem) * (size_t)L.n_items);     // <= raw_bytes: one item per block here
+    const size_t ws_bytes = sizeof(int) * (size_t)(n_warps + 1), cub_bytes = sizeof(bs::CubicCoef) * (size_t)L.n_items;
+    std::vector<bs::CubicCoef> cubic_items(L.n_items);       // the third-order terms in item order
+    for (int k = 0; k < L.n_items; ++k) cubic_items[k] = cubic_blocks[(size_t)grouped[k].by * blocks_x + grouped[k].bx];
+    e = upload_now(h, d_plan, grouped.data(), sizeof(bs::WorkItem) * (size_t)L.n_items);     // <= raw_bytes (at most two items per block)
     if (e == cudaSuccess) e = cudaMalloc(&m.d_warp_start, ws_bytes);
     if (e == cudaSuccess) e = upload_now(h, m.d_warp_start, warp_start.data(), ws_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&m.d_cubic, cub_bytes);
+    if (e == cudaSuccess) e = upload_now(h, m.d_cubic, cubic_items.data(), cub_bytes);
     if (e != cudaSuccess) {
         cudaFree(d_plan);
         cudaFree(m.d_warp_start);
+        cudaFree(m.d_cubic);
         m.d_warp_start = nullptr;
+        m.d_cubic = nullptr;
         return fail(h, BS_ERR_CUDA, "lens plan upload failed: %s", cudaGetErrorString(e));
     }
     m.d_items = static_cast<bs::WorkItem *>(d_plan);
-    m.bytes += raw_bytes + ws_bytes;
-    h->device_bytes += raw_bytes + ws_bytes;
+    m.bytes += raw_bytes + ws_bytes + cub_bytes;
+    h->device_bytes += raw_bytes + ws_bytes + cub_bytes;
     m.plan_ok = true;
     return BS_OK;
 }
@@ -1291,8 +1330,11 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     return BS_OK;
 }
 
-int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch, void *d_dst, size_t dpitch, void *stream)
+int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch, void *d_dst, size_t dpitch, void *stream,
+                        unsigned submit_flags)
 {
+    if (h && (submit_flags & ~BS_SUBMIT_SOURCES_SETTLED))
+        return fail(h, BS_ERR_INVALID_ARG, "bs_undistort_device: unknown submit flags 0x%x", submit_flags);
     if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_undistort_device: NULL handle");
     if (cam < 0 || cam >= h->n_cams || !d_src || !d_dst || d_src == d_dst)
         return fail(h, BS_ERR_INVALID_ARG, "bs_undistort_device: bad camera index or buffers");
@@ -1307,7 +1349,7 @@ int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch,
         if (cudaMemcpy2DAsync(d_dst, dpitch, d_src, spitch, (size_t)h->sw[cam] * 3, h->sh[cam], cudaMemcpyDeviceToDevice, st) != cudaSuccess)
             rc = fail(h, BS_ERR_CUDA, "bs_undistort_device: copy failed: %s", cudaGetErrorString(cudaGetLastError()));
     } else {
-        rc = undistort_one(h, cam, d_src, spitch, static_cast<uint8_t *>(d_dst), dpitch, st, true);
+        rc = undistort_one(h, cam, d_src, spitch, static_cast<uint8_t *>(d_dst), dpitch, st, !(submit_flags & BS_SUBMIT_SOURCES_SETTLED));
     }
     if (prev_dev != h->device) cudaSetDevice(prev_dev);
     return rc;

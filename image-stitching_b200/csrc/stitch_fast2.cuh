@@ -70,7 +70,8 @@ struct Fast2Args {
     int wait_sources;                      // 1: the source frames may come from the kernel just before this one in
                                            // the stream: order every source read behind it (griddepcontrol.wait first)
     int lens_mode;                         // 1: the plan is a lens plan (cv::undistort of one frame, stitch_undistort.cuh):
-    UndistortArgs lens;                    //    its EXACT blocks evaluate this model with BORDER_CONSTANT 0
+    UndistortArgs lens;                    //    its EXACT blocks evaluate this model with BORDER_CONSTANT 0,
+    const CubicCoef *lens_cubic;           //    and item k's expansion has the third-order terms lens_cubic[k]
 };
 
 // ---- packed fp32 pairs (x in the low half, y in the high half) -------------------------------------
@@ -109,6 +110,16 @@ __device__ __forceinline__ LaneCoef2 lane_coef2(const BlockCoef &c, float uf)
     l.a0 = fma2(u2, fma2(u2, pack2(c.hxuu, c.hyuu), pack2(c.xu, c.yu)), pack2(c.fx, c.fy));
     l.a1 = fma2(u2, pack2(c.xuv, c.yuv), pack2(c.xv, c.yv));
     l.a2 = pack2(c.hxvv, c.hyvv);
+    return l;
+}
+// The lens-plan form (lane_coef_cubic() of stitch_plan.cuh): third-order terms in the column offset.
+__device__ __forceinline__ LaneCoef2 lane_coef2_cubic(const BlockCoef &c, const CubicCoef &q, float uf)
+{
+    const uint64_t u2 = pack2(uf, uf);
+    LaneCoef2 l;
+    l.a0 = fma2(u2, fma2(u2, fma2(u2, pack2(q.xuuu, q.yuuu), pack2(c.hxuu, c.hyuu)), pack2(c.xu, c.yu)), pack2(c.fx, c.fy));
+    l.a1 = fma2(u2, fma2(u2, pack2(q.xuuv, q.yuuv), pack2(c.xuv, c.yuv)), pack2(c.xv, c.yv));
+    l.a2 = fma2(u2, pack2(q.xuvv, q.yuvv), pack2(c.hxvv, c.hyvv));
     return l;
 }
 // What only the partially covered layers need: the whole-texel parts, to test a pixel's source texel
@@ -534,7 +545,16 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if (n + 2 < cnt && lane == 0) issue_box(lds128(rec_addr(n + 2)), (uint32_t)n & 1u);
         if (type == (uint32_t)kBlockFast) {
             const BlockCoef bc = load_block_coef(ra);
-            const LaneCoef2 lc = lane_coef2(bc, uf);
+            LaneCoef2 lc;
+            if (A.lens_mode) {
+                CubicCoef q;
+                const float4 q0 = __ldg(reinterpret_cast<const float4 *>(A.lens_cubic + i0 + n));
+                const float2 q1 = __ldg(reinterpret_cast<const float2 *>(A.lens_cubic + i0 + n) + 2);
+                q.xuuu = q0.x; q.yuuu = q0.y; q.xuuv = q0.z; q.yuuv = q0.w; q.xuvv = q1.x; q.yuvv = q1.y;
+                lc = lane_coef2_cubic(bc, q, uf);
+            } else {
+                lc = lane_coef2(bc, uf);
+            }
             const int ustep = (int)(int16_t)(bc.aux & 0xFFFFu), vstep = (int)(int16_t)(bc.aux >> 16);
             const uint32_t run0 = conv + r.w + (uint32_t)(u * ustep);
             const uint32_t groups = r.y >> 24;

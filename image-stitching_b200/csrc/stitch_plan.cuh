@@ -162,6 +162,33 @@ __device__ __forceinline__ LaneCoef lane_coef(const BlockCoef &c, int u)
     return l;
 }
 
+// Lens plans (stitch_undistort.cuh) carry the expansion to third order in the column offset u: a radial lens
+// field has a constant third derivative, which the second-order form misses by up to 1/400 of a 1/32-pixel
+// step at a block's corners -- enough to flag a third of all blocks.  The u^3, u^2 v and u v^2 terms only
+// change the lane coefficients (no cost per pixel); v^3 is left out (|v| <= 8).
+struct CubicCoef {                 // 32 bytes per work item, kept beside the item list
+    float xuuu, yuuu;              // third derivatives / 6, / 2, / 2
+    float xuuv, yuuv;
+    float xuvv, yuvv;
+    float pad0, pad1;
+};
+__device__ __forceinline__ LaneCoef lane_coef_cubic(const BlockCoef &c, const CubicCoef &q, int u)
+{
+    const float uf = (float)u;
+    LaneCoef l;
+    l.a0x = __fmaf_rn(uf, __fmaf_rn(uf, __fmaf_rn(uf, q.xuuu, c.hxuu), c.xu), c.fx);
+    l.a1x = __fmaf_rn(uf, __fmaf_rn(uf, q.xuuv, c.xuv), c.xv);
+    l.a2x = __fmaf_rn(uf, q.xuvv, c.hxvv);
+    l.a0y = __fmaf_rn(uf, __fmaf_rn(uf, __fmaf_rn(uf, q.yuuu, c.hyuu), c.yu), c.fy);
+    l.a1y = __fmaf_rn(uf, __fmaf_rn(uf, q.yuuv, c.yuv), c.yv);
+    l.a2y = __fmaf_rn(uf, q.yuvv, c.hyvv);
+    l.bx = c.ix - kMagicBias + 32 * (int)c.nxu * u;
+    l.by = c.iy - kMagicBias + 32 * (int)c.nyu * u;
+    l.nxv = c.nxv;
+    l.nyv = c.nyv;
+    return l;
+}
+
 // Row v = k - kRun/2 of the lane's run.  Returns the raw bits of (s + 1.5*2^23): their low bits are
 // rint(s) (round half to even, done by the fp32 adder), so
 //   X = bits + l.bx + 32 l.nxv v,   X & 31 = bits & 31,   X >> 5 = (bits >> 5) + (l.bx >> 5) + l.nxv v.

@@ -111,6 +111,7 @@ struct LensPlanArgs {
     UndistortArgs U;
     int blocks_x, blocks_y;
     BlockRec *out;
+    CubicCoef *cubic;      // one per block, row-major like `out`
 };
 
 __global__ void __launch_bounds__(32 * kPlanWarps) lens_plan_kernel(const __grid_constant__ LensPlanArgs P)
@@ -131,7 +132,9 @@ __global__ void __launch_bounds__(32 * kPlanWarps) lens_plan_kernel(const __grid
 
     // the expansion around the block centre: derivatives by central differences of the exact (unrounded) field
     BlockCoef bc;
+    CubicCoef cq;
     memset(&bc, 0, sizeof bc);
+    memset(&cq, 0, sizeof cq);
     if (whole) {
         const int xc = bx * kBlockW + kBlockW / 2, yc = y0 + kBlockH / 2;      // xc +- 1, yc +- 1 lie inside the frame
         double g[3][3][2];
@@ -147,8 +150,28 @@ __global__ void __launch_bounds__(32 * kPlanWarps) lens_plan_kernel(const __grid
             d[c][5] = 0.5 * (g[2][1][c] - 2.0 * g[1][1][c] + g[0][1][c]);
         }
         bc = make_block_coef(d[0][0], d[1][0], d[0][1], d[0][2], d[1][1], d[1][2], d[0][3], d[0][4], d[0][5], d[1][3], d[1][4], d[1][5]);
+        // third order with a step of 4 pixels (the samples stay inside the block)
+        const int s4 = 4;
+        auto F = [&](int dx, int dy, double &fu, double &fv) { undistort_real(A, xc + dx * s4, yc + dy * s4, fu, fv); };
+        double p2[2], p1[2], m1[2], m2[2], c0[2], t[2];
+        F(2, 0, p2[0], p2[1]); F(1, 0, p1[0], p1[1]); F(-1, 0, m1[0], m1[1]); F(-2, 0, m2[0], m2[1]); F(0, 0, c0[0], c0[1]);
+        const double h3 = (double)(s4 * s4 * s4);
+        double uuu[2], uuv[2], uvv[2];
+        for (int c = 0; c < 2; ++c) uuu[c] = (p2[c] - 2.0 * p1[c] + 2.0 * m1[c] - m2[c]) / (2.0 * h3) / 6.0;      // f_uuu / 6
+        double a11[2], a01[2], am1[2], b11[2], b01[2], bm1[2];
+        F(1, 1, a11[0], a11[1]); F(0, 1, a01[0], a01[1]); F(-1, 1, am1[0], am1[1]);
+        F(1, -1, b11[0], b11[1]); F(0, -1, b01[0], b01[1]); F(-1, -1, bm1[0], bm1[1]);
+        for (int c = 0; c < 2; ++c) {
+            uuv[c] = ((a11[c] - 2.0 * a01[c] + am1[c]) - (b11[c] - 2.0 * b01[c] + bm1[c])) / (2.0 * h3) / 2.0;    // f_uuv / 2
+            uvv[c] = ((a11[c] - 2.0 * p1[c] + b11[c]) - (am1[c] - 2.0 * m1[c] + bm1[c])) / (2.0 * h3) / 2.0;      // f_uvv / 2
+            t[c] = 0.0;
+        }
+        (void)t;
+        cq.xuuu = (float)uuu[0]; cq.yuuu = (float)uuu[1];
+        cq.xuuv = (float)uuv[0]; cq.yuuv = (float)uuv[1];
+        cq.xuvv = (float)uvv[0]; cq.yuvv = (float)uvv[1];
     }
-    const LaneCoef lc = lane_coef(bc, lane - kBlockW / 2);
+    const LaneCoef lc = lane_coef_cubic(bc, cq, lane - kBlockW / 2);
 
     bool all_interior = whole, all_outside = true, zf = false;
     unsigned mism = 0u;
@@ -196,7 +219,10 @@ __global__ void __launch_bounds__(32 * kPlanWarps) lens_plan_kernel(const __grid
         rec.layer[0].zero_frac = __any_sync(FULLMASK, zf) ? 1 : 0;
         rec.coef[0] = bc;
     }
-    if (lane == 0) *dst = rec;
+    if (lane == 0) {
+        *dst = rec;
+        P.cubic[(size_t)by * P.blocks_x + bx] = cq;
+    }
 }
 
 // Four horizontally consecutive destination pixels starting at (x0, y), the exact way: fp64 lens model,

@@ -165,9 +165,10 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
 
 /* cv::undistort of one frame of camera `cam` with the model set by bs_set_undistort, between DEVICE
  * buffers (packed BGR, d_src != d_dst), asynchronous on `stream`: tools/stitch/main.cpp:148-149 for callers
- * whose frames are already on the GPU.  A camera without a model is copied. */
+ * whose frames are already on the GPU.  A camera without a model is copied.  submit_flags as for
+ * bs_submit_device_ex (BS_SUBMIT_SOURCES_SETTLED: no kernel directly before this call writes d_src). */
 int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch, void *d_dst, size_t dpitch,
-                        void *stream);
+                        void *stream, unsigned submit_flags);
 
 /* Drop-in for ONE cv::undistort(src, dst, K, dist) call on host buffers (main.cpp:148-149). */
 int bs_undistort(const uint8_t *src, int w, int h, size_t spitch, uint8_t *dst, size_t dpitch,

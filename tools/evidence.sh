@@ -13,7 +13,7 @@ for w in cfg2 cfg5 cfg1; do
   python bench.py --workload $w --steps 20 --cpu-seconds 6 > gpurun_out/${T}_bench_$w.json 2> gpurun_out/${T}_bench_$w.err
 done
 python bench.py --lens --steps 20 --cpu-seconds 8 > gpurun_out/${T}_bench_lens.json 2> gpurun_out/${T}_bench_lens.err
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${T}_ncu_list.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${T}_ncu_list.log 2>&1
 tools/prof.sh $T
 for w in cfg3 cfg2 cfg5; do python tools/traffic.py run $w > /dev/null 2>&1; done
 CMD="python bench.py --lens --steps 2 --warmup 3 --frames-per-step 8 --no-e2e --no-cpu-baseline"

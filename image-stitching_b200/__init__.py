@@ -33,7 +33,7 @@ EXPORTS = [
     "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
     "bs_set_undistort", "bs_undistort", "bs_submit_device_ex", "bs_undistort_device",
     "bs_pool_create", "bs_pool_destroy", "bs_pool_size", "bs_pool_depth", "bs_pool_handle", "bs_pool_last_error",
-    "bs_pool_set_undistort", "bs_pool_submit", "bs_pool_wait", "bs_pool_sync",
+    "bs_pool_set_undistort", "bs_pool_submit", "bs_pool_wait", "bs_pool_sync", "bs_submit_jpeg",
 ]
 
 
@@ -41,6 +41,10 @@ class StitchError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"b200_stitch error {code}: {msg}")
         self.code = code
+
+
+class JpegOut(ctypes.Structure):
+    _fields_ = [("data", ctypes.c_void_p), ("capacity", ctypes.c_size_t), ("size", ctypes.c_size_t), ("quality", ctypes.c_int)]
 
 
 class Stats(ctypes.Structure):
@@ -97,6 +101,8 @@ def lib():
     L.bs_undistort.argtypes = [vp, i, i, sz, vp, sz, dp, dp, i]
     L.bs_stitch_device_static.argtypes = [i, ip, ip, ctypes.POINTER(vp), ctypes.POINTER(sz), i, i, vp, sz, dp,
                                           ctypes.c_uint, vp]
+    L.bs_submit_jpeg.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz, ctypes.POINTER(JpegOut),
+                                 ctypes.POINTER(ctypes.c_int64)]
     L.bs_pool_create.argtypes = [i, ip, i, ip, ip, i, i, dp, ctypes.c_uint, ctypes.POINTER(vp)]
     L.bs_pool_destroy.argtypes = [vp]
     L.bs_pool_size.argtypes = [vp]
@@ -215,6 +221,32 @@ class Stitcher:
             out = self.new_canvas()
         self.wait(self.submit(frames, out))
         return out
+
+    # --- compressed frames ----------------------------------------------------------------
+    def submit_jpeg(self, jpegs, out=None, jpeg_capacity=0, quality=0):
+        """bs_submit_jpeg: `jpegs` = one bytes-like JPEG bitstream per camera, decoded on the GPU.  The panorama
+        comes back raw in `out` and/or, when jpeg_capacity > 0, as a JPEG (see jpeg_result).  Returns the ticket."""
+        bufs = [np.frombuffer(bytes(j), dtype=np.uint8) for j in jpegs]
+        ptrs = (ctypes.c_void_p * self.n_cams)(*[b.ctypes.data for b in bufs])
+        sizes = (ctypes.c_size_t * self.n_cams)(*[b.size for b in bufs])
+        jout = None
+        if jpeg_capacity:
+            store = np.empty(int(jpeg_capacity), np.uint8)
+            jout = JpegOut(store.ctypes.data, store.size, 0, int(quality))
+        if out is not None:
+            _check_img(out, "out")
+        t = ctypes.c_int64(-1)
+        _check(lib().bs_submit_jpeg(self._h, ptrs, sizes, out.ctypes.data if out is not None else None,
+                                    out.strides[0] if out is not None else 0, ctypes.byref(jout) if jout else None,
+                                    ctypes.byref(t)), self._h)
+        self._jpeg_pending = getattr(self, "_jpeg_pending", {})
+        self._jpeg_pending[t.value] = (bufs, jout, store if jpeg_capacity else None)     # keep the buffers alive until wait()
+        return t.value
+
+    def jpeg_result(self, ticket):
+        """After wait(ticket): the panorama's JPEG bitstream (bytes) of a submit_jpeg with jpeg_capacity > 0."""
+        bufs, jout, store = self._jpeg_pending.pop(ticket)
+        return bytes(store[:jout.size]) if jout else None
 
     # --- device buffers -------------------------------------------------------------------
     def submit_device(self, frame_ptrs, frame_pitches, canvas_ptr, canvas_pitch, stream=0, submit_flags=None):

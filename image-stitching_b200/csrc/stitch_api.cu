@@ -37,6 +37,7 @@ struct Slot {
     cudaEvent_t ev_h2d = nullptr, ev_kernel = nullptr, ev_done = nullptr;
     int64_t ticket = -1;
     bool busy = false;
+    bs_jpeg_out *jout = nullptr;          // the frame in this slot leaves as a JPEG (bs_submit_jpeg): filled by bs_wait
 };
 
 // Lens model of one camera (cv::undistort, tools/stitch/main.cpp:148-149).
@@ -47,6 +48,8 @@ struct TmapEntry {
     CUtensorMap map;
 };
 constexpr int kTmapCacheWays = 8;
+
+struct JpegCtx;                           // nvJPEG state of a handle (stitch_jpeg.inl), created by the first bs_submit_jpeg
 
 struct LensModel {
     bool enabled = false;                // false: no model, or all coefficients zero (undistort is then a copy)
@@ -98,6 +101,7 @@ struct bs_handle {
     unsigned tmap_next[bs::kMaxCamsPerLaunch] = {0};
     uint64_t device_bytes = 0, scratch_bytes = 0;
     uint64_t h2d_bytes_last = 0;         // bytes the last bs_submit uploaded
+    JpegCtx *jpeg = nullptr;
     char err[512] = "";
 };
 
@@ -921,6 +925,8 @@ int issue_frame(bs_handle *h, Slot &s, const uint8_t *const *frames, const size_
     return BS_OK;
 }
 
+int retrieve_jpeg(bs_handle *h, Slot &s, int slot_index);    // stitch_jpeg.inl
+void jpeg_ctx_destroy(JpegCtx *c);
 }  // namespace
 
 extern "C" {
@@ -1011,6 +1017,7 @@ int bs_destroy(bs_handle *h)
         cudaFree(m.d_cubic);
         cudaFree(m.d_warp_start);
     }
+    jpeg_ctx_destroy(h->jpeg);
     for (uint8_t *p : h->d_undist) cudaFree(p);
     for (Slot &s : h->ring) {
         for (uint8_t *p : s.d_undist) cudaFree(p);
@@ -1050,8 +1057,8 @@ int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
     const int64_t t = h->next_ticket;
     Slot &s = h->ring[t % kPipelineDepth];
     if (s.busy) {   // the slot's previous frame must have left the device
-        BS_CUDA(h, cudaEventSynchronize(s.ev_done));
-        s.busy = false;
+        rc = bs_wait(h, s.ticket);
+        if (rc != BS_OK) return rc;
     }
     rc = issue_frame(h, s, frames, pitch, out, out_pitch);
     if (rc != BS_OK) {
@@ -1083,7 +1090,7 @@ int bs_wait(bs_handle *h, int64_t ticket)
     BS_CUDA(h, cudaSetDevice(h->device));
     BS_CUDA(h, cudaEventSynchronize(s.ev_done));
     s.busy = false;
-    return BS_OK;
+    return retrieve_jpeg(h, s, (int)(ticket % kPipelineDepth));
 }
 
 int bs_stitch(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, uint8_t *out,
@@ -1670,3 +1677,5 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     BS_CUDA(nullptr, cudaStreamSynchronize(s));
     return BS_OK;
 }
+
+#include "stitch_jpeg.inl"

@@ -181,6 +181,26 @@ void bs_host_free(void *p);
 int bs_get_stats(const bs_handle *h, bs_stats *out);
 
 /*
+ * Compressed frames in, and optionally a compressed panorama out: the device-side form of
+ * imread / VideoCapture at tools/stitch/main.cpp:107,114,127-147 and of imwrite at :125.  jpeg[i] / jpeg_bytes[i]
+ * are the JPEG bitstreams of the cameras' frames (baseline JPEG, the handle's frame sizes); they are decoded
+ * on the GPU (nvJPEG) straight into the handle's frame ring, so no decoded frame crosses PCIe.  The panorama
+ * is returned raw in `out` (may be NULL), and/or as a JPEG in `jout` (may be NULL): jout->data / capacity name
+ * the caller's buffer, quality is 1..100 (0 = 95, cv::imwrite's default; 4:2:0 chroma as there), and jout->size
+ * holds the bitstream length after bs_wait(ticket) -- only the bitstream is copied from the device.  All
+ * buffers, and *jout itself, must stay valid until bs_wait.  Decoded pixels are nvJPEG's; they can differ by a
+ * unit or two from libjpeg's, as between any two JPEG decoders.
+ */
+typedef struct bs_jpeg_out {
+    uint8_t *data;
+    size_t capacity;
+    size_t size;       /* out: bytes written (or needed, when bs_wait reports that capacity was too small) */
+    int quality;
+} bs_jpeg_out;
+int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const size_t *jpeg_bytes, uint8_t *out, size_t out_pitch,
+                   bs_jpeg_out *jout, int64_t *ticket);
+
+/*
  * Frame-parallel dispatch over several GPUs of one box.  Replaces the single loop of
  * tools/stitch/main.cpp:143-155 for video: every output frame is independent (the canvas is re-created at
  * :144), so frame f runs on GPU f mod G with a full replica of the calibration; no data is exchanged between

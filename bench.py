@@ -64,6 +64,7 @@ def parse_args():
                     help="every camera gets a lens model (cv::undistort before the warp, the video-mode loop "
                          "of tools/stitch/main.cpp:148-151); adds the `undistort` record")
     ap.add_argument("--no-host-ceiling", action="store_true")
+    ap.add_argument("--no-compressed", action="store_true", help="skip the e2e_compressed record (JPEG frames in)")
     return ap.parse_args()
 
 
@@ -489,6 +490,47 @@ def run_b200(args, rank, local_rank, world):
             e2e["matches_device_path"] = bool(np.array_equal(h_out[j % len(h_out)],
                                                              d_canvas[j % RING].cpu().numpy()))
 
+    # ---- end to end with COMPRESSED frames: JPEG bitstreams up, decoded on the device (bs_submit_jpeg) ----
+    e2e_jpeg = None
+    if not args.no_e2e and not args.no_compressed:
+        try:
+            import cv2
+            # hash noise does not compress (its JPEG is as large as the raw frame), so this record uses the smooth
+            # content plus a little texture; the panorama comes back raw, as in `e2e`
+            def textured(i, f):
+                a = wl.gen_frame_numpy(sw, sh, i, rank + world * f, "smooth").astype(np.int16)
+                a += (wl.gen_frame_numpy(sw, sh, i, f, "noise") >> 5).astype(np.int16) - 4
+                return np.clip(a, 0, 255).astype(np.uint8)
+            jf = [[np.frombuffer(cv2.imencode(".jpg", textured(i, f), [cv2.IMWRITE_JPEG_QUALITY, 90])[1].tobytes(), dtype=np.uint8).copy()
+                   for i in range(n)] for f in range(3)]
+            jbytes = int(sum(b.size for b in jf[0]))
+            depth = pkg.lib().bs_pipeline_depth(st._h)
+            hj_out = [pkg.pinned_empty((H, W, 3)) for _ in range(depth + 1)]
+
+            def jpeg_frames(k):
+                tickets = []
+                for j in range(k):
+                    if len(tickets) >= depth:
+                        st.wait(tickets[len(tickets) - depth])
+                    tickets.append(st.submit_jpeg(jf[j % len(jf)], hj_out[j % len(hj_out)]))
+                for t in tickets[-depth:]:
+                    st.wait(t)
+            jpeg_frames(4)
+            nj = max(8, min(48, args.steps * 2))
+            barrier()
+            t0 = time.perf_counter()
+            jpeg_frames(nj)
+            st.sync()
+            t1 = time.perf_counter()
+            barrier()
+            js = max_over_ranks(t1 - t0)
+            e2e_jpeg = {"value": world * nj / js, "unit": UNIT, "h2d_bytes_per_frame": jbytes, "d2h_bytes_per_frame": w.canvas_bytes,
+                        "frames": nj, "content": "smooth ramp + 3 bits of texture, JPEG quality 90 (cv2.imencode)",
+                        "decoder": f"nvJPEG ({st.jpeg_backend()}) into the device frame ring (bs_submit_jpeg), panorama returned raw",
+                        "raw_h2d_bytes_per_frame_for_comparison": h2d_per_frame if e2e else None}
+        except Exception as ex:   # pragma: no cover
+            e2e_jpeg = {"unavailable": f"{type(ex).__name__}: {ex}"}
+
     stats = st.stats()
     stats_kernel = ["stitch_exact_kernel", "stitch_fast_kernel (general staged)", "stitch_fast2_kernel (compact boxes)"][stats["frame_kernel"]]
     st.close()
@@ -552,7 +594,7 @@ def run_b200(args, rank, local_rank, world):
                 "tiles_fast_exact_empty": [stats["n_tiles_fast"], stats["n_tiles_exact"], stats["n_tiles_empty"]],
                 "kernel": stats_kernel},
         "undistort": undist,
-        "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "e2e": e2e, "e2e_compressed": e2e_jpeg, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "clocks": sampler.summary(), "parity": parity,
     }
     print(json.dumps(line), flush=True)

@@ -33,7 +33,7 @@ EXPORTS = [
     "bs_warp_perspective", "bs_host_alloc", "bs_host_free", "bs_get_stats", "bs_stitch_device_static",
     "bs_set_undistort", "bs_undistort", "bs_submit_device_ex", "bs_undistort_device",
     "bs_pool_create", "bs_pool_destroy", "bs_pool_size", "bs_pool_depth", "bs_pool_handle", "bs_pool_last_error",
-    "bs_pool_set_undistort", "bs_pool_submit", "bs_pool_wait", "bs_pool_sync", "bs_submit_jpeg",
+    "bs_pool_set_undistort", "bs_pool_submit", "bs_pool_wait", "bs_pool_sync", "bs_submit_jpeg", "bs_jpeg_backend",
 ]
 
 
@@ -103,6 +103,8 @@ def lib():
                                           ctypes.c_uint, vp]
     L.bs_submit_jpeg.argtypes = [vp, ctypes.POINTER(vp), ctypes.POINTER(sz), vp, sz, ctypes.POINTER(JpegOut),
                                  ctypes.POINTER(ctypes.c_int64)]
+    L.bs_jpeg_backend.argtypes = [vp]
+    L.bs_jpeg_backend.restype = ctypes.c_char_p
     L.bs_pool_create.argtypes = [i, ip, i, ip, ip, i, i, dp, ctypes.c_uint, ctypes.POINTER(vp)]
     L.bs_pool_destroy.argtypes = [vp]
     L.bs_pool_size.argtypes = [vp]
@@ -226,7 +228,7 @@ class Stitcher:
     def submit_jpeg(self, jpegs, out=None, jpeg_capacity=0, quality=0):
         """bs_submit_jpeg: `jpegs` = one bytes-like JPEG bitstream per camera, decoded on the GPU.  The panorama
         comes back raw in `out` and/or, when jpeg_capacity > 0, as a JPEG (see jpeg_result).  Returns the ticket."""
-        bufs = [np.frombuffer(bytes(j), dtype=np.uint8) for j in jpegs]
+        bufs = [j if isinstance(j, np.ndarray) and j.dtype == np.uint8 else np.frombuffer(bytes(j), dtype=np.uint8) for j in jpegs]
         ptrs = (ctypes.c_void_p * self.n_cams)(*[b.ctypes.data for b in bufs])
         sizes = (ctypes.c_size_t * self.n_cams)(*[b.size for b in bufs])
         jout = None
@@ -242,6 +244,9 @@ class Stitcher:
         self._jpeg_pending = getattr(self, "_jpeg_pending", {})
         self._jpeg_pending[t.value] = (bufs, jout, store if jpeg_capacity else None)     # keep the buffers alive until wait()
         return t.value
+
+    def jpeg_backend(self):
+        return lib().bs_jpeg_backend(self._h).decode()
 
     def jpeg_result(self, ticket):
         """After wait(ticket): the panorama's JPEG bitstream (bytes) of a submit_jpeg with jpeg_capacity > 0."""

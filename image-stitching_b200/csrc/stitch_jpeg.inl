@@ -12,8 +12,13 @@
 namespace {
 
 struct JpegCtx {
-    nvjpegHandle_t lib = nullptr;
+    nvjpegHandle_t lib = nullptr;              // per-image decoder (host Huffman stage) and the encoder
     std::vector<nvjpegJpegState_t> dec;        // kPipelineDepth x n_cams decode states (one per frame in flight)
+    // Batched decoder, one batch = the cameras of one frame: the GPU's JPEG engine when the library drives one
+    // on this device, else GPU-assisted Huffman decoding; nullptr when neither initialises.
+    nvjpegHandle_t blib = nullptr;
+    nvjpegJpegState_t bdec[kPipelineDepth] = {nullptr, nullptr, nullptr};
+    bool batched_ok = false;
     nvjpegEncoderState_t enc[kPipelineDepth] = {nullptr, nullptr, nullptr};
     nvjpegEncoderParams_t enc_params[kPipelineDepth] = {nullptr, nullptr, nullptr};
     const char *backend = "default";
@@ -34,6 +39,32 @@ int jpeg_ctx(bs_handle *h, JpegCtx **out)
         delete c;
         return fail(h, BS_ERR_CUDA, "nvjpegCreate failed");
     }
+    static const char *force = getenv("BS_DEBUG_JPEG_BACKEND");      // test hook: "simple", "gpu_hybrid", "hardware"
+    const struct { nvjpegBackend_t be; const char *name; } tries[2] = {{NVJPEG_BACKEND_HARDWARE, "hardware"},
+                                                                        {NVJPEG_BACKEND_GPU_HYBRID, "gpu_hybrid"}};
+    for (int k = 0; k < 2 && !c->batched_ok; ++k) {
+        if (force && strcmp(force, tries[k].name) != 0) continue;
+        if (nvjpegCreateEx(tries[k].be, nullptr, nullptr, NVJPEG_FLAGS_DEFAULT, &c->blib) != NVJPEG_STATUS_SUCCESS) {
+            c->blib = nullptr;
+            continue;
+        }
+        bool ok2 = true;
+        for (int q = 0; q < kPipelineDepth && ok2; ++q)
+            ok2 = nvjpegJpegStateCreate(c->blib, &c->bdec[q]) == NVJPEG_STATUS_SUCCESS &&
+                  nvjpegDecodeBatchedInitialize(c->blib, c->bdec[q], h->n_cams, std::min(h->n_cams, 8), NVJPEG_OUTPUT_BGRI) == NVJPEG_STATUS_SUCCESS;
+        if (ok2) {
+            c->batched_ok = true;
+            c->backend = tries[k].name;
+        } else {
+            for (int q = 0; q < kPipelineDepth; ++q) {
+                if (c->bdec[q]) nvjpegJpegStateDestroy(c->bdec[q]);
+                c->bdec[q] = nullptr;
+            }
+            nvjpegDestroy(c->blib);
+            c->blib = nullptr;
+        }
+    }
+    cudaGetLastError();
     c->dec.assign((size_t)kPipelineDepth * h->n_cams, nullptr);
     bool ok = true;
     for (auto &st : c->dec) ok = ok && nvjpegJpegStateCreate(c->lib, &st) == NVJPEG_STATUS_SUCCESS;
@@ -51,6 +82,9 @@ void jpeg_ctx_destroy(JpegCtx *c)
     if (!c) return;
     for (auto st : c->dec)
         if (st) nvjpegJpegStateDestroy(st);
+    for (int k = 0; k < kPipelineDepth; ++k)
+        if (c->bdec[k]) nvjpegJpegStateDestroy(c->bdec[k]);
+    if (c->blib) nvjpegDestroy(c->blib);
     for (int k = 0; k < kPipelineDepth; ++k) {
         if (c->enc_params[k]) nvjpegEncoderParamsDestroy(c->enc_params[k]);
         if (c->enc[k]) nvjpegEncoderStateDestroy(c->enc[k]);
@@ -68,6 +102,7 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
     int rc = jpeg_ctx(h, &c);
     if (rc != BS_OK) return rc;
     h->h2d_bytes_last = 0;
+    std::vector<nvjpegImage_t> imgs(h->n_cams);
     for (int i = 0; i < h->n_cams; ++i) {
         int nc = 0, ws[NVJPEG_MAX_COMPONENT], hs[NVJPEG_MAX_COMPONENT];
         nvjpegChromaSubsampling_t ss;
@@ -76,14 +111,22 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
         if (ws[0] != h->sw[i] || hs[0] != h->sh[i])
             return fail(h, BS_ERR_INVALID_ARG, "bs_submit_jpeg: frame %d is %dx%d, the handle expects %dx%d", i, ws[0], hs[0], h->sw[i],
                         h->sh[i]);
-        nvjpegImage_t img;
-        memset(&img, 0, sizeof img);
-        img.channel[0] = s.d_frame[i];
-        img.pitch[0] = h->d_frame_pitch[i];
-        const nvjpegStatus_t st = nvjpegDecode(c->lib, c->dec[(size_t)slot_index * h->n_cams + i], jpeg[i], jpeg_bytes[i], NVJPEG_OUTPUT_BGRI,
-                                              &img, h->s_h2d);
-        if (st != NVJPEG_STATUS_SUCCESS) return fail(h, BS_ERR_CUDA, "bs_submit_jpeg: nvjpegDecode of frame %d failed (%d)", i, (int)st);
+        memset(&imgs[i], 0, sizeof imgs[i]);
+        imgs[i].channel[0] = s.d_frame[i];
+        imgs[i].pitch[0] = h->d_frame_pitch[i];
         h->h2d_bytes_last += jpeg_bytes[i];
+    }
+    bool decoded = false;
+    if (c->batched_ok) {
+        // all cameras of the frame in one batch; a bitstream this backend cannot take (progressive, odd sampling)
+        // sends the frame to the per-image decoder below
+        decoded = nvjpegDecodeBatched(c->blib, c->bdec[slot_index], jpeg, jpeg_bytes, imgs.data(), h->s_h2d) == NVJPEG_STATUS_SUCCESS;
+        if (!decoded) cudaGetLastError();
+    }
+    for (int i = 0; i < h->n_cams && !decoded; ++i) {
+        const nvjpegStatus_t st = nvjpegDecode(c->lib, c->dec[(size_t)slot_index * h->n_cams + i], jpeg[i], jpeg_bytes[i], NVJPEG_OUTPUT_BGRI,
+                                              &imgs[i], h->s_h2d);
+        if (st != NVJPEG_STATUS_SUCCESS) return fail(h, BS_ERR_CUDA, "bs_submit_jpeg: nvjpegDecode of frame %d failed (%d)", i, (int)st);
     }
     const bool keep = (h->flags & BS_FLAG_KEEP_CANVAS) != 0;
     if (keep && out)
@@ -182,4 +225,9 @@ extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const si
     h->next_ticket++;
     if (ticket) *ticket = t;
     return BS_OK;
+}
+
+extern "C" const char *bs_jpeg_backend(const bs_handle *h)
+{
+    return (h && h->jpeg) ? h->jpeg->backend : "";
 }

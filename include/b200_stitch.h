@@ -199,6 +199,10 @@ typedef struct bs_jpeg_out {
 } bs_jpeg_out;
 int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const size_t *jpeg_bytes, uint8_t *out, size_t out_pitch,
                    bs_jpeg_out *jout, int64_t *ticket);
+/* Which nvJPEG decoder the handle's bs_submit_jpeg uses: "hardware" (the GPU's JPEG engine, batched),
+ * "gpu_hybrid" (GPU-assisted Huffman decoding, batched), "default" (per image, Huffman stage on the host);
+ * "" before the first bs_submit_jpeg. */
+const char *bs_jpeg_backend(const bs_handle *h);
 
 /*
  * Frame-parallel dispatch over several GPUs of one box.  Replaces the single loop of

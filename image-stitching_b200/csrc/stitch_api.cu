@@ -1419,7 +1419,10 @@ int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8
 void *bs_host_alloc(size_t bytes)
 {
     void *p = nullptr;
-    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+    // BS_HOST_ALLOC_WC=1 (experiment hook): write-combined pages -- fast for the host to fill and for
+    // the device to read, very slow for the host to read back, so only for buffers that are uploaded
+    static const bool wc = getenv("BS_HOST_ALLOC_WC") != nullptr;
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable | (wc ? cudaHostAllocWriteCombined : 0)) != cudaSuccess) {
         cudaGetLastError();
         fail(nullptr, BS_ERR_NOMEM, "bs_host_alloc: cudaHostAlloc(%zu) failed", bytes);
         return nullptr;

@@ -20,6 +20,7 @@ FLAG_LEGACY_BORDER = 0x1
 FLAG_KEEP_CANVAS = 0x2
 FLAG_EXACT_ONLY = 0x4
 FLAG_BORDER_CONSTANT = 0x8
+FLAG_FEATHER = 0x10   # opt-in, not the reference's result: weighted mean where cameras overlap (include/b200_stitch.h)
 SUBMIT_SOURCES_SETTLED = 0x1   # bs_submit_device_ex: no kernel directly before the call writes the source frames
 
 # names of the cv2 constants the reference passes (tools/stitch/main.cpp:116-117)

@@ -433,6 +433,7 @@ int build_plan(bs_handle *h)
     P->block_w = opencv_block_width(h->W, h->H);
     P->legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
     P->keep_canvas = (h->flags & BS_FLAG_KEEP_CANVAS) ? 1 : 0;
+    P->feather = (h->flags & BS_FLAG_FEATHER) ? 1 : 0;
     P->blocks_x = h->blocks_x;
     P->blocks_y = h->blocks_y;
     // device scratch: raw records first, later overwritten by the item list (at most 2 items of 80 bytes per block)
@@ -788,6 +789,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.block_w = opencv_block_width(h->W, h->H);
         A.legacy_border = (h->flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
         A.keep_canvas = keep ? 1 : 0;
+        A.feather = (h->flags & BS_FLAG_FEATHER) ? 1 : 0;
         A.canvas_in_4g = canvas_in_4g(d_canvas, cpitch, h->H);
         // Programmatic dependent launch: the prologue and first block of this frame may overlap the
         // tail of the previous kernel on the same stream (see stitch_fast.cuh).  When that kernel may
@@ -848,6 +850,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
         A.keep_canvas = (keep || base > 0) ? 1 : 0;
         A.cam_base = base;
         A.border_constant = (h->flags & BS_FLAG_BORDER_CONSTANT) ? 1 : 0;
+        A.feather = (h->flags & BS_FLAG_FEATHER) ? 1 : 0;
         dim3 grid((h->W + bs::kExactTileW - 1) / bs::kExactTileW,
                   (h->H + bs::kExactTileH - 1) / bs::kExactTileH);
         bs::stitch_exact_kernel<<<grid, dim3(32, bs::kExactTileH), 0, stream>>>(A);
@@ -961,6 +964,15 @@ int bs_create(int device_id, int n_cams, const int *src_w, const int *src_h, int
         if (src_w[i] < 1 || src_h[i] < 1 || src_w[i] > BS_MAX_DIM || src_h[i] > BS_MAX_DIM)
             return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: camera %d is %dx%d, outside [1, %d]",
                         i, src_w[i], src_h[i], BS_MAX_DIM);
+    if (flags & ~(BS_FLAG_LEGACY_BORDER | BS_FLAG_KEEP_CANVAS | BS_FLAG_EXACT_ONLY | BS_FLAG_BORDER_CONSTANT | BS_FLAG_FEATHER))
+        return fail(nullptr, BS_ERR_INVALID_ARG, "bs_create: unknown flags 0x%x", flags);
+    if (flags & BS_FLAG_FEATHER) {
+        if (flags & BS_FLAG_BORDER_CONSTANT)
+            return fail(nullptr, BS_ERR_UNSUPPORTED, "bs_create: BS_FLAG_FEATHER with BS_FLAG_BORDER_CONSTANT: every camera covers every pixel there");
+        if (n_cams > bs::kMaxCamsPerLaunch)
+            return fail(nullptr, BS_ERR_UNSUPPORTED, "bs_create: BS_FLAG_FEATHER takes at most %d cameras (one launch must see all of them), got %d",
+                        bs::kMaxCamsPerLaunch, n_cams);
+    }
     int rc = require_device(nullptr);
     if (rc != BS_OK) return rc;
     int ndev = bs_device_count();
@@ -1402,6 +1414,7 @@ int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8
                         size_t dpitch, const double H[9], unsigned flags)
 {
     if (!src || !dst || !H) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_warp_perspective: NULL argument");
+    if (flags & BS_FLAG_FEATHER) return fail(nullptr, BS_ERR_UNSUPPORTED, "bs_warp_perspective: BS_FLAG_FEATHER needs a handle with all cameras");
     int rc = require_device(nullptr);
     if (rc != BS_OK) return rc;
     bs_handle *h = nullptr;

@@ -34,6 +34,7 @@ struct FrameArgs {
     int cam_base;         // index of cam[0] among all cameras (multi-launch for > 16 cameras)
     int canvas_in_4g;     // 1: all canvas addresses share their upper 32 bits (staged kernel: rows may be stored with 32-bit address steps)
     int border_constant;  // 1: cv::BORDER_CONSTANT 0 instead of BORDER_TRANSPARENT (exact kernel only)
+    int feather;          // 1: BS_FLAG_FEATHER, pixels written by several cameras are a weighted mean (composite_feather)
 };
 
 // ---- Appendix A.1, exact form -------------------------------------------------------------
@@ -124,10 +125,42 @@ __device__ __forceinline__ uint32_t sample_constant(const CamDev &c, int X, int 
     return out;
 }
 
+// BS_FLAG_FEATHER (nothing in the reference does this, the OpenCV call only overwrites):
+// every camera that would write the pixel under the active border rule contributes its own bilinear result
+// P_i with the integer weight d_i = 1 + its distance to the nearest source edge in 1/32 pixels,
+//     d_i = max(1, 1 + min(X, 32 (w - 1) - X, Y, 32 (h - 1) - Y)),
+// and the pixel is (sum d_i P_i + (sum d_i) / 2) / sum d_i per channel, integer division.  A pixel one camera
+// writes is that camera's pixel unchanged, so blocks without overlap keep the staged path.
+// d_i < 2^20, P_i < 2^8, at most 16 cameras: the sums fit 32 bits.  oracle_stitch_feather is the same sequence.
+__device__ __forceinline__ bool composite_feather(const FrameArgs &A, int xb, int x1, int y, uint32_t &bgr)
+{
+    uint32_t acc0 = 0, acc1 = 0, acc2 = 0, wsum = 0;
+    for (int i = 0; i < A.n_cams; ++i) {
+        int X, Y;
+        uint32_t p;
+        coord_exact(A.cam[i].M, xb, x1, y, X, Y);
+        if (!sample_exact(A.cam[i], X, Y, A.legacy_border, p)) continue;
+        const int d = min(min(X, 32 * (A.cam[i].w - 1) - X), min(Y, 32 * (A.cam[i].h - 1) - Y));
+        const uint32_t w = (uint32_t)max(1, d + 1);
+        acc0 += w * (p & 0xffu);
+        acc1 += w * ((p >> 8) & 0xffu);
+        acc2 += w * ((p >> 16) & 0xffu);
+        wsum += w;
+    }
+    if (wsum == 0) {
+        bgr = 0;
+        return false;
+    }
+    const uint32_t half = wsum >> 1;
+    bgr = ((acc0 + half) / wsum) | (((acc1 + half) / wsum) << 8) | (((acc2 + half) / wsum) << 16);
+    return true;
+}
+
 __device__ __forceinline__ bool composite_exact(const FrameArgs &A, int x, int y, uint32_t &bgr)
 {
     const int xb = (x / A.block_w) * A.block_w;
     const int x1 = x - xb;
+    if (A.feather) return composite_feather(A, xb, x1, y, bgr);
     if (A.border_constant) {            // the last camera writes every pixel
         int X, Y;
         coord_exact(A.cam[A.n_cams - 1].M, xb, x1, y, X, Y);

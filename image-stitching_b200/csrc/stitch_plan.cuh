@@ -208,6 +208,7 @@ struct PlanArgs {
     int block_w;                   // OpenCV's coordinate block width (not ours)
     int legacy_border;
     int keep_canvas;               // blocks with uncovered pixels then need the read-modify-write path
+    int feather;                   // BS_FLAG_FEATHER: blocks where two cameras write one pixel go to the per-pixel path
     int blocks_x, blocks_y;
     BlockRec *out;                 // blocks_y * blocks_x records, row-major
 };
@@ -245,6 +246,13 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
                 coord_exact(P.M[i], xb, x - xb, y, X, Y);
                 cls = cover_class(X, Y, P.w[i], P.h[i], P.legacy_border);
                 if (cls) break;
+            }
+            if (P.feather && cls) {            // does a lower camera write this pixel too?
+                for (int j = i - 1; j >= 0 && !edge; --j) {
+                    int X, Y;
+                    coord_exact(P.M[j], xb, x - xb, y, X, Y);
+                    if (cover_class(X, Y, P.w[j], P.h[j], P.legacy_border)) edge = true;   // same fate as an edge block: exact
+                }
             }
             if (cls == 0) unc = true;
             else {

@@ -51,6 +51,17 @@ extern "C" {
  * (projectToTheFloor) uses; SURVEY.md row f3.  Meant for bs_warp_perspective; in a handle the last
  * camera then overwrites the whole canvas, as N such OpenCV calls would.  Implies BS_FLAG_EXACT_ONLY. */
 #define BS_FLAG_BORDER_CONSTANT 0x8u
+/* OPT-IN, NOT the reference's result: where several cameras write one canvas pixel, store
+ * their weighted mean instead of the last camera's pixel.  Camera i contributes the pixel P_i the OpenCV call
+ * would have written, with the integer weight d_i = max(1, 1 + min(X, 32 (w_i - 1) - X, Y, 32 (h_i - 1) - Y)),
+ * its distance to the nearest source edge in 1/32 pixels (X, Y the fixed-point source coordinate of SURVEY.md
+ * Appendix A.1); each channel is (sum d_i P_i + (sum d_i) / 2) / sum d_i in integers.  Pixels one camera
+ * writes are unchanged, so are uncovered pixels.  The reference has no blending at all
+ * (tools/stitch/main.cpp:117,151 overwrite), so there is nothing to be bit-exact with: the CPU restatement
+ * oracle_stitch_feather is "parity unpinned" and is excluded from the parity metric.  Blocks of the canvas where
+ * cameras overlap take the per-pixel path (several times slower than the default); at most 16 cameras;
+ * not with BS_FLAG_BORDER_CONSTANT; handles only (the one-shot calls and bs_stitch_device_static refuse it). */
+#define BS_FLAG_FEATHER 0x10u
 
 #define BS_MAX_CAMERAS 64
 #define BS_MAX_DIM 32767 /* OpenCV keeps integer source coordinates in int16 */

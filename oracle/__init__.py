@@ -47,6 +47,10 @@ def lib():
                                               u8p, ctypes.c_int, ctypes.c_int, ctypes.c_size_t,
                                               dp, ctypes.c_int, ctypes.c_int]
         L.oracle_warp_perspective.restype = None
+        L.oracle_stitch_feather.argtypes = [ctypes.c_int, ctypes.POINTER(u8p), ctypes.POINTER(ctypes.c_int),
+                                            ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_size_t), u8p,
+                                            ctypes.c_int, ctypes.c_int, ctypes.c_size_t, dp, ctypes.c_int, ctypes.c_int]
+        L.oracle_stitch_feather.restype = None
         L.oracle_undistort.argtypes = [u8p, ctypes.c_int, ctypes.c_int, ctypes.c_size_t, u8p,
                                        ctypes.c_size_t, dp, dp, ctypes.c_int, ctypes.c_int]
         L.oracle_undistort.restype = None
@@ -99,6 +103,23 @@ def stitch(srcs, Hs, canvas_wh, border_rule=BORDER_CV4, nthreads=None):
     canvas = np.zeros((Hc, W, 3), dtype=np.uint8)
     for s, H in zip(srcs, Hs):
         warp_perspective(s, H, canvas, border_rule, nthreads)
+    return canvas
+
+
+def stitch_feather(srcs, Hs, canvas_wh, border_rule=BORDER_CV4, nthreads=None):
+    """BS_FLAG_FEATHER restated (PARITY UNPINNED: the reference does not blend; include/b200_stitch.h defines it)."""
+    W, Hc = canvas_wh
+    n = len(srcs)
+    assert all(s.dtype == np.uint8 and s.ndim == 3 and s.shape[2] == 3 and s.strides[1] == 3 and s.strides[2] == 1 for s in srcs)
+    canvas = np.zeros((Hc, W, 3), dtype=np.uint8)
+    u8p = ctypes.POINTER(ctypes.c_uint8)
+    ptrs = (u8p * n)(*[_u8(s) for s in srcs])
+    sw = (ctypes.c_int * n)(*[s.shape[1] for s in srcs])
+    sh = (ctypes.c_int * n)(*[s.shape[0] for s in srcs])
+    sp = (ctypes.c_size_t * n)(*[s.strides[0] for s in srcs])
+    Hflat = np.ascontiguousarray(np.asarray(Hs, dtype=np.float64).reshape(n * 9))
+    lib().oracle_stitch_feather(n, ptrs, sw, sh, sp, _u8(canvas), W, Hc, canvas.strides[0], _d(Hflat), border_rule,
+                                nthreads or default_threads())
     return canvas
 
 

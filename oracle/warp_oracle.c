@@ -209,6 +209,47 @@ void oracle_stitch(int n_cams, const uint8_t *const *srcs, const int *sw, const 
                                 border_rule, nthreads);
 }
 
+/* BS_FLAG_FEATHER (include/b200_stitch.h).  PARITY UNPINNED: the reference has no blending
+ * (tools/stitch/main.cpp:117,151 overwrite), so this function restates the product's own definition and cites
+ * nothing in the reference.  Camera i contributes the pixel the OpenCV call would have written with the integer
+ * weight d_i = max(1, 1 + distance of the fixed-point source coordinate to the nearest source edge, in 1/32 px);
+ * each channel is (sum d_i P_i + (sum d_i) / 2) / sum d_i. */
+void oracle_stitch_feather(int n_cams, const uint8_t *const *srcs, const int *sw, const int *sh,
+                           const size_t *spitch, uint8_t *dst, int dw, int dh, size_t dpitch,
+                           const double *H, int border_rule, int nthreads)
+{
+    double M[64][9];
+    if (n_cams > 64) n_cams = 64;
+    for (int i = 0; i < n_cams; ++i) oracle_invert3x3(H + 9 * i, M[i]);
+    const int bw = block_width(dw, dh);
+    (void)nthreads;
+#ifdef _OPENMP
+#pragma omp parallel for schedule(static) num_threads(nthreads > 0 ? nthreads : 1)
+#endif
+    for (int y = 0; y < dh; ++y) {
+        uint8_t *drow = dst + (size_t)y * dpitch;
+        for (int x = 0; x < dw; ++x) {
+            const int xb = (x / bw) * bw;
+            uint64_t acc[3] = {0, 0, 0}, wsum = 0;
+            for (int i = 0; i < n_cams; ++i) {
+                int X, Y;
+                uint8_t px[3];
+                coord_rel(M[i], xb, x - xb, y, &X, &Y);
+                if (!sample_transparent(srcs[i], sw[i], sh[i], spitch[i], X, Y, border_rule, px)) continue;
+                int64_t d = X;
+                const int64_t dr = 32 * (int64_t)(sw[i] - 1) - X, db = 32 * (int64_t)(sh[i] - 1) - Y;
+                if (dr < d) d = dr;
+                if (Y < d) d = Y;
+                if (db < d) d = db;
+                const uint64_t w = (uint64_t)(d + 1 > 1 ? d + 1 : 1);
+                for (int c = 0; c < 3; ++c) acc[c] += w * px[c];
+                wsum += w;
+            }
+            for (int c = 0; c < 3; ++c) drow[3 * x + c] = wsum ? (uint8_t)((acc[c] + wsum / 2) / wsum) : 0;
+        }
+    }
+}
+
 /* ------------------------------------------------------------------------------------------
  * cv::undistort (tools/stitch/main.cpp:148-149), Appendix A.6.
  * OpenCV builds the map in row stripes of height min(max(1, 4096 / w), h); inside a stripe

@@ -61,6 +61,13 @@ void oracle_stitch(int n_cams, const uint8_t *const *srcs, const int *sw, const 
                    const size_t *spitch, uint8_t *dst, int dw, int dh, size_t dpitch,
                    const double *H /* n_cams x 9 */, int border_rule, int nthreads);
 
+/* BS_FLAG_FEATHER: weighted mean over the cameras that write a pixel instead of last-camera-wins.
+ * PARITY UNPINNED -- the reference does not blend; this restates include/b200_stitch.h's definition only and
+ * is not part of the parity metric. */
+void oracle_stitch_feather(int n_cams, const uint8_t *const *srcs, const int *sw, const int *sh,
+                           const size_t *spitch, uint8_t *dst, int dw, int dh, size_t dpitch,
+                           const double *H, int border_rule, int nthreads);
+
 /* cv::undistort(src, dst, K, dist) with bilinear interpolation and BORDER_CONSTANT 0
  * (tools/stitch/main.cpp:148-149).  K = fx,0,cx,0,fy,cy,0,0,1
  * row-major; dist has n_dist (0, 4, 5 or 8) coefficients k1 k2 p1 p2 k3 k4 k5 k6. */

@@ -45,6 +45,7 @@ struct Slot {
 struct TmapEntry {
     const void *ptr = nullptr;
     size_t pitch = 0;
+    int box_h = 0;                        // lens plans: rows of the box the map was encoded with
     CUtensorMap map;
 };
 constexpr int kTmapCacheWays = 8;
@@ -66,6 +67,23 @@ struct LensModel {
     int grid = 0, smem_bytes = 0, box_h = 0;
     TmapEntry tmaps[kTmapCacheWays];          // source frames come from small rings
     unsigned tmap_next = 0;
+    // what the combined launch over several cameras is built from (LensSet): the plan before it was dealt to warps
+    std::vector<bs::WorkItem> items_host;     // two-layer blocks first (a lens plan has none), then one item per block
+    std::vector<bs::CubicCoef> cubic_blocks;  // per block, row-major
+    int n_items = 0, n_two = 0, blocks_x = 0;
+};
+
+// The lens plans of all cameras of a handle dealt to the warps of ONE launch (a 4K frame alone gives a warp only
+// 3.4 blocks: four frames in one launch amortise the per-warp set-up and fill the tail).  Rebuilt whenever a
+// camera's model changes; valid with two or more plans.
+struct LensSet {
+    bool valid = false;
+    std::vector<int> cams;
+    bs::WorkItem *d_items = nullptr;
+    bs::CubicCoef *d_cubic = nullptr;
+    int *d_warp_start = nullptr;
+    int grid = 0, smem_bytes = 0, box_h = 0;
+    uint64_t bytes = 0;
 };
 
 }  // namespace
@@ -84,6 +102,8 @@ struct bs_handle {
     int64_t next_ticket = 0;
     int64_t kernel_launches = 0;
     std::vector<LensModel> lens;         // per camera
+    LensSet lens_set;                    // their plans as one launch
+    bs::UndistortArgs *d_lens_models = nullptr;   // n_cams entries: model constants the lens launches read (rare paths)
     std::vector<int> up_x0, up_y0, up_x1, up_y1;   // per camera: source texels the plan can touch (inclusive); empty = whole frame
     std::vector<uint8_t *> d_undist;     // undistorted frames for bs_submit_device (one set, stream-ordered)
     // tile plan (static per calibration)
@@ -517,8 +537,8 @@ int build_plan(bs_handle *h)
         h->smem_bytes = bs::kWarps2 * bs::kWarp2Smem + 128;
         int per_sm = 0;
         if (h->smem_bytes > optin) return BS_OK;
-        BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-        BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel, bs::kFast2Threads, h->smem_bytes));
+        BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+        BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<false>, bs::kFast2Threads, h->smem_bytes));
         if (per_sm < 1) return BS_OK;
         h->grid = std::max(1, std::min((h->n_blocks + bs::kWarps2 - 1) / bs::kWarps2, per_sm * sms));
         if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
@@ -578,6 +598,74 @@ bs::UndistortArgs lens_args(const bs_handle *h, const LensModel &m, int i)
     return U;
 }
 
+// One launch of the compact frame kernel over lens plans (stitch_undistort.cuh): cv::undistort of one frame of each
+// camera in `cams`, src[k] -> dst[k].  `items` / `warp_start` / `cubic` are either one camera's plan or the
+// handle's LensSet; every item names its camera.  All buffers 16-byte aligned (the callers check).
+int launch_lens(bs_handle *h, const int *cams, int n, const bs::WorkItem *d_items, const int *d_warp_start, const bs::CubicCoef *d_cubic,
+                int grid, int smem_bytes, int box_h, const void *const *d_src, const size_t *spitch, uint8_t *const *d_dst,
+                const size_t *dpitch, cudaStream_t stream, bool sources_from_kernel)
+{
+    bs::Fast2Args FA;
+    memset(&FA, 0, sizeof FA);
+    FA.F.n_cams = h->n_cams < bs::kMaxCamsPerLaunch ? h->n_cams : bs::kMaxCamsPerLaunch;
+    FA.F.block_w = 1;
+    FA.F.canvas_in_4g = 1;
+    for (int k = 0; k < n; ++k) {
+        const int c = cams[k];
+        LensModel &m = h->lens[c];
+        FA.F.cam[c].ptr = static_cast<const uint8_t *>(d_src[k]);
+        FA.F.cam[c].pitch = (long long)spitch[k];
+        FA.F.cam[c].w = h->sw[c];
+        FA.F.cam[c].h = h->sh[c];
+        FA.lens_dst[c] = d_dst[k];
+        FA.lens_dpitch[c] = (long long)dpitch[k];
+        if (!canvas_in_4g(d_dst[k], dpitch[k], h->sh[c])) FA.F.canvas_in_4g = 0;
+        TmapEntry *hit = nullptr;
+        for (int w = 0; w < kTmapCacheWays && !hit; ++w)
+            if (m.tmaps[w].ptr == d_src[k] && m.tmaps[w].pitch == spitch[k] && m.tmaps[w].box_h == box_h) hit = &m.tmaps[w];
+        if (!hit) {
+            hit = &m.tmaps[m.tmap_next++ % kTmapCacheWays];
+            hit->ptr = nullptr;
+            const int er = encode_frame_map(&hit->map, d_src[k], spitch[k], h->sh[c], bs::kRawPitch / 4, box_h);
+            if (er != 0) return fail(h, BS_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for the lens plan of camera %d", er, c);
+            hit->ptr = d_src[k];
+            hit->pitch = spitch[k];
+            hit->box_h = box_h;
+        }
+        FA.tmap[c] = hit->map;
+    }
+    FA.F.canvas = FA.lens_dst[cams[0]];      // not used by lens launches; kept valid for debuggers
+    FA.F.cpitch = FA.lens_dpitch[cams[0]];
+    FA.F.W = h->sw[cams[0]];
+    FA.F.H = h->sh[cams[0]];
+    FA.items = d_items;
+    FA.warp_start = d_warp_start;
+    FA.box_bytes = bs::kRawPitch * box_h;
+    FA.wait_sources = sources_from_kernel ? 1 : 0;
+    FA.lens_cubic = d_cubic;
+    FA.lens_models = h->d_lens_models;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof cfg);
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(bs::kFast2Threads);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel<true>, FA));
+    if (getenv("BS_DEBUG_SYNC")) {
+        cudaError_t e1 = cudaDeviceSynchronize();
+        if (e1 != cudaSuccess)
+            return fail(h, BS_ERR_CUDA, "[debug] lens kernel over %d camera(s) (first %d, grid %d, smem %d, box rows %d) faulted: %s", n, cams[0],
+                        grid, smem_bytes, box_h, cudaGetErrorString(e1));
+    }
+    h->kernel_launches++;
+    return BS_OK;
+}
+
 // cv::undistort of one frame of camera `cam` (which has a lens model) between device buffers.
 // `sources_from_kernel`: see launch_frame.
 int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8_t *d_dst, size_t dpitch, cudaStream_t stream,
@@ -588,60 +676,8 @@ int undistort_one(bs_handle *h, int cam, const void *d_src, size_t spitch, uint8
                           (reinterpret_cast<uintptr_t>(d_dst) & 3) == 0 && (dpitch & 3) == 0;
     if (m.plan_ok && aligned16(d_src, spitch) && aligned16(d_dst, dpitch)) {
         // the lens field as a block plan: the compact frame kernel resamples the frame (stitch_undistort.cuh)
-        bs::Fast2Args FA;
-        memset(&FA, 0, sizeof FA);
-        FA.F.n_cams = 1;
-        FA.F.cam[0].ptr = static_cast<const uint8_t *>(d_src);
-        FA.F.cam[0].pitch = (long long)spitch;
-        FA.F.cam[0].w = h->sw[cam];
-        FA.F.cam[0].h = h->sh[cam];
-        FA.F.canvas = d_dst;
-        FA.F.cpitch = (long long)dpitch;
-        FA.F.W = h->sw[cam];
-        FA.F.H = h->sh[cam];
-        FA.F.block_w = 1;
-        FA.F.canvas_in_4g = canvas_in_4g(d_dst, dpitch, h->sh[cam]);
-        TmapEntry *hit = nullptr;
-        for (int k = 0; k < kTmapCacheWays && !hit; ++k)
-            if (m.tmaps[k].ptr == d_src && m.tmaps[k].pitch == spitch) hit = &m.tmaps[k];
-        if (!hit) {
-            hit = &m.tmaps[m.tmap_next++ % kTmapCacheWays];
-            hit->ptr = nullptr;
-            const int er = encode_frame_map(&hit->map, d_src, spitch, h->sh[cam], bs::kRawPitch / 4, m.box_h);
-            if (er != 0) return fail(h, BS_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for the lens plan of camera %d", er, cam);
-            hit->ptr = d_src;
-            hit->pitch = spitch;
-        }
-        FA.tmap[0] = hit->map;
-        FA.items = m.d_items;
-        FA.warp_start = m.d_warp_start;
-        FA.box_bytes = bs::kRawPitch * m.box_h;
-        FA.wait_sources = sources_from_kernel ? 1 : 0;
-        FA.lens_mode = 1;
-        FA.lens_cubic = m.d_cubic;
-        FA.lens = lens_args(h, m, cam);
-        FA.lens.src = static_cast<const uint8_t *>(d_src);
-        FA.lens.dst = d_dst;
-        FA.lens.spitch = (long long)spitch;
-        FA.lens.dpitch = (long long)dpitch;
-        cudaLaunchConfig_t cfg;
-        memset(&cfg, 0, sizeof cfg);
-        cfg.gridDim = dim3(m.grid);
-        cfg.blockDim = dim3(bs::kFast2Threads);
-        cfg.dynamicSmemBytes = (size_t)m.smem_bytes;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel, FA));
-        if (getenv("BS_DEBUG_SYNC")) {
-            cudaError_t e1 = cudaDeviceSynchronize();
-            if (e1 != cudaSuccess)
-                return fail(h, BS_ERR_CUDA, "[debug] lens kernel of camera %d (grid %d, smem %d, box rows %d) faulted: %s", cam, m.grid,
-                            m.smem_bytes, m.box_h, cudaGetErrorString(e1));
-        }
+        return launch_lens(h, &cam, 1, m.d_items, m.d_warp_start, m.d_cubic, m.grid, m.smem_bytes, m.box_h, &d_src, &spitch, &d_dst, &dpitch,
+                           stream, sources_from_kernel);
     } else if (m.d_map && aligned4) {
         // cached map: one word per pixel instead of the fp64 lens model (stitch_undistort.cuh)
         bs::RemapArgs R;
@@ -683,6 +719,30 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
                      const void **out_frames, size_t *out_pitch, cudaStream_t stream, bool sources_from_kernel, bool *launched = nullptr)
 {
     if (launched) *launched = false;
+    // all lens plans in one launch when every member's buffers qualify
+    const LensSet &S = h->lens_set;
+    bool use_set = S.valid;
+    for (size_t k = 0; k < S.cams.size() && use_set; ++k) {
+        const int c = S.cams[k];
+        use_set = (int)tmp.size() >= h->n_cams && tmp[c] && aligned16(d_frames[c], pitch[c]) && aligned16(tmp[c], h->d_frame_pitch[c]);
+    }
+    if (use_set) {
+        const void *src[bs::kMaxCamsPerLaunch];
+        size_t sp[bs::kMaxCamsPerLaunch], dp[bs::kMaxCamsPerLaunch];
+        uint8_t *dst[bs::kMaxCamsPerLaunch];
+        const int n = (int)S.cams.size();
+        for (int k = 0; k < n; ++k) {
+            const int c = S.cams[k];
+            src[k] = d_frames[c];
+            sp[k] = pitch[c];
+            dst[k] = tmp[c];
+            dp[k] = h->d_frame_pitch[c];
+        }
+        const int rc = launch_lens(h, S.cams.data(), n, S.d_items, S.d_warp_start, S.d_cubic, S.grid, S.smem_bytes, S.box_h, src, sp, dst, dp,
+                                   stream, sources_from_kernel);
+        if (rc != BS_OK) return rc;
+        if (launched) *launched = true;
+    }
     for (int i = 0; i < h->n_cams; ++i) {
         out_frames[i] = d_frames[i];
         out_pitch[i] = pitch[i];
@@ -690,11 +750,12 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
         const LensModel &m = h->lens[i];
         if ((int)tmp.size() < h->n_cams || !tmp[i])     // allocated by bs_set_undistort / ensure_ring, never here
             return fail(h, BS_ERR_INVALID_ARG, "internal: no undistort buffer for camera %d", i);
+        out_frames[i] = tmp[i];
+        out_pitch[i] = h->d_frame_pitch[i];
+        if (use_set && m.plan_ok && std::find(S.cams.begin(), S.cams.end(), i) != S.cams.end()) continue;   // done above
         const int rc = undistort_one(h, i, d_frames[i], pitch[i], tmp[i], h->d_frame_pitch[i], stream, sources_from_kernel);
         if (rc != BS_OK) return rc;
         if (launched) *launched = true;
-        out_frames[i] = tmp[i];
-        out_pitch[i] = h->d_frame_pitch[i];
     }
     return BS_OK;
 }
@@ -810,7 +871,7 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             FA2.wait_sources = sources_from_kernel ? 1 : 0;
             FA2.box_bytes = bs::kRawPitch * h->box_h[0];
             cfg.blockDim = dim3(bs::kFast2Threads);
-            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel, FA2));
+            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel<false>, FA2));
         } else {
             FA1.items = h->d_items;
             FA1.warp_start = h->d_warp_start;
@@ -1041,6 +1102,10 @@ int bs_destroy(bs_handle *h)
     }
     cudaFree(h->d_items);
     cudaFree(h->d_warp_start);
+    cudaFree(h->lens_set.d_items);
+    cudaFree(h->lens_set.d_cubic);
+    cudaFree(h->lens_set.d_warp_start);
+    cudaFree(h->d_lens_models);
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_compute) cudaStreamDestroy(h->s_compute);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
@@ -1185,7 +1250,8 @@ void clear_lens(bs_handle *h, LensModel &m)
 int build_lens_plan(bs_handle *h, LensModel &m, int cam)
 {
     const int w = h->sw[cam], hh = h->sh[cam];
-    if (!get_encoder() || w * 3 < bs::kRawPitch || hh < bs::kRawRows) return BS_OK;
+    // (an item names its camera, and the launch carries 16 cameras: later cameras keep the per-pixel map)
+    if (!get_encoder() || w * 3 < bs::kRawPitch || hh < bs::kRawRows || cam >= bs::kMaxCamsPerLaunch) return BS_OK;
     const int blocks_x = (w + bs::kBlockW - 1) / bs::kBlockW, blocks_y = (hh + bs::kBlockH - 1) / bs::kBlockH;
     const int n_blocks = blocks_x * blocks_y;
     const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)n_blocks;
@@ -1219,6 +1285,7 @@ int build_lens_plan(bs_handle *h, LensModel &m, int cam)
     std::vector<bs::WorkItem> items((size_t)n_blocks * bs::kMaxLayers);
     PlanLayout L;
     layout_plan(recs.data(), n_blocks, 1, items.data(), &L, true);
+    for (int i = 0; i < L.n_items; ++i) items[i].cam = (uint8_t)cam;
     if (getenv("BS_DEBUG_PLAN_SUMMARY")) {
         long flagged = 0, direct = 0, plain = 0;
         for (int i = 0; i < L.n_items; ++i)
@@ -1232,12 +1299,12 @@ int build_lens_plan(bs_handle *h, LensModel &m, int cam)
                 L.box_h[0]);
     }
     int optin = 0, sms = 0, per_sm = 0;
-    const int smem = bs::kWarps2 * bs::kWarp2Smem + 128;
+    const int smem = bs::kWarps2 * bs::kWarp2SmemLens + 128;
     cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
     if (!L.compact || L.n_fast == 0 || smem > optin ||
-        cudaFuncSetAttribute(bs::stitch_fast2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin) != cudaSuccess ||
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel, bs::kFast2Threads, smem) != cudaSuccess || per_sm < 1) {
+        cudaFuncSetAttribute(bs::stitch_fast2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<true>, bs::kFast2Threads, smem) != cudaSuccess || per_sm < 1) {
         cudaGetLastError();
         cudaFree(d_plan);
         return BS_OK;
@@ -1268,7 +1335,90 @@ int build_lens_plan(bs_handle *h, LensModel &m, int cam)
     m.d_items = static_cast<bs::WorkItem *>(d_plan);
     m.bytes += raw_bytes + ws_bytes + cub_bytes;
     h->device_bytes += raw_bytes + ws_bytes + cub_bytes;
+    items.resize(L.n_items);
+    m.items_host.swap(items);
+    m.cubic_blocks.swap(cubic_blocks);
+    m.n_items = L.n_items;
+    m.n_two = L.n_two;
+    m.blocks_x = blocks_x;
     m.plan_ok = true;
+    return BS_OK;
+}
+
+void clear_lens_set(bs_handle *h)
+{
+    LensSet &S = h->lens_set;
+    cudaFree(S.d_items);
+    cudaFree(S.d_cubic);
+    cudaFree(S.d_warp_start);
+    h->device_bytes -= S.bytes;
+    S = LensSet();
+}
+
+// Deal the lens plans of all cameras that have one to the warps of one launch (see LensSet).
+int build_lens_set(bs_handle *h)
+{
+    clear_lens_set(h);
+    LensSet &S = h->lens_set;
+    static const bool never = getenv("BS_DEBUG_NO_LENS_SET") != nullptr;     // test hook: one launch per camera
+    if (never) return BS_OK;
+    int n_units = 0, n_two = 0, n_items = 0, n_blocks = 0;
+    for (int c = 0; c < h->n_cams && c < bs::kMaxCamsPerLaunch; ++c)
+        if (h->lens[c].enabled && h->lens[c].plan_ok) {
+            const LensModel &m = h->lens[c];
+            S.cams.push_back(c);
+            S.box_h = std::max(S.box_h, m.box_h);
+            S.smem_bytes = m.smem_bytes;
+            n_two += m.n_two;
+            n_units += m.n_items - m.n_two;
+            n_items += m.n_items;
+            n_blocks += (int)m.cubic_blocks.size();
+        }
+    if (S.cams.size() < 2) {
+        S = LensSet();
+        return BS_OK;
+    }
+    // two-layer blocks first (a lens plan has none, kept general), then the single items, cameras interleaved
+    // block by block so that the warps of a CTA work on neighbouring blocks of one frame
+    std::vector<bs::WorkItem> in;
+    in.reserve(n_items);
+    for (int c : S.cams) in.insert(in.end(), h->lens[c].items_host.begin(), h->lens[c].items_host.begin() + 2 * h->lens[c].n_two);
+    for (int c : S.cams) in.insert(in.end(), h->lens[c].items_host.begin() + 2 * h->lens[c].n_two, h->lens[c].items_host.end());
+    int sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<true>, bs::kFast2Threads, S.smem_bytes) != cudaSuccess || per_sm < 1) {
+        cudaGetLastError();
+        S = LensSet();
+        return BS_OK;
+    }
+    S.grid = std::max(1, std::min((n_blocks + bs::kWarps2 - 1) / bs::kWarps2, per_sm * sms));
+    const int n_warps = S.grid * bs::kWarps2;
+    std::vector<bs::WorkItem> grouped(in.size());
+    std::vector<int> warp_start(n_warps + 1);
+    group_items_by_warp(in.data(), n_units, n_two, n_warps, grouped.data(), warp_start.data());
+    std::vector<bs::CubicCoef> cubic(n_items);
+    for (int k = 0; k < n_items; ++k) {
+        const LensModel &m = h->lens[grouped[k].cam];
+        cubic[k] = m.cubic_blocks[(size_t)grouped[k].by * m.blocks_x + grouped[k].bx];
+    }
+    const size_t it_bytes = sizeof(bs::WorkItem) * (size_t)n_items, ws_bytes = sizeof(int) * (size_t)(n_warps + 1),
+                 cub_bytes = sizeof(bs::CubicCoef) * (size_t)n_items;
+    cudaError_t e = cudaMalloc(&S.d_items, it_bytes);
+    if (e == cudaSuccess) e = upload_now(h, S.d_items, grouped.data(), it_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&S.d_warp_start, ws_bytes);
+    if (e == cudaSuccess) e = upload_now(h, S.d_warp_start, warp_start.data(), ws_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&S.d_cubic, cub_bytes);
+    if (e == cudaSuccess) e = upload_now(h, S.d_cubic, cubic.data(), cub_bytes);
+    if (e != cudaSuccess) {
+        cudaFree(S.d_items);
+        cudaFree(S.d_warp_start);
+        cudaFree(S.d_cubic);
+        S = LensSet();
+        return fail(h, BS_ERR_CUDA, "lens set upload failed: %s", cudaGetErrorString(e));
+    }
+    S.bytes = it_bytes + ws_bytes + cub_bytes;
+    h->device_bytes += S.bytes;
+    S.valid = true;
     return BS_OK;
 }
 }  // namespace
@@ -1291,7 +1441,7 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
         m.k[i] = dist[i];
         nonzero = nonzero || dist[i] != 0.0;
     }
-    if (!K || !nonzero) return BS_OK;     // cv::undistort with a zero model is an exact copy: nothing to run
+    if (!K || !nonzero) return build_lens_set(h);     // cv::undistort with a zero model is an exact copy: nothing to run
     std::vector<double> xs, ys;
     if (build_lens_tables(h->sw[cam], h->sh[cam], K, m, xs, ys) != BS_OK)
         return fail(h, BS_ERR_UNSUPPORTED, "bs_set_undistort: camera matrix must be [[fx 0 cx] [0 fy cy] [0 0 1]]");
@@ -1306,6 +1456,15 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     if (e == cudaSuccess) {
         m.bytes = tab_bytes;
         h->device_bytes += tab_bytes;
+    }
+    // the model constants as the lens launches read them (per camera, in device memory: the launch carries pointers only)
+    if (e == cudaSuccess && !h->d_lens_models) {
+        e = cudaMalloc(&h->d_lens_models, sizeof(bs::UndistortArgs) * (size_t)h->n_cams);
+        if (e == cudaSuccess) h->device_bytes += sizeof(bs::UndistortArgs) * (size_t)h->n_cams;
+    }
+    if (e == cudaSuccess) {
+        const bs::UndistortArgs U = lens_args(h, m, cam);
+        e = upload_now(h, h->d_lens_models + cam, &U, sizeof U);
     }
     // where this camera's undistorted frames go: the device-submit buffer now, the ring's slots if they exist
     int rc = BS_OK;
@@ -1342,11 +1501,12 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     }
     if (e != cudaSuccess || rc != BS_OK) {
         clear_lens(h, m);                                    // never leave a half-built model behind
+        build_lens_set(h);
         if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "bs_set_undistort: %s", cudaGetErrorString(e));
         return rc;
     }
     m.enabled = true;
-    return BS_OK;
+    return build_lens_set(h);
 }
 
 int bs_undistort_device(bs_handle *h, int cam, const void *d_src, size_t spitch, void *d_dst, size_t dpitch, void *stream,

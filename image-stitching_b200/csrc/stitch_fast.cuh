@@ -413,15 +413,15 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr)
 }
 
 // Rows x 96 bytes of one block, with bounds checks: zero fill (src == 0) or copy from shared.
-__device__ __noinline__ void store_block_checked(const FrameArgs &F, uint32_t src, int tx0, int ty0, int lane)
+__device__ __noinline__ void store_block_checked(uint8_t *canvas, long long cpitch, int W, int H, uint32_t src, int tx0, int ty0, int lane)
 {
-    const int wbytes = min(32, F.W - tx0) * 3;
+    const int wbytes = min(32, W - tx0) * 3;
     for (int c = lane; c < kRun * 6; c += 32) {
         const int row = c / 6, cb = (c % 6) * 16;
-        if (ty0 + row >= F.H || cb >= wbytes) continue;
+        if (ty0 + row >= H || cb >= wbytes) continue;
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (src) v = lds128(src + (uint32_t)(row * kBlockRowBytes + cb));
-        uint8_t *p = F.canvas + (long long)(ty0 + row) * F.cpitch + (long long)tx0 * 3 + cb;
+        uint8_t *p = canvas + (long long)(ty0 + row) * cpitch + (long long)tx0 * 3 + cb;
         if (cb + 16 <= wbytes) {
             *reinterpret_cast<uint4 *>(p) = v;
         } else {
@@ -596,9 +596,9 @@ __global__ void __launch_bounds__(kFastThreads, BS_MIN_CTAS) stitch_fast_kernel(
                 for (int j = 0; j < 3; ++j)
                     *reinterpret_cast<uint4 *>(gp + 32 * j) = wrote ? lds128(so + 32u * j) : make_uint4(0u, 0u, 0u, 0u);
             } else if (!wrote) {
-                store_block_checked(A.F, 0u, tx0, ty0, lane);
+                store_block_checked(A.F.canvas, A.F.cpitch, A.F.W, A.F.H, 0u, tx0, ty0, lane);
             } else {
-                store_block_checked(A.F, out_blk, tx0, ty0, lane);
+                store_block_checked(A.F.canvas, A.F.cpitch, A.F.W, A.F.H, out_blk, tx0, ty0, lane);
             }
             wrote = false;
             __syncwarp();             // the output block is free again

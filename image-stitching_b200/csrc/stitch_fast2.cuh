@@ -50,6 +50,9 @@ constexpr int kRawStages = BS2_RAW_STAGES;               // boxes in flight ahea
 constexpr int kRec2Slots = BS2_REC_SLOTS;                // record ring slots per warp (two halves)
 constexpr int kWarp2Smem = kRawStages * kRawStage + kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
 static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
+// lens launches: a second ring beside the records with every item's third-order terms (32 bytes each)
+constexpr int kWarp2SmemLens = kWarp2Smem + kRec2Slots * (int)sizeof(CubicCoef);
+static_assert(sizeof(CubicCoef) == 32 && kWarp2SmemLens % 128 == 0, "cubic ring");
 static_assert(kRawStages == 2, "the item pipeline is written for two raw stages");
 
 #ifndef BS2_WARPS_PER_CTA
@@ -69,9 +72,14 @@ struct Fast2Args {
     int box_bytes;                         // 128 * box rows (all cameras use the same box; what the mbarrier expects)
     int wait_sources;                      // 1: the source frames may come from the kernel just before this one in
                                            // the stream: order every source read behind it (griddepcontrol.wait first)
-    int lens_mode;                         // 1: the plan is a lens plan (cv::undistort of one frame, stitch_undistort.cuh):
-    UndistortArgs lens;                    //    its EXACT blocks evaluate this model with BORDER_CONSTANT 0,
-    const CubicCoef *lens_cubic;           //    and item k's expansion has the third-order terms lens_cubic[k]
+    // Lens launches only (stitch_fast2_kernel<true>: cv::undistort of one frame of each of up to 16 cameras in ONE
+    // launch, stitch_undistort.cuh).  An item's camera field names the camera c it belongs to: F.cam[c] is the
+    // distorted frame, lens_dst[c] the frame to write (same size), lens_models[c] the model its EXACT blocks and
+    // flagged rows evaluate (BORDER_CONSTANT 0), and item k's expansion has the third-order terms lens_cubic[k].
+    const UndistortArgs *lens_models;      // device array indexed by camera; the frame pointers in it are not used
+    const CubicCoef *lens_cubic;
+    uint8_t *lens_dst[kMaxCamsPerLaunch];
+    long long lens_dpitch[kMaxCamsPerLaunch];
 };
 
 // ---- packed fp32 pairs (x in the low half, y in the high half) -------------------------------------
@@ -420,6 +428,8 @@ __device__ __noinline__ void patch_lens2(const UndistortArgs &U, uint32_t conv_o
     }
 }
 
+// kLens = false: the panorama frame kernel.  kLens = true: the same loop over a lens plan (stitch_undistort.cuh).
+template <bool kLens>
 __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kernel(const __grid_constant__ Fast2Args A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -427,13 +437,14 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const uint32_t raw0 = raw_base + (uint32_t)(warp * kWarp2Smem);           // 128-byte aligned
+    const uint32_t raw0 = raw_base + (uint32_t)(warp * (kLens ? kWarp2SmemLens : kWarp2Smem));   // 128-byte aligned
     const uint32_t conv0 = raw0 + kRawStages * kRawStage;
     const uint32_t out_blk = conv0 + kConvRegion;
     const uint32_t rec0 = out_blk + kWarpOutBytes;
     constexpr uint32_t rec_slots = kRec2Slots, rec_half = kRec2Slots / 2;
     const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per raw stage
     const uint32_t rbar0 = dbar0 + 16;                                         // record barriers, one per half of the ring
+    const uint32_t cub0 = raw0 + kWarp2Smem;                                   // lens launches: ring of third-order terms
 
     // Programmatic dependent launch, as in stitch_fast_kernel: the next frame's kernel may start at once;
     // it touches the canvas only after griddepcontrol.wait.
@@ -452,13 +463,19 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
 
     // lane 0 is this warp's producer ------------------------------------------------------------------
     auto request_records = [&](int first) {
-        const uint32_t bytes = (uint32_t)(min((int)rec_half, cnt - first) * kRecBytes);
+        const uint32_t n_rec = (uint32_t)min((int)rec_half, cnt - first);
+        const uint32_t bytes = n_rec * kRecBytes, cbytes = kLens ? n_rec * (uint32_t)sizeof(CubicCoef) : 0u;
         const uint32_t half = ((uint32_t)first / rec_half) & 1u;
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * half), "r"(bytes) : "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(rbar0 + 8 * half), "r"(bytes + cbytes) : "memory");
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                          rec0 + kRecBytes * rec_half * half),
                      "l"(A.items + i0 + first), "r"(bytes), "r"(rbar0 + 8 * half)
                      : "memory");
+        if constexpr (kLens)        // the items' third-order terms ride on the same barrier
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             cub0 + (uint32_t)sizeof(CubicCoef) * rec_half * half),
+                         "l"(A.lens_cubic + i0 + first), "r"(cbytes), "r"(rbar0 + 8 * half)
+                         : "memory");
     };
     // source box of the item whose header words are `r` -> raw stage; items without a box just arrive
     const uint64_t tmap0 = reinterpret_cast<uint64_t>(&A.tmap[0]);
@@ -521,8 +538,32 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const float uf = (float)u;
     // this lane's word of canvas row 0, block column 0; a block adds by * 16 * pitch + bx * 96 (32-bit: direct
     // stores need the canvas inside one 4 GB window anyway)
-    const uint64_t gbase = reinterpret_cast<uint64_t>(A.F.canvas) + 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
+    const uint32_t lane_word = 4u * (uint32_t)(3 * (lane >> 2) + (lane & 3));
+    const uint64_t gbase = reinterpret_cast<uint64_t>(A.F.canvas) + lane_word;
     const uint32_t cpitch = (uint32_t)A.F.cpitch, brow = cpitch * kBlockH;
+    // where an item's pixels go: the canvas, or (lens launches) the undistorted frame of the item's camera
+    struct Dst {
+        uint8_t *base;
+        long long pitch;
+        int W, H;
+    };
+    auto dst_of = [&](uint32_t hdr_y) {
+        if constexpr (kLens) {
+            const uint32_t c = (hdr_y >> 16) & 0xFFu;
+            return Dst{A.lens_dst[c], A.lens_dpitch[c], A.F.cam[c].w, A.F.cam[c].h};
+        } else {
+            return Dst{A.F.canvas, A.F.cpitch, A.F.W, A.F.H};
+        }
+    };
+    auto lens_of = [&](uint32_t hdr_y) {     // the model of the item's camera with this launch's frames (rare paths)
+        const uint32_t c = (hdr_y >> 16) & 0xFFu;
+        UndistortArgs U = A.lens_models[c];
+        U.src = A.F.cam[c].ptr;
+        U.spitch = A.F.cam[c].pitch;
+        U.dst = A.lens_dst[c];
+        U.dpitch = A.lens_dpitch[c];
+        return U;
+    };
     bool wrote = false;               // some layer has written into the current block
     bool can_direct = prior_grid_done && A.F.canvas_in_4g;
     for (int n = 0; n < cnt; ++n) {
@@ -546,11 +587,13 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
         if (type == (uint32_t)kBlockFast) {
             const BlockCoef bc = load_block_coef(ra);
             LaneCoef2 lc;
-            if (A.lens_mode) {
+            if constexpr (kLens) {
                 CubicCoef q;
-                const float4 q0 = __ldg(reinterpret_cast<const float4 *>(A.lens_cubic + i0 + n));
-                const float2 q1 = __ldg(reinterpret_cast<const float2 *>(A.lens_cubic + i0 + n) + 2);
-                q.xuuu = q0.x; q.yuuu = q0.y; q.xuuv = q0.z; q.yuuv = q0.w; q.xuvv = q1.x; q.yuvv = q1.y;
+                const uint32_t qa = cub0 + (uint32_t)sizeof(CubicCoef) * ((uint32_t)n & (rec_slots - 1));
+                const uint4 q0 = lds128(qa);
+                const uint2 q1 = lds64(qa + 16);
+                q.xuuu = __uint_as_float(q0.x); q.yuuu = __uint_as_float(q0.y); q.xuuv = __uint_as_float(q0.z);
+                q.yuuv = __uint_as_float(q0.w); q.xuvv = __uint_as_float(q1.x); q.yuvv = __uint_as_float(q1.y);
                 lc = lane_coef2_cubic(bc, q, uf);
             } else {
                 lc = lane_coef2(bc, uf);
@@ -560,17 +603,25 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             const uint32_t groups = r.y >> 24;
             if (flags & kItemFull) {
                 direct = can_direct && (flags & kItemDirect);
-                const uint64_t grow = gbase + (by * brow + bx * (uint32_t)kBlockRowBytes);
+                uint64_t grow;
+                uint32_t rpitch = cpitch;
+                if constexpr (kLens) {
+                    const uint32_t c = (r.y >> 16) & 0xFFu;
+                    rpitch = (uint32_t)A.lens_dpitch[c];
+                    grow = reinterpret_cast<uint64_t>(A.lens_dst[c]) + lane_word + (by * (rpitch * kBlockH) + bx * (uint32_t)kBlockRowBytes);
+                } else {
+                    grow = gbase + (by * brow + bx * (uint32_t)kBlockRowBytes);
+                }
                 if (direct && (flags & kItemPlain))
-                    run_full2<true, true>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
+                    run_full2<true, true>(lc, run0, vstep, out_blk, lane, grow, rpitch, sel, storing);
                 else if (direct)
-                    run_full2<true, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
+                    run_full2<true, false>(lc, run0, vstep, out_blk, lane, grow, rpitch, sel, storing);
                 else
-                    run_full2<false, false>(lc, run0, vstep, out_blk, lane, grow, cpitch, sel, storing);
+                    run_full2<false, false>(lc, run0, vstep, out_blk, lane, grow, rpitch, sel, storing);
                 if (groups != 0u) {
                     __syncwarp();
-                    if (A.lens_mode)
-                        patch_lens2(A.lens, conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane, (int)by * kBlockH, lane);
+                    if constexpr (kLens)
+                        patch_lens2(lens_of(r.y), conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane, (int)by * kBlockH, lane);
                     else
                         patch_exact2(A.F, A.F.cam[(r.y >> 16) & 0xFFu], conv_origin_of(conv, r), out_blk, groups, (int)bx * kBlockW + lane,
                                      (int)by * kBlockH, lane);
@@ -579,9 +630,10 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                 const CamDev &cam = A.F.cam[(r.y >> 16) & 0xFFu];
                 const LaneBase2 lb = lane_base2(bc, u);
                 const int tx0 = (int)bx * kBlockW, ty0 = (int)by * kBlockH;
+                const Dst d = dst_of(r.y);
                 if (groups == 0u)
-                    run_masked2(lc, lb, run0, vstep, out_blk, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
-                else
+                    run_masked2(lc, lb, run0, vstep, out_blk, lane, cam.w, cam.h, tx0 + lane < d.W, d.H - ty0, !wrote);
+                else          // (the lens plan has no partially covered layers: its blocks are full, EXACT or EMPTY)
                     run_general2(A.F, cam, lc, lb, conv_origin_of(conv, r), out_blk, groups, !wrote, tx0 + lane, ty0, lane);
             }
             wrote = !direct;
@@ -594,27 +646,29 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
                 prior_grid_done = true;
                 can_direct = A.F.canvas_in_4g != 0;
             }
+            const Dst d = dst_of(r.y);
             if (type == (uint32_t)kBlockExact) {
                 // lane takes the 4-pixel group (lane & 7) of rows (lane >> 3) + 4 j; the item names its row groups j
                 const uint32_t rows = r.y >> 24;
-                for (int j = 0; j < kRun / 4; ++j)
-                    if ((rows >> j) & 1u) {
-                        if (A.lens_mode) lens_quad(A.lens, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
-                        else exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
-                    }
-            } else if (!wrote && A.F.keep_canvas) {
+                if constexpr (kLens) {
+                    const UndistortArgs U = lens_of(r.y);
+                    for (int j = 0; j < kRun / 4; ++j)
+                        if ((rows >> j) & 1u) lens_quad(U, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+                } else {
+                    for (int j = 0; j < kRun / 4; ++j)
+                        if ((rows >> j) & 1u) exact_quad(A.F, tx0 + (lane & 7) * 4, ty0 + (lane >> 3) + 4 * j);
+                }
+            } else if (!wrote && !kLens && A.F.keep_canvas) {
                 // nobody writes here and the canvas keeps its contents
-            } else if (tx0 + kBlockW <= A.F.W && ty0 + kRun <= A.F.H) {
+            } else if (tx0 + kBlockW <= d.W && ty0 + kRun <= d.H) {
                 // flush (or zero fill of an empty block): lane pair (2r, 2r+1) writes one full 32-byte sector of row r per instruction
                 const uint32_t so = out_blk + (uint32_t)((lane >> 1) * kBlockRowBytes + (lane & 1) * 16);
-                uint8_t *const gp = A.F.canvas + (long long)(ty0 + (lane >> 1)) * A.F.cpitch + (long long)tx0 * 3 + (lane & 1) * 16;
+                uint8_t *const gp = d.base + (long long)(ty0 + (lane >> 1)) * d.pitch + (long long)tx0 * 3 + (lane & 1) * 16;
 #pragma unroll
                 for (int j = 0; j < 3; ++j)
                     *reinterpret_cast<uint4 *>(gp + 32 * j) = wrote ? lds128(so + 32u * j) : make_uint4(0u, 0u, 0u, 0u);
-            } else if (!wrote) {
-                store_block_checked(A.F, 0u, tx0, ty0, lane);
             } else {
-                store_block_checked(A.F, out_blk, tx0, ty0, lane);
+                store_block_checked(d.base, d.pitch, d.W, d.H, wrote ? out_blk : 0u, tx0, ty0, lane);
             }
             wrote = false;
             __syncwarp();             // the output block is free again

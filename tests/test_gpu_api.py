@@ -210,3 +210,41 @@ def test_pool_reports_a_failed_frame():
         with pytest.raises(p.StitchError) as e:
             pool.wait(idx.value)
         assert "frame 1 on device 0" in str(e.value) and "pitch" in str(e.value)
+
+
+def test_lens_set_mixed_cameras():
+    """All cameras' lens plans run as one launch: cameras of different sizes and models, one camera without a model
+    in between, a model replaced and one removed afterwards (the set is rebuilt each time)."""
+    p = pkg()
+    whs = [(640, 360), (512, 300), (704, 400)]
+    Hs = [np.array([[1.02, 0.004, 5.0 + 420 * i], [-0.003, 0.99, 3.0 + 2 * i], [1e-6 * (i - 1), -5e-7, 1.0]]) for i in range(3)]
+    W, Hc = 1400, 440
+    frames = [oracle.gen_frame(w_, h_, i, 3, oracle.NOISE) for i, (w_, h_) in enumerate(whs)]
+    models = {0: lens(*whs[0], 0), 2: lens(*whs[2], 1)}
+
+    def want():
+        und = [oracle.undistort(frames[i], *models[i]) if i in models else frames[i] for i in range(3)]
+        return oracle.stitch(und, Hs, (W, Hc))
+
+    with p.Stitcher(whs, (W, Hc), Hs) as st:
+        for i, m in models.items():
+            st.set_undistort(i, *m)
+        got = st.stitch(frames)
+        assert np.array_equal(got, want())
+        launches = st.stats()["kernel_launches"]
+        st.stitch(frames)
+        assert st.stats()["kernel_launches"] - launches == 2, "one lens launch for both cameras + the frame kernel"
+        models[1] = lens(*whs[1], 0)             # a third member
+        st.set_undistort(1, *models[1])
+        assert np.array_equal(st.stitch(frames), want())
+        models[0] = lens(*whs[0], 1)             # replaced
+        st.set_undistort(0, *models[0])
+        assert np.array_equal(st.stitch(frames), want())
+        del models[2]                            # removed (zero model = copy)
+        st.set_undistort(2, np.eye(3), np.zeros(5))
+        assert np.array_equal(st.stitch(frames), want())
+        d_in = [dev(f) for f in frames]          # device submit through the same set
+        d_out = torch.zeros((Hc, W, 3), dtype=torch.uint8, device="cuda")
+        st.submit_device([t.data_ptr() for t in d_in], [t.stride(0) for t in d_in], d_out.data_ptr(), d_out.stride(0), 0)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_out.cpu().numpy(), want())

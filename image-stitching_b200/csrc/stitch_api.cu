@@ -354,7 +354,8 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
                 it.flags |= (uint8_t)(((3 * t0 - 4 * (int)it.c0) >> 2) << bs::kItemRawOffShift);
                 if (r.layer[l].full && r.layer[l].groups == 0 && nl == 1) {
                     it.flags |= bs::kItemDirect;
-                    if (!r.layer[l].zero_frac && vstep == bs::kConvPitch) it.flags |= bs::kItemPlain;
+                    static const bool no_plain = getenv("BS_DEBUG_NO_PLAIN") != nullptr;   // experiment hook: one hot-loop variant only
+                    if (!r.layer[l].zero_frac && vstep == bs::kConvPitch && !no_plain) it.flags |= bs::kItemPlain;
                 }
             }
         }

@@ -238,6 +238,29 @@ __device__ __forceinline__ uint32_t tap_addr(uint32_t base, int xbits, int ybits
     const uint32_t ym = (uint32_t)ybits & ~31u, xm = (uint32_t)xbits & ~31u;
     return __umulhi(xm, 1u << 29) + (ym * (uint32_t)(kConvPitch / 32) + base);      // LEA.HI + IMAD
 }
+// The hot loop's form of the same address.  `s` = the coordinate pair after the magic add, i.e. the floats
+// 1.5 * 2^23 + X (X = the 1/32-pixel integers).  fma.rm(s, 1/32, 2^23) = floor(393216 + X / 32 + 2^23) exactly
+// (the sum lies in [2^23, 2^24): one ulp is 1, round-down is floor), so its bits are kTexelBias + floor(X / 32) and
+// the address is base + 4 qx + pitch qy with the bias folded into `base` (tap_base_bias): FFMA2 + IMAD + LEA
+// instead of two masks + IMAD + LEA.HI.
+constexpr uint32_t kTexelBias = 0x4B000000u + 393216u;
+// tap_addr() sees the texel indices with the bias of the magic add, (0x4B400000 >> 5), and the host folded that
+// into the item's run base; tap_addr_q() sees them with kTexelBias: the difference, mod 2^32
+constexpr uint32_t kTapBaseBias = (kTexelBias - (0x4B400000u >> 5)) * (4u + (uint32_t)kConvPitch);
+__device__ __forceinline__ uint64_t fma2_rm(uint64_t a, uint64_t b, uint64_t c)
+{
+    uint64_t d;
+    asm("fma.rm.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t tap_addr_q(uint32_t biased_base, uint64_t s)
+{
+    int qx, qy;
+    unpack2(fma2_rm(s, pack2(0.03125f, 0.03125f), pack2(8388608.0f, 8388608.0f)), qx, qy);
+    uint32_t a;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(a) : "r"((uint32_t)qy), "n"(kConvPitch), "r"(biased_base));
+    return a + 4u * (uint32_t)qx;
+}
 // tap_weights() of stitch_fast.cuh with the subtraction kept as one shift-and-subtract (LEA).
 __device__ __forceinline__ uint2 tap_weights2(uint32_t a, uint32_t b)
 {
@@ -281,18 +304,19 @@ __device__ __forceinline__ void run_full2(const LaneCoef2 &lc, uint32_t run0, in
     // The 16 rows run as kRun / kRowsPerPass passes of an unrolled body (one pass by default: two passes of
     // eight rows halve the code, but cost four more instructions per row and were 7 % slower).
     float vf = (float)(-kRun / 2);          // row offset v of the pixel being fetched: -8, -7, ... (exact in fp32)
-    uint32_t rbase = run0;                  // converted-buffer base of the current pass
+    uint32_t rbase = run0 - kTapBaseBias;   // converted-buffer base of the current pass (tap_addr_q's form)
     auto fetch = [&](auto jc) {
         constexpr int j = decltype(jc)::value;
         const uint64_t v2 = pack2(vf, vf);
         const uint64_t sxy = fma2(v2, fma2(v2, lc.a2, lc.a1), lc.a0);
         int xbits, ybits;
-        unpack2(add2(sxy, pack2(12582912.0f, 12582912.0f)), xbits, ybits);
+        const uint64_t sm = add2(sxy, pack2(12582912.0f, 12582912.0f));
+        unpack2(sm, xbits, ybits);
         vf += 1.0f;
         if constexpr (kPlain)
-            return fetch_taps2<j * kConvPitch>(tap_addr(rbase, xbits, ybits), tap_weights2_nz((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
+            return fetch_taps2<j * kConvPitch>(tap_addr_q(rbase, sm), tap_weights2_nz((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
         else
-            return fetch_taps2<0>(tap_addr(rbase + (uint32_t)(j * vstep), xbits, ybits),
+            return fetch_taps2<0>(tap_addr_q(rbase + (uint32_t)(j * vstep), sm),
                                   tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u));
     };
     Taps2 cur = fetch(std::integral_constant<int, 0>{});

@@ -9,7 +9,75 @@
 // which is why the parity tests feed raw pixels and the JPEG tests compare against nvJPEG's own decode.
 #include <nvjpeg.h>
 
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
+
 namespace {
+
+// The entropy (Huffman) stage of a baseline JPEG is sequential and, on this image's nvJPEG, runs on the host:
+// ~20 ms for a 4K frame.  The cameras of one frame are independent, so bs_submit_jpeg runs their host stages on
+// a few worker threads of its own (nvJPEG's decoupled API: parse + nvjpegDecodeJpegHost per camera in parallel,
+// then transfer + device stage on the upload stream in camera order).
+struct JpegLane {                              // one camera of one pipeline slot
+    nvjpegJpegState_t state = nullptr;
+    nvjpegBufferPinned_t pinned = nullptr;
+    nvjpegBufferDevice_t device = nullptr;
+    nvjpegJpegStream_t stream = nullptr;
+};
+
+struct JpegWorkers {
+    std::vector<std::thread> th;
+    std::mutex m;
+    std::condition_variable cv_job, cv_done;
+    std::function<void(int)> job;              // job(i) for i in [0, n_jobs)
+    int n_jobs = 0, next = 0, done = 0;
+    uint64_t generation = 0;
+    bool stop = false;
+
+    void start(int n, int device)
+    {
+        for (int k = 0; k < n; ++k)
+            th.emplace_back([this, device] {
+                cudaSetDevice(device);
+                uint64_t seen = 0;
+                std::unique_lock<std::mutex> lk(m);
+                for (;;) {
+                    cv_job.wait(lk, [&] { return stop || (generation != seen && next < n_jobs); });
+                    if (stop) return;
+                    while (next < n_jobs) {
+                        const int i = next++;
+                        lk.unlock();
+                        job(i);
+                        lk.lock();
+                        if (++done == n_jobs) cv_done.notify_all();
+                    }
+                    seen = generation;
+                }
+            });
+    }
+    void run(int n, std::function<void(int)> f)    // returns when every job(i) has finished
+    {
+        std::unique_lock<std::mutex> lk(m);
+        job = std::move(f);
+        n_jobs = n;
+        next = done = 0;
+        ++generation;
+        cv_job.notify_all();
+        cv_done.wait(lk, [&] { return done == n_jobs; });
+        n_jobs = 0;
+    }
+    ~JpegWorkers()
+    {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            stop = true;
+        }
+        cv_job.notify_all();
+        for (auto &t : th) t.join();
+    }
+};
 
 struct JpegCtx {
     nvjpegHandle_t lib = nullptr;              // per-image decoder (host Huffman stage) and the encoder
@@ -22,7 +90,60 @@ struct JpegCtx {
     nvjpegEncoderState_t enc[kPipelineDepth] = {nullptr, nullptr, nullptr};
     nvjpegEncoderParams_t enc_params[kPipelineDepth] = {nullptr, nullptr, nullptr};
     const char *backend = "default";
+    // host entropy stage on worker threads (see JpegLane)
+    nvjpegJpegDecoder_t hdec = nullptr;
+    nvjpegDecodeParams_t hparams = nullptr;
+    std::vector<JpegLane> lanes;               // kPipelineDepth x n_cams
+    JpegWorkers *workers = nullptr;
+    bool threaded_ok = false;
 };
+
+void jpeg_lanes_destroy(JpegCtx *c)
+{
+    delete c->workers;                         // joins the threads
+    c->workers = nullptr;
+    for (JpegLane &l : c->lanes) {
+        if (l.stream) nvjpegJpegStreamDestroy(l.stream);
+        if (l.state) nvjpegJpegStateDestroy(l.state);
+        if (l.pinned) nvjpegBufferPinnedDestroy(l.pinned);
+        if (l.device) nvjpegBufferDeviceDestroy(l.device);
+    }
+    c->lanes.clear();
+    if (c->hparams) nvjpegDecodeParamsDestroy(c->hparams);
+    if (c->hdec) nvjpegDecoderDestroy(c->hdec);
+    c->hparams = nullptr;
+    c->hdec = nullptr;
+    c->threaded_ok = false;
+}
+
+// Decoupled decoder with the Huffman stage on the host + one lane per camera and slot + the worker threads.
+void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
+{
+    static const char *off = getenv("BS_DEBUG_JPEG_THREADS");       // test hook: "0" keeps the one-thread decoders
+    if (h->n_cams < 2 || (off && off[0] == '0')) return;
+    bool ok = nvjpegDecoderCreate(c->lib, NVJPEG_BACKEND_HYBRID, &c->hdec) == NVJPEG_STATUS_SUCCESS &&
+              nvjpegDecodeParamsCreate(c->lib, &c->hparams) == NVJPEG_STATUS_SUCCESS &&
+              nvjpegDecodeParamsSetOutputFormat(c->hparams, NVJPEG_OUTPUT_BGRI) == NVJPEG_STATUS_SUCCESS;
+    c->lanes.assign((size_t)kPipelineDepth * h->n_cams, JpegLane());
+    for (size_t k = 0; k < c->lanes.size() && ok; ++k) {
+        JpegLane &l = c->lanes[k];
+        ok = nvjpegDecoderStateCreate(c->lib, c->hdec, &l.state) == NVJPEG_STATUS_SUCCESS &&
+             nvjpegBufferPinnedCreate(c->lib, nullptr, &l.pinned) == NVJPEG_STATUS_SUCCESS &&
+             nvjpegBufferDeviceCreate(c->lib, nullptr, &l.device) == NVJPEG_STATUS_SUCCESS &&
+             nvjpegStateAttachPinnedBuffer(l.state, l.pinned) == NVJPEG_STATUS_SUCCESS &&
+             nvjpegStateAttachDeviceBuffer(l.state, l.device) == NVJPEG_STATUS_SUCCESS &&
+             nvjpegJpegStreamCreate(c->lib, &l.stream) == NVJPEG_STATUS_SUCCESS;
+    }
+    if (ok) {
+        c->workers = new (std::nothrow) JpegWorkers;
+        ok = c->workers != nullptr;
+        if (ok) c->workers->start(std::min(h->n_cams, 8), h->device);
+    }
+    cudaGetLastError();
+    if (!ok) jpeg_lanes_destroy(c);
+    c->threaded_ok = ok;
+    if (ok) c->backend = "hybrid, host entropy stage of the cameras on worker threads";
+}
 
 int jpeg_ctx(bs_handle *h, JpegCtx **out)
 {
@@ -74,12 +195,14 @@ int jpeg_ctx(bs_handle *h, JpegCtx **out)
     h->jpeg = c;
     *out = c;
     if (!ok) return fail(h, BS_ERR_CUDA, "nvJPEG state creation failed");
+    jpeg_lanes_create(h, c);
     return BS_OK;
 }
 
 void jpeg_ctx_destroy(JpegCtx *c)
 {
     if (!c) return;
+    jpeg_lanes_destroy(c);
     for (auto st : c->dec)
         if (st) nvjpegJpegStateDestroy(st);
     for (int k = 0; k < kPipelineDepth; ++k)
@@ -117,7 +240,27 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
         h->h2d_bytes_last += jpeg_bytes[i];
     }
     bool decoded = false;
-    if (c->batched_ok) {
+    if (c->threaded_ok) {
+        // host stages of all cameras at once on the worker threads, device stages in camera order on the upload
+        // stream; a bitstream this decoder cannot take (progressive ...) sends the frame to the decoders below
+        std::vector<int> status(h->n_cams, 0);
+        JpegLane *lanes = &c->lanes[(size_t)slot_index * h->n_cams];
+        c->workers->run(h->n_cams, [&](int i) {
+            nvjpegStatus_t st = nvjpegJpegStreamParse(c->lib, jpeg[i], jpeg_bytes[i], 0, 0, lanes[i].stream);
+            if (st == NVJPEG_STATUS_SUCCESS) st = nvjpegDecodeJpegHost(c->lib, c->hdec, lanes[i].state, c->hparams, lanes[i].stream);
+            status[i] = (int)st;
+        });
+        decoded = true;
+        for (int i = 0; i < h->n_cams; ++i) decoded = decoded && status[i] == (int)NVJPEG_STATUS_SUCCESS;
+        for (int i = 0; i < h->n_cams && decoded; ++i)
+            decoded = nvjpegDecodeJpegTransferToDevice(c->lib, c->hdec, lanes[i].state, lanes[i].stream, h->s_h2d) == NVJPEG_STATUS_SUCCESS &&
+                      nvjpegDecodeJpegDevice(c->lib, c->hdec, lanes[i].state, &imgs[i], h->s_h2d) == NVJPEG_STATUS_SUCCESS;
+        if (!decoded) {
+            cudaStreamSynchronize(h->s_h2d);       // a partly issued frame: let it drain before the fall-back rewrites the frames
+            cudaGetLastError();
+        }
+    }
+    if (!decoded && c->batched_ok) {
         // all cameras of the frame in one batch; a bitstream this backend cannot take (progressive, odd sampling)
         // sends the frame to the per-image decoder below
         decoded = nvjpegDecodeBatched(c->blib, c->bdec[slot_index], jpeg, jpeg_bytes, imgs.data(), h->s_h2d) == NVJPEG_STATUS_SUCCESS;

@@ -89,3 +89,39 @@ def test_compressed_panorama_out_and_errors():
         st.wait(t4)
     decoded = [nvjpeg_pixels(p, j, wh) for j, wh in zip(jpgs, whs)]
     assert np.array_equal(raw, oracle.stitch(decoded, H, canvas_wh))
+
+
+def test_decoders_agree():
+    """The worker-thread decoder (cameras' entropy stages in parallel), the one-thread decoders behind it
+    (BS_DEBUG_JPEG_THREADS=0, in a child process: the switch is read once) and a damaged bitstream that only shows up
+    in the entropy stage (worker thread -> fall-back -> error) all leave the handle usable and give the same pixels."""
+    import hashlib
+    import subprocess
+    import sys
+    from conftest import ROOT
+    p = pkg()
+    jpgs, H, canvas_wh, cv2_dec = fixtures()
+    whs = [(d.shape[1], d.shape[0]) for d in cv2_dec]
+    out = np.empty((canvas_wh[1], canvas_wh[0], 3), np.uint8)
+    with p.Stitcher(whs, canvas_wh, H) as st:
+        st.wait(st.submit_jpeg(jpgs, out))
+        assert "worker threads" in st.jpeg_backend()
+        want = hashlib.sha256(out.tobytes()).hexdigest()
+        broken = bytearray(jpgs[1])
+        broken[len(broken) // 2:len(broken) // 2 + 4096] = b"\xff\x00" * 2048      # header intact, scan data destroyed
+        try:
+            st.wait(st.submit_jpeg([jpgs[0], bytes(broken)], out))                  # decoders may conceal the damage or refuse it
+        except p.StitchError as e:
+            assert e.code in (-2, -1)
+        st.wait(st.submit_jpeg(jpgs, out))
+        assert hashlib.sha256(out.tobytes()).hexdigest() == want
+    code = ("import sys, json, hashlib, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r + '/tests');"
+            "from test_gpu_jpeg import fixtures; from conftest import pkg; p = pkg(); jpgs, H, cwh, dec = fixtures();"
+            "whs = [(d.shape[1], d.shape[0]) for d in dec]; out = np.empty((cwh[1], cwh[0], 3), np.uint8);"
+            "st = p.Stitcher(whs, cwh, H); st.wait(st.submit_jpeg(jpgs, out));"
+            "print(json.dumps({'sha': hashlib.sha256(out.tobytes()).hexdigest(), 'backend': st.jpeg_backend()}))") % (ROOT, ROOT)
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, BS_DEBUG_JPEG_THREADS="0"))
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = json.loads(r.stdout.strip().splitlines()[-1])
+    assert "worker threads" not in got["backend"] and got["sha"] == want

@@ -1652,13 +1652,17 @@ int bs_get_stats(const bs_handle *h, bs_stats *out)
 // cudaHostAlloc, or any host heap routine (error texts go to fixed per-thread buffers).
 //
 // The staged kernel needs scratch memory: the block plan and the per-warp work split.  Here they live
-// in ONE file-scope device array of a fixed size.  Consequences a caller must know:
+// in ONE file-scope device array of a fixed size.  A call whose calibration arguments (cameras, sizes, homographies,
+// flags) equal those of the previous call on the same device finds its plan still there and only launches the frame
+// kernel; any other call rebuilds the plan in full.  Consequences a caller must know:
 //   * every GPU that loads this library holds the array (BS_STATIC_SCRATCH_BYTES) until the process exits;
 //   * canvases that need more than BS_STATIC_MAX_BLOCKS blocks of 32x16 pixels are refused;
-//   * all calls share the array and it keeps the previous call's contents.  The plan is rebuilt in full
-//     and the work split rewritten by every call, so nothing stale is ever read, but two
+//   * all calls share the array and it keeps the previous call's contents.  A call with other calibration
+//     arguments rewrites every record and the whole work split (nothing stale is ever read; the remembered
+//     arguments are compared bit for bit, and only a call that completed is remembered), so two
 //     calls whose GPU work overlaps (different streams, or different host threads on different
-//     streams) race on it.  Issue calls on one stream, or order the streams yourself.
+//     streams) race on it unless their calibrations are equal.  Issue calls on one stream, or order the
+//     streams yourself.
 //   * the first call on each device looks up the array's device address (cudaGetSymbolAddress) and
 //     sets the kernel's shared-memory limit; make that first call before any stream capture begins.
 // ================================================================================================
@@ -1679,11 +1683,24 @@ static_assert(sizeof(bs::WorkItem) * bs::kMaxLayers <= sizeof(bs::BlockRec), "it
 // address comes from cudaGetSymbolAddress (static_device_state), never from &g_static_scratch.
 static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
 
+// What the plan in a device's scratch was built from.  A call with the same calibration arguments as the previous
+// call on that device (a video loop) finds its plan and work split already there and only launches the frame kernel.
+struct StaticKey {
+    int n_cams, W, H;
+    unsigned flags;
+    int sw[bs::kMaxCamsPerLaunch], sh[bs::kMaxCamsPerLaunch];
+    double Hm[bs::kMaxCamsPerLaunch * 9];
+};
 struct StaticDeviceState {
     bool ready = false;
     StaticScratch *scratch = nullptr;   // device address of g_static_scratch on this device
     int sms = 0;
     int smem_optin = 0;
+    // the plan the scratch holds (valid only after a staged call completed)
+    bool plan_valid = false;
+    StaticKey key;
+    PlanLayout L;
+    int grid = 0, rec_slots = 0, per_sm = 0;
 };
 constexpr int kStaticMaxDevices = 64;
 StaticDeviceState g_static_dev[kStaticMaxDevices];
@@ -1763,47 +1780,26 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     const int legacy = (flags & BS_FLAG_LEGACY_BORDER) ? 1 : 0;
     const int block_w = opencv_block_width(canvas_w, canvas_h);
 
-    // ---- plan into the static scratch (every record is rewritten: nothing stale survives) -----------
-    bs::PlanArgs &P = g_static_plan_args;
-    memset(&P, 0, sizeof P);
+    // ---- the plan: still in the scratch from the previous call, or rebuilt in full ---------------------
+    static StaticKey key;                       // (under g_static_mutex; static: no large object on the stack)
+    memset(&key, 0, sizeof key);
+    key.n_cams = n_cams;
+    key.W = canvas_w;
+    key.H = canvas_h;
+    key.flags = flags;
     for (int i = 0; i < n_cams; ++i) {
-        invert3x3(H + 9 * i, P.M[i]);
-        P.w[i] = src_w[i];
-        P.h[i] = src_h[i];
+        key.sw[i] = src_w[i];
+        key.sh[i] = src_h[i];
     }
-    P.n_cams = n_cams;
-    P.W = canvas_w;
-    P.H = canvas_h;
-    P.block_w = block_w;
-    P.legacy_border = legacy;
-    P.keep_canvas = keep ? 1 : 0;
-    P.blocks_x = blocks_x;
-    P.blocks_y = blocks_y;
-    P.out = st->scratch->plan;
-    bs::plan_kernel<<<dim3((blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, blocks_y), 32 * bs::kPlanWarps, 0, s>>>(P);
-    BS_CUDA(nullptr, cudaGetLastError());
-    const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)n_blocks;
-    BS_CUDA(nullptr, cudaMemcpyAsync(g_static_recs, st->scratch->plan, raw_bytes, cudaMemcpyDeviceToHost, s));
-    BS_CUDA(nullptr, cudaStreamSynchronize(s));
-
-    // ---- size one TMA box per camera, flatten to work items, split them over the grid's warps -------
-    PlanLayout L;
-    layout_plan(g_static_recs, n_blocks, n_cams, g_static_items, &L, false);
-    bool fast = L.n_fast > 0 && get_encoder() && cta_smem_bytes(L.stage_bytes, bs::kRecSlotsMax / 2) <= st->smem_optin &&
-                aligned16(d_canvas, canvas_pitch);
-    for (int i = 0; fast && i < n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
-    int per_sm = 0, rec_slots = bs::kRecSlotsMax;
-    if (fast) {
-        per_sm = choose_rec_slots(L.stage_bytes, &rec_slots, &L.smem_bytes);
-        fast = per_sm >= 1;
-    }
+    memcpy(key.Hm, H, sizeof(double) * 9 * (size_t)n_cams);
+    const bool hit = st->plan_valid && memcmp(&key, &st->key, sizeof key) == 0;
 
     bs::FastArgs FA;
     memset(&FA, 0, sizeof FA);
     bs::FrameArgs &A = FA.F;
     A.n_cams = n_cams;
     for (int i = 0; i < n_cams; ++i) {
-        memcpy(A.cam[i].M, P.M[i], 9 * sizeof(double));
+        invert3x3(H + 9 * i, A.cam[i].M);
         A.cam[i].ptr = static_cast<const uint8_t *>(d_frames[i]);
         A.cam[i].pitch = (long long)pitch[i];
         A.cam[i].w = src_w[i];
@@ -1817,6 +1813,42 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
     A.legacy_border = legacy;
     A.keep_canvas = keep ? 1 : 0;
     A.canvas_in_4g = canvas_in_4g(d_canvas, canvas_pitch, canvas_h);
+
+    PlanLayout &L = st->L;
+    if (!hit) {
+        // every record is rewritten: nothing stale survives
+        st->plan_valid = false;
+        bs::PlanArgs &P = g_static_plan_args;
+        memset(&P, 0, sizeof P);
+        for (int i = 0; i < n_cams; ++i) {
+            memcpy(P.M[i], A.cam[i].M, 9 * sizeof(double));
+            P.w[i] = src_w[i];
+            P.h[i] = src_h[i];
+        }
+        P.n_cams = n_cams;
+        P.W = canvas_w;
+        P.H = canvas_h;
+        P.block_w = block_w;
+        P.legacy_border = legacy;
+        P.keep_canvas = keep ? 1 : 0;
+        P.blocks_x = blocks_x;
+        P.blocks_y = blocks_y;
+        P.out = st->scratch->plan;
+        bs::plan_kernel<<<dim3((blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, blocks_y), 32 * bs::kPlanWarps, 0, s>>>(P);
+        BS_CUDA(nullptr, cudaGetLastError());
+        const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)n_blocks;
+        BS_CUDA(nullptr, cudaMemcpyAsync(g_static_recs, st->scratch->plan, raw_bytes, cudaMemcpyDeviceToHost, s));
+        BS_CUDA(nullptr, cudaStreamSynchronize(s));
+        // size one TMA box per camera, flatten to work items
+        L = PlanLayout();
+        layout_plan(g_static_recs, n_blocks, n_cams, g_static_items, &L, false);
+        st->per_sm = 0;
+        st->rec_slots = bs::kRecSlotsMax;
+        if (L.n_fast > 0 && get_encoder() && cta_smem_bytes(L.stage_bytes, bs::kRecSlotsMax / 2) <= st->smem_optin)
+            st->per_sm = choose_rec_slots(L.stage_bytes, &st->rec_slots, &L.smem_bytes);
+    }
+    bool fast = st->per_sm >= 1 && aligned16(d_canvas, canvas_pitch);
+    for (int i = 0; fast && i < n_cams; ++i) fast = aligned16(d_frames[i], pitch[i]);
 
     if (!fast) {
         // no staged blocks (or unaligned buffers): the per-pixel kernel needs no scratch at all
@@ -1835,23 +1867,31 @@ extern "C" int bs_stitch_device_static(int n_cams, const int *src_w, const int *
             if (er != 0) return fail(nullptr, BS_ERR_CUDA, "%s: cuTensorMapEncodeTiled failed (%d) for camera %d", me, er, i);
         }
     }
-    int grid = std::max(1, std::min((n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, per_sm * st->sms));
-    grid = std::min(grid, kStaticMaxWarps / bs::kWarpsPerCta);
-    const int n_warps = grid * bs::kWarpsPerCta;
-    group_items_by_warp(g_static_items, L.n_items - L.n_two, L.n_two, n_warps, g_static_grouped, g_static_warp_start);
-    // the item list replaces the raw records in the scratch; stream-ordered after the previous call's kernels
-    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_grouped, sizeof(bs::WorkItem) * (size_t)L.n_items,
-                                     cudaMemcpyHostToDevice, s));
-    BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->warp_start, g_static_warp_start, sizeof(int) * (size_t)(n_warps + 1),
-                                     cudaMemcpyHostToDevice, s));
+    if (!hit) {
+        // split the items over the grid's warps; the item list replaces the raw records in the scratch,
+        // stream-ordered after the previous call's kernels
+        int grid = std::max(1, std::min((n_blocks + bs::kWarpsPerCta - 1) / bs::kWarpsPerCta, st->per_sm * st->sms));
+        grid = std::min(grid, kStaticMaxWarps / bs::kWarpsPerCta);
+        st->grid = grid;
+        const int n_warps = grid * bs::kWarpsPerCta;
+        group_items_by_warp(g_static_items, L.n_items - L.n_two, L.n_two, n_warps, g_static_grouped, g_static_warp_start);
+        BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->plan, g_static_grouped, sizeof(bs::WorkItem) * (size_t)L.n_items,
+                                         cudaMemcpyHostToDevice, s));
+        BS_CUDA(nullptr, cudaMemcpyAsync(st->scratch->warp_start, g_static_warp_start, sizeof(int) * (size_t)(n_warps + 1),
+                                         cudaMemcpyHostToDevice, s));
+    }
     FA.items = reinterpret_cast<const bs::WorkItem *>(st->scratch->plan);
     FA.warp_start = st->scratch->warp_start;
     FA.stage_bytes = L.stage_bytes;
-    FA.rec_slots = rec_slots;
-    bs::stitch_fast_kernel<<<grid, bs::kFastThreads, L.smem_bytes, s>>>(FA);
+    FA.rec_slots = st->rec_slots;
+    bs::stitch_fast_kernel<<<st->grid, bs::kFastThreads, L.smem_bytes, s>>>(FA);
     BS_CUDA(nullptr, cudaGetLastError());
     // the host staging arrays are reused by the next call: everything queued above must have left them
     BS_CUDA(nullptr, cudaStreamSynchronize(s));
+    if (!hit) {
+        st->key = key;
+        st->plan_valid = true;
+    }
     return BS_OK;
 }
 

@@ -246,8 +246,9 @@ int bs_pool_sync(bs_pool *p);                       /* every submitted frame is 
  * memory and must not allocate while running -- frame loops with a fixed device-memory budget,
  * hosts that forbid cudaMalloc after start-up (it also synchronises the device), plug-ins living
  * inside someone else's allocator.  Same result as bs_create + bs_submit_device for the same
- * arguments (flags: BS_FLAG_LEGACY_BORDER, BS_FLAG_KEEP_CANVAS), but the tile plan is rebuilt on every
- * call, so it is slower per frame; n_cams <= 16.
+ * arguments (flags: BS_FLAG_LEGACY_BORDER, BS_FLAG_KEEP_CANVAS); n_cams <= 16.  The tile plan stays in the
+ * scratch between calls: a call whose n_cams, sizes, H and flags equal the previous call's on the same device (a
+ * video loop) only launches the frame kernel; any other call rebuilds the plan first (about 2 ms at 7680x2160).
  *
  * The staged kernel's scratch (the block plan and the per-warp work split) lives in one static device
  * array of BS_STATIC_SCRATCH_BYTES that every GPU loading the library keeps until exit.  Canvases
@@ -255,8 +256,8 @@ int bs_pool_sync(bs_pool *p);                       /* every submitted frame is 
  * 7680x2160 panorama needs 32400) are refused with BS_ERR_UNSUPPORTED.  All calls share that array:
  * calls whose GPU work overlaps (different streams) race on it, so keep them on one stream.  The
  * first call on each device performs the one-time address lookup and must come before any stream
- * capture.  The call returns after its kernels have finished (it synchronises `stream` once for the
- * plan and once at the end).
+ * capture.  The call returns after its kernels have finished (it synchronises `stream` at the end, and
+ * once more for the plan when it rebuilds it).
  */
 #define BS_STATIC_MAX_BLOCKS 32768
 #define BS_STATIC_SCRATCH_BYTES (BS_STATIC_MAX_BLOCKS * 160 + 32768)

@@ -119,7 +119,34 @@ def test_near_limit_canvas_is_exact_and_nothing_is_allocated():
     ms = 1e3 * (time.perf_counter() - t0) / 9
     assert torch.cuda.mem_get_info()[0] == free0, "bs_stitch_device_static changed the amount of free device memory"
     assert np.array_equal(d_out.cpu().numpy(), want)
-    print(f"bs_stitch_device_static at cfg3: {ms:.2f} ms per call (plan rebuilt every call)")
+    print(f"bs_stitch_device_static at cfg3: {ms:.2f} ms per call (same calibration: the plan stays in the scratch)")
+
+
+def test_plan_kept_between_calls_only_for_the_same_calibration():
+    """A call with the previous call's calibration reuses the plan in the static array; anything that changes the
+    plan (homography, flags, sizes) rebuilds it; calibrations A, B, A, A in turn, new frames and new buffers every
+    time, an unaligned canvas in between (per-pixel kernel, scratch untouched): every result exact."""
+    p = pkg()
+    rng = np.random.default_rng(5)
+    whs = [(320, 200), (320, 200)]
+    canvas = (600, 230)
+    HA = [np.array([[1.0, 0.01, 3.0], [-0.01, 1.0, 5.0], [1e-5, 0, 1.0]]), np.array([[1.02, 0.0, 270.0], [0.01, 0.98, 9.0], [0, 1e-5, 1.0]])]
+    HB = [HA[0].copy(), HA[1].copy()]
+    HB[1][0, 2] += 2.0 ** -20           # differs in one low bit of one entry: a different calibration
+    seq = [(HA, 0), (HB, 0), (HA, 0), (HA, 0), (HA, p.FLAG_LEGACY_BORDER), (HA, 0)]
+    for k, (Hs, flags) in enumerate(seq):
+        srcs = [rng.integers(0, 256, (h, wd, 3), dtype=np.uint8) for wd, h in whs]
+        d_src = [torch.from_numpy(s_).cuda() for s_ in srcs]
+        want = oracle.stitch(srcs, Hs, canvas, border_rule=oracle.BORDER_LEGACY if flags else oracle.BORDER_CV4)
+        got = static_path(p, whs, canvas, Hs, d_src, flags)
+        assert np.array_equal(got, want), f"call {k}"
+        if k == 2:                      # same calibration, canvas 1 byte off alignment: the per-pixel kernel, then staged again
+            buf = torch.zeros(canvas[1] * canvas[0] * 3 + 16, dtype=torch.uint8, device="cuda")
+            off = buf[1:1 + canvas[1] * canvas[0] * 3]
+            p.stitch_device_static(whs, [t.data_ptr() for t in d_src], [t.stride(0) for t in d_src], canvas, off.data_ptr(),
+                                   canvas[0] * 3, Hs, flags=flags, stream=0)
+            torch.cuda.synchronize()
+            assert np.array_equal(off.cpu().numpy().reshape(canvas[1], canvas[0], 3), want)
 
 
 def test_one_block_over_the_limit_and_unknown_flags_are_refused():

@@ -16,8 +16,9 @@ python bench.py --lens --steps 20 --cpu-seconds 8 > gpurun_out/${T}_bench_lens.j
 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file gpurun_out/${T}_launches.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${T}_ncu_list.log 2>&1
 tools/prof.sh $T
 for w in cfg3 cfg2 cfg5; do python tools/traffic.py run $w > /dev/null 2>&1; done
-CMD="python bench.py --lens --steps 2 --warmup 3 --frames-per-step 8 --no-e2e --no-cpu-baseline"
-ncu --set full --clock-control none --import-source on -k regex:stitch_fast2 -s 40 -c 1 -o gpurun_out/prof_${T}_lens -f $CMD > gpurun_out/ncu_${T}_lens.log 2>&1
+tools/prof_lens.sh $T
+python tools/feather_bench.py cfg3 > gpurun_out/${T}_feather_bench.json 2>/dev/null; python tools/feather_bench.py cfg2 >> gpurun_out/${T}_feather_bench.json 2>/dev/null
+python tools/copy_patterns.py > gpurun_out/${T}_copy_patterns.json 2>/dev/null
 tail -2 gpurun_out/${T}_pytest.log; tail -1 gpurun_out/${T}_smoke.log
 python - <<PY
 import json

@@ -38,6 +38,10 @@ struct Slot {
     int64_t ticket = -1;
     bool busy = false;
     bs_jpeg_out *jout = nullptr;          // the frame in this slot leaves as a JPEG (bs_submit_jpeg): filled by bs_wait
+    // bs_submit_jpeg: the frame's host decode stages are still running, its GPU side has not been issued yet
+    bool deferred = false;
+    int deferred_rc = 0;                  // ... and what issuing it later returned (reported by bs_wait of this ticket)
+    char deferred_err[256] = "";
 };
 
 // Lens model of one camera (cv::undistort, tools/stitch/main.cpp:148-149).
@@ -991,6 +995,7 @@ int issue_frame(bs_handle *h, Slot &s, const uint8_t *const *frames, const size_
 }
 
 int retrieve_jpeg(bs_handle *h, Slot &s, int slot_index);    // stitch_jpeg.inl
+int flush_deferred_jpeg(bs_handle *h, int64_t upto);
 void jpeg_ctx_destroy(JpegCtx *c);
 }  // namespace
 
@@ -1132,9 +1137,10 @@ int bs_submit(bs_handle *h, const uint8_t *const *frames, const size_t *pitch, u
     int rc = ensure_ring(h);
     if (rc != BS_OK) return rc;
 
+    flush_deferred_jpeg(h, h->next_ticket - 1);     // compressed frames submitted earlier go to the streams first
     const int64_t t = h->next_ticket;
     Slot &s = h->ring[t % kPipelineDepth];
-    if (s.busy) {   // the slot's previous frame must have left the device
+    if (s.busy || s.deferred_rc != BS_OK) {   // the slot's previous frame must have left the device (or report why it did not)
         rc = bs_wait(h, s.ticket);
         if (rc != BS_OK) return rc;
     }
@@ -1164,8 +1170,15 @@ int bs_wait(bs_handle *h, int64_t ticket)
         return fail(h, BS_ERR_BAD_TICKET, "bs_wait: ticket %lld was never issued", (long long)ticket);
     if (ticket < h->next_ticket - kPipelineDepth) return BS_OK;   // its slot was already recycled => done
     Slot &s = h->ring[ticket % kPipelineDepth];
-    if (s.ticket != ticket || !s.busy) return BS_OK;
+    if (s.ticket != ticket) return BS_OK;
     BS_CUDA(h, cudaSetDevice(h->device));
+    if (s.deferred) flush_deferred_jpeg(h, ticket);             // a compressed frame whose GPU side is still to be issued
+    if (s.deferred_rc != BS_OK) {                               // ... and could not be
+        const int rc = s.deferred_rc;
+        s.deferred_rc = BS_OK;
+        return fail(h, rc, "%s", s.deferred_err);
+    }
+    if (!s.busy) return BS_OK;
     BS_CUDA(h, cudaEventSynchronize(s.ev_done));
     s.busy = false;
     return retrieve_jpeg(h, s, (int)(ticket % kPipelineDepth));
@@ -1223,6 +1236,7 @@ int bs_sync(bs_handle *h)
 {
     if (!h) return fail(nullptr, BS_ERR_INVALID_ARG, "bs_sync: NULL handle");
     BS_CUDA(h, cudaSetDevice(h->device));
+    flush_deferred_jpeg(h, h->next_ticket - 1);
     BS_CUDA(h, cudaStreamSynchronize(h->s_h2d));
     BS_CUDA(h, cudaStreamSynchronize(h->s_compute));
     BS_CUDA(h, cudaStreamSynchronize(h->s_d2h));
@@ -1435,6 +1449,7 @@ int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dis
     BS_CUDA(h, cudaSetDevice(h->device));
     if (h->lens.empty()) h->lens.resize(h->n_cams);
     LensModel &m = h->lens[cam];
+    flush_deferred_jpeg(h, h->next_ticket - 1);          // frames submitted before this call use the old model
     BS_CUDA(h, cudaStreamSynchronize(h->s_compute));     // frames in flight may still be reading the old tables
     clear_lens(h, m);
     bool nonzero = false;

@@ -10,6 +10,7 @@
 #include <nvjpeg.h>
 
 #include <condition_variable>
+#include <deque>
 #include <functional>
 #include <mutex>
 #include <thread>
@@ -27,13 +28,24 @@ struct JpegLane {                              // one camera of one pipeline slo
     nvjpegJpegStream_t stream = nullptr;
 };
 
+// A frame whose host stages are running: everything bs_submit_jpeg was given, kept until the GPU part is issued.
+struct JpegPending {
+    std::vector<const uint8_t *> jpeg;
+    std::vector<size_t> bytes;
+    std::vector<int> status;                   // per camera: nvjpegStatus_t of the host stage
+    uint8_t *out = nullptr;
+    size_t out_pitch = 0;
+    bs_jpeg_out *jout = nullptr;
+    int remaining = 0;                         // host stages still running (guarded by JpegWorkers::m)
+};
+
 struct JpegWorkers {
     std::vector<std::thread> th;
     std::mutex m;
     std::condition_variable cv_job, cv_done;
-    std::function<void(int)> job;              // job(i) for i in [0, n_jobs)
-    int n_jobs = 0, next = 0, done = 0;
-    uint64_t generation = 0;
+    std::deque<std::pair<int, int>> tasks;     // (pipeline slot, camera)
+    std::function<int(int, int)> stage;        // the host stage of (slot, camera) -> status
+    JpegPending *pending = nullptr;            // kPipelineDepth entries
     bool stop = false;
 
     void start(int n, int device)
@@ -41,32 +53,33 @@ struct JpegWorkers {
         for (int k = 0; k < n; ++k)
             th.emplace_back([this, device] {
                 cudaSetDevice(device);
-                uint64_t seen = 0;
                 std::unique_lock<std::mutex> lk(m);
                 for (;;) {
-                    cv_job.wait(lk, [&] { return stop || (generation != seen && next < n_jobs); });
+                    cv_job.wait(lk, [&] { return stop || !tasks.empty(); });
                     if (stop) return;
-                    while (next < n_jobs) {
-                        const int i = next++;
-                        lk.unlock();
-                        job(i);
-                        lk.lock();
-                        if (++done == n_jobs) cv_done.notify_all();
-                    }
-                    seen = generation;
+                    const std::pair<int, int> t = tasks.front();
+                    tasks.pop_front();
+                    lk.unlock();
+                    const int st = stage(t.first, t.second);
+                    lk.lock();
+                    pending[t.first].status[t.second] = st;
+                    if (--pending[t.first].remaining == 0) cv_done.notify_all();
                 }
             });
     }
-    void run(int n, std::function<void(int)> f)    // returns when every job(i) has finished
+    void post(int slot, int n_cams)            // queue the host stages of one frame; returns at once
+    {
+        {
+            std::lock_guard<std::mutex> lk(m);
+            pending[slot].remaining = n_cams;
+            for (int i = 0; i < n_cams; ++i) tasks.emplace_back(slot, i);
+        }
+        cv_job.notify_all();
+    }
+    void wait_slot(int slot)                   // returns when every host stage of that frame has finished
     {
         std::unique_lock<std::mutex> lk(m);
-        job = std::move(f);
-        n_jobs = n;
-        next = done = 0;
-        ++generation;
-        cv_job.notify_all();
-        cv_done.wait(lk, [&] { return done == n_jobs; });
-        n_jobs = 0;
+        cv_done.wait(lk, [&] { return pending[slot].remaining == 0; });
     }
     ~JpegWorkers()
     {
@@ -95,6 +108,7 @@ struct JpegCtx {
     nvjpegDecodeParams_t hparams = nullptr;
     std::vector<JpegLane> lanes;               // kPipelineDepth x n_cams
     JpegWorkers *workers = nullptr;
+    JpegPending pending[kPipelineDepth];
     bool threaded_ok = false;
 };
 
@@ -137,7 +151,21 @@ void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
     if (ok) {
         c->workers = new (std::nothrow) JpegWorkers;
         ok = c->workers != nullptr;
-        if (ok) c->workers->start(std::min(h->n_cams, 8), h->device);
+        if (ok) {
+            const int n_cams = h->n_cams;
+            c->workers->pending = c->pending;
+            c->workers->stage = [c, n_cams](int slot, int i) {
+                JpegLane &l = c->lanes[(size_t)slot * n_cams + i];
+                const JpegPending &p = c->pending[slot];
+                nvjpegStatus_t st = nvjpegJpegStreamParse(c->lib, p.jpeg[i], p.bytes[i], 0, 0, l.stream);
+                if (st == NVJPEG_STATUS_SUCCESS) st = nvjpegDecodeJpegHost(c->lib, c->hdec, l.state, c->hparams, l.stream);
+                return (int)st;
+            };
+            // enough threads for the frames the pipeline holds, but not more than the machine has cores to spare
+            const int hw = (int)std::thread::hardware_concurrency();
+            const int want = std::min(kPipelineDepth * n_cams, 16);
+            c->workers->start(std::max(std::min(want, hw > 2 ? hw - 1 : 1), std::min(n_cams, 4)), h->device);
+        }
     }
     cudaGetLastError();
     if (!ok) jpeg_lanes_destroy(c);
@@ -216,16 +244,9 @@ void jpeg_ctx_destroy(JpegCtx *c)
     delete c;
 }
 
-// Queue one frame whose camera images arrive as JPEG bitstreams: decode into the slot's device frames on the
-// upload stream, kernels on the compute stream, then the panorama leaves raw (out), as a JPEG (jout), or both.
-int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const *jpeg, const size_t *jpeg_bytes, uint8_t *out,
-                     size_t out_pitch, bs_jpeg_out *jout)
+// bs_submit_jpeg's checks: every bitstream is a JPEG of its camera's frame size.
+int check_jpeg_frames(bs_handle *h, JpegCtx *c, const uint8_t *const *jpeg, const size_t *jpeg_bytes)
 {
-    JpegCtx *c = nullptr;
-    int rc = jpeg_ctx(h, &c);
-    if (rc != BS_OK) return rc;
-    h->h2d_bytes_last = 0;
-    std::vector<nvjpegImage_t> imgs(h->n_cams);
     for (int i = 0; i < h->n_cams; ++i) {
         int nc = 0, ws[NVJPEG_MAX_COMPONENT], hs[NVJPEG_MAX_COMPONENT];
         nvjpegChromaSubsampling_t ss;
@@ -234,24 +255,33 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
         if (ws[0] != h->sw[i] || hs[0] != h->sh[i])
             return fail(h, BS_ERR_INVALID_ARG, "bs_submit_jpeg: frame %d is %dx%d, the handle expects %dx%d", i, ws[0], hs[0], h->sw[i],
                         h->sh[i]);
+    }
+    return BS_OK;
+}
+
+// Queue the GPU side of one frame whose camera images arrive as JPEG bitstreams: decode into the slot's device
+// frames on the upload stream, kernels on the compute stream, then the panorama leaves raw (out), as a JPEG (jout),
+// or both.  `host_status` != nullptr: the host stages already ran on the worker threads (one status per camera).
+int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const *jpeg, const size_t *jpeg_bytes, uint8_t *out,
+                     size_t out_pitch, bs_jpeg_out *jout, const int *host_status)
+{
+    JpegCtx *c = h->jpeg;
+    int rc = BS_OK;
+    h->h2d_bytes_last = 0;
+    std::vector<nvjpegImage_t> imgs(h->n_cams);
+    for (int i = 0; i < h->n_cams; ++i) {
         memset(&imgs[i], 0, sizeof imgs[i]);
         imgs[i].channel[0] = s.d_frame[i];
         imgs[i].pitch[0] = h->d_frame_pitch[i];
         h->h2d_bytes_last += jpeg_bytes[i];
     }
     bool decoded = false;
-    if (c->threaded_ok) {
-        // host stages of all cameras at once on the worker threads, device stages in camera order on the upload
-        // stream; a bitstream this decoder cannot take (progressive ...) sends the frame to the decoders below
-        std::vector<int> status(h->n_cams, 0);
+    if (host_status) {
+        // device stages in camera order on the upload stream; a bitstream the decoupled decoder could not take
+        // (progressive ...) sends the frame to the decoders below
         JpegLane *lanes = &c->lanes[(size_t)slot_index * h->n_cams];
-        c->workers->run(h->n_cams, [&](int i) {
-            nvjpegStatus_t st = nvjpegJpegStreamParse(c->lib, jpeg[i], jpeg_bytes[i], 0, 0, lanes[i].stream);
-            if (st == NVJPEG_STATUS_SUCCESS) st = nvjpegDecodeJpegHost(c->lib, c->hdec, lanes[i].state, c->hparams, lanes[i].stream);
-            status[i] = (int)st;
-        });
         decoded = true;
-        for (int i = 0; i < h->n_cams; ++i) decoded = decoded && status[i] == (int)NVJPEG_STATUS_SUCCESS;
+        for (int i = 0; i < h->n_cams; ++i) decoded = decoded && host_status[i] == (int)NVJPEG_STATUS_SUCCESS;
         for (int i = 0; i < h->n_cams && decoded; ++i)
             decoded = nvjpegDecodeJpegTransferToDevice(c->lib, c->hdec, lanes[i].state, lanes[i].stream, h->s_h2d) == NVJPEG_STATUS_SUCCESS &&
                       nvjpegDecodeJpegDevice(c->lib, c->hdec, lanes[i].state, &imgs[i], h->s_h2d) == NVJPEG_STATUS_SUCCESS;
@@ -330,6 +360,35 @@ int retrieve_jpeg(bs_handle *h, Slot &s, int slot_index)
     return BS_OK;
 }
 
+// Issue the GPU side of every frame whose host stages were left running by bs_submit_jpeg, oldest first, up to
+// ticket `upto` (frames go to the streams in ticket order).  A frame that fails is dropped and its error kept in
+// its slot for the bs_wait of that ticket.
+int flush_deferred_jpeg(bs_handle *h, int64_t upto)
+{
+    if (!h->jpeg || h->ring.empty()) return BS_OK;
+    JpegCtx *c = h->jpeg;
+    for (int64_t t = std::max<int64_t>(0, h->next_ticket - kPipelineDepth); t <= upto && t < h->next_ticket; ++t) {
+        const int slot_index = (int)(t % kPipelineDepth);
+        Slot &s = h->ring[slot_index];
+        if (s.ticket != t || !s.deferred) continue;
+        c->workers->wait_slot(slot_index);
+        s.deferred = false;
+        JpegPending &p = c->pending[slot_index];
+        const int rc = issue_frame_jpeg(h, s, slot_index, p.jpeg.data(), p.bytes.data(), p.out, p.out_pitch, p.jout, p.status.data());
+        if (rc != BS_OK) {
+            cudaStreamSynchronize(h->s_h2d);
+            cudaStreamSynchronize(h->s_compute);
+            cudaStreamSynchronize(h->s_d2h);
+            cudaGetLastError();
+            s.busy = false;
+            s.jout = nullptr;
+            s.deferred_rc = rc;
+            snprintf(s.deferred_err, sizeof s.deferred_err, "%s", h->err);
+        }
+    }
+    return BS_OK;
+}
+
 }  // namespace
 
 extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const size_t *jpeg_bytes, uint8_t *out, size_t out_pitch,
@@ -345,23 +404,43 @@ extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const si
     BS_CUDA(h, cudaSetDevice(h->device));
     int rc = ensure_ring(h);
     if (rc != BS_OK) return rc;
+    JpegCtx *c = nullptr;
+    rc = jpeg_ctx(h, &c);
+    if (rc != BS_OK) return rc;
+    rc = check_jpeg_frames(h, c, jpeg, jpeg_bytes);
+    if (rc != BS_OK) return rc;
     const int64_t t = h->next_ticket;
     const int slot_index = (int)(t % kPipelineDepth);
     Slot &s = h->ring[slot_index];
-    if (s.busy) {
+    if (s.busy || s.deferred_rc != BS_OK) {
         rc = bs_wait(h, s.ticket);
         if (rc != BS_OK) return rc;
     }
-    rc = issue_frame_jpeg(h, s, slot_index, jpeg, jpeg_bytes, out, out_pitch, jout);
-    if (rc != BS_OK) {
-        cudaStreamSynchronize(h->s_h2d);
-        cudaStreamSynchronize(h->s_compute);
-        cudaStreamSynchronize(h->s_d2h);
-        cudaGetLastError();
-        s.busy = false;
-        s.ticket = -1;
-        s.jout = nullptr;
-        return rc;
+    if (c->threaded_ok) {
+        // The entropy stages start on the worker threads now; the GPU side is issued when they are done -- by the
+        // next call on this handle that needs the frame (bs_wait, a later submit, bs_sync), so that the host stages
+        // of up to bs_pipeline_depth frames overlap.  The bitstreams must stay valid until bs_wait, as `out` must.
+        JpegPending &p = c->pending[slot_index];
+        p.jpeg.assign(jpeg, jpeg + h->n_cams);
+        p.bytes.assign(jpeg_bytes, jpeg_bytes + h->n_cams);
+        p.status.assign(h->n_cams, 0);
+        p.out = out;
+        p.out_pitch = out_pitch;
+        p.jout = jout;
+        c->workers->post(slot_index, h->n_cams);
+        s.deferred = true;
+    } else {
+        rc = issue_frame_jpeg(h, s, slot_index, jpeg, jpeg_bytes, out, out_pitch, jout, nullptr);
+        if (rc != BS_OK) {
+            cudaStreamSynchronize(h->s_h2d);
+            cudaStreamSynchronize(h->s_compute);
+            cudaStreamSynchronize(h->s_d2h);
+            cudaGetLastError();
+            s.busy = false;
+            s.ticket = -1;
+            s.jout = nullptr;
+            return rc;
+        }
     }
     s.ticket = t;
     s.busy = true;

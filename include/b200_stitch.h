@@ -199,8 +199,13 @@ int bs_get_stats(const bs_handle *h, bs_stats *out);
  * is returned raw in `out` (may be NULL), and/or as a JPEG in `jout` (may be NULL): jout->data / capacity name
  * the caller's buffer, quality is 1..100 (0 = 95, cv::imwrite's default; 4:2:0 chroma as there), and jout->size
  * holds the bitstream length after bs_wait(ticket) -- only the bitstream is copied from the device.  All
- * buffers, and *jout itself, must stay valid until bs_wait.  Decoded pixels are nvJPEG's; they can differ by a
- * unit or two from libjpeg's, as between any two JPEG decoders.
+ * buffers (the bitstreams included), and *jout itself, must stay valid until bs_wait.  Decoded pixels are
+ * nvJPEG's; they can differ by a unit or two from libjpeg's, as between any two JPEG decoders.
+ * bs_submit_jpeg checks the headers (a JPEG of the camera's frame size) and returns; the entropy (Huffman) stages
+ * of the cameras then run on worker threads of the handle and the GPU side is issued when they are done, by the
+ * next call that needs the frame (bs_wait of the ticket, a later submit, bs_sync) -- so the host stages of up to
+ * bs_pipeline_depth() frames overlap.  A bitstream that turns out to be undecodable is therefore reported by
+ * bs_wait of its ticket (or by the next submit that needs its slot), not by bs_submit_jpeg.
  */
 typedef struct bs_jpeg_out {
     uint8_t *data;

@@ -82,8 +82,9 @@ def test_compressed_panorama_out_and_errors():
         with pytest.raises(p.StitchError) as e:
             st.submit_jpeg([b"not a jpeg at all", jpgs[1]], raw)
         assert e.value.code == -1 and "frame 0" in str(e.value)
-        with pytest.raises(p.StitchError) as e:
-            st.submit_jpeg([jpgs[0], jpgs[0][:200]], raw)                     # truncated bitstream
+        t5 = st.submit_jpeg([jpgs[0], jpgs[0][:200]], raw)                    # truncated bitstream: the header is fine, so it is
+        with pytest.raises(p.StitchError) as e:                               # the decode that fails -- reported by bs_wait
+            st.wait(t5)
         assert "frame 1" in str(e.value)
         t4 = st.submit_jpeg(jpgs, raw)
         st.wait(t4)
@@ -125,3 +126,37 @@ def test_decoders_agree():
     assert r.returncode == 0, r.stderr[-2000:]
     got = json.loads(r.stdout.strip().splitlines()[-1])
     assert "worker threads" not in got["backend"] and got["sha"] == want
+
+
+def test_compressed_and_raw_submits_interleave_in_ticket_order():
+    """bs_submit_jpeg leaves the host decode stages running and issues the GPU side later; a raw submit, bs_sync or
+    a lens-model change right behind it must still see the frames in ticket order."""
+    p = pkg()
+    jpgs, H, canvas_wh, cv2_dec = fixtures()
+    whs = [(d.shape[1], d.shape[0]) for d in cv2_dec]
+    decoded = [nvjpeg_pixels(p, j, wh) for j, wh in zip(jpgs, whs)]
+    want = oracle.stitch(decoded, H, canvas_wh)
+    other = [np.ascontiguousarray(d[::-1]) for d in decoded]            # different pixels for the raw frames
+    want_other = oracle.stitch(other, H, canvas_wh)
+    outs = [np.full((canvas_wh[1], canvas_wh[0], 3), 99, np.uint8) for _ in range(5)]
+    with p.Stitcher(whs, canvas_wh, H) as st:
+        t0 = st.submit_jpeg(jpgs, outs[0])
+        t1 = st.submit(other, outs[1])                                   # raw frame behind a compressed one, no wait in between
+        t2 = st.submit_jpeg(jpgs, outs[2])
+        t3 = st.submit_jpeg(jpgs, outs[3])                               # fourth frame of a three-slot pipeline
+        for t in (t3, t0, t2, t1):                                       # waits in any order
+            st.wait(t)
+        assert np.array_equal(outs[0], want) and np.array_equal(outs[2], want) and np.array_equal(outs[3], want)
+        assert np.array_equal(outs[1], want_other)
+        st.submit_jpeg(jpgs, outs[4])
+        st.sync()                                                        # bs_sync alone completes a compressed frame
+        assert np.array_equal(outs[4], want)
+        K = np.array([[0.9 * whs[0][0], 0, whs[0][0] / 2], [0, 0.9 * whs[0][0], whs[0][1] / 2], [0, 0, 1]])
+        dist = np.array([-0.15, 0.03, 0.001, -0.001, 0.0])
+        t5 = st.submit_jpeg(jpgs, outs[0])                               # submitted before the model: must not see it
+        st.set_undistort(0, K, dist)
+        st.wait(t5)
+        assert np.array_equal(outs[0], want)
+        st.wait(st.submit_jpeg(jpgs, outs[1]))                           # submitted after: sees it
+        und = [oracle.undistort(decoded[0], K, dist), decoded[1]]
+        assert np.array_equal(outs[1], oracle.stitch(und, H, canvas_wh))

@@ -265,7 +265,7 @@ struct PlanLayout {
 inline int compact_t0(int x0) { return x0 & ~3; }
 inline int compact_c0(int x0) { return bs::box_elem0(compact_t0(x0)); }
 
-void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *items, PlanLayout *L, bool allow_compact)
+void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *items, PlanLayout *L, bool allow_compact, bool feather = false)
 {
     int we[bs::kMaxCamsPerLaunch] = {0}, bh[bs::kMaxCamsPerLaunch] = {0};
     // compact: every staged layer's texels fit 40 converted columns, 128 staged bytes per row and 18 rows
@@ -284,6 +284,12 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
     for (int t = 0; t < n_blocks; ++t) {
         bs::BlockRec &r = recs[t];
         if (r.type != bs::kBlockFast) continue;
+        // BS_FLAG_FEATHER: two-layer blocks are blended by the compact kernel's run_feather2, which takes the cheap
+        // coordinates only; anything else (general kernel, flagged rows) is blended per pixel
+        if (feather && r.n_layers == 2 && (!compact || r.layer[0].groups != 0 || r.layer[1].groups != 0)) {
+            r.type = bs::kBlockExact;
+            continue;
+        }
         int twe[bs::kMaxLayers], tbh[bs::kMaxLayers];
         bool ok = true;
         for (int l = 0; l < r.n_layers; ++l) {
@@ -356,6 +362,7 @@ void layout_plan(bs::BlockRec *recs, int n_blocks, int n_cams, bs::WorkItem *ite
                 it.origin_off = (uint32_t)run_rel;
                 it.coef.aux = ((uint32_t)ustep & 0xFFFFu) | ((uint32_t)vstep << 16);
                 it.flags |= (uint8_t)(((3 * t0 - 4 * (int)it.c0) >> 2) << bs::kItemRawOffShift);
+                if (feather && nl == 2) it.flags |= bs::kItemFeather;
                 if (r.layer[l].full && r.layer[l].groups == 0 && nl == 1) {
                     it.flags |= bs::kItemDirect;
                     static const bool no_plain = getenv("BS_DEBUG_NO_PLAIN") != nullptr;   // experiment hook: one hot-loop variant only
@@ -487,7 +494,7 @@ int build_plan(bs_handle *h)
     // the compact kernel's fixed TMA box (32 elements x up to 18 rows) must fit inside every frame
     bool frames_fit = true;
     for (int i = 0; i < h->n_cams; ++i) frames_fit = frames_fit && h->sw[i] * 3 >= bs::kRawPitch && h->sh[i] >= bs::kRawRows;
-    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L, !no_compact && frames_fit);
+    layout_plan(recs.data(), h->n_blocks, h->n_cams, items.data(), &L, !no_compact && frames_fit, (h->flags & BS_FLAG_FEATHER) != 0);
     h->compact = L.compact;
     memcpy(h->box_we, L.box_we, sizeof h->box_we);
     memcpy(h->box_h, L.box_h, sizeof h->box_h);
@@ -539,11 +546,16 @@ int build_plan(bs_handle *h)
     // the device's opt-in maximum, so a handle with a small plan cannot lower it for another one.
     BS_CUDA(h, cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, h->device));
     if (h->compact) {
-        h->smem_bytes = bs::kWarps2 * bs::kWarp2Smem + 128;
+        h->smem_bytes = bs::kWarps2 * ((h->flags & BS_FLAG_FEATHER) ? bs::kWarp2SmemFeather : bs::kWarp2Smem) + 128;
         int per_sm = 0;
         if (h->smem_bytes > optin) return BS_OK;
-        BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
-        BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<false>, bs::kFast2Threads, h->smem_bytes));
+        if (h->flags & BS_FLAG_FEATHER) {
+            BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast2_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+            BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<false, true>, bs::kFast2Threads, h->smem_bytes));
+        } else {
+            BS_CUDA(h, cudaFuncSetAttribute(bs::stitch_fast2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, optin));
+            BS_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<false>, bs::kFast2Threads, h->smem_bytes));
+        }
         if (per_sm < 1) return BS_OK;
         h->grid = std::max(1, std::min((h->n_blocks + bs::kWarps2 - 1) / bs::kWarps2, per_sm * sms));
         if (const char *g = getenv("BS_DEBUG_GRID")) h->grid = std::max(1, atoi(g));
@@ -876,7 +888,8 @@ int launch_frame(bs_handle *h, const void *const *d_frames, const size_t *pitch,
             FA2.wait_sources = sources_from_kernel ? 1 : 0;
             FA2.box_bytes = bs::kRawPitch * h->box_h[0];
             cfg.blockDim = dim3(bs::kFast2Threads);
-            BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel<false>, FA2));
+            if (h->flags & BS_FLAG_FEATHER) BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel<false, true>, FA2));
+            else BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel<false>, FA2));
         } else {
             FA1.items = h->d_items;
             FA1.warp_start = h->d_warp_start;

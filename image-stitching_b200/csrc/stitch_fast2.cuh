@@ -50,6 +50,9 @@ constexpr int kRawStages = BS2_RAW_STAGES;               // boxes in flight ahea
 constexpr int kRec2Slots = BS2_REC_SLOTS;                // record ring slots per warp (two halves)
 constexpr int kWarp2Smem = kRawStages * kRawStage + kConvRegion + kWarpOutBytes + (kRec2Slots * kRecBytes + 32 + 127) / 128 * 128;
 static_assert(kWarp2Smem % 128 == 0, "per-warp regions stay 128-byte aligned");
+// BS_FLAG_FEATHER launches: one blend weight per pixel of the block, kept between a block's two layers
+constexpr int kWarp2SmemFeather = kWarp2Smem + kBlockW * kRun * 4;
+static_assert(kWarp2SmemFeather % 128 == 0, "weight block");
 // lens launches: a second ring beside the records with every item's third-order terms (32 bytes each)
 constexpr int kWarp2SmemLens = kWarp2Smem + kRec2Slots * (int)sizeof(CubicCoef);
 static_assert(sizeof(CubicCoef) == 32 && kWarp2SmemLens % 128 == 0, "cubic ring");
@@ -392,6 +395,57 @@ __device__ __noinline__ void run_masked2(const LaneCoef2 lc, const LaneBase2 lb,
     }
 }
 
+// BS_FLAG_FEATHER, a block two cameras write into (include/b200_stitch.h): the first layer leaves its pixels in the
+// output block and their weights d = 1 + distance to the nearest source edge (1/32 pixel) in `wgt`; the second layer
+// blends where both cover, (d0 P0 + d1 P1 + (d0 + d1) / 2) / (d0 + d1) per channel, writes its own pixel where only it
+// covers and leaves the rest.  Same fetch as run_masked2 (coverage = interior samples; border-rule pixels made the
+// plan send the block to the per-pixel path).
+__device__ __noinline__ void run_feather2(const LaneCoef2 lc, const LaneBase2 lb, uint32_t run0, int vstep, uint32_t out_blk, uint32_t wgt,
+                                          int lane, int src_w, int src_h, bool col_in_canvas, int rows_in_canvas, bool first_layer)
+{
+    const uint32_t safe = out_blk - 2 * kConvPitch;     // inside the converted buffer: valid for every tap offset
+    const int xmax = 32 * (src_w - 1), ymax = 32 * (src_h - 1);
+#pragma unroll 2
+    for (int k = 0; k < kRun; ++k) {
+        const int v = k - kRun / 2;
+        int xbits, ybits;
+        lane_coord_bits2(lc, (float)v, xbits, ybits);
+        const int X = xbits + lb.bx + 32 * lb.nxv * v, Y = ybits + lb.by + 32 * lb.nyv * v;
+        const int sx = X >> kFracBits, sy = Y >> kFracBits;
+        const bool in = col_in_canvas && k < rows_in_canvas && (uint32_t)sx < (uint32_t)(src_w - 1) && (uint32_t)sy < (uint32_t)(src_h - 1);
+        const uint32_t o = tap_addr(run0 + (uint32_t)(k * vstep), xbits, ybits);
+        const uint32_t px = blend_taps2(fetch_taps2(in ? o : safe, tap_weights2((uint32_t)xbits & 31u, (uint32_t)ybits & 31u)));
+        const uint32_t d = in ? (uint32_t)max(1, 1 + min(min(X, xmax - X), min(Y, ymax - Y))) : 0u;
+        const uint32_t p8 = out_blk + (uint32_t)(k * kBlockRowBytes) + 3u * (uint32_t)lane;
+        const uint32_t wa = wgt + 4u * (uint32_t)(k * kBlockW + lane);
+        if (first_layer) {
+            store_px_bytes(p8, in ? px : 0u);
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(wa), "r"(d) : "memory");
+        } else if (in) {
+            const uint32_t d0 = lds32(wa);
+            uint32_t res = px;
+            if (d0 != 0u) {
+                uint32_t b0, g0, r0;
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(b0) : "r"(p8));
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(g0) : "r"(p8 + 1));
+                asm volatile("ld.shared.u8 %0, [%1];" : "=r"(r0) : "r"(p8 + 2));
+                const uint32_t den = d0 + d, half = den >> 1;
+                const float rden = __frcp_rn((float)den);           // den < 2^21: exact as a float
+                auto quot = [&](uint32_t num) {                     // floor(num / den), num < 2^29: estimate, then one correction
+                    uint32_t q = (uint32_t)(__uint2float_rz(num) * rden);
+                    int rem = (int)(num - q * den);
+                    if (rem < 0) --q;
+                    else if (rem >= (int)den) ++q;
+                    return q;
+                };
+                res = quot(d0 * b0 + d * (px & 0xFFu) + half) | (quot(d0 * g0 + d * ((px >> 8) & 0xFFu) + half) << 8) |
+                      (quot(d0 * r0 + d * ((px >> 16) & 0xFFu) + half) << 16);
+            }
+            store_px_bytes(p8, res);
+        }
+    }
+}
+
 // General path: partially covered layers with flagged 32x4 groups (those use the exact fp64 coordinates).
 // `conv_origin` = address texel (0, 0) of the camera would have in the converted buffer.
 __device__ __noinline__ void run_general2(const FrameArgs &F, const CamDev &cam, const LaneCoef2 lc, const LaneBase2 lb,
@@ -453,7 +507,8 @@ __device__ __noinline__ void patch_lens2(const UndistortArgs &U, uint32_t conv_o
 }
 
 // kLens = false: the panorama frame kernel.  kLens = true: the same loop over a lens plan (stitch_undistort.cuh).
-template <bool kLens>
+// kFeather (with kLens = false): the BS_FLAG_FEATHER build of the frame kernel (two-layer blocks are blended).
+template <bool kLens, bool kFeather = false>
 __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kernel(const __grid_constant__ Fast2Args A)
 {
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -461,7 +516,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t raw_base = (smem_u32(smem_raw) + 127u) & ~127u;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const uint32_t raw0 = raw_base + (uint32_t)(warp * (kLens ? kWarp2SmemLens : kWarp2Smem));   // 128-byte aligned
+    const uint32_t raw0 = raw_base + (uint32_t)(warp * (kLens ? kWarp2SmemLens : (kFeather ? kWarp2SmemFeather : kWarp2Smem)));   // 128-byte aligned
     const uint32_t conv0 = raw0 + kRawStages * kRawStage;
     const uint32_t out_blk = conv0 + kConvRegion;
     const uint32_t rec0 = out_blk + kWarpOutBytes;
@@ -469,6 +524,7 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
     const uint32_t dbar0 = rec0 + rec_slots * kRecBytes;                       // data barriers, one per raw stage
     const uint32_t rbar0 = dbar0 + 16;                                         // record barriers, one per half of the ring
     const uint32_t cub0 = raw0 + kWarp2Smem;                                   // lens launches: ring of third-order terms
+    const uint32_t wgt0 = raw0 + kWarp2Smem;                                   // feather launches: the block's weights
 
     // Programmatic dependent launch, as in stitch_fast_kernel: the next frame's kernel may start at once;
     // it touches the canvas only after griddepcontrol.wait.
@@ -625,7 +681,11 @@ __global__ void __launch_bounds__(kFast2Threads, BS2_MIN_CTAS) stitch_fast2_kern
             const int ustep = (int)(int16_t)(bc.aux & 0xFFFFu), vstep = (int)(int16_t)(bc.aux >> 16);
             const uint32_t run0 = conv + r.w + (uint32_t)(u * ustep);
             const uint32_t groups = r.y >> 24;
-            if (flags & kItemFull) {
+            if (kFeather && (flags & kItemFeather)) {
+                const CamDev &cam = A.F.cam[(r.y >> 16) & 0xFFu];
+                const int tx0 = (int)bx * kBlockW, ty0 = (int)by * kBlockH;
+                run_feather2(lc, lane_base2(bc, u), run0, vstep, out_blk, wgt0, lane, cam.w, cam.h, tx0 + lane < A.F.W, A.F.H - ty0, !wrote);
+            } else if (flags & kItemFull) {
                 direct = can_direct && (flags & kItemDirect);
                 uint64_t grow;
                 uint32_t rpitch = cpitch;

@@ -77,6 +77,8 @@ constexpr uint8_t kItemFirst = 1, kItemLast = 2, kItemFull = 4;
 // canvas row (the hot loop's leanest variant); bits 4-5 = (byte offset of the first converted texel in the
 // staged row) / 4
 constexpr uint8_t kItemDirect = 8, kItemPlain = 0x40;
+// BS_FLAG_FEATHER: the item is one of the two layers of a block whose pixels are blended by weight (run_feather2)
+constexpr uint8_t kItemFeather = 0x80;
 constexpr int kItemRawOffShift = 4;
 
 // ---- cheap coordinates ---------------------------------------------------------------------------
@@ -208,7 +210,7 @@ struct PlanArgs {
     int block_w;                   // OpenCV's coordinate block width (not ours)
     int legacy_border;
     int keep_canvas;               // blocks with uncovered pixels then need the read-modify-write path
-    int feather;                   // BS_FLAG_FEATHER: blocks where two cameras write one pixel go to the per-pixel path
+    int feather;                   // BS_FLAG_FEATHER: a block's layers are all cameras writing any of its pixels (at most two, else per-pixel path)
     int blocks_x, blocks_y;
     BlockRec *out;                 // blocks_y * blocks_x records, row-major
 };
@@ -240,19 +242,31 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
         for (int k = 0; k < kRun; ++k) {
             const int y = y0 + k;
             if (y >= P.H) break;
+            if (P.feather) {
+                // BS_FLAG_FEATHER: every camera that writes a pixel contributes, so the block's layers are all
+                // cameras that write any of its pixels; border-rule pixels and more than kMaxLayers cameras on one
+                // pixel go to the per-pixel path
+                int n_cov = 0;
+                for (int i = 0; i < P.n_cams; ++i) {
+                    int X, Y;
+                    coord_exact(P.M[i], xb, x - xb, y, X, Y);
+                    const int c = cover_class(X, Y, P.w[i], P.h[i], P.legacy_border);
+                    if (!c) continue;
+                    ++n_cov;
+                    if (i < 32) win_lo |= 1u << i;
+                    else win_hi |= 1u << (i - 32);
+                    if (c == 2) edge = true;
+                }
+                if (n_cov == 0) unc = true;
+                if (n_cov > kMaxLayers) edge = true;
+                continue;
+            }
             int cls = 0, i = P.n_cams - 1;
             for (; i >= 0; --i) {
                 int X, Y;
                 coord_exact(P.M[i], xb, x - xb, y, X, Y);
                 cls = cover_class(X, Y, P.w[i], P.h[i], P.legacy_border);
                 if (cls) break;
-            }
-            if (P.feather && cls) {            // does a lower camera write this pixel too?
-                for (int j = i - 1; j >= 0 && !edge; --j) {
-                    int X, Y;
-                    coord_exact(P.M[j], xb, x - xb, y, X, Y);
-                    if (cover_class(X, Y, P.w[j], P.h[j], P.legacy_border)) edge = true;   // same fate as an edge block: exact
-                }
             }
             if (cls == 0) unc = true;
             else {

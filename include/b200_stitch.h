@@ -58,9 +58,11 @@ extern "C" {
  * Appendix A.1); each channel is (sum d_i P_i + (sum d_i) / 2) / sum d_i in integers.  Pixels one camera
  * writes are unchanged, so are uncovered pixels.  The reference has no blending at all
  * (tools/stitch/main.cpp:117,151 overwrite), so there is nothing to be bit-exact with: the CPU restatement
- * oracle_stitch_feather is "parity unpinned" and is excluded from the parity metric.  Blocks of the canvas where
- * cameras overlap take the per-pixel path (several times slower than the default); at most 16 cameras;
- * not with BS_FLAG_BORDER_CONSTANT; handles only (the one-shot calls and bs_stitch_device_static refuse it). */
+ * oracle_stitch_feather is "parity unpinned" and is excluded from the parity metric.  Blocks of the canvas that
+ * two cameras write into are blended by the staged kernel from the weights of their two layers (about four times
+ * the cost of a plain block); blocks with three or more cameras on a pixel, with last-row/column pixels or with
+ * rows that need exact coordinates take the per-pixel path; at most 16 cameras; not with
+ * BS_FLAG_BORDER_CONSTANT; handles only (the one-shot calls and bs_stitch_device_static refuse it). */
 #define BS_FLAG_FEATHER 0x10u
 
 #define BS_MAX_CAMERAS 64

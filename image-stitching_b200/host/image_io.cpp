@@ -180,6 +180,54 @@ bool write_jpeg(const std::string &path, const Image &im, std::string *err) {
 
 }  // namespace
 
+bool is_jpeg_path(const std::string &path) {
+  const std::string e = lower_ext(path);
+  return e == "jpg" || e == "jpeg";
+}
+
+bool read_bytes(const std::string &path, std::vector<uint8_t> &data) {
+  FILE *f = fopen(path.c_str(), "rb");
+  if (!f) return false;
+  fseek(f, 0, SEEK_END);
+  const long n = ftell(f);
+  fseek(f, 0, SEEK_SET);
+  data.resize(n > 0 ? (size_t)n : 0);
+  const bool ok = n > 0 && fread(data.data(), 1, data.size(), f) == data.size();
+  fclose(f);
+  return ok;
+}
+
+bool write_bytes(const std::string &path, const uint8_t *data, size_t n) {
+  FILE *f = fopen(path.c_str(), "wb");
+  if (!f) return false;
+  const bool ok = fwrite(data, 1, n, f) == n;
+  fclose(f);
+  return ok;
+}
+
+// Walk the marker segments up to the first frame header (baseline, extended or progressive DCT).
+bool jpeg_size(const uint8_t *d, size_t n, int *w, int *h) {
+  if (n < 4 || d[0] != 0xFF || d[1] != 0xD8) return false;
+  size_t i = 2;
+  while (i + 4 <= n) {
+    if (d[i] != 0xFF) return false;
+    const uint8_t m = d[i + 1];
+    if (m == 0xFF) { ++i; continue; }                            // fill byte
+    if (m == 0x01 || (m >= 0xD0 && m <= 0xD8)) { i += 2; continue; }   // markers without a length
+    const size_t len = ((size_t)d[i + 2] << 8) | d[i + 3];
+    if (len < 2 || i + 2 + len > n) return false;
+    if (m >= 0xC0 && m <= 0xC2) {
+      if (len < 7) return false;
+      *h = (d[i + 5] << 8) | d[i + 6];
+      *w = (d[i + 7] << 8) | d[i + 8];
+      return *w > 0 && *h > 0;
+    }
+    if (m == 0xDA) return false;                                 // scan data before any frame header
+    i += 2 + len;
+  }
+  return false;
+}
+
 bool have_jpeg() {
 #ifdef BS_WITH_NVJPEG
   return true;

@@ -61,5 +61,11 @@ class FrameStream {
 
 bool have_jpeg();
 
+// For the compressed path of the stitch tool (bs_submit_jpeg takes the bitstreams as they are):
+bool is_jpeg_path(const std::string &path);                               // .jpg / .jpeg, any case
+bool read_bytes(const std::string &path, std::vector<uint8_t> &data);     // the whole file
+bool jpeg_size(const uint8_t *data, size_t n, int *w, int *h);            // from the frame header (SOF0..SOF2), no decoder involved
+bool write_bytes(const std::string &path, const uint8_t *data, size_t n);
+
 }  // namespace bsio
 #endif

@@ -117,6 +117,67 @@ int main(int argc, char *argv[]) {
   // frames and panoramas in pinned memory: the engine's copies then go by DMA straight from / to them
   if (bs_device_count() > 0) bsio::set_pixel_allocator(bs_host_alloc, bs_host_free);
 
+  bool all_jpeg = bsio::have_jpeg() && !opts.video;
+  for (size_t i = 0; i < n && all_jpeg; ++i) all_jpeg = bsio::is_jpeg_path(opts.file_paths[i]);
+  if (all_jpeg) {
+    // JPEG photos (imread at main.cpp:107,114, imwrite at :125): the bitstreams go to the GPU as they are and are
+    // decoded there into the handle's frames; when the result is a JPEG too, it is encoded from the device canvas
+    // and only its bitstream comes back (bs_submit_jpeg).
+    std::vector<std::vector<uint8_t>> bits(n);
+    std::vector<int> sw(n), sh(n);
+    std::vector<double> Hall(9 * n);
+    for (size_t i = 0; i < n; ++i) {
+      if (!bsio::read_bytes(opts.file_paths[i], bits[i]) || !bsio::jpeg_size(bits[i].data(), bits[i].size(), &sw[i], &sh[i])) {
+        std::cout << "Failed to read " << opts.file_paths[i] << ": not a JPEG file" << std::endl;
+        return 5;
+      }
+      memcpy(&Hall[9 * i], H[i].data.data(), 9 * sizeof(double));
+    }
+    const std::string out = opts.output.empty() ? "final.jpg" : opts.output;
+    const bool jpeg_out = bsio::is_jpeg_path(out);
+    bs_handle *h = nullptr;
+    if (bs_create(opts.device, (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags, &h) != BS_OK)
+      return fail_bs("bs_create failed", nullptr);
+    bsio::Image result;
+    std::vector<uint8_t> jbuf;
+    bs_jpeg_out jo = {nullptr, 0, 0, 0};       // quality 0 = 95, cv::imwrite's default
+    if (jpeg_out) {
+      jbuf.resize((size_t)result_w * result_h * 3 / 2 + (1u << 16));
+      jo.data = jbuf.data();
+      jo.capacity = jbuf.size();
+    } else {
+      result.w = result_w;
+      result.h = result_h;
+      result.bgr.assign((size_t)result_w * result_h * 3, 0);
+    }
+    std::vector<const uint8_t *> ptrs(n);
+    std::vector<size_t> sizes(n);
+    for (size_t i = 0; i < n; ++i) {
+      ptrs[i] = bits[i].data();
+      sizes[i] = bits[i].size();
+    }
+    auto start = std::chrono::steady_clock::now();
+    int64_t ticket = -1;
+    int rc = bs_submit_jpeg(h, ptrs.data(), sizes.data(), jpeg_out ? nullptr : result.bgr.data(), jpeg_out ? 0 : result.pitch(),
+                            jpeg_out ? &jo : nullptr, &ticket);
+    if (rc == BS_OK) rc = bs_wait(h, ticket);
+    auto end = std::chrono::steady_clock::now();
+    if (rc != BS_OK) {
+      rc = fail_bs("warpPerspective failed", h);
+      bs_destroy(h);
+      return rc;
+    }
+    bs_destroy(h);
+    for (size_t i = 0; i < n; ++i) std::cout << std::chrono::duration<double, std::milli>(end - start).count() / (double)n << std::endl;
+    std::string err;
+    const bool ok = jpeg_out ? bsio::write_bytes(out, jo.data, jo.size) : bsio::write_image(out, result, &err);
+    if (!ok) {
+      std::cout << "Failed to write " << out << ": " << err << std::endl;
+      return 6;
+    }
+    return 0;
+  }
+
   if (!opts.video) {
     // One handle for all images: every photo is uploaded once, one launch warps and composites them in
     // the reference's order (later images overwrite earlier ones, main.cpp:113-117), the canvas comes

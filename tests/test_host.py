@@ -282,3 +282,48 @@ def test_stitch_tool_video_mode_over_a_pool_of_replicas(tmp_path):
     for k in range(n_frames):
         want = oracle.stitch([frames[0][k + 1], frames[1][k + 1]], Hs, (200, 70))
         assert np.array_equal(read_ppm(tmp_path / f"p_{k:03d}.ppm"), want), f"frame {k}"
+
+
+@pytest.mark.gpu
+def test_stitch_tool_image_mode_with_jpeg_photos(tmp_path):
+    """JPEG in (imread, tools/stitch/main.cpp:107,114) and JPEG out (imwrite, :125) through the tool: the bitstreams are
+    decoded on the GPU by bs_submit_jpeg, so the panorama equals the oracle applied to the pixels nvJPEG decodes; with
+    a .jpg output only the encoded panorama comes back."""
+    import shutil
+    from conftest import GOLDEN
+    p = pkg()
+    z = np.load(os.path.join(GOLDEN, "real_crop.npz"))
+    meta = json.loads(bytes(z["meta"]).decode())
+    H, canvas_wh = z["H"], tuple(meta["canvas_wh"])
+    paths = []
+    for i in range(2):
+        shutil.copy(os.path.join(GOLDEN, f"jpeg_src{i}.jpg"), tmp_path / f"{i}.jpg")
+        paths.append(tmp_path / f"{i}.jpg")
+    decoded = []
+    for pth in paths:                                   # the frames as nvJPEG decodes them (identity warp, raw output)
+        bits = open(pth, "rb").read()
+        dec = np.load(os.path.join(GOLDEN, "jpeg_cv2_decode.npz"))[f"src{len(decoded)}_cv2"]
+        wh = (dec.shape[1], dec.shape[0])
+        with p.Stitcher([wh], wh, [np.eye(3)]) as st:
+            out = np.empty((wh[1], wh[0], 3), np.uint8)
+            st.wait(st.submit_jpeg([bits], out))
+        decoded.append(out)
+    cfg = tmp_path / "stitch.conf.xml"
+    make_config(cfg, 0, paths, canvas_wh, list(H))
+    r = run_stitch(tmp_path, "--out=final.ppm")
+    assert r.returncode == 0, r.stdout + r.stderr
+    want = oracle.stitch(decoded, H, canvas_wh)
+    assert np.array_equal(read_ppm(tmp_path / "final.ppm"), want)
+    r = run_stitch(tmp_path)                            # default output: final.jpg, as the reference writes
+    assert r.returncode == 0, r.stdout + r.stderr
+    bits = open(tmp_path / "final.jpg", "rb").read()
+    assert bits[:2] == b"\xff\xd8" and bits[-2:] == b"\xff\xd9"
+    cv2 = pytest.importorskip("cv2")
+    back = cv2.imdecode(np.frombuffer(bits, np.uint8), cv2.IMREAD_COLOR)
+    assert back.shape == want.shape
+    mse = float(((back.astype(float) - want.astype(float)) ** 2).mean())
+    assert 10 * np.log10(255.0 ** 2 / max(mse, 1e-9)) > 30.0
+    (tmp_path / "bad.jpg").write_bytes(b"\xff\xd8 not really a jpeg")
+    make_config(cfg, 0, [paths[0], tmp_path / "bad.jpg"], canvas_wh, list(H))
+    r = run_stitch(tmp_path)
+    assert r.returncode == 5 and "bad.jpg" in r.stdout

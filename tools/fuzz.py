@@ -2,7 +2,7 @@
 """Randomised parity run, longer than the test-suite's: random camera counts, sizes, homographies (near-unit-scale
 panorama rigs that take the compact kernel, and strong ones that take the general kernel), both border rules,
 KEEP_CANVAS, lens models, BS_FLAG_FEATHER -- every panorama compared bit for bit with the oracle.
-usage (GPU box): python tools/fuzz.py [seconds] [seed]"""
+usage (GPU box): python tools/fuzz.py [seconds] [seed] [size scale, default 1]"""
 import importlib, os, sys, time
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -11,6 +11,7 @@ import oracle
 p = importlib.import_module("image-stitching_b200")
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
 rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 2026)
+SC = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0
 
 def rig(n, sw, sh):      # side-by-side cameras with overlap, mild rotation/perspective: the compact kernel's case
     step = rng.uniform(0.45, 0.95) * sw
@@ -41,12 +42,12 @@ while time.time() - t0 < budget:
     n = int(rng.integers(1, 6))
     compact = rng.random() < 0.6
     if compact:
-        sw, sh = int(rng.integers(160, 900)), int(rng.integers(64, 500))
+        sw, sh = int(rng.integers(160, 900 * SC)), int(rng.integers(64, 500 * SC))
         whs = [(sw, sh)] * n
         Hs, (dw, dh) = rig(n, sw, sh)
     else:
-        dw, dh = int(rng.integers(1, 1200)), int(rng.integers(1, 700))
-        whs = [(int(rng.integers(1, 700)), int(rng.integers(1, 500))) for _ in range(n)]
+        dw, dh = int(rng.integers(1, 1200 * SC)), int(rng.integers(1, 700 * SC))
+        whs = [(int(rng.integers(1, 700 * SC)), int(rng.integers(1, 500 * SC))) for _ in range(n)]
         Hs = strong(n, dw, dh)
     srcs = [rng.integers(0, 256, (h_, w_, 3), dtype=np.uint8) for w_, h_ in whs]
     mode = rng.choice(["plain", "legacy", "keep", "feather", "lens", "feather_legacy"])

@@ -426,7 +426,8 @@ def run_b200(args, rank, local_rank, world):
         undist.update({"us_per_camera_frame_in_submit": set_us, "achieved_gbs_in_submit": und_bytes / (set_us * 1e-6) / 1e9,
                        "frame_us_without_lens": plain_us,
                        "in_submit_how": "(pipelined frame time with lens models - without) / cameras; a submit runs all "
-                                        "cameras' lens plans as one launch"})
+                                        "cameras' lens plans as one launch and only the blocks of each undistorted frame "
+                                        "that the panorama plan can read (the part of the frame where that camera wins)"})
 
     # ---- what the host side can carry: the e2e copies alone, all ranks at once ----------------------
     def host_ceiling(h2d_bytes, d2h_bytes, reps=12):

@@ -82,7 +82,9 @@ struct LensModel {
 // camera's model changes; valid with two or more plans.
 struct LensSet {
     bool valid = false;
+    bool trimmed = false;                     // lens blocks the panorama plan never reads were left out
     std::vector<int> cams;
+    std::vector<int> src_x0, src_y0, src_x1, src_y1;   // per camera: the distorted-frame rectangle the launch reads (-1: all of it)
     bs::WorkItem *d_items = nullptr;
     bs::CubicCoef *d_cubic = nullptr;
     int *d_warp_start = nullptr;
@@ -770,6 +772,7 @@ int undistort_frames(bs_handle *h, const void *const *d_frames, const size_t *pi
         out_frames[i] = tmp[i];
         out_pitch[i] = h->d_frame_pitch[i];
         if (use_set && m.plan_ok && std::find(S.cams.begin(), S.cams.end(), i) != S.cams.end()) continue;   // done above
+        if (use_set && S.trimmed && h->up_x1[i] < 0) continue;                 // no panorama pixel reads this camera
         const int rc = undistort_one(h, i, d_frames[i], pitch[i], tmp[i], h->d_frame_pitch[i], stream, sources_from_kernel);
         if (rc != BS_OK) return rc;
         if (launched) *launched = true;
@@ -971,8 +974,19 @@ int issue_frame(bs_handle *h, Slot &s, const uint8_t *const *frames, const size_
     h->h2d_bytes_last = 0;
     for (int i = 0; i < h->n_cams; ++i) {
         int x0 = 0, y0 = 0, x1 = h->sw[i] - 1, y1 = h->sh[i] - 1;
-        const bool whole = !h->fast_ok || h->up_x0.empty() || (!h->lens.empty() && h->lens[i].enabled);
-        if (!whole) {
+        const bool has_lens = !h->lens.empty() && h->lens[i].enabled;
+        const LensSet &S = h->lens_set;
+        bool whole = !h->fast_ok || h->up_x0.empty() || has_lens;
+        if (has_lens && S.valid && S.trimmed) {
+            // the lens launch reads only the boxes of the blocks the panorama needs (build_lens_set)
+            if (h->up_x1[i] < 0) continue;           // no panorama pixel reads this camera
+            if (S.src_x1[i] >= 0) {
+                x0 = (S.src_x0[i] / 64) * 64;
+                y0 = S.src_y0[i];
+                x1 = std::min(x1, S.src_x1[i]);
+                y1 = std::min(y1, S.src_y1[i]);
+            }
+        } else if (!whole) {
             if (h->up_x1[i] < 0) continue;           // this camera contributes nothing to the canvas
             x0 = (h->up_x0[i] / 64) * 64;            // rows start on a 64-byte boundary of the frame (3 * 64 texel bytes)
             y0 = h->up_y0[i];
@@ -1390,28 +1404,64 @@ int build_lens_set(bs_handle *h)
     LensSet &S = h->lens_set;
     static const bool never = getenv("BS_DEBUG_NO_LENS_SET") != nullptr;     // test hook: one launch per camera
     if (never) return BS_OK;
-    int n_units = 0, n_two = 0, n_items = 0, n_blocks = 0;
+    // Only the part of an undistorted frame that the panorama plan can read has to exist: when that plan knows the
+    // source rectangle of every camera (no per-pixel blocks, which gather anywhere), the lens blocks outside it are
+    // left out of the launch -- at cfg3 a camera wins 47 % of its frame, so half of the lens work disappears.  (The
+    // frame kernel's TMA boxes reach a little beyond the rectangle; what they load from there is never used.)
+    static const bool no_trim = getenv("BS_DEBUG_NO_LENS_TRIM") != nullptr;        // test hook: whole frames
+    const bool trim = h->fast_ok && !h->up_x0.empty() && !no_trim;
+    auto needed = [&](int c, const bs::WorkItem &it) {
+        if (!trim) return true;
+        if (h->up_x1[c] < 0) return false;
+        const int x0 = it.bx * bs::kBlockW, y0 = it.by * bs::kBlockH;
+        return x0 <= h->up_x1[c] && x0 + bs::kBlockW - 1 >= h->up_x0[c] && y0 <= h->up_y1[c] && y0 + bs::kBlockH - 1 >= h->up_y0[c];
+    };
+    const int n_two = 0;        // a lens plan has one camera: no two-layer blocks
+    std::vector<bs::WorkItem> in;
+    S.src_x0.assign(h->n_cams, -1);
+    S.src_y0.assign(h->n_cams, -1);
+    S.src_x1.assign(h->n_cams, -1);
+    S.src_y1.assign(h->n_cams, -1);
     for (int c = 0; c < h->n_cams && c < bs::kMaxCamsPerLaunch; ++c)
         if (h->lens[c].enabled && h->lens[c].plan_ok) {
             const LensModel &m = h->lens[c];
+            if (m.n_two != 0) {
+                S = LensSet();
+                return BS_OK;
+            }
+            // the distorted-frame rectangle the kept blocks read (their whole TMA boxes): what bs_submit must upload
+            int sx0 = INT_MAX, sy0 = INT_MAX, sx1 = -1, sy1 = -1;
+            bool any = false, gathers = false;
+            for (const bs::WorkItem &it : m.items_host) {
+                if (!needed(c, it)) continue;
+                in.push_back(it);
+                any = true;
+                if (it.type == bs::kBlockFast) {
+                    sx0 = std::min(sx0, 4 * (int)it.c0 / 3);
+                    sx1 = std::max(sx1, (4 * (int)it.c0 + bs::kRawPitch - 1) / 3);
+                    sy0 = std::min(sy0, (int)it.y0);
+                    sy1 = std::max(sy1, (int)it.y0 + m.box_h - 1);
+                } else if (it.type == bs::kBlockExact) {
+                    gathers = true;          // evaluated tap by tap from anywhere in the frame
+                }
+            }
+            if (!any) continue;              // nothing of this camera's frame is ever read
             S.cams.push_back(c);
             S.box_h = std::max(S.box_h, m.box_h);
             S.smem_bytes = m.smem_bytes;
-            n_two += m.n_two;
-            n_units += m.n_items - m.n_two;
-            n_items += m.n_items;
-            n_blocks += (int)m.cubic_blocks.size();
+            if (trim && !gathers && sx1 >= 0) {
+                S.src_x0[c] = std::max(0, sx0);
+                S.src_y0[c] = std::max(0, sy0);
+                S.src_x1[c] = std::min(h->sw[c] - 1, sx1);
+                S.src_y1[c] = std::min(h->sh[c] - 1, sy1);
+            }
         }
-    if (S.cams.size() < 2) {
+    const int n_items = (int)in.size(), n_units = n_items, n_blocks = n_items;
+    if (S.cams.empty() || (S.cams.size() < 2 && !trim)) {
         S = LensSet();
         return BS_OK;
     }
-    // two-layer blocks first (a lens plan has none, kept general), then the single items, cameras interleaved
-    // block by block so that the warps of a CTA work on neighbouring blocks of one frame
-    std::vector<bs::WorkItem> in;
-    in.reserve(n_items);
-    for (int c : S.cams) in.insert(in.end(), h->lens[c].items_host.begin(), h->lens[c].items_host.begin() + 2 * h->lens[c].n_two);
-    for (int c : S.cams) in.insert(in.end(), h->lens[c].items_host.begin() + 2 * h->lens[c].n_two, h->lens[c].items_host.end());
+    S.trimmed = trim;
     int sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bs::stitch_fast2_kernel<true>, bs::kFast2Threads, S.smem_bytes) != cudaSuccess || per_sm < 1) {

@@ -248,3 +248,31 @@ def test_lens_set_mixed_cameras():
         st.submit_device([t.data_ptr() for t in d_in], [t.stride(0) for t in d_in], d_out.data_ptr(), d_out.stride(0), 0)
         torch.cuda.synchronize()
         assert np.array_equal(d_out.cpu().numpy(), want())
+
+
+def test_lens_launch_trimmed_to_what_the_panorama_reads():
+    """cfg3 (no per-pixel blocks in the panorama plan) with a lens model on every camera: the lens launch covers only
+    the blocks of each undistorted frame inside the rectangle where that camera wins, and bs_submit uploads only the
+    rectangle those blocks read -- the panorama must still equal the full-frame pipeline (undistort everything, then
+    warp) bit for bit, from host buffers and from device buffers."""
+    p = pkg()
+    w = workloads().get("cfg3")
+    sw, sh = w.src_wh
+    n = w.n_cams
+    frames = [oracle.gen_frame(sw, sh, i, 2, oracle.NOISE) for i in range(n)]
+    und = [oracle.undistort(frames[i], *lens(sw, sh, i)) for i in range(n)]
+    want = oracle.stitch(und, w.H, w.canvas_wh)
+    with p.Stitcher([w.src_wh] * n, w.canvas_wh, w.H) as st:
+        assert st.stats()["n_tiles_exact"] == 0
+        for i in range(n):
+            st.set_undistort(i, *lens(sw, sh, i))
+        got = st.stitch(frames)
+        assert np.array_equal(got, want), f"host path: {(got != want).any(axis=2).sum()} pixels differ"
+        up = st.stats()["h2d_bytes_last_submit"]
+        assert up < 0.9 * n * sw * sh * 3, f"uploaded {up} bytes: the source rectangles were not trimmed"
+        d_in = [dev(f) for f in frames]
+        d_out = torch.zeros((w.canvas_wh[1], w.canvas_wh[0], 3), dtype=torch.uint8, device="cuda")
+        for _ in range(2):          # twice: the second launch finds the undistorted buffers holding the first one's pixels
+            st.submit_device([t.data_ptr() for t in d_in], [t.stride(0) for t in d_in], d_out.data_ptr(), d_out.stride(0), 0)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_out.cpu().numpy(), want)

@@ -173,6 +173,10 @@ int bs_warp_perspective(const uint8_t *src, int sw, int sh, size_t spitch, uint8
  * SURVEY.md Appendix A.6).  K = fx 0 cx 0 fy cy 0 0 1 (row-major); dist = k1 k2 p1 p2 [k3 [k4 k5 k6]],
  * n_dist in 0..8 (calibrate writes 8, tools/calibrate/main.cpp:173-178).  A model whose
  * coefficients are all zero (or K == NULL) disables the step: cv::undistort is then an exact copy.
+ * The undistorted frame is internal to the handle: inside bs_submit* the lens models of all cameras run as one
+ * launch, and only the part of each undistorted frame that the panorama can read is computed (and, from host
+ * buffers, only the part of the distorted frame that this needs is uploaded) -- the panorama is the same bit for
+ * bit; bs_undistort_device below produces whole frames.
  */
 int bs_set_undistort(bs_handle *h, int cam, const double K[9], const double *dist, int n_dist);
 

@@ -474,9 +474,19 @@ int build_plan(bs_handle *h)
     const size_t raw_bytes = sizeof(bs::BlockRec) * (size_t)h->n_blocks;
     void *d_plan = nullptr;
     cudaError_t e = cudaMalloc(&d_plan, raw_bytes);
+    // per camera, the source rectangle the per-pixel blocks can read (kept beside the staged boxes' rectangles)
+    std::vector<int> exact_bbox(4 * (size_t)h->n_cams);
+    for (int i = 0; i < h->n_cams; ++i) {
+        exact_bbox[4 * i + 0] = exact_bbox[4 * i + 1] = INT_MAX;
+        exact_bbox[4 * i + 2] = exact_bbox[4 * i + 3] = -1;
+    }
+    int *d_bbox = nullptr;
+    if (e == cudaSuccess) e = cudaMalloc(&d_bbox, sizeof(int) * exact_bbox.size());
+    if (e == cudaSuccess) e = upload_now(h, d_bbox, exact_bbox.data(), sizeof(int) * exact_bbox.size());
     if (e == cudaSuccess) {
         h->d_items = static_cast<bs::WorkItem *>(d_plan);
         P->out = static_cast<bs::BlockRec *>(d_plan);
+        P->exact_bbox = d_bbox;
         bs::plan_kernel<<<dim3((h->blocks_x + bs::kPlanWarps - 1) / bs::kPlanWarps, h->blocks_y), 32 * bs::kPlanWarps, 0,
                           h->s_compute>>>(*P);
         e = cudaGetLastError();
@@ -484,7 +494,9 @@ int build_plan(bs_handle *h)
     delete P;
     std::vector<bs::BlockRec> recs(h->n_blocks);
     if (e == cudaSuccess) e = cudaMemcpyAsync(recs.data(), d_plan, raw_bytes, cudaMemcpyDeviceToHost, h->s_compute);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(exact_bbox.data(), d_bbox, sizeof(int) * exact_bbox.size(), cudaMemcpyDeviceToHost, h->s_compute);
     if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_compute);
+    cudaFree(d_bbox);
     if (e != cudaSuccess) return fail(h, BS_ERR_CUDA, "block plan failed: %s", cudaGetErrorString(e));
     h->kernel_launches++;
     h->device_bytes += raw_bytes;
@@ -500,23 +512,31 @@ int build_plan(bs_handle *h)
     h->compact = L.compact;
     memcpy(h->box_we, L.box_we, sizeof h->box_we);
     memcpy(h->box_h, L.box_h, sizeof h->box_h);
-    // Source region each camera can contribute: with no EXACT block (they gather anywhere) it is the
-    // union of the staged boxes' bounding boxes, and bs_submit uploads only that part of every frame.
+    // Source region each camera can contribute: the union of the staged boxes' bounding boxes (blocks the layout
+    // demoted to the per-pixel path keep theirs) and of what the plan kernel found for its per-pixel blocks;
+    // bs_submit uploads only that part of every frame, and the lens launch computes only that part (build_lens_set).
+    static const bool whole_frames = getenv("BS_DEBUG_WHOLE_FRAMES") != nullptr;     // test hook
     h->up_x0.clear();
-    if (L.n_exact == 0) {
+    if (!whole_frames) {
         h->up_x0.assign(h->n_cams, INT_MAX);
         h->up_y0.assign(h->n_cams, INT_MAX);
         h->up_x1.assign(h->n_cams, -1);
         h->up_y1.assign(h->n_cams, -1);
         for (const bs::BlockRec &r : recs) {
-            if (r.type != bs::kBlockFast) continue;
-            for (int l = 0; l < r.n_layers; ++l) {
+            if (r.type != bs::kBlockFast && r.type != bs::kBlockExact) continue;
+            for (int l = 0; l < r.n_layers; ++l) {      // (0 layers in the plan kernel's own per-pixel blocks)
                 const int c = r.layer[l].cam;
                 h->up_x0[c] = std::min(h->up_x0[c], (int)r.layer[l].x0);
                 h->up_y0[c] = std::min(h->up_y0[c], (int)r.layer[l].y0);
                 h->up_x1[c] = std::max(h->up_x1[c], (int)r.layer[l].x1);
                 h->up_y1[c] = std::max(h->up_y1[c], (int)r.layer[l].y1);
             }
+        }
+        for (int c = 0; c < h->n_cams; ++c) {
+            h->up_x0[c] = std::min(h->up_x0[c], exact_bbox[4 * c + 0]);
+            h->up_y0[c] = std::min(h->up_y0[c], exact_bbox[4 * c + 1]);
+            h->up_x1[c] = std::max(h->up_x1[c], exact_bbox[4 * c + 2]);
+            h->up_y1[c] = std::max(h->up_y1[c], exact_bbox[4 * c + 3]);
         }
     }
     h->stage_bytes = L.stage_bytes;

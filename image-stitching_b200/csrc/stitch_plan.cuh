@@ -213,6 +213,8 @@ struct PlanArgs {
     int feather;                   // BS_FLAG_FEATHER: a block's layers are all cameras writing any of its pixels (at most two, else per-pixel path)
     int blocks_x, blocks_y;
     BlockRec *out;                 // blocks_y * blocks_x records, row-major
+    int *exact_bbox;               // may be null; per camera x0, y0, x1, y1 (init INT_MAX, INT_MAX, -1, -1): the source
+                                   // texels the per-pixel blocks can read, so that uploads can still be trimmed to a rectangle
 };
 
 // 0 = not written, 1 = interior (Appendix A.3), 2 = written by the last-row/column rule (A.4)
@@ -296,6 +298,37 @@ __global__ void __launch_bounds__(32 * kPlanWarps) plan_kernel(const __grid_cons
     if (n_layers > kMaxLayers || edge || (P.keep_canvas && unc)) {
         rec.type = kBlockExact;
         if (lane == 0) *dst = rec;
+        if (P.exact_bbox) {
+            // What the per-pixel path can read here: the taps of every camera in the mask (the winners; with
+            // BS_FLAG_FEATHER all cameras that write) at the pixels that camera covers -- a superset, which is fine.
+            unsigned long long mm = ((unsigned long long)win_hi << 32) | win_lo;
+            while (mm) {
+                const int c = __ffsll((long long)mm) - 1;
+                mm &= mm - 1;
+                int bx0 = INT_MAX, by0 = INT_MAX, bx1 = -1, by1 = -1;
+                if (x < P.W)
+                    for (int k = 0; k < kRun && y0 + k < P.H; ++k) {
+                        int X, Y;
+                        coord_exact(P.M[c], xb, x - xb, y0 + k, X, Y);
+                        if (!cover_class(X, Y, P.w[c], P.h[c], P.legacy_border)) continue;
+                        const int sx = X >> kFracBits, sy = Y >> kFracBits;
+                        bx0 = min(bx0, sx);
+                        by0 = min(by0, sy);
+                        bx1 = max(bx1, min(sx + 1, P.w[c] - 1));
+                        by1 = max(by1, min(sy + 1, P.h[c] - 1));
+                    }
+                bx0 = __reduce_min_sync(FULLMASK, bx0);
+                by0 = __reduce_min_sync(FULLMASK, by0);
+                bx1 = __reduce_max_sync(FULLMASK, bx1);
+                by1 = __reduce_max_sync(FULLMASK, by1);
+                if (lane == 0 && bx1 >= 0) {
+                    atomicMin(P.exact_bbox + 4 * c + 0, bx0);
+                    atomicMin(P.exact_bbox + 4 * c + 1, by0);
+                    atomicMax(P.exact_bbox + 4 * c + 2, bx1);
+                    atomicMax(P.exact_bbox + 4 * c + 3, by1);
+                }
+            }
+        }
         return;
     }
     // ---- phase 2: per layer, source bounding box and validity of the cheap coordinates -----------

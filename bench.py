@@ -518,7 +518,11 @@ def run_b200(args, rank, local_rank, world):
                 a = wl.gen_frame_numpy(sw, sh, i, rank + world * f, "smooth").astype(np.int16)
                 a += (wl.gen_frame_numpy(sw, sh, i, f, "noise") >> 5).astype(np.int16) - 4
                 return np.clip(a, 0, 255).astype(np.uint8)
-            jf = [[np.frombuffer(cv2.imencode(".jpg", textured(i, f), [cv2.IMWRITE_JPEG_QUALITY, 90])[1].tobytes(), dtype=np.uint8).copy()
+            enc_args = [cv2.IMWRITE_JPEG_QUALITY, 90]
+            rst = int(os.environ.get("BS_BENCH_JPEG_RST", "0"))      # experiment: restart interval in MCUs (0 = none, cv2's default)
+            if rst:
+                enc_args += [cv2.IMWRITE_JPEG_RST_INTERVAL, rst]
+            jf = [[np.frombuffer(cv2.imencode(".jpg", textured(i, f), enc_args)[1].tobytes(), dtype=np.uint8).copy()
                    for i in range(n)] for f in range(3)]
             jbytes = int(sum(b.size for b in jf[0]))
             depth = pkg.lib().bs_pipeline_depth(st._h)

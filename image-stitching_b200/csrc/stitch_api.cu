@@ -695,7 +695,8 @@ int launch_lens(bs_handle *h, const int *cams, int n, const bs::WorkItem *d_item
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     BS_CUDA(h, cudaLaunchKernelEx(&cfg, bs::stitch_fast2_kernel<true>, FA));
-    if (getenv("BS_DEBUG_SYNC")) {
+    static const bool dbg_sync_lens = getenv("BS_DEBUG_SYNC") != nullptr;
+    if (dbg_sync_lens) {
         cudaError_t e1 = cudaDeviceSynchronize();
         if (e1 != cudaSuccess)
             return fail(h, BS_ERR_CUDA, "[debug] lens kernel over %d camera(s) (first %d, grid %d, smem %d, box rows %d) faulted: %s", n, cams[0],

@@ -1,6 +1,11 @@
 // image_io.cpp -- see image_io.hpp.
 #include "image_io.hpp"
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <algorithm>
 #include <cctype>
 #include <cstdlib>
@@ -224,6 +229,63 @@ bool jpeg_size(const uint8_t *d, size_t n, int *w, int *h) {
     }
     if (m == 0xDA) return false;                                 // scan data before any frame header
     i += 2 + len;
+  }
+  return false;
+}
+
+bool is_mjpeg_path(const std::string &path) {
+  const std::string e = lower_ext(path);
+  return e == "mjpeg" || e == "mjpg";
+}
+
+JpegStream::~JpegStream() {
+  if (base_) munmap(const_cast<uint8_t *>(base_), size_);
+}
+
+bool JpegStream::open(const std::string &path) {
+  const int fd = ::open(path.c_str(), O_RDONLY);
+  if (fd < 0) return false;
+  struct stat st;
+  if (fstat(fd, &st) != 0 || st.st_size <= 0) {
+    ::close(fd);
+    return false;
+  }
+  void *p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+  ::close(fd);
+  if (p == MAP_FAILED) return false;
+  base_ = static_cast<const uint8_t *>(p);
+  size_ = (size_t)st.st_size;
+  pos_ = 0;
+  return true;
+}
+
+// One frame = SOI ... EOI.  Marker segments are skipped by their length; inside entropy-coded data a 0xFF is
+// followed by 0x00 (stuffing) or RSTn, anything else is the next marker.
+bool JpegStream::next(const uint8_t **frame, size_t *bytes) {
+  const uint8_t *d = base_;
+  size_t i = pos_;
+  while (i + 1 < size_ && !(d[i] == 0xFF && d[i + 1] == 0xD8)) ++i;      // padding between frames
+  if (i + 4 > size_) return false;
+  const size_t start = i;
+  i += 2;
+  while (i + 1 < size_) {
+    if (d[i] != 0xFF) return false;
+    const uint8_t m = d[i + 1];
+    if (m == 0xFF) { ++i; continue; }
+    if (m == 0xD9) {
+      *frame = d + start;
+      *bytes = i + 2 - start;
+      pos_ = i + 2;
+      return true;
+    }
+    if (m == 0x01 || (m >= 0xD0 && m <= 0xD7)) { i += 2; continue; }
+    if (i + 3 >= size_) return false;
+    const size_t len = ((size_t)d[i + 2] << 8) | d[i + 3];
+    if (len < 2 || i + 2 + len > size_) return false;
+    i += 2 + len;
+    if (m == 0xDA) {                                            // entropy-coded data follows the scan header
+      while (i + 1 < size_ && !(d[i] == 0xFF && d[i + 1] != 0x00 && !(d[i + 1] >= 0xD0 && d[i + 1] <= 0xD7))) ++i;
+    }
   }
   return false;
 }

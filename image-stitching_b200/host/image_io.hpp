@@ -67,5 +67,19 @@ bool read_bytes(const std::string &path, std::vector<uint8_t> &data);     // the
 bool jpeg_size(const uint8_t *data, size_t n, int *w, int *h);            // from the frame header (SOF0..SOF2), no decoder involved
 bool write_bytes(const std::string &path, const uint8_t *data, size_t n);
 
+// A compressed "video": concatenated JPEG frames (Motion-JPEG elementary stream, `ffmpeg -i in.mp4 -c:v mjpeg -f mjpeg
+// out.mjpeg`), mapped read-only; next() hands out the frames' bitstreams in place, for bs_submit_jpeg.
+bool is_mjpeg_path(const std::string &path);                              // .mjpeg / .mjpg, any case
+class JpegStream {
+ public:
+  ~JpegStream();
+  bool open(const std::string &path);
+  bool isOpened() const { return base_ != nullptr; }
+  bool next(const uint8_t **frame, size_t *bytes);   // false at end of stream (or at bytes that are not a JPEG frame)
+ private:
+  const uint8_t *base_ = nullptr;
+  size_t size_ = 0, pos_ = 0;
+};
+
 }  // namespace bsio
 #endif

@@ -231,6 +231,106 @@ int main(int argc, char *argv[]) {
     return 0;
   }
 
+  // ---- video mode, compressed streams -------------------------------------------------------------
+  bool all_mjpeg = bsio::have_jpeg();
+  for (size_t i = 0; i < n && all_mjpeg; ++i) all_mjpeg = bsio::is_mjpeg_path(opts.file_paths[i]);
+  if (all_mjpeg) {
+    // Motion-JPEG streams (what cv::VideoCapture >> frame decodes on the host at main.cpp:147): every frame's
+    // bitstream goes to the GPU as it is (bs_submit_jpeg), up to bs_pipeline_depth frames in flight; with a .jpg
+    // --out pattern the panoramas are encoded on the GPU as well.  One GPU (--device); the streams are mapped.
+    std::vector<bsio::JpegStream> streams(n);
+    std::vector<int> sw(n), sh(n);
+    std::vector<double> Hall(9 * n);
+    for (size_t i = 0; i < n; ++i) {
+      const uint8_t *f0 = nullptr;
+      size_t b0 = 0;
+      // the reference reads and drops the first frame of every stream (main.cpp:136-141)
+      if (!streams[i].open(opts.file_paths[i]) || !streams[i].next(&f0, &b0) || !bsio::jpeg_size(f0, b0, &sw[i], &sh[i])) {
+        std::cout << "Failed to open file " << opts.file_paths[i] << "!" << std::endl;
+        return 5;
+      }
+      memcpy(&Hall[9 * i], H[i].data.data(), 9 * sizeof(double));
+    }
+    bs_handle *h = nullptr;
+    if (bs_create(opts.device, (int)n, sw.data(), sh.data(), result_w, result_h, Hall.data(), flags, &h) != BS_OK)
+      return fail_bs("bs_create failed", nullptr);
+    for (size_t i = 0; i < n; ++i) {
+      const bsfs::Matrix &K = cameraMatrix[i], &d = distCoeffs[i];
+      if (K.empty()) continue;
+      if (K.rows != 3 || K.cols != 3 || bs_set_undistort(h, (int)i, K.data.data(), d.empty() ? nullptr : d.data.data(), (int)d.data.size()) != BS_OK) {
+        std::cout << "bs_set_undistort failed: " << bs_last_error(h) << std::endl;
+        bs_destroy(h);
+        return 6;
+      }
+    }
+    const int depth = bs_pipeline_depth(h);
+    const bool want_out = !opts.output.empty(), jpeg_out = want_out && bsio::is_jpeg_path(opts.output);
+    std::vector<bsio::Image> results(depth);
+    std::vector<std::vector<uint8_t>> jbufs(depth);
+    std::vector<bs_jpeg_out> jouts(depth);
+    std::vector<int64_t> tickets(depth, -1);
+    for (int k = 0; k < depth; ++k) {
+      if (jpeg_out) {
+        jbufs[k].resize((size_t)result_w * result_h * 3 / 2 + (1u << 16));
+        jouts[k] = bs_jpeg_out{jbufs[k].data(), jbufs[k].size(), 0, 0};
+      } else {
+        results[k].w = result_w;
+        results[k].h = result_h;
+        results[k].bgr.assign((size_t)result_w * result_h * 3, 0);
+      }
+    }
+    auto emit = [&](int slot, long index) -> bool {
+      if (bs_wait(h, tickets[slot]) != BS_OK) return false;
+      tickets[slot] = -1;
+      if (!jpeg_out) displayResult("Final", results[slot]);
+      if (want_out) {
+        char name[4096];
+        snprintf(name, sizeof name, opts.output.c_str(), index);   // e.g. --out=pano_%05ld.jpg
+        std::string err;
+        const bool ok = jpeg_out ? bsio::write_bytes(name, jouts[slot].data, jouts[slot].size) : bsio::write_image(name, results[slot], &err);
+        if (!ok) std::cout << "Failed to write " << name << ": " << err << std::endl;
+      }
+      return true;
+    };
+    long produced = 0, emitted = 0;
+    auto t0 = std::chrono::steady_clock::now();
+    bool ok = true;
+    while (ok && (opts.max_frames < 0 || produced < opts.max_frames)) {
+      const int slot = (int)(produced % depth);
+      if (tickets[slot] >= 0) {
+        if (!emit(slot, emitted)) { ok = false; break; }
+        ++emitted;
+      }
+      std::vector<const uint8_t *> ptrs(n);
+      std::vector<size_t> sizes(n);
+      bool eof = false;
+      for (size_t i = 0; i < n && !eof; ++i) eof = !streams[i].next(&ptrs[i], &sizes[i]);
+      if (eof) break;
+      if (bs_submit_jpeg(h, ptrs.data(), sizes.data(), jpeg_out ? nullptr : results[slot].bgr.data(), jpeg_out ? 0 : results[slot].pitch(),
+                         jpeg_out ? &jouts[slot] : nullptr, &tickets[slot]) != BS_OK) {
+        ok = false;
+        break;
+      }
+      ++produced;
+    }
+    while (ok && emitted < produced) {
+      const int slot = (int)(emitted % depth);
+      if (!emit(slot, emitted)) { ok = false; break; }
+      ++emitted;
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    int rc = 0;
+    if (!ok) {
+      std::cout << "stitching failed: " << bs_last_error(h) << std::endl;
+      rc = 6;
+    } else if (opts.verbosity > 0) {
+      std::cout << produced << " frames on 1 GPU(s), " << std::chrono::duration<double, std::milli>(t1 - t0).count() / (produced ? produced : 1)
+                << " ms/frame" << std::endl;
+    }
+    bs_destroy(h);
+    return rc;
+  }
+
   // ---- video mode ------------------------------------------------------------------------------
   std::vector<bsio::FrameStream> videos(n);
   for (size_t i = 0; i < n; ++i) {

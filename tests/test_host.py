@@ -327,3 +327,47 @@ def test_stitch_tool_image_mode_with_jpeg_photos(tmp_path):
     make_config(cfg, 0, [paths[0], tmp_path / "bad.jpg"], canvas_wh, list(H))
     r = run_stitch(tmp_path)
     assert r.returncode == 5 and "bad.jpg" in r.stdout
+
+
+@pytest.mark.gpu
+def test_stitch_tool_video_mode_from_motion_jpeg(tmp_path):
+    """Compressed video in (cv::VideoCapture at tools/stitch/main.cpp:127-147): Motion-JPEG streams, every frame handed to
+    bs_submit_jpeg as a bitstream; lens models set; panoramas out raw and, in a second run, as JPEG files."""
+    cv2 = pytest.importorskip("cv2")
+    p = pkg()
+    rng = np.random.default_rng(9)
+    sw, sh, n_frames = 320, 192, 4
+    Hs = [np.array([[1.01, 0.0, 3.0], [0.0, 1.01, 2.0], [0, 0, 1.0]]), np.array([[1.0, 0.01, 280.0], [0.0, 1.0, 4.0], [0, 1e-5, 1.0]])]
+    Ks = [np.array([[300.0, 0, 160.0], [0, 300.0, 96.0], [0, 0, 1.0]])] * 2
+    dists = [np.array([[-0.12, 0.02, 0.001, -0.001, 0.0, 0.0, 0.0, 0.0]]).T, np.zeros((8, 1))]
+    bits = [[], []]
+    for c in range(2):
+        base = cv2.GaussianBlur(rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8), (0, 0), 3)
+        with open(tmp_path / f"cam{c}.mjpeg", "wb") as f:
+            for k in range(n_frames + 1):                    # + the first frame, which the reference drops
+                img = np.roll(base, 7 * k, axis=1)
+                enc = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 92] + ([cv2.IMWRITE_JPEG_RST_INTERVAL, 5] if k % 2 else []))[1].tobytes()
+                bits[c].append(enc)
+                f.write(enc + (b"\x00\x00\x00" if k % 2 else b""))      # some streams pad between frames
+    def decoded(b):
+        with p.Stitcher([(sw, sh)], (sw, sh), [np.eye(3)]) as st:
+            out = np.empty((sh, sw, 3), np.uint8)
+            st.wait(st.submit_jpeg([b], out))
+        return out
+    cfg = tmp_path / "v.xml"
+    make_config(cfg, 1, [tmp_path / "cam0.mjpeg", tmp_path / "cam1.mjpeg"], (620, 200), Hs, Ks, dists)
+    r = run_stitch(tmp_path, f"--s-conf={cfg}", "--out=pano_%03ld.ppm")
+    assert r.returncode == 0, r.stdout + r.stderr
+    wants = []
+    for k in range(n_frames):
+        f0 = oracle.undistort(decoded(bits[0][k + 1]), Ks[0], dists[0].reshape(-1))
+        wants.append(oracle.stitch([f0, decoded(bits[1][k + 1])], Hs, (620, 200)))
+        assert np.array_equal(read_ppm(tmp_path / f"pano_{k:03d}.ppm"), wants[k]), f"frame {k}"
+    assert not os.path.exists(tmp_path / f"pano_{n_frames:03d}.ppm")
+    r = run_stitch(tmp_path, f"--s-conf={cfg}", "--out=enc_%03ld.jpg", "--frames=3")
+    assert r.returncode == 0, r.stdout + r.stderr
+    for k in range(3):
+        back = cv2.imdecode(np.frombuffer(open(tmp_path / f"enc_{k:03d}.jpg", "rb").read(), np.uint8), cv2.IMREAD_COLOR)
+        mse = float(((back.astype(float) - wants[k].astype(float)) ** 2).mean())
+        assert back.shape == wants[k].shape and 10 * np.log10(255.0 ** 2 / max(mse, 1e-9)) > 30.0
+    assert not os.path.exists(tmp_path / "enc_003.jpg")

@@ -151,6 +151,8 @@ int fail(bs_handle *h, int code, const char *fmt, ...)
                         __FILE__, __LINE__);                                                  \
     } while (0)
 
+#define BS_CUDA_QUIET(call) do { if ((call) != cudaSuccess) cudaGetLastError(); } while (0)
+
 // Host -> device copy that is complete when it returns.  (A plain cudaMemcpy from pageable memory
 // may return while the DMA out of the driver's staging buffer is still running, and the handle's
 // streams are non-blocking, so a kernel on them would not wait for it.)
@@ -1043,7 +1045,7 @@ int issue_frame(bs_handle *h, Slot &s, const uint8_t *const *frames, const size_
 }
 
 int retrieve_jpeg(bs_handle *h, Slot &s, int slot_index);    // stitch_jpeg.inl
-int flush_deferred_jpeg(bs_handle *h, int64_t upto);
+int flush_deferred_jpeg(bs_handle *h, int64_t upto, bool only_ready = false);
 void jpeg_ctx_destroy(JpegCtx *c);
 }  // namespace
 

@@ -9,6 +9,8 @@
 // which is why the parity tests feed raw pixels and the JPEG tests compare against nvJPEG's own decode.
 #include <nvjpeg.h>
 
+#include "stitch_jpegdec.cuh"
+
 #include <condition_variable>
 #include <deque>
 #include <functional>
@@ -21,11 +23,113 @@ namespace {
 // ~20 ms for a 4K frame.  The cameras of one frame are independent, so bs_submit_jpeg runs their host stages on
 // a few worker threads of its own (nvJPEG's decoupled API: parse + nvjpegDecodeJpegHost per camera in parallel,
 // then transfer + device stage on the upload stream in camera order).
+// ---- entropy decoding on the GPU for JPEGs with a restart interval (stitch_jpegdec.cuh) ---------------------------
+// One thread per restart interval: Huffman-decodes its MCUs into the components' coefficient blocks.
+constexpr int kEntropyWarps = 4;      // restart intervals per block: one per warp (see below)
+__global__ void __launch_bounds__(32 * kEntropyWarps) jpeg_entropy_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ scan,
+                                                         const uint32_t *__restrict__ offs, int n_intervals, int16_t *c0, int16_t *c1,
+                                                         int16_t *c2)
+{
+    // the tables every symbol goes through live in shared memory: a thread is one long dependent chain of look-ups
+    __shared__ jd::HuffTable tabs[4];
+    __shared__ jd::Header hdr;                // (its own copies of the tables are not used below)
+    __shared__ uint8_t nat[64];
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(H);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(&hdr);
+        for (int i = (int)threadIdx.x; i < (int)(sizeof(jd::Header) / 4); i += (int)blockDim.x) dst[i] = src[i];
+        for (int i = (int)threadIdx.x; i < 64; i += (int)blockDim.x) nat[i] = (uint8_t)jd::natural(i);
+    }
+    __syncthreads();
+    for (int t = 0; t < 4; ++t) {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(t < 2 ? &hdr.dc[t] : &hdr.ac[t - 2]);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(&tabs[t]);
+        for (int i = (int)threadIdx.x; i < (int)(sizeof(jd::HuffTable) / 4); i += (int)blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    // ONE interval per warp, decoded by its first lane: 32 intervals in the lanes of one warp diverge at every symbol
+    // (measured: 6.5 of 32 lanes active per instruction), which costs more than the idle lanes do -- there are far
+    // more warp slots on the GPU than restart intervals in a frame.
+    const int r = (int)(blockIdx.x * kEntropyWarps + (threadIdx.x >> 5));
+    if (r >= n_intervals || (threadIdx.x & 31) != 0) return;
+    int16_t *const coef[3] = {c0, c1, c2};
+    jd::decode_interval(hdr, tabs, nat, scan, offs, r, coef);
+}
+// One thread per 8x8 block of any component: dequantise, inverse DCT, samples into the component's plane.
+__global__ void __launch_bounds__(128) jpeg_idct_kernel(const jd::Header *__restrict__ H, const int16_t *c0, const int16_t *c1, const int16_t *c2,
+                                                       uint8_t *p0, uint8_t *p1, uint8_t *p2)
+{
+    const int n0 = jd::blocks_w(*H, 0) * jd::blocks_h(*H, 0), n1 = jd::blocks_w(*H, 1) * jd::blocks_h(*H, 1);
+    int i = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    if (i >= n0 + 2 * n1) return;
+    const int c = i < n0 ? 0 : (i < n0 + n1 ? 1 : 2);
+    i -= c == 0 ? 0 : (c == 1 ? n0 : n0 + n1);
+    const int bw = jd::blocks_w(*H, c);
+    const size_t pitch = (size_t)bw * 8;
+    const int16_t *coef = (c == 0 ? c0 : (c == 1 ? c1 : c2)) + 64 * (size_t)i;
+    uint8_t *plane = c == 0 ? p0 : (c == 1 ? p1 : p2);
+    jd::idct_islow(coef, H->quant[c], plane + (size_t)(i / bw) * 8 * pitch + (size_t)(i % bw) * 8, pitch);
+}
+// One thread per four horizontally adjacent pixels: chroma up-sampling, colour conversion, packed BGR into the frame.
+__global__ void __launch_bounds__(256) jpeg_color_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ p0, const uint8_t *__restrict__ p1,
+                                                        const uint8_t *__restrict__ p2, uint8_t *dst, size_t dpitch)
+{
+    const int w = H->w, h = H->h, hs = H->hs;
+    const int x0 = 4 * (int)(blockIdx.x * blockDim.x + threadIdx.x), y = (int)blockIdx.y;
+    if (x0 >= w || y >= h) return;
+    const size_t pitch0 = (size_t)jd::blocks_w(*H, 0) * 8, pitch1 = (size_t)jd::blocks_w(*H, 1) * 8;
+    const int cw = (w + hs - 1) / hs, ch = (h + H->vs - 1) / H->vs;
+    uint32_t px[4];
+    const int n = min(4, w - x0);
+    for (int k = 0; k < n; ++k) {
+        const int x = x0 + k;
+        const int Y = p0[(size_t)y * pitch0 + x];
+        int cb, cr;
+        if (hs == 2) {
+            cb = jd::chroma_h2v2(p1, pitch1, cw, ch, x, y);
+            cr = jd::chroma_h2v2(p2, pitch1, cw, ch, x, y);
+        } else {
+            cb = p1[(size_t)y * pitch1 + x];
+            cr = p2[(size_t)y * pitch1 + x];
+        }
+        px[k] = jd::ycc_to_bgr(Y, cb, cr);
+    }
+    uint8_t *o = dst + (size_t)y * dpitch + (size_t)x0 * 3;
+    if (n == 4 && ((reinterpret_cast<uintptr_t>(o) & 3) == 0)) {
+        uint32_t *o32 = reinterpret_cast<uint32_t *>(o);
+        o32[0] = px[0] | (px[1] << 24);
+        o32[1] = (px[1] >> 8) | (px[2] << 16);
+        o32[2] = (px[2] >> 16) | (px[3] << 8);
+    } else {
+        for (int k = 0; k < n; ++k) {
+            o[3 * k + 0] = (uint8_t)px[k];
+            o[3 * k + 1] = (uint8_t)(px[k] >> 8);
+            o[3 * k + 2] = (uint8_t)(px[k] >> 16);
+        }
+    }
+}
+
+// Buffers of the GPU decoder for one camera of one pipeline slot (allocated by the first frame that takes this path).
+struct DevDec {
+    bool ready = false;
+    jd::Header *h_hdr = nullptr, *d_hdr = nullptr;      // pinned / device
+    uint8_t *h_scan = nullptr, *d_scan = nullptr;       // entropy-coded data
+    size_t scan_cap = 0;
+    uint32_t *h_offs = nullptr, *d_offs = nullptr;      // restart interval offsets
+    int offs_cap = 0, n_intervals = 0;
+    int16_t *d_coef = nullptr;                          // the three components' coefficient blocks, one allocation
+    size_t coef_bytes[3] = {0, 0, 0};
+    uint8_t *d_planes = nullptr;                        // the three components' sample planes, one allocation
+    size_t plane_bytes[3] = {0, 0, 0};
+    uint64_t device_bytes = 0;
+};
+
 struct JpegLane {                              // one camera of one pipeline slot
     nvjpegJpegState_t state = nullptr;
     nvjpegBufferPinned_t pinned = nullptr;
     nvjpegBufferDevice_t device = nullptr;
     nvjpegJpegStream_t stream = nullptr;
+    DevDec dev;
 };
 
 // A frame whose host stages are running: everything bs_submit_jpeg was given, kept until the GPU part is issued.
@@ -36,6 +140,7 @@ struct JpegPending {
     uint8_t *out = nullptr;
     size_t out_pitch = 0;
     bs_jpeg_out *jout = nullptr;
+    bool use_dev = false;                      // every frame has a restart interval: entropy decoding on the GPU
     int remaining = 0;                         // host stages still running (guarded by JpegWorkers::m)
 };
 
@@ -76,6 +181,11 @@ struct JpegWorkers {
         }
         cv_job.notify_all();
     }
+    bool slot_done(int slot)                   // every host stage of that frame has finished (does not block)
+    {
+        std::lock_guard<std::mutex> lk(m);
+        return pending[slot].remaining == 0;
+    }
     void wait_slot(int slot)                   // returns when every host stage of that frame has finished
     {
         std::unique_lock<std::mutex> lk(m);
@@ -110,6 +220,11 @@ struct JpegCtx {
     JpegWorkers *workers = nullptr;
     JpegPending pending[kPipelineDepth];
     bool threaded_ok = false;
+    bool last_use_dev = false;                 // the last submitted frame took the GPU entropy decoder
+    // GPU decoder: the cameras of a frame decode side by side, each on its own stream, joined into the upload stream
+    std::vector<cudaStream_t> dec_stream;
+    std::vector<cudaEvent_t> dec_done;
+    cudaEvent_t dec_start = nullptr;
 };
 
 void jpeg_lanes_destroy(JpegCtx *c)
@@ -121,8 +236,22 @@ void jpeg_lanes_destroy(JpegCtx *c)
         if (l.state) nvjpegJpegStateDestroy(l.state);
         if (l.pinned) nvjpegBufferPinnedDestroy(l.pinned);
         if (l.device) nvjpegBufferDeviceDestroy(l.device);
+        cudaFreeHost(l.dev.h_hdr);
+        cudaFreeHost(l.dev.h_scan);
+        cudaFreeHost(l.dev.h_offs);
+        cudaFree(l.dev.d_hdr);
+        cudaFree(l.dev.d_scan);
+        cudaFree(l.dev.d_offs);
+        cudaFree(l.dev.d_coef);
+        cudaFree(l.dev.d_planes);
     }
     c->lanes.clear();
+    for (cudaStream_t st : c->dec_stream) cudaStreamDestroy(st);
+    for (cudaEvent_t ev : c->dec_done) cudaEventDestroy(ev);
+    if (c->dec_start) cudaEventDestroy(c->dec_start);
+    c->dec_stream.clear();
+    c->dec_done.clear();
+    c->dec_start = nullptr;
     if (c->hparams) nvjpegDecodeParamsDestroy(c->hparams);
     if (c->hdec) nvjpegDecoderDestroy(c->hdec);
     c->hparams = nullptr;
@@ -134,7 +263,7 @@ void jpeg_lanes_destroy(JpegCtx *c)
 void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
 {
     static const char *off = getenv("BS_DEBUG_JPEG_THREADS");       // test hook: "0" keeps the one-thread decoders
-    if (h->n_cams < 2 || (off && off[0] == '0')) return;
+    if (off && off[0] == '0') return;
     bool ok = nvjpegDecoderCreate(c->lib, NVJPEG_BACKEND_HYBRID, &c->hdec) == NVJPEG_STATUS_SUCCESS &&
               nvjpegDecodeParamsCreate(c->lib, &c->hparams) == NVJPEG_STATUS_SUCCESS &&
               nvjpegDecodeParamsSetOutputFormat(c->hparams, NVJPEG_OUTPUT_BGRI) == NVJPEG_STATUS_SUCCESS;
@@ -157,6 +286,17 @@ void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
             c->workers->stage = [c, n_cams](int slot, int i) {
                 JpegLane &l = c->lanes[(size_t)slot * n_cams + i];
                 const JpegPending &p = c->pending[slot];
+                if (p.use_dev) {
+                    // GPU entropy decoding: the host only locates the restart intervals and moves the scan data
+                    // into pinned memory (a memchr pass and a memcpy, ~0.5 ms per 4K frame)
+                    DevDec &d = l.dev;
+                    const jd::Header &H = *d.h_hdr;
+                    const uint8_t *scan = p.jpeg[i] + H.scan_off;
+                    d.n_intervals = jd::find_intervals(scan, H.scan_len, H, d.h_offs, d.offs_cap - 1);
+                    if (d.n_intervals < 0) return -1;
+                    memcpy(d.h_scan, scan, H.scan_len);
+                    return 0;
+                }
                 nvjpegStatus_t st = nvjpegJpegStreamParse(c->lib, p.jpeg[i], p.bytes[i], 0, 0, l.stream);
                 if (st == NVJPEG_STATUS_SUCCESS) st = nvjpegDecodeJpegHost(c->lib, c->hdec, l.state, c->hparams, l.stream);
                 return (int)st;
@@ -166,6 +306,14 @@ void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
             const int want = std::min(kPipelineDepth * n_cams, 16);
             c->workers->start(std::max(std::min(want, hw > 2 ? hw - 1 : 1), std::min(n_cams, 4)), h->device);
         }
+    }
+    if (ok) {
+        c->dec_stream.assign(h->n_cams, nullptr);
+        c->dec_done.assign(h->n_cams, nullptr);
+        ok = cudaEventCreateWithFlags(&c->dec_start, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; i < h->n_cams && ok; ++i)
+            ok = cudaStreamCreateWithFlags(&c->dec_stream[i], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&c->dec_done[i], cudaEventDisableTiming) == cudaSuccess;
     }
     cudaGetLastError();
     if (!ok) jpeg_lanes_destroy(c);
@@ -244,6 +392,97 @@ void jpeg_ctx_destroy(JpegCtx *c)
     delete c;
 }
 
+// GPU-decoder set-up of one camera's frame (calling thread): parse the headers, size the lane's buffers.  False when
+// the file is not one the GPU decoder takes (no restart interval, progressive, other sampling ...) or memory is short.
+bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, size_t bytes)
+{
+    DevDec &d = l.dev;
+    if (!d.h_hdr && cudaHostAlloc(reinterpret_cast<void **>(&d.h_hdr), sizeof(jd::Header), cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        d.h_hdr = nullptr;
+        return false;
+    }
+    jd::Header &H = *d.h_hdr;
+    if (!jd::parse_header(jpeg, bytes, H) || H.w != h->sw[cam] || H.h != h->sh[cam]) return false;
+    if (H.hs == 2 && (H.w < 3 || H.h < 3)) return false;                  // the up-sampling's edge cases need two chroma columns
+    const long total = (long)H.mcus_x * H.mcus_y;
+    const int n_iv = (int)((total + H.dri - 1) / H.dri);
+    size_t cb[3], pb[3];
+    for (int c = 0; c < 3; ++c) {
+        const size_t blocks = (size_t)jd::blocks_w(H, c) * jd::blocks_h(H, c);
+        cb[c] = blocks * 64 * sizeof(int16_t);
+        pb[c] = blocks * 64;
+    }
+    cudaError_t e = cudaSuccess;
+    if (!d.d_hdr) e = cudaMalloc(reinterpret_cast<void **>(&d.d_hdr), sizeof(jd::Header));
+    if (e == cudaSuccess && d.scan_cap < H.scan_len) {
+        BS_CUDA_QUIET(cudaStreamSynchronize(h->s_h2d));                      // the old buffers may still be in use
+        cudaFreeHost(d.h_scan);
+        cudaFree(d.d_scan);
+        d.h_scan = d.d_scan = nullptr;
+        d.scan_cap = std::max<size_t>(2 * H.scan_len, 1u << 20);
+        e = cudaHostAlloc(reinterpret_cast<void **>(&d.h_scan), d.scan_cap, cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d.d_scan), d.scan_cap);
+        if (e != cudaSuccess) d.scan_cap = 0;
+    }
+    if (e == cudaSuccess && d.offs_cap < n_iv + 2) {
+        BS_CUDA_QUIET(cudaStreamSynchronize(h->s_h2d));
+        cudaFreeHost(d.h_offs);
+        cudaFree(d.d_offs);
+        d.h_offs = d.d_offs = nullptr;
+        d.offs_cap = n_iv + 2;
+        e = cudaHostAlloc(reinterpret_cast<void **>(&d.h_offs), sizeof(uint32_t) * (size_t)d.offs_cap, cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d.d_offs), sizeof(uint32_t) * (size_t)d.offs_cap);
+        if (e != cudaSuccess) d.offs_cap = 0;
+    }
+    if (e == cudaSuccess && (d.coef_bytes[0] != cb[0] || d.coef_bytes[1] != cb[1])) {
+        BS_CUDA_QUIET(cudaStreamSynchronize(h->s_h2d));
+        cudaFree(d.d_coef);
+        cudaFree(d.d_planes);
+        d.d_coef = nullptr;
+        d.d_planes = nullptr;
+        h->device_bytes -= d.device_bytes;
+        d.device_bytes = 0;
+        e = cudaMalloc(reinterpret_cast<void **>(&d.d_coef), cb[0] + cb[1] + cb[2]);
+        if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d.d_planes), pb[0] + pb[1] + pb[2]);
+        for (int c = 0; c < 3; ++c) {
+            d.coef_bytes[c] = e == cudaSuccess ? cb[c] : 0;
+            d.plane_bytes[c] = e == cudaSuccess ? pb[c] : 0;
+        }
+        if (e == cudaSuccess) {
+            d.device_bytes = cb[0] + cb[1] + cb[2] + pb[0] + pb[1] + pb[2];
+            h->device_bytes += d.device_bytes;
+        }
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    d.ready = true;
+    return true;
+}
+
+// Queue the GPU decode of one camera's frame (headers, scan data and interval offsets are in the lane's pinned
+// buffers): three copies, a memset and three kernels on the upload stream, BGR into the slot's device frame.
+int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cudaStream_t st)
+{
+    DevDec &d = l.dev;
+    const jd::Header &H = *d.h_hdr;
+    BS_CUDA(h, cudaMemcpyAsync(d.d_hdr, d.h_hdr, sizeof(jd::Header), cudaMemcpyHostToDevice, st));
+    BS_CUDA(h, cudaMemcpyAsync(d.d_scan, d.h_scan, H.scan_len, cudaMemcpyHostToDevice, st));
+    BS_CUDA(h, cudaMemcpyAsync(d.d_offs, d.h_offs, sizeof(uint32_t) * (size_t)(d.n_intervals + 1), cudaMemcpyHostToDevice, st));
+    BS_CUDA(h, cudaMemsetAsync(d.d_coef, 0, d.coef_bytes[0] + d.coef_bytes[1] + d.coef_bytes[2], st));
+    int16_t *c0 = d.d_coef, *c1 = c0 + d.coef_bytes[0] / 2, *c2 = c1 + d.coef_bytes[1] / 2;
+    uint8_t *p0 = d.d_planes, *p1 = p0 + d.plane_bytes[0], *p2 = p1 + d.plane_bytes[1];
+    jpeg_entropy_kernel<<<(d.n_intervals + kEntropyWarps - 1) / kEntropyWarps, 32 * kEntropyWarps, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, d.n_intervals, c0, c1, c2);
+    const int n_blocks = (int)((d.plane_bytes[0] + d.plane_bytes[1] + d.plane_bytes[2]) / 64);
+    jpeg_idct_kernel<<<(n_blocks + 127) / 128, 128, 0, st>>>(d.d_hdr, c0, c1, c2, p0, p1, p2);
+    jpeg_color_kernel<<<dim3(((H.w + 3) / 4 + 255) / 256, H.h), 256, 0, st>>>(d.d_hdr, p0, p1, p2, d_frame, pitch);
+    BS_CUDA(h, cudaGetLastError());
+    h->kernel_launches += 3;
+    return BS_OK;
+}
+
 // bs_submit_jpeg's checks: every bitstream is a JPEG of its camera's frame size.
 int check_jpeg_frames(bs_handle *h, JpegCtx *c, const uint8_t *const *jpeg, const size_t *jpeg_bytes)
 {
@@ -276,7 +515,27 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
         h->h2d_bytes_last += jpeg_bytes[i];
     }
     bool decoded = false;
-    if (host_status) {
+    if (host_status && c->pending[slot_index].use_dev) {
+        // entropy decoding on the GPU (every frame has a restart interval): the workers located the intervals
+        decoded = true;
+        for (int i = 0; i < h->n_cams; ++i) decoded = decoded && host_status[i] == 0;
+        if (decoded) {
+            // fork: every camera's chain starts where the upload stream is now, and the upload stream continues
+            // when all of them are done
+            BS_CUDA(h, cudaEventRecord(c->dec_start, h->s_h2d));
+            for (int i = 0; i < h->n_cams; ++i) {
+                BS_CUDA(h, cudaStreamWaitEvent(c->dec_stream[i], c->dec_start, 0));
+                rc = devdec_issue(h, c->lanes[(size_t)slot_index * h->n_cams + i], s.d_frame[i], h->d_frame_pitch[i], c->dec_stream[i]);
+                if (rc != BS_OK) return rc;
+                BS_CUDA(h, cudaEventRecord(c->dec_done[i], c->dec_stream[i]));
+                BS_CUDA(h, cudaStreamWaitEvent(h->s_h2d, c->dec_done[i], 0));
+            }
+        }
+        if (!decoded) {
+            cudaStreamSynchronize(h->s_h2d);
+            cudaGetLastError();
+        }
+    } else if (host_status) {
         // device stages in camera order on the upload stream; a bitstream the decoupled decoder could not take
         // (progressive ...) sends the frame to the decoders below
         JpegLane *lanes = &c->lanes[(size_t)slot_index * h->n_cams];
@@ -363,7 +622,7 @@ int retrieve_jpeg(bs_handle *h, Slot &s, int slot_index)
 // Issue the GPU side of every frame whose host stages were left running by bs_submit_jpeg, oldest first, up to
 // ticket `upto` (frames go to the streams in ticket order).  A frame that fails is dropped and its error kept in
 // its slot for the bs_wait of that ticket.
-int flush_deferred_jpeg(bs_handle *h, int64_t upto)
+int flush_deferred_jpeg(bs_handle *h, int64_t upto, bool only_ready)
 {
     if (!h->jpeg || h->ring.empty()) return BS_OK;
     JpegCtx *c = h->jpeg;
@@ -371,6 +630,7 @@ int flush_deferred_jpeg(bs_handle *h, int64_t upto)
         const int slot_index = (int)(t % kPipelineDepth);
         Slot &s = h->ring[slot_index];
         if (s.ticket != t || !s.deferred) continue;
+        if (only_ready && !c->workers->slot_done(slot_index)) break;      // frames go to the streams in ticket order
         c->workers->wait_slot(slot_index);
         s.deferred = false;
         JpegPending &p = c->pending[slot_index];
@@ -409,6 +669,7 @@ extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const si
     if (rc != BS_OK) return rc;
     rc = check_jpeg_frames(h, c, jpeg, jpeg_bytes);
     if (rc != BS_OK) return rc;
+    flush_deferred_jpeg(h, h->next_ticket - 1, true);       // earlier frames whose host stages are done go to the GPU now
     const int64_t t = h->next_ticket;
     const int slot_index = (int)(t % kPipelineDepth);
     Slot &s = h->ring[slot_index];
@@ -421,6 +682,11 @@ extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const si
         // next call on this handle that needs the frame (bs_wait, a later submit, bs_sync), so that the host stages
         // of up to bs_pipeline_depth frames overlap.  The bitstreams must stay valid until bs_wait, as `out` must.
         JpegPending &p = c->pending[slot_index];
+        static const bool no_dev = getenv("BS_DEBUG_JPEG_NO_GPU_ENTROPY") != nullptr;     // test hook: always nvJPEG
+        p.use_dev = !no_dev;
+        for (int i = 0; i < h->n_cams && p.use_dev; ++i)
+            p.use_dev = devdec_prepare(h, c->lanes[(size_t)slot_index * h->n_cams + i], i, jpeg[i], jpeg_bytes[i]);
+        c->last_use_dev = p.use_dev;
         p.jpeg.assign(jpeg, jpeg + h->n_cams);
         p.bytes.assign(jpeg_bytes, jpeg_bytes + h->n_cams);
         p.status.assign(h->n_cams, 0);
@@ -451,5 +717,6 @@ extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const si
 
 extern "C" const char *bs_jpeg_backend(const bs_handle *h)
 {
-    return (h && h->jpeg) ? h->jpeg->backend : "";
+    if (!h || !h->jpeg) return "";
+    return h->jpeg->last_use_dev ? "b200 (entropy decoding on the GPU, one thread per restart interval; libjpeg arithmetic)" : h->jpeg->backend;
 }

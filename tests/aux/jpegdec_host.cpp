@@ -1,0 +1,68 @@
+// Host build of the device JPEG decoder's functions (image-stitching_b200/csrc/stitch_jpegdec.cuh): decodes a file the
+// way the GPU kernels do, block by block and pixel by pixel, and writes raw BGR.  Test infrastructure: lets
+// tests/test_jpegdec.py pin the decoder's arithmetic against cv2.imdecode without a GPU.
+// usage: jpegdec_host in.jpg out.bgr   (prints "w h hs vs dri intervals", exit 2 = not a file this decoder takes)
+#include <cstdio>
+#include <vector>
+
+#include "../../image-stitching_b200/csrc/stitch_jpegdec.cuh"
+
+int main(int argc, char **argv)
+{
+    if (argc < 3) return 1;
+    FILE *f = fopen(argv[1], "rb");
+    if (!f) return 1;
+    std::vector<uint8_t> d;
+    for (int c; (c = fgetc(f)) != EOF;) d.push_back((uint8_t)c);
+    fclose(f);
+    jd::Header H;
+    if (!jd::parse_header(d.data(), d.size(), H)) return 2;
+    const long total = (long)H.mcus_x * H.mcus_y;
+    const int max_iv = (int)((total + H.dri - 1) / H.dri);
+    std::vector<uint32_t> offs(max_iv + 1);
+    const int n_iv = jd::find_intervals(d.data() + H.scan_off, H.scan_len, H, offs.data(), max_iv);
+    if (n_iv < 0) return 2;
+    std::vector<int16_t> coef[3];
+    int16_t *cp[3];
+    for (int c = 0; c < 3; ++c) {
+        coef[c].assign((size_t)64 * jd::blocks_w(H, c) * jd::blocks_h(H, c), 0);
+        cp[c] = coef[c].data();
+    }
+    const jd::HuffTable tabs[4] = {H.dc[0], H.dc[1], H.ac[0], H.ac[1]};
+    for (int r = 0; r < n_iv; ++r) jd::decode_interval(H, tabs, jd::kNaturalHost, d.data() + H.scan_off, offs.data(), r, cp);
+    std::vector<uint8_t> plane[3];
+    size_t pitch[3];
+    for (int c = 0; c < 3; ++c) {
+        const int bw = jd::blocks_w(H, c), bh = jd::blocks_h(H, c);
+        pitch[c] = (size_t)bw * 8;
+        plane[c].assign(pitch[c] * bh * 8, 0);
+        for (int by = 0; by < bh; ++by)
+            for (int bx = 0; bx < bw; ++bx)
+                jd::idct_islow(cp[c] + 64 * ((size_t)by * bw + bx), H.quant[c], plane[c].data() + (size_t)by * 8 * pitch[c] + bx * 8, pitch[c]);
+    }
+    std::vector<uint8_t> out((size_t)H.w * H.h * 3);
+    const int cw = (H.w + H.hs - 1) / H.hs, ch = (H.h + H.vs - 1) / H.vs;
+    for (int y = 0; y < H.h; ++y)
+        for (int x = 0; x < H.w; ++x) {
+            const int Y = plane[0][(size_t)y * pitch[0] + x];
+            int cb, cr;
+            if (H.hs == 2) {
+                cb = jd::chroma_h2v2(plane[1].data(), pitch[1], cw, ch, x, y);
+                cr = jd::chroma_h2v2(plane[2].data(), pitch[2], cw, ch, x, y);
+            } else {
+                cb = plane[1][(size_t)y * pitch[1] + x];
+                cr = plane[2][(size_t)y * pitch[2] + x];
+            }
+            const uint32_t p = jd::ycc_to_bgr(Y, cb, cr);
+            uint8_t *o = &out[((size_t)y * H.w + x) * 3];
+            o[0] = (uint8_t)p;
+            o[1] = (uint8_t)(p >> 8);
+            o[2] = (uint8_t)(p >> 16);
+        }
+    f = fopen(argv[2], "wb");
+    if (!f) return 1;
+    fwrite(out.data(), 1, out.size(), f);
+    fclose(f);
+    printf("%d %d %d %d %d %d\n", H.w, H.h, H.hs, H.vs, H.dri, n_iv);
+    return 0;
+}

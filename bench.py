@@ -508,49 +508,56 @@ def run_b200(args, rank, local_rank, world):
                                                              d_canvas[j % RING].cpu().numpy()))
 
     # ---- end to end with COMPRESSED frames: JPEG bitstreams up, decoded on the device (bs_submit_jpeg) ----
+    # Two records: plain JPEGs as cv2.imencode writes them (no restart interval: the entropy stage runs on the host,
+    # nvJPEG), and the same frames written with a restart interval of one MCU row (the entropy stage runs on the GPU,
+    # stitch_jpegdec.cuh, and the decoded pixels equal cv2.imdecode's).
     e2e_jpeg = None
+    e2e_jpeg_rst = None
     if not args.no_e2e and not args.no_compressed:
         try:
             import cv2
-            # hash noise does not compress (its JPEG is as large as the raw frame), so this record uses the smooth
+            # hash noise does not compress (its JPEG is as large as the raw frame), so these records use the smooth
             # content plus a little texture; the panorama comes back raw, as in `e2e`
             def textured(i, f):
                 a = wl.gen_frame_numpy(sw, sh, i, rank + world * f, "smooth").astype(np.int16)
                 a += (wl.gen_frame_numpy(sw, sh, i, f, "noise") >> 5).astype(np.int16) - 4
                 return np.clip(a, 0, 255).astype(np.uint8)
-            enc_args = [cv2.IMWRITE_JPEG_QUALITY, 90]
-            rst = int(os.environ.get("BS_BENCH_JPEG_RST", "0"))      # experiment: restart interval in MCUs (0 = none, cv2's default)
-            if rst:
-                enc_args += [cv2.IMWRITE_JPEG_RST_INTERVAL, rst]
-            jf = [[np.frombuffer(cv2.imencode(".jpg", textured(i, f), enc_args)[1].tobytes(), dtype=np.uint8).copy()
-                   for i in range(n)] for f in range(3)]
-            jbytes = int(sum(b.size for b in jf[0]))
+            pics = [[textured(i, f) for i in range(n)] for f in range(3)]
             depth = pkg.lib().bs_pipeline_depth(st._h)
             hj_out = [pkg.pinned_empty((H, W, 3)) for _ in range(depth + 1)]
 
-            def jpeg_frames(k):
-                tickets = []
-                for j in range(k):
-                    if len(tickets) >= depth:
-                        st.wait(tickets[len(tickets) - depth])
-                    tickets.append(st.submit_jpeg(jf[j % len(jf)], hj_out[j % len(hj_out)]))
-                for t in tickets[-depth:]:
-                    st.wait(t)
-            jpeg_frames(4)
-            nj = max(8, min(48, args.steps * 2))
-            barrier()
-            t0 = time.perf_counter()
-            jpeg_frames(nj)
-            st.sync()
-            t1 = time.perf_counter()
-            barrier()
-            js = max_over_ranks(t1 - t0)
-            e2e_jpeg = {"value": world * nj / js, "unit": UNIT, "h2d_bytes_per_frame": jbytes, "d2h_bytes_per_frame": w.canvas_bytes,
-                        "frames": nj, "content": "smooth ramp + 3 bits of texture, JPEG quality 90 (cv2.imencode)",
-                        "decoder": f"nvJPEG ({st.jpeg_backend()}) into the device frame ring (bs_submit_jpeg), panorama returned raw",
+            def compressed_record(rst):
+                enc_args = [cv2.IMWRITE_JPEG_QUALITY, 90] + ([cv2.IMWRITE_JPEG_RST_INTERVAL, rst] if rst else [])
+                jf = [[np.frombuffer(cv2.imencode(".jpg", pic, enc_args)[1].tobytes(), dtype=np.uint8).copy() for pic in fs] for fs in pics]
+                jbytes = int(sum(b.size for b in jf[0]))
+
+                def jpeg_frames(k):
+                    tickets = []
+                    for j in range(k):
+                        if len(tickets) >= depth:
+                            st.wait(tickets[len(tickets) - depth])
+                        tickets.append(st.submit_jpeg(jf[j % len(jf)], hj_out[j % len(hj_out)]))
+                    for t in tickets[-depth:]:
+                        st.wait(t)
+                jpeg_frames(4)
+                nj = max(8, min(48, args.steps * 2))
+                barrier()
+                t0 = time.perf_counter()
+                jpeg_frames(nj)
+                st.sync()
+                t1 = time.perf_counter()
+                barrier()
+                js = max_over_ranks(t1 - t0)
+                return {"value": world * nj / js, "unit": UNIT, "h2d_bytes_per_frame": jbytes, "d2h_bytes_per_frame": w.canvas_bytes,
+                        "frames": nj, "restart_interval_mcus": rst,
+                        "content": "smooth ramp + 3 bits of texture, JPEG quality 90, 4:2:0 (cv2.imencode)",
+                        "decoder": f"{st.jpeg_backend()}; into the device frame ring (bs_submit_jpeg), panorama returned raw",
                         "raw_h2d_bytes_per_frame_for_comparison": h2d_per_frame if e2e else None}
+            rst_env = int(os.environ.get("BS_BENCH_JPEG_RST", "0"))     # experiment: another restart interval for the second record
+            e2e_jpeg = compressed_record(0)
+            e2e_jpeg_rst = compressed_record(rst_env if rst_env else (sw + 15) // 16)
         except Exception as ex:   # pragma: no cover
-            e2e_jpeg = {"unavailable": f"{type(ex).__name__}: {ex}"}
+            e2e_jpeg = e2e_jpeg or {"unavailable": f"{type(ex).__name__}: {ex}"}
 
     stats = st.stats()
     stats_kernel = ["stitch_exact_kernel", "stitch_fast_kernel (general staged)", "stitch_fast2_kernel (compact boxes)"][stats["frame_kernel"]]
@@ -615,7 +622,7 @@ def run_b200(args, rank, local_rank, world):
                 "tiles_fast_exact_empty": [stats["n_tiles_fast"], stats["n_tiles_exact"], stats["n_tiles_empty"]],
                 "kernel": stats_kernel},
         "undistort": undist,
-        "e2e": e2e, "e2e_compressed": e2e_jpeg, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "e2e": e2e, "e2e_compressed": e2e_jpeg, "e2e_compressed_restart": e2e_jpeg_rst, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "clocks": sampler.summary(), "parity": parity,
     }
     print(json.dumps(line), flush=True)

@@ -31,8 +31,7 @@ __global__ void __launch_bounds__(32 * kEntropyWarps) jpeg_entropy_kernel(const 
                                                          int16_t *c2)
 {
     // the tables every symbol goes through live in shared memory: a thread is one long dependent chain of look-ups
-    __shared__ jd::HuffTable tabs[4];
-    __shared__ jd::Header hdr;                // (its own copies of the tables are not used below)
+    __shared__ jd::Header hdr;
     __shared__ uint8_t nat[64];
     {
         const uint32_t *src = reinterpret_cast<const uint32_t *>(H);
@@ -41,12 +40,8 @@ __global__ void __launch_bounds__(32 * kEntropyWarps) jpeg_entropy_kernel(const 
         for (int i = (int)threadIdx.x; i < 64; i += (int)blockDim.x) nat[i] = (uint8_t)jd::natural(i);
     }
     __syncthreads();
-    for (int t = 0; t < 4; ++t) {
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(t < 2 ? &hdr.dc[t] : &hdr.ac[t - 2]);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(&tabs[t]);
-        for (int i = (int)threadIdx.x; i < (int)(sizeof(jd::HuffTable) / 4); i += (int)blockDim.x) dst[i] = src[i];
-    }
-    __syncthreads();
+    const jd::HuffTable *tabs = hdr.dc;       // dc[0], dc[1], ac[0], ac[1] are adjacent members
+    static_assert(offsetof(jd::Header, ac) == offsetof(jd::Header, dc) + 2 * sizeof(jd::HuffTable), "table layout");
     // ONE interval per warp, decoded by its first lane: 32 intervals in the lanes of one warp diverge at every symbol
     // (measured: 6.5 of 32 lanes active per instruction), which costs more than the idle lanes do -- there are far
     // more warp slots on the GPU than restart intervals in a frame.
@@ -407,6 +402,10 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
     if (H.hs == 2 && (H.w < 3 || H.h < 3)) return false;                  // the up-sampling's edge cases need two chroma columns
     const long total = (long)H.mcus_x * H.mcus_y;
     const int n_iv = (int)((total + H.dri - 1) / H.dri);
+    // One GPU thread per interval is a long serial chain (measured at 4K, 4:2:0, quality 90: one MCU row = 240 MCUs
+    // per interval still beats the host decoders, 166 against 104 panoramas/s); a large frame cut into a handful of
+    // intervals is better off with nvJPEG's host stage.
+    if (n_iv < 64 && total > 4096) return false;
     size_t cb[3], pb[3];
     for (int c = 0; c < 3; ++c) {
         const size_t blocks = (size_t)jd::blocks_w(H, c) * jd::blocks_h(H, c);

@@ -52,6 +52,7 @@ struct HuffTable {
     int32_t maxcode[18];     // largest code of each length (-1: none); [17] ends every search
     int32_t valoff[17];      // index of the first value of a length minus its smallest code
     uint16_t look[512];      // 9 bits of look-ahead: length << 8 | value, 0 when the code is longer
+    int16_t fast[512];       // AC tables: when code + magnitude bits fit the 9 bits, value << 8 | run << 4 | total length
 };
 
 struct Header {
@@ -89,6 +90,18 @@ inline bool build_huff(const uint8_t *bits /* 16 counts */, const uint8_t *vals,
         code <<= 1;
     }
     t.maxcode[17] = 0x7fffffff;
+    // run/size symbols whose code AND magnitude bits fit the look-ahead decode in one step (most AC coefficients)
+    for (int i = 0; i < 512; ++i) {
+        t.fast[i] = 0;
+        const int e = t.look[i];
+        if (!e) continue;
+        const int len = e >> 8, run = (e >> 4) & 15, mag = e & 15;
+        if (mag && len + mag <= 9) {
+            int v = ((i << len) & 511) >> (9 - mag);
+            if (v < (1 << (mag - 1))) v -= (1 << mag) - 1;
+            if (v >= -128 && v <= 127) t.fast[i] = (int16_t)(v * 256 + run * 16 + len + mag);
+        }
+    }
     return k == nvals;
 }
 
@@ -270,6 +283,14 @@ JD_HD void decode_block(BitReader &b, const HuffTable &dc, const HuffTable &ac, 
     if (s) pred += receive_extend(b, s & 15);
     coef[0] = (int16_t)pred;
     for (int k = 1; k < 64; ++k) {
+        if (b.cnt < 16) br_fill(b);
+        const int f = ac.fast[br_peek(b, 9)];
+        if (f) {                                             // code and magnitude in one look-up
+            k += (f >> 4) & 15;
+            br_skip(b, f & 15);
+            if (k < 64) coef[nat[k]] = (int16_t)(f >> 8);
+            continue;
+        }
         const int rs = huff_decode(b, ac);
         const int r = rs >> 4;
         s = rs & 15;
@@ -299,10 +320,14 @@ JD_HD void decode_interval(const Header &H, const HuffTable *tabs, const uint8_t
     b.buf = 0;
     b.cnt = 0;
     int pred[3] = {0, 0, 0};
-    const long total = (long)H.mcus_x * H.mcus_y;
-    const long m0 = (long)r * H.dri, m1 = (m0 + H.dri < total) ? m0 + H.dri : total;
-    for (long m = m0; m < m1; ++m) {
-        const int mx = (int)(m % H.mcus_x), my = (int)(m / H.mcus_x);
+    const int total = H.mcus_x * H.mcus_y;                   // (< 2^24: dimensions are 16-bit)
+    const int m0 = r * H.dri, m1 = (m0 + H.dri < total) ? m0 + H.dri : total;
+    int mx = m0 % H.mcus_x, my = m0 / H.mcus_x;
+    for (int m = m0; m < m1; ++m, ++mx) {
+        if (mx == H.mcus_x) {
+            mx = 0;
+            ++my;
+        }
         for (int c = 0; c < 3; ++c) {
             const int hs = c == 0 ? H.hs : 1, vs = c == 0 ? H.vs : 1, bw = blocks_w(H, c);
             for (int v = 0; v < vs; ++v)

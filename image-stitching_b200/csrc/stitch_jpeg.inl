@@ -125,6 +125,10 @@ struct JpegLane {                              // one camera of one pipeline slo
     nvjpegBufferDevice_t device = nullptr;
     nvjpegJpegStream_t stream = nullptr;
     DevDec dev;
+    // GPU decoder: every camera of every pipeline slot decodes on a stream of its own (the chains of consecutive frames
+    // and of the cameras of one frame overlap: a chain is a few hundred single-lane warps), joined into the upload stream
+    cudaStream_t dec_stream = nullptr;
+    cudaEvent_t dec_done = nullptr;
 };
 
 // A frame whose host stages are running: everything bs_submit_jpeg was given, kept until the GPU part is issued.
@@ -216,10 +220,6 @@ struct JpegCtx {
     JpegPending pending[kPipelineDepth];
     bool threaded_ok = false;
     bool last_use_dev = false;                 // the last submitted frame took the GPU entropy decoder
-    // GPU decoder: the cameras of a frame decode side by side, each on its own stream, joined into the upload stream
-    std::vector<cudaStream_t> dec_stream;
-    std::vector<cudaEvent_t> dec_done;
-    cudaEvent_t dec_start = nullptr;
 };
 
 void jpeg_lanes_destroy(JpegCtx *c)
@@ -239,14 +239,10 @@ void jpeg_lanes_destroy(JpegCtx *c)
         cudaFree(l.dev.d_offs);
         cudaFree(l.dev.d_coef);
         cudaFree(l.dev.d_planes);
+        if (l.dec_stream) cudaStreamDestroy(l.dec_stream);
+        if (l.dec_done) cudaEventDestroy(l.dec_done);
     }
     c->lanes.clear();
-    for (cudaStream_t st : c->dec_stream) cudaStreamDestroy(st);
-    for (cudaEvent_t ev : c->dec_done) cudaEventDestroy(ev);
-    if (c->dec_start) cudaEventDestroy(c->dec_start);
-    c->dec_stream.clear();
-    c->dec_done.clear();
-    c->dec_start = nullptr;
     if (c->hparams) nvjpegDecodeParamsDestroy(c->hparams);
     if (c->hdec) nvjpegDecoderDestroy(c->hdec);
     c->hparams = nullptr;
@@ -302,14 +298,9 @@ void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
             c->workers->start(std::max(std::min(want, hw > 2 ? hw - 1 : 1), std::min(n_cams, 4)), h->device);
         }
     }
-    if (ok) {
-        c->dec_stream.assign(h->n_cams, nullptr);
-        c->dec_done.assign(h->n_cams, nullptr);
-        ok = cudaEventCreateWithFlags(&c->dec_start, cudaEventDisableTiming) == cudaSuccess;
-        for (int i = 0; i < h->n_cams && ok; ++i)
-            ok = cudaStreamCreateWithFlags(&c->dec_stream[i], cudaStreamNonBlocking) == cudaSuccess &&
-                 cudaEventCreateWithFlags(&c->dec_done[i], cudaEventDisableTiming) == cudaSuccess;
-    }
+    for (size_t k = 0; k < c->lanes.size() && ok; ++k)
+        ok = cudaStreamCreateWithFlags(&c->lanes[k].dec_stream, cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&c->lanes[k].dec_done, cudaEventDisableTiming) == cudaSuccess;
     cudaGetLastError();
     if (!ok) jpeg_lanes_destroy(c);
     c->threaded_ok = ok;
@@ -415,7 +406,7 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
     cudaError_t e = cudaSuccess;
     if (!d.d_hdr) e = cudaMalloc(reinterpret_cast<void **>(&d.d_hdr), sizeof(jd::Header));
     if (e == cudaSuccess && d.scan_cap < H.scan_len) {
-        BS_CUDA_QUIET(cudaStreamSynchronize(h->s_h2d));                      // the old buffers may still be in use
+        BS_CUDA_QUIET(cudaStreamSynchronize(l.dec_stream));                  // the old buffers may still be in use
         cudaFreeHost(d.h_scan);
         cudaFree(d.d_scan);
         d.h_scan = d.d_scan = nullptr;
@@ -425,7 +416,7 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
         if (e != cudaSuccess) d.scan_cap = 0;
     }
     if (e == cudaSuccess && d.offs_cap < n_iv + 2) {
-        BS_CUDA_QUIET(cudaStreamSynchronize(h->s_h2d));
+        BS_CUDA_QUIET(cudaStreamSynchronize(l.dec_stream));
         cudaFreeHost(d.h_offs);
         cudaFree(d.d_offs);
         d.h_offs = d.d_offs = nullptr;
@@ -435,7 +426,7 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
         if (e != cudaSuccess) d.offs_cap = 0;
     }
     if (e == cudaSuccess && (d.coef_bytes[0] != cb[0] || d.coef_bytes[1] != cb[1])) {
-        BS_CUDA_QUIET(cudaStreamSynchronize(h->s_h2d));
+        BS_CUDA_QUIET(cudaStreamSynchronize(l.dec_stream));
         cudaFree(d.d_coef);
         cudaFree(d.d_planes);
         d.d_coef = nullptr;
@@ -518,17 +509,14 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
         // entropy decoding on the GPU (every frame has a restart interval): the workers located the intervals
         decoded = true;
         for (int i = 0; i < h->n_cams; ++i) decoded = decoded && host_status[i] == 0;
-        if (decoded) {
-            // fork: every camera's chain starts where the upload stream is now, and the upload stream continues
-            // when all of them are done
-            BS_CUDA(h, cudaEventRecord(c->dec_start, h->s_h2d));
-            for (int i = 0; i < h->n_cams; ++i) {
-                BS_CUDA(h, cudaStreamWaitEvent(c->dec_stream[i], c->dec_start, 0));
-                rc = devdec_issue(h, c->lanes[(size_t)slot_index * h->n_cams + i], s.d_frame[i], h->d_frame_pitch[i], c->dec_stream[i]);
-                if (rc != BS_OK) return rc;
-                BS_CUDA(h, cudaEventRecord(c->dec_done[i], c->dec_stream[i]));
-                BS_CUDA(h, cudaStreamWaitEvent(h->s_h2d, c->dec_done[i], 0));
-            }
+        for (int i = 0; i < h->n_cams && decoded; ++i) {
+            // the chain needs nothing from the upload stream (the slot's buffers were released by bs_wait); the
+            // upload stream goes on when every camera's chain is done
+            JpegLane &l = c->lanes[(size_t)slot_index * h->n_cams + i];
+            rc = devdec_issue(h, l, s.d_frame[i], h->d_frame_pitch[i], l.dec_stream);
+            if (rc != BS_OK) return rc;
+            BS_CUDA(h, cudaEventRecord(l.dec_done, l.dec_stream));
+            BS_CUDA(h, cudaStreamWaitEvent(h->s_h2d, l.dec_done, 0));
         }
         if (!decoded) {
             cudaStreamSynchronize(h->s_h2d);

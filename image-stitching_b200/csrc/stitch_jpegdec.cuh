@@ -231,8 +231,36 @@ JD_HD uint32_t br_byte(const uint8_t *p)
     return *p;
 #endif
 }
+// Four bytes at p (any alignment), first byte in the low bits.  The buffer has 8 spare bytes behind the data.
+JD_HD uint32_t br_word(const uint8_t *p)
+{
+#ifdef __CUDA_ARCH__
+    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
+    return __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8u * (uint32_t)(a & 3));
+#else
+    uint32_t v;
+    memcpy(&v, p, 4);
+    return v;
+#endif
+}
 JD_HD void br_fill(BitReader &b)
 {
+    // four bytes at once while none of them is 0xFF (no stuffing, no marker): the common case
+    if (b.cnt <= 32 && b.p + 4 <= b.end) {
+        const uint32_t v = br_word(b.p);
+        if ((((~v) - 0x01010101u) & v & 0x80808080u) == 0) {
+#ifdef __CUDA_ARCH__
+            const uint32_t be = __byte_perm(v, 0, 0x0123);
+#else
+            const uint32_t be = __builtin_bswap32(v);
+#endif
+            b.buf |= (uint64_t)be << (32 - b.cnt);
+            b.cnt += 32;
+            b.p += 4;
+            return;
+        }
+    }
     while (b.cnt <= 56) {
         uint32_t byte = 0;
         if (b.p < b.end) {
@@ -319,7 +347,8 @@ JD_HD void decode_interval(const Header &H, const HuffTable *tabs, const uint8_t
     b.end = scan + offs[r + 1];
     b.buf = 0;
     b.cnt = 0;
-    int pred[3] = {0, 0, 0};
+    int pred0 = 0, pred1 = 0, pred2 = 0;
+    const int bw0 = blocks_w(H, 0);
     const int total = H.mcus_x * H.mcus_y;                   // (< 2^24: dimensions are 16-bit)
     const int m0 = r * H.dri, m1 = (m0 + H.dri < total) ? m0 + H.dri : total;
     int mx = m0 % H.mcus_x, my = m0 / H.mcus_x;
@@ -328,13 +357,14 @@ JD_HD void decode_interval(const Header &H, const HuffTable *tabs, const uint8_t
             mx = 0;
             ++my;
         }
-        for (int c = 0; c < 3; ++c) {
-            const int hs = c == 0 ? H.hs : 1, vs = c == 0 ? H.vs : 1, bw = blocks_w(H, c);
-            for (int v = 0; v < vs; ++v)
-                for (int u = 0; u < hs; ++u)
-                    decode_block(b, tabs[H.dc_tab[c]], tabs[2 + H.ac_tab[c]], pred[c],
-                                 coef[c] + 64 * ((size_t)(my * vs + v) * bw + (size_t)(mx * hs + u)), nat);
-        }
+        // luma blocks of the MCU, then one Cb and one Cr block (predictors and pointers stay in registers)
+        for (int v = 0; v < H.vs; ++v)
+            for (int u = 0; u < H.hs; ++u)
+                decode_block(b, tabs[H.dc_tab[0]], tabs[2 + H.ac_tab[0]], pred0,
+                             coef[0] + 64 * ((size_t)(my * H.vs + v) * bw0 + (size_t)(mx * H.hs + u)), nat);
+        const size_t cblk = 64 * ((size_t)my * H.mcus_x + (size_t)mx);
+        decode_block(b, tabs[H.dc_tab[1]], tabs[2 + H.ac_tab[1]], pred1, coef[1] + cblk, nat);
+        decode_block(b, tabs[H.dc_tab[2]], tabs[2 + H.ac_tab[2]], pred2, coef[2] + cblk, nat);
     }
 }
 

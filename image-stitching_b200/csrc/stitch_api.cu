@@ -28,7 +28,10 @@ constexpr size_t kErrLen = 512;
 thread_local char g_last_error[kErrLen] = "";
 thread_local int g_last_device = 0;
 
-constexpr int kPipelineDepth = 3;
+#ifndef BS_PIPELINE_DEPTH
+#define BS_PIPELINE_DEPTH 3
+#endif
+constexpr int kPipelineDepth = BS_PIPELINE_DEPTH;
 
 struct Slot {
     std::vector<uint8_t *> d_frame;

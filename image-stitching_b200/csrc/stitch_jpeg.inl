@@ -207,10 +207,10 @@ struct JpegCtx {
     // Batched decoder, one batch = the cameras of one frame: the GPU's JPEG engine when the library drives one
     // on this device, else GPU-assisted Huffman decoding; nullptr when neither initialises.
     nvjpegHandle_t blib = nullptr;
-    nvjpegJpegState_t bdec[kPipelineDepth] = {nullptr, nullptr, nullptr};
+    nvjpegJpegState_t bdec[kPipelineDepth] = {};
     bool batched_ok = false;
-    nvjpegEncoderState_t enc[kPipelineDepth] = {nullptr, nullptr, nullptr};
-    nvjpegEncoderParams_t enc_params[kPipelineDepth] = {nullptr, nullptr, nullptr};
+    nvjpegEncoderState_t enc[kPipelineDepth] = {};
+    nvjpegEncoderParams_t enc_params[kPipelineDepth] = {};
     const char *backend = "default";
     // host entropy stage on worker threads (see JpegLane)
     nvjpegJpegDecoder_t hdec = nullptr;

@@ -50,6 +50,121 @@ __global__ void __launch_bounds__(32 * kEntropyWarps) jpeg_entropy_kernel(const 
     int16_t *const coef[3] = {c0, c1, c2};
     jd::decode_interval(hdr, tabs, nat, scan, offs, r, coef);
 }
+// The chunked, self-synchronising form (stitch_jpegdec.cuh): ONE BLOCK per restart interval (or per whole scan when
+// the file has no restart markers), one thread per chunk of the interval's stuffing-free data.
+__global__ void __launch_bounds__(1024) jpeg_entropy_sync_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ data,
+                                                                const uint32_t *__restrict__ offs, int n_intervals, int dri, int16_t *c0,
+                                                                int16_t *c1, int16_t *c2, int *__restrict__ not_converged)
+{
+    __shared__ jd::Header hdr;
+    __shared__ uint8_t nat[64];
+    __shared__ jd::SyncState exit_state[1024];
+    __shared__ int first_block[1024];
+    __shared__ int dc_off[1024][3];
+    const int T = (int)blockDim.x, j = (int)threadIdx.x, r = (int)blockIdx.x;
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(H);
+        uint32_t *dst = reinterpret_cast<uint32_t *>(&hdr);
+        for (int i = j; i < (int)(sizeof(jd::Header) / 4); i += T) dst[i] = src[i];
+        for (int i = j; i < 64; i += T) nat[i] = (uint8_t)jd::natural(i);
+    }
+    __syncthreads();
+    const jd::HuffTable *tabs = hdr.dc;
+    const uint8_t *base = data + offs[r];
+    const uint32_t data_bits = (offs[r + 1] - offs[r]) * 8u;
+    uint32_t chunk_bits = ((data_bits + (uint32_t)T - 1) / (uint32_t)T + 7u) & ~7u;
+    if (chunk_bits < 64u) chunk_bits = 64u;
+    const int total = hdr.mcus_x * hdr.mcus_y, m_first = r * dri;
+    const int nb = hdr.hs * hdr.vs + 2, max_block = min(dri, total - m_first) * nb;
+    int16_t *const coef[3] = {c0, c1, c2};
+    const uint32_t limit = (uint32_t)(j + 1) * chunk_bits;
+    jd::ChunkOut co;
+    jd::SyncState s;
+    // round 0: every chunk starts from a guess
+    s.pos = (uint32_t)j * chunk_bits;
+    s.blk = 0;
+    s.k = 0;
+    exit_state[j] = jd::run_chunk<false>(hdr, tabs, nat, base, data_bits, s, limit, 0, 0x7fffffff, m_first, coef, co);
+    __syncthreads();
+    // rounds: start from what the chunk before left behind, until a round changes nothing
+    int started = 0;
+    for (int round = 0; round < T + 2; ++round) {
+        if (j == 0) {
+            s.pos = 0;
+            s.blk = 0;
+            s.k = 0;
+        } else {
+            s = exit_state[j - 1];
+        }
+        const jd::SyncState ns = jd::run_chunk<false>(hdr, tabs, nat, base, data_bits, s, limit, 0, 0x7fffffff, m_first, coef, co);
+        started = co.started;
+        const int changed = __syncthreads_or(!jd::same(ns, exit_state[j]));        // (also: everybody has read its entry state)
+        exit_state[j] = ns;
+        __syncthreads();
+        if (!changed) break;
+        if (round == T + 1 && j == 0) atomicAdd(not_converged, 1);
+    }
+    // index of the first block started in every chunk (T is small: one thread adds them up)
+    first_block[j] = started;
+    __syncthreads();
+    if (j == 0) {
+        int acc = 0;
+        for (int i = 0; i < T; ++i) {
+            const int n = first_block[i];
+            first_block[i] = acc;
+            acc += n;
+        }
+    }
+    __syncthreads();
+    // write pass: coefficients to their blocks, DC as differences
+    if (j == 0) {
+        s.pos = 0;
+        s.blk = 0;
+        s.k = 0;
+    } else {
+        s = exit_state[j - 1];
+    }
+    const int first = first_block[j];
+    jd::run_chunk<true>(hdr, tabs, nat, base, data_bits, s, limit, first, max_block, m_first, coef, co);
+    dc_off[j][0] = co.dc_sum[0];
+    dc_off[j][1] = co.dc_sum[1];
+    dc_off[j][2] = co.dc_sum[2];
+    __syncthreads();                           // (everybody has read its first_block)
+    first_block[j] = co.started;               // blocks actually written: they must add up to the interval's
+    __syncthreads();
+    if (j == 3 % T) {
+        int acc = 0;
+        for (int i = 0; i < T; ++i) acc += first_block[i];
+        if (acc != max_block) atomicAdd(not_converged, 1);
+    }
+    if (j < 3) {
+        int acc = 0;
+        for (int i = 0; i < T; ++i) {
+            const int n = dc_off[i][j];
+            dc_off[i][j] = acc;
+            acc += n;
+        }
+    }
+    __syncthreads();
+    // DC predictors of the blocks started in this chunk
+    int pred[3] = {dc_off[j][0], dc_off[j][1], dc_off[j][2]};
+    const int bw0 = jd::blocks_w(hdr, 0);
+    for (int bi = first; bi < first + co.started && bi < max_block; ++bi) {
+        const int sub = bi % nb, m = m_first + bi / nb, mx = m % hdr.mcus_x, my = m / hdr.mcus_x;
+        int16_t *cf;
+        int comp;
+        if (sub < nb - 2) {
+            comp = 0;
+            cf = c0 + 64 * ((size_t)(my * hdr.vs + sub / hdr.hs) * bw0 + (size_t)(mx * hdr.hs + sub % hdr.hs));
+        } else {
+            comp = sub - (nb - 2) + 1;
+            cf = (comp == 1 ? c1 : c2) + 64 * ((size_t)my * hdr.mcus_x + (size_t)mx);
+        }
+        pred[comp] += cf[0];
+        cf[0] = (int16_t)pred[comp];
+    }
+}
+
 // One thread per 8x8 block of any component: dequantise, inverse DCT, samples into the component's plane.
 __global__ void __launch_bounds__(128) jpeg_idct_kernel(const jd::Header *__restrict__ H, const int16_t *c0, const int16_t *c1, const int16_t *c2,
                                                        uint8_t *p0, uint8_t *p1, uint8_t *p2)
@@ -112,6 +227,8 @@ struct DevDec {
     size_t scan_cap = 0;
     uint32_t *h_offs = nullptr, *d_offs = nullptr;      // restart interval offsets
     int offs_cap = 0, n_intervals = 0;
+    uint32_t clean_bytes = 0;                           // stuffing-free scan data in h_scan
+    int *h_flag = nullptr, *d_flag = nullptr;           // != 0 after the launch: the chunks did not synchronise (never seen)
     int16_t *d_coef = nullptr;                          // the three components' coefficient blocks, one allocation
     size_t coef_bytes[3] = {0, 0, 0};
     uint8_t *d_planes = nullptr;                        // the three components' sample planes, one allocation
@@ -239,6 +356,8 @@ void jpeg_lanes_destroy(JpegCtx *c)
         cudaFree(l.dev.d_offs);
         cudaFree(l.dev.d_coef);
         cudaFree(l.dev.d_planes);
+        cudaFree(l.dev.d_flag);
+        cudaFreeHost(l.dev.h_flag);
         if (l.dec_stream) cudaStreamDestroy(l.dec_stream);
         if (l.dec_done) cudaEventDestroy(l.dec_done);
     }
@@ -278,14 +397,14 @@ void jpeg_lanes_create(bs_handle *h, JpegCtx *c)
                 JpegLane &l = c->lanes[(size_t)slot * n_cams + i];
                 const JpegPending &p = c->pending[slot];
                 if (p.use_dev) {
-                    // GPU entropy decoding: the host only locates the restart intervals and moves the scan data
-                    // into pinned memory (a memchr pass and a memcpy, ~0.5 ms per 4K frame)
+                    // GPU entropy decoding: the host only removes the byte stuffing and the restart markers while it
+                    // moves the scan data into pinned memory (memchr + memcpy, ~0.5 ms per 4K frame)
                     DevDec &d = l.dev;
                     const jd::Header &H = *d.h_hdr;
                     const uint8_t *scan = p.jpeg[i] + H.scan_off;
-                    d.n_intervals = jd::find_intervals(scan, H.scan_len, H, d.h_offs, d.offs_cap - 1);
+                    d.n_intervals = jd::unstuff_scan(scan, H.scan_len, H, d.h_scan, d.h_offs, d.offs_cap - 1);
                     if (d.n_intervals < 0) return -1;
-                    memcpy(d.h_scan, scan, H.scan_len);
+                    d.clean_bytes = d.h_offs[d.n_intervals];
                     return 0;
                 }
                 nvjpegStatus_t st = nvjpegJpegStreamParse(c->lib, p.jpeg[i], p.bytes[i], 0, 0, l.stream);
@@ -392,11 +511,7 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
     if (!jd::parse_header(jpeg, bytes, H) || H.w != h->sw[cam] || H.h != h->sh[cam]) return false;
     if (H.hs == 2 && (H.w < 3 || H.h < 3)) return false;                  // the up-sampling's edge cases need two chroma columns
     const long total = (long)H.mcus_x * H.mcus_y;
-    const int n_iv = (int)((total + H.dri - 1) / H.dri);
-    // One GPU thread per interval is a long serial chain (measured at 4K, 4:2:0, quality 90: one MCU row = 240 MCUs
-    // per interval still beats the host decoders, 166 against 104 panoramas/s); a large frame cut into a handful of
-    // intervals is better off with nvJPEG's host stage.
-    if (n_iv < 64 && total > 4096) return false;
+    const int n_iv = H.dri > 0 ? (int)((total + H.dri - 1) / H.dri) : 1;
     size_t cb[3], pb[3];
     for (int c = 0; c < 3; ++c) {
         const size_t blocks = (size_t)jd::blocks_w(H, c) * jd::blocks_h(H, c);
@@ -405,12 +520,17 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
     }
     cudaError_t e = cudaSuccess;
     if (!d.d_hdr) e = cudaMalloc(reinterpret_cast<void **>(&d.d_hdr), sizeof(jd::Header));
-    if (e == cudaSuccess && d.scan_cap < H.scan_len) {
+    if (e == cudaSuccess && !d.d_flag) {
+        e = cudaMalloc(reinterpret_cast<void **>(&d.d_flag), sizeof(int));
+        if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&d.h_flag), sizeof(int), cudaHostAllocDefault);
+        if (e == cudaSuccess) *d.h_flag = 0;
+    }
+    if (e == cudaSuccess && d.scan_cap < H.scan_len + 16) {
         BS_CUDA_QUIET(cudaStreamSynchronize(l.dec_stream));                  // the old buffers may still be in use
         cudaFreeHost(d.h_scan);
         cudaFree(d.d_scan);
         d.h_scan = d.d_scan = nullptr;
-        d.scan_cap = std::max<size_t>(2 * H.scan_len, 1u << 20);
+        d.scan_cap = std::max<size_t>(2 * H.scan_len + 16, 1u << 20);
         e = cudaHostAlloc(reinterpret_cast<void **>(&d.h_scan), d.scan_cap, cudaHostAllocDefault);
         if (e == cudaSuccess) e = cudaMalloc(reinterpret_cast<void **>(&d.d_scan), d.scan_cap);
         if (e != cudaSuccess) d.scan_cap = 0;
@@ -459,16 +579,24 @@ int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cuda
     DevDec &d = l.dev;
     const jd::Header &H = *d.h_hdr;
     BS_CUDA(h, cudaMemcpyAsync(d.d_hdr, d.h_hdr, sizeof(jd::Header), cudaMemcpyHostToDevice, st));
-    BS_CUDA(h, cudaMemcpyAsync(d.d_scan, d.h_scan, H.scan_len, cudaMemcpyHostToDevice, st));
+    BS_CUDA(h, cudaMemcpyAsync(d.d_scan, d.h_scan, (size_t)d.clean_bytes + 8, cudaMemcpyHostToDevice, st));
     BS_CUDA(h, cudaMemcpyAsync(d.d_offs, d.h_offs, sizeof(uint32_t) * (size_t)(d.n_intervals + 1), cudaMemcpyHostToDevice, st));
     BS_CUDA(h, cudaMemsetAsync(d.d_coef, 0, d.coef_bytes[0] + d.coef_bytes[1] + d.coef_bytes[2], st));
+    BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, sizeof(int), st));
     int16_t *c0 = d.d_coef, *c1 = c0 + d.coef_bytes[0] / 2, *c2 = c1 + d.coef_bytes[1] / 2;
     uint8_t *p0 = d.d_planes, *p1 = p0 + d.plane_bytes[0], *p2 = p1 + d.plane_bytes[1];
-    jpeg_entropy_kernel<<<(d.n_intervals + kEntropyWarps - 1) / kEntropyWarps, 32 * kEntropyWarps, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, d.n_intervals, c0, c1, c2);
+    // one block per interval, one thread per ~256 bytes of it (chunks that short still re-synchronise inside themselves)
+    const long total_mcus = (long)H.mcus_x * H.mcus_y;
+    const int dri = H.dri > 0 ? H.dri : (int)total_mcus;
+    const uint32_t avg = d.clean_bytes / (uint32_t)d.n_intervals + 1;
+    int T = (int)((avg / 256u + 31u) / 32u * 32u);
+    T = T < 32 ? 32 : (T > 1024 ? 1024 : T);
+    jpeg_entropy_sync_kernel<<<d.n_intervals, T, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, d.n_intervals, dri, c0, c1, c2, d.d_flag);
     const int n_blocks = (int)((d.plane_bytes[0] + d.plane_bytes[1] + d.plane_bytes[2]) / 64);
     jpeg_idct_kernel<<<(n_blocks + 127) / 128, 128, 0, st>>>(d.d_hdr, c0, c1, c2, p0, p1, p2);
     jpeg_color_kernel<<<dim3(((H.w + 3) / 4 + 255) / 256, H.h), 256, 0, st>>>(d.d_hdr, p0, p1, p2, d_frame, pitch);
     BS_CUDA(h, cudaGetLastError());
+    BS_CUDA(h, cudaMemcpyAsync(d.h_flag, d.d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
     h->kernel_launches += 3;
     return BS_OK;
 }
@@ -587,6 +715,15 @@ int issue_frame_jpeg(bs_handle *h, Slot &s, int slot_index, const uint8_t *const
 // bs_wait's part for a frame that leaves as a JPEG: fetch the bitstream (only it crosses the link).
 int retrieve_jpeg(bs_handle *h, Slot &s, int slot_index)
 {
+    if (h->jpeg && !h->jpeg->lanes.empty())
+        for (int i = 0; i < h->n_cams; ++i) {
+            DevDec &d = h->jpeg->lanes[(size_t)slot_index * h->n_cams + i].dev;
+            if (d.h_flag && *d.h_flag) {
+                *d.h_flag = 0;
+                s.jout = nullptr;
+                return fail(h, BS_ERR_CUDA, "bs_wait: the entropy-coded data of frame %d could not be decoded (damaged bitstream)", i);
+            }
+        }
     bs_jpeg_out *jout = s.jout;
     s.jout = nullptr;
     if (!jout) return BS_OK;
@@ -705,5 +842,5 @@ extern "C" int bs_submit_jpeg(bs_handle *h, const uint8_t *const *jpeg, const si
 extern "C" const char *bs_jpeg_backend(const bs_handle *h)
 {
     if (!h || !h->jpeg) return "";
-    return h->jpeg->last_use_dev ? "b200 (entropy decoding on the GPU, one thread per restart interval; libjpeg arithmetic)" : h->jpeg->backend;
+    return h->jpeg->last_use_dev ? "b200 (entropy decoding on the GPU in self-synchronising chunks; libjpeg arithmetic)" : h->jpeg->backend;
 }

@@ -176,7 +176,6 @@ inline bool parse_header(const uint8_t *d, size_t n, Header &H)
                 memcpy(H.quant[c], qt[comp_tq[c]], sizeof H.quant[c]);
             }
             if (s[7] != 0 || s[8] != 63 || s[9] != 0) return false;   // spectral selection / approximation of a sequential scan
-            if (H.dri < 1) return false;
             H.mcus_x = (H.w + 8 * H.hs - 1) / (8 * H.hs);
             H.mcus_y = (H.h + 8 * H.vs - 1) / (8 * H.vs);
             H.scan_off = i + 2 + len;
@@ -366,6 +365,282 @@ JD_HD void decode_interval(const Header &H, const HuffTable *tabs, const uint8_t
         decode_block(b, tabs[H.dc_tab[1]], tabs[2 + H.ac_tab[1]], pred1, coef[1] + cblk, nat);
         decode_block(b, tabs[H.dc_tab[2]], tabs[2 + H.ac_tab[2]], pred2, coef[2] + cblk, nat);
     }
+}
+
+// ============================================================================================================
+// Parallel entropy decoding INSIDE a restart interval (or inside a whole scan without restart markers).
+//
+// The host removes the byte stuffing (0xFF 0x00 -> 0xFF) and the restart markers while it copies the scan data
+// (unstuff_scan), so that a position in an interval is a plain bit offset.  An interval is cut into chunks of equal
+// size; the state of the decoder at a symbol boundary is (bit position, block within the MCU, zig-zag index).  Every
+// thread decodes ITS chunk starting from the exit state of the chunk before it -- a guess in the first round
+// (chunk start, block 0, index 0), the previous round's result afterwards -- and records the state in which it
+// leaves the chunk.  Chunk 0 starts from the truth, every exit state is a function of the entry state, so after
+// round r at least the first r chunks are right; Huffman streams re-synchronise quickly, so in practice every exit
+// state is right after two or three rounds, and a round in which nothing changed proves it (the fixed point is the
+// sequential decode).  Then: blocks started per chunk -> prefix sum -> every chunk knows the index of its first
+// block; one more pass writes the coefficients (DC as differences); DC predictors follow from a prefix sum of the
+// differences per component.  (Weissenberger & Schmidt's self-synchronising scheme, restated for this layout.)
+// ============================================================================================================
+struct SyncState {
+    uint32_t pos;        // bit offset in the interval's data
+    int16_t blk;         // block within the MCU whose coefficients come next (0 .. blocks per MCU - 1)
+    int16_t k;           // zig-zag index that comes next (0: the block's DC coefficient)
+};
+JD_HD bool same(const SyncState &a, const SyncState &b) { return a.pos == b.pos && a.blk == b.blk && a.k == b.k; }
+
+// Copies entropy-coded data without stuffing and markers; offs[i] = byte offset of interval i in `dst`
+// (n_intervals + 1 entries).  Returns the interval count, or -1 when the markers do not fit the header.
+// `dst` needs len + 16 bytes (8 bytes of zero padding are written behind the data).
+inline int unstuff_scan(const uint8_t *scan, size_t len, const Header &H, uint8_t *dst, uint32_t *offs, int max_intervals)
+{
+    const long total = (long)H.mcus_x * H.mcus_y;
+    const int want = H.dri > 0 ? (int)((total + H.dri - 1) / H.dri) : 1;
+    if (want > max_intervals) return -1;
+    int n = 0;
+    size_t o = 0;
+    offs[n++] = 0;
+    const uint8_t *p = scan, *end = scan + len;
+    while (p < end) {
+        const uint8_t *q = static_cast<const uint8_t *>(memchr(p, 0xFF, (size_t)(end - p)));
+        if (!q) q = end;
+        memcpy(dst + o, p, (size_t)(q - p));
+        o += (size_t)(q - p);
+        if (q + 1 >= end) break;
+        if (q[1] == 0x00) {
+            dst[o++] = 0xFF;
+            p = q + 2;
+        } else if (q[1] >= 0xD0 && q[1] <= 0xD7) {
+            if (n >= want || q[1] != 0xD0 + ((n - 1) & 7)) return -1;
+            offs[n++] = (uint32_t)o;
+            p = q + 2;
+        } else if (q[1] == 0xFF) {
+            p = q + 1;                                   // fill byte
+        } else {
+            break;                                       // any other marker ends the scan
+        }
+    }
+    if (n != want) return -1;
+    offs[n] = (uint32_t)o;
+    memset(dst + o, 0, 8);
+    return want;
+}
+
+// A bit reader over stuffing-free data: position = a bit offset.
+struct CleanReader {
+    const uint8_t *base;
+    uint32_t pos, end;       // bits
+    uint64_t buf;
+    int cnt;                 // valid bits in buf (the reader has consumed `pos` bits; buf holds the next cnt)
+};
+JD_HD void cr_init(CleanReader &b, const uint8_t *base, uint32_t pos, uint32_t end_bits)
+{
+    b.base = base;
+    b.pos = pos;
+    b.end = end_bits;
+    b.buf = 0;
+    b.cnt = 0;
+    // the first byte may be used from the middle: load it and drop the bits in front
+    const uint32_t byte = pos >> 3, off = pos & 7;
+    b.buf = (uint64_t)br_byte(base + byte) << 56;
+    b.buf <<= off;
+    b.cnt = 8 - (int)off;
+}
+JD_HD void cr_fill(CleanReader &b)      // data has 8 readable bytes behind its end
+{
+    uint32_t next = (b.pos + (uint32_t)b.cnt) >> 3;      // first byte not in the buffer
+    while (b.cnt <= 56) {
+        b.buf |= (uint64_t)br_byte(b.base + next) << (56 - b.cnt);
+        b.cnt += 8;
+        ++next;
+    }
+}
+JD_HD uint32_t cr_peek(const CleanReader &b, int n) { return (uint32_t)(b.buf >> (64 - n)); }
+JD_HD void cr_skip(CleanReader &b, int n)
+{
+    b.buf <<= n;
+    b.cnt -= n;
+    b.pos += (uint32_t)n;
+}
+
+// What a pass over a chunk does besides following the symbols.
+struct ChunkOut {
+    int started;             // blocks whose DC symbol lies in the chunk
+    int dc_sum[3];           // write pass: sum of the DC differences per component of the blocks started here
+};
+
+// Decodes from state `s` up to the first symbol boundary at or behind bit `limit` (or the end of the data, or block
+// `max_block` of the interval).  kWrite: coefficients go to their blocks (DC as a difference); `first_block` = index,
+// within the interval, of the first block STARTED in this chunk (the block in progress at entry is first_block - 1).
+template <bool kWrite>
+JD_HD SyncState run_chunk(const Header &H, const HuffTable *tabs, const uint8_t *nat, const uint8_t *data, uint32_t data_bits, SyncState s,
+                          uint32_t limit, int first_block, int max_block, int m_first, int16_t *const coef[3], ChunkOut &out)
+{
+    const int nb = H.hs * H.vs + 2;
+    out.started = 0;
+    out.dc_sum[0] = out.dc_sum[1] = out.dc_sum[2] = 0;
+    if (s.pos >= limit || s.pos >= data_bits) return s;
+    CleanReader b;
+    cr_init(b, data, s.pos, data_bits);
+    int blk = s.blk, k = s.k;
+    int block_index = first_block - 1;          // of the block in progress
+    int16_t *cf = nullptr;
+    const int bw0 = blocks_w(H, 0);
+    auto block_ptr = [&](int bi, int sub) -> int16_t * {
+        const int m = m_first + bi / nb, mx = m % H.mcus_x, my = m / H.mcus_x;
+        if (sub < nb - 2) {
+            const int u = sub % H.hs, v = sub / H.hs;
+            return coef[0] + 64 * ((size_t)(my * H.vs + v) * bw0 + (size_t)(mx * H.hs + u));
+        }
+        return coef[sub - (nb - 2) + 1] + 64 * ((size_t)my * H.mcus_x + (size_t)mx);
+    };
+    if (kWrite && k > 0 && block_index >= 0 && block_index < max_block) cf = block_ptr(block_index, blk);
+    while (b.pos < limit && b.pos < data_bits) {
+        const int comp = blk < nb - 2 ? 0 : blk - (nb - 2) + 1;
+        if (b.cnt < 32) cr_fill(b);
+        if (k == 0) {                                          // DC
+            if (first_block + out.started >= max_block) break; // the interval's blocks are all there (padding bits follow)
+            const HuffTable &t = tabs[H.dc_tab[comp]];
+            const uint32_t e = t.look[cr_peek(b, 9)];
+            int sym, len;
+            if (e) {
+                len = (int)(e >> 8);
+                sym = (int)(e & 0xFF);
+            } else {
+                const uint32_t c16 = cr_peek(b, 16);
+                len = 10;
+                while (len <= 16 && (int)(c16 >> (16 - len)) > t.maxcode[len]) ++len;
+                sym = len <= 16 ? t.vals[((int)(c16 >> (16 - len)) + t.valoff[len]) & 0xFF] : 0;
+                if (len > 16) len = 16;
+            }
+            cr_skip(b, len);
+            sym &= 15;
+            int diff = 0;
+            if (sym) {
+                const int v = (int)cr_peek(b, sym);
+                cr_skip(b, sym);
+                diff = v < (1 << (sym - 1)) ? v - (1 << sym) + 1 : v;
+            }
+            block_index = first_block + out.started;
+            ++out.started;
+            if (kWrite) {
+                cf = block_ptr(block_index, blk);
+                cf[0] = (int16_t)diff;
+                out.dc_sum[comp] += diff;
+            }
+            k = 1;
+            continue;
+        }
+        const HuffTable &t = tabs[2 + H.ac_tab[comp]];
+        const int f = t.fast[cr_peek(b, 9)];
+        if (f) {
+            k += (f >> 4) & 15;
+            cr_skip(b, f & 15);
+            if (kWrite && cf && k < 64) cf[nat[k]] = (int16_t)(f >> 8);
+            ++k;
+        } else {
+            const uint32_t e = t.look[cr_peek(b, 9)];
+            int sym, len;
+            if (e) {
+                len = (int)(e >> 8);
+                sym = (int)(e & 0xFF);
+            } else {
+                const uint32_t c16 = cr_peek(b, 16);
+                len = 10;
+                while (len <= 16 && (int)(c16 >> (16 - len)) > t.maxcode[len]) ++len;
+                sym = len <= 16 ? t.vals[((int)(c16 >> (16 - len)) + t.valoff[len]) & 0xFF] : 0;
+                if (len > 16) len = 16;
+            }
+            cr_skip(b, len);
+            const int r = sym >> 4, sz = sym & 15;
+            if (sz) {
+                k += r;
+                const int v = (int)cr_peek(b, sz);
+                cr_skip(b, sz);
+                if (kWrite && cf && k < 64) cf[nat[k]] = (int16_t)(v < (1 << (sz - 1)) ? v - (1 << sz) + 1 : v);
+                ++k;
+            } else if (r == 15) {
+                k += 16;
+            } else {
+                k = 64;                                        // end of block
+            }
+        }
+        if (k >= 64) {
+            k = 0;
+            blk = blk + 1 == nb ? 0 : blk + 1;
+            cf = nullptr;
+        }
+    }
+    SyncState o;
+    o.pos = b.pos;
+    o.blk = (int16_t)blk;
+    o.k = (int16_t)k;
+    return o;
+}
+
+// Host model of the kernel (one "thread" after the other): decodes interval [m_first, m_first + n_mcus) from `data`
+// with `T` chunks.  Used by the CPU check; the kernel in stitch_jpeg.inl has the same steps with barriers in between.
+inline int decode_interval_chunked_host(const Header &H, const HuffTable *tabs, const uint8_t *nat, const uint8_t *data, uint32_t bytes, int T,
+                                        int m_first, int n_mcus, int16_t *const coef[3])
+{
+    const int nb = H.hs * H.vs + 2, max_block = n_mcus * nb;
+    const uint32_t data_bits = bytes * 8u;
+    uint32_t chunk_bits = ((data_bits + (uint32_t)T - 1) / (uint32_t)T + 7u) & ~7u;
+    if (chunk_bits < 64) chunk_bits = 64;
+    SyncState *exit_state = new SyncState[T], *next_state = new SyncState[T];
+    int *started = new int[T];
+    ChunkOut co;
+    for (int j = 0; j < T; ++j) {                 // round 0: guesses
+        SyncState s;
+        s.pos = (uint32_t)j * chunk_bits;
+        s.blk = 0;
+        s.k = 0;
+        exit_state[j] = run_chunk<false>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, m_first, coef, co);
+    }
+    int rounds = 1;
+    for (;; ++rounds) {
+        bool changed = false;
+        for (int j = 0; j < T; ++j) {
+            SyncState s;
+            if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
+            next_state[j] = run_chunk<false>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, m_first, coef, co);
+            started[j] = co.started;
+            changed = changed || !same(next_state[j], exit_state[j]);
+        }
+        for (int j = 0; j < T; ++j) exit_state[j] = next_state[j];
+        if (!changed) break;
+        if (rounds > T + 2) break;
+    }
+    int first = 0;
+    int dc_off[3] = {0, 0, 0};
+    for (int j = 0; j < T; ++j) {                 // write pass + DC prefix (sequential here)
+        SyncState s;
+        if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
+        run_chunk<true>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, first, max_block, m_first, coef, co);
+        // DC predictors of the blocks started in this chunk
+        int pred[3] = {dc_off[0], dc_off[1], dc_off[2]};
+        const int bw0 = blocks_w(H, 0);
+        for (int bi = first; bi < first + co.started && bi < max_block; ++bi) {
+            const int sub = bi % nb, m = m_first + bi / nb, mx = m % H.mcus_x, my = m / H.mcus_x;
+            int16_t *cf;
+            int comp;
+            if (sub < nb - 2) {
+                comp = 0;
+                cf = coef[0] + 64 * ((size_t)(my * H.vs + sub / H.hs) * bw0 + (size_t)(mx * H.hs + sub % H.hs));
+            } else {
+                comp = sub - (nb - 2) + 1;
+                cf = coef[comp] + 64 * ((size_t)my * H.mcus_x + (size_t)mx);
+            }
+            pred[comp] += cf[0];
+            cf[0] = (int16_t)pred[comp];
+        }
+        for (int c = 0; c < 3; ++c) dc_off[c] += co.dc_sum[c];
+        first += co.started;
+    }
+    delete[] exit_state;
+    delete[] next_state;
+    delete[] started;
+    return first == max_block ? rounds : -rounds;
 }
 
 // ---- inverse DCT: libjpeg's jpeg_idct_islow (jidctint.c), 13-bit constants, two passes -----------------------

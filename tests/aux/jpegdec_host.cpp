@@ -2,7 +2,9 @@
 // way the GPU kernels do, block by block and pixel by pixel, and writes raw BGR.  Test infrastructure: lets
 // tests/test_jpegdec.py pin the decoder's arithmetic against cv2.imdecode without a GPU.
 // usage: jpegdec_host in.jpg out.bgr   (prints "w h hs vs dri intervals", exit 2 = not a file this decoder takes)
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 #include "../../image-stitching_b200/csrc/stitch_jpegdec.cuh"
@@ -18,10 +20,9 @@ int main(int argc, char **argv)
     jd::Header H;
     if (!jd::parse_header(d.data(), d.size(), H)) return 2;
     const long total = (long)H.mcus_x * H.mcus_y;
-    const int max_iv = (int)((total + H.dri - 1) / H.dri);
+    const int chunks = argc > 3 ? atoi(argv[3]) : 0;        // 0: one thread per restart interval; T > 0: T chunks per interval
+    const int max_iv = H.dri > 0 ? (int)((total + H.dri - 1) / H.dri) : 1;
     std::vector<uint32_t> offs(max_iv + 1);
-    const int n_iv = jd::find_intervals(d.data() + H.scan_off, H.scan_len, H, offs.data(), max_iv);
-    if (n_iv < 0) return 2;
     std::vector<int16_t> coef[3];
     int16_t *cp[3];
     for (int c = 0; c < 3; ++c) {
@@ -29,7 +30,24 @@ int main(int argc, char **argv)
         cp[c] = coef[c].data();
     }
     const jd::HuffTable tabs[4] = {H.dc[0], H.dc[1], H.ac[0], H.ac[1]};
-    for (int r = 0; r < n_iv; ++r) jd::decode_interval(H, tabs, jd::kNaturalHost, d.data() + H.scan_off, offs.data(), r, cp);
+    int n_iv = 0, worst_rounds = 0;
+    if (chunks > 0) {
+        std::vector<uint8_t> clean(H.scan_len + 16);
+        n_iv = jd::unstuff_scan(d.data() + H.scan_off, H.scan_len, H, clean.data(), offs.data(), max_iv);
+        if (n_iv < 0) return 2;
+        const int dri = H.dri > 0 ? H.dri : (int)total;
+        for (int r = 0; r < n_iv; ++r) {
+            const int m0 = r * dri, n_mcus = (int)std::min<long>(dri, total - m0);
+            const int rounds = jd::decode_interval_chunked_host(H, tabs, jd::kNaturalHost, clean.data() + offs[r], offs[r + 1] - offs[r], chunks, m0, n_mcus, cp);
+            if (rounds < 0) { fprintf(stderr, "interval %d: block count mismatch after %d rounds\n", r, -rounds); return 3; }
+            worst_rounds = std::max(worst_rounds, rounds);
+        }
+    } else {
+        if (H.dri < 1) return 2;
+        n_iv = jd::find_intervals(d.data() + H.scan_off, H.scan_len, H, offs.data(), max_iv);
+        if (n_iv < 0) return 2;
+        for (int r = 0; r < n_iv; ++r) jd::decode_interval(H, tabs, jd::kNaturalHost, d.data() + H.scan_off, offs.data(), r, cp);
+    }
     std::vector<uint8_t> plane[3];
     size_t pitch[3];
     for (int c = 0; c < 3; ++c) {
@@ -63,6 +81,6 @@ int main(int argc, char **argv)
     if (!f) return 1;
     fwrite(out.data(), 1, out.size(), f);
     fclose(f);
-    printf("%d %d %d %d %d %d\n", H.w, H.h, H.hs, H.vs, H.dri, n_iv);
+    printf("%d %d %d %d %d %d %d\n", H.w, H.h, H.hs, H.vs, H.dri, n_iv, worst_rounds);
     return 0;
 }

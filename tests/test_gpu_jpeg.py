@@ -93,9 +93,10 @@ def test_compressed_panorama_out_and_errors():
 
 
 def test_decoders_agree():
-    """The worker-thread decoder (cameras' entropy stages in parallel), the one-thread decoders behind it
-    (BS_DEBUG_JPEG_THREADS=0, in a child process: the switch is read once) and a damaged bitstream that only shows up
-    in the entropy stage (worker thread -> fall-back -> error) all leave the handle usable and give the same pixels."""
+    """The library's own GPU decoder gives cv2's pixels; nvJPEG behind it (BS_DEBUG_JPEG_NO_GPU_ENTROPY: entropy stages
+    on worker threads; additionally BS_DEBUG_JPEG_THREADS=0: nvJPEG's one-call decoders on the calling thread -- child
+    processes, the switches are read once) gives the same pixels either way; a damaged bitstream leaves the handle
+    usable."""
     import hashlib
     import subprocess
     import sys
@@ -106,7 +107,8 @@ def test_decoders_agree():
     out = np.empty((canvas_wh[1], canvas_wh[0], 3), np.uint8)
     with p.Stitcher(whs, canvas_wh, H) as st:
         st.wait(st.submit_jpeg(jpgs, out))
-        assert "worker threads" in st.jpeg_backend()
+        assert st.jpeg_backend().startswith("b200")
+        assert np.array_equal(out, oracle.stitch(cv2_dec, H, canvas_wh)), "JPEG in = the reference's imread + warpPerspective"
         want = hashlib.sha256(out.tobytes()).hexdigest()
         broken = bytearray(jpgs[1])
         broken[len(broken) // 2:len(broken) // 2 + 4096] = b"\xff\x00" * 2048      # header intact, scan data destroyed
@@ -121,11 +123,13 @@ def test_decoders_agree():
             "whs = [(d.shape[1], d.shape[0]) for d in dec]; out = np.empty((cwh[1], cwh[0], 3), np.uint8);"
             "st = p.Stitcher(whs, cwh, H); st.wait(st.submit_jpeg(jpgs, out));"
             "print(json.dumps({'sha': hashlib.sha256(out.tobytes()).hexdigest(), 'backend': st.jpeg_backend()}))") % (ROOT, ROOT)
-    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300,
-                       env=dict(os.environ, BS_DEBUG_JPEG_THREADS="0"))
-    assert r.returncode == 0, r.stderr[-2000:]
-    got = json.loads(r.stdout.strip().splitlines()[-1])
-    assert "worker threads" not in got["backend"] and got["sha"] == want
+    got = []
+    for extra in ({"BS_DEBUG_JPEG_NO_GPU_ENTROPY": "1"}, {"BS_DEBUG_JPEG_NO_GPU_ENTROPY": "1", "BS_DEBUG_JPEG_THREADS": "0"}):
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300, env=dict(os.environ, **extra))
+        assert r.returncode == 0, r.stderr[-2000:]
+        got.append(json.loads(r.stdout.strip().splitlines()[-1]))
+    assert "worker threads" in got[0]["backend"] and "worker threads" not in got[1]["backend"] and not got[1]["backend"].startswith("b200")
+    assert got[0]["sha"] == got[1]["sha"]
 
 
 def test_compressed_and_raw_submits_interleave_in_ticket_order():

@@ -19,7 +19,7 @@ cv2 = pytest.importorskip("cv2")
 
 
 def encode(img, quality=90, rst=4, sampling=None):
-    args = [cv2.IMWRITE_JPEG_QUALITY, quality, cv2.IMWRITE_JPEG_RST_INTERVAL, rst]
+    args = [cv2.IMWRITE_JPEG_QUALITY, quality] + ([cv2.IMWRITE_JPEG_RST_INTERVAL, rst] if rst else [])
     if sampling is not None:
         args += [cv2.IMWRITE_JPEG_SAMPLING_FACTOR, sampling]
     ok, enc = cv2.imencode(".jpg", img, args)
@@ -43,10 +43,12 @@ def host_decoder(tmp_path_factory):
     return str(exe)
 
 
-def host_decode(exe, bits, tmp_path):
+def host_decode(exe, bits, tmp_path, chunks=0):
+    """chunks = 0: one thread per restart interval; T > 0: the chunked, self-synchronising decoder with T chunks per
+    interval (what the kernel runs; files without restart markers are one interval)."""
     src, dst = tmp_path / "in.jpg", tmp_path / "out.bgr"
     src.write_bytes(bits)
-    r = subprocess.run([exe, str(src), str(dst)], capture_output=True, text=True)
+    r = subprocess.run([exe, str(src), str(dst)] + ([str(chunks)] if chunks else []), capture_output=True, text=True)
     if r.returncode != 0:
         return r.returncode, None
     w, h = [int(v) for v in r.stdout.split()[:2]]
@@ -63,6 +65,20 @@ def test_host_build_of_the_decoder_equals_cv2(host_decoder, tmp_path, name, qual
     assert np.array_equal(got, cv2.imdecode(np.frombuffer(bits, np.uint8), cv2.IMREAD_COLOR))
 
 
+@pytest.mark.parametrize("chunks", [1, 3, 16, 200])
+@pytest.mark.parametrize("rst", [0, 6, 1000])
+def test_chunked_decoder_equals_cv2(host_decoder, tmp_path, chunks, rst):
+    """The self-synchronising form: chunks start from guesses and converge to the sequential decode, with and without
+    restart markers, from one chunk (sequential) to chunks too short to synchronise inside themselves."""
+    for name in ("smooth", "noise", "tiny"):
+        img = pictures()[name]
+        args = [cv2.IMWRITE_JPEG_QUALITY, 85] + ([cv2.IMWRITE_JPEG_RST_INTERVAL, rst] if rst else [])
+        bits = cv2.imencode(".jpg", img, args)[1].tobytes()
+        rc, got = host_decode(host_decoder, bits, tmp_path, chunks)
+        assert rc == 0, name
+        assert np.array_equal(got, cv2.imdecode(np.frombuffer(bits, np.uint8), cv2.IMREAD_COLOR)), name
+
+
 def test_444_and_refusals(host_decoder, tmp_path):
     img = pictures()["smooth"]
     try:
@@ -71,12 +87,11 @@ def test_444_and_refusals(host_decoder, tmp_path):
         pytest.skip("this cv2 cannot choose the sampling factor")
     rc, got = host_decode(host_decoder, bits, tmp_path)
     assert rc == 0 and np.array_equal(got, cv2.imdecode(np.frombuffer(bits, np.uint8), cv2.IMREAD_COLOR))
-    # no restart interval, progressive, grey: not for this decoder (bs_submit_jpeg then uses nvJPEG)
-    plain = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 90])[1].tobytes()
+    # progressive, grey: not for this decoder (bs_submit_jpeg then uses nvJPEG)
     prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1, cv2.IMWRITE_JPEG_RST_INTERVAL, 4])[1].tobytes()
     grey = cv2.imencode(".jpg", img[:, :, 0], [cv2.IMWRITE_JPEG_RST_INTERVAL, 4])[1].tobytes()
-    for bits in (plain, prog, grey, b"\xff\xd8 garbage"):
-        assert host_decode(host_decoder, bits, tmp_path)[0] == 2
+    for bits in (prog, grey, b"\xff\xd8 garbage"):
+        assert host_decode(host_decoder, bits, tmp_path, 8)[0] == 2
 
 
 @pytest.mark.gpu
@@ -87,13 +102,13 @@ def test_gpu_decoder_gives_cv2_pixels_and_the_reference_panorama():
     frames = [cv2.GaussianBlur(rng.integers(0, 256, (sh, sw, 3), dtype=np.uint8), (0, 0), 1.5 + i) for i in range(3)]
     Hs = [np.array([[1.01, 0.004 * i, 5.0 + 560 * i], [-0.003, 0.99, 3.0 + i], [1e-6 * (i - 1), 0, 1.0]]) for i in range(3)]
     canvas = (1800, 380)
-    for rst in (40, 3, 2000):                      # one MCU row, tiny intervals, one interval for the whole frame
+    for rst in (40, 3, 2000, 0):                   # one MCU row, tiny intervals, one interval for the whole frame, no markers
         bits = [encode(f, 88, rst) for f in frames]
         ref = [cv2.imdecode(np.frombuffer(b, np.uint8), cv2.IMREAD_COLOR) for b in bits]
         with p.Stitcher([(sw, sh)], (sw, sh), [np.eye(3)]) as st:      # identity warp: the decoded frame itself
             out = np.empty((sh, sw, 3), np.uint8)
             st.wait(st.submit_jpeg([bits[0]], out))
-            assert "restart interval" in st.jpeg_backend()
+            assert st.jpeg_backend().startswith("b200")
             assert np.array_equal(out, ref[0]), f"rst {rst}: {(out != ref[0]).any(axis=2).sum()} pixels differ from cv2.imdecode"
         want = oracle.stitch(ref, Hs, canvas)      # what the reference computes: imread, then warpPerspective per camera
         with p.Stitcher([(sw, sh)] * 3, canvas, Hs) as st:
@@ -116,16 +131,17 @@ def test_gpu_decoder_odd_sizes_444_and_mixed_streams():
             variants.append(encode(img, 95, 2, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_444))
         except AttributeError:
             pass
-        plain = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 90])[1].tobytes()      # no restart interval: nvJPEG
+        plain = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_QUALITY, 90])[1].tobytes()      # no restart markers: one interval
+        prog = cv2.imencode(".jpg", img, [cv2.IMWRITE_JPEG_PROGRESSIVE, 1])[1].tobytes()    # progressive: nvJPEG
         with p.Stitcher([(w, h)], (w, h), [np.eye(3)]) as st:
             out = np.empty((h, w, 3), np.uint8)
-            for bits in variants + [plain] + variants[:1]:
+            for bits in variants + [plain, prog] + variants[:1]:
                 st.wait(st.submit_jpeg([bits], out))
                 ref = cv2.imdecode(np.frombuffer(bits, np.uint8), cv2.IMREAD_COLOR)
-                if bits is plain:
-                    assert "restart interval" not in st.jpeg_backend()
+                if bits is prog:
+                    assert not st.jpeg_backend().startswith("b200")
                     mse = float(((out.astype(float) - ref.astype(float)) ** 2).mean())      # nvJPEG: another decoder
                     assert 10 * np.log10(255.0 ** 2 / max(mse, 1e-9)) > 30.0
                 else:
-                    assert "restart interval" in st.jpeg_backend()
+                    assert st.jpeg_backend().startswith("b200")
                     assert np.array_equal(out, ref)

@@ -23,146 +23,148 @@ namespace {
 // ~20 ms for a 4K frame.  The cameras of one frame are independent, so bs_submit_jpeg runs their host stages on
 // a few worker threads of its own (nvJPEG's decoupled API: parse + nvjpegDecodeJpegHost per camera in parallel,
 // then transfer + device stage on the upload stream in camera order).
-// ---- entropy decoding on the GPU for JPEGs with a restart interval (stitch_jpegdec.cuh) ---------------------------
-// One thread per restart interval: Huffman-decodes its MCUs into the components' coefficient blocks.
-constexpr int kEntropyWarps = 4;      // restart intervals per block: one per warp (see below)
-__global__ void __launch_bounds__(32 * kEntropyWarps) jpeg_entropy_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ scan,
-                                                         const uint32_t *__restrict__ offs, int n_intervals, int16_t *c0, int16_t *c1,
-                                                         int16_t *c2)
+// ---- the repo's own JPEG decoder on the GPU (stitch_jpegdec.cuh) ---------------------------------------------------
+// The chunked, self-synchronising form (stitch_jpegdec.cuh).  Every restart interval (a marker-less scan is one
+// interval) is cut into `T` chunks of its stuffing-free data; one thread per chunk, grid = (T / 128, intervals).
+// A ROUND is one launch: every chunk decodes from the state the chunk before it left in the previous round.
+struct ChunkRec {
+    jd::SyncState st[2];     // exit state of the chunk in even / odd rounds
+    int started;             // blocks started in the chunk (last round); after jpeg_scan_kernel: index of its first block
+    int dc_sum[3];           // DC differences of those blocks per component; after the scan: predictors at the chunk's entry
+    int moved[2];            // the exit state changed in the last even / odd round
+};
+constexpr int kSyncThreads = 128;
+struct SyncShared {
+    jd::Header hdr;
+    uint8_t nat[64];
+};
+__device__ __forceinline__ void sync_load_tables(SyncShared &sh, const jd::Header *H)
 {
-    // the tables every symbol goes through live in shared memory: a thread is one long dependent chain of look-ups
-    __shared__ jd::Header hdr;
-    __shared__ uint8_t nat[64];
-    {
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(H);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(&hdr);
-        for (int i = (int)threadIdx.x; i < (int)(sizeof(jd::Header) / 4); i += (int)blockDim.x) dst[i] = src[i];
-        for (int i = (int)threadIdx.x; i < 64; i += (int)blockDim.x) nat[i] = (uint8_t)jd::natural(i);
-    }
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(H);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(&sh.hdr);
+    for (int i = (int)threadIdx.x; i < (int)(sizeof(jd::Header) / 4); i += (int)blockDim.x) dst[i] = src[i];
+    for (int i = (int)threadIdx.x; i < 64; i += (int)blockDim.x) sh.nat[i] = (uint8_t)jd::natural(i);
     __syncthreads();
-    const jd::HuffTable *tabs = hdr.dc;       // dc[0], dc[1], ac[0], ac[1] are adjacent members
-    static_assert(offsetof(jd::Header, ac) == offsetof(jd::Header, dc) + 2 * sizeof(jd::HuffTable), "table layout");
-    // ONE interval per warp, decoded by its first lane: 32 intervals in the lanes of one warp diverge at every symbol
-    // (measured: 6.5 of 32 lanes active per instruction), which costs more than the idle lanes do -- there are far
-    // more warp slots on the GPU than restart intervals in a frame.
-    const int r = (int)(blockIdx.x * kEntropyWarps + (threadIdx.x >> 5));
-    if (r >= n_intervals || (threadIdx.x & 31) != 0) return;
-    int16_t *const coef[3] = {c0, c1, c2};
-    jd::decode_interval(hdr, tabs, nat, scan, offs, r, coef);
 }
-// The chunked, self-synchronising form (stitch_jpegdec.cuh): ONE BLOCK per restart interval (or per whole scan when
-// the file has no restart markers), one thread per chunk of the interval's stuffing-free data.
-__global__ void __launch_bounds__(1024) jpeg_entropy_sync_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ data,
-                                                                const uint32_t *__restrict__ offs, int n_intervals, int dri, int16_t *c0,
-                                                                int16_t *c1, int16_t *c2, int *__restrict__ not_converged)
+__device__ __forceinline__ uint32_t sync_chunk_bits(uint32_t data_bits, int T)
 {
-    __shared__ jd::Header hdr;
-    __shared__ uint8_t nat[64];
-    __shared__ jd::SyncState exit_state[1024];
-    __shared__ int first_block[1024];
-    __shared__ int dc_off[1024][3];
-    const int T = (int)blockDim.x, j = (int)threadIdx.x, r = (int)blockIdx.x;
-    {
-        const uint32_t *src = reinterpret_cast<const uint32_t *>(H);
-        uint32_t *dst = reinterpret_cast<uint32_t *>(&hdr);
-        for (int i = j; i < (int)(sizeof(jd::Header) / 4); i += T) dst[i] = src[i];
-        for (int i = j; i < 64; i += T) nat[i] = (uint8_t)jd::natural(i);
-    }
-    __syncthreads();
-    const jd::HuffTable *tabs = hdr.dc;
+    const uint32_t c = ((data_bits + (uint32_t)T - 1) / (uint32_t)T + 7u) & ~7u;
+    return c < 64u ? 64u : c;
+}
+// round 0: guesses (chunk start, block 0, index 0).  round r > 0: from the exit states of round r - 1; `changed` counts
+// the chunks whose exit state moved.
+__global__ void __launch_bounds__(kSyncThreads) jpeg_sync_round_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ data,
+                                                                      const uint32_t *__restrict__ offs, int T, int round, ChunkRec *recs,
+                                                                      int *changed)
+{
+    __shared__ SyncShared sh;
+    sync_load_tables(sh, H);
+    const int j = (int)(blockIdx.x * blockDim.x + threadIdx.x), r = (int)blockIdx.y;
+    if (j >= T) return;
     const uint8_t *base = data + offs[r];
-    const uint32_t data_bits = (offs[r + 1] - offs[r]) * 8u;
-    uint32_t chunk_bits = ((data_bits + (uint32_t)T - 1) / (uint32_t)T + 7u) & ~7u;
-    if (chunk_bits < 64u) chunk_bits = 64u;
-    const int total = hdr.mcus_x * hdr.mcus_y, m_first = r * dri;
-    const int nb = hdr.hs * hdr.vs + 2, max_block = min(dri, total - m_first) * nb;
-    int16_t *const coef[3] = {c0, c1, c2};
-    const uint32_t limit = (uint32_t)(j + 1) * chunk_bits;
-    jd::ChunkOut co;
+    const uint32_t data_bits = (offs[r + 1] - offs[r]) * 8u, chunk_bits = sync_chunk_bits(data_bits, T);
+    ChunkRec *rec = recs + (size_t)r * T;
     jd::SyncState s;
-    // round 0: every chunk starts from a guess
-    s.pos = (uint32_t)j * chunk_bits;
-    s.blk = 0;
-    s.k = 0;
-    exit_state[j] = jd::run_chunk<false>(hdr, tabs, nat, base, data_bits, s, limit, 0, 0x7fffffff, m_first, coef, co);
-    __syncthreads();
-    // rounds: start from what the chunk before left behind, until a round changes nothing
-    int started = 0;
-    for (int round = 0; round < T + 2; ++round) {
-        if (j == 0) {
-            s.pos = 0;
-            s.blk = 0;
-            s.k = 0;
-        } else {
-            s = exit_state[j - 1];
-        }
-        const jd::SyncState ns = jd::run_chunk<false>(hdr, tabs, nat, base, data_bits, s, limit, 0, 0x7fffffff, m_first, coef, co);
-        started = co.started;
-        const int changed = __syncthreads_or(!jd::same(ns, exit_state[j]));        // (also: everybody has read its entry state)
-        exit_state[j] = ns;
-        __syncthreads();
-        if (!changed) break;
-        if (round == T + 1 && j == 0) atomicAdd(not_converged, 1);
+    if (round == 0 || j == 0) {
+        s.pos = round == 0 ? (uint32_t)j * chunk_bits : 0u;
+        s.blk = 0;
+        s.k = 0;
+    } else {
+        s = rec[j - 1].st[(round - 1) & 1];
     }
-    // index of the first block started in every chunk (T is small: one thread adds them up)
-    first_block[j] = started;
+    // a chunk whose entry state did not move in the previous round leaves as it did: later rounds cost almost nothing
+    // once the stream has settled, so there can be plenty of them
+    if (round >= 2 && (j == 0 || !rec[j - 1].moved[(round - 1) & 1])) {
+        rec[j].st[round & 1] = rec[j].st[(round - 1) & 1];
+        rec[j].moved[round & 1] = 0;
+        return;
+    }
+    jd::ChunkOut co;
+    int16_t *const none[3] = {nullptr, nullptr, nullptr};
+    const jd::SyncState ns = jd::run_chunk<false>(sh.hdr, sh.hdr.dc, sh.nat, base, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, 0, none, co);
+    const int moved = round == 0 || !jd::same(ns, rec[j].st[(round - 1) & 1]);
+    if (round > 0 && moved) atomicAdd(changed, 1);
+    rec[j].moved[round & 1] = moved;
+    rec[j].st[round & 1] = ns;
+    rec[j].started = co.started;
+    rec[j].dc_sum[0] = co.dc_sum[0];
+    rec[j].dc_sum[1] = co.dc_sum[1];
+    rec[j].dc_sum[2] = co.dc_sum[2];
+}
+// Exclusive prefix sums over the chunks of every interval (one block per interval): started -> first block index,
+// dc_sum -> DC predictors at the chunk's entry.
+__global__ void __launch_bounds__(256) jpeg_scan_kernel(ChunkRec *recs, int T)
+{
+    __shared__ int part[256][4];
+    ChunkRec *rec = recs + (size_t)blockIdx.x * T;
+    const int t = (int)threadIdx.x, per = (T + 255) / 256, lo = min(T, t * per), hi = min(T, lo + per);
+    int acc[4] = {0, 0, 0, 0};
+    for (int i = lo; i < hi; ++i) {
+        acc[0] += rec[i].started;
+        acc[1] += rec[i].dc_sum[0];
+        acc[2] += rec[i].dc_sum[1];
+        acc[3] += rec[i].dc_sum[2];
+    }
+    for (int q = 0; q < 4; ++q) part[t][q] = acc[q];
     __syncthreads();
-    if (j == 0) {
-        int acc = 0;
-        for (int i = 0; i < T; ++i) {
-            const int n = first_block[i];
-            first_block[i] = acc;
-            acc += n;
+    if (t < 4) {
+        int run = 0;
+        for (int i = 0; i < 256; ++i) {
+            const int v = part[i][t];
+            part[i][t] = run;
+            run += v;
         }
     }
     __syncthreads();
-    // write pass: coefficients to their blocks, DC as differences
+    for (int q = 0; q < 4; ++q) acc[q] = part[t][q];
+    for (int i = lo; i < hi; ++i) {
+        const int v0 = rec[i].started, v1 = rec[i].dc_sum[0], v2 = rec[i].dc_sum[1], v3 = rec[i].dc_sum[2];
+        rec[i].started = acc[0];
+        rec[i].dc_sum[0] = acc[1];
+        rec[i].dc_sum[1] = acc[2];
+        rec[i].dc_sum[2] = acc[3];
+        acc[0] += v0;
+        acc[1] += v1;
+        acc[2] += v2;
+        acc[3] += v3;
+    }
+}
+// The write pass: every chunk decodes once more from its (now final) entry state, coefficients to their blocks.
+__global__ void __launch_bounds__(kSyncThreads) jpeg_sync_write_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ data,
+                                                                      const uint32_t *__restrict__ offs, int T, int final_round, int dri,
+                                                                      const ChunkRec *__restrict__ recs, int16_t *c0, int16_t *c1, int16_t *c2,
+                                                                      int *written)
+{
+    __shared__ SyncShared sh;
+    sync_load_tables(sh, H);
+    const int j = (int)(blockIdx.x * blockDim.x + threadIdx.x), r = (int)blockIdx.y;
+    if (j >= T) return;
+    const uint8_t *base = data + offs[r];
+    const uint32_t data_bits = (offs[r + 1] - offs[r]) * 8u, chunk_bits = sync_chunk_bits(data_bits, T);
+    const ChunkRec *rec = recs + (size_t)r * T;
+    jd::SyncState s;
     if (j == 0) {
         s.pos = 0;
         s.blk = 0;
         s.k = 0;
     } else {
-        s = exit_state[j - 1];
+        s = rec[j - 1].st[final_round & 1];
     }
-    const int first = first_block[j];
-    jd::run_chunk<true>(hdr, tabs, nat, base, data_bits, s, limit, first, max_block, m_first, coef, co);
-    dc_off[j][0] = co.dc_sum[0];
-    dc_off[j][1] = co.dc_sum[1];
-    dc_off[j][2] = co.dc_sum[2];
-    __syncthreads();                           // (everybody has read its first_block)
-    first_block[j] = co.started;               // blocks actually written: they must add up to the interval's
-    __syncthreads();
-    if (j == 3 % T) {
-        int acc = 0;
-        for (int i = 0; i < T; ++i) acc += first_block[i];
-        if (acc != max_block) atomicAdd(not_converged, 1);
-    }
-    if (j < 3) {
-        int acc = 0;
-        for (int i = 0; i < T; ++i) {
-            const int n = dc_off[i][j];
-            dc_off[i][j] = acc;
-            acc += n;
-        }
-    }
-    __syncthreads();
-    // DC predictors of the blocks started in this chunk
-    int pred[3] = {dc_off[j][0], dc_off[j][1], dc_off[j][2]};
-    const int bw0 = jd::blocks_w(hdr, 0);
-    for (int bi = first; bi < first + co.started && bi < max_block; ++bi) {
-        const int sub = bi % nb, m = m_first + bi / nb, mx = m % hdr.mcus_x, my = m / hdr.mcus_x;
-        int16_t *cf;
-        int comp;
-        if (sub < nb - 2) {
-            comp = 0;
-            cf = c0 + 64 * ((size_t)(my * hdr.vs + sub / hdr.hs) * bw0 + (size_t)(mx * hdr.hs + sub % hdr.hs));
-        } else {
-            comp = sub - (nb - 2) + 1;
-            cf = (comp == 1 ? c1 : c2) + 64 * ((size_t)my * hdr.mcus_x + (size_t)mx);
-        }
-        pred[comp] += cf[0];
-        cf[0] = (int16_t)pred[comp];
-    }
+    const int total = sh.hdr.mcus_x * sh.hdr.mcus_y, m_first = r * dri, nb = sh.hdr.hs * sh.hdr.vs + 2;
+    const int max_block = min(dri, total - m_first) * nb;
+    jd::ChunkOut co;
+    co.dc_base[0] = rec[j].dc_sum[0];
+    co.dc_base[1] = rec[j].dc_sum[1];
+    co.dc_base[2] = rec[j].dc_sum[2];
+    int16_t *const coef[3] = {c0, c1, c2};
+    jd::run_chunk<true>(sh.hdr, sh.hdr.dc, sh.nat, base, data_bits, s, (uint32_t)(j + 1) * chunk_bits, rec[j].started, max_block, m_first, coef, co);
+    if (co.started) atomicAdd(written, co.started);
+}
+// flag[0] = chunks that changed in the last round, flag[1] = blocks written: both must be as expected.
+__global__ void jpeg_sync_check_kernel(const jd::Header *__restrict__ H, int *flag)
+{
+    const int expected = H->mcus_x * H->mcus_y * (H->hs * H->vs + 2);
+    flag[0] = (flag[0] != 0 || flag[1] != expected) ? 1 : 0;
 }
 
 // One thread per 8x8 block of any component: dequantise, inverse DCT, samples into the component's plane.
@@ -228,7 +230,9 @@ struct DevDec {
     uint32_t *h_offs = nullptr, *d_offs = nullptr;      // restart interval offsets
     int offs_cap = 0, n_intervals = 0;
     uint32_t clean_bytes = 0;                           // stuffing-free scan data in h_scan
-    int *h_flag = nullptr, *d_flag = nullptr;           // != 0 after the launch: the chunks did not synchronise (never seen)
+    int *h_flag = nullptr, *d_flag = nullptr;           // [0] != 0 after the launches: the chunks did not synchronise / a block is missing
+    ChunkRec *d_recs = nullptr;                         // one record per chunk
+    size_t recs_cap = 0;
     int16_t *d_coef = nullptr;                          // the three components' coefficient blocks, one allocation
     size_t coef_bytes[3] = {0, 0, 0};
     uint8_t *d_planes = nullptr;                        // the three components' sample planes, one allocation
@@ -357,6 +361,7 @@ void jpeg_lanes_destroy(JpegCtx *c)
         cudaFree(l.dev.d_coef);
         cudaFree(l.dev.d_planes);
         cudaFree(l.dev.d_flag);
+        cudaFree(l.dev.d_recs);
         cudaFreeHost(l.dev.h_flag);
         if (l.dec_stream) cudaStreamDestroy(l.dec_stream);
         if (l.dec_done) cudaEventDestroy(l.dec_done);
@@ -521,7 +526,7 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
     cudaError_t e = cudaSuccess;
     if (!d.d_hdr) e = cudaMalloc(reinterpret_cast<void **>(&d.d_hdr), sizeof(jd::Header));
     if (e == cudaSuccess && !d.d_flag) {
-        e = cudaMalloc(reinterpret_cast<void **>(&d.d_flag), sizeof(int));
+        e = cudaMalloc(reinterpret_cast<void **>(&d.d_flag), 2 * sizeof(int));
         if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&d.h_flag), sizeof(int), cudaHostAllocDefault);
         if (e == cudaSuccess) *d.h_flag = 0;
     }
@@ -582,22 +587,41 @@ int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cuda
     BS_CUDA(h, cudaMemcpyAsync(d.d_scan, d.h_scan, (size_t)d.clean_bytes + 8, cudaMemcpyHostToDevice, st));
     BS_CUDA(h, cudaMemcpyAsync(d.d_offs, d.h_offs, sizeof(uint32_t) * (size_t)(d.n_intervals + 1), cudaMemcpyHostToDevice, st));
     BS_CUDA(h, cudaMemsetAsync(d.d_coef, 0, d.coef_bytes[0] + d.coef_bytes[1] + d.coef_bytes[2], st));
-    BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, sizeof(int), st));
     int16_t *c0 = d.d_coef, *c1 = c0 + d.coef_bytes[0] / 2, *c2 = c1 + d.coef_bytes[1] / 2;
     uint8_t *p0 = d.d_planes, *p1 = p0 + d.plane_bytes[0], *p2 = p1 + d.plane_bytes[1];
-    // one block per interval, one thread per ~256 bytes of it (chunks that short still re-synchronise inside themselves)
+    // one thread per ~384 bytes of an interval (chunks that short usually re-synchronise inside themselves): a guess
+    // round, up to twelve rounds from the neighbours' states (photographs with long flat areas took five; settled
+    // chunks skip their round; the last round must change nothing), prefix sums, the write pass, the check
     const long total_mcus = (long)H.mcus_x * H.mcus_y;
     const int dri = H.dri > 0 ? H.dri : (int)total_mcus;
-    const uint32_t avg = d.clean_bytes / (uint32_t)d.n_intervals + 1;
-    int T = (int)((avg / 256u + 31u) / 32u * 32u);
-    T = T < 32 ? 32 : (T > 1024 ? 1024 : T);
-    jpeg_entropy_sync_kernel<<<d.n_intervals, T, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, d.n_intervals, dri, c0, c1, c2, d.d_flag);
+    uint32_t longest = 0;
+    for (int i = 0; i < d.n_intervals; ++i) longest = std::max(longest, d.h_offs[i + 1] - d.h_offs[i]);
+    const int T = (int)std::max<uint32_t>(1u, (longest + 383u) / 384u);
+    const size_t need = (size_t)T * (size_t)d.n_intervals;
+    if (d.recs_cap < need) {
+        BS_CUDA_QUIET(cudaStreamSynchronize(st));
+        cudaFree(d.d_recs);
+        d.d_recs = nullptr;
+        d.recs_cap = 0;
+        BS_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&d.d_recs), sizeof(ChunkRec) * need * 2));
+        d.recs_cap = need * 2;
+    }
+    constexpr int kRounds = 12;
+    BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, 2 * sizeof(int), st));
+    const dim3 grid((T + kSyncThreads - 1) / kSyncThreads, d.n_intervals);
+    for (int round = 0; round <= kRounds; ++round) {
+        if (round == kRounds) BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, sizeof(int), st));      // only the last round's changes count
+        jpeg_sync_round_kernel<<<grid, kSyncThreads, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, T, round, d.d_recs, d.d_flag);
+    }
+    jpeg_scan_kernel<<<d.n_intervals, 256, 0, st>>>(d.d_recs, T);
+    jpeg_sync_write_kernel<<<grid, kSyncThreads, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, T, kRounds, dri, d.d_recs, c0, c1, c2, d.d_flag + 1);
+    jpeg_sync_check_kernel<<<1, 1, 0, st>>>(d.d_hdr, d.d_flag);
     const int n_blocks = (int)((d.plane_bytes[0] + d.plane_bytes[1] + d.plane_bytes[2]) / 64);
     jpeg_idct_kernel<<<(n_blocks + 127) / 128, 128, 0, st>>>(d.d_hdr, c0, c1, c2, p0, p1, p2);
     jpeg_color_kernel<<<dim3(((H.w + 3) / 4 + 255) / 256, H.h), 256, 0, st>>>(d.d_hdr, p0, p1, p2, d_frame, pitch);
     BS_CUDA(h, cudaGetLastError());
     BS_CUDA(h, cudaMemcpyAsync(d.h_flag, d.d_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
-    h->kernel_launches += 3;
+    h->kernel_launches += 9;
     return BS_OK;
 }
 

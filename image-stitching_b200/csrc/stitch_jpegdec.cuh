@@ -466,7 +466,9 @@ JD_HD void cr_skip(CleanReader &b, int n)
 // What a pass over a chunk does besides following the symbols.
 struct ChunkOut {
     int started;             // blocks whose DC symbol lies in the chunk
-    int dc_sum[3];           // write pass: sum of the DC differences per component of the blocks started here
+    int dc_sum[3];           // sum of the DC differences per component of the blocks started here
+    int dc_base[3];          // in, write pass: DC predictor of each component at the chunk's entry (a block's DC
+                             // coefficient is dc_base + the running dc_sum)
 };
 
 // Decodes from state `s` up to the first symbol boundary at or behind bit `limit` (or the end of the data, or block
@@ -523,10 +525,10 @@ JD_HD SyncState run_chunk(const Header &H, const HuffTable *tabs, const uint8_t 
             }
             block_index = first_block + out.started;
             ++out.started;
+            out.dc_sum[comp] += diff;
             if (kWrite) {
                 cf = block_ptr(block_index, blk);
-                cf[0] = (int16_t)diff;
-                out.dc_sum[comp] += diff;
+                cf[0] = (int16_t)(out.dc_base[comp] + out.dc_sum[comp]);     // predictor so far + this difference (or the bare difference)
             }
             k = 1;
             continue;
@@ -611,32 +613,22 @@ inline int decode_interval_chunked_host(const Header &H, const HuffTable *tabs, 
         if (!changed) break;
         if (rounds > T + 2) break;
     }
-    int first = 0;
+    // prefix sums over the chunks: index of the first block started in a chunk, DC predictors at its entry
+    // (the counts and sums of the last, unchanged round are the true ones)
+    int first = 0, total_written = 0;
     int dc_off[3] = {0, 0, 0};
-    for (int j = 0; j < T; ++j) {                 // write pass + DC prefix (sequential here)
+    for (int j = 0; j < T; ++j) {
         SyncState s;
         if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
+        co.dc_base[0] = dc_off[0];
+        co.dc_base[1] = dc_off[1];
+        co.dc_base[2] = dc_off[2];
         run_chunk<true>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, first, max_block, m_first, coef, co);
-        // DC predictors of the blocks started in this chunk
-        int pred[3] = {dc_off[0], dc_off[1], dc_off[2]};
-        const int bw0 = blocks_w(H, 0);
-        for (int bi = first; bi < first + co.started && bi < max_block; ++bi) {
-            const int sub = bi % nb, m = m_first + bi / nb, mx = m % H.mcus_x, my = m / H.mcus_x;
-            int16_t *cf;
-            int comp;
-            if (sub < nb - 2) {
-                comp = 0;
-                cf = coef[0] + 64 * ((size_t)(my * H.vs + sub / H.hs) * bw0 + (size_t)(mx * H.hs + sub % H.hs));
-            } else {
-                comp = sub - (nb - 2) + 1;
-                cf = coef[comp] + 64 * ((size_t)my * H.mcus_x + (size_t)mx);
-            }
-            pred[comp] += cf[0];
-            cf[0] = (int16_t)pred[comp];
-        }
         for (int c = 0; c < 3; ++c) dc_off[c] += co.dc_sum[c];
-        first += co.started;
+        first += started[j];
+        total_written += co.started;
     }
+    first = total_written;
     delete[] exit_state;
     delete[] next_state;
     delete[] started;

@@ -15,6 +15,8 @@
 #include <new>
 #include <string>
 #include <vector>
+#include <chrono>
+#include <thread>
 
 #include <algorithm>
 
@@ -1232,6 +1234,18 @@ int bs_wait(bs_handle *h, int64_t ticket)
         return fail(h, rc, "%s", s.deferred_err);
     }
     if (!s.busy) return BS_OK;
+    // While this frame finishes, later compressed frames whose host stages complete go to the GPU (they would
+    // otherwise wait for the caller's next call): poll instead of blocking as long as such frames exist.
+    for (;;) {
+        bool later_deferred = false;
+        for (const Slot &o : h->ring) later_deferred = later_deferred || (o.deferred && o.ticket > ticket);
+        if (!later_deferred) break;
+        flush_deferred_jpeg(h, h->next_ticket - 1, true);
+        const cudaError_t q = cudaEventQuery(s.ev_done);
+        if (q == cudaSuccess) break;
+        if (q != cudaErrorNotReady) return fail(h, BS_ERR_CUDA, "bs_wait: %s", cudaGetErrorString(q));
+        std::this_thread::sleep_for(std::chrono::microseconds(50));
+    }
     BS_CUDA(h, cudaEventSynchronize(s.ev_done));
     s.busy = false;
     return retrieve_jpeg(h, s, (int)(ticket % kPipelineDepth));

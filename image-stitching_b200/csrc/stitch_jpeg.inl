@@ -589,14 +589,16 @@ int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cuda
     BS_CUDA(h, cudaMemsetAsync(d.d_coef, 0, d.coef_bytes[0] + d.coef_bytes[1] + d.coef_bytes[2], st));
     int16_t *c0 = d.d_coef, *c1 = c0 + d.coef_bytes[0] / 2, *c2 = c1 + d.coef_bytes[1] / 2;
     uint8_t *p0 = d.d_planes, *p1 = p0 + d.plane_bytes[0], *p2 = p1 + d.plane_bytes[1];
-    // one thread per ~384 bytes of an interval (chunks that short usually re-synchronise inside themselves): a guess
-    // round, up to twelve rounds from the neighbours' states (photographs with long flat areas took five; settled
-    // chunks skip their round; the last round must change nothing), prefix sums, the write pass, the check
+    // one thread per ~256 bytes of an interval (chunks that short usually re-synchronise inside themselves; shorter
+    // ones decode faster -- 192 bytes: +12 % -- but need more rounds): a guess round, up to twenty rounds from the
+    // neighbours' states (photographs with long flat areas took five; settled chunks skip their round; the last
+    // round must change nothing), prefix sums, the write pass, the check
     const long total_mcus = (long)H.mcus_x * H.mcus_y;
     const int dri = H.dri > 0 ? H.dri : (int)total_mcus;
     uint32_t longest = 0;
     for (int i = 0; i < d.n_intervals; ++i) longest = std::max(longest, d.h_offs[i + 1] - d.h_offs[i]);
-    const int T = (int)std::max<uint32_t>(1u, (longest + 383u) / 384u);
+    static const uint32_t chunk_bytes = getenv("BS_DEBUG_JPEG_CHUNK") ? (uint32_t)std::max(64, atoi(getenv("BS_DEBUG_JPEG_CHUNK"))) : 256u;   // experiment hook
+    const int T = (int)std::max<uint32_t>(1u, (longest + chunk_bytes - 1u) / chunk_bytes);
     const size_t need = (size_t)T * (size_t)d.n_intervals;
     if (d.recs_cap < need) {
         BS_CUDA_QUIET(cudaStreamSynchronize(st));
@@ -606,7 +608,7 @@ int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cuda
         BS_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&d.d_recs), sizeof(ChunkRec) * need * 2));
         d.recs_cap = need * 2;
     }
-    constexpr int kRounds = 12;
+    constexpr int kRounds = 20;
     BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, 2 * sizeof(int), st));
     const dim3 grid((T + kSyncThreads - 1) / kSyncThreads, d.n_intervals);
     for (int round = 0; round <= kRounds; ++round) {

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_round_kernel(const jd:
     int16_t *const none[3] = {nullptr, nullptr, nullptr};
     const jd::SyncState ns = jd::run_chunk<false>(sh.hdr, sh.hdr.dc, sh.nat, base, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, 0, none, co);
     const int moved = round == 0 || !jd::same(ns, rec[j].st[(round - 1) & 1]);
-    if (round > 0 && moved) atomicAdd(changed, 1);
+    if (round > 0 && moved) atomicAdd(changed + r, 1);
     rec[j].moved[round & 1] = moved;
     rec[j].st[round & 1] = ns;
     rec[j].started = co.started;
@@ -133,12 +133,12 @@ __global__ void __launch_bounds__(256) jpeg_scan_kernel(ChunkRec *recs, int T)
 __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_write_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ data,
                                                                       const uint32_t *__restrict__ offs, int T, int final_round, int dri,
                                                                       const ChunkRec *__restrict__ recs, int16_t *c0, int16_t *c1, int16_t *c2,
-                                                                      int *written)
+                                                                      int *written, const int *__restrict__ unsettled)
 {
     __shared__ SyncShared sh;
     sync_load_tables(sh, H);
     const int j = (int)(blockIdx.x * blockDim.x + threadIdx.x), r = (int)blockIdx.y;
-    if (j >= T) return;
+    if (j >= T || unsettled[r]) return;          // (an interval whose chunks still moved is decoded by jpeg_sync_serial_kernel)
     const uint8_t *base = data + offs[r];
     const uint32_t data_bits = (offs[r + 1] - offs[r]) * 8u, chunk_bits = sync_chunk_bits(data_bits, T);
     const ChunkRec *rec = recs + (size_t)r * T;
@@ -160,11 +160,34 @@ __global__ void __launch_bounds__(kSyncThreads) jpeg_sync_write_kernel(const jd:
     jd::run_chunk<true>(sh.hdr, sh.hdr.dc, sh.nat, base, data_bits, s, (uint32_t)(j + 1) * chunk_bits, rec[j].started, max_block, m_first, coef, co);
     if (co.started) atomicAdd(written, co.started);
 }
-// flag[0] = chunks that changed in the last round, flag[1] = blocks written: both must be as expected.
+// The way out for streams that do not re-synchronise (a long flat area is a periodic bit pattern that a decoder can
+// follow at the wrong phase for ever; the rounds then advance one chunk at a time): an interval whose chunks still
+// moved in the last round is decoded by ONE thread from its start.  Slow and rare; never wrong.
+__global__ void __launch_bounds__(32) jpeg_sync_serial_kernel(const jd::Header *__restrict__ H, const uint8_t *__restrict__ data,
+                                                             const uint32_t *__restrict__ offs, int n_intervals, int dri, int16_t *c0,
+                                                             int16_t *c1, int16_t *c2, int *written, const int *__restrict__ unsettled)
+{
+    __shared__ SyncShared sh;
+    sync_load_tables(sh, H);
+    const int r = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    if (r >= n_intervals || !unsettled[r]) return;
+    const int total = sh.hdr.mcus_x * sh.hdr.mcus_y, m_first = r * dri, nb = sh.hdr.hs * sh.hdr.vs + 2;
+    const uint32_t data_bits = (offs[r + 1] - offs[r]) * 8u;
+    jd::SyncState s;
+    s.pos = 0;
+    s.blk = 0;
+    s.k = 0;
+    jd::ChunkOut co;
+    co.dc_base[0] = co.dc_base[1] = co.dc_base[2] = 0;
+    int16_t *const coef[3] = {c0, c1, c2};
+    jd::run_chunk<true>(sh.hdr, sh.hdr.dc, sh.nat, data + offs[r], data_bits, s, data_bits, 0, min(dri, total - m_first) * nb, m_first, coef, co);
+    atomicAdd(written, co.started);
+}
+// flag[0] <- 1 unless every block of the frame was written (flag[1] counts them): the data is damaged.
 __global__ void jpeg_sync_check_kernel(const jd::Header *__restrict__ H, int *flag)
 {
     const int expected = H->mcus_x * H->mcus_y * (H->hs * H->vs + 2);
-    flag[0] = (flag[0] != 0 || flag[1] != expected) ? 1 : 0;
+    flag[0] = flag[1] != expected ? 1 : 0;
 }
 
 // One thread per 8x8 block of any component: dequantise, inverse DCT, samples into the component's plane.
@@ -526,7 +549,7 @@ bool devdec_prepare(bs_handle *h, JpegLane &l, int cam, const uint8_t *jpeg, siz
     cudaError_t e = cudaSuccess;
     if (!d.d_hdr) e = cudaMalloc(reinterpret_cast<void **>(&d.d_hdr), sizeof(jd::Header));
     if (e == cudaSuccess && !d.d_flag) {
-        e = cudaMalloc(reinterpret_cast<void **>(&d.d_flag), 2 * sizeof(int));
+        e = cudaMalloc(reinterpret_cast<void **>(&d.d_flag), 2 * sizeof(int));     // status, blocks written (per-interval counters live behind the chunk records)
         if (e == cudaSuccess) e = cudaHostAlloc(reinterpret_cast<void **>(&d.h_flag), sizeof(int), cudaHostAllocDefault);
         if (e == cudaSuccess) *d.h_flag = 0;
     }
@@ -589,17 +612,20 @@ int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cuda
     BS_CUDA(h, cudaMemsetAsync(d.d_coef, 0, d.coef_bytes[0] + d.coef_bytes[1] + d.coef_bytes[2], st));
     int16_t *c0 = d.d_coef, *c1 = c0 + d.coef_bytes[0] / 2, *c2 = c1 + d.coef_bytes[1] / 2;
     uint8_t *p0 = d.d_planes, *p1 = p0 + d.plane_bytes[0], *p2 = p1 + d.plane_bytes[1];
-    // one thread per ~256 bytes of an interval (chunks that short usually re-synchronise inside themselves; shorter
-    // ones decode faster -- 192 bytes: +12 % -- but need more rounds): a guess round, up to twenty rounds from the
-    // neighbours' states (photographs with long flat areas took five; settled chunks skip their round; the last
-    // round must change nothing), prefix sums, the write pass, the check
+    // a guess round, 24 rounds from the neighbours' states (settled chunks skip their round, so late rounds cost a
+    // launch; 200 random pictures of five kinds needed at most 21 with the chunk size below), prefix sums, the write
+    // pass for the intervals that settled, the one-thread pass for those that did not, the check
     const long total_mcus = (long)H.mcus_x * H.mcus_y;
     const int dri = H.dri > 0 ? H.dri : (int)total_mcus;
     uint32_t longest = 0;
     for (int i = 0; i < d.n_intervals; ++i) longest = std::max(longest, d.h_offs[i + 1] - d.h_offs[i]);
-    static const uint32_t chunk_bytes = getenv("BS_DEBUG_JPEG_CHUNK") ? (uint32_t)std::max(64, atoi(getenv("BS_DEBUG_JPEG_CHUNK"))) : 256u;   // experiment hook
+    // a chunk should hold enough BLOCKS to re-synchronise inside itself: 32 average blocks, at least 256 bytes
+    // (noise at high quality has 100-byte blocks, flat areas 1-byte blocks)
+    static const int env_chunk = getenv("BS_DEBUG_JPEG_CHUNK") ? std::max(64, atoi(getenv("BS_DEBUG_JPEG_CHUNK"))) : 0;   // experiment hook
+    const double avg_block = (double)d.clean_bytes / ((double)total_mcus * (H.hs * H.vs + 2));
+    const uint32_t chunk_bytes = env_chunk ? (uint32_t)env_chunk : (uint32_t)std::min(16384.0, std::max(256.0, 32.0 * avg_block));
     const int T = (int)std::max<uint32_t>(1u, (longest + chunk_bytes - 1u) / chunk_bytes);
-    const size_t need = (size_t)T * (size_t)d.n_intervals;
+    const size_t need = (size_t)T * (size_t)d.n_intervals + ((size_t)d.n_intervals * sizeof(int) + sizeof(ChunkRec) - 1) / sizeof(ChunkRec);
     if (d.recs_cap < need) {
         BS_CUDA_QUIET(cudaStreamSynchronize(st));
         cudaFree(d.d_recs);
@@ -608,15 +634,17 @@ int devdec_issue(bs_handle *h, JpegLane &l, uint8_t *d_frame, size_t pitch, cuda
         BS_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&d.d_recs), sizeof(ChunkRec) * need * 2));
         d.recs_cap = need * 2;
     }
-    constexpr int kRounds = 20;
+    int *unsettled = reinterpret_cast<int *>(d.d_recs + (size_t)T * (size_t)d.n_intervals);      // per interval: chunks that moved in the last round
+    constexpr int kRounds = 24;
     BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, 2 * sizeof(int), st));
     const dim3 grid((T + kSyncThreads - 1) / kSyncThreads, d.n_intervals);
     for (int round = 0; round <= kRounds; ++round) {
-        if (round == kRounds) BS_CUDA(h, cudaMemsetAsync(d.d_flag, 0, sizeof(int), st));      // only the last round's changes count
-        jpeg_sync_round_kernel<<<grid, kSyncThreads, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, T, round, d.d_recs, d.d_flag);
+        if (round == kRounds) BS_CUDA(h, cudaMemsetAsync(unsettled, 0, sizeof(int) * (size_t)d.n_intervals, st));    // only the last round's changes count
+        jpeg_sync_round_kernel<<<grid, kSyncThreads, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, T, round, d.d_recs, unsettled);
     }
     jpeg_scan_kernel<<<d.n_intervals, 256, 0, st>>>(d.d_recs, T);
-    jpeg_sync_write_kernel<<<grid, kSyncThreads, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, T, kRounds, dri, d.d_recs, c0, c1, c2, d.d_flag + 1);
+    jpeg_sync_write_kernel<<<grid, kSyncThreads, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, T, kRounds, dri, d.d_recs, c0, c1, c2, d.d_flag + 1, unsettled);
+    jpeg_sync_serial_kernel<<<(d.n_intervals + 31) / 32, 32, 0, st>>>(d.d_hdr, d.d_scan, d.d_offs, d.n_intervals, dri, c0, c1, c2, d.d_flag + 1, unsettled);
     jpeg_sync_check_kernel<<<1, 1, 0, st>>>(d.d_hdr, d.d_flag);
     const int n_blocks = (int)((d.plane_bytes[0] + d.plane_bytes[1] + d.plane_bytes[2]) / 64);
     jpeg_idct_kernel<<<(n_blocks + 127) / 128, 128, 0, st>>>(d.d_hdr, c0, c1, c2, p0, p1, p2);

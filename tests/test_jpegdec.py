@@ -145,3 +145,29 @@ def test_gpu_decoder_odd_sizes_444_and_mixed_streams():
                 else:
                     assert st.jpeg_backend().startswith("b200")
                     assert np.array_equal(out, ref)
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_on_streams_that_do_not_resynchronise():
+    """Flat pictures are periodic bit patterns: chunks can follow them at the wrong phase for ever, the rounds then move
+    one chunk at a time and the one-thread pass finishes the interval.  Noise at quality 100 has very long blocks.
+    Every picture must still come out as cv2.imdecode decodes it."""
+    p = pkg()
+    rng = np.random.default_rng(8)
+    w, h = 1280, 720
+    flat = np.zeros((h, w, 3), np.uint8)
+    flat[:] = (40, 90, 200)
+    disc = flat.copy()
+    cv2.circle(disc, (w // 2, h // 2), 200, (250, 20, 60), -1)
+    stripes = np.dstack([np.tile(np.linspace(0, 255, w).astype(np.uint8), (h, 1))] * 3)
+    stripes[::7] = 255 - stripes[::7]
+    noise = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    cases = [("flat", flat, 90, 0), ("disc", disc, 90, 0), ("disc, one MCU row per interval", disc, 90, 80), ("stripes", stripes, 75, 0),
+             ("noise q100", noise, 100, 0), ("noise q30", noise, 30, 40)]
+    with p.Stitcher([(w, h)], (w, h), [np.eye(3)]) as st:
+        out = np.empty((h, w, 3), np.uint8)
+        for name, img, q, rst in cases:
+            bits = encode(img, q, rst)
+            st.wait(st.submit_jpeg([bits], out))
+            assert st.jpeg_backend().startswith("b200"), name
+            assert np.array_equal(out, cv2.imdecode(np.frombuffer(bits, np.uint8), cv2.IMREAD_COLOR)), name

@@ -207,9 +207,9 @@ int bs_get_stats(const bs_handle *h, bs_stats *out);
  * holds the bitstream length after bs_wait(ticket) -- only the bitstream is copied from the device.  All
  * buffers (the bitstreams included), and *jout itself, must stay valid until bs_wait.  Decoded pixels are
  * nvJPEG's; they can differ by a unit or two from libjpeg's, as between any two JPEG decoders.
- * Frames that carry a restart interval (baseline, 4:2:0 or 4:4:4) are decoded by the library's own GPU decoder --
- * entropy decoding on the device, one restart interval per warp, libjpeg's arithmetic: the pixels equal
- * cv::imread's (libjpeg-turbo) bit for bit; all other JPEGs go through nvJPEG.
+ * Baseline JPEGs with three components sampled 4:2:0 or 4:4:4 (with or without restart markers) are decoded by the
+ * library's own GPU decoder -- entropy decoding on the device in self-synchronising chunks, libjpeg's arithmetic:
+ * the pixels equal cv::imread's (libjpeg-turbo) bit for bit; all other JPEGs go through nvJPEG.
  * bs_submit_jpeg checks the headers (a JPEG of the camera's frame size) and returns; the entropy (Huffman) stages
  * of the cameras then run on worker threads of the handle and the GPU side is issued when they are done, by the
  * next call that needs the frame (bs_wait of the ticket, a later submit, bs_sync) -- so the host stages of up to

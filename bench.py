@@ -508,9 +508,10 @@ def run_b200(args, rank, local_rank, world):
                                                              d_canvas[j % RING].cpu().numpy()))
 
     # ---- end to end with COMPRESSED frames: JPEG bitstreams up, decoded on the device (bs_submit_jpeg) ----
-    # Two records: plain JPEGs as cv2.imencode writes them (no restart interval: the entropy stage runs on the host,
-    # nvJPEG), and the same frames written with a restart interval of one MCU row (the entropy stage runs on the GPU,
-    # stitch_jpegdec.cuh, and the decoded pixels equal cv2.imdecode's).
+    # Two records: plain JPEGs as cv2.imencode writes them (no restart markers) and the same frames written with a
+    # restart interval of one MCU row.  Both are baseline 4:2:0, so both are decoded by the library's own GPU decoder
+    # (stitch_jpegdec.cuh: entropy stage on the GPU, pixels equal cv2.imdecode's); `decoder` in the record says which
+    # decoder ran (nvJPEG takes what that decoder does not: progressive, grey ...).
     e2e_jpeg = None
     e2e_jpeg_rst = None
     if not args.no_e2e and not args.no_compressed:

@@ -19,6 +19,7 @@ for w in cfg3 cfg2 cfg5; do python tools/traffic.py run $w > /dev/null 2>&1; don
 tools/prof_lens.sh $T
 python tools/feather_bench.py cfg3 > gpurun_out/${T}_feather_bench.json 2>/dev/null; python tools/feather_bench.py cfg2 >> gpurun_out/${T}_feather_bench.json 2>/dev/null
 python tools/copy_patterns.py > gpurun_out/${T}_copy_patterns.json 2>/dev/null
+tools/jpeg_launches.sh $T
 tail -2 gpurun_out/${T}_pytest.log; tail -1 gpurun_out/${T}_smoke.log
 python - <<PY
 import json

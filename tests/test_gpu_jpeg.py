@@ -1,9 +1,11 @@
 """Row f2 of SURVEY.md section 8: compressed frames in, compressed panorama out (bs_submit_jpeg), the device-side
-form of imread / imwrite at /root/reference/tools/stitch/main.cpp:107,114,125.  nvJPEG is the codec (libjpeg is the
-reference's); two JPEG decoders may differ by a unit or two per pixel, so the parity statement here is: the
-panorama made from compressed frames is BIT-EQUAL to the oracle applied to the pixels nvJPEG decodes (obtained
-through the same entry point with an identity homography); how far those pixels are from cv2's decode is reported
-and loosely bounded, not asserted as parity."""
+form of imread / imwrite at /root/reference/tools/stitch/main.cpp:107,114,125.  Baseline 4:2:0 / 4:4:4 JPEGs are
+decoded by the library's own GPU decoder, whose pixels equal cv2.imdecode's (tests/test_jpegdec.py pins that); other
+JPEGs, and the panorama encoder, are nvJPEG's, and two JPEG decoders may differ by a unit or two per pixel.  The
+parity statements here therefore come in two strengths: the panorama made from compressed frames is BIT-EQUAL to the
+oracle applied to the pixels the same entry point decodes (obtained with an identity homography) -- whatever the
+decoder -- and, for the fixtures (baseline 4:2:0), also to the oracle applied to cv2's decode, i.e. to the
+reference's own imread + warpPerspective."""
 import json
 import os
 

@@ -2,10 +2,9 @@
 //
 // Why: the reference decodes every frame on the host (cv::imread / cv::VideoCapture, tools/stitch/main.cpp:107,114,147),
 // and this image's nvJPEG does the same for its Huffman stage (~20 ms per 4K frame and core), which caps
-// bs_submit_jpeg far below what the link and the kernels can carry.  Huffman data is sequential -- except across
-// RESTART MARKERS: a JPEG written with a restart interval (DRI; every MJPEG camera pipeline and encoder can, e.g.
-// cv2.IMWRITE_JPEG_RST_INTERVAL, ffmpeg/libjpeg -restart) is a list of independent entropy segments.  Here one
-// thread decodes one restart interval; IDCT, chroma upsampling and colour conversion are one more kernel.
+// bs_submit_jpeg far below what the link and the kernels can carry.  Here the Huffman data is decoded on the device,
+// in parallel inside a scan (self-synchronising chunks, see "Parallel entropy decoding" below); inverse DCT, chroma
+// up-sampling and colour conversion are two more kernels (stitch_jpeg.inl).
 //
 // Arithmetic: libjpeg's, so that the pixels are what cv::imread yields (libjpeg-turbo, default settings): the
 // integer "islow" inverse DCT (jidctint.c), "fancy" h2v2 chroma upsampling (jdsample.c: the triangle filter with its
@@ -13,7 +12,7 @@
 // host build of these same functions against cv2.imdecode bit for bit.
 //
 // Supported: baseline sequential DCT (SOF0), 8 bit, three components with Y sampled 2x2 or 1x1 and chroma 1x1,
-// one interleaved scan, a restart interval.  Everything else is left to nvJPEG (stitch_jpeg.inl).
+// one interleaved scan, with or without a restart interval.  Everything else is left to nvJPEG (stitch_jpeg.inl).
 //
 // The functions below compile for the device and for the host (the CPU check of the decoder needs no GPU).
 #pragma once
@@ -191,37 +190,7 @@ inline bool parse_header(const uint8_t *d, size_t n, Header &H)
     return false;
 }
 
-// Byte offsets (relative to the scan data) where the restart intervals start; n_intervals + 1 entries.
-// Returns the number of intervals, or -1 when the markers do not add up to the MCU count.
-inline int find_intervals(const uint8_t *scan, size_t len, const Header &H, uint32_t *offs, int max_intervals)
-{
-    const long total = (long)H.mcus_x * H.mcus_y;
-    const int want = (int)((total + H.dri - 1) / H.dri);
-    if (want > max_intervals) return -1;
-    int n = 0;
-    offs[n++] = 0;
-    const uint8_t *p = scan, *end = scan + len;
-    while (n < want) {
-        p = static_cast<const uint8_t *>(memchr(p, 0xFF, (size_t)(end - p)));
-        if (!p || p + 1 >= end) return -1;
-        if (p[1] >= 0xD0 && p[1] <= 0xD7) {
-            if (p[1] != 0xD0 + ((n - 1) & 7)) return -1;
-            offs[n++] = (uint32_t)(p + 2 - scan);
-            p += 2;
-        } else {
-            p += (p[1] == 0x00) ? 2 : 1;
-        }
-    }
-    offs[n] = (uint32_t)len;
-    return want;
-}
-
-// ---- entropy decoding of one restart interval (host and device) -------------------------------------------
-struct BitReader {
-    const uint8_t *p, *end;
-    uint64_t buf;
-    int cnt;
-};
+// ---- entropy decoding (host and device) ------------------------------------------------------------------------
 JD_HD uint32_t br_byte(const uint8_t *p)
 {
 #ifdef __CUDA_ARCH__
@@ -230,142 +199,10 @@ JD_HD uint32_t br_byte(const uint8_t *p)
     return *p;
 #endif
 }
-// Four bytes at p (any alignment), first byte in the low bits.  The buffer has 8 spare bytes behind the data.
-JD_HD uint32_t br_word(const uint8_t *p)
-{
-#ifdef __CUDA_ARCH__
-    const uintptr_t a = reinterpret_cast<uintptr_t>(p);
-    const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~(uintptr_t)3);
-    return __funnelshift_r(__ldg(wp), __ldg(wp + 1), 8u * (uint32_t)(a & 3));
-#else
-    uint32_t v;
-    memcpy(&v, p, 4);
-    return v;
-#endif
-}
-JD_HD void br_fill(BitReader &b)
-{
-    // four bytes at once while none of them is 0xFF (no stuffing, no marker): the common case
-    if (b.cnt <= 32 && b.p + 4 <= b.end) {
-        const uint32_t v = br_word(b.p);
-        if ((((~v) - 0x01010101u) & v & 0x80808080u) == 0) {
-#ifdef __CUDA_ARCH__
-            const uint32_t be = __byte_perm(v, 0, 0x0123);
-#else
-            const uint32_t be = __builtin_bswap32(v);
-#endif
-            b.buf |= (uint64_t)be << (32 - b.cnt);
-            b.cnt += 32;
-            b.p += 4;
-            return;
-        }
-    }
-    while (b.cnt <= 56) {
-        uint32_t byte = 0;
-        if (b.p < b.end) {
-            byte = br_byte(b.p++);
-            if (byte == 0xFF) {
-                if (b.p < b.end && br_byte(b.p) == 0x00) ++b.p;  // stuffed zero
-                else { b.p = b.end; byte = 0; }                  // a marker: the segment ends here, pad with zeros
-            }
-        }
-        b.buf |= (uint64_t)byte << (56 - b.cnt);
-        b.cnt += 8;
-    }
-}
-JD_HD uint32_t br_peek(const BitReader &b, int n) { return (uint32_t)(b.buf >> (64 - n)); }
-JD_HD void br_skip(BitReader &b, int n)
-{
-    b.buf <<= n;
-    b.cnt -= n;
-}
-JD_HD int huff_decode(BitReader &b, const HuffTable &t)
-{
-    if (b.cnt < 16) br_fill(b);
-    const uint32_t e = t.look[br_peek(b, 9)];
-    if (e) {
-        br_skip(b, (int)(e >> 8));
-        return (int)(e & 0xFF);
-    }
-    const uint32_t c16 = br_peek(b, 16);
-    int l = 10;
-    while (l <= 16 && (int)(c16 >> (16 - l)) > t.maxcode[l]) ++l;
-    if (l > 16) return 0;                                        // corrupt data: keep going with zeros
-    br_skip(b, l);
-    return t.vals[((int)(c16 >> (16 - l)) + t.valoff[l]) & 0xFF];
-}
-JD_HD int receive_extend(BitReader &b, int s)
-{
-    if (b.cnt < s) br_fill(b);
-    const int v = (int)br_peek(b, s);
-    br_skip(b, s);
-    return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v;
-}
-
-// One 8x8 block: quantised coefficients into `coef` (natural order; the caller zeroed it).  `nat` = the zig-zag ->
-// natural-order table (the kernels keep a copy in shared memory).
-JD_HD void decode_block(BitReader &b, const HuffTable &dc, const HuffTable &ac, int &pred, int16_t *coef, const uint8_t *nat)
-{
-    int s = huff_decode(b, dc);
-    if (s) pred += receive_extend(b, s & 15);
-    coef[0] = (int16_t)pred;
-    for (int k = 1; k < 64; ++k) {
-        if (b.cnt < 16) br_fill(b);
-        const int f = ac.fast[br_peek(b, 9)];
-        if (f) {                                             // code and magnitude in one look-up
-            k += (f >> 4) & 15;
-            br_skip(b, f & 15);
-            if (k < 64) coef[nat[k]] = (int16_t)(f >> 8);
-            continue;
-        }
-        const int rs = huff_decode(b, ac);
-        const int r = rs >> 4;
-        s = rs & 15;
-        if (s) {
-            k += r;
-            const int v = receive_extend(b, s);
-            if (k < 64) coef[nat[k]] = (int16_t)v;
-        } else {
-            if (r != 15) break;
-            k += 15;
-        }
-    }
-}
 
 // Where component c keeps its coefficient blocks: `blocks_w(c)` blocks per row, padded to whole MCUs.
 JD_HD int blocks_w(const Header &H, int c) { return H.mcus_x * (c == 0 ? H.hs : 1); }
 JD_HD int blocks_h(const Header &H, int c) { return H.mcus_y * (c == 0 ? H.vs : 1); }
-
-// Restart interval `r`: MCUs [r * dri, ...).  coef[c] = that component's block array (64 int16 per block);
-// `tabs` = the four Huffman tables (dc0, dc1, ac0, ac1) and `nat` the natural-order table, wherever they are fastest.
-JD_HD void decode_interval(const Header &H, const HuffTable *tabs, const uint8_t *nat, const uint8_t *scan, const uint32_t *offs, int r,
-                           int16_t *const coef[3])
-{
-    BitReader b;
-    b.p = scan + offs[r];
-    b.end = scan + offs[r + 1];
-    b.buf = 0;
-    b.cnt = 0;
-    int pred0 = 0, pred1 = 0, pred2 = 0;
-    const int bw0 = blocks_w(H, 0);
-    const int total = H.mcus_x * H.mcus_y;                   // (< 2^24: dimensions are 16-bit)
-    const int m0 = r * H.dri, m1 = (m0 + H.dri < total) ? m0 + H.dri : total;
-    int mx = m0 % H.mcus_x, my = m0 / H.mcus_x;
-    for (int m = m0; m < m1; ++m, ++mx) {
-        if (mx == H.mcus_x) {
-            mx = 0;
-            ++my;
-        }
-        // luma blocks of the MCU, then one Cb and one Cr block (predictors and pointers stay in registers)
-        for (int v = 0; v < H.vs; ++v)
-            for (int u = 0; u < H.hs; ++u)
-                decode_block(b, tabs[H.dc_tab[0]], tabs[2 + H.ac_tab[0]], pred0,
-                             coef[0] + 64 * ((size_t)(my * H.vs + v) * bw0 + (size_t)(mx * H.hs + u)), nat);
-        const size_t cblk = 64 * ((size_t)my * H.mcus_x + (size_t)mx);
-        decode_block(b, tabs[H.dc_tab[1]], tabs[2 + H.ac_tab[1]], pred1, coef[1] + cblk, nat);
-        decode_block(b, tabs[H.dc_tab[2]], tabs[2 + H.ac_tab[2]], pred2, coef[2] + cblk, nat);
-    }
-}
 
 // ============================================================================================================
 // Parallel entropy decoding INSIDE a restart interval (or inside a whole scan without restart markers).
@@ -578,61 +415,6 @@ JD_HD SyncState run_chunk(const Header &H, const HuffTable *tabs, const uint8_t 
     o.blk = (int16_t)blk;
     o.k = (int16_t)k;
     return o;
-}
-
-// Host model of the kernel (one "thread" after the other): decodes interval [m_first, m_first + n_mcus) from `data`
-// with `T` chunks.  Used by the CPU check; the kernel in stitch_jpeg.inl has the same steps with barriers in between.
-inline int decode_interval_chunked_host(const Header &H, const HuffTable *tabs, const uint8_t *nat, const uint8_t *data, uint32_t bytes, int T,
-                                        int m_first, int n_mcus, int16_t *const coef[3])
-{
-    const int nb = H.hs * H.vs + 2, max_block = n_mcus * nb;
-    const uint32_t data_bits = bytes * 8u;
-    uint32_t chunk_bits = ((data_bits + (uint32_t)T - 1) / (uint32_t)T + 7u) & ~7u;
-    if (chunk_bits < 64) chunk_bits = 64;
-    SyncState *exit_state = new SyncState[T], *next_state = new SyncState[T];
-    int *started = new int[T];
-    ChunkOut co;
-    for (int j = 0; j < T; ++j) {                 // round 0: guesses
-        SyncState s;
-        s.pos = (uint32_t)j * chunk_bits;
-        s.blk = 0;
-        s.k = 0;
-        exit_state[j] = run_chunk<false>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, m_first, coef, co);
-    }
-    int rounds = 1;
-    for (;; ++rounds) {
-        bool changed = false;
-        for (int j = 0; j < T; ++j) {
-            SyncState s;
-            if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
-            next_state[j] = run_chunk<false>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, m_first, coef, co);
-            started[j] = co.started;
-            changed = changed || !same(next_state[j], exit_state[j]);
-        }
-        for (int j = 0; j < T; ++j) exit_state[j] = next_state[j];
-        if (!changed) break;
-        if (rounds > T + 2) break;
-    }
-    // prefix sums over the chunks: index of the first block started in a chunk, DC predictors at its entry
-    // (the counts and sums of the last, unchanged round are the true ones)
-    int first = 0, total_written = 0;
-    int dc_off[3] = {0, 0, 0};
-    for (int j = 0; j < T; ++j) {
-        SyncState s;
-        if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
-        co.dc_base[0] = dc_off[0];
-        co.dc_base[1] = dc_off[1];
-        co.dc_base[2] = dc_off[2];
-        run_chunk<true>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, first, max_block, m_first, coef, co);
-        for (int c = 0; c < 3; ++c) dc_off[c] += co.dc_sum[c];
-        first += started[j];
-        total_written += co.started;
-    }
-    first = total_written;
-    delete[] exit_state;
-    delete[] next_state;
-    delete[] started;
-    return first == max_block ? rounds : -rounds;
 }
 
 // ---- inverse DCT: libjpeg's jpeg_idct_islow (jidctint.c), 13-bit constants, two passes -----------------------

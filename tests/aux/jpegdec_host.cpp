@@ -9,6 +9,65 @@
 
 #include "../../image-stitching_b200/csrc/stitch_jpegdec.cuh"
 
+namespace jd {
+// Host model of the kernels' rounds (one "thread" after the other): decodes interval [m_first, m_first + n_mcus) from
+// `data` with `T` chunks, calling the product's run_chunk; the kernels in stitch_jpeg.inl run the same steps, one launch
+// per round.  Test infrastructure: it lives here, not in the product header.
+static int decode_interval_chunked_host(const Header &H, const HuffTable *tabs, const uint8_t *nat, const uint8_t *data, uint32_t bytes, int T,
+                                        int m_first, int n_mcus, int16_t *const coef[3])
+{
+    const int nb = H.hs * H.vs + 2, max_block = n_mcus * nb;
+    const uint32_t data_bits = bytes * 8u;
+    uint32_t chunk_bits = ((data_bits + (uint32_t)T - 1) / (uint32_t)T + 7u) & ~7u;
+    if (chunk_bits < 64) chunk_bits = 64;
+    SyncState *exit_state = new SyncState[T], *next_state = new SyncState[T];
+    int *started = new int[T];
+    ChunkOut co;
+    for (int j = 0; j < T; ++j) {                 // round 0: guesses
+        SyncState s;
+        s.pos = (uint32_t)j * chunk_bits;
+        s.blk = 0;
+        s.k = 0;
+        exit_state[j] = run_chunk<false>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, m_first, coef, co);
+    }
+    int rounds = 1;
+    for (;; ++rounds) {
+        bool changed = false;
+        for (int j = 0; j < T; ++j) {
+            SyncState s;
+            if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
+            next_state[j] = run_chunk<false>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, 0, 0x7fffffff, m_first, coef, co);
+            started[j] = co.started;
+            changed = changed || !same(next_state[j], exit_state[j]);
+        }
+        for (int j = 0; j < T; ++j) exit_state[j] = next_state[j];
+        if (!changed) break;
+        if (rounds > T + 2) break;
+    }
+    // prefix sums over the chunks: index of the first block started in a chunk, DC predictors at its entry
+    // (the counts and sums of the last, unchanged round are the true ones)
+    int first = 0, total_written = 0;
+    int dc_off[3] = {0, 0, 0};
+    for (int j = 0; j < T; ++j) {
+        SyncState s;
+        if (j == 0) { s.pos = 0; s.blk = 0; s.k = 0; } else s = exit_state[j - 1];
+        co.dc_base[0] = dc_off[0];
+        co.dc_base[1] = dc_off[1];
+        co.dc_base[2] = dc_off[2];
+        run_chunk<true>(H, tabs, nat, data, data_bits, s, (uint32_t)(j + 1) * chunk_bits, first, max_block, m_first, coef, co);
+        for (int c = 0; c < 3; ++c) dc_off[c] += co.dc_sum[c];
+        first += started[j];
+        total_written += co.started;
+    }
+    first = total_written;
+    delete[] exit_state;
+    delete[] next_state;
+    delete[] started;
+    return first == max_block ? rounds : -rounds;
+}
+
+}  // namespace jd
+
 int main(int argc, char **argv)
 {
     if (argc < 3) return 1;
@@ -20,7 +79,7 @@ int main(int argc, char **argv)
     jd::Header H;
     if (!jd::parse_header(d.data(), d.size(), H)) return 2;
     const long total = (long)H.mcus_x * H.mcus_y;
-    const int chunks = argc > 3 ? atoi(argv[3]) : 0;        // 0: one thread per restart interval; T > 0: T chunks per interval
+    const int chunks = argc > 3 && atoi(argv[3]) > 0 ? atoi(argv[3]) : 1;        // chunks per interval (1: the sequential decode)
     const int max_iv = H.dri > 0 ? (int)((total + H.dri - 1) / H.dri) : 1;
     std::vector<uint32_t> offs(max_iv + 1);
     std::vector<int16_t> coef[3];
@@ -31,7 +90,7 @@ int main(int argc, char **argv)
     }
     const jd::HuffTable tabs[4] = {H.dc[0], H.dc[1], H.ac[0], H.ac[1]};
     int n_iv = 0, worst_rounds = 0;
-    if (chunks > 0) {
+    {
         std::vector<uint8_t> clean(H.scan_len + 16);
         n_iv = jd::unstuff_scan(d.data() + H.scan_off, H.scan_len, H, clean.data(), offs.data(), max_iv);
         if (n_iv < 0) return 2;
@@ -42,11 +101,6 @@ int main(int argc, char **argv)
             if (rounds < 0) { fprintf(stderr, "interval %d: block count mismatch after %d rounds\n", r, -rounds); return 3; }
             worst_rounds = std::max(worst_rounds, rounds);
         }
-    } else {
-        if (H.dri < 1) return 2;
-        n_iv = jd::find_intervals(d.data() + H.scan_off, H.scan_len, H, offs.data(), max_iv);
-        if (n_iv < 0) return 2;
-        for (int r = 0; r < n_iv; ++r) jd::decode_interval(H, tabs, jd::kNaturalHost, d.data() + H.scan_off, offs.data(), r, cp);
     }
     std::vector<uint8_t> plane[3];
     size_t pitch[3];

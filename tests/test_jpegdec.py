@@ -44,8 +44,8 @@ def host_decoder(tmp_path_factory):
 
 
 def host_decode(exe, bits, tmp_path, chunks=0):
-    """chunks = 0: one thread per restart interval; T > 0: the chunked, self-synchronising decoder with T chunks per
-    interval (what the kernel runs; files without restart markers are one interval)."""
+    """chunks = T chunks per interval of the self-synchronising decoder the kernels run (files without restart markers
+    are one interval); 0 or 1: one chunk, i.e. the sequential decode."""
     src, dst = tmp_path / "in.jpg", tmp_path / "out.bgr"
     src.write_bytes(bits)
     r = subprocess.run([exe, str(src), str(dst)] + ([str(chunks)] if chunks else []), capture_output=True, text=True)

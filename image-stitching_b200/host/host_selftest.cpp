@@ -90,5 +90,22 @@ int main(int argc, char **argv) {
     std::cout << im.w << " " << im.h << std::endl;
     return 0;
   }
+  if (cmd == "mjpeg" && argc >= 3) {
+    // the frames of a Motion-JPEG stream as the stitch tool sees them: "offset bytes width height" per frame
+    bsio::JpegStream st;
+    if (!st.open(argv[2])) {
+      std::cout << "open failed" << std::endl;
+      return 2;
+    }
+    const uint8_t *f = nullptr, *first = nullptr;
+    size_t n = 0;
+    while (st.next(&f, &n)) {
+      if (!first) first = f;
+      int w = 0, h = 0;
+      const bool ok = bsio::jpeg_size(f, n, &w, &h);
+      std::cout << (f - first) << " " << n << " " << (ok ? w : -1) << " " << (ok ? h : -1) << std::endl;
+    }
+    return 0;
+  }
   return 64;
 }

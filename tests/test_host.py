@@ -371,3 +371,35 @@ def test_stitch_tool_video_mode_from_motion_jpeg(tmp_path):
         mse = float(((back.astype(float) - wants[k].astype(float)) ** 2).mean())
         assert back.shape == wants[k].shape and 10 * np.log10(255.0 ** 2 / max(mse, 1e-9)) > 30.0
     assert not os.path.exists(tmp_path / "enc_003.jpg")
+
+
+def test_motion_jpeg_stream_is_split_at_frame_boundaries(tmp_path):
+    """The stitch tool's view of a .mjpeg file (host/image_io.cpp JpegStream + jpeg_size): frames with and without
+    restart markers, stuffed 0xFF bytes in the entropy data, an APP segment that contains 0xFFD9, padding between
+    frames, a truncated last frame."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(2)
+    frames = []
+    for k, (w, h) in enumerate([(160, 96), (333, 200), (64, 48)]):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)          # noise: plenty of 0xFF 0x00 in the scan
+        args = [cv2.IMWRITE_JPEG_QUALITY, 95] + ([cv2.IMWRITE_JPEG_RST_INTERVAL, 3] if k == 1 else [])
+        bits = cv2.imencode(".jpg", img, args)[1].tobytes()
+        assert b"\xff\x00" in bits
+        if k == 2:                                                       # an application segment holding an EOI look-alike
+            bits = bits[:2] + b"\xff\xe1\x00\x08ab\xff\xd9cd" + bits[2:]
+        frames.append((bits, w, h))
+    path = tmp_path / "s.mjpeg"
+    with open(path, "wb") as f:
+        off, want = 0, []
+        for k, (bits, w, h) in enumerate(frames):
+            pad = b"\x00" * (3 * k)
+            f.write(pad + bits)
+            if k == 0:
+                first = len(pad)
+            want.append((off + len(pad) - first, len(bits), w, h))
+            off += len(pad) + len(bits)
+        f.write(frames[0][0][:500])                                      # truncated frame at the end: not reported
+    r = subprocess.run([SELFTEST, "mjpeg", str(path)], capture_output=True, text=True)
+    assert r.returncode == 0
+    got = [tuple(int(v) for v in ln.split()) for ln in r.stdout.strip().splitlines()]
+    assert got == want

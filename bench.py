@@ -541,6 +541,14 @@ def run_b200(args, rank, local_rank, world):
                     for t in tickets[-depth:]:
                         st.wait(t)
                 jpeg_frames(4)
+                # parity of the compressed path (rank 0, untimed): the panorama from the bitstreams must equal the panorama the
+                # raw entry point makes from the pixels cv2.imdecode (the reference's imread) gives for the same bitstreams
+                same = None
+                if rank == 0:
+                    chk = pkg.pinned_empty((H, W, 3))
+                    st.wait(st.submit_jpeg(jf[0], chk))
+                    dec = [np.ascontiguousarray(cv2.imdecode(b, cv2.IMREAD_COLOR)) for b in jf[0]]
+                    same = bool(np.array_equal(chk, st.stitch(dec)))
                 nj = max(8, min(48, args.steps * 2))
                 barrier()
                 t0 = time.perf_counter()
@@ -550,7 +558,7 @@ def run_b200(args, rank, local_rank, world):
                 barrier()
                 js = max_over_ranks(t1 - t0)
                 return {"value": world * nj / js, "unit": UNIT, "h2d_bytes_per_frame": jbytes, "d2h_bytes_per_frame": w.canvas_bytes,
-                        "frames": nj, "restart_interval_mcus": rst,
+                        "frames": nj, "restart_interval_mcus": rst, "equals_raw_path_on_cv2_imdecode_pixels": same,
                         "content": "smooth ramp + 3 bits of texture, JPEG quality 90, 4:2:0 (cv2.imencode)",
                         "decoder": f"{st.jpeg_backend()}; into the device frame ring (bs_submit_jpeg), panorama returned raw",
                         "raw_h2d_bytes_per_frame_for_comparison": h2d_per_frame if e2e else None}

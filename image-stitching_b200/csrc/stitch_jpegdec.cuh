@@ -433,7 +433,7 @@ JD_HD void idct_islow(const int16_t *coef, const uint16_t *q, uint8_t *out, size
         int tmp2 = z1 + z3 * (-F1_847), tmp3 = z1 + z2 * F0_765;
         z2 = coef[x] * q[x];
         z3 = coef[32 + x] * q[32 + x];
-        int tmp0 = (z2 + z3) << C, tmp1 = (z2 - z3) << C;
+        int tmp0 = (z2 + z3) * (1 << C), tmp1 = (z2 - z3) * (1 << C);      // (a multiplication: the sums may be negative)
         const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
         tmp0 = coef[56 + x] * q[56 + x];
         tmp1 = coef[40 + x] * q[40 + x];
@@ -470,7 +470,7 @@ JD_HD void idct_islow(const int16_t *coef, const uint16_t *q, uint8_t *out, size
         int z2 = w[2], z3 = w[6];
         int z1 = (z2 + z3) * F0_541;
         int tmp2 = z1 + z3 * (-F1_847), tmp3 = z1 + z2 * F0_765;
-        int tmp0 = (w[0] + w[4]) << C, tmp1 = (w[0] - w[4]) << C;
+        int tmp0 = (w[0] + w[4]) * (1 << C), tmp1 = (w[0] - w[4]) * (1 << C);
         const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
         tmp0 = w[7];
         tmp1 = w[5];
